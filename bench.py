@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""Benchmark of the WOFT per-frame hot path on B200: tracked frames/s at 1280x720.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl woft|reference] [--corr-mode tf32|tf32x3|bf16|fp32]
+
+A step is one tracked frame of BASELINE.json configs[1]: one WeightedRAFT flow + uncertainty pass on a synthetic
+1280x720 frame pair (160x90x256 feature maps, 12 GRU iterations, 13 correlation lookups), the correspondence
+mask, the 500-point Sobol pick, the weighted homography fit and the inlier test.
+  value      frames/s over all ranks with the frames already resident in HBM (uint8), nothing copied to the host
+  e2e        frames/s through the public API (PlanarTracker.track on host uint8 frames): host pre-warp, pinned
+             H2D upload of both frames, the device path, D2H of the 3x3 homography and of the success flag
+  roofline   the correlation lookup (K3), the kernel BASELINE.json's metric names, timed alone with CUDA events on
+             its launch stream with L2 flushed between launches; `kernels` adds K1+K2 and K4 the same way
+  cpu_baseline / --impl reference: the oracle port of the reference's CPU path on this box's host cores
+Under torchrun each rank tracks its own synthetic sequence (weak scaling, no data-path collective); times are
+taken on the device and reduced with MAX over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+from types import SimpleNamespace
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+HEIGHT, WIDTH, ITERS = 720, 1280, 12
+METRIC = "tracked frames/s @1280x720"
+LOOKUP_BYTES_PER_QUERY = 4 * 10 * 10 * 4 + 8 + 324 * 4  # 2904 B per query pixel per call
+
+
+def make_sequence(n_frames, seed):
+    """Smooth textured base frame and `n_frames` warps of it by a small random-walk homography (BGR uint8)."""
+    import cv2
+    rng = np.random.RandomState(seed)
+    base = rng.randint(0, 256, (HEIGHT // 8, WIDTH // 8, 3)).astype(np.uint8)
+    base = cv2.resize(base, (WIDTH, HEIGHT), interpolation=cv2.INTER_CUBIC)
+    frames, H = [], np.eye(3)
+    for _ in range(n_frames):
+        step = np.eye(3)
+        step[:2, :2] += rng.randn(2, 2) * 2e-3
+        step[:2, 2] += rng.randn(2) * 1.5
+        step[2, :2] += rng.randn(2) * 2e-6
+        H = step @ H
+        frames.append(cv2.warpPerspective(base, H, (WIDTH, HEIGHT), flags=cv2.INTER_LINEAR,
+                                          borderMode=cv2.BORDER_REFLECT))
+    mask = np.zeros((HEIGHT, WIDTH), np.uint8)
+    mask[200:520, 400:880] = 255  # fixed rectangular init mask in place of the interactive ROI
+    return base, frames, mask
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while a timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.25)
+            self.proc.terminate()
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def dist_setup(args):
+    import torch
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        import torch.distributed as dist
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29511")
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", rank=rank, world_size=world)
+    return rank, world, local
+
+
+def barrier():
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized():
+        dist.barrier()
+
+
+def flush_l2(scratch):
+    scratch.zero_()  # 256 MiB > 126 MB L2
+
+
+def time_launches(fn, n, scratch, torch):
+    """Average device time (s) of `fn()` over n launches, each bracketed by its own event pair on the launch stream,
+    L2 flushed before each."""
+    total = 0.0
+    for i in range(n + 3):
+        flush_l2(scratch)
+        torch.cuda._sleep(400_000)  # ~0.2 ms of device-side delay so the host has enqueued fn() before `a` fires
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        if i >= 3:
+            total += a.elapsed_time(b) * 1e-3
+    return total / n
+
+
+def kernel_rooflines(torch, dev, corr_mode, peaks):
+    """K3 (the headline), K1+K2 and K4 timed alone at BASELINE config sizes."""
+    from woft_b200 import least_squares_H as lsq
+    from woft_b200.corr import CorrBlock
+    scratch = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    g = torch.Generator(device=dev).manual_seed(0)
+    B, C, H, W = 1, 256, HEIGHT // 8, WIDTH // 8
+    f1 = torch.randn((B, C, H, W), generator=g, device=dev)
+    f2 = torch.randn((B, C, H, W), generator=g, device=dev)
+    holder = {}
+
+    def build():
+        holder["blk"] = CorrBlock(f1, f2, mode=corr_mode)
+
+    t_build = time_launches(build, 5, scratch, torch)
+    blk = holder["blk"]
+    blk.check()
+    level_bytes = sum(l.numel() * 4 for l in blk.corr_pyramid)
+    corr_bytes = 2 * f1.numel() * 4 + level_bytes
+    ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W, device=dev), indexing="ij")
+    coords = torch.stack([xs, ys]).float()[None] + torch.randn((1, 2, H, W), generator=g, device=dev) * 2.0
+    t_lookup = time_launches(lambda: blk(coords), 20, scratch, torch)
+    lookup_bytes = LOOKUP_BYTES_PER_QUERY * B * H * W
+
+    Bh, Nh = 1024, 14400  # BASELINE config 3
+    p1 = torch.rand((Bh, Nh, 2), generator=g, device=dev) * torch.tensor([1280.0, 720.0], device=dev)
+    p2 = p1 + torch.randn((Bh, Nh, 2), generator=g, device=dev)
+    w = torch.rand((Bh, Nh), generator=g, device=dev)
+    t_h = time_launches(lambda: lsq.find_homography_nonhomogeneous_QR(p1, p2, w), 5, scratch, torch)
+    h_bytes = Bh * Nh * 20 + Bh * 36
+    del scratch
+    hbm = peaks["hbm_gbs"]
+
+    def entry(bytes_, t):
+        a = bytes_ / t / 1e9
+        return {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
+                "traffic": None, "us_per_launch": round(t * 1e6, 2), "algorithmic_bytes": bytes_}
+
+    k3 = entry(lookup_bytes, t_lookup)
+    k3["kernel"] = "corr_lookup_kernel<4> (K3), 14400 queries x 4 levels, L2 flushed before every launch"
+    k1 = entry(corr_bytes, t_build)
+    k1["kernel"] = f"pack + corr_tc_kernel + row-mean (K1+K2), mode {corr_mode}; 106.2 GFLOP"
+    k1["tflops"] = round(2.0 * (H * W) ** 2 * C / t_build / 1e12, 1)
+    k4 = entry(h_bytes, t_h)
+    k4["kernel"] = "homography_fit_kernel (K4), B=1024 x N=14400, nonhomogeneous"
+    return k3, {"corr_pyramid": k1, "homography_fit_config3": k4}, peaks["source"]
+
+
+def load_peaks():
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        p = json.loads(f.read_text())
+        return {"hbm_gbs": float(p["hbm_gbs"]), "bf16_tflops": float(p["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "source": "fallback"}
+
+
+def cpu_frame_seconds(n_frames, seed=0):
+    """Oracle port of the reference's CPU path: seconds per tracked frame on the host cores."""
+    import torch
+    from oracle import cpu_pipeline
+    torch.set_num_threads(os.cpu_count() or 1)
+    net = cpu_pipeline.make_net(seed)
+    base, frames, mask = make_sequence(max(n_frames, 1), seed)
+    times = []
+    for i in range(n_frames):
+        t0 = time.perf_counter()
+        cpu_pipeline.track_frame(net, base, frames[i], mask, np.eye(3), ITERS)
+        times.append(time.perf_counter() - t0)
+    return times, torch.get_num_threads()
+
+
+def run_reference(args, rank, world):
+    """`--impl reference`: the reference's CPU implementation of the path (oracle port; the Python reference cannot
+    travel to the GPU box) on the host cores.  Rank 0 alone works."""
+    if rank != 0:
+        return
+    budget = float(os.environ.get("WOFT_REF_MAX_SECONDS", "240"))
+    import torch
+    from oracle import cpu_pipeline
+    torch.set_num_threads(os.cpu_count() or 1)
+    net = cpu_pipeline.make_net(0)
+    base, frames, mask = make_sequence(8, 0)
+    t_start = time.perf_counter()
+    warm = 0
+    for i in range(args.warmup):
+        cpu_pipeline.track_frame(net, base, frames[i % 8], mask, np.eye(3), ITERS)
+        warm += 1
+        if time.perf_counter() - t_start > budget / 3:
+            break
+    done, t0 = 0, time.perf_counter()
+    for i in range(args.steps):
+        cpu_pipeline.track_frame(net, base, frames[i % 8], mask, np.eye(3), ITERS)
+        done += 1
+        if time.perf_counter() - t_start > budget:
+            break
+    dt = time.perf_counter() - t0
+    fps = done / dt
+    cores = torch.get_num_threads()
+    sample = (f"{done} full 1280x720 frames ({ITERS} iters) per the oracle port of the reference's CPU path, "
+              f"{cores} threads" + ("" if done == args.steps and warm == args.warmup else
+                                    f"; stopped early by the {budget:.0f} s budget (asked {args.steps} steps, {args.warmup} warm-up)"))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": round(fps, 4), "unit": "frames/s", "n_gpus": args.gpus,
+        "steps": done, "warmup": warm, "ms_per_step": round(1e3 * dt / done, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: single RAFT flow+uncertainty pass on a synthetic 1280x720 frame pair "
+                               "(160x90x256 feature maps, 12 GRU iters) + 500-point weighted homography fit",
+                   "weights": "seeded random init (WOFT checkpoints not shipped)"},
+        "cpu_baseline": {"value": round(fps, 4), "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": round(fps, 4), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}), flush=True)
+
+
+def run_woft(args, rank, world, local):
+    import torch
+    from woft_b200 import build as wbuild
+    wbuild.build()
+    from woft_b200 import tracker as wtracker
+    from woft_b200.corr import CorrBlock
+    from woft_b200.optical_flow import RAFTWrapper
+    import functools
+
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    peaks = load_peaks()
+    flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False, alternate_corr=False),
+                                model=None, seeded_weights=0, iters=ITERS, padding_mode="nopad")
+    flower = RAFTWrapper(flow_conf, device=dev, use_cuda_graph=True,
+                         corr_block=functools.partial(CorrBlock, mode=args.corr_mode))
+    trk = wtracker.PlanarTracker(wtracker.default_config(flow_conf), flower=flower)
+    n_seq_frames = 8
+    base, frames, mask = make_sequence(n_seq_frames, seed=rank)
+    trk.init(base, mask)
+    base_dev = torch.from_numpy(base).to(dev)
+    frames_dev = [torch.from_numpy(f).to(dev) for f in frames]
+    pw_all = torch.ones((HEIGHT, WIDTH), dtype=torch.bool, device=dev)
+
+    def device_step(i):
+        return trk.estimate_global(base_dev, frames_dev[i % n_seq_frames], pw_all)
+
+    def e2e_step(i):
+        return trk.track(frames[i % n_seq_frames])
+
+    results = {}
+    clocks = None
+    for name, step in (("device", device_step), ("e2e", e2e_step)):
+        for i in range(args.warmup):
+            step(i)
+        torch.cuda.synchronize(dev)
+        barrier()
+        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        passes0 = trk.flow_passes
+        with ClockSampler(local) as sampler:
+            start.record()
+            for i in range(args.steps):
+                step(i)
+            stop.record()
+            torch.cuda.synchronize(dev)
+        barrier()
+        from woft_b200.sharding import max_over_ranks
+        seconds = max_over_ranks(start.elapsed_time(stop) * 1e-3, device=dev)
+        results[name] = {"seconds": seconds, "flow_passes": trk.flow_passes - passes0}
+        if name == "device":
+            clocks = sampler.summary()
+
+    if rank != 0:
+        return
+    k3, kernels, peak_src = kernel_rooflines(torch, dev, args.corr_mode, peaks)
+    k3["peak_source"] = f"MEASURED_PEAKS.json ({peak_src})"
+    out = {
+        "metric": METRIC,
+        "value": round(world * args.steps / results["device"]["seconds"], 3),
+        "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": round(1e3 * results["device"]["seconds"] / args.steps, 3),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": {"tf32": "tf32", "tf32x3": "f32 (3xTF32)", "bf16": "bf16", "fp32": "f32"}[args.corr_mode],
+        "data": "synthetic",
+        "config": {"workload": "configs[1]: single RAFT flow+uncertainty pass on a synthetic 1280x720 frame pair "
+                               "(160x90x256 feature maps, 12 GRU iters, 13 lookups) + correspondence mask + 500-point "
+                               "Sobol pick + weighted homography fit + inlier test, one independent sequence per GPU",
+                   "corr_mode": args.corr_mode, "weights": "seeded random init (WOFT checkpoints not shipped)",
+                   "convolutions": "cuDNN, torch defaults (TF32 allowed)", "cuda_graph": True,
+                   "l2": "step working set (1.1 GB correlation pyramid) exceeds the 126 MB L2, no flush between "
+                         "steps; per-kernel roofline launches are preceded by a 256 MiB L2 flush",
+                   "flow_passes_per_frame": results["device"]["flow_passes"] / args.steps},
+        "e2e": {"value": round(world * args.steps / results["e2e"]["seconds"], 3), "unit": "frames/s",
+                "h2d_bytes_per_step": 2 * HEIGHT * WIDTH * 3 + HEIGHT * WIDTH, "d2h_bytes_per_step": 36 + 1,
+                "flow_passes_per_frame": results["e2e"]["flow_passes"] / args.steps,
+                "api": "woft_b200.tracker.PlanarTracker.track(host uint8 frame) -> 3x3 homography on the host"},
+        "gpu_launches": int(args.steps * (5 + (ITERS + 1) + 2)),
+        "clocks": clocks,
+        "roofline": k3,
+        "kernels": kernels,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        times, cores = cpu_frame_seconds(2)
+        out["cpu_baseline"] = {"value": round(1.0 / min(times), 4), "unit": "frames/s", "cores": cores, "kind": "port",
+                               "sample": f"2 full 1280x720 frames (12 iters) through the oracle port of the reference's "
+                                         f"CPU path, best of 2: {min(times):.2f} s/frame on {cores} threads"}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["woft", "reference"], default="woft")
+    ap.add_argument("--corr-mode", default=os.environ.get("WOFT_CORR_MODE", "tf32"),
+                    choices=["tf32", "tf32x3", "bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "woft" else args.warmup
+    if args.impl == "reference":
+        # no process group: rank 0 alone times the CPU path, the other ranks leave at once
+        run_reference(args, int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")))
+        return
+    rank, world, local = dist_setup(args)
+    try:
+        run_woft(args, rank, world, local)
+    finally:
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized():
+            dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,120 @@
+/* woft_b200.h -- C ABI of libwoft_b200.so: the per-frame hot path of the WOFT planar tracker on B200 (sm_100a).
+ *
+ * The reference (serycjon/WOFT) is Python/PyTorch; its only FFI is the pybind11 module `alt_cuda_corr`
+ * (pytracking/external/RAFT/alt_cuda_corr/correlation.cpp:23-54).  Every entry point below therefore cites
+ * the reference *operator* it replaces; INTEGRATION.md shows the ctypes binding a maintainer adds on the
+ * reference side.
+ *
+ * Conventions
+ *   - all pointers are DEVICE pointers unless the parameter comment says "host"; tensors are dense, row-major
+ *     (C-contiguous) fp32 in exactly the layout the reference uses at that seam;
+ *   - the caller (PyTorch in this repo) owns every buffer, including workspaces; the library never allocates,
+ *     frees or keeps a pointer after the call returns;
+ *   - `stream` is a cudaStream_t passed as void*; work is enqueued on it and the call returns without
+ *     synchronising;
+ *   - return value: WOFT_OK or a negative-free error code below; `woft_last_error()` gives a thread-local,
+ *     human-readable reason.  No C++ exception crosses the boundary.
+ */
+#ifndef WOFT_B200_H
+#define WOFT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define WOFT_ABI_VERSION 1
+
+enum woft_status {
+  WOFT_OK = 0,
+  WOFT_ERR_INVALID_ARGUMENT = 1, /* bad shape, null pointer, unsupported radius / level count */
+  WOFT_ERR_CUDA = 2,             /* a CUDA runtime / driver call failed; see woft_last_error() */
+  WOFT_ERR_UNSUPPORTED = 3,      /* valid request this build cannot serve (e.g. tensor-core path off sm_100) */
+  WOFT_ERR_WORKSPACE = 4         /* workspace pointer null or smaller than woft_corr_workspace_bytes() */
+};
+
+/* Arithmetic of the all-pairs correlation (K1).  The reference multiplies in fp32 (corr.py:67). */
+enum woft_corr_mode {
+  WOFT_CORR_FP32_SIMT = 0, /* fp32 FMA on CUDA cores: same precision class as the reference, slowest */
+  WOFT_CORR_TF32 = 1,      /* tcgen05 kind::tf32, operands rounded to tf32 once, fp32 accumulate in TMEM */
+  WOFT_CORR_TF32X3 = 2,    /* tcgen05, error-compensated 3xTF32 split (hi*hi + hi*lo + lo*hi): fp32-class result */
+  WOFT_CORR_BF16 = 3       /* tcgen05 kind::f16 with bf16 operands, fp32 accumulate */
+};
+
+/* Estimators of pytracking/utils/least_squares_H.py served by woft_homography_fit (K4). */
+enum woft_h_method {
+  WOFT_H_NONHOMOGENEOUS = 0, /* find_homography_nonhomogeneous_QR (:142-210) and ..._nonhomogeneous (:56-139):
+                                8-parameter system, rows scaled by w, least squares */
+  WOFT_H_DLT = 1,            /* find_homography_dlt (:213-265): 9x9 Gram A^T (w A), smallest eigenvector */
+  WOFT_H_IRLS_L1 = 2,        /* find_homography_IRLSq_QR (:280-346) with IRLSq_L1 (:268-269) */
+  WOFT_H_IRLS_HUBER = 3      /* find_homography_IRLSq_QR with IRLSq_Huber(k) (:272-277) */
+};
+
+int woft_abi_version(void);
+const char* woft_last_error(void);
+
+/* Bytes of scratch woft_corr_pyramid needs for this shape and mode (0 for WOFT_CORR_FP32_SIMT). */
+size_t woft_corr_workspace_bytes(int batch, int channels, int height, int width, int mode);
+
+/* K1 + K2.  Replaces CorrBlock.__init__ + CorrBlock.corr
+ * (pytracking/external/RAFT/raft_core/corr.py:13-27, 61-69): all-pairs correlation
+ *   level0[b*H*W + i][j] = sum_c fmap1[b][c][i] * fmap2[b][c][j] / sqrt(C)
+ * and `num_levels-1` successive 2x2 average poolings over the (H, W) plane of every query (floor on odd sizes).
+ *   fmap1, fmap2 : (B, C, H, W)
+ *   levels       : HOST array of `num_levels` device pointers; level l is (B*H*W, 1, H_l, W_l), H_l = H_{l-1}/2
+ *   row_mean     : (B*H*W) mean of level 0 over its (H, W) plane, what WeightHead.forward
+ *                  (weighted_raft.py:358-361) reduces from the volume; may be NULL
+ *   workspace    : >= woft_corr_workspace_bytes(...) bytes, 256-byte aligned
+ */
+int woft_corr_pyramid(const float* fmap1, const float* fmap2, int batch, int channels, int height, int width,
+                      int num_levels, float* const* levels, float* row_mean, void* workspace,
+                      size_t workspace_bytes, int mode, void* stream);
+
+/* Synchronises `stream` and reports whether the last woft_corr_pyramid on `workspace` ran to completion.  The
+ * tensor-core kernel bounds every pipeline wait (2 s) and raises a flag in the workspace instead of hanging;
+ * this reads the flag back (one 4-byte device-to-host copy).  No counterpart in the reference. */
+int woft_corr_check(const void* workspace, void* stream);
+
+/* K3.  Replaces CorrBlock.__call__ + bilinear_sampler (corr.py:29-59, raft_core/utils/utils.py:59-73):
+ * for every query pixel and level l a (2r+1)^2 window of level l, centred at coords / 2^l, bilinear,
+ * zero outside the map.
+ *   levels : HOST array of `num_levels` device pointers as written by woft_corr_pyramid (h2 x w2 at level 0)
+ *   coords : (B, 2, H1, W1), channel 0 = x, channel 1 = y
+ *   out    : (B, num_levels*(2r+1)^2, H1, W1); channel = l*(2r+1)^2 + (xoff+r)*(2r+1) + (yoff+r)
+ * Level maps narrower than 2 pixels make the reference return NaN (division by W-1 = 0, utils.py:63-64);
+ * this call rejects them with WOFT_ERR_INVALID_ARGUMENT instead.
+ */
+int woft_corr_lookup(const float* const* levels, int num_levels, const float* coords, int batch, int h1, int w1,
+                     int h2, int w2, int radius, float* out, int flags, void* stream);
+
+/* A''.  Replaces alt_cuda_corr.forward (alt_cuda_corr/correlation.cpp:23-33, correlation_kernel.cu:18-119,
+ * 260-286), the reference's one native op: on-the-fly local correlation without a materialised volume.
+ *   fmap1 : (B, H1, W1, C) channels-last      fmap2 : (B, H2, W2, C) channels-last
+ *   coords: (B, N, H1, W1, 2) as (x, y)        out   : (B, N, (2r+1)^2, H1, W1), UNSCALED dot products,
+ *   channel = (yoff+r) + (2r+1)*(xoff+r).  Unlike the reference op the output is caller-allocated.
+ */
+int woft_alt_corr_forward(const float* fmap1, const float* fmap2, const float* coords, int batch, int h1, int w1,
+                          int h2, int w2, int channels, int n_coords, int radius, float* out, void* stream);
+
+/* K4.  Replaces find_homography_nonhomogeneous_QR / _nonhomogeneous / _dlt / _IRLSq_QR
+ * (pytracking/utils/least_squares_H.py:56-346) including the Hartley normalisation they call
+ * (kornia.geometry.epipolar.normalize_points) and the final de-normalisation and division by H33 + 1e-8.
+ *   points1, points2 : (B, N, 2)      weights : (B, N) or NULL      H_out : (B, 3, 3), maps points1 -> points2
+ *   n_iter, huber_k  : IRLS only (reference defaults 5 and 1); n_iter+1 solves are made
+ * One launch per call: normalisation, Gram accumulation in fp64, in-kernel 8x8 Cholesky or 9x9 Jacobi.
+ */
+int woft_homography_fit(const float* points1, const float* points2, const float* weights, int batch, int n_points,
+                        int method, int n_iter, float huber_k, float* H_out, void* stream);
+
+/* Replaces torch_proj_errors (least_squares_H.py:474-489): L2 distance between H*pts_a and pts_b.
+ *   H : (B, 3, 3)    pts_a, pts_b : (B, 2, N)    err : (B, N)
+ */
+int woft_proj_errors(const float* H, const float* pts_a, const float* pts_b, int batch, int n_points, float* err,
+                     void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* WOFT_B200_H */

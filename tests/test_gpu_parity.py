@@ -1,0 +1,330 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle and the reference-generated golden vectors.
+
+Tolerances (absolute, on correlation values of unit scale; stated per arithmetic mode of the GEMM):
+  fp32 / tf32x3   1e-4   same precision class as the reference's fp32 matmul (summation order differs)
+  tf32            6e-3   operands rounded once to 10-bit mantissa, 256-term dot product / 16
+  bf16            5e-2   operands rounded to 7-bit mantissa
+Flow: mean end-point error <= 0.01 px against the reference network output in the fp32-class modes (north star),
+<= 0.05 px stated for tf32 / bf16.  Homography: corner error <= 0.05 px on a 1280x720 frame.
+"""
+import functools
+
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import woft_oracle as wo
+
+pytestmark = pytest.mark.gpu
+
+CORR_ATOL = {"fp32": 1e-4, "tf32x3": 1e-4, "tf32": 6e-3, "bf16": 5e-2}
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _exact_convs():
+    # keep cuDNN/cuBLAS out of TF32 so the fp32 tolerance is not spent on library noise
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+# ----------------------------------------------------------------------------------------------------
+# K3 lookup
+# ----------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("flags", [0, 1])
+def test_lookup_on_golden_pyramid(golden, flags):
+    """K3 alone: feed the reference's own pyramid, compare with the reference's lookup."""
+    from woft_b200.corr import CorrBlock
+    g = golden("corr_small")
+    blk = CorrBlock.__new__(CorrBlock)
+    blk.num_levels, blk.radius, blk.shape = 4, 4, (1, 16, 16, 24)
+    blk.corr_pyramid = [cu(g[f"level{l}"]) for l in range(4)]
+    for tag in ("grid", "jitter", "oob"):
+        out = blk(cu(g[f"coords_{tag}"]), flags=flags)
+        assert out.shape == (1, 324, 16, 24) and out.is_contiguous()
+        np.testing.assert_allclose(out.cpu().numpy(), g[f"lookup_{tag}"], atol=2e-5, err_msg=tag)
+
+
+@pytest.mark.parametrize("name", ["corr_small", "corr_odd", "corr_c256"])
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3", "tf32", "bf16"])
+def test_corr_block_matches_golden(golden, name, mode):
+    from woft_b200.corr import CorrBlock
+    g = golden(name)
+    blk = CorrBlock(cu(g["fmap1"]), cu(g["fmap2"]), num_levels=4, radius=4, mode=mode)
+    blk.check()
+    atol = CORR_ATOL[mode]
+    for l, lvl in enumerate(blk.corr_pyramid):
+        assert tuple(lvl.shape) == tuple(g[f"level{l}_shape"])
+        if f"level{l}" in g:
+            np.testing.assert_allclose(lvl.cpu().numpy(), g[f"level{l}"], atol=atol, err_msg=f"level {l}")
+        assert lvl.double().sum().item() == pytest.approx(float(g[f"level{l}_sum"]), abs=atol * lvl.numel() ** 0.5 * 4)
+    np.testing.assert_allclose(blk.mean_response().cpu().numpy(), g["mean_response"], atol=1e-4)
+    for tag in ("grid", "jitter", "oob"):
+        out = blk(cu(g[f"coords_{tag}"]))
+        assert not torch.isnan(out).any()
+        np.testing.assert_allclose(out.cpu().numpy(), g[f"lookup_{tag}"], atol=atol, err_msg=tag)
+
+
+@pytest.mark.parametrize("shape", [(1, 256, 48, 64), (2, 64, 45, 80), (1, 40, 20, 36), (1, 256, 33, 70)])
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3", "tf32", "bf16"])
+def test_corr_pyramid_vs_oracle_ragged_shapes(shape, mode):
+    """Partial tiles in every direction, level widths that do and do not allow TMA stores, K padding (C=40)."""
+    from woft_b200.corr import CorrBlock
+    B, C, H, W = shape
+    g = torch.Generator().manual_seed(H * 1000 + W)
+    f1, f2 = torch.randn(shape, generator=g), torch.randn(shape, generator=g)
+    ref = wo.corr_pyramid(f1, f2, 4)
+    blk = CorrBlock(f1.to(DEV), f2.to(DEV), mode=mode)
+    blk.check()
+    for l in range(4):
+        assert blk.corr_pyramid[l].shape == ref[l].shape
+        np.testing.assert_allclose(blk.corr_pyramid[l].cpu().numpy(), ref[l].numpy(), atol=CORR_ATOL[mode],
+                                   err_msg=f"{shape} {mode} level {l}")
+
+
+def test_corr_block_rejects_what_the_reference_turns_into_nan():
+    from woft_b200.corr import CorrBlock
+    f = torch.randn(1, 16, 8, 12, device=DEV)  # coarsest level would be 1x1 -> reference returns NaN
+    with pytest.raises(AssertionError, match="too small"):
+        CorrBlock(f, f)
+    f = torch.randn(1, 16, 16, 16, device=DEV)
+    blk = CorrBlock(f, f, mode="fp32")
+    with pytest.raises(AssertionError):
+        blk(torch.zeros(1, 2, 8, 8, device=DEV))
+
+
+@pytest.mark.parametrize("mode", ["tf32", "tf32x3", "bf16"])
+def test_full_size_properties(mode):
+    """BASELINE config 2 size (90x160x256): properties that need no CPU volume."""
+    from woft_b200.corr import CorrBlock
+    torch.manual_seed(0)
+    B, C, H, W = 1, 256, 90, 160
+    f1 = torch.randn(B, C, H, W, device=DEV)
+    f2 = torch.randn(B, C, H, W, device=DEV)
+    blk = CorrBlock(f1, f2, mode=mode)
+    blk.check()
+    lv = blk.corr_pyramid
+    assert [tuple(l.shape[2:]) for l in lv] == [(90, 160), (45, 80), (22, 40), (11, 20)]
+    # (a) sampled entries against fp64 dot products
+    idx = torch.randint(0, H * W, (2, 20000), device=DEV)
+    a = f1.view(C, H * W)[:, idx[0]].double()
+    b = f2.view(C, H * W)[:, idx[1]].double()
+    want = (a * b).sum(0) / 16.0
+    got = lv[0].view(H * W, H * W)[idx[0], idx[1]].double()
+    assert (got - want).abs().max().item() < CORR_ATOL[mode]
+    # (b) every level is the 2x2 mean of the one below (avg_pool2d semantics, floor on 45 -> 22)
+    for l in range(3):
+        assert torch.allclose(lv[l + 1], F.avg_pool2d(lv[l], 2, stride=2), atol=2e-6)
+    # (c) the mean response is the mean of the level-0 plane
+    assert torch.allclose(blk.mean_response().view(-1), lv[0].mean(dim=(1, 2, 3)), atol=1e-4)
+    # (d) lookup at integer coordinates returns volume entries; out-of-map taps are exactly zero
+    ys, xs = torch.meshgrid(torch.arange(H, device=DEV), torch.arange(W, device=DEV), indexing="ij")
+    grid = torch.stack([xs, ys]).float()[None]
+    out = blk(grid)
+    q = 37 * W + 91
+    assert out[0, (2 + 4) * 9 + (-3 + 4), 37, 91].item() == pytest.approx(lv[0][q, 0, 37 - 3, 91 + 2].item(), abs=1e-6)
+    assert out[0, 0, 0, 0].item() == 0.0  # tap (-4, -4) of the corner query
+    # (e) lookup of a block of queries against grid_sample on the same device pyramid
+    coords = grid + (torch.rand_like(grid) * 2 - 1) * 8
+    out = blk(coords)
+    sel = torch.arange(3000, 3600, device=DEV)
+    ref = wo.corr_lookup([l[sel].cpu() for l in lv], coords.view(2, -1)[:, sel].cpu().view(1, 2, 1, -1))
+    got = out.view(324, -1)[:, sel].cpu().view(1, 324, 1, -1)
+    assert (got - ref).abs().max().item() < 2e-5 * max(1.0, ref.abs().max().item())
+
+
+# ----------------------------------------------------------------------------------------------------
+# A'' alt_cuda_corr
+# ----------------------------------------------------------------------------------------------------
+def test_alt_corr_forward_vs_oracle():
+    from woft_b200.corr import AlternateCorrBlock, CorrBlock, alt_cuda_corr
+    g = torch.Generator().manual_seed(3)
+    B, C, H, W = 2, 64, 16, 24
+    f1 = torch.randn((B, H, W, C), generator=g)
+    f2 = torch.randn((B, 8, 12, C), generator=g)
+    coords = torch.rand((B, 1, H, W, 2), generator=g) * torch.tensor([14.0, 10.0]) - 1.0
+    want = wo.alt_corr_forward(f1, f2, coords, 4)
+    got, = alt_cuda_corr.forward(f1.to(DEV), f2.to(DEV), coords.to(DEV), 4)
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), atol=2e-4)
+    with pytest.raises(RuntimeError):
+        alt_cuda_corr.forward(f1, f2.to(DEV), coords.to(DEV), 4)
+    # the on-the-fly block agrees with the materialised one (pooling is linear)
+    n1 = torch.randn((1, 64, 16, 24), generator=g).to(DEV)
+    n2 = torch.randn((1, 64, 16, 24), generator=g).to(DEV)
+    c = (torch.rand((1, 2, 16, 24), generator=g) * 12 + 2).to(DEV)
+    a = AlternateCorrBlock(n1, n2)(c)
+    m = CorrBlock(n1, n2, mode="fp32")(c)
+    np.testing.assert_allclose(a.cpu().numpy(), m.cpu().numpy(), atol=2e-4)
+
+
+# ----------------------------------------------------------------------------------------------------
+# K4 homography
+# ----------------------------------------------------------------------------------------------------
+def _h_cases(g):
+    for tag in ("exact4", "plain100", "tracker500", "batch3", "ragged37"):
+        p1, p2 = g[tag + "_p1"], g[tag + "_p2"]
+        w = g[tag + "_w"] if tag + "_w" in g else None
+        yield tag, p1, p2, w
+
+
+def _corner_err(Ha, Hb):
+    return wo.corner_error(torch.as_tensor(Ha), torch.as_tensor(Hb), 1280, 720)
+
+
+def test_homography_matches_reference(golden):
+    from woft_b200 import least_squares_H as lsq
+    g = golden("homography")
+    huber2 = functools.partial(lsq.IRLSq_Huber, k=2)
+    fns = {"qr": (lsq.find_homography_nonhomogeneous_QR, "qr_f64"),
+           "pinv": (lsq.find_homography_nonhomogeneous, "qr_f64"),
+           "dlt": (lsq.find_homography_dlt, "dlt_f64"),
+           "irls_l1": (lsq.find_homography_IRLSq_QR, "irls_l1_f64"),
+           "irls_huber2": (functools.partial(lsq.find_homography_IRLSq_QR, reweighting_fn=huber2), None)}
+    for tag, p1, p2, w in _h_cases(g):
+        wd = cu(w) if w is not None else None
+        for key, (fn, f64key) in fns.items():
+            H = fn(cu(p1), cu(p2), wd)
+            assert H.shape == (p1.shape[0], 3, 3) and H.dtype == torch.float32
+            H = H.cpu()
+            assert torch.allclose(H[:, 2, 2], torch.ones(p1.shape[0]), atol=1e-6)
+            # against the reference's fp64 run (truth), and against its fp32 run within that run's own error
+            if f64key is not None:
+                e64 = _corner_err(H, g[f"{tag}_{f64key}"])
+                ref_own = _corner_err(g[f"{tag}_{key}"], g[f"{tag}_{f64key}"])
+                assert e64 <= 0.05, f"{tag}/{key}: {e64} px from the fp64 reference"
+                assert _corner_err(H, g[f"{tag}_{key}"]) <= 0.05 + ref_own, f"{tag}/{key}"
+            else:
+                assert _corner_err(H, g[f"{tag}_{key}"]) <= 0.05 or tag == "exact4", f"{tag}/{key}"
+        Hq = cu(g[f"{tag}_qr"])
+        err = lsq.torch_proj_errors(Hq, cu(p1).permute(0, 2, 1).contiguous(), cu(p2).permute(0, 2, 1).contiguous())
+        np.testing.assert_allclose(err.cpu().numpy(), g[f"{tag}_proj_err"], rtol=1e-4, atol=1e-3)
+
+
+def test_homography_error_behaviour():
+    from woft_b200 import least_squares_H as lsq
+    p = torch.rand(1, 3, 2, device=DEV)
+    with pytest.raises(AssertionError):
+        lsq.find_homography_nonhomogeneous_QR(p, p)
+    with pytest.raises(AssertionError):
+        lsq.find_homography_dlt(torch.rand(1, 5, 2, device=DEV), torch.rand(1, 6, 2, device=DEV))
+    with pytest.raises(AssertionError):
+        lsq.find_homography_nonhomogeneous_QR(torch.rand(1, 5, 2, device=DEV), torch.rand(1, 5, 2, device=DEV),
+                                              torch.rand(1, 4, device=DEV))
+
+
+def test_homography_stress_config3_properties():
+    """BASELINE config 3: B=1024 flow fields of 160x90 correspondences with weights; properties + a CPU subset."""
+    from oracle.gen_golden import make_h_case
+    from woft_b200 import least_squares_H as lsq
+    B, N = 1024, 14400
+    p1, p2, w, Ht = make_h_case(B=B, N=N, seed=0, noise=0.5, outlier_frac=0.3, with_weights=True)
+    d1, d2, dw = p1.to(DEV), p2.to(DEV), w.to(DEV)
+    H = lsq.find_homography_nonhomogeneous_QR(d1, d2, dw)
+    assert torch.isfinite(H).all()
+    ref = wo.find_homography_nonhomogeneous_QR(p1[:6].double(), p2[:6].double(), w[:6].double())
+    assert _corner_err(H[:6].cpu(), ref) <= 0.05
+    # order of the correspondences does not matter
+    perm = torch.randperm(N, device=DEV)
+    Hp = lsq.find_homography_nonhomogeneous_QR(d1[:32, perm].contiguous(), d2[:32, perm].contiguous(),
+                                               dw[:32, perm].contiguous())
+    assert _corner_err(H[:32].cpu(), Hp.cpu()) <= 1e-3
+    # a common scale on the weights does not matter; Huber(k=2) reweighting never triggers on such data
+    Hs = lsq.find_homography_nonhomogeneous_QR(d1[:32], d2[:32], dw[:32] * 3.0)
+    assert _corner_err(H[:32].cpu(), Hs.cpu()) <= 1e-3
+    Hh = lsq.find_homography_IRLSq_QR(d1[:32], d2[:32], dw[:32],
+                                      reweighting_fn=functools.partial(lsq.IRLSq_Huber, k=2))
+    assert _corner_err(H[:32].cpu(), Hh.cpu()) <= 1e-3
+    # IRLS-L1 and DLT against the CPU oracle in fp64 on a few problems
+    Hl = lsq.find_homography_IRLSq_QR(d1[:4], d2[:4], dw[:4])
+    refl = wo.find_homography_IRLSq_QR(p1[:4].double(), p2[:4].double(), w[:4].double())
+    assert _corner_err(Hl.cpu(), refl) <= 0.05
+    Hd = lsq.find_homography_dlt(d1[:4], d2[:4], dw[:4])
+    refd = wo.find_homography_dlt(p1[:4].double(), p2[:4].double(), w[:4].double())
+    assert _corner_err(Hd.cpu(), refd) <= 0.05
+
+
+# ----------------------------------------------------------------------------------------------------
+# network + flow wrapper + tracker
+# ----------------------------------------------------------------------------------------------------
+def _net_inputs(g):
+    t1 = torch.from_numpy(g["img1_bgr"][:, :, ::-1].copy()).permute(2, 0, 1).float()[None].to(DEV)
+    t2 = torch.from_numpy(g["img2_bgr"][:, :, ::-1].copy()).permute(2, 0, 1).float()[None].to(DEV)
+    return t1, t2
+
+
+@pytest.mark.parametrize("mode,epe_tol", [("fp32", 0.01), ("tf32x3", 0.01), ("tf32", 0.05), ("bf16", 0.05)])
+def test_flow_pass_matches_reference_network(golden, mode, epe_tol):
+    from woft_b200.corr import CorrBlock
+    from woft_b200.raft_net import WeightedRAFT, seeded_state_dict
+    g = golden("net_small")
+    net = WeightedRAFT().eval()
+    net.load_state_dict(seeded_state_dict(net, 0))
+    net = net.to(DEV)
+    t1, t2 = _net_inputs(g)
+    with torch.no_grad():
+        flow_low, flow_up, vol, w_low, w_up = net(t1, t2, iters=12, corr_block=functools.partial(CorrBlock, mode=mode))
+    epe = (flow_up.cpu() - torch.from_numpy(g["it12_flow_up"])).norm(dim=1).mean().item()
+    assert epe <= epe_tol, f"{mode}: mean EPE {epe} px"
+    assert (w_up.cpu() - torch.from_numpy(g["it12_w_up"])).abs().max().item() <= (2e-3 if epe_tol == 0.01 else 2e-2)
+    assert vol.shape == (320, 1, 16, 20)
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_flow_wrapper_matches_reference_wrapper(golden, graph):
+    from types import SimpleNamespace
+    from woft_b200.optical_flow import RAFTWrapper
+    from woft_b200.corr import CorrBlock
+    g, gw = golden("net_small"), golden("wrapper_small")
+    conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False, alternate_corr=False),
+                           model=None, seeded_weights=0, iters=12, padding_mode="nopad")
+    wrapper = RAFTWrapper(conf, device=DEV, use_cuda_graph=graph, corr_block=functools.partial(CorrBlock, mode="tf32x3"))
+    for _ in range(2):  # second call replays the graph
+        src, dst, w = wrapper.compute_flow(g["img1_bgr"], g["img2_bgr"], mode="TC", do_sigmoid=True)
+    assert src.dtype == torch.int64 and src.shape == (2, 128 * 160) and w.shape == (1, 128 * 160)
+    np.testing.assert_array_equal(src.cpu().numpy(), gw["tc_src"])
+    assert (dst.cpu() - torch.from_numpy(gw["tc_dst"])).norm(dim=0).mean().item() <= 0.01
+    np.testing.assert_allclose(w.cpu().numpy(), gw["tc_w"], atol=1e-3)
+    assert wrapper.last_flow_shape == {"batch": 1, "delta": 2, "H": 128, "W": 160}
+    flow, w2 = wrapper.compute_flow(g["img1_bgr"], g["img2_bgr"], mode="flow", numpy_out=True)
+    assert flow.shape == (2, 128, 160) and w2.shape == (1, 128, 160)
+    assert np.abs(w2 - gw["flow_w"]).max() <= 5e-3
+
+
+def test_tracker_runs_and_masks_like_the_reference():
+    from types import SimpleNamespace
+    import cv2
+    from oracle.gen_golden import make_frames
+    from woft_b200 import tracker
+    from woft_b200.optical_flow import RAFTWrapper
+    H, W = 256, 320
+    flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False), model=None,
+                                seeded_weights=0, iters=12, padding_mode="nopad")
+    trk = tracker.PlanarTracker(tracker.default_config(flow_conf), flower=RAFTWrapper(flow_conf, device=DEV))
+    img0, img1 = make_frames(H, W, 3)
+    mask = np.zeros((H, W), np.uint8)
+    mask[64:192, 80:240] = 255
+    trk.init(img0, mask)
+    for frame in (img1, img0, img1):
+        Hc, meta = trk.track(frame)
+        assert Hc.shape == (3, 3) and np.all(np.isfinite(Hc)) and Hc[2, 2] == pytest.approx(1.0)
+    assert 3 <= trk.flow_passes <= 6
+    # the device-side correspondence mask against the oracle's restatement of _mask_coords
+    g = torch.Generator().manual_seed(1)
+    n = H * W
+    from woft_b200.misc import torch_get_featuremap_coords
+    src = torch_get_featuremap_coords((H, W), device="cpu")
+    cur = src.float() + torch.randn((2, n), generator=g) * 30
+    wts = torch.rand((1, n), generator=g)
+    pw = torch.from_numpy(cv2.warpPerspective(np.ones((H, W)), np.array([[1, 0.02, 8], [0, 1, -5], [0, 0, 1.0]]), (W, H)) > 0)
+    want = wo.mask_coords(torch.from_numpy(mask > 0), src, cur, wts, pw)
+    got = trk._mask_coords(src.to(DEV), cur.to(DEV), wts.to(DEV), pw.to(DEV))
+    for a, b in zip(got, want):
+        assert torch.equal(a.cpu(), b)

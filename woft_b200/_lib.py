@@ -1,0 +1,95 @@
+"""ctypes binding of libwoft_b200.so (include/woft_b200.h).
+
+There is no fallback: if the library is missing, does not export the ABI version this package was written
+for, or a call fails, a RuntimeError is raised.  Importing this module does not need a GPU; calling a
+compute entry point does.
+"""
+import ctypes
+from ctypes import POINTER, c_char_p, c_float, c_int, c_size_t, c_void_p
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "libwoft_b200.so"
+ABI_VERSION = 1
+
+OK, ERR_INVALID_ARGUMENT, ERR_CUDA, ERR_UNSUPPORTED, ERR_WORKSPACE = range(5)
+CORR_FP32_SIMT, CORR_TF32, CORR_TF32X3, CORR_BF16 = range(4)
+H_NONHOMOGENEOUS, H_DLT, H_IRLS_L1, H_IRLS_HUBER = range(4)
+
+CORR_MODES = {"fp32": CORR_FP32_SIMT, "tf32": CORR_TF32, "tf32x3": CORR_TF32X3, "bf16": CORR_BF16}
+
+_FLOATP_ARRAY = POINTER(c_void_p)
+
+# name -> (restype, argtypes); kept in step with include/woft_b200.h (tests/test_abi.py checks both ways)
+SIGNATURES = {
+    "woft_abi_version": (c_int, []),
+    "woft_last_error": (c_char_p, []),
+    "woft_corr_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
+    "woft_corr_pyramid": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, _FLOATP_ARRAY, c_void_p,
+                                  c_void_p, c_size_t, c_int, c_void_p]),
+    "woft_corr_check": (c_int, [c_void_p, c_void_p]),
+    "woft_corr_lookup": (c_int, [_FLOATP_ARRAY, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                 c_int, c_void_p]),
+    "woft_alt_corr_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                      c_int, c_void_p, c_void_p]),
+    "woft_homography_fit": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,
+                                    c_void_p]),
+    "woft_proj_errors": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+}
+
+_lib = None
+
+
+def load():
+    """Load the shared library once and declare every signature.  Raises RuntimeError if it cannot."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        raise RuntimeError(
+            f"{LIB_PATH} is missing: build it with `python -m woft_b200.build` (needs nvcc). "
+            "woft_b200 has no CPU or PyTorch fallback for its CUDA kernels.")
+    lib = ctypes.CDLL(str(LIB_PATH))
+    for name, (restype, argtypes) in SIGNATURES.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as exc:
+            raise RuntimeError(f"{LIB_PATH} does not export {name}; rebuild it") from exc
+        fn.restype, fn.argtypes = restype, argtypes
+    if lib.woft_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"{LIB_PATH} has ABI version {lib.woft_abi_version()}, expected {ABI_VERSION}; rebuild it")
+    _lib = lib
+    return lib
+
+
+def last_error():
+    return load().woft_last_error().decode(errors="replace")
+
+
+def check(status, what):
+    """Turn a non-zero status into the exception the reference seam would raise."""
+    if status == OK:
+        return
+    msg = f"{what}: {last_error()} (status {status})"
+    if status == ERR_INVALID_ARGUMENT:
+        raise AssertionError(msg)  # the reference's shape checks raise AssertionError (least_squares_H.py:158-163)
+    raise RuntimeError(msg)
+
+
+def require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("woft_b200 kernels run on CUDA tensors only; got a tensor on " + str(t.device))
+
+
+def ptr(t):
+    return c_void_p(t.data_ptr()) if t is not None else c_void_p(0)
+
+
+def ptr_array(tensors):
+    arr = (c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+    return ctypes.cast(arr, _FLOATP_ARRAY), arr  # keep `arr` alive for the duration of the call
+
+
+def current_stream(device):
+    import torch
+    return c_void_p(torch.cuda.current_stream(device).cuda_stream)

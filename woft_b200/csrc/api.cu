@@ -1,0 +1,83 @@
+// C-ABI glue: error reporting, woft_corr_pyramid dispatch over the arithmetic modes, workspace sizing.
+#include <cstring>
+
+#include "common.cuh"
+
+namespace woft {
+
+char* last_error_buffer() {
+  static thread_local char buf[512] = "";
+  return buf;
+}
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(last_error_buffer(), 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+int corr_pyramid_simt(const float*, const float*, int, int, int, int, int, float* const*, cudaStream_t);
+int corr_pyramid_tc(const float*, const float*, int, int, int, int, int, float* const*, void*, int, cudaStream_t);
+size_t corr_tc_workspace_bytes(int, int, int, int);
+int launch_row_mean(const float*, const float*, int, int, int, float*, float*, cudaStream_t);
+
+static size_t simt_workspace_bytes(int B, int C) { return 256 + ((size_t)B * C * 4 + 255) / 256 * 256; }
+
+}  // namespace woft
+
+extern "C" int woft_abi_version(void) { return WOFT_ABI_VERSION; }
+
+extern "C" const char* woft_last_error(void) { return woft::last_error_buffer(); }
+
+extern "C" size_t woft_corr_workspace_bytes(int batch, int channels, int height, int width, int mode) {
+  if (batch <= 0 || channels <= 0 || height <= 0 || width <= 0) return 0;
+  if (mode == WOFT_CORR_FP32_SIMT) return woft::simt_workspace_bytes(batch, channels);
+  return woft::corr_tc_workspace_bytes(batch, channels, height * width, mode);
+}
+
+extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int batch, int channels, int height,
+                                 int width, int num_levels, float* const* levels, float* row_mean, void* workspace,
+                                 size_t workspace_bytes, int mode, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(fmap1 && fmap2 && levels, "woft_corr_pyramid: null pointer");
+  WOFT_REQUIRE(batch > 0 && channels > 0 && height > 0 && width > 0, "woft_corr_pyramid: non-positive extent");
+  WOFT_REQUIRE(num_levels >= 1 && num_levels <= kMaxLevels, "woft_corr_pyramid: num_levels %d not in [1,%d]",
+               num_levels, kMaxLevels);
+  WOFT_REQUIRE(mode >= WOFT_CORR_FP32_SIMT && mode <= WOFT_CORR_BF16, "woft_corr_pyramid: unknown mode %d", mode);
+  WOFT_REQUIRE((long long)batch * height * width < (1ll << 31), "woft_corr_pyramid: too many query pixels");
+  for (int l = 0, h = height, w = width; l < num_levels; ++l, h /= 2, w /= 2) {
+    WOFT_REQUIRE(h >= 1 && w >= 1, "woft_corr_pyramid: level %d is empty", l);
+    WOFT_REQUIRE(levels[l], "woft_corr_pyramid: level %d pointer is null", l);
+  }
+  const size_t need = woft_corr_workspace_bytes(batch, channels, height, width, mode);
+  if (!workspace || workspace_bytes < need)
+    return fail(WOFT_ERR_WORKSPACE, "woft_corr_pyramid: workspace of %zu bytes given, %zu needed", workspace_bytes,
+                need);
+  WOFT_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "woft_corr_pyramid: workspace not 256-byte aligned");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int rc;
+  if (mode == WOFT_CORR_FP32_SIMT) {
+    rc = corr_pyramid_simt(fmap1, fmap2, batch, channels, height, width, num_levels, levels, s);
+  } else {
+    rc = corr_pyramid_tc(fmap1, fmap2, batch, channels, height, width, num_levels, levels, workspace, mode, s);
+  }
+  if (rc != WOFT_OK) return rc;
+  if (row_mean) {
+    float* mean2 = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + 256);
+    rc = launch_row_mean(fmap1, fmap2, batch, channels, height * width, row_mean, mean2, s);
+  }
+  return rc;
+}
+
+extern "C" int woft_corr_check(const void* workspace, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(workspace, "woft_corr_check: null workspace");
+  int flag = 0;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  WOFT_CUDA_CHECK(cudaMemcpyAsync(&flag, workspace, sizeof(int), cudaMemcpyDeviceToHost, s));
+  WOFT_CUDA_CHECK(cudaStreamSynchronize(s));
+  if (flag != 0) return fail(WOFT_ERR_CUDA, "correlation kernel aborted: a pipeline barrier timed out (flag=%d)", flag);
+  return WOFT_OK;
+}

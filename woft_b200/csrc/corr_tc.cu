@@ -1,0 +1,571 @@
+// K1 + K2 on the Blackwell tensor cores: all-pairs correlation as a tcgen05/TMEM GEMM fed by TMA, with the
+// 4-level average-pooled pyramid formed in the epilogue.
+//
+// Replaces CorrBlock.corr (torch.matmul + a separate divide pass) and the three avg_pool2d passes of
+// CorrBlock.__init__ (pytracking/external/RAFT/raft_core/corr.py:13-27, 61-69): the reference writes the
+// 829 MB level-0 volume, re-reads and re-writes it for the 1/sqrt(C) scaling, and re-reads each level to pool
+// the next.  Here every level is written exactly once and nothing is re-read.
+//
+// Data layout
+//   fmaps arrive NCHW, i.e. both GEMM operands are (C, HW) with HW contiguous ("MN-major").  pack_kernel
+//   transposes them once into K-major rows (HW, Kp) in the caller's workspace -- rounded to tf32 (one plane),
+//   split into tf32 hi + lo planes (3xTF32), or converted to bf16 -- so TMA can fetch 128-byte swizzled K rows.
+//   Output levels keep the reference layout (B*H*W, 1, H_l, W_l) fp32.
+//
+// Tiling
+//   One output tile = 128 consecutive query pixels (UMMA M) x an 8 x 32 patch of the (h2, w2) plane
+//   (UMMA N = 256).  The patch is fetched by ONE 4-D TMA box over (K, W2, H2, B) so its 256 rows sit in shared
+//   memory in (h, w) order and whole 2x2 / 4x4 / 8x8 pooling cells live inside one accumulator row.
+//   floor() semantics of avg_pool2d: a level-l cell exists iff its index is < H_l, W_l at that level; TMA
+//   zero-fills reads past the map, and stores past it are clipped (columns, queries) or skipped (rows).
+//
+// Warp roles (192 threads, persistent CTAs, static round-robin over tiles)
+//   warp 0      TMA producer: A box (Kblk x 128 queries) + B box (Kblk x 32 x 8) per stage, 3 stages of 48 KB
+//   warp 1      allocates all 512 TMEM columns (2 accumulators of 128 lanes x 256 fp32 columns), issues
+//               tcgen05.mma (kind::tf32 or kind::f16, M=128 N=256), commits stages back to the producer
+//   warps 2-5   epilogue: tcgen05.ld one (h) row of 32 columns at a time, scale by 1/sqrt(C), stage the row in
+//               a 3-slot shared-memory ring (128-byte swizzled) and TMA-store it (box 32 x 1 x 128 queries:
+//               one full 128-byte line per query); 2x2 sums are carried in registers and the three pooled
+//               levels leave through the same ring at the end of the tile.  Accumulator i+1 is being
+//               computed while accumulator i drains.
+// Every mbarrier wait has a 2 s timeout that raises an abort flag in the workspace instead of hanging the GPU.
+//
+// Algorithmic bytes per launch: 2 * B*C*HW*4 (fmaps in) + sum_l B*HW*H_l*W_l*4 (levels out); 2*B*HW^2*C flop
+// (x3 for WOFT_CORR_TF32X3).  At 1280x720 (HW = 14 400, C = 256): 1.10 GB, 106 GFLOP -> HBM-write bound.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace woft {
+
+constexpr int BM = 128;
+constexpr int TH = 8, TW = 32;
+constexpr int BN = TH * TW;
+constexpr int A_STAGE = BM * 128;  // bytes: 128 rows of one 128-byte K row
+constexpr int B_STAGE = BN * 128;
+constexpr int STAGES = 3;
+constexpr int SLOT = 16384;
+constexpr int NSLOT = 3;
+constexpr int TC_THREADS = 192;
+constexpr int EPI_THREADS = 128;
+constexpr int TC_SMEM = STAGES * (A_STAGE + B_STAGE) + NSLOT * SLOT + 256 + 1024;  // + barriers + alignment slack
+constexpr int kMaxTcLevels = 4;
+
+struct CorrTcParams {
+  CUtensorMap tmA;                   // (Kp, HW, B*planes), box (Kblk, 128, 1)
+  CUtensorMap tmB;                   // (Kp, W, H, B*planes), box (Kblk, 32, 8, 1)
+  CUtensorMap tmOut[kMaxTcLevels];   // (W_l, H_l, HW, B), box (32 >> l, 1, 128, 1)
+  float* level[kMaxTcLevels];
+  int lh[kMaxTcLevels];
+  int lw[kMaxTcLevels];
+  int tma_ok[kMaxTcLevels];
+  int num_levels;
+  int B, HW, H, W;
+  int m_tiles, h_tiles, w_tiles, total_tiles;
+  int k_blocks;   // 128-byte K rows per plane
+  int k_elems;    // elements per 128-byte K row (32 tf32 / 64 bf16)
+  int n_pairs;    // 1, or 3 for the hi/lo split
+  int bf16;
+  float scale;
+  int* abort_flag;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// pack: (B, C, HW) fp32 -> K-major (planes, B, HW, Kp)
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+template <int MODE>  // 1 tf32, 2 tf32 hi/lo, 3 bf16
+__global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src, void* __restrict__ dst, int C,
+                                                   int HW, int Kp, size_t plane_elems, int* flag) {
+  __shared__ float tile[32][33];
+  if (flag && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) *flag = 0;
+  const int b = blockIdx.z;
+  const int hw0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+  const float* s = src + (size_t)b * C * HW;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + ty + i * 8, hw = hw0 + tx;
+    tile[ty + i * 8][tx] = (c < C && hw < HW) ? __ldg(s + (size_t)c * HW + hw) : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int hw = hw0 + ty + i * 8, c = c0 + tx;
+    if (hw >= HW || c >= Kp) continue;
+    const float v = tile[tx][ty + i * 8];
+    const size_t o = ((size_t)b * HW + hw) * Kp + c;
+    if (MODE == 3) {
+      reinterpret_cast<__nv_bfloat16*>(dst)[o] = __float2bfloat16_rn(v);
+    } else {
+      const float hi = round_tf32(v);
+      reinterpret_cast<float*>(dst)[o] = hi;
+      if (MODE == 2) reinterpret_cast<float*>(dst)[plane_elems + o] = round_tf32(v - hi);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// GEMM + pooled epilogue
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool wait_or_abort(uint64_t* bar, uint32_t parity, int* abort_flag) {
+  if (ptx::mbar_try_wait(bar, parity)) return true;
+  const uint64_t t0 = ptx::globaltimer_ns();
+  uint32_t spins = 0;
+  while (!ptx::mbar_try_wait(bar, parity)) {
+    if ((++spins & 63u) == 0) {
+      if (*reinterpret_cast<volatile int*>(abort_flag) != 0) return false;
+      if (ptx::globaltimer_ns() - t0 > 2000000000ull) {
+        atomicExch(abort_flag, 1);
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);  // start address, 16-byte units
+  d |= (uint64_t)1 << 16;                    // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;          // stride byte offset: 8 rows x 128 B between row groups
+  d |= (uint64_t)1 << 46;                    // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
+  return d;
+}
+
+struct TileCoord {
+  int b, m0, h0, w0;
+};
+__device__ __forceinline__ TileCoord decode_tile(const CorrTcParams& p, int t) {
+  TileCoord c;
+  const int wt = t % p.w_tiles;
+  t /= p.w_tiles;
+  const int ht = t % p.h_tiles;
+  t /= p.h_tiles;
+  const int mt = t % p.m_tiles;
+  c.b = t / p.m_tiles;
+  c.m0 = mt * BM;
+  c.h0 = ht * TH;
+  c.w0 = wt * TW;
+  return c;
+}
+
+// swizzled staging of one pooled/unpooled row of NV fp32 values (NV*4 bytes per query) for a TMA store whose
+// box is (NV, 1, 128): 16-byte chunk index XOR-ed the way CU_TENSOR_MAP_SWIZZLE_{128,64,32}B expects.
+template <int NV>
+__device__ __forceinline__ void stage_row(uint8_t* sub_slot, int m, const float* v) {
+  constexpr int CH = NV / 4;  // 16-byte chunks per query row
+  uint8_t* row = sub_slot + m * (NV * 4);
+  const int x = (NV == 32) ? (m & 7) : (NV == 16) ? ((m >> 1) & 3) : (NV == 8) ? ((m >> 2) & 1) : 0;
+#pragma unroll
+  for (int c = 0; c < CH; ++c)
+    *reinterpret_cast<float4*>(row + ((c ^ x) << 4)) = make_float4(v[4 * c], v[4 * c + 1], v[4 * c + 2], v[4 * c + 3]);
+}
+
+template <int NV>
+__device__ __forceinline__ void direct_row(float* level, int lh, int lw, int HW, int b, int m, int h, int w0,
+                                           const float* v) {
+  if (m >= HW || h >= lh) return;
+  float* dst = level + (((size_t)b * HW + m) * lh + h) * lw;
+#pragma unroll
+  for (int j = 0; j < NV; ++j)
+    if (w0 + j < lw) dst[w0 + j] = v[j];
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_constant__ CorrTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + STAGES * A_STAGE;
+  uint8_t* ring = sB + STAGES * B_STAGE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + NSLOT * SLOT);
+  uint64_t* full = bars;                 // [STAGES] TMA -> MMA
+  uint64_t* empty = bars + STAGES;       // [STAGES] MMA -> TMA
+  uint64_t* tfull = bars + 2 * STAGES;   // [2] MMA -> epilogue
+  uint64_t* tempty = tfull + 2;          // [2] epilogue -> MMA
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
+  volatile int* epi_go = reinterpret_cast<volatile int*>(tmem_ptr + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      ptx::mbar_init(full + s, 1);
+      ptx::mbar_init(empty + s, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(tfull + i, 1);
+      ptx::mbar_init(tempty + i, EPI_THREADS);
+    }
+    ptx::fence_mbar_init();
+    ptx::prefetch_tmap(&p.tmA);
+    ptx::prefetch_tmap(&p.tmB);
+    for (int l = 0; l < p.num_levels; ++l)
+      if (p.tma_ok[l]) ptx::prefetch_tmap(&p.tmOut[l]);
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_ptr, 512);
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  const int k_steps = p.k_blocks * p.n_pairs;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      bool alive = true;
+      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x) {
+        const TileCoord tc = decode_tile(p, t);
+        for (int ks = 0; ks < k_steps; ++ks) {
+          const int kb = ks / p.n_pairs, pr = ks - kb * p.n_pairs;
+          const int plane_a = (pr == 2) ? 1 : 0, plane_b = (pr == 1) ? 1 : 0;  // hi*hi, hi*lo, lo*hi
+          if (!wait_or_abort(empty + stage, phase ^ 1u, p.abort_flag)) {
+            alive = false;
+            break;
+          }
+          ptx::mbar_arrive_expect_tx(full + stage, A_STAGE + B_STAGE);
+          ptx::tma_load_3d(sA + stage * A_STAGE, &p.tmA, full + stage, kb * p.k_elems, tc.m0, plane_a * p.B + tc.b);
+          ptx::tma_load_4d(sB + stage * B_STAGE, &p.tmB, full + stage, kb * p.k_elems, tc.w0, tc.h0,
+                           plane_b * p.B + tc.b);
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (lane == 0) {
+      const uint32_t fmt = p.bf16 ? 1u : 2u;  // F16F32Format: BF16 = 1, TF32 = 2
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(BN >> 3) << 17) | (uint32_t(BM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      bool alive = true;
+      int it = 0;
+      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t use = uint32_t(it >> 1);
+        if (!wait_or_abort(tempty + buf, (use & 1u) ^ 1u, p.abort_flag)) break;
+        ptx::tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + uint32_t(buf * BN);
+        for (int ks = 0; ks < k_steps; ++ks) {
+          if (!wait_or_abort(full + stage, phase, p.abort_flag)) {
+            alive = false;
+            break;
+          }
+          ptx::tc_fence_after_sync();
+          const uint64_t da = make_kmajor_sw128_desc(ptx::smem_u32(sA + stage * A_STAGE));
+          const uint64_t db = make_kmajor_sw128_desc(ptx::smem_u32(sB + stage * B_STAGE));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row: UMMA_K = 8 (tf32) / 16 (bf16)
+            const uint32_t acc = (ks > 0 || k > 0) ? 1u : 0u;
+            if (p.bf16)
+              ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+            else
+              ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+          }
+          ptx::mma_commit(empty + stage);  // frees the stage once these MMAs have read it
+          if (++stage == STAGES) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        if (alive) ptx::mma_commit(tfull + buf);
+      }
+    }
+  } else {
+    // ================================ epilogue ================================
+    const int et = threadIdx.x - 64;              // 0..127
+    const bool issuer = (et == 0);
+    const int m = (warp & 3) * 32 + lane;         // TMEM lane == query row of the tile
+    const uint32_t lane_base = uint32_t((warp & 3) * 32) << 16;
+    const float scale = p.scale;
+    uint32_t ev = 0;  // ring event counter (identical in all epilogue threads)
+    int it = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+      const TileCoord tc = decode_tile(p, t);
+      const int buf = it & 1;
+      const uint32_t use = uint32_t(it >> 1);
+      if (issuer) *epi_go = wait_or_abort(tfull + buf, use & 1u, p.abort_flag) ? 1 : 0;
+      ptx::named_bar_sync(1, EPI_THREADS);
+      if (*epi_go == 0) break;
+      ptx::tc_fence_after_sync();
+      const int mq = tc.m0 + m;
+
+      float hs[16];      // horizontal pair sums of the even row
+      float l1[4][16];   // level-1 rows of this tile
+#pragma unroll
+      for (int r = 0; r < TH; ++r) {
+        float v[32];
+        ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * BN + r * TW), v);
+        if (r == TH - 1) {  // accumulator fully read: hand it back to the MMA warp
+          ptx::tc_fence_before_sync();
+          ptx::mbar_arrive(tempty + buf);
+        }
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] *= scale;
+        uint8_t* slot = ring + (ev % NSLOT) * SLOT;
+        if (p.tma_ok[0]) {
+          stage_row<32>(slot, m, v);
+          ptx::fence_proxy_async_smem();
+        } else {
+          direct_row<32>(p.level[0], p.lh[0], p.lw[0], p.HW, tc.b, mq, tc.h0 + r, tc.w0, v);
+        }
+        ptx::named_bar_sync(1, EPI_THREADS);
+        if (issuer) {
+          if (p.tma_ok[0] && tc.h0 + r < p.lh[0]) ptx::tma_store_4d(&p.tmOut[0], slot, tc.w0, tc.h0 + r, tc.m0, tc.b);
+          ptx::tma_store_commit();
+          ptx::tma_store_wait_read<1>();
+        }
+        ++ev;
+        // 2x2 mean in avg_pool2d's summation order: ((a00 + a01) + a10) + a11, then * 0.25
+        if ((r & 1) == 0) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) hs[j] = v[2 * j] + v[2 * j + 1];
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) l1[r >> 1][j] = ((hs[j] + v[2 * j]) + v[2 * j + 1]) * 0.25f;
+        }
+      }
+
+      if (p.num_levels > 1) {
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {  // level-1 rows {0,1} then {2,3}
+          uint8_t* slot = ring + (ev % NSLOT) * SLOT;
+#pragma unroll
+          for (int rr = 0; rr < 2; ++rr) {
+            const int r1 = half * 2 + rr;
+            if (p.tma_ok[1])
+              stage_row<16>(slot + rr * 8192, m, l1[r1]);
+            else
+              direct_row<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, tc.h0 / 2 + r1, tc.w0 / 2, l1[r1]);
+          }
+          if (p.tma_ok[1]) ptx::fence_proxy_async_smem();
+          ptx::named_bar_sync(1, EPI_THREADS);
+          if (issuer) {
+            if (p.tma_ok[1]) {
+#pragma unroll
+              for (int rr = 0; rr < 2; ++rr) {
+                const int h1 = tc.h0 / 2 + half * 2 + rr;
+                if (h1 < p.lh[1]) ptx::tma_store_4d(&p.tmOut[1], slot + rr * 8192, tc.w0 / 2, h1, tc.m0, tc.b);
+              }
+            }
+            ptx::tma_store_commit();
+            ptx::tma_store_wait_read<1>();
+          }
+          ++ev;
+        }
+      }
+      if (p.num_levels > 2) {
+        float l2[2][8], l3[4];
+#pragma unroll
+        for (int i = 0; i < 2; ++i)
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            l2[i][j] = ((l1[2 * i][2 * j] + l1[2 * i][2 * j + 1]) + l1[2 * i + 1][2 * j] + l1[2 * i + 1][2 * j + 1]) * 0.25f;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) l3[j] = ((l2[0][2 * j] + l2[0][2 * j + 1]) + l2[1][2 * j] + l2[1][2 * j + 1]) * 0.25f;
+        uint8_t* slot = ring + (ev % NSLOT) * SLOT;
+#pragma unroll
+        for (int i = 0; i < 2; ++i) {
+          if (p.tma_ok[2])
+            stage_row<8>(slot + i * 4096, m, l2[i]);
+          else
+            direct_row<8>(p.level[2], p.lh[2], p.lw[2], p.HW, tc.b, mq, tc.h0 / 4 + i, tc.w0 / 4, l2[i]);
+        }
+        if (p.num_levels > 3) {
+          if (p.tma_ok[3])
+            stage_row<4>(slot + 8192, m, l3);
+          else
+            direct_row<4>(p.level[3], p.lh[3], p.lw[3], p.HW, tc.b, mq, tc.h0 / 8, tc.w0 / 8, l3);
+        }
+        ptx::fence_proxy_async_smem();
+        ptx::named_bar_sync(1, EPI_THREADS);
+        if (issuer) {
+          if (p.tma_ok[2]) {
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+              const int h2 = tc.h0 / 4 + i;
+              if (h2 < p.lh[2]) ptx::tma_store_4d(&p.tmOut[2], slot + i * 4096, tc.w0 / 4, h2, tc.m0, tc.b);
+            }
+          }
+          if (p.num_levels > 3 && p.tma_ok[3] && tc.h0 / 8 < p.lh[3])
+            ptx::tma_store_4d(&p.tmOut[3], slot + 8192, tc.w0 / 8, tc.h0 / 8, tc.m0, tc.b);
+          ptx::tma_store_commit();
+          ptx::tma_store_wait_read<1>();
+        }
+        ++ev;
+      }
+    }
+    if (issuer) ptx::tma_store_wait_all();
+  }
+
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after_sync();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  return reinterpret_cast<EncodeTiledFn>(fn);
+}
+
+static bool encode(EncodeTiledFn fn, CUtensorMap* map, CUtensorMapDataType dt, int elem_bytes, int rank, void* base,
+                   const cuuint64_t* dims, const cuuint32_t* box, CUtensorMapSwizzle swz) {
+  cuuint64_t strides[4];
+  cuuint64_t s = elem_bytes;
+  for (int i = 0; i < rank - 1; ++i) {
+    s *= dims[i];
+    strides[i] = s;
+    if (s % 16 != 0) return false;
+  }
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  return fn(map, dt, rank, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct TcLayout {
+  int Kp, k_elems, planes, elem_bytes;
+  size_t plane_bytes, off_mean, off_a, off_b, total;
+};
+
+TcLayout tc_layout(int B, int C, int HW, int mode) {
+  TcLayout L{};
+  L.elem_bytes = (mode == WOFT_CORR_BF16) ? 2 : 4;
+  L.k_elems = 128 / L.elem_bytes;
+  L.Kp = (C + L.k_elems - 1) / L.k_elems * L.k_elems;
+  L.planes = (mode == WOFT_CORR_TF32X3) ? 2 : 1;
+  L.plane_bytes = (size_t)B * HW * L.Kp * L.elem_bytes;  // Kp*elem_bytes is a multiple of 128
+  L.off_mean = 256;
+  L.off_a = align_up(L.off_mean + (size_t)B * C * 4, 1024);
+  L.off_b = L.off_a + L.planes * L.plane_bytes;
+  L.total = align_up(L.off_b + L.planes * L.plane_bytes, 256);
+  return L;
+}
+
+int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H, int W, int num_levels,
+                    float* const* levels, void* workspace, int mode, cudaStream_t stream) {
+  if (num_levels > kMaxTcLevels)
+    return fail(WOFT_ERR_UNSUPPORTED, "tensor-core correlation supports at most %d levels (8x32 pooling tile)",
+                kMaxTcLevels);
+  int dev = 0, major = 0;
+  WOFT_CUDA_CHECK(cudaGetDevice(&dev));
+  WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) return fail(WOFT_ERR_UNSUPPORTED, "tcgen05 path needs sm_100; device is sm_%d*", major);
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+
+  const int HW = H * W;
+  const TcLayout L = tc_layout(B, C, HW, mode);
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  int* flag = reinterpret_cast<int*>(ws);
+  void* packA = ws + L.off_a;
+  void* packB = ws + L.off_b;
+
+  // ---- pack both fmaps into K-major planes (also clears the abort flag)
+  {
+    dim3 grid(ceil_div(HW, 32), L.Kp / 32, B);
+    const size_t plane_elems = L.plane_bytes / L.elem_bytes;
+    if (mode == WOFT_CORR_BF16) {
+      pack_kernel<3><<<grid, 256, 0, stream>>>(fmap1, packA, C, HW, L.Kp, plane_elems, flag);
+      pack_kernel<3><<<grid, 256, 0, stream>>>(fmap2, packB, C, HW, L.Kp, plane_elems, nullptr);
+    } else if (mode == WOFT_CORR_TF32X3) {
+      pack_kernel<2><<<grid, 256, 0, stream>>>(fmap1, packA, C, HW, L.Kp, plane_elems, flag);
+      pack_kernel<2><<<grid, 256, 0, stream>>>(fmap2, packB, C, HW, L.Kp, plane_elems, nullptr);
+    } else {
+      pack_kernel<1><<<grid, 256, 0, stream>>>(fmap1, packA, C, HW, L.Kp, plane_elems, flag);
+      pack_kernel<1><<<grid, 256, 0, stream>>>(fmap2, packB, C, HW, L.Kp, plane_elems, nullptr);
+    }
+    int rc = launch_status("pack_kernel");
+    if (rc != WOFT_OK) return rc;
+  }
+
+  CorrTcParams p{};
+  const CUtensorMapDataType dt = (mode == WOFT_CORR_BF16) ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  // the hi and lo planes lie back to back, so they fold into the batch dimension of the operand maps
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)L.Kp, (cuuint64_t)HW, (cuuint64_t)(B * L.planes)};
+    cuuint32_t box[3] = {(cuuint32_t)L.k_elems, BM, 1};
+    if (!encode(enc, &p.tmA, dt, L.elem_bytes, 3, packA, dims, box, CU_TENSOR_MAP_SWIZZLE_128B))
+      return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the fmap1 operand");
+  }
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)L.Kp, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)(B * L.planes)};
+    cuuint32_t box[4] = {(cuuint32_t)L.k_elems, TW, TH, 1};
+    if (!encode(enc, &p.tmB, dt, L.elem_bytes, 4, packB, dims, box, CU_TENSOR_MAP_SWIZZLE_128B))
+      return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the fmap2 operand");
+  }
+  int h = H, w = W;
+  for (int l = 0; l < num_levels; ++l) {
+    p.level[l] = levels[l];
+    p.lh[l] = h;
+    p.lw[l] = w;
+    const CUtensorMapSwizzle swz = l == 0   ? CU_TENSOR_MAP_SWIZZLE_128B
+                                   : l == 1 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                   : l == 2 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                            : CU_TENSOR_MAP_SWIZZLE_NONE;
+    cuuint64_t dims[4] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)HW, (cuuint64_t)B};
+    cuuint32_t box[4] = {(cuuint32_t)(TW >> l), 1, BM, 1};
+    p.tma_ok[l] = (h > 0 && w > 0 && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0 &&
+                   encode(enc, &p.tmOut[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, 4, levels[l], dims, box, swz))
+                      ? 1
+                      : 0;
+    h /= 2;
+    w /= 2;
+  }
+  p.num_levels = num_levels;
+  p.B = B;
+  p.HW = HW;
+  p.H = H;
+  p.W = W;
+  p.m_tiles = ceil_div(HW, BM);
+  p.h_tiles = ceil_div(H, TH);
+  p.w_tiles = ceil_div(W, TW);
+  p.total_tiles = B * p.m_tiles * p.h_tiles * p.w_tiles;
+  p.k_blocks = L.Kp / L.k_elems;
+  p.k_elems = L.k_elems;
+  p.n_pairs = (mode == WOFT_CORR_TF32X3) ? 3 : 1;
+  p.bf16 = (mode == WOFT_CORR_BF16) ? 1 : 0;
+  p.scale = 1.0f / sqrtf(float(C));
+  p.abort_flag = flag;
+
+  int sms = 0;
+  WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
+  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  corr_tc_kernel<<<grid, TC_THREADS, TC_SMEM, stream>>>(p);
+  return launch_status("corr_tc_kernel");
+}
+
+size_t corr_tc_workspace_bytes(int B, int C, int HW, int mode) { return tc_layout(B, C, HW, mode).total; }
+
+}  // namespace woft

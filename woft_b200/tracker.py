@@ -1,0 +1,190 @@
+"""The caller of both seams: WOFT's per-frame tracker state machine, kept as the reference has it.
+
+Mirror of `YAOFTrackerSingleControl` (pytracking/tracker/YAOF_tracker_single_control.py:18-327) and of the
+default config's plug-ins (pytracking/configs/YAOFT_single_control_repRAFT_sub500_noreliableinl_wLSq.py:14-53):
+pre-warp by the last good homography, template->pre-warped flow + weights, mask, Sobol-subsample to 500,
+weighted homography, inlier check, and on failure the frame-to-frame fallback chained onto the previous
+homography.  It exists so the whole tracked-frame path can be run and timed where the reference is absent;
+with the reference present, its own tracker runs unchanged on top of `RAFTWrapper` and `find_homography_*`
+(INTEGRATION.md).
+
+Kept on the host exactly as in the reference: cv2.warpPerspective pre-warp (:89-95), compose_H in float64
+numpy (utils/geom_utils.py:365-373).  Moved to the device: the correspondence mask and the Sobol pick, which the
+reference does with boolean indexing plus a GPU->CPU->GPU round trip of the mask (:287-312, config :31-53);
+here the (deterministic) Sobol positions are drawn once per point count and applied as a device gather.
+"""
+from types import SimpleNamespace
+
+import cv2
+import numpy as np
+import torch
+
+from . import least_squares_H as lsq
+from .optical_flow import RAFTWrapper, _cfg
+
+
+def compose_H(*Hs):
+    """geom_utils.py:365-373: product in reverse order, normalised by the bottom-right element."""
+    for H in Hs:
+        if H is None:
+            return None
+    out = np.eye(3)
+    for H in Hs:
+        out = np.dot(H, out)
+    return out / out[2, 2]
+
+
+_SOBOL = {}
+
+
+def sobol_positions(to_draw=500):
+    """First `to_draw` points of the unscrambled 1-D Sobol sequence (config :44-46), cached."""
+    if to_draw not in _SOBOL:
+        _SOBOL[to_draw] = torch.quasirandom.SobolEngine(dimension=1).draw(to_draw).numpy().flatten()
+    return _SOBOL[to_draw]
+
+
+def sobol_keep_indices(n_pts, to_draw=500):
+    """Sorted unique indices round(n_pts * u_k) the reference's boolean mask selects (config :31-53).
+    None when to_draw >= n_pts (everything is kept).  np.round is round-half-to-even, as in the reference."""
+    if to_draw >= n_pts:
+        return None
+    idx = np.round(n_pts * sobol_positions(to_draw)).astype(np.int32)
+    return np.unique(idx)
+
+
+def subsampler(coords_a, coords_b, weights, to_draw=500):
+    """config :31-53 on device tensors: (2,N), (2,N), (1,N) -> at most `to_draw` columns, raster order kept."""
+    assert coords_a.shape == coords_b.shape
+    n_pts = coords_a.shape[1]
+    assert weights.shape == (1, n_pts)
+    keep = sobol_keep_indices(n_pts, to_draw)
+    if keep is None:
+        return coords_a, coords_b, weights
+    idx = torch.from_numpy(keep.astype(np.int64)).to(coords_a.device, non_blocking=True)
+    return coords_a[:, idx], coords_b[:, idx], weights[:, idx]
+
+
+def redet_success_fn(H, template_coords, cur_coords, weights=None, thr=5.0, min_frac=0.2):
+    """config :14-21: fraction of correspondences reprojecting within `thr` px must exceed `min_frac`."""
+    errs = lsq.torch_proj_errors(H, cur_coords[None], template_coords[None])
+    return torch.mean((errs <= thr).float()) > min_frac
+
+
+def find_homography(pts_A, pts_B, weights=None):
+    """config :24-28."""
+    return lsq.find_homography_nonhomogeneous_QR(pts_A, pts_B, weights=weights)
+
+
+def default_config(flow_config):
+    """get_config() of the default tracker config (:56-71)."""
+    return SimpleNamespace(flow_config=flow_config, H_estimator=find_homography, redet_success_fn=redet_success_fn,
+                           pw_mask=True, no_prewarp_after_N=10, subsampler_fn=subsampler, no_local_H=False,
+                           do_not_mask_TCs_by_prewarped=False)
+
+
+class PlanarTracker:
+    """YAOF_tracker_single_control.py:18-327 (no debug drawing, no fast-forward, no input downscaling)."""
+
+    def __init__(self, config, flower=None):
+        self.C = config
+        self.flower = flower if flower is not None else RAFTWrapper(config.flow_config)
+        self.device = self.flower.device
+        self.flow_passes = 0
+
+    def init(self, img, mask):
+        """:26-47."""
+        self.template_img = img
+        self.template_mask = torch.from_numpy(mask > 0).to(self.device)
+        self.np_template_mask = mask
+        self.prev_H2init = np.eye(3)
+        self.last_good_H2init = np.eye(3)
+        self.prev_img = img
+        self.lost = False
+        self.N_lost = 0
+
+    def track(self, input_img):
+        """:57-285.  Returns (H_cur2init (3,3) float64 numpy, meta)."""
+        meta = SimpleNamespace()
+        n_max = _cfg(self.C, "no_prewarp_after_N")
+        if n_max and self.N_lost > n_max:
+            self.last_good_H2init = np.eye(3)
+        prewarp_H = self.last_good_H2init
+        h, w = input_img.shape[:2]
+        prewarped = cv2.warpPerspective(input_img, prewarp_H, (w, h), flags=cv2.INTER_LINEAR)
+        pw_mask = cv2.warpPerspective(np.ones((h, w)), prewarp_H, (w, h), flags=cv2.INTER_LINEAR)
+        pw_mask = torch.from_numpy(pw_mask > 0).to(self.device, non_blocking=True)
+
+        H_pw2init, ok, t_coords, c_coords, weights = self.estimate_global(self.template_img, prewarped, pw_mask)
+        H_np = H_pw2init.detach().cpu().numpy()[0].astype(np.float64)   # D2H of the 3x3 (reference :156)
+        H_global = compose_H(prewarp_H, H_np)
+        meta.H_global_cur2init = H_global.copy()
+
+        if bool(ok):  # device sync on the flag, as in the reference (:167)
+            H_cur2init = H_global
+            self.lost, self.N_lost = False, 0
+        else:
+            self.lost = True
+            self.N_lost += 1
+            if _cfg(self.C, "no_local_H", False):
+                H_cur2init = H_global
+            else:
+                p_coords, c2_coords, w2 = self.flower.compute_flow(self.prev_img, input_img, mode="TC", do_sigmoid=True)
+                self.flow_passes += 1
+                p_coords, c2_coords, w2 = self._mask_coords_flow(p_coords, c2_coords, w2)
+                if self.C.subsampler_fn:
+                    p_coords, c2_coords, w2 = self.C.subsampler_fn(p_coords.float(), c2_coords, w2)
+                try:
+                    H_flow = self.C.H_estimator(c2_coords.T[None].contiguous(), p_coords.float().T[None].contiguous(), w2)
+                    H_flow = H_flow.detach().cpu().numpy()[0].astype(np.float64)
+                    H_local = compose_H(H_flow, self.prev_H2init)
+                    if not np.all(np.isfinite(H_local)):
+                        raise FloatingPointError("degenerate local homography")
+                except Exception:
+                    H_local = self.prev_H2init
+                meta.H_local_cur2init = H_local.copy()
+                H_cur2init = H_local
+
+        self.prev_img = input_img.copy()
+        self.prev_H2init = H_cur2init.copy()
+        if not self.lost:
+            self.last_good_H2init = H_cur2init.copy()
+        meta.lost, meta.N_lost, meta.global_H_success = self.lost, self.N_lost, bool(ok)
+        return H_cur2init, meta
+
+    def estimate_global(self, template_img, prewarped_img, pw_mask):
+        """The device part of one tracked frame (:101-163): template -> pre-warped flow + weights, correspondence
+        mask, Sobol pick, weighted homography, inlier test.  Images may be host uint8 arrays or device uint8
+        tensors; nothing is copied back to the host here.  Returns (H (1,3,3), ok (0-dim bool tensor), and the
+        correspondences that were fitted)."""
+        t_coords, c_coords, weights = self.flower.compute_flow(template_img, prewarped_img, mode="TC", do_sigmoid=True)
+        self.flow_passes += 1
+        t_coords, c_coords, weights, _ = self._mask_coords(
+            t_coords, c_coords, weights, pw_mask, do_pw_mask=not _cfg(self.C, "do_not_mask_TCs_by_prewarped", False))
+        t_coords = t_coords.float()
+        if self.C.subsampler_fn:
+            t_coords, c_coords, weights = self.C.subsampler_fn(t_coords, c_coords, weights)
+        H_pw2init = self.C.H_estimator(c_coords.T[None].contiguous(), t_coords.T[None].contiguous(), weights).float()
+        ok = self.C.redet_success_fn(H_pw2init, t_coords, c_coords, weights)
+        return H_pw2init, ok, t_coords, c_coords, weights
+
+    def _mask_coords(self, template_coords, cur_coords, weights, pw_mask, do_pw_mask=True):
+        """:287-312 without the in-place boolean scatter: keep = template mask & in bounds & pre-warp mask."""
+        in_template = self.template_mask[template_coords[1], template_coords[0]]
+        H, W = pw_mask.shape
+        cur_int = cur_coords.round().long()
+        inb = ~(torch.any(cur_coords < 0, dim=0) | (cur_int[0] >= W) | (cur_int[1] >= H))
+        if do_pw_mask:
+            # (cur >= 0 as floats can still round to -0 -> index 0; clamp only guards the masked-out columns)
+            inb = inb & pw_mask[cur_int[1].clamp(0, H - 1), cur_int[0].clamp(0, W - 1)]
+        keep = in_template & inb
+        return template_coords[:, keep], cur_coords[:, keep], weights[:, keep], keep
+
+    def _mask_coords_flow(self, prev_coords, cur_coords, weights):
+        """:314-327."""
+        h, w = self.template_mask.shape
+        prev_mask = cv2.warpPerspective(self.np_template_mask, np.linalg.inv(self.prev_H2init), (w, h),
+                                        flags=cv2.INTER_NEAREST) > 0
+        prev_mask = torch.from_numpy(prev_mask).to(prev_coords.device)
+        keep = prev_mask[prev_coords[1], prev_coords[0]]
+        return prev_coords[:, keep], cur_coords[:, keep], weights[:, keep]

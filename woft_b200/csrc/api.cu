@@ -57,6 +57,7 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
                 need);
   WOFT_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "woft_corr_pyramid: workspace not 256-byte aligned");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  WOFT_CUDA_CHECK(cudaMemsetAsync(workspace, 0, sizeof(int), s));  // the abort flag woft_corr_check reads
   int rc;
   if (mode == WOFT_CORR_FP32_SIMT) {
     rc = corr_pyramid_simt(fmap1, fmap2, batch, channels, height, width, num_levels, levels, s);

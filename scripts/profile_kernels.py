@@ -43,8 +43,8 @@ for mode in ("tf32", "tf32x3", "bf16"):
     timed(f"corr_pyramid[{mode}]", build, 3)
     blocks[mode].check()
 blk = blocks["tf32"]
-timed("corr_lookup flags=0", lambda: blk(coords, flags=0), 5)
-timed("corr_lookup flags=1 (cp.async)", lambda: blk(coords, flags=1), 5)
+timed("corr_lookup flags=0 (float4 rows)", lambda: blk(coords, flags=0), 5)
+timed("corr_lookup flags=1 (scalar rows)", lambda: blk(coords, flags=1), 5)
 f1b = torch.randn((4, C, H, W), generator=g, device=dev)
 del blocks["tf32x3"], blocks["bf16"]
 Bh, Nh = 1024, 14400

@@ -26,6 +26,7 @@ namespace woft {
 
 constexpr int kHThreads = 256;
 constexpr int kHWarps = kHThreads / 32;
+constexpr int kHUnroll = 4;  // independent loads in flight per thread and pass
 
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll
@@ -140,7 +141,7 @@ struct HParams {
   float huber_k;
 };
 
-__global__ void __launch_bounds__(kHThreads) homography_fit_kernel(const HParams prm) {
+__global__ void __launch_bounds__(kHThreads, 2) homography_fit_kernel(const HParams prm) {
   __shared__ double scratch[kHWarps * 30 + 30];
   __shared__ double h9[9];  // current solution in normalised coordinates (h9[8] = 1 for the 8-parameter system)
 
@@ -152,9 +153,18 @@ __global__ void __launch_bounds__(kHThreads) homography_fit_kernel(const HParams
 
   // ---- pass 1: means
   double m[4] = {0.0, 0.0, 0.0, 0.0};
-  for (int i = threadIdx.x; i < N; i += kHThreads) {
-    const float2 a = __ldg(P1 + i), c = __ldg(P2 + i);
-    m[0] += a.x; m[1] += a.y; m[2] += c.x; m[3] += c.y;
+  for (int i0 = threadIdx.x; i0 < N; i0 += kHThreads * kHUnroll) {
+    float2 a[kHUnroll], c[kHUnroll];
+#pragma unroll
+    for (int u = 0; u < kHUnroll; ++u) {  // all loads of the batch first: the loop is latency bound otherwise
+      const int i = i0 + u * kHThreads;
+      a[u] = i < N ? __ldg(P1 + i) : make_float2(0.f, 0.f);
+      c[u] = i < N ? __ldg(P2 + i) : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < kHUnroll; ++u) {
+      m[0] += a[u].x; m[1] += a[u].y; m[2] += c[u].x; m[3] += c[u].y;
+    }
   }
   block_sum<4>(m, scratch);
   const double inv_n = 1.0 / double(N);
@@ -162,11 +172,25 @@ __global__ void __launch_bounds__(kHThreads) homography_fit_kernel(const HParams
 
   // ---- pass 2: mean distance to the mean -> isotropic scale sqrt(2) / (dist + eps)
   double d[2] = {0.0, 0.0};
-  for (int i = threadIdx.x; i < N; i += kHThreads) {
-    const float2 a = __ldg(P1 + i), c = __ldg(P2 + i);
-    const double ax = a.x - mx1, ay = a.y - my1, cx = c.x - mx2, cy = c.y - my2;
-    d[0] += sqrt(ax * ax + ay * ay);
-    d[1] += sqrt(cx * cx + cy * cy);
+  for (int i0 = threadIdx.x; i0 < N; i0 += kHThreads * kHUnroll) {
+    float2 a[kHUnroll], c[kHUnroll];
+    bool live[kHUnroll];
+#pragma unroll
+    for (int u = 0; u < kHUnroll; ++u) {
+      const int i = i0 + u * kHThreads;
+      live[u] = i < N;
+      a[u] = live[u] ? __ldg(P1 + i) : make_float2(0.f, 0.f);
+      c[u] = live[u] ? __ldg(P2 + i) : make_float2(0.f, 0.f);
+    }
+#pragma unroll
+    for (int u = 0; u < kHUnroll; ++u) {
+      if (!live[u]) continue;
+      // differences in fp64, the square root in fp32 (1e-7 relative on a quantity that only sets the scale)
+      const float ax = float(a[u].x - mx1), ay = float(a[u].y - my1);
+      const float cx = float(c[u].x - mx2), cy = float(c[u].y - my2);
+      d[0] += double(sqrtf(ax * ax + ay * ay));
+      d[1] += double(sqrtf(cx * cx + cy * cy));
+    }
   }
   block_sum<2>(d, scratch);
   const double s1 = 1.4142135623730951 / (d[0] * inv_n + 1e-8);
@@ -187,11 +211,23 @@ __global__ void __launch_bounds__(kHThreads) homography_fit_kernel(const HParams
 #pragma unroll
       for (int k = 0; k < 9; ++k) h[k] = h9[k];
     }
-    for (int i = threadIdx.x; i < N; i += kHThreads) {
-      const float2 a = __ldg(P1 + i), c = __ldg(P2 + i);
+    for (int i0 = threadIdx.x; i0 < N; i0 += kHThreads * kHUnroll) {
+      float2 pa[kHUnroll], pc[kHUnroll];
+      float pw[kHUnroll];
+#pragma unroll
+      for (int u = 0; u < kHUnroll; ++u) {
+        const int i = i0 + u * kHThreads;
+        pa[u] = i < N ? __ldg(P1 + i) : make_float2(0.f, 0.f);
+        pc[u] = i < N ? __ldg(P2 + i) : make_float2(0.f, 0.f);
+        pw[u] = i < N ? (Wt ? __ldg(Wt + i) : 1.0f) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < kHUnroll; ++u) {
+      if (i0 + u * kHThreads >= N) continue;
+      const float2 a = pa[u], c = pc[u];
       const double x1 = (a.x - mx1) * s1, y1 = (a.y - my1) * s1;
       const double x2 = (c.x - mx2) * s2, y2 = (c.y - my2) * s2;
-      const double w = Wt ? double(__ldg(Wt + i)) : 1.0;
+      const double w = double(pw[u]);
       double wx = dlt ? w : w * w, wy = wx;  // row weights of the a_x and a_y rows
       if (it > 0) {
         // residual of each w-scaled row at the previous solution (least_squares_H.py:336), normalised units
@@ -216,6 +252,7 @@ __global__ void __launch_bounds__(kHThreads) homography_fit_kernel(const HParams
         S[12 + k] += c2 * pp[k];
         S[18 + k] += c3 * pp[k];
         S[24 + k] += c4 * pp[k];
+      }
       }
     }
     block_sum<30>(S, scratch);

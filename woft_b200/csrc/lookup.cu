@@ -5,15 +5,21 @@
 // linspace/meshgrid + one grid_sample per level + cat + permute, 13 times per flow pass.
 //
 // Memory-bound gather.  Per query pixel and level the (2r+1)^2 bilinear taps share one fractional offset,
-// so the kernel loads the (2r+2)^2 integer footprint once and forms all taps from it:
-//   - a CTA owns 32 consecutive query pixels; warp w serves level w (loops if there are more levels);
-//   - load phase: the warp walks the 32 footprints row segment by row segment, 32/(2r+2) segments per
-//     instruction, so one load instruction touches 3 rows of 40 B (r=4) instead of 32 scattered lines;
-//     footprints land in shared memory at an odd per-query stride (bank-conflict free for lane = query);
-//   - compute phase: lane = query; horizontal then vertical lerp in registers, row by row, and every tap
-//     is stored with lane = query, i.e. one coalesced 128-byte line per store instruction in the
-//     reference's channel-first output layout.
+// so the kernel loads the (2r+2)^2 integer footprint once and forms all taps from it.  A CTA of 128 threads
+// owns 16 consecutive query pixels and up to 4 levels at a time:
+//   load phase     one thread per footprint ROW (4 levels x 16 queries x 10 rows = 640 rows, 5 per thread).
+//                  A row is 40 contiguous bytes at an arbitrary 4-byte offset; when every level's width is a
+//                  multiple of 4 the thread fetches it as the 3-4 aligned float4 chunks that cover it (a chunk
+//                  is then wholly inside or wholly outside the map, so zero padding is a per-chunk predicate)
+//                  and drops the values into shared memory with the sub-chunk shift applied; otherwise it
+//                  falls back to 10 predicated scalar loads.  All of a thread's loads are issued before any
+//                  is consumed, so a CTA keeps tens of kilobytes in flight.
+//   compute phase  warp = level, lane = (query, upper/lower half of the window): horizontal then vertical
+//                  lerp in registers, row by row, footprints read from shared memory at an odd per-query
+//                  stride (conflict free).  Every tap is stored with consecutive lanes = consecutive queries,
+//                  i.e. two full 64-byte segments per store instruction in the reference's channel-first layout.
 // Algorithmic bytes per query pixel (r=4, 4 levels): 4*10*10*4 B read + 8 B coords + 324*4 B written = 2904 B.
+// DRAM moves more than that: a 40-byte row at a random offset costs one or two 64-byte sectors pairs.
 #include "common.cuh"
 
 namespace woft {
@@ -29,131 +35,159 @@ struct LookupParams {
   int hw1;              // H1*W1
 };
 
-constexpr int kLookupWarps = 4;
-constexpr int kQueriesPerCta = 32;
+constexpr int kLookupThreads = 128;
+constexpr int kQueriesPerCta = 16;
+constexpr int kLevelsPerPass = 4;  // one warp per level in the compute phase
 
 template <int R>
 struct LookupGeom {
   static constexpr int P = 2 * R + 1;
   static constexpr int WIN = P + 1;
-  static constexpr int STRIDE = WIN * WIN + 1;  // odd => lanes hit distinct banks
-  static constexpr int SEG_PER_INSTR = 32 / WIN;
-  static constexpr int NSEG = kQueriesPerCta * WIN;
-  static constexpr size_t SMEM = size_t(kLookupWarps) * kQueriesPerCta * STRIDE * sizeof(float);
+  static constexpr int STRIDE = WIN * WIN + 1;  // odd => lanes (queries) hit distinct banks
+  static constexpr int NCHUNK = (WIN + 3 + 3) / 4;  // aligned float4 chunks that cover any WIN-float run
+  static constexpr int ROWS = kLevelsPerPass * kQueriesPerCta * WIN;
+  static constexpr int ROWS_PER_THREAD = (ROWS + kLookupThreads - 1) / kLookupThreads;
 };
 
-__device__ __forceinline__ void cp_async_4(float* smem_dst, const float* gsrc, bool pred) {
-  unsigned dst = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
-  int src_bytes = pred ? 4 : 0;  // 0 => hardware zero-fill, the source is not read
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(dst), "l"(gsrc), "r"(src_bytes) : "memory");
-}
-
-template <int R, bool CP_ASYNC>
-__global__ void __launch_bounds__(kLookupWarps * 32) corr_lookup_kernel(const __grid_constant__ LookupParams p) {
+template <int R, bool VEC>
+__global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __grid_constant__ LookupParams p) {
   using G = LookupGeom<R>;
   constexpr int P = G::P, WIN = G::WIN, STRIDE = G::STRIDE;
-  extern __shared__ float smem[];
+  __shared__ float win[kLevelsPerPass * kQueriesPerCta * STRIDE];
+  __shared__ int s_x0[kLevelsPerPass * kQueriesPerCta], s_y0[kLevelsPerPass * kQueriesPerCta];
+  __shared__ float s_ax[kLevelsPerPass * kQueriesPerCta], s_ay[kLevelsPerPass * kQueriesPerCta];
 
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
+  const int tid = threadIdx.x;
   const int q0 = blockIdx.x * kQueriesPerCta;
-  const int q = q0 + lane;
-  const bool valid = q < p.nq;
-  const int b = valid ? q / p.hw1 : 0;
-  const int pix = valid ? q - b * p.hw1 : 0;
-  float cx = 0.f, cy = 0.f;
-  if (valid) {
-    cx = __ldg(p.coords + (size_t)(2 * b) * p.hw1 + pix);
-    cy = __ldg(p.coords + (size_t)(2 * b + 1) * p.hw1 + pix);
-  }
-  float* win = smem + warp * kQueriesPerCta * STRIDE;
-  const int sub = lane / WIN;        // which of the SEG_PER_INSTR row segments this lane helps load
-  const int col = lane - sub * WIN;  // column within the segment
-  const bool loader = sub < G::SEG_PER_INSTR;
   const int channels = p.num_levels * P * P;
 
-  for (int lvl = warp; lvl < p.num_levels; lvl += kLookupWarps) {
-    const int H = p.lh[lvl], W = p.lw[lvl];
-    const size_t plane = (size_t)H * W;
-    const float* __restrict__ base = p.level[lvl];
-    const float inv = 1.0f / float(1 << lvl);
-    const float x = cx * inv, y = cy * inv;  // centroid_lvl = coords / 2**i (corr.py:41)
-    float fx = floorf(x), fy = floorf(y);
-    const float ax = x - fx, ay = y - fy;
-    fx = fminf(fmaxf(fx, -1048576.f), 1048576.f);
-    fy = fminf(fmaxf(fy, -1048576.f), 1048576.f);
-    const int x0 = int(fx) - R, y0 = int(fy) - R;
+  for (int lv0 = 0; lv0 < p.num_levels; lv0 += kLevelsPerPass) {
+    // ---- window origins and fractions for (level slot, query): 64 threads
+    if (tid < kLevelsPerPass * kQueriesPerCta) {
+      const int slot = tid >> 4, ql = tid & 15;
+      const int q = q0 + ql, lvl = lv0 + slot;
+      float cx = 0.f, cy = 0.f;
+      if (q < p.nq && lvl < p.num_levels) {
+        const int b = q / p.hw1, pix = q - b * p.hw1;
+        cx = __ldg(p.coords + (size_t)(2 * b) * p.hw1 + pix);
+        cy = __ldg(p.coords + (size_t)(2 * b + 1) * p.hw1 + pix);
+      }
+      const float inv = 1.0f / float(1 << (lvl & 31));
+      const float x = cx * inv, y = cy * inv;  // centroid_lvl = coords / 2**i (corr.py:41)
+      float fx = floorf(x), fy = floorf(y);
+      s_ax[tid] = x - fx;
+      s_ay[tid] = y - fy;
+      fx = fminf(fmaxf(fx, -1048576.f), 1048576.f);
+      fy = fminf(fmaxf(fy, -1048576.f), 1048576.f);
+      s_x0[tid] = int(fx) - R;
+      s_y0[tid] = int(fy) - R;
+    }
+    __syncthreads();
 
-    // ---- load phase: 32 footprints of WIN x WIN, SEG_PER_INSTR row segments per instruction
-    constexpr int UNROLL = 8;
-    constexpr int STEP = G::SEG_PER_INSTR * UNROLL;
-#pragma unroll 1
-    for (int s0 = 0; s0 < G::NSEG; s0 += STEP) {
-      float v[UNROLL];
-      int dst[UNROLL];
+    // ---- load phase: one footprint row per thread and step, all loads issued before any store
+    float vals[G::ROWS_PER_THREAD][VEC ? 4 * G::NCHUNK : WIN];
 #pragma unroll
-      for (int j = 0; j < UNROLL; ++j) {
-        const int s = s0 + j * G::SEG_PER_INSTR + sub;
-        const bool ok = loader && s < G::NSEG;
-        const int ql = ok ? s / WIN : 0;
-        const int r = s - ql * WIN;
-        const int xx = __shfl_sync(0xffffffffu, x0, ql) + col;
-        const int yy = __shfl_sync(0xffffffffu, y0, ql) + r;
-        const bool inb = ok && (q0 + ql < p.nq) && xx >= 0 && xx < W && yy >= 0 && yy < H;
-        const float* src = base + (size_t)(q0 + ql) * plane + (size_t)(inb ? yy * W + xx : 0);
-        dst[j] = ok ? ql * STRIDE + r * WIN + col : -1;
-        if (CP_ASYNC) {
-          if (ok) cp_async_4(win + dst[j], inb ? src : base, inb);
-        } else {
-          v[j] = inb ? __ldg(src) : 0.f;
+    for (int j = 0; j < G::ROWS_PER_THREAD; ++j) {
+      const int s = tid + j * kLookupThreads;
+      const int sq = s / WIN, r = s - sq * WIN;      // sq = slot*16 + ql
+      const int slot = sq >> 4, ql = sq & 15;
+      const int lvl = lv0 + slot;
+      const bool live = s < G::ROWS && lvl < p.num_levels && (q0 + ql) < p.nq;
+      const int lvc = live ? lvl : 0;
+      const int H = p.lh[lvc], W = p.lw[lvc];
+      const int x0 = s_x0[sq & (kLevelsPerPass * kQueriesPerCta - 1)];
+      const int y = s_y0[sq & (kLevelsPerPass * kQueriesPerCta - 1)] + r;
+      const bool row_in = live && y >= 0 && y < H;
+      const float* row = p.level[lvc] + ((size_t)(q0 + ql) * H + (row_in ? y : 0)) * W;
+      if (VEC) {
+        const int xa = x0 & ~3;
+        const int sh = x0 - xa;
+#pragma unroll
+        for (int k = 0; k < G::NCHUNK; ++k) {
+          const int xc = xa + 4 * k;
+          const bool need = (4 * k < sh + WIN);  // the last chunk is only touched for the largest shifts
+          float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (row_in && need && xc >= 0 && xc < W) c = __ldg(reinterpret_cast<const float4*>(row + xc));
+          vals[j][4 * k] = c.x;
+          vals[j][4 * k + 1] = c.y;
+          vals[j][4 * k + 2] = c.z;
+          vals[j][4 * k + 3] = c.w;
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < WIN; ++c) {
+          const int xx = x0 + c;
+          vals[j][c] = (row_in && xx >= 0 && xx < W) ? __ldg(row + xx) : 0.f;
         }
       }
-      if (!CP_ASYNC) {
+    }
 #pragma unroll
-        for (int j = 0; j < UNROLL; ++j)
-          if (dst[j] >= 0) win[dst[j]] = v[j];
+    for (int j = 0; j < G::ROWS_PER_THREAD; ++j) {
+      const int s = tid + j * kLookupThreads;
+      if (s >= G::ROWS) continue;
+      const int sq = s / WIN, r = s - sq * WIN;
+      float* d = win + sq * STRIDE + r * WIN;
+      if (VEC) {
+        const int sh = s_x0[sq] & 3;  // x0 - (x0 & ~3)
+#pragma unroll
+        for (int k = 0; k < 4 * G::NCHUNK; ++k) {
+          const int c = k - sh;
+          if (c >= 0 && c < WIN) d[c] = vals[j][k];
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < WIN; ++c) d[c] = vals[j][c];
       }
     }
-    if (CP_ASYNC) asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
-    __syncwarp();
+    __syncthreads();
 
-    // ---- compute phase: lane = query; taps formed row by row, stored coalesced across queries
-    const float* my = win + lane * STRIDE;
-    float* o = p.out + ((size_t)b * channels + (size_t)lvl * P * P) * p.hw1 + pix;
-    const float bx = 1.f - ax, by = 1.f - ay;
-    float prev[P], cur[P];
+    // ---- compute phase: warp = level slot, lane = (half, query); taps stored coalesced across queries
+    {
+      const int slot = tid >> 5, lane = tid & 31;
+      const int ql = lane & 15, half = lane >> 4;
+      const int lvl = lv0 + slot;
+      const int q = q0 + ql;
+      if (lvl < p.num_levels && q < p.nq) {
+        const int b = q / p.hw1, pix = q - b * p.hw1;
+        const float* my = win + (slot * kQueriesPerCta + ql) * STRIDE;
+        const float ax = s_ax[slot * kQueriesPerCta + ql], ay = s_ay[slot * kQueriesPerCta + ql];
+        const float bx = 1.f - ax, by = 1.f - ay;
+        float* o = p.out + ((size_t)b * channels + (size_t)lvl * P * P) * p.hw1 + pix;
+        constexpr int HALF = (P + 1) / 2;              // output rows [0, HALF) and [HALF, P)
+        const int r_begin = half ? HALF : 0;
+        const int r_end = half ? P : HALF;             // window rows r_begin .. r_end (inclusive)
+        float prev[P], cur[P];
 #pragma unroll
-    for (int r = 0; r < WIN; ++r) {
-      float v[WIN];
+        for (int rr = 0; rr <= HALF; ++rr) {
+          const int r = r_begin + rr;
+          if (r <= r_end) {
+            float v[WIN];
 #pragma unroll
-      for (int c = 0; c < WIN; ++c) v[c] = my[r * WIN + c];
+            for (int c = 0; c < WIN; ++c) v[c] = my[r * WIN + c];
 #pragma unroll
-      for (int xo = 0; xo < P; ++xo) cur[xo] = fmaf(ax, v[xo + 1], bx * v[xo]);
-      if (r > 0 && valid) {
+            for (int xo = 0; xo < P; ++xo) cur[xo] = fmaf(ax, v[xo + 1], bx * v[xo]);
+            if (rr > 0) {
 #pragma unroll
-        for (int xo = 0; xo < P; ++xo)  // channel = (xoff+r)*P + (yoff+r): x walks slowest (corr.py:37-43)
-          o[(size_t)(xo * P + (r - 1)) * p.hw1] = fmaf(ay, cur[xo], by * prev[xo]);
+              for (int xo = 0; xo < P; ++xo)  // channel = (xoff+r)*P + (yoff+r): x walks slowest (corr.py:37-43)
+                o[(size_t)(xo * P + (r - 1)) * p.hw1] = fmaf(ay, cur[xo], by * prev[xo]);
+            }
+#pragma unroll
+            for (int xo = 0; xo < P; ++xo) prev[xo] = cur[xo];
+          }
+        }
       }
-#pragma unroll
-      for (int xo = 0; xo < P; ++xo) prev[xo] = cur[xo];
     }
-    __syncwarp();
+    __syncthreads();  // the next pass (more than 4 levels) reuses the shared buffers
   }
 }
 
 template <int R>
-static int launch_lookup(const LookupParams& p, int flags, cudaStream_t stream) {
-  using G = LookupGeom<R>;
+static int launch_lookup(const LookupParams& p, bool vec, cudaStream_t stream) {
   const int grid = ceil_div(p.nq, kQueriesPerCta);
-  if (flags & 1) {
-    WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_lookup_kernel<R, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)G::SMEM));
-    corr_lookup_kernel<R, true><<<grid, kLookupWarps * 32, G::SMEM, stream>>>(p);
-  } else {
-    WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_lookup_kernel<R, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)G::SMEM));
-    corr_lookup_kernel<R, false><<<grid, kLookupWarps * 32, G::SMEM, stream>>>(p);
-  }
+  if (vec)
+    corr_lookup_kernel<R, true><<<grid, kLookupThreads, 0, stream>>>(p);
+  else
+    corr_lookup_kernel<R, false><<<grid, kLookupThreads, 0, stream>>>(p);
   return launch_status("corr_lookup_kernel");
 }
 
@@ -170,6 +204,7 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   WOFT_REQUIRE((long long)batch * h1 * w1 < (1ll << 31), "woft_corr_lookup: too many query pixels");
   LookupParams p{};
   int h = h2, w = w2;
+  bool vec = (flags & 1) == 0;  // flags bit 0 forces the scalar load path (testing)
   for (int l = 0; l < num_levels; ++l) {
     // the reference divides by (W-1), (H-1) and returns NaN for 1-pixel maps (utils.py:63-64)
     WOFT_REQUIRE(h >= 2 && w >= 2, "woft_corr_lookup: level %d is %dx%d; every level must be at least 2x2", l, h, w);
@@ -177,6 +212,7 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
     p.level[l] = levels[l];
     p.lh[l] = h;
     p.lw[l] = w;
+    vec = vec && (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0);
     h /= 2;
     w /= 2;
   }
@@ -187,9 +223,9 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   p.hw1 = h1 * w1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (radius) {
-    case 1: return launch_lookup<1>(p, flags, s);
-    case 2: return launch_lookup<2>(p, flags, s);
-    case 3: return launch_lookup<3>(p, flags, s);
-    default: return launch_lookup<4>(p, flags, s);
+    case 1: return launch_lookup<1>(p, vec, s);
+    case 2: return launch_lookup<2>(p, vec, s);
+    case 3: return launch_lookup<3>(p, vec, s);
+    default: return launch_lookup<4>(p, vec, s);
   }
 }

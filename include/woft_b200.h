@@ -55,7 +55,7 @@ enum woft_h_method {
 int woft_abi_version(void);
 const char* woft_last_error(void);
 
-/* Bytes of scratch woft_corr_pyramid needs for this shape and mode (0 for WOFT_CORR_FP32_SIMT). */
+/* Bytes of scratch woft_corr_pyramid needs for this shape and mode (0 if an extent is not positive). */
 size_t woft_corr_workspace_bytes(int batch, int channels, int height, int width, int mode);
 
 /* K1 + K2.  Replaces CorrBlock.__init__ + CorrBlock.corr
@@ -71,6 +71,23 @@ size_t woft_corr_workspace_bytes(int batch, int channels, int height, int width,
 int woft_corr_pyramid(const float* fmap1, const float* fmap2, int batch, int channels, int height, int width,
                       int num_levels, float* const* levels, float* row_mean, void* workspace,
                       size_t workspace_bytes, int mode, void* stream);
+
+/* woft_corr_pyramid for callers that cannot allocate.  No counterpart in the reference (there PyTorch allocates
+ * whatever an op needs).  It is meant for code that only holds the input and output buffers it was handed and
+ * has no device allocator to turn to -- a plug-in inside a host application that owns all GPU memory, a thin
+ * binding from another language -- or that may not pay for cudaMalloc/cudaFree inside its frame loop.
+ * Arguments are those of woft_corr_pyramid without the workspace: the scratch lives in a fixed 32 MiB device
+ * array inside the library (held by every GPU that loads the library, until the process exits).
+ *   - Shapes/modes whose woft_corr_workspace_bytes() exceeds 32 MiB are refused with WOFT_ERR_WORKSPACE; one
+ *     1280x720 frame pair (90x160x256 feature maps) fits in the fp32, tf32 and bf16 modes, 3xTF32 does not.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that first
+ *     call with the device current and outside any stream capture.
+ *   - All calls on a device share the one array.  Calls whose GPU work can overlap (different streams, or
+ *     different host threads) race on it: serialise them.  Nothing is carried over between calls: the status
+ *     word is cleared and every scratch byte that is read has been rewritten by the same call.
+ *   - No cudaMalloc, cudaFree or other allocating call is made. */
+int woft_corr_pyramid_static(const float* fmap1, const float* fmap2, int batch, int channels, int height, int width,
+                             int num_levels, float* const* levels, float* row_mean, int mode, void* stream);
 
 /* Synchronises `stream` and reports whether the last woft_corr_pyramid on `workspace` ran to completion.  The
  * tensor-core kernel bounds every pipeline wait (2 s) and raises a flag in the workspace instead of hanging;

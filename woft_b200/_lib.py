@@ -26,6 +26,8 @@ SIGNATURES = {
     "woft_corr_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
     "woft_corr_pyramid": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, _FLOATP_ARRAY, c_void_p,
                                   c_void_p, c_size_t, c_int, c_void_p]),
+    "woft_corr_pyramid_static": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, _FLOATP_ARRAY, c_void_p,
+                                         c_int, c_void_p]),
     "woft_corr_check": (c_int, [c_void_p, c_void_p]),
     "woft_corr_lookup": (c_int, [_FLOATP_ARRAY, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                  c_int, c_void_p]),

@@ -106,24 +106,35 @@ __global__ void __launch_bounds__(256) channel_mean_kernel(const float* __restri
   }
 }
 
-// row_mean[b, q] = sum_c fmap1[b, c, q] * mean2[b, c] * scale
-__global__ void row_mean_kernel(const float* __restrict__ f1, const float* __restrict__ mean2,
-                                float* __restrict__ row_mean, int C, int HW, float denom) {
+// row_mean[b, q] = sum_c fmap1[b, c, q] * mean2[b, c] / sqrt(C): 32 queries x 8 channel groups per CTA
+__global__ void __launch_bounds__(256) row_mean_kernel(const float* __restrict__ f1, const float* __restrict__ mean2,
+                                                       float* __restrict__ row_mean, int C, int HW, float denom) {
+  __shared__ float part[8][33];
   const int b = blockIdx.y;
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= HW) return;
+  const int qx = threadIdx.x & 31, cg = threadIdx.x >> 5;
+  const int q = blockIdx.x * 32 + qx;
   const float* a = f1 + (size_t)b * C * HW + q;
   const float* m = mean2 + (size_t)b * C;
   float s = 0.f;
-  for (int c = 0; c < C; ++c) s = fmaf(__ldg(a + (size_t)c * HW), __ldg(m + c), s);
-  row_mean[(size_t)b * HW + q] = s / denom;
+  if (q < HW) {
+#pragma unroll 4
+    for (int c = cg; c < C; c += 8) s = fmaf(__ldg(a + (size_t)c * HW), __ldg(m + c), s);
+  }
+  part[cg][qx] = s;
+  __syncthreads();
+  if (cg == 0 && q < HW) {
+    float t = 0.f;
+#pragma unroll
+    for (int g = 0; g < 8; ++g) t += part[g][qx];
+    row_mean[(size_t)b * HW + q] = t / denom;
+  }
 }
 
 int launch_row_mean(const float* fmap1, const float* fmap2, int B, int C, int HW, float* row_mean, float* mean2,
                     cudaStream_t stream) {
   channel_mean_kernel<<<B * C, 256, 0, stream>>>(fmap2, mean2, HW);
-  dim3 grid(ceil_div(HW, 128), B);
-  row_mean_kernel<<<grid, 128, 0, stream>>>(fmap1, mean2, row_mean, C, HW, sqrtf(float(C)));
+  dim3 grid(ceil_div(HW, 32), B);
+  row_mean_kernel<<<grid, 256, 0, stream>>>(fmap1, mean2, row_mean, C, HW, sqrtf(float(C)));
   return launch_status("row_mean kernels");
 }
 

@@ -82,11 +82,15 @@ __device__ __forceinline__ float round_tf32(float x) {
 }
 
 template <int MODE>  // 1 tf32, 2 tf32 hi/lo, 3 bf16
-__global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src, void* __restrict__ dst, int C,
+__global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src1, const float* __restrict__ src2,
+                                                   void* __restrict__ dst1, void* __restrict__ dst2, int B, int C,
                                                    int HW, int Kp, size_t plane_elems, int* flag) {
   __shared__ float tile[32][33];
   if (flag && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && threadIdx.x == 0) *flag = 0;
-  const int b = blockIdx.z;
+  const bool second = (int)blockIdx.z >= B;  // grid.z = 2B: both feature maps in one launch
+  const float* __restrict__ src = second ? src2 : src1;
+  void* __restrict__ dst = second ? dst2 : dst1;
+  const int b = second ? blockIdx.z - B : blockIdx.z;
   const int hw0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
   const float* s = src + (size_t)b * C * HW;
@@ -493,18 +497,14 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
 
   // ---- pack both fmaps into K-major planes (also clears the abort flag)
   {
-    dim3 grid(ceil_div(HW, 32), L.Kp / 32, B);
+    dim3 grid(ceil_div(HW, 32), L.Kp / 32, 2 * B);
     const size_t plane_elems = L.plane_bytes / L.elem_bytes;
-    if (mode == WOFT_CORR_BF16) {
-      pack_kernel<3><<<grid, 256, 0, stream>>>(fmap1, packA, C, HW, L.Kp, plane_elems, flag);
-      pack_kernel<3><<<grid, 256, 0, stream>>>(fmap2, packB, C, HW, L.Kp, plane_elems, nullptr);
-    } else if (mode == WOFT_CORR_TF32X3) {
-      pack_kernel<2><<<grid, 256, 0, stream>>>(fmap1, packA, C, HW, L.Kp, plane_elems, flag);
-      pack_kernel<2><<<grid, 256, 0, stream>>>(fmap2, packB, C, HW, L.Kp, plane_elems, nullptr);
-    } else {
-      pack_kernel<1><<<grid, 256, 0, stream>>>(fmap1, packA, C, HW, L.Kp, plane_elems, flag);
-      pack_kernel<1><<<grid, 256, 0, stream>>>(fmap2, packB, C, HW, L.Kp, plane_elems, nullptr);
-    }
+    if (mode == WOFT_CORR_BF16)
+      pack_kernel<3><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
+    else if (mode == WOFT_CORR_TF32X3)
+      pack_kernel<2><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
+    else
+      pack_kernel<1><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
     int rc = launch_status("pack_kernel");
     if (rc != WOFT_OK) return rc;
   }

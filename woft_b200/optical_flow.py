@@ -119,8 +119,12 @@ def sigmoid(xs):
 
 
 class RAFTWrapper:
-    def __init__(self, config, device="cuda", use_cuda_graph=True, corr_block=None):
+    def __init__(self, config, device="cuda", use_cuda_graph=True, corr_block=None, channels_last=True,
+                 cudnn_benchmark=True):
         self.C = config
+        self.channels_last = channels_last
+        if cudnn_benchmark:
+            torch.backends.cudnn.benchmark = True  # fixed shapes per sequence: let cuDNN pick its fastest kernels
         params = _cfg(config, "class_params")
         raft_type = _cfg(config, "raft_type", "weighted")
         if raft_type not in ("orig", "weighted"):
@@ -141,6 +145,10 @@ class RAFTWrapper:
         net = WeightedRAFT(structure, with_weights=(raft_type == "weighted"))
         net.load_state_dict(self._load_weights(net), strict=not _cfg(config, "non_strict_loading", False))
         self.net = net.to(self.device).requires_grad_(False).eval()
+        if channels_last:
+            # cuDNN's sm_100 convolution kernels are NHWC: keep weights and activations channels-last so it does not
+            # wrap every convolution in a pair of layout-conversion kernels
+            self.net = self.net.to(memory_format=torch.channels_last)
         self.iters = int(_cfg(config, "iters", 12))
         self.use_cuda_graph = use_cuda_graph
         self.corr_block = corr_block
@@ -233,7 +241,8 @@ class RAFTWrapper:
                 raise ValueError(f"invalid padding_mode '{padding_mode}'")
             padder = _PADDERS[padding_mode](dst.shape)
             src, dst = padder.pad(src, dst)
-            out = self._forward(src.contiguous(), dst.contiguous())
+            fmt = torch.channels_last if self.channels_last else torch.contiguous_format
+            out = self._forward(src.contiguous(memory_format=fmt), dst.contiguous(memory_format=fmt))
             if self.raft_type == "orig":
                 flow_up, weights_up = out[1], None
             else:

@@ -210,8 +210,8 @@ class WeightedRAFT(nn.Module):
 
     def encode(self, image1, image2):
         """weighted_raft.py:194-219: scale to [-1,1], feature maps of both frames, context of frame 1."""
-        image1 = (2 * (image1 / 255.0) - 1.0).contiguous()
-        image2 = (2 * (image2 / 255.0) - 1.0).contiguous()
+        image1 = 2 * (image1 / 255.0) - 1.0   # memory format (NCHW or channels-last) is kept as given
+        image2 = 2 * (image2 / 255.0) - 1.0
         fmap1, fmap2 = self.fnet(torch.cat([image1, image2], dim=0)).float().chunk(2, dim=0)
         net, inp = torch.split(self.cnet(image1), [self.hidden_dim, self.context_dim], dim=1)
         return fmap1.contiguous(), fmap2.contiguous(), torch.tanh(net), torch.relu(inp)

@@ -133,6 +133,24 @@ def time_launches(fn, n, scratch, torch):
     return total / n
 
 
+def time_burst(fns, n, scratch, torch):
+    """Average device time (s) per call of a burst of calls issued back to back between ONE event pair, L2 flushed
+    before the burst: launch and event overheads (a few microseconds) are amortised over len(fns) launches."""
+    total = 0.0
+    for i in range(n + 2):
+        flush_l2(scratch)
+        torch.cuda._sleep(2_000_000)  # ~1 ms: the host enqueues the whole burst while the device idles here
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for fn in fns:
+            fn()
+        b.record()
+        b.synchronize()
+        if i >= 2:
+            total += a.elapsed_time(b) * 1e-3
+    return total / n / len(fns)
+
+
 def kernel_rooflines(torch, dev, corr_mode, peaks):
     """K3 (the headline), K1+K2 and K4 timed alone at BASELINE config sizes."""
     from woft_b200 import least_squares_H as lsq
@@ -153,9 +171,22 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
     level_bytes = sum(l.numel() * 4 for l in blk.corr_pyramid)
     corr_bytes = 2 * f1.numel() * 4 + level_bytes
     ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W, device=dev), indexing="ij")
-    coords = torch.stack([xs, ys]).float()[None] + torch.randn((1, 2, H, W), generator=g, device=dev) * 2.0
-    t_lookup = time_launches(lambda: blk(coords), 20, scratch, torch)
+    grid = torch.stack([xs, ys]).float()[None]
+    # coordinates of the 13 lookups of one flow pass: a smooth sub-pixel flow that grows by ~0.3 px per iteration
+    base_flow = torch.randn((1, 2, H, W), generator=g, device=dev) * 2.0
+    coords_seq = [grid + base_flow * (0.4 + 0.05 * i) for i in range(ITERS + 1)]
+    t_lookup_cold = time_launches(lambda: blk(coords_seq[-1]), 20, scratch, torch)
+    t_lookup_pass = time_burst([(lambda c=c: blk(c)) for c in coords_seq], 10, scratch, torch)
     lookup_bytes = LOOKUP_BYTES_PER_QUERY * B * H * W
+
+    # the same kernel on a batch of 4 frame pairs (4.4 GB of pyramid), cold: a launch long enough to hide overheads
+    B4 = 4
+    f1b = torch.randn((B4, C, H, W), generator=g, device=dev)
+    f2b = torch.randn((B4, C, H, W), generator=g, device=dev)
+    blk4 = CorrBlock(f1b, f2b, mode=corr_mode)
+    coords4 = grid.repeat(B4, 1, 1, 1) + torch.randn((B4, 2, H, W), generator=g, device=dev) * 2.0
+    t_lookup_b4 = time_launches(lambda: blk4(coords4), 10, scratch, torch)
+    del blk4, f1b, f2b
 
     Bh, Nh = 1024, 14400  # BASELINE config 3
     p1 = torch.rand((Bh, Nh, 2), generator=g, device=dev) * torch.tensor([1280.0, 720.0], device=dev)
@@ -165,20 +196,31 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
     h_bytes = Bh * Nh * 20 + Bh * 36
     del scratch
     hbm = peaks["hbm_gbs"]
+    traffic = {}
+    tf = ROOT / "profiles" / "traffic.json"  # dram__bytes_read+write per launch from the committed ncu --set full captures
+    if tf.exists():
+        traffic = json.loads(tf.read_text())
 
-    def entry(bytes_, t):
+    def entry(bytes_, t, key=None):
         a = bytes_ / t / 1e9
         return {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
-                "traffic": None, "us_per_launch": round(t * 1e6, 2), "algorithmic_bytes": bytes_}
+                "traffic": traffic.get(key), "us_per_launch": round(t * 1e6, 2), "algorithmic_bytes": bytes_}
 
-    k3 = entry(lookup_bytes, t_lookup)
-    k3["kernel"] = "corr_lookup_kernel<4> (K3), 14400 queries x 4 levels, L2 flushed before every launch"
-    k1 = entry(corr_bytes, t_build)
+    k3 = entry(lookup_bytes, t_lookup_pass, "corr_lookup")
+    k3["kernel"] = ("corr_lookup_kernel<4> (K3): 14400 queries x 4 levels per launch; average over the 13 launches of one "
+                    "flow pass issued back to back between one CUDA-event pair on the launch stream, L2 flushed before "
+                    "the pass (first launch cold, the rest see what L2 kept, as inside a frame)")
+    k3_cold = entry(lookup_bytes, t_lookup_cold, "corr_lookup")
+    k3_cold["kernel"] = "K3, one launch per event pair, L2 flushed before every launch (includes ~5 us of launch/event overhead)"
+    k3_b4 = entry(lookup_bytes * B4, t_lookup_b4)
+    k3_b4["kernel"] = "K3 on a batch of 4 frame pairs (57600 queries, 4.4 GB pyramid), L2 flushed before every launch"
+    k1 = entry(corr_bytes, t_build, "corr_pyramid_" + corr_mode)
     k1["kernel"] = f"pack + corr_tc_kernel + row-mean (K1+K2), mode {corr_mode}; 106.2 GFLOP"
     k1["tflops"] = round(2.0 * (H * W) ** 2 * C / t_build / 1e12, 1)
-    k4 = entry(h_bytes, t_h)
+    k4 = entry(h_bytes, t_h, "homography_fit_config3")
     k4["kernel"] = "homography_fit_kernel (K4), B=1024 x N=14400, nonhomogeneous"
-    return k3, {"corr_pyramid": k1, "homography_fit_config3": k4}, peaks["source"]
+    return k3, {"corr_lookup_cold": k3_cold, "corr_lookup_batch4_cold": k3_b4, "corr_pyramid": k1,
+                "homography_fit_config3": k4}, peaks["source"]
 
 
 def load_peaks():
@@ -286,11 +328,15 @@ def run_woft(args, rank, world, local):
         start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         passes0 = trk.flow_passes
         with ClockSampler(local) as sampler:
+            if name == "device":
+                torch.cuda.profiler.start()  # `ncu --profile-from-start off` then lists exactly the timed steps
             start.record()
             for i in range(args.steps):
                 step(i)
             stop.record()
             torch.cuda.synchronize(dev)
+            if name == "device":
+                torch.cuda.profiler.stop()
         barrier()
         from woft_b200.sharding import max_over_ranks
         seconds = max_over_ranks(start.elapsed_time(stop) * 1e-3, device=dev)

@@ -45,6 +45,16 @@ for mode in ("tf32", "tf32x3", "bf16"):
 blk = blocks["tf32"]
 timed("corr_lookup flags=0 (float4 rows)", lambda: blk(coords, flags=0), 5)
 timed("corr_lookup flags=1 (scalar rows)", lambda: blk(coords, flags=1), 5)
+# 13 lookups back to back as in one flow pass (L2 warm after the first): amortises the ~5 us event/launch overhead
+cs = [coords + 0.3 * i for i in range(13)]
+timed("13 x corr_lookup (one flow pass)", lambda: [blk(c) for c in cs], 5)
+if "--l2gran" in sys.argv:
+    import ctypes
+    rt = ctypes.CDLL("libcudart.so.12")
+    for gran in (32, 64, 128):
+        rc = rt.cudaDeviceSetLimit(5, ctypes.c_size_t(gran))  # cudaLimitMaxL2FetchGranularity
+        timed(f"corr_lookup, L2 fetch granularity {gran} (rc {rc})", lambda: blk(coords), 5)
+        timed(f"corr_pyramid[tf32], granularity {gran}", lambda: CorrBlock(f1, f2, mode="tf32"), 2)
 f1b = torch.randn((4, C, H, W), generator=g, device=dev)
 del blocks["tf32x3"], blocks["bf16"]
 Bh, Nh = 1024, 14400

@@ -35,6 +35,8 @@
 #include <cuda.h>
 #include <cuda_bf16.h>
 
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -45,12 +47,11 @@ constexpr int TH = 8, TW = 32;
 constexpr int BN = TH * TW;
 constexpr int A_STAGE = BM * 128;  // bytes: 128 rows of one 128-byte K row
 constexpr int B_STAGE = BN * 128;
-constexpr int STAGES = 3;
+constexpr int MAX_STAGES = 4;
 constexpr int SLOT = 16384;
-constexpr int NSLOT = 3;
 constexpr int TC_THREADS = 192;
 constexpr int EPI_THREADS = 128;
-constexpr int TC_SMEM = STAGES * (A_STAGE + B_STAGE) + NSLOT * SLOT + 256 + 1024;  // + barriers + alignment slack
+constexpr int TC_SMEM_LIMIT = 232448;  // 227 KB opt-in maximum per CTA
 constexpr int kMaxTcLevels = 4;
 
 struct CorrTcParams {
@@ -68,6 +69,10 @@ struct CorrTcParams {
   int k_elems;    // elements per 128-byte K row (32 tf32 / 64 bf16)
   int n_pairs;    // 1, or 3 for the hi/lo split
   int bf16;
+  int a_resident; // 1: the A tile (all k blocks) stays in shared memory while a CTA walks `unit` consecutive N tiles
+  int unit;       // tiles per work unit (consecutive tile ids share b and the M tile)
+  int stages;     // operand stages (A+B, or B only when A is resident)
+  int nslot;      // epilogue staging ring slots
   float scale;
   int* abort_flag;
 };
@@ -145,6 +150,14 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t saddr) {
   return d;
 }
 
+// after committing a store group: with 3 slots one older group may still be reading its slot, with 2 none may
+__device__ __forceinline__ void store_ring_wait(int nslot) {
+  if (nslot >= 3)
+    ptx::tma_store_wait_read<1>();
+  else
+    ptx::tma_store_wait_read<0>();
+}
+
 struct TileCoord {
   int b, m0, h0, w0;
 };
@@ -179,6 +192,13 @@ __device__ __forceinline__ void direct_row(float* level, int lh, int lw, int HW,
                                            const float* v) {
   if (m >= HW || h >= lh) return;
   float* dst = level + (((size_t)b * HW + m) * lh + h) * lw;
+  if ((lw & 3) == 0 && (reinterpret_cast<uintptr_t>(level) & 15) == 0) {
+    // rows are 16-byte aligned and a 4-float chunk is wholly inside or outside the map
+#pragma unroll
+    for (int j = 0; j < NV; j += 4)
+      if (w0 + j < lw) *reinterpret_cast<float4*>(dst + w0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    return;
+  }
 #pragma unroll
   for (int j = 0; j < NV; ++j)
     if (w0 + j < lw) dst[w0 + j] = v[j];
@@ -187,15 +207,18 @@ __device__ __forceinline__ void direct_row(float* level, int lh, int lw, int HW,
 __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_constant__ CorrTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sA = smem;
-  uint8_t* sB = sA + STAGES * A_STAGE;
+  const int STAGES = p.stages, NSLOT = p.nslot;
+  uint8_t* sA = smem;  // streamed: STAGES x 16 KB; resident: k_blocks x 16 KB
+  uint8_t* sB = sA + (p.a_resident ? p.k_blocks : STAGES) * A_STAGE;
   uint8_t* ring = sB + STAGES * B_STAGE;
   uint64_t* bars = reinterpret_cast<uint64_t*>(ring + NSLOT * SLOT);
-  uint64_t* full = bars;                 // [STAGES] TMA -> MMA
-  uint64_t* empty = bars + STAGES;       // [STAGES] MMA -> TMA
-  uint64_t* tfull = bars + 2 * STAGES;   // [2] MMA -> epilogue
-  uint64_t* tempty = tfull + 2;          // [2] epilogue -> MMA
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* full = bars;                     // [MAX_STAGES] TMA -> MMA
+  uint64_t* empty = bars + MAX_STAGES;       // [MAX_STAGES] MMA -> TMA
+  uint64_t* tfull = bars + 2 * MAX_STAGES;   // [2] MMA -> epilogue
+  uint64_t* tempty = tfull + 2;              // [2] epilogue -> MMA
+  uint64_t* a_full = tempty + 2;             // resident A tile landed
+  uint64_t* a_empty = a_full + 1;            // every MMA reading the resident A tile has completed
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(a_empty + 1);
   volatile int* epi_go = reinterpret_cast<volatile int*>(tmem_ptr + 1);
 
   const int warp = threadIdx.x >> 5;
@@ -210,6 +233,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
       ptx::mbar_init(tfull + i, 1);
       ptx::mbar_init(tempty + i, EPI_THREADS);
     }
+    ptx::mbar_init(a_full, 1);
+    ptx::mbar_init(a_empty, 1);
     ptx::fence_mbar_init();
     ptx::prefetch_tmap(&p.tmA);
     ptx::prefetch_tmap(&p.tmB);
@@ -230,22 +255,56 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       bool alive = true;
-      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x) {
-        const TileCoord tc = decode_tile(p, t);
-        for (int ks = 0; ks < k_steps; ++ks) {
-          const int kb = ks / p.n_pairs, pr = ks - kb * p.n_pairs;
-          const int plane_a = (pr == 2) ? 1 : 0, plane_b = (pr == 1) ? 1 : 0;  // hi*hi, hi*lo, lo*hi
-          if (!wait_or_abort(empty + stage, phase ^ 1u, p.abort_flag)) {
-            alive = false;
-            break;
+      int cur_a = -1;          // (b, M tile) whose A tile is resident
+      uint32_t a_loads = 0;
+      for (int chunk = blockIdx.x; chunk * p.unit < p.total_tiles && alive; chunk += gridDim.x) {
+        const int t_end = min((chunk + 1) * p.unit, p.total_tiles);
+        for (int t = chunk * p.unit; t < t_end && alive; ++t) {
+          const TileCoord tc = decode_tile(p, t);
+          const int a_id = tc.b * p.m_tiles + tc.m0 / BM;
+          const bool reload = p.a_resident && a_id != cur_a;
+          cur_a = a_id;
+          // with a resident A tile, first queue as many B stages of this tile as the ring takes, then swap A in
+          const int pre = reload ? min(STAGES, k_steps) : 0;
+          for (int ks = 0; ks < k_steps; ++ks) {
+            if (reload && ks == pre) {
+              if (!wait_or_abort(a_empty, (a_loads & 1u) ^ 1u, p.abort_flag)) {
+                alive = false;
+                break;
+              }
+              ptx::mbar_arrive_expect_tx(a_full, uint32_t(p.k_blocks) * A_STAGE);
+              for (int kb = 0; kb < p.k_blocks; ++kb)
+                ptx::tma_load_3d(sA + kb * A_STAGE, &p.tmA, a_full, kb * p.k_elems, tc.m0, tc.b);
+              ++a_loads;
+            }
+            const int kb = ks / p.n_pairs, pr = ks - kb * p.n_pairs;
+            const int plane_a = (pr == 2) ? 1 : 0, plane_b = (pr == 1) ? 1 : 0;  // hi*hi, hi*lo, lo*hi
+            if (!wait_or_abort(empty + stage, phase ^ 1u, p.abort_flag)) {
+              alive = false;
+              break;
+            }
+            if (p.a_resident) {
+              ptx::mbar_arrive_expect_tx(full + stage, B_STAGE);
+            } else {
+              ptx::mbar_arrive_expect_tx(full + stage, A_STAGE + B_STAGE);
+              ptx::tma_load_3d(sA + stage * A_STAGE, &p.tmA, full + stage, kb * p.k_elems, tc.m0, plane_a * p.B + tc.b);
+            }
+            ptx::tma_load_4d(sB + stage * B_STAGE, &p.tmB, full + stage, kb * p.k_elems, tc.w0, tc.h0,
+                             plane_b * p.B + tc.b);
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
           }
-          ptx::mbar_arrive_expect_tx(full + stage, A_STAGE + B_STAGE);
-          ptx::tma_load_3d(sA + stage * A_STAGE, &p.tmA, full + stage, kb * p.k_elems, tc.m0, plane_a * p.B + tc.b);
-          ptx::tma_load_4d(sB + stage * B_STAGE, &p.tmB, full + stage, kb * p.k_elems, tc.w0, tc.h0,
-                           plane_b * p.B + tc.b);
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1u;
+          if (reload && alive && pre == k_steps) {  // k_steps <= STAGES: the A swap comes after all B loads
+            if (!wait_or_abort(a_empty, (a_loads & 1u) ^ 1u, p.abort_flag)) {
+              alive = false;
+              break;
+            }
+            ptx::mbar_arrive_expect_tx(a_full, uint32_t(p.k_blocks) * A_STAGE);
+            for (int kb = 0; kb < p.k_blocks; ++kb)
+              ptx::tma_load_3d(sA + kb * A_STAGE, &p.tmA, a_full, kb * p.k_elems, tc.m0, tc.b);
+            ++a_loads;
           }
         }
       }
@@ -259,35 +318,55 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
       uint32_t phase = 0;
       bool alive = true;
       int it = 0;
-      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x, ++it) {
-        const int buf = it & 1;
-        const uint32_t use = uint32_t(it >> 1);
-        if (!wait_or_abort(tempty + buf, (use & 1u) ^ 1u, p.abort_flag)) break;
-        ptx::tc_fence_after_sync();
-        const uint32_t d_tmem = tmem_base + uint32_t(buf * BN);
-        for (int ks = 0; ks < k_steps; ++ks) {
-          if (!wait_or_abort(full + stage, phase, p.abort_flag)) {
+      int cur_a = -1;
+      uint32_t a_loads = 0;
+      for (int chunk = blockIdx.x; chunk * p.unit < p.total_tiles && alive; chunk += gridDim.x) {
+        const int t_end = min((chunk + 1) * p.unit, p.total_tiles);
+        for (int t = chunk * p.unit; t < t_end && alive; ++t, ++it) {
+          if (p.a_resident) {
+            const TileCoord tc = decode_tile(p, t);
+            const int a_id = tc.b * p.m_tiles + tc.m0 / BM;
+            if (a_id != cur_a) {
+              if (cur_a >= 0) ptx::mma_commit(a_empty);  // everything issued so far has read the old A tile
+              cur_a = a_id;
+              if (!wait_or_abort(a_full, a_loads & 1u, p.abort_flag)) break;
+              ++a_loads;
+              ptx::tc_fence_after_sync();
+            }
+          }
+          const int buf = it & 1;
+          const uint32_t use = uint32_t(it >> 1);
+          if (!wait_or_abort(tempty + buf, (use & 1u) ^ 1u, p.abort_flag)) {
             alive = false;
             break;
           }
           ptx::tc_fence_after_sync();
-          const uint64_t da = make_kmajor_sw128_desc(ptx::smem_u32(sA + stage * A_STAGE));
-          const uint64_t db = make_kmajor_sw128_desc(ptx::smem_u32(sB + stage * B_STAGE));
+          const uint32_t d_tmem = tmem_base + uint32_t(buf * BN);
+          for (int ks = 0; ks < k_steps; ++ks) {
+            if (!wait_or_abort(full + stage, phase, p.abort_flag)) {
+              alive = false;
+              break;
+            }
+            ptx::tc_fence_after_sync();
+            const int a_slot = p.a_resident ? ks : stage;  // resident: k block ks of the A tile (n_pairs == 1)
+            const uint64_t da = make_kmajor_sw128_desc(ptx::smem_u32(sA + a_slot * A_STAGE));
+            const uint64_t db = make_kmajor_sw128_desc(ptx::smem_u32(sB + stage * B_STAGE));
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row: UMMA_K = 8 (tf32) / 16 (bf16)
-            const uint32_t acc = (ks > 0 || k > 0) ? 1u : 0u;
-            if (p.bf16)
-              ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-            else
-              ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+            for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row: UMMA_K = 8 (tf32) / 16 (bf16)
+              const uint32_t acc = (ks > 0 || k > 0) ? 1u : 0u;
+              if (p.bf16)
+                ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+              else
+                ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+            }
+            ptx::mma_commit(empty + stage);  // frees the stage once these MMAs have read it
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
           }
-          ptx::mma_commit(empty + stage);  // frees the stage once these MMAs have read it
-          if (++stage == STAGES) {
-            stage = 0;
-            phase ^= 1u;
-          }
+          if (alive) ptx::mma_commit(tfull + buf);
         }
-        if (alive) ptx::mma_commit(tfull + buf);
       }
     }
   } else {
@@ -299,13 +378,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
     const float scale = p.scale;
     uint32_t ev = 0;  // ring event counter (identical in all epilogue threads)
     int it = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+    bool go = true;
+    for (int chunk = blockIdx.x; chunk * p.unit < p.total_tiles && go; chunk += gridDim.x) {
+    const int t_end = min((chunk + 1) * p.unit, p.total_tiles);
+    for (int t = chunk * p.unit; t < t_end; ++t, ++it) {
       const TileCoord tc = decode_tile(p, t);
       const int buf = it & 1;
       const uint32_t use = uint32_t(it >> 1);
       if (issuer) *epi_go = wait_or_abort(tfull + buf, use & 1u, p.abort_flag) ? 1 : 0;
       ptx::named_bar_sync(1, EPI_THREADS);
-      if (*epi_go == 0) break;
+      if (*epi_go == 0) {
+        go = false;
+        break;
+      }
       ptx::tc_fence_after_sync();
       const int mq = tc.m0 + m;
 
@@ -332,7 +417,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
         if (issuer) {
           if (p.tma_ok[0] && tc.h0 + r < p.lh[0]) ptx::tma_store_4d(&p.tmOut[0], slot, tc.w0, tc.h0 + r, tc.m0, tc.b);
           ptx::tma_store_commit();
-          ptx::tma_store_wait_read<1>();
+          store_ring_wait(NSLOT);
         }
         ++ev;
         // 2x2 mean in avg_pool2d's summation order: ((a00 + a01) + a10) + a11, then * 0.25
@@ -357,20 +442,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
             else
               direct_row<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, tc.h0 / 2 + r1, tc.w0 / 2, l1[r1]);
           }
-          if (p.tma_ok[1]) ptx::fence_proxy_async_smem();
-          ptx::named_bar_sync(1, EPI_THREADS);
-          if (issuer) {
-            if (p.tma_ok[1]) {
+          if (p.tma_ok[1]) {  // (kernel parameter: uniform) no ring event when the level goes out by direct stores
+            ptx::fence_proxy_async_smem();
+            ptx::named_bar_sync(1, EPI_THREADS);
+            if (issuer) {
 #pragma unroll
               for (int rr = 0; rr < 2; ++rr) {
                 const int h1 = tc.h0 / 2 + half * 2 + rr;
                 if (h1 < p.lh[1]) ptx::tma_store_4d(&p.tmOut[1], slot + rr * 8192, tc.w0 / 2, h1, tc.m0, tc.b);
               }
+              ptx::tma_store_commit();
+              store_ring_wait(NSLOT);
             }
-            ptx::tma_store_commit();
-            ptx::tma_store_wait_read<1>();
+            ++ev;
           }
-          ++ev;
         }
       }
       if (p.num_levels > 2) {
@@ -396,23 +481,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
           else
             direct_row<4>(p.level[3], p.lh[3], p.lw[3], p.HW, tc.b, mq, tc.h0 / 8, tc.w0 / 8, l3);
         }
-        ptx::fence_proxy_async_smem();
-        ptx::named_bar_sync(1, EPI_THREADS);
-        if (issuer) {
-          if (p.tma_ok[2]) {
+        if (p.tma_ok[2] || (p.num_levels > 3 && p.tma_ok[3])) {
+          ptx::fence_proxy_async_smem();
+          ptx::named_bar_sync(1, EPI_THREADS);
+          if (issuer) {
+            if (p.tma_ok[2]) {
 #pragma unroll
-            for (int i = 0; i < 2; ++i) {
-              const int h2 = tc.h0 / 4 + i;
-              if (h2 < p.lh[2]) ptx::tma_store_4d(&p.tmOut[2], slot + i * 4096, tc.w0 / 4, h2, tc.m0, tc.b);
+              for (int i = 0; i < 2; ++i) {
+                const int h2 = tc.h0 / 4 + i;
+                if (h2 < p.lh[2]) ptx::tma_store_4d(&p.tmOut[2], slot + i * 4096, tc.w0 / 4, h2, tc.m0, tc.b);
+              }
             }
+            if (p.num_levels > 3 && p.tma_ok[3] && tc.h0 / 8 < p.lh[3])
+              ptx::tma_store_4d(&p.tmOut[3], slot + 8192, tc.w0 / 8, tc.h0 / 8, tc.m0, tc.b);
+            ptx::tma_store_commit();
+            store_ring_wait(NSLOT);
           }
-          if (p.num_levels > 3 && p.tma_ok[3] && tc.h0 / 8 < p.lh[3])
-            ptx::tma_store_4d(&p.tmOut[3], slot + 8192, tc.w0 / 8, tc.h0 / 8, tc.m0, tc.b);
-          ptx::tma_store_commit();
-          ptx::tma_store_wait_read<1>();
+          ++ev;
         }
-        ++ev;
       }
+    }
     }
     if (issuer) ptx::tma_store_wait_all();
   }
@@ -535,7 +623,9 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
                                             : CU_TENSOR_MAP_SWIZZLE_NONE;
     cuuint64_t dims[4] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)HW, (cuuint64_t)B};
     cuuint32_t box[4] = {(cuuint32_t)(TW >> l), 1, BM, 1};
-    p.tma_ok[l] = (h > 0 && w > 0 && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0 &&
+    const char* env_pool = getenv("WOFT_CORR_POOL_TMA");  // bit l set => level l may use TMA stores
+    const int tma_levels = env_pool ? atoi(env_pool) : 0xF;
+    p.tma_ok[l] = (((tma_levels >> l) & 1) && h > 0 && w > 0 && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0 &&
                    encode(enc, &p.tmOut[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, 4, levels[l], dims, box, swz))
                       ? 1
                       : 0;
@@ -558,11 +648,47 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   p.scale = 1.0f / sqrtf(float(C));
   p.abort_flag = flag;
 
+  // Shared-memory plan.  Keeping the A tile resident removes its re-fetch from L2 for every N tile (the kernel is
+  // L2-bandwidth bound on operand traffic); it needs k_blocks x 16 KB, which leaves room for 3 B
+  // stages + 3 ring slots (bf16, K <= 256) or 2 + 2 (tf32, K <= 256).  The 3xTF32 split streams both operands.
+  const int fixed = 256 + 1024;
+  p.a_resident = 0;
+  p.unit = 1;
+  p.stages = 3;
+  p.nslot = 3;
+  const char* env_res = getenv("WOFT_CORR_A_RESIDENT");
+  const bool want_res = p.n_pairs == 1 && env_res && env_res[0] == '1';  // off by default: measured slower
+  if (want_res) {
+    const int a_bytes = p.k_blocks * A_STAGE;
+    if (a_bytes + 3 * B_STAGE + 3 * SLOT + fixed <= TC_SMEM_LIMIT) {
+      p.a_resident = 1;
+    } else if (a_bytes + 2 * B_STAGE + 2 * SLOT + fixed <= TC_SMEM_LIMIT) {
+      p.a_resident = 1;
+      p.stages = 2;
+      p.nslot = 2;
+    }
+    if (p.a_resident) {
+      const char* env_unit = getenv("WOFT_CORR_UNIT");
+      const int n_tiles = p.h_tiles * p.w_tiles;
+      int unit = env_unit ? atoi(env_unit) : 6;
+      if (unit < 1) unit = 1;
+      // units must not straddle M tiles more than necessary: prefer a divisor of the N-tile count near `unit`
+      for (int u = unit; u >= 1; --u)
+        if (n_tiles % u == 0) {
+          unit = u;
+          break;
+        }
+      p.unit = unit;
+    }
+  }
+  const int smem_bytes = (p.a_resident ? p.k_blocks : p.stages) * A_STAGE + p.stages * B_STAGE + p.nslot * SLOT + fixed;
+
   int sms = 0;
   WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM));
-  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
-  corr_tc_kernel<<<grid, TC_THREADS, TC_SMEM, stream>>>(p);
+  WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  const int chunks = ceil_div(p.total_tiles, p.unit);
+  const int grid = chunks < sms ? chunks : sms;
+  corr_tc_kernel<<<grid, TC_THREADS, smem_bytes, stream>>>(p);
   return launch_status("corr_tc_kernel");
 }
 

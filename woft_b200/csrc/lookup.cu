@@ -50,7 +50,7 @@ struct LookupGeom {
 };
 
 template <int R, bool VEC>
-__global__ void __launch_bounds__(kLookupThreads, 7) corr_lookup_kernel(const __grid_constant__ LookupParams p) {
+__global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __grid_constant__ LookupParams p) {
   using G = LookupGeom<R>;
   constexpr int P = G::P, WIN = G::WIN, STRIDE = G::STRIDE;
   __shared__ float win[kLevelsPerPass * kQueriesPerCta * STRIDE];

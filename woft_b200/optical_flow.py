@@ -119,7 +119,7 @@ def sigmoid(xs):
 
 
 class RAFTWrapper:
-    def __init__(self, config, device="cuda", use_cuda_graph=True, corr_block=None, channels_last=True,
+    def __init__(self, config, device="cuda", use_cuda_graph=True, corr_block=None, channels_last=False,
                  cudnn_benchmark=True):
         self.C = config
         self.channels_last = channels_last

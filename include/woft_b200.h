@@ -131,6 +131,23 @@ int woft_homography_fit(const float* points1, const float* points2, const float*
 int woft_proj_errors(const float* H, const float* pts_a, const float* pts_b, int batch, int n_points, float* err,
                      void* stream);
 
+/* Fused element-wise stages between the update block's cuDNN convolutions.  Replace the gate arithmetic of
+ * SepConvGRU.forward (pytracking/external/RAFT/raft_core/update.py:45-60), per half step:
+ *   woft_gru_gates : zr = bias-free conv of [h, x] with convz and convr weights stacked, (B, 2C, HW);
+ *                    z = sigmoid(zr[:, :C] + bz), rh = sigmoid(zr[:, C:] + br) * h      -> (B, C, HW) each
+ *   woft_gru_update: h_new = (1 - z) * h + z * tanh(q + bq), q = bias-free convq([rh, x])
+ * NCHW fp32 contiguous, H*W a multiple of 4; bias_zr is [bz; br] (2C). */
+int woft_gru_gates(const float* zr, const float* bias_zr, const float* h, int batch, int channels, int hw, float* z,
+                   float* rh, void* stream);
+int woft_gru_update(const float* q, const float* bias_q, const float* z, const float* h, int batch, int channels,
+                    int hw, float* h_new, void* stream);
+
+/* Replaces nn.InstanceNorm2d + ReLU after each convolution of the feature encoder
+ * (raft_core/extractor.py:30-32, 49-50, 127, 180-181): per (n, c) plane y = (x - mean) / sqrt(var + eps), biased
+ * variance, no affine parameters, followed by ReLU when `relu` is non-zero (the 1x1 projection branch has none).
+ * x, y: (planes, HW) fp32, may alias. */
+int woft_instance_norm_relu(const float* x, int planes, int hw, float eps, int relu, float* y, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -328,3 +328,48 @@ def test_tracker_runs_and_masks_like_the_reference():
     got = trk._mask_coords(src.to(DEV), cur.to(DEV), wts.to(DEV), pw.to(DEV))
     for a, b in zip(got, want):
         assert torch.equal(a.cpu(), b)
+
+
+# ----------------------------------------------------------------------------------------------------
+# fused element-wise kernels and the fused inference schedule (started)
+# ----------------------------------------------------------------------------------------------------
+def test_fused_gru_and_instance_norm_kernels():
+    from woft_b200 import fast_net
+    g = torch.Generator().manual_seed(5)
+    B, C, H, W = 2, 128, 22, 36
+    zr = torch.randn((B, 2 * C, H, W), generator=g).to(DEV)
+    h = torch.randn((B, C, H, W), generator=g).to(DEV)
+    bias = torch.randn((2 * C,), generator=g).to(DEV)
+    z, rh = fast_net.gru_gates(zr, bias, h)
+    zb = zr + bias.view(1, -1, 1, 1)
+    assert torch.allclose(z, torch.sigmoid(zb[:, :C]), atol=1e-6)
+    assert torch.allclose(rh, torch.sigmoid(zb[:, C:]) * h, atol=1e-6)
+    q = torch.randn((B, C, H, W), generator=g).to(DEV)
+    bq = torch.randn((C,), generator=g).to(DEV)
+    hn = fast_net.gru_update(q, bq, z, h)
+    assert torch.allclose(hn, (1 - z) * h + z * torch.tanh(q + bq.view(1, -1, 1, 1)), atol=2e-6)
+    x = (torch.randn((3, 16, 45, 80), generator=g) * 3 + 7).to(DEV)
+    for relu in (True, False):
+        want = F.instance_norm(x, eps=1e-5)
+        want = F.relu(want) if relu else want
+        assert torch.allclose(fast_net.instance_norm_relu(x, relu=relu), want, atol=2e-5)
+
+
+def test_fused_schedule_matches_layer_by_layer(golden):
+    from woft_b200.corr import CorrBlock
+    from woft_b200.fast_net import FastWeightedRAFT
+    from woft_b200.raft_net import WeightedRAFT, seeded_state_dict
+    g = golden("net_small")
+    net = WeightedRAFT().eval()
+    net.load_state_dict(seeded_state_dict(net, 0))
+    net = net.to(DEV).requires_grad_(False)
+    t1, t2 = _net_inputs(g)
+    blk = functools.partial(CorrBlock, mode="tf32x3")
+    with torch.no_grad():
+        slow = net(t1, t2, iters=12, corr_block=blk)
+    fast = FastWeightedRAFT(net)(t1, t2, iters=12, corr_block=blk)
+    epe = (fast[1] - slow[1]).norm(dim=1).mean().item()
+    assert epe <= 2e-3, f"fused vs layer-by-layer schedule: mean EPE {epe} px"
+    assert (fast[4] - slow[4]).abs().max().item() <= 2e-3
+    ref_epe = (fast[1].cpu() - torch.from_numpy(g["it12_flow_up"])).norm(dim=1).mean().item()
+    assert ref_epe <= 0.01, f"fused schedule vs reference network: mean EPE {ref_epe} px"

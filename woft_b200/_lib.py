@@ -36,6 +36,9 @@ SIGNATURES = {
     "woft_homography_fit": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,
                                     c_void_p]),
     "woft_proj_errors": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "woft_gru_gates": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "woft_gru_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "woft_instance_norm_relu": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p]),
 }
 
 _lib = None

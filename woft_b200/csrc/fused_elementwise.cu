@@ -1,0 +1,155 @@
+// Fused element-wise stages of the flow network that sit between cuDNN convolutions.
+//
+// SepConvGRU.forward (pytracking/external/RAFT/raft_core/update.py:45-60) per half step:
+//     z = sigmoid(convz(hx)); r = sigmoid(convr(hx)); q = tanh(convq(cat[r*h, x])); h = (1-z)*h + z*q
+// In PyTorch that is 3 bias adds + 2 sigmoids + 1 tanh + 1 mul + 4 blend kernels per half step, 24 half steps
+// per flow pass.  Here the z and r convolutions are one bias-free convolution with stacked weights, and
+//   gru_gates_kernel   z = sigmoid(zr[:, :C] + bz),  rh = sigmoid(zr[:, C:] + br) * h
+//   gru_update_kernel  h' = (1 - z) * h + z * tanh(q + bq)
+// BasicEncoder with norm_fn='instance' (raft_core/extractor.py:118-192) does conv -> InstanceNorm2d -> ReLU;
+//   instance_norm_relu_kernel  one CTA per (n, c) plane: mean / biased variance, then (x - mean) * rstd, ReLU
+//                              (eps 1e-5, no affine: nn.InstanceNorm2d defaults), second read served by L2.
+// All tensors NCHW fp32 contiguous.
+#include "common.cuh"
+
+namespace woft {
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+// zr: (B, 2C, HW); h: (B, C, HW) -> z, rh: (B, C, HW).  One thread per 4 consecutive pixels.
+__global__ void gru_gates_kernel(const float* __restrict__ zr, const float* __restrict__ bias, const float* __restrict__ h,
+                                 float* __restrict__ z, float* __restrict__ rh, int C, int HW4, long long total4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int p4 = int(i % HW4);
+    const long long bc = i / HW4;
+    const int c = int(bc % C);
+    const long long b = bc / C;
+    const float4 zp = __ldg(reinterpret_cast<const float4*>(zr) + ((b * 2 * C + c) * HW4 + p4));
+    const float4 rp = __ldg(reinterpret_cast<const float4*>(zr) + ((b * 2 * C + C + c) * HW4 + p4));
+    const float4 hv = __ldg(reinterpret_cast<const float4*>(h) + i);
+    const float bz = __ldg(bias + c), br = __ldg(bias + C + c);
+    float4 zo, ro;
+    zo.x = sigmoidf_(zp.x + bz); zo.y = sigmoidf_(zp.y + bz); zo.z = sigmoidf_(zp.z + bz); zo.w = sigmoidf_(zp.w + bz);
+    ro.x = sigmoidf_(rp.x + br) * hv.x; ro.y = sigmoidf_(rp.y + br) * hv.y;
+    ro.z = sigmoidf_(rp.z + br) * hv.z; ro.w = sigmoidf_(rp.w + br) * hv.w;
+    reinterpret_cast<float4*>(z)[i] = zo;
+    reinterpret_cast<float4*>(rh)[i] = ro;
+  }
+}
+
+__global__ void gru_update_kernel(const float* __restrict__ q, const float* __restrict__ bias, const float* __restrict__ z,
+                                  const float* __restrict__ h, float* __restrict__ h_new, int C, int HW4,
+                                  long long total4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = int((i / HW4) % C);
+    const float bq = __ldg(bias + c);
+    const float4 qv = __ldg(reinterpret_cast<const float4*>(q) + i);
+    const float4 zv = __ldg(reinterpret_cast<const float4*>(z) + i);
+    const float4 hv = __ldg(reinterpret_cast<const float4*>(h) + i);
+    float4 o;
+    o.x = (1.f - zv.x) * hv.x + zv.x * tanhf(qv.x + bq);
+    o.y = (1.f - zv.y) * hv.y + zv.y * tanhf(qv.y + bq);
+    o.z = (1.f - zv.z) * hv.z + zv.z * tanhf(qv.z + bq);
+    o.w = (1.f - zv.w) * hv.w + zv.w * tanhf(qv.w + bq);
+    reinterpret_cast<float4*>(h_new)[i] = o;
+  }
+}
+
+__global__ void __launch_bounds__(512) instance_norm_relu_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                                 int HW, float eps, int relu) {
+  __shared__ float s_sum[16], s_sq[16];
+  __shared__ float s_mean, s_rstd;
+  const float* src = x + (size_t)blockIdx.x * HW;
+  float* dst = y + (size_t)blockIdx.x * HW;
+  const int n4 = HW >> 2;
+  // pass 1: sum and sum of squares around a pivot (the first element) to keep the variance well conditioned
+  const float pivot = __ldg(src);
+  float s = 0.f, q = 0.f;
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+    const float a = v.x - pivot, b = v.y - pivot, c = v.z - pivot, d = v.w - pivot;
+    s += (a + b) + (c + d);
+    q += (a * a + b * b) + (c * c + d * d);
+  }
+  for (int i = (n4 << 2) + threadIdx.x; i < HW; i += blockDim.x) {
+    const float a = __ldg(src + i) - pivot;
+    s += a;
+    q += a * a;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    s_sum[threadIdx.x >> 5] = s;
+    s_sq[threadIdx.x >> 5] = q;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double ts = 0.0, tq = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
+      ts += s_sum[w];
+      tq += s_sq[w];
+    }
+    const double m = ts / HW;
+    const double var = tq / HW - m * m;  // biased variance, as nn.InstanceNorm2d uses for normalisation
+    s_mean = float(m) + pivot;
+    s_rstd = rsqrtf(fmaxf(float(var), 0.f) + eps);
+  }
+  __syncthreads();
+  const float mean = s_mean, rstd = s_rstd;
+  const float floor_ = relu ? 0.f : -3.4e38f;
+  for (int i = threadIdx.x; i < n4; i += blockDim.x) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+    float4 o;
+    o.x = fmaxf((v.x - mean) * rstd, floor_);
+    o.y = fmaxf((v.y - mean) * rstd, floor_);
+    o.z = fmaxf((v.z - mean) * rstd, floor_);
+    o.w = fmaxf((v.w - mean) * rstd, floor_);
+    reinterpret_cast<float4*>(dst)[i] = o;
+  }
+  for (int i = (n4 << 2) + threadIdx.x; i < HW; i += blockDim.x) dst[i] = fmaxf((__ldg(src + i) - mean) * rstd, floor_);
+}
+
+static int ew_grid(long long total4) {
+  const long long blocks = (total4 + 255) / 256;
+  return int(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
+}
+
+}  // namespace woft
+
+extern "C" int woft_gru_gates(const float* zr, const float* bias_zr, const float* h, int batch, int channels, int hw,
+                              float* z, float* rh, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(zr && bias_zr && h && z && rh, "woft_gru_gates: null pointer");
+  WOFT_REQUIRE(batch > 0 && channels > 0 && hw > 0 && hw % 4 == 0, "woft_gru_gates: H*W must be a positive multiple of 4");
+  const long long total4 = (long long)batch * channels * (hw / 4);
+  gru_gates_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(zr, bias_zr, h, z, rh, channels,
+                                                                                   hw / 4, total4);
+  return launch_status("gru_gates_kernel");
+}
+
+extern "C" int woft_gru_update(const float* q, const float* bias_q, const float* z, const float* h, int batch,
+                               int channels, int hw, float* h_new, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(q && bias_q && z && h && h_new, "woft_gru_update: null pointer");
+  WOFT_REQUIRE(batch > 0 && channels > 0 && hw > 0 && hw % 4 == 0, "woft_gru_update: H*W must be a positive multiple of 4");
+  const long long total4 = (long long)batch * channels * (hw / 4);
+  gru_update_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(q, bias_q, z, h, h_new, channels,
+                                                                                    hw / 4, total4);
+  return launch_status("gru_update_kernel");
+}
+
+extern "C" int woft_instance_norm_relu(const float* x, int planes, int hw, float eps, int relu, float* y, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(x && y, "woft_instance_norm_relu: null pointer");
+  WOFT_REQUIRE(planes > 0 && hw > 0, "woft_instance_norm_relu: bad extent");
+  WOFT_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(y) & 15) == 0 &&
+                   (hw % 4 == 0),
+               "woft_instance_norm_relu: planes must be 16-byte aligned (H*W a multiple of 4)");
+  instance_norm_relu_kernel<<<planes, 512, 0, static_cast<cudaStream_t>(stream)>>>(x, y, hw, eps, relu);
+  return launch_status("instance_norm_relu_kernel");
+}

@@ -1,0 +1,204 @@
+"""Inference schedule of the flow network for the GPU: same arithmetic as raft_net.WeightedRAFT, fewer passes.
+
+`raft_net.WeightedRAFT` is the layer-by-layer mirror of the reference (and what the CPU oracle runs).  On the GPU
+one frame of that schedule is ~1 500 launches of which two thirds are bias adds, ReLUs, layout conversions,
+concatenations and the three-pass instance norm around the cuDNN convolutions (profiles/r1_step_breakdown.txt).
+`FastWeightedRAFT` runs the same network from the same parameters with those stages fused:
+
+  feature encoder   conv -> InstanceNorm -> ReLU   : bias-free cuDNN conv (a per-channel constant cancels in the
+                    norm) + woft_instance_norm_relu (one kernel, two reads, one write)
+  context encoder   conv -> BatchNorm(eval) -> ReLU: BN folded into the conv weights, cuDNN fused conv+bias+ReLU
+  motion encoder, flow head, mask head, weight head: cuDNN fused conv+bias+ReLU; the weight head runs channels-last
+                    end to end (its 597 MB activations are never transposed)
+  SepConvGRU        convz and convr as ONE bias-free conv with stacked weights + woft_gru_gates / woft_gru_update
+                    (update.py:45-60: 11 element-wise kernels per half step become 2)
+
+Results agree with the layer-by-layer schedule to fp32 rounding (tests/test_gpu_parity.py).
+"""
+import torch
+import torch.nn.functional as F
+
+from . import _lib
+from .raft_net import convex_upsample, pixel_grid
+
+
+def _conv_relu(x, w, b, stride=(1, 1), padding=(0, 0)):
+    return torch.cudnn_convolution_relu(x, w, b, stride, padding, (1, 1), 1)
+
+
+def instance_norm_relu(x, relu=True, eps=1e-5):
+    """(N, C, H, W) fp32 contiguous -> same shape; woft_instance_norm_relu."""
+    x = x.contiguous()
+    N, C, H, W = x.shape
+    y = torch.empty_like(x)
+    with torch.cuda.device(x.device):
+        rc = _lib.load().woft_instance_norm_relu(_lib.ptr(x), N * C, H * W, eps, int(relu), _lib.ptr(y),
+                                                 _lib.current_stream(x.device))
+    _lib.check(rc, "woft_instance_norm_relu")
+    return y
+
+
+def gru_gates(zr, bias_zr, h):
+    B, C2, H, W = zr.shape
+    C = C2 // 2
+    z, rh = torch.empty_like(h), torch.empty_like(h)
+    with torch.cuda.device(h.device):
+        rc = _lib.load().woft_gru_gates(_lib.ptr(zr), _lib.ptr(bias_zr), _lib.ptr(h), B, C, H * W, _lib.ptr(z), _lib.ptr(rh),
+                                        _lib.current_stream(h.device))
+    _lib.check(rc, "woft_gru_gates")
+    return z, rh
+
+
+def gru_update(q, bias_q, z, h):
+    B, C, H, W = h.shape
+    out = torch.empty_like(h)
+    with torch.cuda.device(h.device):
+        rc = _lib.load().woft_gru_update(_lib.ptr(q), _lib.ptr(bias_q), _lib.ptr(z), _lib.ptr(h), B, C, H * W, _lib.ptr(out),
+                                         _lib.current_stream(h.device))
+    _lib.check(rc, "woft_gru_update")
+    return out
+
+
+class FastWeightedRAFT:
+    """Callable with the signature of WeightedRAFT.forward; built from a WeightedRAFT that already sits on the GPU."""
+
+    def __init__(self, net):
+        self.net = net
+        self.with_weights = net.with_weights
+        dev = next(net.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("FastWeightedRAFT needs the network on a CUDA device")
+        with torch.no_grad():
+            self.cnet = self._fold_encoder(net.cnet)
+            g = net.update_block.gru
+            self.gru = {}
+            for tag in ("1", "2"):
+                cz, cr, cq = (getattr(g, f"conv{k}{tag}") for k in "zrq")
+                self.gru[tag] = dict(w_zr=torch.cat([cz.weight, cr.weight], 0).contiguous(),
+                                     b_zr=torch.cat([cz.bias, cr.bias], 0).contiguous(),
+                                     w_q=cq.weight.contiguous(), b_q=cq.bias.contiguous(), padding=cz.padding)
+            if self.with_weights:
+                self.head = [(m.weight.contiguous(memory_format=torch.channels_last), m.bias, m.padding)
+                             for m in net.weight_head.net if isinstance(m, torch.nn.Conv2d)]
+
+    # ---- context encoder: fold eval-mode BatchNorm into the convolutions ---------------------------------
+    @staticmethod
+    def _fold(conv, bn):
+        if not isinstance(bn, torch.nn.BatchNorm2d):
+            return conv.weight, conv.bias
+        s = bn.weight / torch.sqrt(bn.running_var + bn.eps)
+        return (conv.weight * s.view(-1, 1, 1, 1)).contiguous(), ((conv.bias - bn.running_mean) * s + bn.bias).contiguous()
+
+    def _fold_encoder(self, enc):
+        out = {"stem": self._fold(enc.conv1, enc.norm1), "blocks": [], "out": (enc.conv2.weight, enc.conv2.bias)}
+        for layer in (enc.layer1, enc.layer2, enc.layer3):
+            for blk in layer:
+                d = {"c1": self._fold(blk.conv1, blk.norm1), "c2": self._fold(blk.conv2, blk.norm2),
+                     "stride": blk.conv1.stride, "down": None}
+                if blk.downsample is not None:
+                    d["down"] = self._fold(blk.downsample[0], blk.downsample[1])
+                out["blocks"].append(d)
+        return out
+
+    def _context(self, x):
+        c = self.cnet
+        x = _conv_relu(x, *c["stem"], stride=(2, 2), padding=(3, 3))
+        for d in c["blocks"]:
+            y = _conv_relu(x, *d["c1"], stride=d["stride"], padding=(1, 1))
+            y = _conv_relu(y, *d["c2"], padding=(1, 1))
+            if d["down"] is not None:
+                x = F.conv2d(x, d["down"][0], d["down"][1], stride=d["stride"])
+            x = F.relu(x + y)
+        return F.conv2d(x, *c["out"])
+
+    # ---- feature encoder: bias-free conv + fused instance norm / ReLU --------------------------------------
+    def _features(self, x):
+        enc = self.net.fnet
+        x = instance_norm_relu(F.conv2d(x, enc.conv1.weight, None, stride=2, padding=3))
+        for layer in (enc.layer1, enc.layer2, enc.layer3):
+            for blk in layer:
+                y = instance_norm_relu(F.conv2d(x, blk.conv1.weight, None, stride=blk.conv1.stride, padding=1))
+                y = instance_norm_relu(F.conv2d(y, blk.conv2.weight, None, padding=1))
+                if blk.downsample is not None:
+                    x = instance_norm_relu(F.conv2d(x, blk.downsample[0].weight, None, stride=blk.downsample[0].stride),
+                                           relu=False)
+                x = F.relu(x + y)
+        return F.conv2d(x, enc.conv2.weight, enc.conv2.bias)
+
+    # ---- update block ---------------------------------------------------------------------------------------
+    def _gru_half(self, h, x, tag):
+        g = self.gru[tag]
+        zr = F.conv2d(torch.cat([h, x], dim=1), g["w_zr"], None, padding=g["padding"])
+        z, rh = gru_gates(zr, g["b_zr"], h)
+        q = F.conv2d(torch.cat([rh, x], dim=1), g["w_q"], None, padding=g["padding"])
+        return gru_update(q, g["b_q"], z, h)
+
+    def _update(self, net, inp, corr, flow, need_mask):
+        ub = self.net.update_block
+        e = ub.encoder
+        cor = _conv_relu(corr, e.convc1.weight, e.convc1.bias)
+        cor = _conv_relu(cor, e.convc2.weight, e.convc2.bias, padding=(1, 1))
+        flo = _conv_relu(flow, e.convf1.weight, e.convf1.bias, padding=(3, 3))
+        flo = _conv_relu(flo, e.convf2.weight, e.convf2.bias, padding=(1, 1))
+        out = _conv_relu(torch.cat([cor, flo], dim=1), e.conv.weight, e.conv.bias, padding=(1, 1))
+        x = torch.cat([inp, out, flow], dim=1)
+        net = self._gru_half(self._gru_half(net, x, "1"), x, "2")
+        fh = ub.flow_head
+        dflow = F.conv2d(_conv_relu(net, fh.conv1.weight, fh.conv1.bias, padding=(1, 1)), fh.conv2.weight, fh.conv2.bias,
+                         padding=1)
+        mask = None
+        if need_mask:
+            m = _conv_relu(net, ub.mask[0].weight, ub.mask[0].bias, padding=(1, 1))
+            mask = 0.25 * F.conv2d(m, ub.mask[2].weight, ub.mask[2].bias)
+        return net, mask, dflow
+
+    # ---- weight head, channels-last -----------------------------------------------------------------------------
+    def _weights(self, window, mean_response):
+        B, ch, H1, W1 = window.shape
+        L = self.head[0][0].shape[1] - 1
+        P = int(round((ch // L) ** 0.5))
+        n = B * H1 * W1
+        # NHWC buffer (n, P, P, L+1): CNN input [lvl', hp, wp] is lookup channel hp*P*L + wp*L + lvl'
+        # (the reference's reinterpretation of the lookup channels, weighted_raft.py:267-272)
+        buf = torch.empty((n, P, P, L + 1), device=window.device, dtype=window.dtype)
+        buf[..., :L] = window.view(B, P, P, L, H1, W1).permute(0, 4, 5, 1, 2, 3).reshape(n, P, P, L)
+        buf[..., L] = mean_response.reshape(n, 1, 1)
+        x = buf.permute(0, 3, 1, 2)  # logical NCHW, channels-last in memory
+        for w, b, pad in self.head[:-1]:
+            x = _conv_relu(x, w, b, padding=pad)
+        w, b, _ = self.head[-1]
+        # mean over the patch of a 1x1 convolution = 1x1 convolution of the patch mean
+        pooled = x.mean(dim=(2, 3))
+        logit = pooled @ w.reshape(1, -1).T + b
+        return logit.view(B, H1, W1).unsqueeze(1)
+
+    @torch.no_grad()
+    def __call__(self, image1, image2, iters=12, flow_init=None, test_mode=True, corr_block=None):
+        net_ = self.net
+        if corr_block is None:
+            from .corr import CorrBlock as corr_block
+        image1 = 2 * (image1 / 255.0) - 1.0
+        image2 = 2 * (image2 / 255.0) - 1.0
+        fmap1, fmap2 = self._features(torch.cat([image1, image2], dim=0)).chunk(2, dim=0)
+        corr_fn = corr_block(fmap1.contiguous(), fmap2.contiguous(), num_levels=net_.corr_levels, radius=net_.corr_radius)
+        net, inp = torch.split(self._context(image1), [net_.hidden_dim, net_.context_dim], dim=1)
+        net, inp = torch.tanh(net), torch.relu(inp)
+
+        B, _, H, W = image1.shape
+        coords0 = pixel_grid(B, H // 8, W // 8, image1.device)
+        coords1 = coords0.clone()
+        if flow_init is not None:
+            coords1 = coords1 + flow_init
+        up_mask = None
+        for it in range(iters):
+            corr = corr_fn(coords1)
+            net, up_mask, dflow = self._update(net, inp, corr, coords1 - coords0, need_mask=(it == iters - 1))
+            coords1 = coords1 + dflow
+        flow_low = coords1 - coords0
+        flow_up = convex_upsample(flow_low, up_mask)
+        if not self.with_weights:
+            return flow_low, flow_up
+        window = corr_fn(coords1)
+        weights = self._weights(window, corr_fn.mean_response())
+        weights_up = convex_upsample(weights, up_mask) / 8
+        return flow_low, flow_up, corr_fn.corr_pyramid[0], weights, weights_up

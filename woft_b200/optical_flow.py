@@ -120,9 +120,10 @@ def sigmoid(xs):
 
 class RAFTWrapper:
     def __init__(self, config, device="cuda", use_cuda_graph=True, corr_block=None, channels_last=False,
-                 cudnn_benchmark=True):
+                 cudnn_benchmark=True, fused=True):
         self.C = config
         self.channels_last = channels_last
+        self.fused = fused
         if cudnn_benchmark:
             torch.backends.cudnn.benchmark = True  # fixed shapes per sequence: let cuDNN pick its fastest kernels
         params = _cfg(config, "class_params")
@@ -149,6 +150,12 @@ class RAFTWrapper:
             # cuDNN's sm_100 convolution kernels are NHWC: keep weights and activations channels-last so it does not
             # wrap every convolution in a pair of layout-conversion kernels
             self.net = self.net.to(memory_format=torch.channels_last)
+        # fused inference schedule (fast_net.py) unless the layer-by-layer mirror is asked for
+        if fused and not channels_last:
+            from .fast_net import FastWeightedRAFT
+            self._run = FastWeightedRAFT(self.net)
+        else:
+            self._run = self.net
         self.iters = int(_cfg(config, "iters", 12))
         self.use_cuda_graph = use_cuda_graph
         self.corr_block = corr_block
@@ -202,7 +209,7 @@ class RAFTWrapper:
     def _forward(self, src, dst):
         kwargs = dict(iters=self.iters, test_mode=True, corr_block=self.corr_block)
         if not self.use_cuda_graph:
-            return self.net(src, dst, **kwargs)
+            return self._run(src, dst, **kwargs)
         key = tuple(src.shape)
         entry = self._graphs.get(key)
         if entry is None:
@@ -213,11 +220,11 @@ class RAFTWrapper:
             side.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(side):  # warm-up outside capture: cuDNN autotune, workspace allocation
                 for _ in range(2):
-                    self.net(s_in, d_in, **kwargs)
+                    self._run(s_in, d_in, **kwargs)
             torch.cuda.current_stream(self.device).wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                out = self.net(s_in, d_in, **kwargs)
+                out = self._run(s_in, d_in, **kwargs)
             entry = (graph, s_in, d_in, out)
             self._graphs[key] = entry
         graph, s_in, d_in, out = entry

@@ -7,8 +7,9 @@ A step is one tracked frame of BASELINE.json configs[1]: one WeightedRAFT flow +
 1280x720 frame pair (160x90x256 feature maps, 12 GRU iterations, 13 correlation lookups), the correspondence
 mask, the 500-point Sobol pick, the weighted homography fit and the inlier test.
   value      frames/s over all ranks with the frames already resident in HBM (uint8), nothing copied to the host
-  e2e        frames/s through the public API (PlanarTracker.track on host uint8 frames): host pre-warp, pinned
-             H2D upload of both frames, the device path, D2H of the 3x3 homography and of the success flag
+  e2e        frames/s through the public API (PlanarTracker.track on a host uint8 frame): pinned H2D upload of the
+             frame (the template was uploaded once by init), device pre-warp, the device path, D2H of the 3x3
+             homography and of the success flag
   roofline   the correlation lookup (K3), the kernel BASELINE.json's metric names, timed alone with CUDA events on
              its launch stream with L2 flushed between launches; `kernels` adds K1+K2 and K4 the same way
   cpu_baseline / --impl reference: the oracle port of the reference's CPU path on this box's host cores
@@ -365,7 +366,7 @@ def run_woft(args, rank, world, local):
                          "steps; per-kernel roofline launches are preceded by a 256 MiB L2 flush",
                    "flow_passes_per_frame": results["device"]["flow_passes"] / args.steps},
         "e2e": {"value": round(world * args.steps / results["e2e"]["seconds"], 3), "unit": "frames/s",
-                "h2d_bytes_per_step": 2 * HEIGHT * WIDTH * 3 + HEIGHT * WIDTH, "d2h_bytes_per_step": 36 + 1,
+                "h2d_bytes_per_step": HEIGHT * WIDTH * 3, "d2h_bytes_per_step": 36 + 1,
                 "flow_passes_per_frame": results["e2e"]["flow_passes"] / args.steps,
                 "api": "woft_b200.tracker.PlanarTracker.track(host uint8 frame) -> 3x3 homography on the host"},
         "gpu_launches": int(args.steps * (5 + (ITERS + 1) + 2)),

@@ -148,6 +148,17 @@ int woft_gru_update(const float* q, const float* bias_q, const float* z, const f
  * x, y: (planes, HW) fp32, may alias. */
 int woft_instance_norm_relu(const float* x, int planes, int hw, float eps, int relu, float* y, void* stream);
 
+/* Replaces the two cv2.warpPerspective calls of YAOFTrackerSingleControl.track
+ * (pytracking/tracker/YAOF_tracker_single_control.py:89-95): bilinear warp of an 8-bit frame with a zero border,
+ * plus the validity mask the reference gets from warping an image of ones (`> 0`).
+ *   src, dst   : (H, W, C) uint8, C <= 4           valid_mask : (H, W) uint8 0/1, may be NULL
+ *   inv_matrix_host : HOST pointer to 9 doubles, row-major, mapping destination (x, y, 1) to source -- the inverse of
+ *                     the matrix cv2.warpPerspective is given (it inverts it unless WARP_INVERSE_MAP is set)
+ * Coordinates are quantised to 1/32 px as OpenCV does; pixel values differ from OpenCV's fixed-point blend by at
+ * most one grey level. */
+int woft_warp_perspective_u8(const uint8_t* src, int height, int width, int channels, const double* inv_matrix_host,
+                             uint8_t* dst, uint8_t* valid_mask, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

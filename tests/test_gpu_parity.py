@@ -373,3 +373,20 @@ def test_fused_schedule_matches_layer_by_layer(golden):
     assert (fast[4] - slow[4]).abs().max().item() <= 2e-3
     ref_epe = (fast[1].cpu() - torch.from_numpy(g["it12_flow_up"])).norm(dim=1).mean().item()
     assert ref_epe <= 0.01, f"fused schedule vs reference network: mean EPE {ref_epe} px"
+
+
+def test_device_prewarp_matches_opencv():
+    """woft_warp_perspective_u8 against cv2.warpPerspective (YAOF_tracker_single_control.py:89-95)."""
+    import cv2
+    from oracle.gen_golden import make_frames
+    from woft_b200.tracker import prewarp_on_device
+    img, _ = make_frames(360, 640, 9)
+    for M in (np.eye(3), np.array([[1.02, 0.015, 12.5], [-0.01, 0.97, -7.25], [2e-5, -1e-5, 1.0]]),
+              np.array([[0.8, 0.2, 40.0], [-0.15, 1.1, 30.0], [1e-4, 2e-4, 1.0]])):
+        want = cv2.warpPerspective(img, M, (640, 360), flags=cv2.INTER_LINEAR)
+        want_mask = cv2.warpPerspective(np.ones((360, 640)), M, (640, 360), flags=cv2.INTER_LINEAR) > 0
+        got, mask = prewarp_on_device(torch.from_numpy(img).to(DEV), M)
+        diff = np.abs(got.cpu().numpy().astype(np.int32) - want.astype(np.int32))
+        assert diff.max() <= 1, f"max grey-level difference {diff.max()}"
+        assert diff.mean() < 0.05
+        assert (mask.cpu().numpy() != want_mask).mean() < 1e-3

@@ -36,6 +36,8 @@ SIGNATURES = {
     "woft_homography_fit": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,
                                     c_void_p]),
     "woft_proj_errors": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
+    "woft_warp_perspective_u8": (c_int, [c_void_p, c_int, c_int, c_int, POINTER(ctypes.c_double), c_void_p, c_void_p,
+                                         c_void_p]),
     "woft_gru_gates": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "woft_gru_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_instance_norm_relu": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p]),

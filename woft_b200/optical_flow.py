@@ -189,22 +189,26 @@ class RAFTWrapper:
         w = fn(flat_weights.view(s["batch"], 1, s["H"], s["W"]))
         return w.reshape(s["batch"], s["H"] * s["W"])
 
-    def _upload(self, img, slot):
-        """uint8 BGR (H,W,3) numpy -> float RGB (1,3,H,W) on the device, via a pinned staging buffer."""
+    def upload_u8(self, img, slot):
+        """(H,W,3) uint8 host array -> device uint8 tensor through a pinned staging buffer (asynchronous copy).
+        Device tensors pass through."""
         if isinstance(img, torch.Tensor):
-            t = img.to(self.device, non_blocking=True)
-        else:
-            key = (slot, img.shape)
-            entry = self._pinned.get(key)
-            if entry is None:
-                entry = (torch.empty(img.shape, dtype=torch.uint8).pin_memory(), torch.cuda.Event())
-                self._pinned[key] = entry
-            buf, done = entry
-            done.synchronize()  # the previous upload from this buffer must have left the host
-            buf.numpy()[...] = img
-            t = buf.to(self.device, non_blocking=True)
-            done.record(torch.cuda.current_stream(self.device))
-        return t.flip(-1).permute(2, 0, 1).float()[None]
+            return img.to(self.device, non_blocking=True)
+        key = (slot, img.shape)
+        entry = self._pinned.get(key)
+        if entry is None:
+            entry = (torch.empty(img.shape, dtype=torch.uint8).pin_memory(), torch.cuda.Event())
+            self._pinned[key] = entry
+        buf, done = entry
+        done.synchronize()  # the previous upload from this buffer must have left the host
+        buf.numpy()[...] = img
+        t = buf.to(self.device, non_blocking=True)
+        done.record(torch.cuda.current_stream(self.device))
+        return t
+
+    def _upload(self, img, slot):
+        """uint8 BGR (H,W,3) -> float RGB (1,3,H,W) on the device (raft.py:113-120, conversion moved to the device)."""
+        return self.upload_u8(img, slot).flip(-1).permute(2, 0, 1).float()[None]
 
     def _forward(self, src, dst):
         kwargs = dict(iters=self.iters, test_mode=True, corr_block=self.corr_block)

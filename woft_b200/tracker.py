@@ -76,11 +76,30 @@ def find_homography(pts_A, pts_B, weights=None):
     return lsq.find_homography_nonhomogeneous_QR(pts_A, pts_B, weights=weights)
 
 
-def default_config(flow_config):
-    """get_config() of the default tracker config (:56-71)."""
+def default_config(flow_config, device_prewarp=True):
+    """get_config() of the default tracker config (:56-71).  `device_prewarp` (not a reference key) moves the
+    cv2.warpPerspective pre-warp and its validity mask onto the GPU (woft_warp_perspective_u8)."""
     return SimpleNamespace(flow_config=flow_config, H_estimator=find_homography, redet_success_fn=redet_success_fn,
                            pw_mask=True, no_prewarp_after_N=10, subsampler_fn=subsampler, no_local_H=False,
-                           do_not_mask_TCs_by_prewarped=False)
+                           do_not_mask_TCs_by_prewarped=False, device_prewarp=device_prewarp)
+
+
+def prewarp_on_device(frame_u8, H, want_mask=True):
+    """(H,W,3) uint8 device tensor warped by the 3x3 matrix `H` the way cv2.warpPerspective(frame, H, (W,H),
+    flags=INTER_LINEAR) does, and the `> 0` mask of an image of ones warped alike (:89-95)."""
+    from . import _lib
+    import ctypes
+    h, w, c = frame_u8.shape
+    frame_u8 = frame_u8.contiguous()
+    out = torch.empty_like(frame_u8)
+    mask = torch.empty((h, w), dtype=torch.uint8, device=frame_u8.device) if want_mask else None
+    inv = np.ascontiguousarray(np.linalg.inv(np.asarray(H, dtype=np.float64)))
+    with torch.cuda.device(frame_u8.device):
+        rc = _lib.load().woft_warp_perspective_u8(_lib.ptr(frame_u8), h, w, c,
+                                                  inv.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), _lib.ptr(out),
+                                                  _lib.ptr(mask), _lib.current_stream(frame_u8.device))
+    _lib.check(rc, "woft_warp_perspective_u8")
+    return out, (mask.bool() if want_mask else None)
 
 
 class PlanarTracker:
@@ -95,6 +114,8 @@ class PlanarTracker:
     def init(self, img, mask):
         """:26-47."""
         self.template_img = img
+        self.template_dev = self.flower.upload_u8(img, slot=2).clone() if _cfg(self.C, "device_prewarp", False) else None
+        self.prev_dev = self.template_dev
         self.template_mask = torch.from_numpy(mask > 0).to(self.device)
         self.np_template_mask = mask
         self.prev_H2init = np.eye(3)
@@ -111,11 +132,19 @@ class PlanarTracker:
             self.last_good_H2init = np.eye(3)
         prewarp_H = self.last_good_H2init
         h, w = input_img.shape[:2]
-        prewarped = cv2.warpPerspective(input_img, prewarp_H, (w, h), flags=cv2.INTER_LINEAR)
-        pw_mask = cv2.warpPerspective(np.ones((h, w)), prewarp_H, (w, h), flags=cv2.INTER_LINEAR)
-        pw_mask = torch.from_numpy(pw_mask > 0).to(self.device, non_blocking=True)
+        on_device = _cfg(self.C, "device_prewarp", False)
+        if on_device:
+            frame_dev = self.flower.upload_u8(input_img, slot=1)
+            prewarped, pw_mask = prewarp_on_device(frame_dev, prewarp_H)
+            template = self.template_dev
+        else:
+            frame_dev = None
+            prewarped = cv2.warpPerspective(input_img, prewarp_H, (w, h), flags=cv2.INTER_LINEAR)
+            pw_mask = cv2.warpPerspective(np.ones((h, w)), prewarp_H, (w, h), flags=cv2.INTER_LINEAR)
+            pw_mask = torch.from_numpy(pw_mask > 0).to(self.device, non_blocking=True)
+            template = self.template_img
 
-        H_pw2init, ok, t_coords, c_coords, weights = self.estimate_global(self.template_img, prewarped, pw_mask)
+        H_pw2init, ok, t_coords, c_coords, weights = self.estimate_global(template, prewarped, pw_mask)
         H_np = H_pw2init.detach().cpu().numpy()[0].astype(np.float64)   # D2H of the 3x3 (reference :156)
         H_global = compose_H(prewarp_H, H_np)
         meta.H_global_cur2init = H_global.copy()
@@ -129,7 +158,9 @@ class PlanarTracker:
             if _cfg(self.C, "no_local_H", False):
                 H_cur2init = H_global
             else:
-                p_coords, c2_coords, w2 = self.flower.compute_flow(self.prev_img, input_img, mode="TC", do_sigmoid=True)
+                p_coords, c2_coords, w2 = self.flower.compute_flow(self.prev_dev if on_device else self.prev_img,
+                                                                   frame_dev if on_device else input_img, mode="TC",
+                                                                   do_sigmoid=True)
                 self.flow_passes += 1
                 p_coords, c2_coords, w2 = self._mask_coords_flow(p_coords, c2_coords, w2)
                 if self.C.subsampler_fn:
@@ -145,7 +176,10 @@ class PlanarTracker:
                 meta.H_local_cur2init = H_local.copy()
                 H_cur2init = H_local
 
-        self.prev_img = input_img.copy()
+        if on_device:
+            self.prev_dev = frame_dev
+        else:
+            self.prev_img = input_img.copy()
         self.prev_H2init = H_cur2init.copy()
         if not self.lost:
             self.last_good_H2init = H_cur2init.copy()

@@ -41,6 +41,7 @@ def test_version_and_sizes_without_gpu(lib):
     tf32 = lib.woft_corr_workspace_bytes(1, 256, 90, 160, 1)
     x3 = lib.woft_corr_workspace_bytes(1, 256, 90, 160, 2)
     bf16 = lib.woft_corr_workspace_bytes(1, 256, 90, 160, 3)
+    assert lib.woft_corr_workspace_bytes(1, 256, 90, 160, 4) == bf16
     packed = 14400 * 256 * 4
     assert 0 < simt < 8192
     assert 2 * packed <= tf32 < 2 * packed + 8192

@@ -17,9 +17,12 @@ import torch.nn.functional as F
 
 from . import _lib
 
-#: arithmetic of the all-pairs GEMM: "tf32" (tensor cores, default), "tf32x3" (tensor cores, fp32-class result),
-#: "bf16" (tensor cores), "fp32" (CUDA cores, the reference's precision class)
-DEFAULT_MODE = os.environ.get("WOFT_CORR_MODE", "tf32")
+#: arithmetic of the all-pairs GEMM, all with fp32 accumulation:
+#:   "fp16"   tensor cores, operands rounded to fp16 (10-bit mantissa like tf32, half the operand bytes) -- default
+#:   "tf32"   tensor cores, operands rounded to tf32        "bf16"  tensor cores, 7-bit mantissa
+#:   "tf32x3" tensor cores, error-compensated split, fp32-class result
+#:   "fp32"   CUDA cores, the reference's own precision class
+DEFAULT_MODE = os.environ.get("WOFT_CORR_MODE", "fp16")
 
 
 def _as_f32c(t):

@@ -34,6 +34,7 @@
 // (x3 for WOFT_CORR_TF32X3).  At 1280x720 (HW = 14 400, C = 256): 1.10 GB, 106 GFLOP -> HBM-write bound.
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <cstdlib>
 
@@ -68,14 +69,19 @@ struct CorrTcParams {
   int k_blocks;   // 128-byte K rows per plane
   int k_elems;    // elements per 128-byte K row (32 tf32 / 64 bf16)
   int n_pairs;    // 1, or 3 for the hi/lo split
-  int bf16;
+  int bf16;       // 16-bit operands (kind::f16): 1 = bf16, 2 = fp16; 0 = tf32 (kind::tf32)
   int a_resident; // 1: the A tile (all k blocks) stays in shared memory while a CTA walks `unit` consecutive N tiles
   int unit;       // tiles per work unit (consecutive tile ids share b and the M tile)
   int stages;     // operand stages (A+B, or B only when A is resident)
   int nslot;      // epilogue staging ring slots
   float scale;
   int* abort_flag;
+  unsigned long long* trace;  // debug (WOFT_CORR_TRACE): [cta < 4][tile < 64][6] globaltimer stamps, else null
 };
+
+__device__ __forceinline__ void trace_stamp(const CorrTcParams& p, int it, int slot) {
+  if (p.trace && blockIdx.x < 4 && it < 64) p.trace[(blockIdx.x * 64 + it) * 6 + slot] = ptx::globaltimer_ns();
+}
 
 // ---------------------------------------------------------------------------------------------------
 // pack: (B, C, HW) fp32 -> K-major (planes, B, HW, Kp)
@@ -86,7 +92,7 @@ __device__ __forceinline__ float round_tf32(float x) {
   return __uint_as_float(r);
 }
 
-template <int MODE>  // 1 tf32, 2 tf32 hi/lo, 3 bf16
+template <int MODE>  // 1 tf32, 2 tf32 hi/lo, 3 bf16, 4 fp16
 __global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src1, const float* __restrict__ src2,
                                                    void* __restrict__ dst1, void* __restrict__ dst2, int B, int C,
                                                    int HW, int Kp, size_t plane_elems, int* flag) {
@@ -113,6 +119,8 @@ __global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src
     const size_t o = ((size_t)b * HW + hw) * Kp + c;
     if (MODE == 3) {
       reinterpret_cast<__nv_bfloat16*>(dst)[o] = __float2bfloat16_rn(v);
+    } else if (MODE == 4) {
+      reinterpret_cast<__half*>(dst)[o] = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));  // saturate, no inf
     } else {
       const float hi = round_tf32(v);
       reinterpret_cast<float*>(dst)[o] = hi;
@@ -257,10 +265,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
       bool alive = true;
       int cur_a = -1;          // (b, M tile) whose A tile is resident
       uint32_t a_loads = 0;
+      int pit = 0;
       for (int chunk = blockIdx.x; chunk * p.unit < p.total_tiles && alive; chunk += gridDim.x) {
         const int t_end = min((chunk + 1) * p.unit, p.total_tiles);
-        for (int t = chunk * p.unit; t < t_end && alive; ++t) {
+        for (int t = chunk * p.unit; t < t_end && alive; ++t, ++pit) {
           const TileCoord tc = decode_tile(p, t);
+          trace_stamp(p, pit, 0);
           const int a_id = tc.b * p.m_tiles + tc.m0 / BM;
           const bool reload = p.a_resident && a_id != cur_a;
           cur_a = a_id;
@@ -296,6 +306,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
               phase ^= 1u;
             }
           }
+          trace_stamp(p, pit, 1);
           if (reload && alive && pre == k_steps) {  // k_steps <= STAGES: the A swap comes after all B loads
             if (!wait_or_abort(a_empty, (a_loads & 1u) ^ 1u, p.abort_flag)) {
               alive = false;
@@ -312,7 +323,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
     if (lane == 0) {
-      const uint32_t fmt = p.bf16 ? 1u : 2u;  // F16F32Format: BF16 = 1, TF32 = 2
+      const uint32_t fmt = p.bf16 == 1 ? 1u : p.bf16 == 2 ? 0u : 2u;  // F16F32Format: F16 = 0, BF16 = 1, TF32 = 2
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(BN >> 3) << 17) | (uint32_t(BM >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
@@ -341,6 +352,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
             break;
           }
           ptx::tc_fence_after_sync();
+          trace_stamp(p, it, 2);
           const uint32_t d_tmem = tmem_base + uint32_t(buf * BN);
           for (int ks = 0; ks < k_steps; ++ks) {
             if (!wait_or_abort(full + stage, phase, p.abort_flag)) {
@@ -366,6 +378,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
             }
           }
           if (alive) ptx::mma_commit(tfull + buf);
+          trace_stamp(p, it, 3);
         }
       }
     }
@@ -391,6 +404,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
         go = false;
         break;
       }
+      if (issuer) trace_stamp(p, it, 4);
       ptx::tc_fence_after_sync();
       const int mq = tc.m0 + m;
 
@@ -500,6 +514,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
           ++ev;
         }
       }
+      if (issuer) trace_stamp(p, it, 5);
     }
     }
     if (issuer) ptx::tma_store_wait_all();
@@ -552,7 +567,7 @@ struct TcLayout {
 
 TcLayout tc_layout(int B, int C, int HW, int mode) {
   TcLayout L{};
-  L.elem_bytes = (mode == WOFT_CORR_BF16) ? 2 : 4;
+  L.elem_bytes = (mode == WOFT_CORR_BF16 || mode == WOFT_CORR_FP16) ? 2 : 4;
   L.k_elems = 128 / L.elem_bytes;
   L.Kp = (C + L.k_elems - 1) / L.k_elems * L.k_elems;
   L.planes = (mode == WOFT_CORR_TF32X3) ? 2 : 1;
@@ -589,6 +604,8 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
     const size_t plane_elems = L.plane_bytes / L.elem_bytes;
     if (mode == WOFT_CORR_BF16)
       pack_kernel<3><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
+    else if (mode == WOFT_CORR_FP16)
+      pack_kernel<4><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
     else if (mode == WOFT_CORR_TF32X3)
       pack_kernel<2><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
     else
@@ -598,7 +615,9 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   }
 
   CorrTcParams p{};
-  const CUtensorMapDataType dt = (mode == WOFT_CORR_BF16) ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  const CUtensorMapDataType dt = (mode == WOFT_CORR_BF16)   ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
+                                 : (mode == WOFT_CORR_FP16) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                                            : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   // the hi and lo planes lie back to back, so they fold into the batch dimension of the operand maps
   {
     cuuint64_t dims[3] = {(cuuint64_t)L.Kp, (cuuint64_t)HW, (cuuint64_t)(B * L.planes)};
@@ -644,7 +663,7 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   p.k_blocks = L.Kp / L.k_elems;
   p.k_elems = L.k_elems;
   p.n_pairs = (mode == WOFT_CORR_TF32X3) ? 3 : 1;
-  p.bf16 = (mode == WOFT_CORR_BF16) ? 1 : 0;
+  p.bf16 = (mode == WOFT_CORR_BF16) ? 1 : (mode == WOFT_CORR_FP16) ? 2 : 0;
   p.scale = 1.0f / sqrtf(float(C));
   p.abort_flag = flag;
 
@@ -688,8 +707,30 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   const int chunks = ceil_div(p.total_tiles, p.unit);
   const int grid = chunks < sms ? chunks : sms;
+  const char* trace_path = getenv("WOFT_CORR_TRACE");  // debug aid: per-role timestamps of the first 4 CTAs
+  p.trace = nullptr;
+  const size_t trace_bytes = 4 * 64 * 6 * sizeof(unsigned long long);
+  if (trace_path) {
+    WOFT_CUDA_CHECK(cudaMalloc(&p.trace, trace_bytes));
+    WOFT_CUDA_CHECK(cudaMemsetAsync(p.trace, 0, trace_bytes, stream));
+  }
   corr_tc_kernel<<<grid, TC_THREADS, smem_bytes, stream>>>(p);
-  return launch_status("corr_tc_kernel");
+  int rc = launch_status("corr_tc_kernel");
+  if (trace_path && rc == WOFT_OK) {
+    static unsigned long long host_trace[4 * 64 * 6];
+    WOFT_CUDA_CHECK(cudaMemcpyAsync(host_trace, p.trace, trace_bytes, cudaMemcpyDeviceToHost, stream));
+    WOFT_CUDA_CHECK(cudaStreamSynchronize(stream));
+    WOFT_CUDA_CHECK(cudaFree(p.trace));
+    if (FILE* f = fopen(trace_path, "w")) {
+      for (int c = 0; c < 4; ++c)
+        for (int t = 0; t < 64; ++t) {
+          const unsigned long long* r = host_trace + (c * 64 + t) * 6;
+          if (r[0] || r[2] || r[4]) fprintf(f, "%d %d %llu %llu %llu %llu %llu %llu\n", c, t, r[0], r[1], r[2], r[3], r[4], r[5]);
+        }
+      fclose(f);
+    }
+  }
+  return rc;
 }
 
 size_t corr_tc_workspace_bytes(int B, int C, int HW, int mode) { return tc_layout(B, C, HW, mode).total; }

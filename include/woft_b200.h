@@ -102,6 +102,8 @@ int woft_corr_check(const void* workspace, void* stream);
  *   levels : HOST array of `num_levels` device pointers as written by woft_corr_pyramid (h2 x w2 at level 0)
  *   coords : (B, 2, H1, W1), channel 0 = x, channel 1 = y
  *   out    : (B, num_levels*(2r+1)^2, H1, W1); channel = l*(2r+1)^2 + (xoff+r)*(2r+1) + (yoff+r)
+ *   flags  : bit 0 = scalar loads (testing); bit 3 (8) = write `out` channels-last, (B, H1, W1, channels), for an
+ *            NHWC consumer (same values)
  * Level maps narrower than 2 pixels make the reference return NaN (division by W-1 = 0, utils.py:63-64);
  * this call rejects them with WOFT_ERR_INVALID_ARGUMENT instead.
  */
@@ -143,6 +145,21 @@ int woft_gru_gates(const float* zr, const float* bias_zr, const float* h, int ba
                    float* rh, void* stream);
 int woft_gru_update(const float* q, const float* bias_q, const float* z, const float* h, int batch, int channels,
                     int hw, float* h_new, void* stream);
+
+/* Channels-last (NHWC) forms of the two GRU kernels, and the concatenation that feeds the update block's
+ * convolutions (torch.cat at update.py:47,51,54,58,96-97,129).  Tensors are (pixels, channels) with the channels of a
+ * pixel contiguous; `*_stride` is the distance in floats between consecutive pixels, so an operand can be a channel
+ * slice of a wider buffer -- the GRU keeps [h | x] and [r*h | x] in two persistent buffers and never concatenates.
+ *   woft_gru_gates_nhwc : zr (pixels, 2C) dense; h, rh strided; z (pixels, C) dense
+ *   woft_gru_update_nhwc: h_out may alias h; h_dense (pixels, C) is an optional second, dense copy of the result
+ *   woft_concat_nhwc    : up to 4 dense sources (HOST arrays of pointers / channel counts) written side by side at
+ *                         channel offset dst_offset of dst (and of dst2 when not NULL) */
+int woft_gru_gates_nhwc(const float* zr, const float* bias_zr, const float* h, int h_stride, long long pixels,
+                        int channels, float* z, float* rh, int rh_stride, void* stream);
+int woft_gru_update_nhwc(const float* q, const float* bias_q, const float* z, const float* h, int h_stride,
+                         long long pixels, int channels, float* h_out, int h_out_stride, float* h_dense, void* stream);
+int woft_concat_nhwc(const float* const* srcs, const int* channels, int n_src, long long pixels, float* dst,
+                     int dst_stride, int dst_offset, float* dst2, int dst2_stride, int dst2_offset, void* stream);
 
 /* Replaces nn.InstanceNorm2d + ReLU after each convolution of the feature encoder
  * (raft_core/extractor.py:30-32, 49-50, 127, 180-181): per (n, c) plane y = (x - mean) / sqrt(var + eps), biased

@@ -39,7 +39,7 @@ def cu(a):
 # ----------------------------------------------------------------------------------------------------
 # K3 lookup
 # ----------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("flags", [0, 1])
+@pytest.mark.parametrize("flags", [0, 1, 8, 9])
 def test_lookup_on_golden_pyramid(golden, flags):
     """K3 alone: feed the reference's own pyramid, compare with the reference's lookup."""
     from woft_b200.corr import CorrBlock
@@ -49,7 +49,8 @@ def test_lookup_on_golden_pyramid(golden, flags):
     blk.corr_pyramid = [cu(g[f"level{l}"]) for l in range(4)]
     for tag in ("grid", "jitter", "oob"):
         out = blk(cu(g[f"coords_{tag}"]), flags=flags)
-        assert out.shape == (1, 324, 16, 24) and out.is_contiguous()
+        assert out.shape == (1, 324, 16, 24)
+        assert out.is_contiguous(memory_format=torch.channels_last if flags & 8 else torch.contiguous_format)
         np.testing.assert_allclose(out.cpu().numpy(), g[f"lookup_{tag}"], atol=2e-5, err_msg=tag)
 
 
@@ -390,3 +391,44 @@ def test_device_prewarp_matches_opencv():
         assert diff.max() <= 1, f"max grey-level difference {diff.max()}"
         assert diff.mean() < 0.05
         assert (mask.cpu().numpy() != want_mask).mean() < 1e-3
+
+
+def test_nhwc_gru_and_concat_kernels():
+    from woft_b200 import _lib, fast_net
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(6)
+    B, C, H, W = 2, 128, 18, 28
+    cl = torch.channels_last
+    a = torch.randn((B, 192, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    b = torch.randn((B, 126, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    c = torch.randn((B, 2, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    d1 = torch.zeros((B, 384, H, W), device=DEV).contiguous(memory_format=cl)
+    d2 = torch.zeros((B, 400, H, W), device=DEV).contiguous(memory_format=cl)
+    fast_net.concat_nhwc([a, b, c], d1, 64, d2, 80)
+    want = torch.cat([a, b, c], dim=1)
+    assert torch.equal(d1[:, 64:], want) and torch.equal(d2[:, 80:], want)
+    assert d1[:, :64].abs().sum().item() == 0
+    # gates / update on channel slices of wider buffers, against the NCHW formulas
+    buf1 = torch.randn((B, 3 * C, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    buf2 = torch.zeros_like(buf1)
+    zr = torch.randn((B, 2 * C, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    bias = torch.randn((2 * C,), generator=g).to(DEV)
+    z = torch.empty((B, C, H, W), device=DEV).contiguous(memory_format=cl)
+    h = buf1[:, :C].clone()
+    st = _lib.current_stream(torch.device(DEV))
+    rc = lib.woft_gru_gates_nhwc(_lib.ptr(zr), _lib.ptr(bias), _lib.ptr(buf1), 3 * C, B * H * W, C, _lib.ptr(z),
+                                 _lib.ptr(buf2), 3 * C, st)
+    assert rc == 0
+    zb = zr + bias.view(1, -1, 1, 1)
+    assert torch.allclose(z, torch.sigmoid(zb[:, :C]), atol=1e-6)
+    assert torch.allclose(buf2[:, :C], torch.sigmoid(zb[:, C:]) * h, atol=1e-6)
+    q = torch.randn((B, C, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    bq = torch.randn((C,), generator=g).to(DEV)
+    hd = torch.empty((B, C, H, W), device=DEV).contiguous(memory_format=cl)
+    tail = buf1[:, C:].clone()
+    rc = lib.woft_gru_update_nhwc(_lib.ptr(q), _lib.ptr(bq), _lib.ptr(z), _lib.ptr(buf1), 3 * C, B * H * W, C,
+                                  _lib.ptr(buf1), 3 * C, _lib.ptr(hd), st)
+    assert rc == 0
+    want = (1 - z) * h + z * torch.tanh(q + bq.view(1, -1, 1, 1))
+    assert torch.allclose(hd, want, atol=2e-6) and torch.allclose(buf1[:, :C], want, atol=2e-6)
+    assert torch.equal(buf1[:, C:], tail)

@@ -75,7 +75,9 @@ class CorrBlock:
             raise AssertionError(f"coords must be ({B},2,{H},{W}), got {tuple(coords.shape)}")
         P = 2 * self.radius + 1
         dev = coords.device
-        out = torch.empty((B, self.num_levels * P * P, H, W), device=dev, dtype=torch.float32)
+        # flags bit 3: channels-last output for an NHWC consumer (same logical shape and values)
+        fmt = torch.channels_last if flags & 8 else torch.contiguous_format
+        out = torch.empty((B, self.num_levels * P * P, H, W), device=dev, dtype=torch.float32, memory_format=fmt)
         with torch.cuda.device(dev):
             levels, keep = _lib.ptr_array(self.corr_pyramid)
             rc = _lib.load().woft_corr_lookup(levels, self.num_levels, _lib.ptr(coords), B, H, W, H, W, self.radius,

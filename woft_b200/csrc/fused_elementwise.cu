@@ -114,6 +114,90 @@ __global__ void __launch_bounds__(512) instance_norm_relu_kernel(const float* __
   for (int i = (n4 << 2) + threadIdx.x; i < HW; i += blockDim.x) dst[i] = fmaxf((__ldg(src + i) - mean) * rstd, floor_);
 }
 
+// ---- channels-last (NHWC) variants: a pixel's channels are contiguous; operands may be channel slices of wider
+// buffers (pixel stride > channel count), which is how the GRU avoids torch.cat: [h | x] and [r*h | x] live in two
+// persistent (pixels, C + Cx) buffers whose x part is written once per iteration.
+__global__ void gru_gates_nhwc_kernel(const float* __restrict__ zr, const float* __restrict__ bias,
+                                      const float* __restrict__ h, int h_stride, float* __restrict__ z,
+                                      float* __restrict__ rh, int rh_stride, int C4, long long total4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / C4;
+    const int c4 = int(i - pix * C4);
+    const float4 zp = __ldg(reinterpret_cast<const float4*>(zr + pix * (8 * C4)) + c4);
+    const float4 rp = __ldg(reinterpret_cast<const float4*>(zr + pix * (8 * C4) + 4 * C4) + c4);
+    const float4 hv = __ldg(reinterpret_cast<const float4*>(h + pix * h_stride) + c4);
+    const float4 bz = __ldg(reinterpret_cast<const float4*>(bias) + c4);
+    const float4 br = __ldg(reinterpret_cast<const float4*>(bias + 4 * C4) + c4);
+    float4 zo, ro;
+    zo.x = sigmoidf_(zp.x + bz.x); zo.y = sigmoidf_(zp.y + bz.y); zo.z = sigmoidf_(zp.z + bz.z); zo.w = sigmoidf_(zp.w + bz.w);
+    ro.x = sigmoidf_(rp.x + br.x) * hv.x; ro.y = sigmoidf_(rp.y + br.y) * hv.y;
+    ro.z = sigmoidf_(rp.z + br.z) * hv.z; ro.w = sigmoidf_(rp.w + br.w) * hv.w;
+    reinterpret_cast<float4*>(z + pix * (4 * C4))[c4] = zo;
+    reinterpret_cast<float4*>(rh + pix * rh_stride)[c4] = ro;
+  }
+}
+
+__global__ void gru_update_nhwc_kernel(const float* __restrict__ q, const float* __restrict__ bias,
+                                       const float* __restrict__ z, const float* h, int h_stride, float* h_out,
+                                       int h_out_stride, float* __restrict__ h_dense, int C4, long long total4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / C4;
+    const int c4 = int(i - pix * C4);
+    const float4 qv = __ldg(reinterpret_cast<const float4*>(q + pix * (4 * C4)) + c4);
+    const float4 zv = __ldg(reinterpret_cast<const float4*>(z + pix * (4 * C4)) + c4);
+    const float4 hv = *(reinterpret_cast<const float4*>(h + pix * h_stride) + c4);  // may alias h_out
+    const float4 bq = __ldg(reinterpret_cast<const float4*>(bias) + c4);
+    float4 o;
+    o.x = (1.f - zv.x) * hv.x + zv.x * tanhf(qv.x + bq.x);
+    o.y = (1.f - zv.y) * hv.y + zv.y * tanhf(qv.y + bq.y);
+    o.z = (1.f - zv.z) * hv.z + zv.z * tanhf(qv.z + bq.z);
+    o.w = (1.f - zv.w) * hv.w + zv.w * tanhf(qv.w + bq.w);
+    reinterpret_cast<float4*>(h_out + pix * h_out_stride)[c4] = o;
+    if (h_dense) reinterpret_cast<float4*>(h_dense + pix * (4 * C4))[c4] = o;
+  }
+}
+
+struct ConcatParams {
+  const float* src[4];
+  int ch[4];      // channels of each source (dense: pixel stride = channels)
+  int off[4];     // channel offset of each source inside a destination pixel
+  int n_src;
+  int total_ch;
+  float* dst[2];
+  int dst_stride[2];
+  int dst_off[2];
+  int n_dst;
+};
+
+// dst[d][pix * stride_d + off_d + off_i + c] = src_i[pix * ch_i + c]; VW floats per thread and step
+template <int VW>
+__global__ void concat_nhwc_kernel(const ConcatParams p, long long pixels) {
+  const int per_pixel = p.total_ch / VW;
+  const long long total = pixels * per_pixel;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long pix = i / per_pixel;
+    int c = int(i - pix * per_pixel) * VW;  // channel within the concatenation
+    int s = 0;
+    while (s + 1 < p.n_src && c >= p.off[s + 1]) ++s;
+    const float* src = p.src[s] + pix * p.ch[s] + (c - p.off[s]);
+    float v[VW];
+#pragma unroll
+    for (int k = 0; k < VW; ++k) v[k] = __ldg(src + k);
+    for (int d = 0; d < p.n_dst; ++d) {
+      float* o = p.dst[d] + pix * p.dst_stride[d] + p.dst_off[d] + c;
+      if (VW == 4)
+        *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[VW > 3 ? 3 : 0]);
+      else if (VW == 2)
+        *reinterpret_cast<float2*>(o) = make_float2(v[0], v[VW > 1 ? 1 : 0]);
+      else
+        o[0] = v[0];
+    }
+  }
+}
+
 static int ew_grid(long long total4) {
   const long long blocks = (total4 + 255) / 256;
   return int(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
@@ -152,4 +236,72 @@ extern "C" int woft_instance_norm_relu(const float* x, int planes, int hw, float
                "woft_instance_norm_relu: planes must be 16-byte aligned (H*W a multiple of 4)");
   instance_norm_relu_kernel<<<planes, 512, 0, static_cast<cudaStream_t>(stream)>>>(x, y, hw, eps, relu);
   return launch_status("instance_norm_relu_kernel");
+}
+
+extern "C" int woft_gru_gates_nhwc(const float* zr, const float* bias_zr, const float* h, int h_stride,
+                                   long long pixels, int channels, float* z, float* rh, int rh_stride, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(zr && bias_zr && h && z && rh, "woft_gru_gates_nhwc: null pointer");
+  WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0 && h_stride % 4 == 0 && rh_stride % 4 == 0,
+               "woft_gru_gates_nhwc: channels and strides must be positive multiples of 4");
+  const long long total4 = pixels * (channels / 4);
+  gru_gates_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(zr, bias_zr, h, h_stride, z, rh,
+                                                                                        rh_stride, channels / 4, total4);
+  return launch_status("gru_gates_nhwc_kernel");
+}
+
+extern "C" int woft_gru_update_nhwc(const float* q, const float* bias_q, const float* z, const float* h, int h_stride,
+                                    long long pixels, int channels, float* h_out, int h_out_stride, float* h_dense,
+                                    void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(q && bias_q && z && h && h_out, "woft_gru_update_nhwc: null pointer");
+  WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0 && h_stride % 4 == 0 && h_out_stride % 4 == 0,
+               "woft_gru_update_nhwc: channels and strides must be positive multiples of 4");
+  const long long total4 = pixels * (channels / 4);
+  gru_update_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      q, bias_q, z, h, h_stride, h_out, h_out_stride, h_dense, channels / 4, total4);
+  return launch_status("gru_update_nhwc_kernel");
+}
+
+extern "C" int woft_concat_nhwc(const float* const* srcs, const int* channels, int n_src, long long pixels, float* dst,
+                                int dst_stride, int dst_offset, float* dst2, int dst2_stride, int dst2_offset,
+                                void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(srcs && channels && dst, "woft_concat_nhwc: null pointer");
+  WOFT_REQUIRE(n_src >= 1 && n_src <= 4 && pixels > 0, "woft_concat_nhwc: 1..4 sources and a positive pixel count");
+  ConcatParams p{};
+  int off = 0, vw = 4;
+  for (int i = 0; i < n_src; ++i) {
+    WOFT_REQUIRE(srcs[i] && channels[i] > 0, "woft_concat_nhwc: source %d is empty", i);
+    p.src[i] = srcs[i];
+    p.ch[i] = channels[i];
+    p.off[i] = off;
+    off += channels[i];
+    while (vw > 1 && (channels[i] % vw || p.off[i] % vw || (reinterpret_cast<uintptr_t>(srcs[i]) % (4 * vw)))) vw >>= 1;
+  }
+  p.n_src = n_src;
+  p.total_ch = off;
+  p.dst[0] = dst;
+  p.dst_stride[0] = dst_stride;
+  p.dst_off[0] = dst_offset;
+  p.n_dst = 1;
+  if (dst2) {
+    p.dst[1] = dst2;
+    p.dst_stride[1] = dst2_stride;
+    p.dst_off[1] = dst2_offset;
+    p.n_dst = 2;
+  }
+  for (int d = 0; d < p.n_dst; ++d)
+    while (vw > 1 && (p.dst_stride[d] % vw || p.dst_off[d] % vw || (reinterpret_cast<uintptr_t>(p.dst[d]) % (4 * vw))))
+      vw >>= 1;
+  const long long total = pixels * (off / vw);
+  const int grid = ew_grid(total);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (vw == 4)
+    concat_nhwc_kernel<4><<<grid, 256, 0, s>>>(p, pixels);
+  else if (vw == 2)
+    concat_nhwc_kernel<2><<<grid, 256, 0, s>>>(p, pixels);
+  else
+    concat_nhwc_kernel<1><<<grid, 256, 0, s>>>(p, pixels);
+  return launch_status("concat_nhwc_kernel");
 }

@@ -49,7 +49,7 @@ struct LookupGeom {
   static constexpr int ROWS_PER_THREAD = (ROWS + kLookupThreads - 1) / kLookupThreads;
 };
 
-template <int R, bool VEC>
+template <int R, bool VEC, bool NHWC>
 __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __grid_constant__ LookupParams p) {
   using G = LookupGeom<R>;
   constexpr int P = G::P, WIN = G::WIN, STRIDE = G::STRIDE;
@@ -141,8 +141,27 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
     }
     __syncthreads();
 
-    // ---- compute phase: warp = level slot, lane = (half, query); taps stored coalesced across queries
-    {
+    // ---- compute phase
+    if (NHWC) {
+      // channels-last output (B, H1, W1, L*P*P): a warp takes one (level, query) footprint at a time and its lanes
+      // take consecutive taps, so every store instruction writes 128 contiguous bytes of that query's channel row
+      const int warp = tid >> 5, lane = tid & 31;
+      for (int pair = warp; pair < kLevelsPerPass * kQueriesPerCta; pair += kLookupThreads / 32) {
+        const int slot = pair >> 4, ql = pair & 15;
+        const int lvl = lv0 + slot, q = q0 + ql;
+        if (lvl >= p.num_levels || q >= p.nq) continue;  // warp-uniform
+        const float* my = win + pair * STRIDE;
+        const float ax = s_ax[pair], ay = s_ay[pair];
+        const float w00 = (1.f - ax) * (1.f - ay), w01 = ax * (1.f - ay), w10 = (1.f - ax) * ay, w11 = ax * ay;
+        float* o = p.out + (size_t)q * channels + (size_t)lvl * P * P;
+        for (int t = lane; t < P * P; t += 32) {
+          const int xo = t / P, yo = t - xo * P;  // channel = (xoff+r)*P + (yoff+r)
+          const float* c = my + yo * WIN + xo;
+          o[t] = c[0] * w00 + c[1] * w01 + c[WIN] * w10 + c[WIN + 1] * w11;
+        }
+      }
+    } else {
+      // warp = level slot, lane = (half, query); taps stored coalesced across queries (channel-first output)
       const int slot = tid >> 5, lane = tid & 31;
       const int ql = lane & 15, half = lane >> 4;
       const int lvl = lv0 + slot;
@@ -182,12 +201,16 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
 }
 
 template <int R>
-static int launch_lookup(const LookupParams& p, bool vec, cudaStream_t stream) {
+static int launch_lookup(const LookupParams& p, bool vec, bool nhwc, cudaStream_t stream) {
   const int grid = ceil_div(p.nq, kQueriesPerCta);
-  if (vec)
-    corr_lookup_kernel<R, true><<<grid, kLookupThreads, 0, stream>>>(p);
+  if (vec && nhwc)
+    corr_lookup_kernel<R, true, true><<<grid, kLookupThreads, 0, stream>>>(p);
+  else if (vec)
+    corr_lookup_kernel<R, true, false><<<grid, kLookupThreads, 0, stream>>>(p);
+  else if (nhwc)
+    corr_lookup_kernel<R, false, true><<<grid, kLookupThreads, 0, stream>>>(p);
   else
-    corr_lookup_kernel<R, false><<<grid, kLookupThreads, 0, stream>>>(p);
+    corr_lookup_kernel<R, false, false><<<grid, kLookupThreads, 0, stream>>>(p);
   return launch_status("corr_lookup_kernel");
 }
 
@@ -205,6 +228,7 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   LookupParams p{};
   int h = h2, w = w2;
   bool vec = (flags & 1) == 0;  // flags bit 0 forces the scalar load path (testing)
+  const bool nhwc = (flags & 8) != 0;  // flags bit 3: channels-last output (B, H1, W1, L*P*P)
   for (int l = 0; l < num_levels; ++l) {
     // the reference divides by (W-1), (H-1) and returns NaN for 1-pixel maps (utils.py:63-64)
     WOFT_REQUIRE(h >= 2 && w >= 2, "woft_corr_lookup: level %d is %dx%d; every level must be at least 2x2", l, h, w);
@@ -223,9 +247,9 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   p.hw1 = h1 * w1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (radius) {
-    case 1: return launch_lookup<1>(p, vec, s);
-    case 2: return launch_lookup<2>(p, vec, s);
-    case 3: return launch_lookup<3>(p, vec, s);
-    default: return launch_lookup<4>(p, vec, s);
+    case 1: return launch_lookup<1>(p, vec, nhwc, s);
+    case 2: return launch_lookup<2>(p, vec, nhwc, s);
+    case 3: return launch_lookup<3>(p, vec, nhwc, s);
+    default: return launch_lookup<4>(p, vec, nhwc, s);
   }
 }

@@ -19,6 +19,7 @@ import torch
 import torch.nn.functional as F
 
 from . import _lib
+from .corr import CorrBlock as _CorrBlock
 from .raft_net import convex_upsample, pixel_grid
 
 
@@ -59,10 +60,33 @@ def gru_update(q, bias_q, z, h):
     return out
 
 
+def _cl(t):
+    return t if t.is_contiguous(memory_format=torch.channels_last) else t.contiguous(memory_format=torch.channels_last)
+
+
+def _empty_cl(b, c, h, w, like):
+    return torch.empty((b, c, h, w), device=like.device, dtype=torch.float32, memory_format=torch.channels_last)
+
+
+def concat_nhwc(srcs, dst, dst_offset, dst2=None, dst2_offset=0):
+    """Channels-last tensors `srcs` (dense) written side by side into channel slice [dst_offset, ...) of `dst` (and of
+    `dst2`); woft_concat_nhwc."""
+    import ctypes
+    B, _, H, W = srcs[0].shape
+    ptrs, keep = _lib.ptr_array(srcs)
+    chans = (ctypes.c_int * len(srcs))(*[t.shape[1] for t in srcs])
+    with torch.cuda.device(dst.device):
+        rc = _lib.load().woft_concat_nhwc(ptrs, chans, len(srcs), B * H * W, _lib.ptr(dst), dst.shape[1], dst_offset,
+                                          _lib.ptr(dst2), dst2.shape[1] if dst2 is not None else 0, dst2_offset,
+                                          _lib.current_stream(dst.device))
+    del keep
+    _lib.check(rc, "woft_concat_nhwc")
+
+
 class FastWeightedRAFT:
     """Callable with the signature of WeightedRAFT.forward; built from a WeightedRAFT that already sits on the GPU."""
 
-    def __init__(self, net):
+    def __init__(self, net, nhwc_update=True):
         self.net = net
         self.with_weights = net.with_weights
         dev = next(net.parameters()).device
@@ -80,6 +104,18 @@ class FastWeightedRAFT:
             if self.with_weights:
                 self.head = [(m.weight.contiguous(memory_format=torch.channels_last), m.bias, m.padding)
                              for m in net.weight_head.net if isinstance(m, torch.nn.Conv2d)]
+            # channels-last copies of the update block's weights: with NHWC activations cuDNN's sm_100 kernels run
+            # without the NCHW<->NHWC conversion kernels that otherwise wrap every convolution
+            self.nhwc = nhwc_update
+            if nhwc_update:
+                ub, e = net.update_block, net.update_block.encoder
+                self.ubw = {name: (_cl(m.weight), m.bias) for name, m in (
+                    ("convc1", e.convc1), ("convc2", e.convc2), ("convf1", e.convf1), ("convf2", e.convf2),
+                    ("conv", e.conv), ("fh1", ub.flow_head.conv1), ("fh2", ub.flow_head.conv2), ("m0", ub.mask[0]),
+                    ("m2", ub.mask[2]))}
+                for tag in ("1", "2"):
+                    self.gru[tag]["w_zr"] = _cl(self.gru[tag]["w_zr"])
+                    self.gru[tag]["w_q"] = _cl(self.gru[tag]["w_q"])
 
     # ---- context encoder: fold eval-mode BatchNorm into the convolutions ---------------------------------
     @staticmethod
@@ -152,6 +188,52 @@ class FastWeightedRAFT:
             mask = 0.25 * F.conv2d(m, ub.mask[2].weight, ub.mask[2].bias)
         return net, mask, dflow
 
+    # ---- update block with channels-last activations and no torch.cat -----------------------------------------------
+    def _nhwc_state(self, net, inp):
+        B, C, H, W = net.shape
+        st = {"inp": _cl(inp), "h": _cl(net).clone(), "z": _empty_cl(B, C, H, W, net),
+              "buf1": _empty_cl(B, C + 2 * C, H, W, net), "buf2": _empty_cl(B, C + 2 * C, H, W, net), "C": C,
+              "pixels": B * H * W}
+        concat_nhwc([st["h"]], st["buf1"], 0)  # buf1 = [h | x], buf2 = [r*h | x]
+        return st
+
+    def _gru_half_nhwc(self, st, tag):
+        g, C, lib = self.gru[tag], st["C"], _lib.load()
+        buf1, buf2, dev = st["buf1"], st["buf2"], st["h"].device
+        zr = _cl(F.conv2d(buf1, g["w_zr"], None, padding=g["padding"]))
+        with torch.cuda.device(dev):
+            rc = lib.woft_gru_gates_nhwc(_lib.ptr(zr), _lib.ptr(g["b_zr"]), _lib.ptr(buf1), buf1.shape[1], st["pixels"], C,
+                                         _lib.ptr(st["z"]), _lib.ptr(buf2), buf2.shape[1], _lib.current_stream(dev))
+        _lib.check(rc, "woft_gru_gates_nhwc")
+        q = _cl(F.conv2d(buf2, g["w_q"], None, padding=g["padding"]))
+        with torch.cuda.device(dev):
+            rc = lib.woft_gru_update_nhwc(_lib.ptr(q), _lib.ptr(g["b_q"]), _lib.ptr(st["z"]), _lib.ptr(buf1), buf1.shape[1],
+                                          st["pixels"], C, _lib.ptr(buf1), buf1.shape[1], _lib.ptr(st["h"]),
+                                          _lib.current_stream(dev))
+        _lib.check(rc, "woft_gru_update_nhwc")
+
+    def _update_nhwc(self, st, corr, flow, need_mask):
+        w = self.ubw
+        flow = _cl(flow)
+        cor = _conv_relu(corr, *w["convc1"])
+        cor = _conv_relu(cor, *w["convc2"], padding=(1, 1))
+        flo = _conv_relu(flow, *w["convf1"], padding=(3, 3))
+        flo = _conv_relu(flo, *w["convf2"], padding=(1, 1))
+        B, _, H, W = cor.shape
+        cf = _empty_cl(B, cor.shape[1] + flo.shape[1], H, W, cor)
+        concat_nhwc([_cl(cor), _cl(flo)], cf, 0)
+        out = _conv_relu(cf, *w["conv"], padding=(1, 1))
+        C = st["C"]
+        concat_nhwc([st["inp"], _cl(out), flow], st["buf1"], C, st["buf2"], C)  # x = [inp | motion | flow]
+        self._gru_half_nhwc(st, "1")
+        self._gru_half_nhwc(st, "2")
+        h = st["h"]
+        dflow = F.conv2d(_conv_relu(h, *w["fh1"], padding=(1, 1)), *w["fh2"], padding=1)
+        mask = None
+        if need_mask:
+            mask = 0.25 * F.conv2d(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"])
+        return mask, dflow
+
     # ---- weight head, channels-last -----------------------------------------------------------------------------
     def _weights(self, window, mean_response):
         B, ch, H1, W1 = window.shape
@@ -161,7 +243,10 @@ class FastWeightedRAFT:
         # NHWC buffer (n, P, P, L+1): CNN input [lvl', hp, wp] is lookup channel hp*P*L + wp*L + lvl'
         # (the reference's reinterpretation of the lookup channels, weighted_raft.py:267-272)
         buf = torch.empty((n, P, P, L + 1), device=window.device, dtype=window.dtype)
-        buf[..., :L] = window.view(B, P, P, L, H1, W1).permute(0, 4, 5, 1, 2, 3).reshape(n, P, P, L)
+        if window.is_contiguous(memory_format=torch.channels_last) and not window.is_contiguous():
+            buf[..., :L] = window.permute(0, 2, 3, 1).reshape(n, P, P, L)  # NHWC lookup: already (n, hp, wp, lvl')
+        else:
+            buf[..., :L] = window.view(B, P, P, L, H1, W1).permute(0, 4, 5, 1, 2, 3).reshape(n, P, P, L)
         buf[..., L] = mean_response.reshape(n, 1, 1)
         x = buf.permute(0, 3, 1, 2)  # logical NCHW, channels-last in memory
         for w, b, pad in self.head[:-1]:
@@ -190,15 +275,24 @@ class FastWeightedRAFT:
         if flow_init is not None:
             coords1 = coords1 + flow_init
         up_mask = None
+        nhwc = self.nhwc and isinstance(corr_fn, _CorrBlock)
+        lookup_flags = 8 if nhwc else 0
+        state = self._nhwc_state(net, inp) if nhwc else None
         for it in range(iters):
-            corr = corr_fn(coords1)
-            net, up_mask, dflow = self._update(net, inp, corr, coords1 - coords0, need_mask=(it == iters - 1))
-            coords1 = coords1 + dflow
+            last = it == iters - 1
+            if nhwc:
+                corr = corr_fn(coords1, flags=lookup_flags)
+                up_mask, dflow = self._update_nhwc(state, corr, coords1 - coords0, need_mask=last)
+                coords1 = (coords1 + dflow).contiguous()
+            else:
+                corr = corr_fn(coords1)
+                net, up_mask, dflow = self._update(net, inp, corr, coords1 - coords0, need_mask=last)
+                coords1 = coords1 + dflow
         flow_low = coords1 - coords0
-        flow_up = convex_upsample(flow_low, up_mask)
+        flow_up = convex_upsample(flow_low, up_mask.contiguous())
         if not self.with_weights:
             return flow_low, flow_up
-        window = corr_fn(coords1)
+        window = corr_fn(coords1, flags=lookup_flags) if nhwc else corr_fn(coords1)
         weights = self._weights(window, corr_fn.mean_response())
-        weights_up = convex_upsample(weights, up_mask) / 8
+        weights_up = convex_upsample(weights, up_mask.contiguous()) / 8
         return flow_low, flow_up, corr_fn.corr_pyramid[0], weights, weights_up

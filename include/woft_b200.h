@@ -161,6 +161,16 @@ int woft_gru_update_nhwc(const float* q, const float* bias_q, const float* z, co
 int woft_concat_nhwc(const float* const* srcs, const int* channels, int n_src, long long pixels, float* dst,
                      int dst_stride, int dst_offset, float* dst2, int dst2_stride, int dst2_offset, void* stream);
 
+/* Two thin convolutions of the update block, 12 calls each per flow pass, fp32 on CUDA cores:
+ *   woft_flow_conv7x7_relu : BasicMotionEncoder.convf1 + ReLU (update.py:85, 92): 7x7, pad 3, 2 -> 128 channels.
+ *                            flow (B,2,H,W) NCHW, weight (128,2,7,7), bias (128) -> out (B,H,W,128) channels-last
+ *   woft_flow_out3x3       : FlowHead.conv2 (update.py:10, 14): 3x3, pad 1, C -> 2 channels + bias.
+ *                            in (B,H,W,C) channels-last, weight (2,C,3,3), bias (2) -> out (B,2,H,W) NCHW */
+int woft_flow_conv7x7_relu(const float* flow, const float* weight, const float* bias, int batch, int height, int width,
+                           float* out_nhwc, void* stream);
+int woft_flow_out3x3(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
+                     int channels, float* out_nchw, void* stream);
+
 /* Replaces nn.InstanceNorm2d + ReLU after each convolution of the feature encoder
  * (raft_core/extractor.py:30-32, 49-50, 127, 180-181): per (n, c) plane y = (x - mean) / sqrt(var + eps), biased
  * variance, no affine parameters, followed by ReLU when `relu` is non-zero (the 1x1 projection branch has none).

@@ -432,3 +432,25 @@ def test_nhwc_gru_and_concat_kernels():
     want = (1 - z) * h + z * torch.tanh(q + bq.view(1, -1, 1, 1))
     assert torch.allclose(hd, want, atol=2e-6) and torch.allclose(buf1[:, :C], want, atol=2e-6)
     assert torch.equal(buf1[:, C:], tail)
+
+
+def test_thin_convolution_kernels():
+    from woft_b200 import fast_net
+    g = torch.Generator().manual_seed(8)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        for (B, H, W) in ((1, 22, 36), (2, 16, 24)):
+            flow = (torch.randn((B, 2, H, W), generator=g) * 3).to(DEV)
+            w7 = (torch.randn((128, 2, 7, 7), generator=g) * 0.1).to(DEV)
+            b7 = torch.randn((128,), generator=g).to(DEV)
+            got = fast_net.flow_conv7x7_relu(flow, w7, b7)
+            assert got.is_contiguous(memory_format=torch.channels_last)
+            assert torch.allclose(got, F.relu(F.conv2d(flow, w7, b7, padding=3)), atol=2e-5)
+            x = torch.randn((B, 256, H, W), generator=g).to(DEV).contiguous(memory_format=torch.channels_last)
+            w3 = (torch.randn((2, 256, 3, 3), generator=g) * 0.05).to(DEV)
+            b3 = torch.randn((2,), generator=g).to(DEV)
+            got = fast_net.flow_out3x3(x, w3, b3)
+            assert got.is_contiguous() and torch.allclose(got, F.conv2d(x, w3, b3, padding=1), atol=5e-5)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old

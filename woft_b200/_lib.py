@@ -46,6 +46,8 @@ SIGNATURES = {
                                      c_int, c_void_p, c_void_p]),
     "woft_concat_nhwc": (c_int, [_FLOATP_ARRAY, POINTER(c_int), c_int, ctypes.c_longlong, c_void_p, c_int, c_int,
                                  c_void_p, c_int, c_int, c_void_p]),
+    "woft_flow_conv7x7_relu": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "woft_flow_out3x3": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_instance_norm_relu": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p]),
 }
 

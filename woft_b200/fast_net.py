@@ -83,6 +83,30 @@ def concat_nhwc(srcs, dst, dst_offset, dst2=None, dst2_offset=0):
     _lib.check(rc, "woft_concat_nhwc")
 
 
+def flow_conv7x7_relu(flow, weight, bias):
+    """(B,2,H,W) NCHW -> relu(conv7x7) as a channels-last (B,128,H,W) tensor; woft_flow_conv7x7_relu."""
+    flow = flow.contiguous()
+    B, _, H, W = flow.shape
+    out = _empty_cl(B, weight.shape[0], H, W, flow)
+    with torch.cuda.device(flow.device):
+        rc = _lib.load().woft_flow_conv7x7_relu(_lib.ptr(flow), _lib.ptr(weight), _lib.ptr(bias), B, H, W, _lib.ptr(out),
+                                                _lib.current_stream(flow.device))
+    _lib.check(rc, "woft_flow_conv7x7_relu")
+    return out
+
+
+def flow_out3x3(x_cl, weight, bias):
+    """channels-last (B,C,H,W) -> conv3x3 to 2 channels, NCHW (B,2,H,W); woft_flow_out3x3."""
+    x_cl = _cl(x_cl)
+    B, C, H, W = x_cl.shape
+    out = torch.empty((B, 2, H, W), device=x_cl.device, dtype=torch.float32)
+    with torch.cuda.device(x_cl.device):
+        rc = _lib.load().woft_flow_out3x3(_lib.ptr(x_cl), _lib.ptr(weight), _lib.ptr(bias), B, H, W, C, _lib.ptr(out),
+                                          _lib.current_stream(x_cl.device))
+    _lib.check(rc, "woft_flow_out3x3")
+    return out
+
+
 class FastWeightedRAFT:
     """Callable with the signature of WeightedRAFT.forward; built from a WeightedRAFT that already sits on the GPU."""
 
@@ -214,10 +238,11 @@ class FastWeightedRAFT:
 
     def _update_nhwc(self, st, corr, flow, need_mask):
         w = self.ubw
+        e = self.net.update_block.encoder
+        flo = flow_conv7x7_relu(flow, e.convf1.weight, e.convf1.bias)   # NCHW flow in, channels-last out
         flow = _cl(flow)
         cor = _conv_relu(corr, *w["convc1"])
         cor = _conv_relu(cor, *w["convc2"], padding=(1, 1))
-        flo = _conv_relu(flow, *w["convf1"], padding=(3, 3))
         flo = _conv_relu(flo, *w["convf2"], padding=(1, 1))
         B, _, H, W = cor.shape
         cf = _empty_cl(B, cor.shape[1] + flo.shape[1], H, W, cor)
@@ -228,7 +253,8 @@ class FastWeightedRAFT:
         self._gru_half_nhwc(st, "1")
         self._gru_half_nhwc(st, "2")
         h = st["h"]
-        dflow = F.conv2d(_conv_relu(h, *w["fh1"], padding=(1, 1)), *w["fh2"], padding=1)
+        fh = self.net.update_block.flow_head
+        dflow = flow_out3x3(_conv_relu(h, *w["fh1"], padding=(1, 1)), fh.conv2.weight, fh.conv2.bias)
         mask = None
         if need_mask:
             mask = 0.25 * F.conv2d(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"])

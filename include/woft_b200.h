@@ -188,6 +188,12 @@ int woft_instance_norm_relu(const float* x, int planes, int hw, float eps, int r
 int woft_warp_perspective_u8(const uint8_t* src, int height, int width, int channels, const double* inv_matrix_host,
                              uint8_t* dst, uint8_t* valid_mask, void* stream);
 
+/* The same instance norm (+ ReLU) on channels-last tensors x, y: (batch, HW, channels).  `scratch` holds the per-strip
+ * partial sums and the per-channel mean / rstd: woft_instance_norm_nhwc_scratch_bytes(batch, channels) bytes. */
+size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels);
+int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels, float eps, int relu, float* y,
+                                 void* scratch, size_t scratch_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -349,11 +349,14 @@ def test_fused_gru_and_instance_norm_kernels():
     bq = torch.randn((C,), generator=g).to(DEV)
     hn = fast_net.gru_update(q, bq, z, h)
     assert torch.allclose(hn, (1 - z) * h + z * torch.tanh(q + bq.view(1, -1, 1, 1)), atol=2e-6)
-    x = (torch.randn((3, 16, 45, 80), generator=g) * 3 + 7).to(DEV)
-    for relu in (True, False):
-        want = F.instance_norm(x, eps=1e-5)
-        want = F.relu(want) if relu else want
-        assert torch.allclose(fast_net.instance_norm_relu(x, relu=relu), want, atol=2e-5)
+    for C in (16, 96):
+        x = (torch.randn((3, C, 45, 80), generator=g) * 3 + 7).to(DEV)
+        for relu in (True, False):
+            want = F.instance_norm(x, eps=1e-5)
+            want = F.relu(want) if relu else want
+            assert torch.allclose(fast_net.instance_norm_relu(x, relu=relu), want, atol=2e-5)
+            got = fast_net.instance_norm_relu_nhwc(x.contiguous(memory_format=torch.channels_last), relu=relu)
+            assert got.is_contiguous(memory_format=torch.channels_last) and torch.allclose(got, want, atol=2e-5)
 
 
 def test_fused_schedule_matches_layer_by_layer(golden):

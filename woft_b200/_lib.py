@@ -48,6 +48,9 @@ SIGNATURES = {
                                  c_void_p, c_int, c_int, c_void_p]),
     "woft_flow_conv7x7_relu": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_flow_out3x3": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "woft_instance_norm_nhwc_scratch_bytes": (c_size_t, [c_int, c_int]),
+    "woft_instance_norm_relu_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_size_t,
+                                             c_void_p]),
     "woft_instance_norm_relu": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p]),
 }
 

@@ -198,6 +198,79 @@ __global__ void concat_nhwc_kernel(const ConcatParams p, long long pixels) {
   }
 }
 
+// ---- instance norm + ReLU on channels-last tensors (N, HW, C): per-strip partial sums, a tiny finalise, then apply
+constexpr int kInStrips = 64;
+
+__global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __restrict__ x, float* __restrict__ partial,
+                                                              int HW, int C) {
+  __shared__ float4 s_sum[256], s_sq[256];
+  const int n = blockIdx.y, strip = blockIdx.x;
+  const int c4n = C >> 2, ppb = 256 / c4n;
+  const int cq = threadIdx.x % c4n, pl = threadIdx.x / c4n;
+  const int len = (HW + kInStrips - 1) / kInStrips;
+  const int p0 = strip * len, p1 = min(p0 + len, HW);
+  const float4* base = reinterpret_cast<const float4*>(x + (size_t)n * HW * C);
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
+  if (pl < ppb) {
+    const float4 pv = __ldg(base + cq);  // pivot: the plane's first pixel, keeps the variance well conditioned
+    for (int p = p0 + pl; p < p1; p += ppb) {
+      const float4 v = __ldg(base + (size_t)p * c4n + cq);
+      const float a = v.x - pv.x, b = v.y - pv.y, c = v.z - pv.z, d = v.w - pv.w;
+      s.x += a; s.y += b; s.z += c; s.w += d;
+      q.x += a * a; q.y += b * b; q.z += c * c; q.w += d * d;
+    }
+  }
+  s_sum[threadIdx.x] = s;
+  s_sq[threadIdx.x] = q;
+  __syncthreads();
+  if (pl == 0) {
+    for (int k = 1; k < ppb; ++k) {
+      const float4 a = s_sum[k * c4n + cq], b = s_sq[k * c4n + cq];
+      s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
+      q.x += b.x; q.y += b.y; q.z += b.z; q.w += b.w;
+    }
+    float4* dst = reinterpret_cast<float4*>(partial + ((size_t)(n * kInStrips + strip) * 2) * C);
+    dst[cq] = s;
+    dst[c4n + cq] = q;
+  }
+}
+
+__global__ void in_finalize_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ partial,
+                                        float* __restrict__ stats, int HW, int C, float eps) {
+  const int n = blockIdx.x;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    double s = 0.0, q = 0.0;
+    for (int k = 0; k < kInStrips; ++k) {
+      const float* pp = partial + ((size_t)(n * kInStrips + k) * 2) * C;
+      s += pp[c];
+      q += pp[C + c];
+    }
+    const double m = s / HW, var = q / HW - m * m;
+    stats[(size_t)n * 2 * C + c] = float(m) + __ldg(x + (size_t)n * HW * C + c);
+    stats[(size_t)n * 2 * C + C + c] = rsqrtf(fmaxf(float(var), 0.f) + eps);
+  }
+}
+
+__global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ stats, float* __restrict__ y,
+                                     int HW, int C, int relu, long long total4) {
+  const int c4n = C >> 2;
+  const float floor_ = relu ? 0.f : -3.4e38f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int cq = int(i % c4n);
+    const int n = int(i / ((long long)HW * c4n));
+    const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    const float4 m = __ldg(reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C) + cq);
+    const float4 r = __ldg(reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C + C) + cq);
+    float4 o;
+    o.x = fmaxf((v.x - m.x) * r.x, floor_);
+    o.y = fmaxf((v.y - m.y) * r.y, floor_);
+    o.z = fmaxf((v.z - m.z) * r.z, floor_);
+    o.w = fmaxf((v.w - m.w) * r.w, floor_);
+    reinterpret_cast<float4*>(y)[i] = o;
+  }
+}
+
 static int ew_grid(long long total4) {
   const long long blocks = (total4 + 255) / 256;
   return int(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
@@ -304,4 +377,27 @@ extern "C" int woft_concat_nhwc(const float* const* srcs, const int* channels, i
   else
     concat_nhwc_kernel<1><<<grid, 256, 0, s>>>(p, pixels);
   return launch_status("concat_nhwc_kernel");
+}
+
+extern "C" size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels) {
+  if (batch <= 0 || channels <= 0) return 0;
+  return (size_t)batch * channels * 2 * (woft::kInStrips + 1) * sizeof(float);
+}
+
+extern "C" int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels, float eps, int relu,
+                                            float* y, void* scratch, size_t scratch_bytes, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(x && y && scratch, "woft_instance_norm_relu_nhwc: null pointer");
+  WOFT_REQUIRE(batch > 0 && hw > 0 && channels > 0 && channels % 4 == 0 && channels <= 1024 && batch < 65536,
+               "woft_instance_norm_relu_nhwc: channels must be a multiple of 4 (<= 1024)");
+  if (scratch_bytes < woft_instance_norm_nhwc_scratch_bytes(batch, channels))
+    return fail(WOFT_ERR_WORKSPACE, "woft_instance_norm_relu_nhwc: scratch too small");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  float* partial = static_cast<float*>(scratch);
+  float* stats = partial + (size_t)batch * kInStrips * 2 * channels;
+  in_partial_nhwc_kernel<<<dim3(kInStrips, batch), 256, 0, s>>>(x, partial, hw, channels);
+  in_finalize_nhwc_kernel<<<batch, 256, 0, s>>>(x, partial, stats, hw, channels, eps);
+  const long long total4 = (long long)batch * hw * (channels / 4);
+  in_apply_nhwc_kernel<<<ew_grid(total4), 256, 0, s>>>(x, stats, y, hw, channels, relu, total4);
+  return launch_status("instance norm (NHWC) kernels");
 }

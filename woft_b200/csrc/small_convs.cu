@@ -66,7 +66,10 @@ __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __r
   }
 }
 
-// in: (B,H,W,C) channels-last; weight (2,C,3,3); out (B,2,H,W).  One warp per pixel.
+// in: (B,H,W,C) channels-last; weight (2,C,3,3); out (B,2,H,W).  One warp per run of 4 pixels along x: lanes split the
+// input channels, every input pixel and every weight vector loaded once serves up to 3 of the 4 outputs.
+constexpr int kOutRun = 4;
+
 __global__ void __launch_bounds__(256) flow_out3x3_kernel(const float* __restrict__ in, const float* __restrict__ weight,
                                                           const float* __restrict__ bias, float* __restrict__ out,
                                                           int B, int H, int W, int C) {
@@ -77,30 +80,57 @@ __global__ void __launch_bounds__(256) flow_out3x3_kernel(const float* __restric
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const long long p = (long long)blockIdx.x * 8 + warp;
-  if (p >= (long long)B * H * W) return;
-  const int x = int(p % W), y = int((p / W) % H), b = int(p / ((long long)W * H));
-  float a0 = 0.f, a1 = 0.f;
-  for (int tap = 0; tap < 9; ++tap) {
-    const int yy = y + tap / 3 - 1, xx = x + tap % 3 - 1;
-    if (yy < 0 || yy >= H || xx < 0 || xx >= W) continue;  // warp-uniform
-    const float4* src = reinterpret_cast<const float4*>(in + (((size_t)b * H + yy) * W + xx) * C);
-    const float4* w0 = reinterpret_cast<const float4*>(sw + (tap * 2) * C);
-    const float4* w1 = reinterpret_cast<const float4*>(sw + (tap * 2 + 1) * C);
-    for (int c4 = lane; c4 < C / 4; c4 += 32) {
-      const float4 v = __ldg(src + c4), u0 = w0[c4], u1 = w1[c4];
-      a0 = fmaf(v.x, u0.x, fmaf(v.y, u0.y, fmaf(v.z, u0.z, fmaf(v.w, u0.w, a0))));
-      a1 = fmaf(v.x, u1.x, fmaf(v.y, u1.y, fmaf(v.z, u1.z, fmaf(v.w, u1.w, a1))));
+  const int runs_per_row = (W + kOutRun - 1) / kOutRun;
+  const long long run = (long long)blockIdx.x * 8 + warp;
+  if (run >= (long long)B * H * runs_per_row) return;
+  const int xr = int(run % runs_per_row) * kOutRun, y = int((run / runs_per_row) % H);
+  const int b = int(run / ((long long)runs_per_row * H));
+  float a0[kOutRun], a1[kOutRun];
+#pragma unroll
+  for (int j = 0; j < kOutRun; ++j) a0[j] = a1[j] = 0.f;
+  for (int c4 = lane; c4 < C / 4; c4 += 32) {
+    for (int ky = 0; ky < 3; ++ky) {
+      const int yy = y + ky - 1;
+      if (yy < 0 || yy >= H) continue;
+      float4 wa[3], wb[3];
+#pragma unroll
+      for (int kx = 0; kx < 3; ++kx) {
+        wa[kx] = reinterpret_cast<const float4*>(sw + ((ky * 3 + kx) * 2) * C)[c4];
+        wb[kx] = reinterpret_cast<const float4*>(sw + ((ky * 3 + kx) * 2 + 1) * C)[c4];
+      }
+#pragma unroll
+      for (int i = 0; i < kOutRun + 2; ++i) {   // input columns xr-1 .. xr+kOutRun
+        const int xx = xr + i - 1;
+        if (xx < 0 || xx >= W) continue;
+        const float4 v = __ldg(reinterpret_cast<const float4*>(in + (((size_t)b * H + yy) * W + xx) * C) + c4);
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          const int j = i - kx;                 // output pixel this (input column, tap) pair feeds
+          if (j < 0 || j >= kOutRun) continue;
+          a0[j] = fmaf(v.x, wa[kx].x, fmaf(v.y, wa[kx].y, fmaf(v.z, wa[kx].z, fmaf(v.w, wa[kx].w, a0[j]))));
+          a1[j] = fmaf(v.x, wb[kx].x, fmaf(v.y, wb[kx].y, fmaf(v.z, wb[kx].z, fmaf(v.w, wb[kx].w, a1[j]))));
+        }
+      }
     }
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
+  for (int j = 0; j < kOutRun; ++j) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      a0[j] += __shfl_xor_sync(0xffffffffu, a0[j], o);
+      a1[j] += __shfl_xor_sync(0xffffffffu, a1[j], o);
+    }
   }
-  if (lane == 0) {
-    out[((size_t)(b * 2) * H + y) * W + x] = a0 + __ldg(bias);
-    out[((size_t)(b * 2 + 1) * H + y) * W + x] = a1 + __ldg(bias + 1);
+  if (lane < kOutRun && xr + lane < W) {
+    float v0 = a0[0], v1 = a1[0];
+#pragma unroll
+    for (int j = 1; j < kOutRun; ++j)
+      if (lane == j) {
+        v0 = a0[j];
+        v1 = a1[j];
+      }
+    out[((size_t)(b * 2) * H + y) * W + xr + lane] = v0 + __ldg(bias);
+    out[((size_t)(b * 2 + 1) * H + y) * W + xr + lane] = v1 + __ldg(bias + 1);
   }
 }
 
@@ -125,7 +155,7 @@ extern "C" int woft_flow_out3x3(const float* in_nhwc, const float* weight, const
   WOFT_REQUIRE(in_nhwc && weight && bias && out_nchw, "woft_flow_out3x3: null pointer");
   WOFT_REQUIRE(batch > 0 && height > 0 && width > 0, "woft_flow_out3x3: bad extent");
   WOFT_REQUIRE(channels % 4 == 0 && channels <= 1024, "woft_flow_out3x3: channels must be a multiple of 4, <= 1024");
-  const long long pixels = (long long)batch * height * width;
+  const long long pixels = (long long)batch * height * ((width + kOutRun - 1) / kOutRun);  // warps = runs of 4 pixels
   const int smem = 18 * channels * sizeof(float);
   if (smem > 48 * 1024)
     WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_out3x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));

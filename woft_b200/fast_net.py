@@ -39,6 +39,21 @@ def instance_norm_relu(x, relu=True, eps=1e-5):
     return y
 
 
+def instance_norm_relu_nhwc(x, relu=True, eps=1e-5):
+    """channels-last (N, C, H, W) tensor -> same; woft_instance_norm_relu_nhwc."""
+    x = _cl(x)
+    N, C, H, W = x.shape
+    y = torch.empty_like(x)
+    lib = _lib.load()
+    nbytes = lib.woft_instance_norm_nhwc_scratch_bytes(N, C)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = lib.woft_instance_norm_relu_nhwc(_lib.ptr(x), N, H * W, C, eps, int(relu), _lib.ptr(y), _lib.ptr(scratch),
+                                              nbytes, _lib.current_stream(x.device))
+    _lib.check(rc, "woft_instance_norm_relu_nhwc")
+    return y
+
+
 def gru_gates(zr, bias_zr, h):
     B, C2, H, W = zr.shape
     C = C2 // 2
@@ -132,6 +147,21 @@ class FastWeightedRAFT:
             # without the NCHW<->NHWC conversion kernels that otherwise wrap every convolution
             self.nhwc = nhwc_update
             if nhwc_update:
+                fn = net.fnet
+                self.fw = {"stem": _cl(fn.conv1.weight), "out": (_cl(fn.conv2.weight), fn.conv2.bias), "blocks": []}
+                for layer in (fn.layer1, fn.layer2, fn.layer3):
+                    for blk in layer:
+                        self.fw["blocks"].append({"c1": _cl(blk.conv1.weight), "c2": _cl(blk.conv2.weight),
+                                                  "stride": blk.conv1.stride,
+                                                  "down": _cl(blk.downsample[0].weight) if blk.downsample is not None else None})
+                c = self.cnet  # folded context-encoder weights, channels-last as well
+                c["stem"] = (_cl(c["stem"][0]), c["stem"][1])
+                c["out"] = (_cl(c["out"][0]), c["out"][1])
+                for d in c["blocks"]:
+                    d["c1"] = (_cl(d["c1"][0]), d["c1"][1])
+                    d["c2"] = (_cl(d["c2"][0]), d["c2"][1])
+                    if d["down"] is not None:
+                        d["down"] = (_cl(d["down"][0]), d["down"][1])
                 ub, e = net.update_block, net.update_block.encoder
                 self.ubw = {name: (_cl(m.weight), m.bias) for name, m in (
                     ("convc1", e.convc1), ("convc2", e.convc2), ("convf1", e.convf1), ("convf2", e.convf2),
@@ -162,6 +192,8 @@ class FastWeightedRAFT:
 
     def _context(self, x):
         c = self.cnet
+        if self.nhwc:
+            x = _cl(x)
         x = _conv_relu(x, *c["stem"], stride=(2, 2), padding=(3, 3))
         for d in c["blocks"]:
             y = _conv_relu(x, *d["c1"], stride=d["stride"], padding=(1, 1))
@@ -173,6 +205,8 @@ class FastWeightedRAFT:
 
     # ---- feature encoder: bias-free conv + fused instance norm / ReLU --------------------------------------
     def _features(self, x):
+        if self.nhwc:
+            return self._features_nhwc(x)
         enc = self.net.fnet
         x = instance_norm_relu(F.conv2d(x, enc.conv1.weight, None, stride=2, padding=3))
         for layer in (enc.layer1, enc.layer2, enc.layer3):
@@ -184,6 +218,18 @@ class FastWeightedRAFT:
                                            relu=False)
                 x = F.relu(x + y)
         return F.conv2d(x, enc.conv2.weight, enc.conv2.bias)
+
+    def _features_nhwc(self, x):
+        """Same encoder with channels-last activations and weights (no cuDNN layout conversions)."""
+        w = self.fw
+        x = instance_norm_relu_nhwc(F.conv2d(_cl(x), w["stem"], None, stride=2, padding=3))
+        for d in w["blocks"]:
+            y = instance_norm_relu_nhwc(F.conv2d(x, d["c1"], None, stride=d["stride"], padding=1))
+            y = instance_norm_relu_nhwc(F.conv2d(y, d["c2"], None, padding=1))
+            if d["down"] is not None:
+                x = instance_norm_relu_nhwc(F.conv2d(x, d["down"], None, stride=d["stride"]), relu=False)
+            x = F.relu(x + y)
+        return F.conv2d(x, w["out"][0], w["out"][1])
 
     # ---- update block ---------------------------------------------------------------------------------------
     def _gru_half(self, h, x, tag):

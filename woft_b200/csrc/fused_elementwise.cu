@@ -199,7 +199,7 @@ __global__ void concat_nhwc_kernel(const ConcatParams p, long long pixels) {
 }
 
 // ---- instance norm + ReLU on channels-last tensors (N, HW, C): per-strip partial sums, a tiny finalise, then apply
-constexpr int kInStrips = 64;
+constexpr int kInStrips = 256;  // (strips x batch) CTAs in the partial-sum pass: enough to fill 148 SMs at batch 1-2
 
 __global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __restrict__ x, float* __restrict__ partial,
                                                               int HW, int C) {
@@ -235,16 +235,25 @@ __global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __res
   }
 }
 
-__global__ void in_finalize_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ partial,
-                                        float* __restrict__ stats, int HW, int C, float eps) {
-  const int n = blockIdx.x;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    double s = 0.0, q = 0.0;
-    for (int k = 0; k < kInStrips; ++k) {
-      const float* pp = partial + ((size_t)(n * kInStrips + k) * 2) * C;
-      s += pp[c];
-      q += pp[C + c];
-    }
+// one warp per channel: lanes add up the strips, 8 channels per CTA
+__global__ void __launch_bounds__(256) in_finalize_nhwc_kernel(const float* __restrict__ x,
+                                                               const float* __restrict__ partial,
+                                                               float* __restrict__ stats, int HW, int C, float eps) {
+  const int n = blockIdx.y;
+  const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int k = lane; k < kInStrips; k += 32) {
+    const float* pp = partial + ((size_t)(n * kInStrips + k) * 2) * C;
+    s += pp[c];
+    q += pp[C + c];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
     const double m = s / HW, var = q / HW - m * m;
     stats[(size_t)n * 2 * C + c] = float(m) + __ldg(x + (size_t)n * HW * C + c);
     stats[(size_t)n * 2 * C + C + c] = rsqrtf(fmaxf(float(var), 0.f) + eps);
@@ -396,7 +405,7 @@ extern "C" int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, i
   float* partial = static_cast<float*>(scratch);
   float* stats = partial + (size_t)batch * kInStrips * 2 * channels;
   in_partial_nhwc_kernel<<<dim3(kInStrips, batch), 256, 0, s>>>(x, partial, hw, channels);
-  in_finalize_nhwc_kernel<<<batch, 256, 0, s>>>(x, partial, stats, hw, channels, eps);
+  in_finalize_nhwc_kernel<<<dim3(ceil_div(channels, 8), batch), 256, 0, s>>>(x, partial, stats, hw, channels, eps);
   const long long total4 = (long long)batch * hw * (channels / 4);
   in_apply_nhwc_kernel<<<ew_grid(total4), 256, 0, s>>>(x, stats, y, hw, channels, relu, total4);
   return launch_status("instance norm (NHWC) kernels");

@@ -167,6 +167,14 @@ class FastWeightedRAFT:
                     ("convc1", e.convc1), ("convc2", e.convc2), ("convf1", e.convf1), ("convf2", e.convf2),
                     ("conv", e.conv), ("fh1", ub.flow_head.conv1), ("fh2", ub.flow_head.conv2), ("m0", ub.mask[0]),
                     ("m2", ub.mask[2]))}
+                # BasicMotionEncoder.conv has 126 output channels (update.py:87), which cuDNN's sm_100 kernels do not
+                # take; two all-zero filters make it 128, and the flow that the reference concatenates behind the 126
+                # channels (update.py:97) is written over those two
+                wc, bc = e.conv.weight, e.conv.bias
+                pad = (-wc.shape[0]) % 8
+                self.conv_pad = pad
+                self.ubw["conv"] = (_cl(torch.cat([wc, wc.new_zeros((pad,) + tuple(wc.shape[1:]))], 0)),
+                                    torch.cat([bc, bc.new_zeros(pad)], 0).contiguous())
                 for tag in ("1", "2"):
                     self.gru[tag]["w_zr"] = _cl(self.gru[tag]["w_zr"])
                     self.gru[tag]["w_q"] = _cl(self.gru[tag]["w_q"])
@@ -293,9 +301,14 @@ class FastWeightedRAFT:
         B, _, H, W = cor.shape
         cf = _empty_cl(B, cor.shape[1] + flo.shape[1], H, W, cor)
         concat_nhwc([_cl(cor), _cl(flo)], cf, 0)
-        out = _conv_relu(cf, *w["conv"], padding=(1, 1))
+        out = _conv_relu(cf, *w["conv"], padding=(1, 1))      # 126 motion channels + `conv_pad` zero channels
         C = st["C"]
-        concat_nhwc([st["inp"], _cl(out), flow], st["buf1"], C, st["buf2"], C)  # x = [inp | motion | flow]
+        if self.conv_pad == flow.shape[1]:
+            concat_nhwc([st["inp"], _cl(out)], st["buf1"], C, st["buf2"], C)           # x = [inp | motion | 0 0]
+            off = C + st["inp"].shape[1] + out.shape[1] - self.conv_pad
+            concat_nhwc([flow], st["buf1"], off, st["buf2"], off)                       # ... flow over the zeros
+        else:
+            concat_nhwc([st["inp"], _cl(out[:, :out.shape[1] - self.conv_pad]), flow], st["buf1"], C, st["buf2"], C)
         self._gru_half_nhwc(st, "1")
         self._gru_half_nhwc(st, "2")
         h = st["h"]

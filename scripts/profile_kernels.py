@@ -45,6 +45,7 @@ for mode in ("tf32", "tf32x3", "bf16", "fp16"):
 blk = blocks["tf32"]
 timed("corr_lookup flags=0 (float4 rows)", lambda: blk(coords, flags=0), 5)
 timed("corr_lookup flags=1 (scalar rows)", lambda: blk(coords, flags=1), 5)
+timed("corr_lookup flags=8 (NHWC output)", lambda: blk(coords, flags=8), 5)
 # 13 lookups back to back as in one flow pass (L2 warm after the first): amortises the ~5 us event/launch overhead
 cs = [coords + 0.3 * i for i in range(13)]
 timed("13 x corr_lookup (one flow pass)", lambda: [blk(c) for c in cs], 5)

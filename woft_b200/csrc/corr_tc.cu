@@ -79,8 +79,9 @@ struct CorrTcParams {
   unsigned long long* trace;  // debug (WOFT_CORR_TRACE): [cta < 4][tile < 64][6] globaltimer stamps, else null
 };
 
+template <bool TRACE>
 __device__ __forceinline__ void trace_stamp(const CorrTcParams& p, int it, int slot) {
-  if (p.trace && blockIdx.x < 4 && it < 64) p.trace[(blockIdx.x * 64 + it) * 6 + slot] = ptx::globaltimer_ns();
+  if (TRACE && p.trace && blockIdx.x < 4 && it < 64) p.trace[(blockIdx.x * 64 + it) * 6 + slot] = ptx::globaltimer_ns();
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -212,12 +213,18 @@ __device__ __forceinline__ void direct_row(float* level, int lh, int lw, int HW,
     if (w0 + j < lw) dst[w0 + j] = v[j];
 }
 
+// DEBUG = false is the production instantiation: streamed A tile, 3 operand stages, 3 ring slots, no tracing, all of
+// them compile-time so the role loops stay tight.  DEBUG = true takes stages / slots / the resident-A schedule /
+// the trace buffer from the parameters (experiments described in DESIGN.md 4).
+template <bool DEBUG>
 __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_constant__ CorrTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int STAGES = p.stages, NSLOT = p.nslot;
+  const int STAGES = DEBUG ? p.stages : 3, NSLOT = DEBUG ? p.nslot : 3;
+  const bool a_resident = DEBUG && p.a_resident;
+  const int unit = DEBUG ? p.unit : 1;
   uint8_t* sA = smem;  // streamed: STAGES x 16 KB; resident: k_blocks x 16 KB
-  uint8_t* sB = sA + (p.a_resident ? p.k_blocks : STAGES) * A_STAGE;
+  uint8_t* sB = sA + (a_resident ? p.k_blocks : STAGES) * A_STAGE;
   uint8_t* ring = sB + STAGES * B_STAGE;
   uint64_t* bars = reinterpret_cast<uint64_t*>(ring + NSLOT * SLOT);
   uint64_t* full = bars;                     // [MAX_STAGES] TMA -> MMA
@@ -266,13 +273,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
       int cur_a = -1;          // (b, M tile) whose A tile is resident
       uint32_t a_loads = 0;
       int pit = 0;
-      for (int chunk = blockIdx.x; chunk * p.unit < p.total_tiles && alive; chunk += gridDim.x) {
-        const int t_end = min((chunk + 1) * p.unit, p.total_tiles);
-        for (int t = chunk * p.unit; t < t_end && alive; ++t, ++pit) {
+      for (int chunk = blockIdx.x; chunk * unit < p.total_tiles && alive; chunk += gridDim.x) {
+        const int t_end = min((chunk + 1) * unit, p.total_tiles);
+        for (int t = chunk * unit; t < t_end && alive; ++t, ++pit) {
           const TileCoord tc = decode_tile(p, t);
-          trace_stamp(p, pit, 0);
+          trace_stamp<DEBUG>(p, pit, 0);
           const int a_id = tc.b * p.m_tiles + tc.m0 / BM;
-          const bool reload = p.a_resident && a_id != cur_a;
+          const bool reload = a_resident && a_id != cur_a;
           cur_a = a_id;
           // with a resident A tile, first queue as many B stages of this tile as the ring takes, then swap A in
           const int pre = reload ? min(STAGES, k_steps) : 0;
@@ -293,7 +300,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
               alive = false;
               break;
             }
-            if (p.a_resident) {
+            if (a_resident) {
               ptx::mbar_arrive_expect_tx(full + stage, B_STAGE);
             } else {
               ptx::mbar_arrive_expect_tx(full + stage, A_STAGE + B_STAGE);
@@ -306,7 +313,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
               phase ^= 1u;
             }
           }
-          trace_stamp(p, pit, 1);
+          trace_stamp<DEBUG>(p, pit, 1);
           if (reload && alive && pre == k_steps) {  // k_steps <= STAGES: the A swap comes after all B loads
             if (!wait_or_abort(a_empty, (a_loads & 1u) ^ 1u, p.abort_flag)) {
               alive = false;
@@ -331,10 +338,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
       int it = 0;
       int cur_a = -1;
       uint32_t a_loads = 0;
-      for (int chunk = blockIdx.x; chunk * p.unit < p.total_tiles && alive; chunk += gridDim.x) {
-        const int t_end = min((chunk + 1) * p.unit, p.total_tiles);
-        for (int t = chunk * p.unit; t < t_end && alive; ++t, ++it) {
-          if (p.a_resident) {
+      for (int chunk = blockIdx.x; chunk * unit < p.total_tiles && alive; chunk += gridDim.x) {
+        const int t_end = min((chunk + 1) * unit, p.total_tiles);
+        for (int t = chunk * unit; t < t_end && alive; ++t, ++it) {
+          if (a_resident) {
             const TileCoord tc = decode_tile(p, t);
             const int a_id = tc.b * p.m_tiles + tc.m0 / BM;
             if (a_id != cur_a) {
@@ -352,7 +359,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
             break;
           }
           ptx::tc_fence_after_sync();
-          trace_stamp(p, it, 2);
+          trace_stamp<DEBUG>(p, it, 2);
           const uint32_t d_tmem = tmem_base + uint32_t(buf * BN);
           for (int ks = 0; ks < k_steps; ++ks) {
             if (!wait_or_abort(full + stage, phase, p.abort_flag)) {
@@ -360,7 +367,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
               break;
             }
             ptx::tc_fence_after_sync();
-            const int a_slot = p.a_resident ? ks : stage;  // resident: k block ks of the A tile (n_pairs == 1)
+            const int a_slot = a_resident ? ks : stage;  // resident: k block ks of the A tile (n_pairs == 1)
             const uint64_t da = make_kmajor_sw128_desc(ptx::smem_u32(sA + a_slot * A_STAGE));
             const uint64_t db = make_kmajor_sw128_desc(ptx::smem_u32(sB + stage * B_STAGE));
 #pragma unroll
@@ -378,7 +385,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
             }
           }
           if (alive) ptx::mma_commit(tfull + buf);
-          trace_stamp(p, it, 3);
+          trace_stamp<DEBUG>(p, it, 3);
         }
       }
     }
@@ -392,9 +399,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
     uint32_t ev = 0;  // ring event counter (identical in all epilogue threads)
     int it = 0;
     bool go = true;
-    for (int chunk = blockIdx.x; chunk * p.unit < p.total_tiles && go; chunk += gridDim.x) {
-    const int t_end = min((chunk + 1) * p.unit, p.total_tiles);
-    for (int t = chunk * p.unit; t < t_end; ++t, ++it) {
+    for (int chunk = blockIdx.x; chunk * unit < p.total_tiles && go; chunk += gridDim.x) {
+    const int t_end = min((chunk + 1) * unit, p.total_tiles);
+    for (int t = chunk * unit; t < t_end; ++t, ++it) {
       const TileCoord tc = decode_tile(p, t);
       const int buf = it & 1;
       const uint32_t use = uint32_t(it >> 1);
@@ -404,7 +411,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
         go = false;
         break;
       }
-      if (issuer) trace_stamp(p, it, 4);
+      if (issuer) trace_stamp<DEBUG>(p, it, 4);
       ptx::tc_fence_after_sync();
       const int mq = tc.m0 + m;
 
@@ -514,7 +521,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
           ++ev;
         }
       }
-      if (issuer) trace_stamp(p, it, 5);
+      if (issuer) trace_stamp<DEBUG>(p, it, 5);
     }
     }
     if (issuer) ptx::tma_store_wait_all();
@@ -704,7 +711,7 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
 
   int sms = 0;
   WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   const int chunks = ceil_div(p.total_tiles, p.unit);
   const int grid = chunks < sms ? chunks : sms;
   const char* trace_path = getenv("WOFT_CORR_TRACE");  // debug aid: per-role timestamps of the first 4 CTAs
@@ -714,7 +721,13 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
     WOFT_CUDA_CHECK(cudaMalloc(&p.trace, trace_bytes));
     WOFT_CUDA_CHECK(cudaMemsetAsync(p.trace, 0, trace_bytes, stream));
   }
-  corr_tc_kernel<<<grid, TC_THREADS, smem_bytes, stream>>>(p);
+  const bool debug = p.a_resident || p.trace != nullptr || p.stages != 3 || p.nslot != 3 || p.unit != 1;
+  if (debug) {
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    corr_tc_kernel<true><<<grid, TC_THREADS, smem_bytes, stream>>>(p);
+  } else {
+    corr_tc_kernel<false><<<grid, TC_THREADS, smem_bytes, stream>>>(p);
+  }
   int rc = launch_status("corr_tc_kernel");
   if (trace_path && rc == WOFT_OK) {
     static unsigned long long host_trace[4 * 64 * 6];

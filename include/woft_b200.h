@@ -188,6 +188,15 @@ int woft_instance_norm_relu(const float* x, int planes, int hw, float eps, int r
 int woft_warp_perspective_u8(const uint8_t* src, int height, int width, int channels, const double* inv_matrix_host,
                              uint8_t* dst, uint8_t* valid_mask, void* stream);
 
+/* Replaces WeightedRAFT.upsample_flow for the flow and for the weight logits in one pass
+ * (raft_core/weighted_raft.py:92-103, 249-255, 285-288) and, optionally, the sigmoid of
+ * pytracking/optical_flow/raft.py:158-159: convex combination of the 3x3 coarse neighbourhood of 8*field with softmax
+ * weights from `mask`, pixel-shuffled to full resolution; the weights are divided by 8 again.
+ *   flow_low (B,2,H,W), weights_low (B,1,H,W) or NULL, mask (B,576,H,W) NCHW or channels-last (mask_nhwc != 0)
+ *   -> flow_up (B,2,8H,8W), weights_up (B,1,8H,8W) or NULL */
+int woft_convex_upsample(const float* flow_low, const float* weights_low, const float* mask, int mask_nhwc, int batch,
+                         int height, int width, int apply_sigmoid, float* flow_up, float* weights_up, void* stream);
+
 /* The same instance norm (+ ReLU) on channels-last tensors x, y: (batch, HW, channels).  `scratch` holds the per-strip
  * partial sums and the per-channel mean / rstd: woft_instance_norm_nhwc_scratch_bytes(batch, channels) bytes. */
 size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels);

@@ -457,3 +457,21 @@ def test_thin_convolution_kernels():
             assert got.is_contiguous() and torch.allclose(got, F.conv2d(x, w3, b3, padding=1), atol=5e-5)
     finally:
         torch.backends.cudnn.allow_tf32 = old
+
+
+def test_convex_upsample_kernel():
+    from woft_b200.fast_net import convex_upsample_both
+    from woft_b200.raft_net import convex_upsample
+    g = torch.Generator().manual_seed(4)
+    B, H, W = 2, 12, 20
+    flow = (torch.randn((B, 2, H, W), generator=g) * 4).to(DEV)
+    wl = torch.randn((B, 1, H, W), generator=g).to(DEV)
+    mask = torch.randn((B, 576, H, W), generator=g).to(DEV)
+    want_f, want_w = convex_upsample(flow, mask), convex_upsample(wl, mask) / 8
+    for m in (mask, mask.contiguous(memory_format=torch.channels_last)):
+        got_f, got_w = convex_upsample_both(flow, wl, m)
+        assert torch.allclose(got_f, want_f, atol=2e-5) and torch.allclose(got_w, want_w, atol=2e-6)
+        got_f, got_w = convex_upsample_both(flow, wl, m, sigmoid=True)
+        assert torch.allclose(got_w, torch.sigmoid(want_w), atol=2e-6)
+    only_f, none_w = convex_upsample_both(flow, None, mask)
+    assert none_w is None and torch.allclose(only_f, want_f, atol=2e-5)

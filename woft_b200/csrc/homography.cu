@@ -245,15 +245,29 @@ __global__ void __launch_bounds__(kHThreads, 2) homography_fit_kernel(const HPar
       }
       const double pp[6] = {x1 * x1, x1 * y1, x1, y1 * y1, y1, 1.0};
       const double c0 = wy, c1 = wx, c2 = wy * x2, c3 = wx * y2, c4 = wx * y2 * y2 + wy * x2 * x2;
+      if (it == 0) {  // first solve: both rows carry the same weight, so S(wx) == S(wy) and is filled in afterwards
 #pragma unroll
-      for (int k = 0; k < 6; ++k) {
-        S[k] += c0 * pp[k];
-        S[6 + k] += c1 * pp[k];
-        S[12 + k] += c2 * pp[k];
-        S[18 + k] += c3 * pp[k];
-        S[24 + k] += c4 * pp[k];
+        for (int k = 0; k < 6; ++k) {
+          S[k] += c0 * pp[k];
+          S[12 + k] += c2 * pp[k];
+          S[18 + k] += c3 * pp[k];
+          S[24 + k] += c4 * pp[k];
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+          S[k] += c0 * pp[k];
+          S[6 + k] += c1 * pp[k];
+          S[12 + k] += c2 * pp[k];
+          S[18 + k] += c3 * pp[k];
+          S[24 + k] += c4 * pp[k];
+        }
       }
       }
+    }
+    if (it == 0) {
+#pragma unroll
+      for (int k = 0; k < 6; ++k) S[6 + k] = S[k];
     }
     block_sum<30>(S, scratch);
 

@@ -146,6 +146,14 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
       // channels-last output (B, H1, W1, L*P*P): a warp takes one (level, query) footprint at a time and its lanes
       // take consecutive taps, so every store instruction writes 128 contiguous bytes of that query's channel row
       const int warp = tid >> 5, lane = tid & 31;
+      constexpr int ROUNDS = (P * P + 31) / 32;
+      int tap_off[ROUNDS];  // footprint offset of the tap this lane forms in each round (fixed for the whole kernel)
+#pragma unroll
+      for (int k = 0; k < ROUNDS; ++k) {
+        const int t = lane + 32 * k;
+        const int xo = t / P, yo = t - xo * P;  // channel = (xoff+r)*P + (yoff+r)
+        tap_off[k] = t < P * P ? yo * WIN + xo : -1;
+      }
       for (int pair = warp; pair < kLevelsPerPass * kQueriesPerCta; pair += kLookupThreads / 32) {
         const int slot = pair >> 4, ql = pair & 15;
         const int lvl = lv0 + slot, q = q0 + ql;
@@ -153,11 +161,13 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
         const float* my = win + pair * STRIDE;
         const float ax = s_ax[pair], ay = s_ay[pair];
         const float w00 = (1.f - ax) * (1.f - ay), w01 = ax * (1.f - ay), w10 = (1.f - ax) * ay, w11 = ax * ay;
-        float* o = p.out + (size_t)q * channels + (size_t)lvl * P * P;
-        for (int t = lane; t < P * P; t += 32) {
-          const int xo = t / P, yo = t - xo * P;  // channel = (xoff+r)*P + (yoff+r)
-          const float* c = my + yo * WIN + xo;
-          o[t] = c[0] * w00 + c[1] * w01 + c[WIN] * w10 + c[WIN + 1] * w11;
+        float* o = p.out + (size_t)q * channels + (size_t)lvl * P * P + lane;
+#pragma unroll
+        for (int k = 0; k < ROUNDS; ++k) {
+          if (tap_off[k] >= 0) {
+            const float* c = my + tap_off[k];
+            o[32 * k] = c[0] * w00 + c[1] * w01 + c[WIN] * w10 + c[WIN + 1] * w11;
+          }
         }
       }
     } else {

@@ -20,7 +20,7 @@ import torch.nn.functional as F
 
 from . import _lib
 from .corr import CorrBlock as _CorrBlock
-from .raft_net import convex_upsample, pixel_grid
+from .raft_net import pixel_grid
 
 
 def _conv_relu(x, w, b, stride=(1, 1), padding=(0, 0)):
@@ -120,6 +120,27 @@ def flow_out3x3(x_cl, weight, bias):
                                           _lib.current_stream(x_cl.device))
     _lib.check(rc, "woft_flow_out3x3")
     return out
+
+
+def convex_upsample_both(flow_low, weights_low, mask, sigmoid=False):
+    """Flow (B,2,H,W) and weight logits (B,1,H,W) or None -> (flow_up, weights_up) at 8x; woft_convex_upsample.
+    `mask` (B,576,H,W) may be NCHW or channels-last."""
+    flow_low = flow_low.contiguous()
+    B, _, H, W = flow_low.shape
+    nhwc = mask.is_contiguous(memory_format=torch.channels_last) and not mask.is_contiguous()
+    if not nhwc:
+        mask = mask.contiguous()
+    flow_up = torch.empty((B, 2, 8 * H, 8 * W), device=flow_low.device, dtype=torch.float32)
+    w_up = None
+    if weights_low is not None:
+        weights_low = weights_low.contiguous()
+        w_up = torch.empty((B, 1, 8 * H, 8 * W), device=flow_low.device, dtype=torch.float32)
+    with torch.cuda.device(flow_low.device):
+        rc = _lib.load().woft_convex_upsample(_lib.ptr(flow_low), _lib.ptr(weights_low), _lib.ptr(mask), int(nhwc), B, H, W,
+                                              int(sigmoid), _lib.ptr(flow_up), _lib.ptr(w_up),
+                                              _lib.current_stream(flow_low.device))
+    _lib.check(rc, "woft_convex_upsample")
+    return flow_up, w_up
 
 
 class FastWeightedRAFT:
@@ -374,10 +395,9 @@ class FastWeightedRAFT:
                 net, up_mask, dflow = self._update(net, inp, corr, coords1 - coords0, need_mask=last)
                 coords1 = coords1 + dflow
         flow_low = coords1 - coords0
-        flow_up = convex_upsample(flow_low, up_mask.contiguous())
         if not self.with_weights:
-            return flow_low, flow_up
+            return flow_low, convex_upsample_both(flow_low, None, up_mask)[0]
         window = corr_fn(coords1, flags=lookup_flags) if nhwc else corr_fn(coords1)
         weights = self._weights(window, corr_fn.mean_response())
-        weights_up = convex_upsample(weights, up_mask.contiguous()) / 8
+        flow_up, weights_up = convex_upsample_both(flow_low, weights, up_mask)  # one kernel, softmax computed once
         return flow_low, flow_up, corr_fn.corr_pyramid[0], weights, weights_up

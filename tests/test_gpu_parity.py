@@ -475,3 +475,65 @@ def test_convex_upsample_kernel():
         assert torch.allclose(got_w, torch.sigmoid(want_w), atol=2e-6)
     only_f, none_w = convex_upsample_both(flow, None, mask)
     assert none_w is None and torch.allclose(only_f, want_f, atol=2e-5)
+
+
+def test_full_size_properties_1080p():
+    """BASELINE config 5 size (1920x1080 -> 135x240 feature maps): 4.2 GB volume, odd level sizes (135 -> 67 -> 33 -> 16,
+    240 -> 120 -> 60 -> 30: level 3 rows are not 16-byte multiples, so that level takes the direct-store path)."""
+    from woft_b200.corr import CorrBlock
+    torch.manual_seed(1)
+    B, C, H, W = 1, 256, 135, 240
+    f1 = torch.randn(B, C, H, W, device=DEV)
+    f2 = torch.randn(B, C, H, W, device=DEV)
+    blk = CorrBlock(f1, f2, mode="fp16")
+    blk.check()
+    lv = blk.corr_pyramid
+    assert [tuple(l.shape[2:]) for l in lv] == [(135, 240), (67, 120), (33, 60), (16, 30)]
+    idx = torch.randint(0, H * W, (2, 20000), device=DEV)
+    want = (f1.view(C, H * W)[:, idx[0]].double() * f2.view(C, H * W)[:, idx[1]].double()).sum(0) / 16.0
+    got = lv[0].view(H * W, H * W)[idx[0], idx[1]].double()
+    assert (got - want).abs().max().item() < CORR_ATOL["fp16"]
+    for l in range(3):
+        sel = slice(0, 4000)  # a slab of queries is enough; pooling is per query
+        assert torch.allclose(lv[l + 1][sel], F.avg_pool2d(lv[l][sel], 2, stride=2), atol=2e-6)
+        sel = slice(H * W - 3000, H * W)
+        assert torch.allclose(lv[l + 1][sel], F.avg_pool2d(lv[l][sel], 2, stride=2), atol=2e-6)
+    ys, xs = torch.meshgrid(torch.arange(H, device=DEV), torch.arange(W, device=DEV), indexing="ij")
+    coords = torch.stack([xs, ys]).float()[None] + (torch.rand((1, 2, H, W), device=DEV) * 2 - 1) * 8
+    out = blk(coords)
+    out_cl = blk(coords, flags=8)
+    assert torch.allclose(out, out_cl.contiguous(), atol=2e-5)  # separable lerp vs 4-tap weights: same values to rounding
+    sel = torch.arange(20000, 20400, device=DEV)
+    ref = wo.corr_lookup([l[sel].cpu() for l in lv], coords.view(2, -1)[:, sel].cpu().view(1, 2, 1, -1))
+    got = out.view(324, -1)[:, sel].cpu().view(1, 324, 1, -1)
+    assert (got - ref).abs().max().item() < 2e-5 * max(1.0, ref.abs().max().item())
+    del blk, lv, out, out_cl
+    torch.cuda.empty_cache()
+
+
+def test_tracked_frame_matches_cpu_pipeline():
+    """The whole tracked-frame path (flow wrapper -> mask -> Sobol pick -> weighted fit -> inlier test) on the GPU against
+    the oracle's CPU pipeline on the same frames and weights: homography corner error and the success flag."""
+    from types import SimpleNamespace
+    from oracle import cpu_pipeline
+    from oracle.gen_golden import make_frames
+    from woft_b200 import tracker
+    from woft_b200.corr import CorrBlock
+    from woft_b200.optical_flow import RAFTWrapper
+    H, W = 256, 320
+    img0, img1 = make_frames(H, W, 21)
+    mask = np.zeros((H, W), np.uint8)
+    mask[48:208, 64:256] = 255
+    net = cpu_pipeline.make_net(0)
+    torch.set_num_threads(8)
+    H_cpu, ok_cpu, n_cpu = cpu_pipeline.track_frame(net, img0, img1, mask, np.eye(3), 12)
+    flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False), model=None,
+                                seeded_weights=0, iters=12, padding_mode="nopad")
+    for device_prewarp in (False, True):
+        flower = RAFTWrapper(flow_conf, device=DEV, corr_block=functools.partial(CorrBlock, mode="tf32x3"))
+        trk = tracker.PlanarTracker(tracker.default_config(flow_conf, device_prewarp=device_prewarp), flower=flower)
+        trk.init(img0, mask)
+        H_gpu, meta = trk.track(img1)
+        assert meta.global_H_success == ok_cpu
+        err = wo.corner_error(torch.from_numpy(H_gpu), torch.from_numpy(H_cpu), W, H)
+        assert err <= 0.05, f"tracked-frame homography differs from the CPU pipeline by {err} px at the corners"

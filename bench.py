@@ -360,7 +360,7 @@ def run_woft(args, rank, world, local):
         "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(1e3 * results["device"]["seconds"] / args.steps, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": {"tf32": "tf32", "tf32x3": "f32 (3xTF32)", "bf16": "bf16", "fp16": "f16", "fp32": "f32"}[args.corr_mode],
+        "dtype": {"tf32": "tf32", "tf32x3": "f32 (3xTF32)", "bf16": "bf16", "fp16": "f16", "fp16x3": "f32 (3xFP16)", "fp32": "f32"}[args.corr_mode],
         "data": "synthetic",
         "config": {"workload": "configs[1]: single RAFT flow+uncertainty pass on a synthetic 1280x720 frame pair "
                                "(160x90x256 feature maps, 12 GRU iters, 13 lookups) + correspondence mask + 500-point "
@@ -397,7 +397,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["woft", "reference"], default="woft")
     ap.add_argument("--corr-mode", default=os.environ.get("WOFT_CORR_MODE", "fp16"),
-                    choices=["tf32", "tf32x3", "bf16", "fp16", "fp32"])
+                    choices=["tf32", "tf32x3", "bf16", "fp16", "fp16x3", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "woft" else args.warmup

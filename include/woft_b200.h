@@ -41,8 +41,10 @@ enum woft_corr_mode {
   WOFT_CORR_TF32 = 1,      /* tcgen05 kind::tf32, operands rounded to tf32 once, fp32 accumulate in TMEM */
   WOFT_CORR_TF32X3 = 2,    /* tcgen05, error-compensated 3xTF32 split (hi*hi + hi*lo + lo*hi): fp32-class result */
   WOFT_CORR_BF16 = 3,      /* tcgen05 kind::f16 with bf16 operands, fp32 accumulate */
-  WOFT_CORR_FP16 = 4       /* tcgen05 kind::f16 with fp16 operands (tf32's 10-bit mantissa at half the bytes; inputs
+  WOFT_CORR_FP16 = 4,      /* tcgen05 kind::f16 with fp16 operands (tf32's 10-bit mantissa at half the bytes; inputs
                               are saturated to +-65504), fp32 accumulate */
+  WOFT_CORR_FP16X3 = 5     /* tcgen05 kind::f16, error-compensated split into fp16 hi + lo (hi*hi + hi*lo + lo*hi): the
+                              fp32-class result of WOFT_CORR_TF32X3 at half its operand traffic */
 };
 
 /* Estimators of pytracking/utils/least_squares_H.py served by woft_homography_fit (K4). */

@@ -37,7 +37,7 @@ def timed(name, fn, n=5):
 
 
 blocks = {}
-for mode in ("tf32", "tf32x3", "bf16", "fp16"):
+for mode in ("tf32", "tf32x3", "bf16", "fp16", "fp16x3"):
     def build(mode=mode):
         blocks[mode] = CorrBlock(f1, f2, mode=mode)
     timed(f"corr_pyramid[{mode}]", build, 3)
@@ -57,7 +57,7 @@ if "--l2gran" in sys.argv:
         timed(f"corr_lookup, L2 fetch granularity {gran} (rc {rc})", lambda: blk(coords), 5)
         timed(f"corr_pyramid[tf32], granularity {gran}", lambda: CorrBlock(f1, f2, mode="tf32"), 2)
 f1b = torch.randn((4, C, H, W), generator=g, device=dev)
-del blocks["tf32x3"], blocks["bf16"], blocks["fp16"]
+del blocks["tf32x3"], blocks["bf16"], blocks["fp16"], blocks["fp16x3"]
 Bh, Nh = 1024, 14400
 p1 = torch.rand((Bh, Nh, 2), generator=g, device=dev) * torch.tensor([1280.0, 720.0], device=dev)
 p2 = p1 + torch.randn((Bh, Nh, 2), generator=g, device=dev)

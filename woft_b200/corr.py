@@ -20,7 +20,8 @@ from . import _lib
 #: arithmetic of the all-pairs GEMM, all with fp32 accumulation:
 #:   "fp16"   tensor cores, operands rounded to fp16 (10-bit mantissa like tf32, half the operand bytes) -- default
 #:   "tf32"   tensor cores, operands rounded to tf32        "bf16"  tensor cores, 7-bit mantissa
-#:   "tf32x3" tensor cores, error-compensated split, fp32-class result
+#:   "fp16x3" tensor cores, error-compensated fp16 hi/lo split (3 MMAs), fp32-class result
+#:   "tf32x3" tensor cores, the same with tf32 hi/lo planes (twice the operand bytes)
 #:   "fp32"   CUDA cores, the reference's own precision class
 DEFAULT_MODE = os.environ.get("WOFT_CORR_MODE", "fp16")
 

@@ -45,7 +45,7 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
   WOFT_REQUIRE(batch > 0 && channels > 0 && height > 0 && width > 0, "woft_corr_pyramid: non-positive extent");
   WOFT_REQUIRE(num_levels >= 1 && num_levels <= kMaxLevels, "woft_corr_pyramid: num_levels %d not in [1,%d]",
                num_levels, kMaxLevels);
-  WOFT_REQUIRE(mode >= WOFT_CORR_FP32_SIMT && mode <= WOFT_CORR_FP16, "woft_corr_pyramid: unknown mode %d", mode);
+  WOFT_REQUIRE(mode >= WOFT_CORR_FP32_SIMT && mode <= WOFT_CORR_FP16X3, "woft_corr_pyramid: unknown mode %d", mode);
   WOFT_REQUIRE((long long)batch * height * width < (1ll << 31), "woft_corr_pyramid: too many query pixels");
   for (int l = 0, h = height, w = width; l < num_levels; ++l, h /= 2, w /= 2) {
     WOFT_REQUIRE(h >= 1 && w >= 1, "woft_corr_pyramid: level %d is empty", l);

@@ -93,7 +93,7 @@ __device__ __forceinline__ float round_tf32(float x) {
   return __uint_as_float(r);
 }
 
-template <int MODE>  // 1 tf32, 2 tf32 hi/lo, 3 bf16, 4 fp16
+template <int MODE>  // 1 tf32, 2 tf32 hi/lo, 3 bf16, 4 fp16, 5 fp16 hi/lo
 __global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src1, const float* __restrict__ src2,
                                                    void* __restrict__ dst1, void* __restrict__ dst2, int B, int C,
                                                    int HW, int Kp, size_t plane_elems, int* flag) {
@@ -120,8 +120,10 @@ __global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src
     const size_t o = ((size_t)b * HW + hw) * Kp + c;
     if (MODE == 3) {
       reinterpret_cast<__nv_bfloat16*>(dst)[o] = __float2bfloat16_rn(v);
-    } else if (MODE == 4) {
-      reinterpret_cast<__half*>(dst)[o] = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));  // saturate, no inf
+    } else if (MODE == 4 || MODE == 5) {
+      const __half hi = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));  // saturate, no inf
+      reinterpret_cast<__half*>(dst)[o] = hi;
+      if (MODE == 5) reinterpret_cast<__half*>(dst)[plane_elems + o] = __float2half_rn(v - __half2float(hi));
     } else {
       const float hi = round_tf32(v);
       reinterpret_cast<float*>(dst)[o] = hi;
@@ -574,10 +576,10 @@ struct TcLayout {
 
 TcLayout tc_layout(int B, int C, int HW, int mode) {
   TcLayout L{};
-  L.elem_bytes = (mode == WOFT_CORR_BF16 || mode == WOFT_CORR_FP16) ? 2 : 4;
+  L.elem_bytes = (mode == WOFT_CORR_BF16 || mode == WOFT_CORR_FP16 || mode == WOFT_CORR_FP16X3) ? 2 : 4;
   L.k_elems = 128 / L.elem_bytes;
   L.Kp = (C + L.k_elems - 1) / L.k_elems * L.k_elems;
-  L.planes = (mode == WOFT_CORR_TF32X3) ? 2 : 1;
+  L.planes = (mode == WOFT_CORR_TF32X3 || mode == WOFT_CORR_FP16X3) ? 2 : 1;
   L.plane_bytes = (size_t)B * HW * L.Kp * L.elem_bytes;  // Kp*elem_bytes is a multiple of 128
   L.off_mean = 256;
   L.off_a = align_up(L.off_mean + (size_t)B * C * 4, 1024);
@@ -613,6 +615,8 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
       pack_kernel<3><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
     else if (mode == WOFT_CORR_FP16)
       pack_kernel<4><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
+    else if (mode == WOFT_CORR_FP16X3)
+      pack_kernel<5><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
     else if (mode == WOFT_CORR_TF32X3)
       pack_kernel<2><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, B, C, HW, L.Kp, plane_elems, flag);
     else
@@ -623,7 +627,7 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
 
   CorrTcParams p{};
   const CUtensorMapDataType dt = (mode == WOFT_CORR_BF16)   ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16
-                                 : (mode == WOFT_CORR_FP16) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
+                                 : (mode == WOFT_CORR_FP16 || mode == WOFT_CORR_FP16X3) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
                                                             : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   // the hi and lo planes lie back to back, so they fold into the batch dimension of the operand maps
   {
@@ -669,8 +673,8 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   p.total_tiles = B * p.m_tiles * p.h_tiles * p.w_tiles;
   p.k_blocks = L.Kp / L.k_elems;
   p.k_elems = L.k_elems;
-  p.n_pairs = (mode == WOFT_CORR_TF32X3) ? 3 : 1;
-  p.bf16 = (mode == WOFT_CORR_BF16) ? 1 : (mode == WOFT_CORR_FP16) ? 2 : 0;
+  p.n_pairs = (mode == WOFT_CORR_TF32X3 || mode == WOFT_CORR_FP16X3) ? 3 : 1;
+  p.bf16 = (mode == WOFT_CORR_BF16) ? 1 : (mode == WOFT_CORR_FP16 || mode == WOFT_CORR_FP16X3) ? 2 : 0;
   p.scale = 1.0f / sqrtf(float(C));
   p.abort_flag = flag;
 

@@ -42,8 +42,8 @@ def test_version_and_sizes_without_gpu(lib):
     x3 = lib.woft_corr_workspace_bytes(1, 256, 90, 160, 2)
     bf16 = lib.woft_corr_workspace_bytes(1, 256, 90, 160, 3)
     assert lib.woft_corr_workspace_bytes(1, 256, 90, 160, 4) == bf16
-    assert packed * 2 <= lib.woft_corr_workspace_bytes(1, 256, 90, 160, 5) < packed * 2 + 8192
     packed = 14400 * 256 * 4
+    assert packed * 2 <= lib.woft_corr_workspace_bytes(1, 256, 90, 160, 5) < packed * 2 + 8192
     assert 0 < simt < 8192
     assert 2 * packed <= tf32 < 2 * packed + 8192
     assert 4 * packed <= x3 < 4 * packed + 8192

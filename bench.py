@@ -8,8 +8,8 @@ A step is one tracked frame of BASELINE.json configs[1]: one WeightedRAFT flow +
 mask, the 500-point Sobol pick, the weighted homography fit and the inlier test.
   value      frames/s over all ranks with the frames already resident in HBM (uint8), nothing copied to the host
   e2e        frames/s through the public API (PlanarTracker.track on a host uint8 frame): pinned H2D upload of the
-             frame (the template was uploaded once by init), device pre-warp, the device path, D2H of the 3x3
-             homography and of the success flag
+             frame (the template was uploaded once by init), device pre-warp, the device path, one 48-byte D2H of the
+             3x3 homography and the inlier fraction
   roofline   the correlation lookup (K3), the kernel BASELINE.json's metric names, timed alone with CUDA events on
              its launch stream with L2 flushed between launches; `kernels` adds K1+K2 and K4 the same way
   cpu_baseline / --impl reference: the oracle port of the reference's CPU path on this box's host cores
@@ -319,7 +319,7 @@ def run_woft(args, rank, world, local):
     pw_all = torch.ones((HEIGHT, WIDTH), dtype=torch.bool, device=dev)
 
     def device_step(i):
-        return trk.estimate_global(base_dev, frames_dev[i % n_seq_frames], pw_all)
+        return trk.estimate_global_fused(base_dev, frames_dev[i % n_seq_frames], pw_all)
 
     def e2e_step(i):
         return trk.track(frames[i % n_seq_frames])
@@ -371,13 +371,14 @@ def run_woft(args, rank, world, local):
                          "steps; per-kernel roofline launches are preceded by a 256 MiB L2 flush",
                    "flow_passes_per_frame": results["device"]["flow_passes"] / args.steps},
         "e2e": {"value": round(world * args.steps / results["e2e"]["seconds"], 3), "unit": "frames/s",
-                "h2d_bytes_per_step": HEIGHT * WIDTH * 3, "d2h_bytes_per_step": 36 + 1,
+                "h2d_bytes_per_step": HEIGHT * WIDTH * 3, "d2h_bytes_per_step": 48,
                 "flow_passes_per_frame": results["e2e"]["flow_passes"] / args.steps,
                 "api": "woft_b200.tracker.PlanarTracker.track(host uint8 frame) -> 3x3 homography on the host"},
         # hand-written kernels per tracked frame (profiles/r1_bench_launches_summary.md counts the same 173):
         # pack + GEMM + 2 row-mean, 13 lookups, 15 instance norms x 3, per iteration 1 + 3 + 2 + 2 + 1 (7x7 flow conv,
-        # concats, GRU gates, GRU updates, flow head output) + the initial concat, homography fit + reprojection errors
-        "gpu_launches": int(args.steps * (4 + (ITERS + 1) + 45 + ITERS * 9 + 1 + 2)),
+        # concats, GRU gates, GRU updates, flow head output) + the initial concat, convex upsampling, 3 selection kernels,
+        # homography fit, inlier fraction
+        "gpu_launches": int(args.steps * (4 + (ITERS + 1) + 45 + ITERS * 9 + 1 + 1 + 3 + 2)),
         "clocks": clocks,
         "roofline": k3,
         "kernels": kernels,

@@ -190,6 +190,32 @@ int woft_instance_norm_relu(const float* x, int planes, int hw, float eps, int r
 int woft_warp_perspective_u8(const uint8_t* src, int height, int width, int channels, const double* inv_matrix_host,
                              uint8_t* dst, uint8_t* valid_mask, void* stream);
 
+/* Correspondence selection of the tracker's global branch without a host round trip.  Replaces the 'TC' assembly of
+ * RAFTWrapper.compute_flow (pytracking/optical_flow/raft.py:185-218), YAOFTrackerSingleControl._mask_coords
+ * (pytracking/tracker/YAOF_tracker_single_control.py:287-312) and the Sobol subsampler of the default config
+ * (pytracking/configs/YAOFT_single_control_repRAFT_sub500_noreliableinl_wLSq.py:31-53):
+ *   keep pixel i  iff  template_mask[i] and cur = pixel + flow is not < 0 and round(cur) is inside the frame and
+ *                      pw_mask[round(cur)] (pw_mask may be NULL);
+ *   of the N kept pixels, in raster order, those of rank rint(float(N) * u_k) for the first `to_draw` points u_k of
+ *   the unscrambled 1-D Sobol sequence (duplicates once; all of them when N <= to_draw).
+ *   flow_up (2,H,W); weights_up (H*W) logits or probabilities, or NULL (weights 1); masks (H,W) uint8;
+ *   sobol_sorted: DEVICE array of the `to_draw` (<= 1024) Sobol points sorted ascending;
+ *   outputs pts_template / pts_cur (to_draw, 2) as (x, y), weights_out (to_draw), n_selected (1 int), all DEVICE.
+ * scratch: woft_select_scratch_bytes(H, W) bytes.  woft_homography_fit_n is woft_homography_fit for one problem
+ * whose point count is read from device memory (fewer than 4 points give a NaN matrix instead of the reference's
+ * AssertionError); woft_inlier_fraction is the default config's redet_success_fn (:14-21): the fraction of points
+ * with |H a - b| <= threshold (fraction_out[0]; fraction_out[1] receives the point count) and whether it exceeds
+ * min_fraction (ok_out). */
+size_t woft_select_scratch_bytes(int height, int width);
+int woft_select_correspondences(const float* flow_up, const float* weights_up, const uint8_t* template_mask,
+                                const uint8_t* pw_mask, int height, int width, const float* sobol_sorted, int to_draw,
+                                int apply_sigmoid, float* pts_template, float* pts_cur, float* weights_out,
+                                int* n_selected, void* scratch, size_t scratch_bytes, void* stream);
+int woft_homography_fit_n(const float* points1, const float* points2, const float* weights, const int* n_points_dev,
+                          int max_points, int method, int n_iter, float huber_k, float* H_out, void* stream);
+int woft_inlier_fraction(const float* H, const float* pts_a, const float* pts_b, const int* n_points_dev, float threshold,
+                         float min_fraction, float* fraction_out, uint8_t* ok_out, void* stream);
+
 /* Replaces WeightedRAFT.upsample_flow for the flow and for the weight logits in one pass
  * (raft_core/weighted_raft.py:92-103, 249-255, 285-288) and, optionally, the sigmoid of
  * pytracking/optical_flow/raft.py:158-159: convex combination of the 3x3 coarse neighbourhood of 8*field with softmax

@@ -537,3 +537,38 @@ def test_tracked_frame_matches_cpu_pipeline():
         assert meta.global_H_success == ok_cpu
         err = wo.corner_error(torch.from_numpy(H_gpu), torch.from_numpy(H_cpu), W, H)
         assert err <= 0.05, f"tracked-frame homography differs from the CPU pipeline by {err} px at the corners"
+
+
+def test_fused_select_fit_check_matches_reference_pieces():
+    """woft_select_correspondences + woft_homography_fit_n + woft_inlier_fraction against the oracle's restatement of
+    _mask_coords, the Sobol subsampler, find_homography_nonhomogeneous_QR and redet_success_fn."""
+    import cv2
+    from woft_b200 import tracker
+    from woft_b200.misc import torch_get_featuremap_coords
+    g = torch.Generator().manual_seed(12)
+    for (H, W, box) in ((256, 320, (48, 208, 64, 256)), (64, 96, (20, 38, 30, 52))):  # the second keeps < 500 points
+        flow = torch.randn((2, H, W), generator=g) * 6
+        flow[:, : H // 3] += 40  # push a band out of the frame
+        logits = torch.randn((1, H, W), generator=g)
+        tmask = torch.zeros((H, W), dtype=torch.bool)
+        tmask[box[0]:box[1], box[2]:box[3]] = True
+        pw = torch.from_numpy(cv2.warpPerspective(np.ones((H, W)), np.array([[1, 0.03, 9], [0.01, 1, -6], [0, 0, 1.0]]),
+                                                  (W, H)) > 0)
+        src = torch_get_featuremap_coords((H, W), device="cpu")
+        dst = src + flow.reshape(2, -1)
+        wts = torch.sigmoid(logits).reshape(1, -1)
+        t_c, c_c, w_c, _ = wo.mask_coords(tmask, src, dst, wts, pw)
+        keep = wo.sobol_subsample_mask(t_c.shape[1])
+        if keep is not None:
+            t_c, c_c, w_c = t_c[:, keep], c_c[:, keep], w_c[:, keep]
+        res, (pts_t, pts_c, w, n) = tracker.select_fit_check(flow.to(DEV), logits.to(DEV), tmask.to(DEV), pw.to(DEV))
+        m = int(n.item())
+        assert m == t_c.shape[1]
+        assert torch.equal(pts_t[:m].cpu(), t_c.float().T) and torch.equal(pts_c[:m].cpu(), c_c.T)
+        assert torch.allclose(w[:m].cpu(), w_c[0], atol=1e-6)
+        res = res.cpu()
+        assert int(res[10].item()) == m
+        Href = wo.find_homography_nonhomogeneous_QR(c_c.T[None].double(), t_c.T[None].double(), w_c.double())
+        assert wo.corner_error(res[:9].view(1, 3, 3), Href, W, H) <= 0.05
+        errs = wo.torch_proj_errors(res[:9].view(1, 3, 3), c_c[None], t_c.float()[None])
+        assert res[9].item() == pytest.approx((errs <= 5).float().mean().item(), abs=1e-6)

@@ -52,6 +52,13 @@ SIGNATURES = {
     "woft_instance_norm_nhwc_scratch_bytes": (c_size_t, [c_int, c_int]),
     "woft_instance_norm_relu_nhwc": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_size_t,
                                              c_void_p]),
+    "woft_select_scratch_bytes": (c_size_t, [c_int, c_int]),
+    "woft_select_correspondences": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
+                                            c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "woft_homography_fit_n": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p,
+                                      c_void_p]),
+    "woft_inlier_fraction": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p,
+                                     c_void_p]),
     "woft_convex_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                      c_void_p]),
     "woft_instance_norm_relu": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p]),

@@ -136,6 +136,7 @@ struct HParams {
   const float* w;   // (B, N) or null
   float* H;         // (B, 3, 3)
   int n;
+  const int* n_dev;  // when not null, the number of correspondences is read here (batch 1; arrays hold `n` slots)
   int method;
   int n_iter;
   float huber_k;
@@ -146,7 +147,11 @@ __global__ void __launch_bounds__(kHThreads, 2) homography_fit_kernel(const HPar
   __shared__ double h9[9];  // current solution in normalised coordinates (h9[8] = 1 for the 8-parameter system)
 
   const int b = blockIdx.x;
-  const int N = prm.n;
+  const int N = prm.n_dev ? min(*prm.n_dev, prm.n) : prm.n;
+  if (N < 4) {  // only reachable with a device-side count: the host entry point rejects n < 4 (least_squares_H.py:162)
+    if (threadIdx.x < 9) prm.H[(size_t)b * 9 + threadIdx.x] = __int_as_float(0x7fc00000);
+    return;
+  }
   const float2* __restrict__ P1 = reinterpret_cast<const float2*>(prm.p1) + (size_t)b * N;
   const float2* __restrict__ P2 = reinterpret_cast<const float2*>(prm.p2) + (size_t)b * N;
   const float* __restrict__ Wt = prm.w ? prm.w + (size_t)b * N : nullptr;
@@ -347,7 +352,7 @@ extern "C" int woft_homography_fit(const float* points1, const float* points2, c
   WOFT_REQUIRE(n_iter >= 0 && n_iter <= 1000, "woft_homography_fit: n_iter %d", n_iter);
   WOFT_REQUIRE((reinterpret_cast<uintptr_t>(points1) & 7) == 0 && (reinterpret_cast<uintptr_t>(points2) & 7) == 0,
                "woft_homography_fit: point arrays must be 8-byte aligned");
-  HParams p{points1, points2, weights, H_out, n_points, method, n_iter, huber_k};
+  HParams p{points1, points2, weights, H_out, n_points, nullptr, method, n_iter, huber_k};
   homography_fit_kernel<<<batch, kHThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
   return launch_status("homography_fit_kernel");
 }
@@ -360,4 +365,17 @@ extern "C" int woft_proj_errors(const float* H, const float* pts_a, const float*
   dim3 grid(ceil_div(n_points, 256), batch);
   proj_errors_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(H, pts_a, pts_b, n_points, err);
   return launch_status("proj_errors_kernel");
+}
+
+extern "C" int woft_homography_fit_n(const float* points1, const float* points2, const float* weights,
+                                     const int* n_points_dev, int max_points, int method, int n_iter, float huber_k,
+                                     float* H_out, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(points1 && points2 && H_out && n_points_dev, "woft_homography_fit_n: null pointer");
+  WOFT_REQUIRE(max_points >= 4, "woft_homography_fit_n: max_points %d", max_points);
+  WOFT_REQUIRE(method >= WOFT_H_NONHOMOGENEOUS && method <= WOFT_H_IRLS_HUBER, "woft_homography_fit_n: method %d", method);
+  WOFT_REQUIRE(n_iter >= 0 && n_iter <= 1000, "woft_homography_fit_n: n_iter %d", n_iter);
+  HParams p{points1, points2, weights, H_out, max_points, n_points_dev, method, n_iter, huber_k};
+  homography_fit_kernel<<<1, kHThreads, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  return launch_status("homography_fit_kernel");
 }

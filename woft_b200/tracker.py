@@ -76,12 +76,59 @@ def find_homography(pts_A, pts_B, weights=None):
     return lsq.find_homography_nonhomogeneous_QR(pts_A, pts_B, weights=weights)
 
 
+_SOBOL_DEV = {}
+
+
+def select_fit_check(flow_up, weight_logits, template_mask, pw_mask, to_draw=500, thr=5.0, min_frac=0.2):
+    """The default config's post-flow stage as five launches and no host round trip: correspondence mask + Sobol pick
+    (woft_select_correspondences), weighted fit (woft_homography_fit_n), inlier test (woft_inlier_fraction).
+    flow_up (2,H,W), weight_logits (1,H,W) before the sigmoid, masks (H,W) bool/uint8 -- all on the device.
+    Returns a device tensor of 12 floats: H row-major in [0:9], inlier fraction in [9], number of points in [10]."""
+    from . import _lib
+    lib = _lib.load()
+    dev = flow_up.device
+    _, H, W = flow_up.shape
+    key = (dev, to_draw)
+    if key not in _SOBOL_DEV:
+        _SOBOL_DEV[key] = torch.from_numpy(np.sort(sobol_positions(to_draw)).astype(np.float32)).to(dev)
+    flow_up = flow_up.contiguous()
+    weight_logits = weight_logits.contiguous()
+    pts_t = torch.empty((to_draw, 2), device=dev, dtype=torch.float32)
+    pts_c = torch.empty((to_draw, 2), device=dev, dtype=torch.float32)
+    w = torch.empty((to_draw,), device=dev, dtype=torch.float32)
+    n = torch.empty((1,), device=dev, dtype=torch.int32)
+    res = torch.zeros((12,), device=dev, dtype=torch.float32)
+    ok = torch.empty((1,), device=dev, dtype=torch.uint8)
+    nbytes = lib.woft_select_scratch_bytes(H, W)
+    scratch = torch.empty((nbytes,), device=dev, dtype=torch.uint8)
+    with torch.cuda.device(dev):
+        st = _lib.current_stream(dev)
+        rc = lib.woft_select_correspondences(_lib.ptr(flow_up), _lib.ptr(weight_logits), _lib.ptr(template_mask),
+                                             _lib.ptr(pw_mask), H, W, _lib.ptr(_SOBOL_DEV[key]), to_draw, 1, _lib.ptr(pts_t),
+                                             _lib.ptr(pts_c), _lib.ptr(w), _lib.ptr(n), _lib.ptr(scratch), nbytes, st)
+        _lib.check(rc, "woft_select_correspondences")
+        # H maps the current (pre-warped) points onto the template points (tracker :152-155)
+        rc = lib.woft_homography_fit_n(_lib.ptr(pts_c), _lib.ptr(pts_t), _lib.ptr(w), _lib.ptr(n), to_draw,
+                                       _lib.H_NONHOMOGENEOUS, 0, 1.0, _lib.ptr(res), st)
+        _lib.check(rc, "woft_homography_fit_n")
+        rc = lib.woft_inlier_fraction(_lib.ptr(res), _lib.ptr(pts_c), _lib.ptr(pts_t), _lib.ptr(n), thr, min_frac,
+                                      ctypes_offset(res, 9), _lib.ptr(ok), st)
+        _lib.check(rc, "woft_inlier_fraction")
+    return res, (pts_t, pts_c, w, n)
+
+
+def ctypes_offset(t, index):
+    import ctypes
+    return ctypes.c_void_p(t.data_ptr() + index * t.element_size())
+
+
 def default_config(flow_config, device_prewarp=True):
     """get_config() of the default tracker config (:56-71).  `device_prewarp` (not a reference key) moves the
     cv2.warpPerspective pre-warp and its validity mask onto the GPU (woft_warp_perspective_u8)."""
     return SimpleNamespace(flow_config=flow_config, H_estimator=find_homography, redet_success_fn=redet_success_fn,
                            pw_mask=True, no_prewarp_after_N=10, subsampler_fn=subsampler, no_local_H=False,
-                           do_not_mask_TCs_by_prewarped=False, device_prewarp=device_prewarp)
+                           do_not_mask_TCs_by_prewarped=False, device_prewarp=device_prewarp,
+                           fused_select=device_prewarp)
 
 
 def prewarp_on_device(frame_u8, H, want_mask=True):
@@ -144,8 +191,14 @@ class PlanarTracker:
             pw_mask = torch.from_numpy(pw_mask > 0).to(self.device, non_blocking=True)
             template = self.template_img
 
-        H_pw2init, ok, t_coords, c_coords, weights = self.estimate_global(template, prewarped, pw_mask)
-        H_np = H_pw2init.detach().cpu().numpy()[0].astype(np.float64)   # D2H of the 3x3 (reference :156)
+        if _cfg(self.C, "fused_select", False) and on_device:
+            # mask + Sobol pick + fit + inlier test stay on the device; ONE 48-byte copy brings H and the flag back
+            res = self.estimate_global_fused(template, prewarped, pw_mask).cpu().numpy()
+            H_np = res[:9].reshape(3, 3).astype(np.float64)
+            ok = bool(res[9] > 0.2)
+        else:
+            H_pw2init, ok, t_coords, c_coords, weights = self.estimate_global(template, prewarped, pw_mask)
+            H_np = H_pw2init.detach().cpu().numpy()[0].astype(np.float64)   # D2H of the 3x3 (reference :156)
         H_global = compose_H(prewarp_H, H_np)
         meta.H_global_cur2init = H_global.copy()
 
@@ -185,6 +238,14 @@ class PlanarTracker:
             self.last_good_H2init = H_cur2init.copy()
         meta.lost, meta.N_lost, meta.global_H_success = self.lost, self.N_lost, bool(ok)
         return H_cur2init, meta
+
+    def estimate_global_fused(self, template_img, prewarped_img, pw_mask):
+        """estimate_global for the default config's plug-ins, without boolean indexing or host round trips."""
+        flow, w_logits = self.flower.compute_flow(template_img, prewarped_img, mode="flow", do_sigmoid=False)
+        self.flow_passes += 1
+        mask = pw_mask if not _cfg(self.C, "do_not_mask_TCs_by_prewarped", False) else None
+        res, _ = select_fit_check(flow, w_logits, self.template_mask, mask)
+        return res
 
     def estimate_global(self, template_img, prewarped_img, pw_mask):
         """The device part of one tracked frame (:101-163): template -> pre-warped flow + weights, correspondence

@@ -142,9 +142,30 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
     __syncthreads();
 
     // ---- compute phase
-    if (NHWC) {
-      // channels-last output (B, H1, W1, L*P*P): a warp takes one (level, query) footprint at a time and its lanes
-      // take consecutive taps, so every store instruction writes 128 contiguous bytes of that query's channel row
+    if (NHWC && P % 3 == 0) {
+      // channels-last output (B, H1, W1, L*P*P), P divisible by 3 (r = 4, r = 1): a warp takes one (level, query)
+      // footprint at a time; lane t < P*P/3 forms the three consecutive channels (xo, y3..y3+2) from a 4 x 2 patch of
+      // the footprint (8 loads, separable lerp), so a warp writes one contiguous run of P*P floats per footprint
+      const int warp = tid >> 5, lane = tid & 31;
+      constexpr int GROUPS = P * P / 3;
+      const int xo = lane / (P / 3), y3 = (lane - xo * (P / 3)) * 3;
+      const bool active = lane < GROUPS;
+      for (int pair = warp; pair < kLevelsPerPass * kQueriesPerCta; pair += kLookupThreads / 32) {
+        const int slot = pair >> 4, ql = pair & 15;
+        const int lvl = lv0 + slot, q = q0 + ql;
+        if (lvl >= p.num_levels || q >= p.nq || !active) continue;
+        const float* c = win + pair * STRIDE + y3 * WIN + xo;
+        const float ax = s_ax[pair], ay = s_ay[pair];
+        const float bx = 1.f - ax, by = 1.f - ay;
+        float h[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) h[r] = fmaf(ax, c[r * WIN + 1], bx * c[r * WIN]);
+        float* o = p.out + (size_t)q * channels + (size_t)lvl * P * P + xo * P + y3;
+#pragma unroll
+        for (int j = 0; j < 3; ++j) o[j] = fmaf(ay, h[j + 1], by * h[j]);
+      }
+    } else if (NHWC) {
+      // channels-last output, any radius: lanes take consecutive taps, 4-tap bilinear weights
       const int warp = tid >> 5, lane = tid & 31;
       constexpr int ROUNDS = (P * P + 31) / 32;
       int tap_off[ROUNDS];  // footprint offset of the tap this lane forms in each round (fixed for the whole kernel)

@@ -153,11 +153,17 @@ int woft_gru_update(const float* q, const float* bias_q, const float* z, const f
  * pixel contiguous; `*_stride` is the distance in floats between consecutive pixels, so an operand can be a channel
  * slice of a wider buffer -- the GRU keeps [h | x] and [r*h | x] in two persistent buffers and never concatenates.
  *   woft_gru_gates_nhwc : zr (pixels, 2C) dense; h, rh strided; z (pixels, C) dense
+ *   woft_gru_gates_nhwc_split: the same with the z and r pre-activations in two (pixels, C) operands of stride
+ *                         pre_stride and their biases apart -- for a schedule that runs convz and convr as two
+ *                         convolutions (cuDNN has no sm_100 kernel for the stacked 1x5 384->256 shape)
  *   woft_gru_update_nhwc: h_out may alias h; h_dense (pixels, C) is an optional second, dense copy of the result
  *   woft_concat_nhwc    : up to 4 dense sources (HOST arrays of pointers / channel counts) written side by side at
  *                         channel offset dst_offset of dst (and of dst2 when not NULL) */
 int woft_gru_gates_nhwc(const float* zr, const float* bias_zr, const float* h, int h_stride, long long pixels,
                         int channels, float* z, float* rh, int rh_stride, void* stream);
+int woft_gru_gates_nhwc_split(const float* z_pre, const float* r_pre, int pre_stride, const float* bias_z,
+                              const float* bias_r, const float* h, int h_stride, long long pixels, int channels,
+                              float* z, float* rh, int rh_stride, void* stream);
 int woft_gru_update_nhwc(const float* q, const float* bias_q, const float* z, const float* h, int h_stride,
                          long long pixels, int channels, float* h_out, int h_out_stride, float* h_dense, void* stream);
 int woft_concat_nhwc(const float* const* srcs, const int* channels, int n_src, long long pixels, float* dst,

@@ -43,6 +43,8 @@ SIGNATURES = {
     "woft_gru_update": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_gru_gates_nhwc": (c_int, [c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_int, c_void_p, c_void_p,
                                     c_int, c_void_p]),
+    "woft_gru_gates_nhwc_split": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int,
+                                          ctypes.c_longlong, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "woft_gru_update_nhwc": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, ctypes.c_longlong, c_int, c_void_p,
                                      c_int, c_void_p, c_void_p]),
     "woft_concat_nhwc": (c_int, [_FLOATP_ARRAY, POINTER(c_int), c_int, ctypes.c_longlong, c_void_p, c_int, c_int,

@@ -117,18 +117,19 @@ __global__ void __launch_bounds__(512) instance_norm_relu_kernel(const float* __
 // ---- channels-last (NHWC) variants: a pixel's channels are contiguous; operands may be channel slices of wider
 // buffers (pixel stride > channel count), which is how the GRU avoids torch.cat: [h | x] and [r*h | x] live in two
 // persistent (pixels, C + Cx) buffers whose x part is written once per iteration.
-__global__ void gru_gates_nhwc_kernel(const float* __restrict__ zr, const float* __restrict__ bias,
+__global__ void gru_gates_nhwc_kernel(const float* __restrict__ z_pre, const float* __restrict__ r_pre, int pre_stride,
+                                      const float* __restrict__ bias_z, const float* __restrict__ bias_r,
                                       const float* __restrict__ h, int h_stride, float* __restrict__ z,
                                       float* __restrict__ rh, int rh_stride, int C4, long long total4) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
        i += (long long)gridDim.x * blockDim.x) {
     const long long pix = i / C4;
     const int c4 = int(i - pix * C4);
-    const float4 zp = __ldg(reinterpret_cast<const float4*>(zr + pix * (8 * C4)) + c4);
-    const float4 rp = __ldg(reinterpret_cast<const float4*>(zr + pix * (8 * C4) + 4 * C4) + c4);
+    const float4 zp = __ldg(reinterpret_cast<const float4*>(z_pre + pix * pre_stride) + c4);
+    const float4 rp = __ldg(reinterpret_cast<const float4*>(r_pre + pix * pre_stride) + c4);
     const float4 hv = __ldg(reinterpret_cast<const float4*>(h + pix * h_stride) + c4);
-    const float4 bz = __ldg(reinterpret_cast<const float4*>(bias) + c4);
-    const float4 br = __ldg(reinterpret_cast<const float4*>(bias + 4 * C4) + c4);
+    const float4 bz = __ldg(reinterpret_cast<const float4*>(bias_z) + c4);
+    const float4 br = __ldg(reinterpret_cast<const float4*>(bias_r) + c4);
     float4 zo, ro;
     zo.x = sigmoidf_(zp.x + bz.x); zo.y = sigmoidf_(zp.y + bz.y); zo.z = sigmoidf_(zp.z + bz.z); zo.w = sigmoidf_(zp.w + bz.w);
     ro.x = sigmoidf_(rp.x + br.x) * hv.x; ro.y = sigmoidf_(rp.y + br.y) * hv.y;
@@ -327,8 +328,22 @@ extern "C" int woft_gru_gates_nhwc(const float* zr, const float* bias_zr, const 
   WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0 && h_stride % 4 == 0 && rh_stride % 4 == 0,
                "woft_gru_gates_nhwc: channels and strides must be positive multiples of 4");
   const long long total4 = pixels * (channels / 4);
-  gru_gates_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(zr, bias_zr, h, h_stride, z, rh,
-                                                                                        rh_stride, channels / 4, total4);
+  gru_gates_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      zr, zr + channels, 2 * channels, bias_zr, bias_zr + channels, h, h_stride, z, rh, rh_stride, channels / 4, total4);
+  return launch_status("gru_gates_nhwc_kernel");
+}
+
+extern "C" int woft_gru_gates_nhwc_split(const float* z_pre, const float* r_pre, int pre_stride, const float* bias_z,
+                                         const float* bias_r, const float* h, int h_stride, long long pixels,
+                                         int channels, float* z, float* rh, int rh_stride, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(z_pre && r_pre && bias_z && bias_r && h && z && rh, "woft_gru_gates_nhwc_split: null pointer");
+  WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0 && h_stride % 4 == 0 && rh_stride % 4 == 0 &&
+                   pre_stride >= channels && pre_stride % 4 == 0,
+               "woft_gru_gates_nhwc_split: channels and strides must be positive multiples of 4, pre_stride >= channels");
+  const long long total4 = pixels * (channels / 4);
+  gru_gates_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      z_pre, r_pre, pre_stride, bias_z, bias_r, h, h_stride, z, rh, rh_stride, channels / 4, total4);
   return launch_status("gru_gates_nhwc_kernel");
 }
 

@@ -197,8 +197,16 @@ class FastWeightedRAFT:
                 self.ubw["conv"] = (_cl(torch.cat([wc, wc.new_zeros((pad,) + tuple(wc.shape[1:]))], 0)),
                                     torch.cat([bc, bc.new_zeros(pad)], 0).contiguous())
                 for tag in ("1", "2"):
-                    self.gru[tag]["w_zr"] = _cl(self.gru[tag]["w_zr"])
-                    self.gru[tag]["w_q"] = _cl(self.gru[tag]["w_q"])
+                    gt = self.gru[tag]
+                    gt["w_zr"], gt["w_q"] = _cl(gt["w_zr"]), _cl(gt["w_q"])
+                    # cuDNN 9 has no sm_100 kernel for the stacked horizontal 1x5 384->256 shape and falls back to an
+                    # sm_80 one (83 us + a layout conversion, against 14 us for each 128-filter half): run that
+                    # pair as two convolutions (scripts/conv_times.py, profiles/r1_conv_times.txt)
+                    gt["split"] = tuple(gt["w_zr"].shape[2:]) == (1, 5)
+                    if gt["split"]:
+                        cz, cr = (getattr(g, f"conv{k}{tag}") for k in "zr")
+                        gt["w_z"], gt["w_r"] = _cl(cz.weight), _cl(cr.weight)
+                        gt["b_z"], gt["b_r"] = cz.bias.contiguous(), cr.bias.contiguous()
 
     # ---- context encoder: fold eval-mode BatchNorm into the convolutions ---------------------------------
     @staticmethod
@@ -294,16 +302,27 @@ class FastWeightedRAFT:
               "buf1": _empty_cl(B, C + 2 * C, H, W, net), "buf2": _empty_cl(B, C + 2 * C, H, W, net), "C": C,
               "pixels": B * H * W}
         concat_nhwc([st["h"]], st["buf1"], 0)  # buf1 = [h | x], buf2 = [r*h | x]
+        concat_nhwc([st["inp"]], st["buf1"], C, st["buf2"], C)  # x = [inp | motion | flow]: inp is the same every iteration
         return st
 
     def _gru_half_nhwc(self, st, tag):
         g, C, lib = self.gru[tag], st["C"], _lib.load()
         buf1, buf2, dev = st["buf1"], st["buf2"], st["h"].device
-        zr = _cl(F.conv2d(buf1, g["w_zr"], None, padding=g["padding"]))
-        with torch.cuda.device(dev):
-            rc = lib.woft_gru_gates_nhwc(_lib.ptr(zr), _lib.ptr(g["b_zr"]), _lib.ptr(buf1), buf1.shape[1], st["pixels"], C,
-                                         _lib.ptr(st["z"]), _lib.ptr(buf2), buf2.shape[1], _lib.current_stream(dev))
-        _lib.check(rc, "woft_gru_gates_nhwc")
+        if g["split"]:
+            zp = _cl(F.conv2d(buf1, g["w_z"], None, padding=g["padding"]))
+            rp = _cl(F.conv2d(buf1, g["w_r"], None, padding=g["padding"]))
+            with torch.cuda.device(dev):
+                rc = lib.woft_gru_gates_nhwc_split(_lib.ptr(zp), _lib.ptr(rp), C, _lib.ptr(g["b_z"]), _lib.ptr(g["b_r"]),
+                                                   _lib.ptr(buf1), buf1.shape[1], st["pixels"], C, _lib.ptr(st["z"]),
+                                                   _lib.ptr(buf2), buf2.shape[1], _lib.current_stream(dev))
+            _lib.check(rc, "woft_gru_gates_nhwc_split")
+        else:
+            zr = _cl(F.conv2d(buf1, g["w_zr"], None, padding=g["padding"]))
+            with torch.cuda.device(dev):
+                rc = lib.woft_gru_gates_nhwc(_lib.ptr(zr), _lib.ptr(g["b_zr"]), _lib.ptr(buf1), buf1.shape[1],
+                                             st["pixels"], C, _lib.ptr(st["z"]), _lib.ptr(buf2), buf2.shape[1],
+                                             _lib.current_stream(dev))
+            _lib.check(rc, "woft_gru_gates_nhwc")
         q = _cl(F.conv2d(buf2, g["w_q"], None, padding=g["padding"]))
         with torch.cuda.device(dev):
             rc = lib.woft_gru_update_nhwc(_lib.ptr(q), _lib.ptr(g["b_q"]), _lib.ptr(st["z"]), _lib.ptr(buf1), buf1.shape[1],
@@ -325,11 +344,13 @@ class FastWeightedRAFT:
         out = _conv_relu(cf, *w["conv"], padding=(1, 1))      # 126 motion channels + `conv_pad` zero channels
         C = st["C"]
         if self.conv_pad == flow.shape[1]:
-            concat_nhwc([st["inp"], _cl(out)], st["buf1"], C, st["buf2"], C)           # x = [inp | motion | 0 0]
-            off = C + st["inp"].shape[1] + out.shape[1] - self.conv_pad
+            ci = st["inp"].shape[1]
+            concat_nhwc([_cl(out)], st["buf1"], C + ci, st["buf2"], C + ci)            # x = [inp | motion | 0 0]
+            off = C + ci + out.shape[1] - self.conv_pad
             concat_nhwc([flow], st["buf1"], off, st["buf2"], off)                       # ... flow over the zeros
         else:
-            concat_nhwc([st["inp"], _cl(out[:, :out.shape[1] - self.conv_pad]), flow], st["buf1"], C, st["buf2"], C)
+            ci = st["inp"].shape[1]
+            concat_nhwc([_cl(out[:, :out.shape[1] - self.conv_pad]), flow], st["buf1"], C + ci, st["buf2"], C + ci)
         self._gru_half_nhwc(st, "1")
         self._gru_half_nhwc(st, "2")
         h = st["h"]

@@ -237,6 +237,14 @@ size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels);
 int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels, float eps, int relu, float* y,
                                  void* scratch, size_t scratch_bytes, void* stream);
 
+/* The tail of a residual block in one pass (raft_core/extractor.py:45-56: y = relu(norm2(conv2(y))); return relu(x+y)):
+ *   woft_instance_norm_relu_add_nhwc : y = relu(residual + relu(instance_norm(x))), all (batch, HW, channels)
+ *   woft_add_relu                    : y = relu(a + b) over n floats (the batch-norm encoder, whose norm is folded
+ *                                      into the convolution); y may alias a or b */
+int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int hw, int channels, float eps, const float* residual,
+                                     float* y, void* scratch, size_t scratch_bytes, void* stream);
+int woft_add_relu(const float* a, const float* b, long long n, float* y, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

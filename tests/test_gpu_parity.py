@@ -357,6 +357,16 @@ def test_fused_gru_and_instance_norm_kernels():
             assert torch.allclose(fast_net.instance_norm_relu(x, relu=relu), want, atol=2e-5)
             got = fast_net.instance_norm_relu_nhwc(x.contiguous(memory_format=torch.channels_last), relu=relu)
             assert got.is_contiguous(memory_format=torch.channels_last) and torch.allclose(got, want, atol=2e-5)
+        # tail of a residual block in one pass: relu(res + relu(norm(x)))  (extractor.py:45-56)
+        res = torch.randn((3, C, 45, 80), generator=g).to(DEV).contiguous(memory_format=torch.channels_last)
+        got = fast_net.instance_norm_relu_nhwc(x.contiguous(memory_format=torch.channels_last), residual=res)
+        assert torch.allclose(got, F.relu(res + F.relu(F.instance_norm(x, eps=1e-5))), atol=2e-5)
+        for a in (x, x.contiguous(memory_format=torch.channels_last)):
+            b = torch.randn_like(a)
+            got = fast_net.add_relu(a, b)
+            assert got.stride() == a.stride() and torch.equal(got, F.relu(a + b))
+    with pytest.raises(AssertionError):
+        fast_net.add_relu(x, x.contiguous(memory_format=torch.channels_last))
 
 
 def test_fused_schedule_matches_layer_by_layer(golden):

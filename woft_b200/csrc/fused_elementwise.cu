@@ -261,8 +261,10 @@ __global__ void __launch_bounds__(256) in_finalize_nhwc_kernel(const float* __re
   }
 }
 
-__global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ stats, float* __restrict__ y,
-                                     int HW, int C, int relu, long long total4) {
+// `residual` (optional): y = relu(residual + act(norm(x))), the tail of a residual block (extractor.py:56) in one pass
+__global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ stats,
+                                     const float* __restrict__ residual, float* __restrict__ y, int HW, int C,
+                                     int relu, long long total4) {
   const int c4n = C >> 2;
   const float floor_ = relu ? 0.f : -3.4e38f;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
@@ -277,6 +279,22 @@ __global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* _
     o.y = fmaxf((v.y - m.y) * r.y, floor_);
     o.z = fmaxf((v.z - m.z) * r.z, floor_);
     o.w = fmaxf((v.w - m.w) * r.w, floor_);
+    if (residual) {
+      const float4 a = __ldg(reinterpret_cast<const float4*>(residual) + i);
+      o.x = fmaxf(a.x + o.x, 0.f); o.y = fmaxf(a.y + o.y, 0.f); o.z = fmaxf(a.z + o.z, 0.f); o.w = fmaxf(a.w + o.w, 0.f);
+    }
+    reinterpret_cast<float4*>(y)[i] = o;
+  }
+}
+
+__global__ void add_relu_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ y,
+                                long long total4) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
+       i += (long long)gridDim.x * blockDim.x) {
+    const float4 u = __ldg(reinterpret_cast<const float4*>(a) + i);
+    const float4 v = __ldg(reinterpret_cast<const float4*>(b) + i);
+    float4 o;
+    o.x = fmaxf(u.x + v.x, 0.f); o.y = fmaxf(u.y + v.y, 0.f); o.z = fmaxf(u.z + v.z, 0.f); o.w = fmaxf(u.w + v.w, 0.f);
     reinterpret_cast<float4*>(y)[i] = o;
   }
 }
@@ -408,20 +426,43 @@ extern "C" size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels)
   return (size_t)batch * channels * 2 * (woft::kInStrips + 1) * sizeof(float);
 }
 
-extern "C" int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels, float eps, int relu,
-                                            float* y, void* scratch, size_t scratch_bytes, void* stream) {
+static int instance_norm_nhwc_impl(const char* who, const float* x, int batch, int hw, int channels, float eps, int relu,
+                                   const float* residual, float* y, void* scratch, size_t scratch_bytes, void* stream) {
   using namespace woft;
-  WOFT_REQUIRE(x && y && scratch, "woft_instance_norm_relu_nhwc: null pointer");
+  WOFT_REQUIRE(x && y && scratch, "instance norm (NHWC): null pointer");
   WOFT_REQUIRE(batch > 0 && hw > 0 && channels > 0 && channels % 4 == 0 && channels <= 1024 && batch < 65536,
-               "woft_instance_norm_relu_nhwc: channels must be a multiple of 4 (<= 1024)");
+               "instance norm (NHWC): channels must be a multiple of 4 (<= 1024)");
   if (scratch_bytes < woft_instance_norm_nhwc_scratch_bytes(batch, channels))
-    return fail(WOFT_ERR_WORKSPACE, "woft_instance_norm_relu_nhwc: scratch too small");
+    return fail(WOFT_ERR_WORKSPACE, "%s: scratch too small", who);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   float* partial = static_cast<float*>(scratch);
   float* stats = partial + (size_t)batch * kInStrips * 2 * channels;
   in_partial_nhwc_kernel<<<dim3(kInStrips, batch), 256, 0, s>>>(x, partial, hw, channels);
   in_finalize_nhwc_kernel<<<dim3(ceil_div(channels, 8), batch), 256, 0, s>>>(x, partial, stats, hw, channels, eps);
   const long long total4 = (long long)batch * hw * (channels / 4);
-  in_apply_nhwc_kernel<<<ew_grid(total4), 256, 0, s>>>(x, stats, y, hw, channels, relu, total4);
+  in_apply_nhwc_kernel<<<ew_grid(total4), 256, 0, s>>>(x, stats, residual, y, hw, channels, relu, total4);
   return launch_status("instance norm (NHWC) kernels");
+}
+
+extern "C" int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels, float eps, int relu,
+                                            float* y, void* scratch, size_t scratch_bytes, void* stream) {
+  return instance_norm_nhwc_impl("woft_instance_norm_relu_nhwc", x, batch, hw, channels, eps, relu, nullptr, y, scratch,
+                                 scratch_bytes, stream);
+}
+
+extern "C" int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int hw, int channels, float eps,
+                                                const float* residual, float* y, void* scratch, size_t scratch_bytes,
+                                                void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(residual, "woft_instance_norm_relu_add_nhwc: null residual");
+  return instance_norm_nhwc_impl("woft_instance_norm_relu_add_nhwc", x, batch, hw, channels, eps, 1, residual, y, scratch,
+                                 scratch_bytes, stream);
+}
+
+extern "C" int woft_add_relu(const float* a, const float* b, long long n, float* y, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(a && b && y, "woft_add_relu: null pointer");
+  WOFT_REQUIRE(n > 0 && n % 4 == 0, "woft_add_relu: element count must be a positive multiple of 4");
+  add_relu_kernel<<<ew_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, b, y, n / 4);
+  return launch_status("add_relu_kernel");
 }

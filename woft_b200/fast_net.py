@@ -39,8 +39,9 @@ def instance_norm_relu(x, relu=True, eps=1e-5):
     return y
 
 
-def instance_norm_relu_nhwc(x, relu=True, eps=1e-5):
-    """channels-last (N, C, H, W) tensor -> same; woft_instance_norm_relu_nhwc."""
+def instance_norm_relu_nhwc(x, relu=True, eps=1e-5, residual=None):
+    """channels-last (N, C, H, W) tensor -> same; woft_instance_norm_relu_nhwc.  With `residual` (same shape,
+    channels-last) the result is relu(residual + relu(norm(x))): woft_instance_norm_relu_add_nhwc."""
     x = _cl(x)
     N, C, H, W = x.shape
     y = torch.empty_like(x)
@@ -48,9 +49,35 @@ def instance_norm_relu_nhwc(x, relu=True, eps=1e-5):
     nbytes = lib.woft_instance_norm_nhwc_scratch_bytes(N, C)
     scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
-        rc = lib.woft_instance_norm_relu_nhwc(_lib.ptr(x), N, H * W, C, eps, int(relu), _lib.ptr(y), _lib.ptr(scratch),
-                                              nbytes, _lib.current_stream(x.device))
-    _lib.check(rc, "woft_instance_norm_relu_nhwc")
+        if residual is None:
+            what = "woft_instance_norm_relu_nhwc"
+            rc = lib.woft_instance_norm_relu_nhwc(_lib.ptr(x), N, H * W, C, eps, int(relu), _lib.ptr(y),
+                                                  _lib.ptr(scratch), nbytes, _lib.current_stream(x.device))
+        else:
+            what = "woft_instance_norm_relu_add_nhwc"
+            if not relu or residual.shape != x.shape:
+                raise AssertionError("the fused residual tail needs relu=True and a residual of the same shape")
+            residual = _cl(residual)
+            rc = lib.woft_instance_norm_relu_add_nhwc(_lib.ptr(x), N, H * W, C, eps, _lib.ptr(residual), _lib.ptr(y),
+                                                      _lib.ptr(scratch), nbytes, _lib.current_stream(x.device))
+    _lib.check(rc, what)
+    return y
+
+
+def _dense(t):
+    return t.is_contiguous() or (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last))
+
+
+def add_relu(a, b):
+    """relu(a + b) in one pass for two tensors of the same shape and memory layout; woft_add_relu."""
+    if a.shape != b.shape or a.stride() != b.stride() or not _dense(a):
+        raise AssertionError("add_relu needs two dense tensors of the same shape and strides")
+    y = torch.empty_like(a)
+    if y.stride() != a.stride():
+        raise AssertionError("add_relu: unexpected output layout")
+    with torch.cuda.device(a.device):
+        rc = _lib.load().woft_add_relu(_lib.ptr(a), _lib.ptr(b), a.numel(), _lib.ptr(y), _lib.current_stream(a.device))
+    _lib.check(rc, "woft_add_relu")
     return y
 
 
@@ -237,7 +264,7 @@ class FastWeightedRAFT:
             y = _conv_relu(y, *d["c2"], padding=(1, 1))
             if d["down"] is not None:
                 x = F.conv2d(x, d["down"][0], d["down"][1], stride=d["stride"])
-            x = F.relu(x + y)
+            x = add_relu(x, y) if x.stride() == y.stride() and _dense(x) else F.relu(x + y)
         return F.conv2d(x, *c["out"])
 
     # ---- feature encoder: bias-free conv + fused instance norm / ReLU --------------------------------------
@@ -262,10 +289,9 @@ class FastWeightedRAFT:
         x = instance_norm_relu_nhwc(F.conv2d(_cl(x), w["stem"], None, stride=2, padding=3))
         for d in w["blocks"]:
             y = instance_norm_relu_nhwc(F.conv2d(x, d["c1"], None, stride=d["stride"], padding=1))
-            y = instance_norm_relu_nhwc(F.conv2d(y, d["c2"], None, padding=1))
             if d["down"] is not None:
                 x = instance_norm_relu_nhwc(F.conv2d(x, d["down"], None, stride=d["stride"]), relu=False)
-            x = F.relu(x + y)
+            x = instance_norm_relu_nhwc(F.conv2d(y, d["c2"], None, padding=1), residual=x)  # relu(x + relu(norm(..)))
         return F.conv2d(x, w["out"][0], w["out"][1])
 
     # ---- update block ---------------------------------------------------------------------------------------

@@ -168,6 +168,11 @@ int woft_gru_update_nhwc(const float* q, const float* bias_q, const float* z, co
                          long long pixels, int channels, float* h_out, int h_out_stride, float* h_dense, void* stream);
 int woft_concat_nhwc(const float* const* srcs, const int* channels, int n_src, long long pixels, float* dst,
                      int dst_stride, int dst_offset, float* dst2, int dst2_stride, int dst2_offset, void* stream);
+/* The same with a pixel stride per source (HOST array, floats, >= channels[i]): a source may be the leading channels
+ * of a wider tensor, e.g. the 126 motion features in front of the two padding channels of the encoder's last conv. */
+int woft_concat_nhwc_strided(const float* const* srcs, const int* channels, const int* src_strides, int n_src,
+                             long long pixels, float* dst, int dst_stride, int dst_offset, float* dst2, int dst2_stride,
+                             int dst2_offset, void* stream);
 
 /* Two thin convolutions of the update block, 12 calls each per flow pass, fp32 on CUDA cores:
  *   woft_flow_conv7x7_relu : BasicMotionEncoder.convf1 + ReLU (update.py:85, 92): 7x7, pad 3, 2 -> 128 channels.
@@ -178,6 +183,19 @@ int woft_flow_conv7x7_relu(const float* flow, const float* weight, const float* 
                            float* out_nhwc, void* stream);
 int woft_flow_out3x3(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
                      int channels, float* out_nchw, void* stream);
+
+/* FlowHead.conv2 and the step of the refinement loop that follows it (raft_core/weighted_raft.py:244-246:
+ * coords1 = coords1 + delta_flow; next iteration's flow = coords1 - coords0) in two launches that read every input
+ * value once: per input pixel the 18 (tap, output) products, then per output pixel the sum of 9 shifted products.
+ *   in (B,H,W,C) channels-last, C a multiple of 16; weight (2,C,3,3); bias (2)
+ *   scratch: woft_flow_head_scratch_bytes(B,H,W) bytes
+ *   delta_nchw (B,2,H,W) or NULL: the convolution's result, as woft_flow_out3x3 gives it
+ *   coords (B,2,H,W) or NULL: updated IN PLACE by the delta; with it coords0 (B,2,H,W) is required and
+ *   flow_nchw (B,2,H,W) / flow_nhwc (B,H,W,2), each optional, receive coords - coords0 */
+size_t woft_flow_head_scratch_bytes(int batch, int height, int width);
+int woft_flow_head_step(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
+                        int channels, void* scratch, size_t scratch_bytes, float* delta_nchw, float* coords,
+                        const float* coords0, float* flow_nchw, float* flow_nhwc, void* stream);
 
 /* Replaces nn.InstanceNorm2d + ReLU after each convolution of the feature encoder
  * (raft_core/extractor.py:30-32, 49-50, 127, 180-181): per (n, c) plane y = (x - mean) / sqrt(var + eps), biased

@@ -421,6 +421,11 @@ def test_nhwc_gru_and_concat_kernels():
     want = torch.cat([a, b, c], dim=1)
     assert torch.equal(d1[:, 64:], want) and torch.equal(d2[:, 80:], want)
     assert d1[:, :64].abs().sum().item() == 0
+    # channel prefixes of wider sources (the 126 motion features in front of two padding channels, then the flow)
+    wide = torch.randn((B, 128, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    d3 = torch.full((B, 384, H, W), -1.0, device=DEV).contiguous(memory_format=cl)
+    fast_net.concat_nhwc([wide, c], d3, 256, take=[126, 2])
+    assert torch.equal(d3[:, 256:], torch.cat([wide[:, :126], c], dim=1)) and (d3[:, :256] == -1).all()
     # gates / update on channel slices of wider buffers, against the NCHW formulas
     buf1 = torch.randn((B, 3 * C, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
     buf2 = torch.zeros_like(buf1)
@@ -437,6 +442,12 @@ def test_nhwc_gru_and_concat_kernels():
     assert torch.allclose(buf2[:, :C], torch.sigmoid(zb[:, C:]) * h, atol=1e-6)
     q = torch.randn((B, C, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
     bq = torch.randn((C,), generator=g).to(DEV)
+    zp, rp = zr[:, :C].contiguous(memory_format=cl), zr[:, C:].contiguous(memory_format=cl)
+    z2, buf3 = torch.empty_like(z), torch.zeros_like(buf1)
+    rc = lib.woft_gru_gates_nhwc_split(_lib.ptr(zp), _lib.ptr(rp), C, _lib.ptr(bias[:C].contiguous()),
+                                       _lib.ptr(bias[C:].contiguous()), _lib.ptr(buf1), 3 * C, B * H * W, C, _lib.ptr(z2),
+                                       _lib.ptr(buf3), 3 * C, st)
+    assert rc == 0 and torch.equal(z2, z) and torch.equal(buf3[:, :C], buf2[:, :C])
     hd = torch.empty((B, C, H, W), device=DEV).contiguous(memory_format=cl)
     tail = buf1[:, C:].clone()
     rc = lib.woft_gru_update_nhwc(_lib.ptr(q), _lib.ptr(bq), _lib.ptr(z), _lib.ptr(buf1), 3 * C, B * H * W, C,
@@ -453,7 +464,7 @@ def test_thin_convolution_kernels():
     old = torch.backends.cudnn.allow_tf32
     torch.backends.cudnn.allow_tf32 = False
     try:
-        for (B, H, W) in ((1, 22, 36), (2, 16, 24)):
+        for (B, H, W) in ((1, 22, 36), (2, 16, 24), (1, 90, 160), (3, 9, 7)):
             flow = (torch.randn((B, 2, H, W), generator=g) * 3).to(DEV)
             w7 = (torch.randn((128, 2, 7, 7), generator=g) * 0.1).to(DEV)
             b7 = torch.randn((128,), generator=g).to(DEV)
@@ -464,7 +475,19 @@ def test_thin_convolution_kernels():
             w3 = (torch.randn((2, 256, 3, 3), generator=g) * 0.05).to(DEV)
             b3 = torch.randn((2,), generator=g).to(DEV)
             got = fast_net.flow_out3x3(x, w3, b3)
-            assert got.is_contiguous() and torch.allclose(got, F.conv2d(x, w3, b3, padding=1), atol=5e-5)
+            want = F.conv2d(x, w3, b3, padding=1)
+            assert got.is_contiguous() and torch.allclose(got, want, atol=5e-5)
+            # the two-launch form, alone and fused with the coordinate update of the refinement loop
+            assert torch.allclose(fast_net.flow_head_step(x, w3, b3), want, atol=5e-5)
+            c0 = torch.randn((B, 2, H, W), generator=g).to(DEV)
+            c1 = c0 + flow
+            coords, f1 = c1.clone(), torch.empty_like(c1)
+            f2 = torch.empty_like(c1).contiguous(memory_format=torch.channels_last)
+            delta = fast_net.flow_head_step(x, w3, b3, coords=coords, coords0=c0, flow_nchw=f1, flow_nhwc=f2,
+                                            want_delta=True)
+            assert torch.allclose(delta, want, atol=5e-5)
+            assert torch.allclose(coords, c1 + want, atol=1e-4)
+            assert torch.allclose(f1, c1 + want - c0, atol=1e-4) and torch.equal(f1, f2)
     finally:
         torch.backends.cudnn.allow_tf32 = old
 

@@ -49,6 +49,11 @@ SIGNATURES = {
                                      c_int, c_void_p, c_void_p]),
     "woft_concat_nhwc": (c_int, [_FLOATP_ARRAY, POINTER(c_int), c_int, ctypes.c_longlong, c_void_p, c_int, c_int,
                                  c_void_p, c_int, c_int, c_void_p]),
+    "woft_concat_nhwc_strided": (c_int, [_FLOATP_ARRAY, POINTER(c_int), POINTER(c_int), c_int, ctypes.c_longlong,
+                                         c_void_p, c_int, c_int, c_void_p, c_int, c_int, c_void_p]),
+    "woft_flow_head_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "woft_flow_head_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_size_t,
+                                    c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "woft_flow_conv7x7_relu": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_flow_out3x3": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_instance_norm_nhwc_scratch_bytes": (c_size_t, [c_int, c_int]),

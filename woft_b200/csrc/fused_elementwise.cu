@@ -117,53 +117,54 @@ __global__ void __launch_bounds__(512) instance_norm_relu_kernel(const float* __
 // ---- channels-last (NHWC) variants: a pixel's channels are contiguous; operands may be channel slices of wider
 // buffers (pixel stride > channel count), which is how the GRU avoids torch.cat: [h | x] and [r*h | x] live in two
 // persistent (pixels, C + Cx) buffers whose x part is written once per iteration.
+// Index math is 32-bit (the entry points bound the element count): a 64-bit division per element costs more than the
+// loads it addresses.
 __global__ void gru_gates_nhwc_kernel(const float* __restrict__ z_pre, const float* __restrict__ r_pre, int pre_stride,
                                       const float* __restrict__ bias_z, const float* __restrict__ bias_r,
                                       const float* __restrict__ h, int h_stride, float* __restrict__ z,
-                                      float* __restrict__ rh, int rh_stride, int C4, long long total4) {
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long pix = i / C4;
-    const int c4 = int(i - pix * C4);
-    const float4 zp = __ldg(reinterpret_cast<const float4*>(z_pre + pix * pre_stride) + c4);
-    const float4 rp = __ldg(reinterpret_cast<const float4*>(r_pre + pix * pre_stride) + c4);
-    const float4 hv = __ldg(reinterpret_cast<const float4*>(h + pix * h_stride) + c4);
+                                      float* __restrict__ rh, int rh_stride, unsigned C4, unsigned total4) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+    const unsigned pix = i / C4;
+    const unsigned c4 = i - pix * C4;
+    const float4 zp = __ldg(reinterpret_cast<const float4*>(z_pre + (size_t)pix * pre_stride) + c4);
+    const float4 rp = __ldg(reinterpret_cast<const float4*>(r_pre + (size_t)pix * pre_stride) + c4);
+    const float4 hv = __ldg(reinterpret_cast<const float4*>(h + (size_t)pix * h_stride) + c4);
     const float4 bz = __ldg(reinterpret_cast<const float4*>(bias_z) + c4);
     const float4 br = __ldg(reinterpret_cast<const float4*>(bias_r) + c4);
     float4 zo, ro;
     zo.x = sigmoidf_(zp.x + bz.x); zo.y = sigmoidf_(zp.y + bz.y); zo.z = sigmoidf_(zp.z + bz.z); zo.w = sigmoidf_(zp.w + bz.w);
     ro.x = sigmoidf_(rp.x + br.x) * hv.x; ro.y = sigmoidf_(rp.y + br.y) * hv.y;
     ro.z = sigmoidf_(rp.z + br.z) * hv.z; ro.w = sigmoidf_(rp.w + br.w) * hv.w;
-    reinterpret_cast<float4*>(z + pix * (4 * C4))[c4] = zo;
-    reinterpret_cast<float4*>(rh + pix * rh_stride)[c4] = ro;
+    reinterpret_cast<float4*>(z)[i] = zo;
+    reinterpret_cast<float4*>(rh + (size_t)pix * rh_stride)[c4] = ro;
   }
 }
 
 __global__ void gru_update_nhwc_kernel(const float* __restrict__ q, const float* __restrict__ bias,
                                        const float* __restrict__ z, const float* h, int h_stride, float* h_out,
-                                       int h_out_stride, float* __restrict__ h_dense, int C4, long long total4) {
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long pix = i / C4;
-    const int c4 = int(i - pix * C4);
-    const float4 qv = __ldg(reinterpret_cast<const float4*>(q + pix * (4 * C4)) + c4);
-    const float4 zv = __ldg(reinterpret_cast<const float4*>(z + pix * (4 * C4)) + c4);
-    const float4 hv = *(reinterpret_cast<const float4*>(h + pix * h_stride) + c4);  // may alias h_out
+                                       int h_out_stride, float* __restrict__ h_dense, unsigned C4, unsigned total4) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+    const unsigned pix = i / C4;
+    const unsigned c4 = i - pix * C4;
+    const float4 qv = __ldg(reinterpret_cast<const float4*>(q) + i);
+    const float4 zv = __ldg(reinterpret_cast<const float4*>(z) + i);
+    const float4 hv = *(reinterpret_cast<const float4*>(h + (size_t)pix * h_stride) + c4);  // may alias h_out
     const float4 bq = __ldg(reinterpret_cast<const float4*>(bias) + c4);
     float4 o;
     o.x = (1.f - zv.x) * hv.x + zv.x * tanhf(qv.x + bq.x);
     o.y = (1.f - zv.y) * hv.y + zv.y * tanhf(qv.y + bq.y);
     o.z = (1.f - zv.z) * hv.z + zv.z * tanhf(qv.z + bq.z);
     o.w = (1.f - zv.w) * hv.w + zv.w * tanhf(qv.w + bq.w);
-    reinterpret_cast<float4*>(h_out + pix * h_out_stride)[c4] = o;
-    if (h_dense) reinterpret_cast<float4*>(h_dense + pix * (4 * C4))[c4] = o;
+    reinterpret_cast<float4*>(h_out + (size_t)pix * h_out_stride)[c4] = o;
+    if (h_dense) reinterpret_cast<float4*>(h_dense)[i] = o;
   }
 }
 
 struct ConcatParams {
   const float* src[4];
-  int ch[4];      // channels of each source (dense: pixel stride = channels)
-  int off[4];     // channel offset of each source inside a destination pixel
+  int ch[4];          // channels taken from each source
+  int src_stride[4];  // floats between consecutive pixels of each source (>= ch: a source may be a channel prefix)
+  int off[4];         // channel offset of each source inside the concatenation
   int n_src;
   int total_ch;
   float* dst[2];
@@ -172,27 +173,42 @@ struct ConcatParams {
   int n_dst;
 };
 
-// dst[d][pix * stride_d + off_d + off_i + c] = src_i[pix * ch_i + c]; VW floats per thread and step
+// dst[d][pix * stride_d + off_d + off_i + c] = src_i[pix * src_stride_i + c]; VW floats per thread and step.  The source
+// is picked with unrolled selects: indexing the parameter struct with a run-time value would move it to local memory.
 template <int VW>
-__global__ void concat_nhwc_kernel(const ConcatParams p, long long pixels) {
-  const int per_pixel = p.total_ch / VW;
-  const long long total = pixels * per_pixel;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long pix = i / per_pixel;
-    int c = int(i - pix * per_pixel) * VW;  // channel within the concatenation
-    int s = 0;
-    while (s + 1 < p.n_src && c >= p.off[s + 1]) ++s;
-    const float* src = p.src[s] + pix * p.ch[s] + (c - p.off[s]);
-    float v[VW];
+__global__ void concat_nhwc_kernel(const __grid_constant__ ConcatParams p, unsigned total) {
+  const unsigned per_pixel = unsigned(p.total_ch) / VW;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned pix = i / per_pixel;
+    const int c = int(i - pix * per_pixel) * VW;  // channel within the concatenation
+    const float* base = p.src[0];
+    int stride = p.src_stride[0], off = 0;
 #pragma unroll
-    for (int k = 0; k < VW; ++k) v[k] = __ldg(src + k);
-    for (int d = 0; d < p.n_dst; ++d) {
-      float* o = p.dst[d] + pix * p.dst_stride[d] + p.dst_off[d] + c;
+    for (int s = 1; s < 4; ++s)
+      if (s < p.n_src && c >= p.off[s]) {
+        base = p.src[s];
+        stride = p.src_stride[s];
+        off = p.off[s];
+      }
+    const float* src = base + (size_t)pix * stride + (c - off);
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (VW == 4) {
+      const float4 t = __ldg(reinterpret_cast<const float4*>(src));
+      v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else if (VW == 2) {
+      const float2 t = __ldg(reinterpret_cast<const float2*>(src));
+      v[0] = t.x; v[1] = t.y;
+    } else {
+      v[0] = __ldg(src);
+    }
+#pragma unroll
+    for (int d = 0; d < 2; ++d) {
+      if (d >= p.n_dst) break;
+      float* o = p.dst[d] + (size_t)pix * p.dst_stride[d] + p.dst_off[d] + c;
       if (VW == 4)
-        *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[VW > 3 ? 3 : 0]);
+        *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
       else if (VW == 2)
-        *reinterpret_cast<float2*>(o) = make_float2(v[0], v[VW > 1 ? 1 : 0]);
+        *reinterpret_cast<float2*>(o) = make_float2(v[0], v[1]);
       else
         o[0] = v[0];
     }
@@ -214,12 +230,20 @@ __global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __res
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
   if (pl < ppb) {
     const float4 pv = __ldg(base + cq);  // pivot: the plane's first pixel, keeps the variance well conditioned
-    for (int p = p0 + pl; p < p1; p += ppb) {
-      const float4 v = __ldg(base + (size_t)p * c4n + cq);
+    auto add = [&](const float4 v) {
       const float a = v.x - pv.x, b = v.y - pv.y, c = v.z - pv.z, d = v.w - pv.w;
       s.x += a; s.y += b; s.z += c; s.w += d;
       q.x += a * a; q.y += b * b; q.z += c * c; q.w += d * d;
+    };
+    int p = p0 + pl;
+    for (; p + 3 * ppb < p1; p += 4 * ppb) {  // four loads in flight per thread: the pass is latency bound otherwise
+      const float4 v0 = __ldg(base + (size_t)p * c4n + cq);
+      const float4 v1 = __ldg(base + (size_t)(p + ppb) * c4n + cq);
+      const float4 v2 = __ldg(base + (size_t)(p + 2 * ppb) * c4n + cq);
+      const float4 v3 = __ldg(base + (size_t)(p + 3 * ppb) * c4n + cq);
+      add(v0); add(v1); add(v2); add(v3);
     }
+    for (; p < p1; p += ppb) add(__ldg(base + (size_t)p * c4n + cq));
   }
   s_sum[threadIdx.x] = s;
   s_sq[threadIdx.x] = q;
@@ -263,14 +287,14 @@ __global__ void __launch_bounds__(256) in_finalize_nhwc_kernel(const float* __re
 
 // `residual` (optional): y = relu(residual + act(norm(x))), the tail of a residual block (extractor.py:56) in one pass
 __global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ stats,
-                                     const float* __restrict__ residual, float* __restrict__ y, int HW, int C,
-                                     int relu, long long total4) {
-  const int c4n = C >> 2;
+                                     const float* __restrict__ residual, float* __restrict__ y, unsigned HW, unsigned C,
+                                     int relu, unsigned total4) {
+  const unsigned c4n = C >> 2;
+  const unsigned per_image = HW * c4n;
   const float floor_ = relu ? 0.f : -3.4e38f;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
-       i += (long long)gridDim.x * blockDim.x) {
-    const int cq = int(i % c4n);
-    const int n = int(i / ((long long)HW * c4n));
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+    const unsigned cq = i % c4n;
+    const unsigned n = i / per_image;
     const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
     const float4 m = __ldg(reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C) + cq);
     const float4 r = __ldg(reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C + C) + cq);
@@ -298,6 +322,8 @@ __global__ void add_relu_kernel(const float* __restrict__ a, const float* __rest
     reinterpret_cast<float4*>(y)[i] = o;
   }
 }
+
+constexpr long long kMaxElems32 = 0x7fffffffLL;  // the NHWC kernels index with 32-bit integers
 
 static int ew_grid(long long total4) {
   const long long blocks = (total4 + 255) / 256;
@@ -346,8 +372,10 @@ extern "C" int woft_gru_gates_nhwc(const float* zr, const float* bias_zr, const 
   WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0 && h_stride % 4 == 0 && rh_stride % 4 == 0,
                "woft_gru_gates_nhwc: channels and strides must be positive multiples of 4");
   const long long total4 = pixels * (channels / 4);
+  WOFT_REQUIRE(total4 <= kMaxElems32, "woft_gru_gates_nhwc: more than 2^31 - 1 vectors");
   gru_gates_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      zr, zr + channels, 2 * channels, bias_zr, bias_zr + channels, h, h_stride, z, rh, rh_stride, channels / 4, total4);
+      zr, zr + channels, 2 * channels, bias_zr, bias_zr + channels, h, h_stride, z, rh, rh_stride, channels / 4,
+      unsigned(total4));
   return launch_status("gru_gates_nhwc_kernel");
 }
 
@@ -360,8 +388,9 @@ extern "C" int woft_gru_gates_nhwc_split(const float* z_pre, const float* r_pre,
                    pre_stride >= channels && pre_stride % 4 == 0,
                "woft_gru_gates_nhwc_split: channels and strides must be positive multiples of 4, pre_stride >= channels");
   const long long total4 = pixels * (channels / 4);
+  WOFT_REQUIRE(total4 <= kMaxElems32, "woft_gru_gates_nhwc_split: more than 2^31 - 1 vectors");
   gru_gates_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      z_pre, r_pre, pre_stride, bias_z, bias_r, h, h_stride, z, rh, rh_stride, channels / 4, total4);
+      z_pre, r_pre, pre_stride, bias_z, bias_r, h, h_stride, z, rh, rh_stride, channels / 4, unsigned(total4));
   return launch_status("gru_gates_nhwc_kernel");
 }
 
@@ -373,14 +402,15 @@ extern "C" int woft_gru_update_nhwc(const float* q, const float* bias_q, const f
   WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0 && h_stride % 4 == 0 && h_out_stride % 4 == 0,
                "woft_gru_update_nhwc: channels and strides must be positive multiples of 4");
   const long long total4 = pixels * (channels / 4);
+  WOFT_REQUIRE(total4 <= kMaxElems32, "woft_gru_update_nhwc: more than 2^31 - 1 vectors");
   gru_update_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      q, bias_q, z, h, h_stride, h_out, h_out_stride, h_dense, channels / 4, total4);
+      q, bias_q, z, h, h_stride, h_out, h_out_stride, h_dense, channels / 4, unsigned(total4));
   return launch_status("gru_update_nhwc_kernel");
 }
 
-extern "C" int woft_concat_nhwc(const float* const* srcs, const int* channels, int n_src, long long pixels, float* dst,
-                                int dst_stride, int dst_offset, float* dst2, int dst2_stride, int dst2_offset,
-                                void* stream) {
+static int concat_nhwc_impl(const float* const* srcs, const int* channels, const int* src_strides, int n_src,
+                            long long pixels, float* dst, int dst_stride, int dst_offset, float* dst2, int dst2_stride,
+                            int dst2_offset, void* stream) {
   using namespace woft;
   WOFT_REQUIRE(srcs && channels && dst, "woft_concat_nhwc: null pointer");
   WOFT_REQUIRE(n_src >= 1 && n_src <= 4 && pixels > 0, "woft_concat_nhwc: 1..4 sources and a positive pixel count");
@@ -390,9 +420,13 @@ extern "C" int woft_concat_nhwc(const float* const* srcs, const int* channels, i
     WOFT_REQUIRE(srcs[i] && channels[i] > 0, "woft_concat_nhwc: source %d is empty", i);
     p.src[i] = srcs[i];
     p.ch[i] = channels[i];
+    p.src_stride[i] = src_strides ? src_strides[i] : channels[i];
+    WOFT_REQUIRE(p.src_stride[i] >= channels[i], "woft_concat_nhwc: source %d has a stride below its channel count", i);
     p.off[i] = off;
     off += channels[i];
-    while (vw > 1 && (channels[i] % vw || p.off[i] % vw || (reinterpret_cast<uintptr_t>(srcs[i]) % (4 * vw)))) vw >>= 1;
+    while (vw > 1 && (channels[i] % vw || p.off[i] % vw || p.src_stride[i] % vw ||
+                      (reinterpret_cast<uintptr_t>(srcs[i]) % (4 * vw))))
+      vw >>= 1;
   }
   p.n_src = n_src;
   p.total_ch = off;
@@ -410,15 +444,32 @@ extern "C" int woft_concat_nhwc(const float* const* srcs, const int* channels, i
     while (vw > 1 && (p.dst_stride[d] % vw || p.dst_off[d] % vw || (reinterpret_cast<uintptr_t>(p.dst[d]) % (4 * vw))))
       vw >>= 1;
   const long long total = pixels * (off / vw);
+  WOFT_REQUIRE(total <= kMaxElems32, "woft_concat_nhwc: more than 2^31 - 1 vectors");
   const int grid = ew_grid(total);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (vw == 4)
-    concat_nhwc_kernel<4><<<grid, 256, 0, s>>>(p, pixels);
+    concat_nhwc_kernel<4><<<grid, 256, 0, s>>>(p, unsigned(total));
   else if (vw == 2)
-    concat_nhwc_kernel<2><<<grid, 256, 0, s>>>(p, pixels);
+    concat_nhwc_kernel<2><<<grid, 256, 0, s>>>(p, unsigned(total));
   else
-    concat_nhwc_kernel<1><<<grid, 256, 0, s>>>(p, pixels);
+    concat_nhwc_kernel<1><<<grid, 256, 0, s>>>(p, unsigned(total));
   return launch_status("concat_nhwc_kernel");
+}
+
+extern "C" int woft_concat_nhwc(const float* const* srcs, const int* channels, int n_src, long long pixels, float* dst,
+                                int dst_stride, int dst_offset, float* dst2, int dst2_stride, int dst2_offset,
+                                void* stream) {
+  return concat_nhwc_impl(srcs, channels, nullptr, n_src, pixels, dst, dst_stride, dst_offset, dst2, dst2_stride,
+                          dst2_offset, stream);
+}
+
+extern "C" int woft_concat_nhwc_strided(const float* const* srcs, const int* channels, const int* src_strides, int n_src,
+                                        long long pixels, float* dst, int dst_stride, int dst_offset, float* dst2,
+                                        int dst2_stride, int dst2_offset, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(src_strides, "woft_concat_nhwc_strided: null stride array");
+  return concat_nhwc_impl(srcs, channels, src_strides, n_src, pixels, dst, dst_stride, dst_offset, dst2, dst2_stride,
+                          dst2_offset, stream);
 }
 
 extern "C" size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels) {
@@ -440,7 +491,8 @@ static int instance_norm_nhwc_impl(const char* who, const float* x, int batch, i
   in_partial_nhwc_kernel<<<dim3(kInStrips, batch), 256, 0, s>>>(x, partial, hw, channels);
   in_finalize_nhwc_kernel<<<dim3(ceil_div(channels, 8), batch), 256, 0, s>>>(x, partial, stats, hw, channels, eps);
   const long long total4 = (long long)batch * hw * (channels / 4);
-  in_apply_nhwc_kernel<<<ew_grid(total4), 256, 0, s>>>(x, stats, residual, y, hw, channels, relu, total4);
+  WOFT_REQUIRE(total4 <= kMaxElems32, "instance norm (NHWC): more than 2^31 - 1 vectors");
+  in_apply_nhwc_kernel<<<ew_grid(total4), 256, 0, s>>>(x, stats, residual, y, hw, channels, relu, unsigned(total4));
   return launch_status("instance norm (NHWC) kernels");
 }
 

@@ -110,17 +110,23 @@ def _empty_cl(b, c, h, w, like):
     return torch.empty((b, c, h, w), device=like.device, dtype=torch.float32, memory_format=torch.channels_last)
 
 
-def concat_nhwc(srcs, dst, dst_offset, dst2=None, dst2_offset=0):
+def concat_nhwc(srcs, dst, dst_offset, dst2=None, dst2_offset=0, take=None):
     """Channels-last tensors `srcs` (dense) written side by side into channel slice [dst_offset, ...) of `dst` (and of
-    `dst2`); woft_concat_nhwc."""
+    `dst2`); woft_concat_nhwc.  `take[i]` (optional) copies only the first take[i] channels of source i
+    (woft_concat_nhwc_strided)."""
     import ctypes
     B, _, H, W = srcs[0].shape
     ptrs, keep = _lib.ptr_array(srcs)
-    chans = (ctypes.c_int * len(srcs))(*[t.shape[1] for t in srcs])
+    strides = (ctypes.c_int * len(srcs))(*[t.shape[1] for t in srcs])
+    lib = _lib.load()
+    args = (B * H * W, _lib.ptr(dst), dst.shape[1], dst_offset, _lib.ptr(dst2),
+            dst2.shape[1] if dst2 is not None else 0, dst2_offset, _lib.current_stream(dst.device))
     with torch.cuda.device(dst.device):
-        rc = _lib.load().woft_concat_nhwc(ptrs, chans, len(srcs), B * H * W, _lib.ptr(dst), dst.shape[1], dst_offset,
-                                          _lib.ptr(dst2), dst2.shape[1] if dst2 is not None else 0, dst2_offset,
-                                          _lib.current_stream(dst.device))
+        if take is None:
+            rc = lib.woft_concat_nhwc(ptrs, strides, len(srcs), *args)
+        else:
+            chans = (ctypes.c_int * len(srcs))(*take)
+            rc = lib.woft_concat_nhwc_strided(ptrs, chans, strides, len(srcs), *args)
     del keep
     _lib.check(rc, "woft_concat_nhwc")
 
@@ -147,6 +153,25 @@ def flow_out3x3(x_cl, weight, bias):
                                           _lib.current_stream(x_cl.device))
     _lib.check(rc, "woft_flow_out3x3")
     return out
+
+
+def flow_head_step(x_cl, weight, bias, coords=None, coords0=None, flow_nchw=None, flow_nhwc=None, want_delta=False):
+    """FlowHead.conv2 on a channels-last (B,C,H,W) tensor; woft_flow_head_step.  With `coords` the refinement step is
+    fused: coords += delta in place, flow_nchw / flow_nhwc (preallocated, optional) = coords - coords0.  Returns the
+    delta (B,2,H,W) when `want_delta` or when there is nothing else to return."""
+    x_cl = _cl(x_cl)
+    B, C, H, W = x_cl.shape
+    lib = _lib.load()
+    dev = x_cl.device
+    nbytes = lib.woft_flow_head_scratch_bytes(B, H, W)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    delta = torch.empty((B, 2, H, W), device=dev, dtype=torch.float32) if (want_delta or coords is None) else None
+    with torch.cuda.device(dev):
+        rc = lib.woft_flow_head_step(_lib.ptr(x_cl), _lib.ptr(weight), _lib.ptr(bias), B, H, W, C, _lib.ptr(scratch), nbytes,
+                                     _lib.ptr(delta), _lib.ptr(coords), _lib.ptr(coords0), _lib.ptr(flow_nchw),
+                                     _lib.ptr(flow_nhwc), _lib.current_stream(dev))
+    _lib.check(rc, "woft_flow_head_step")
+    return delta
 
 
 def convex_upsample_both(flow_low, weights_low, mask, sigmoid=False):
@@ -322,11 +347,13 @@ class FastWeightedRAFT:
         return net, mask, dflow
 
     # ---- update block with channels-last activations and no torch.cat -----------------------------------------------
-    def _nhwc_state(self, net, inp):
+    def _nhwc_state(self, net, inp, coords0, coords1):
         B, C, H, W = net.shape
+        flow = (coords1 - coords0).contiguous()
         st = {"inp": _cl(inp), "h": _cl(net).clone(), "z": _empty_cl(B, C, H, W, net),
               "buf1": _empty_cl(B, C + 2 * C, H, W, net), "buf2": _empty_cl(B, C + 2 * C, H, W, net), "C": C,
-              "pixels": B * H * W}
+              "pixels": B * H * W, "coords0": coords0.contiguous(), "coords1": coords1.contiguous().clone(),
+              "flow": flow, "flow_cl": _cl(flow).clone()}   # flow_cl: logical (B,2,H,W), stored (B,H,W,2)
         concat_nhwc([st["h"]], st["buf1"], 0)  # buf1 = [h | x], buf2 = [r*h | x]
         concat_nhwc([st["inp"]], st["buf1"], C, st["buf2"], C)  # x = [inp | motion | flow]: inp is the same every iteration
         return st
@@ -356,36 +383,34 @@ class FastWeightedRAFT:
                                           _lib.current_stream(dev))
         _lib.check(rc, "woft_gru_update_nhwc")
 
-    def _update_nhwc(self, st, corr, flow, need_mask):
+    def _update_nhwc(self, st, corr, need_mask):
+        """One refinement iteration on the state of _nhwc_state: st["coords1"] is advanced in place and st["flow"] /
+        st["flow_cl"] (coords1 - coords0, NCHW and (pixels, 2)) are rewritten by the flow head's last kernel."""
         w = self.ubw
         e = self.net.update_block.encoder
-        flo = flow_conv7x7_relu(flow, e.convf1.weight, e.convf1.bias)   # NCHW flow in, channels-last out
-        flow = _cl(flow)
+        flo = flow_conv7x7_relu(st["flow"], e.convf1.weight, e.convf1.bias)   # NCHW flow in, channels-last out
         cor = _conv_relu(corr, *w["convc1"])
         cor = _conv_relu(cor, *w["convc2"], padding=(1, 1))
         flo = _conv_relu(flo, *w["convf2"], padding=(1, 1))
         B, _, H, W = cor.shape
         cf = _empty_cl(B, cor.shape[1] + flo.shape[1], H, W, cor)
         concat_nhwc([_cl(cor), _cl(flo)], cf, 0)
-        out = _conv_relu(cf, *w["conv"], padding=(1, 1))      # 126 motion channels + `conv_pad` zero channels
-        C = st["C"]
-        if self.conv_pad == flow.shape[1]:
-            ci = st["inp"].shape[1]
-            concat_nhwc([_cl(out)], st["buf1"], C + ci, st["buf2"], C + ci)            # x = [inp | motion | 0 0]
-            off = C + ci + out.shape[1] - self.conv_pad
-            concat_nhwc([flow], st["buf1"], off, st["buf2"], off)                       # ... flow over the zeros
-        else:
-            ci = st["inp"].shape[1]
-            concat_nhwc([_cl(out[:, :out.shape[1] - self.conv_pad]), flow], st["buf1"], C + ci, st["buf2"], C + ci)
+        out = _cl(_conv_relu(cf, *w["conv"], padding=(1, 1)))      # 126 motion channels + `conv_pad` zero channels
+        C, ci = st["C"], st["inp"].shape[1]
+        # x = [inp | motion | flow]: inp sits in both GRU buffers since _nhwc_state; the motion features go in without
+        # the padding channels of their convolution, the flow behind them (update.py:97)
+        concat_nhwc([out, st["flow_cl"]], st["buf1"], C + ci, st["buf2"], C + ci,
+                    take=[out.shape[1] - self.conv_pad, st["flow_cl"].shape[1]])
         self._gru_half_nhwc(st, "1")
         self._gru_half_nhwc(st, "2")
         h = st["h"]
         fh = self.net.update_block.flow_head
-        dflow = flow_out3x3(_conv_relu(h, *w["fh1"], padding=(1, 1)), fh.conv2.weight, fh.conv2.bias)
+        flow_head_step(_conv_relu(h, *w["fh1"], padding=(1, 1)), fh.conv2.weight, fh.conv2.bias, coords=st["coords1"],
+                       coords0=st["coords0"], flow_nchw=st["flow"], flow_nhwc=st["flow_cl"])
         mask = None
         if need_mask:
             mask = 0.25 * F.conv2d(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"])
-        return mask, dflow
+        return mask
 
     # ---- weight head, channels-last -----------------------------------------------------------------------------
     def _weights(self, window, mean_response):
@@ -430,13 +455,13 @@ class FastWeightedRAFT:
         up_mask = None
         nhwc = self.nhwc and isinstance(corr_fn, _CorrBlock)
         lookup_flags = 8 if nhwc else 0
-        state = self._nhwc_state(net, inp) if nhwc else None
+        state = self._nhwc_state(net, inp, coords0, coords1) if nhwc else None
         for it in range(iters):
             last = it == iters - 1
             if nhwc:
+                coords1 = state["coords1"]  # advanced in place by the flow head's last kernel
                 corr = corr_fn(coords1, flags=lookup_flags)
-                up_mask, dflow = self._update_nhwc(state, corr, coords1 - coords0, need_mask=last)
-                coords1 = (coords1 + dflow).contiguous()
+                up_mask = self._update_nhwc(state, corr, need_mask=last)
             else:
                 corr = corr_fn(coords1)
                 net, up_mask, dflow = self._update(net, inp, corr, coords1 - coords0, need_mask=last)

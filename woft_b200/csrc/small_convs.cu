@@ -10,90 +10,114 @@
 //                              pixel, lanes over input channels, warp-shuffle reduction.  Input channels-last
 //                              (B,H,W,C), output NCHW (B,2,H,W) so it can be added to the coordinates directly.
 //   flow_head_taps_kernel +    The same convolution in two steps that read every input value once: per input pixel the
-//   flow_head_gather_kernel    18 products t[pixel][tap][o] = <in[pixel,:], w[o,:,tap]> (a 14400 x 256 x 18 product, one
-//                              lane per pixel, four warps splitting the channels), then per output pixel the sum of
+//   flow_head_gather_kernel    18 products t[pixel][tap][o] = <in[pixel,:], w[o,:,tap]> (a 14400 x 256 x 18 product, four
+//                              pixels per lane, eight warps splitting the channels), then per output pixel the sum of
 //                              the 9 shifted taps + bias, fused with the coordinate update that follows the flow
 //                              head in the refinement loop (weighted_raft.py:244-246: coords1 = coords1 + delta_flow).
 #include "common.cuh"
 
 namespace woft {
 
-// One CTA per run of <= 112 consecutive pixels of one image (the runs are sized so that a 160x90 map gives 147 CTAs for
-// 148 SMs: the work is 181 M multiply-adds, so balance matters more than tile shape).  256 threads = 16 pixel slots x
-// 16 groups of 8 output channels; a thread owns 7 pixels (slot, slot+16, ...) x 8 channels = 56 accumulators, so one
-// weight vector pair read from shared memory feeds 56 FMAs.  The weights are staged [tap][cout] with a row stride of
-// 132 floats: global reads coalesced, transposing writes 4-way conflicted instead of 32-way.
-constexpr int kF7Slots = 16, kF7PerThread = 7, kF7MaxRun = kF7Slots * kF7PerThread;
+// The map is cut into row segments of 7 pixels; a CTA takes up to 16 consecutive segments (sized so that a 160x90 map
+// gives 148 CTAs: the work is 181 M multiply-adds, so balance matters more than tile shape).  256 threads = 16 segment
+// slots x 16 channel groups; a thread owns one segment x 8 output channels = 56 accumulators.  Per filter row it loads
+// the 13 input values under its segment once and slides the 7 taps over them in registers, so one weight vector pair
+// from shared memory feeds 56 FMAs and one input value up to 7 x 8.  Weights are staged [tap][cout] with a row stride of
+// 132 floats (coalesced global reads, 4-way instead of 32-way conflicts on the transposing writes); a thread's
+// channels are {4g..4g+3} and {64+4g..64+4g+3}, which keeps both the weight reads and the output stores contiguous
+// across the 16 groups.
+constexpr int kF7Seg = 7, kF7Slots = 16;
 constexpr int kF7Cout = 128, kF7WStride = 132;
 
 __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __restrict__ flow,   // (B,2,H,W)
                                                                 const float* __restrict__ weight, // (128,2,7,7)
                                                                 const float* __restrict__ bias,   // (128)
                                                                 float* __restrict__ out,          // (B,H,W,128)
-                                                                int H, int W, int run, int rows_max) {
+                                                                int H, int W, int segs_per_cta, int rows_max) {
   extern __shared__ __align__(16) float sm[];
   float* sw = sm;                                // [98 taps][132]
-  float* sin = sm + 98 * kF7WStride;             // [2][rows][W + 6], 3 zero columns / rows of halo
+  float* sin = sm + 98 * kF7WStride;             // [2][rows][pitch], 3 zero columns / rows of halo
   const int b = blockIdx.y;
-  const int p0 = blockIdx.x * run, p1 = min(p0 + run, H * W);
-  const int y_lo = p0 / W, y_hi = (p1 - 1) / W;
-  const int rows = y_hi - y_lo + 7, pitch = W + 6, plane = rows_max * pitch;
-  for (int i = threadIdx.x; i < 98 * kF7Cout; i += 256) {
-    const int co = i / 98, tap = i - co * 98;    // tap = ci*49 + ky*7 + kx, the (ci,ky,kx) order of the weight tensor
-    sw[tap * kF7WStride + co] = __ldg(weight + i);
+  const int segs_per_row = (W + kF7Seg - 1) / kF7Seg, total = segs_per_row * H;
+  const int s0 = blockIdx.x * segs_per_cta, s1 = min(s0 + segs_per_cta, total);
+  const int y_lo = s0 / segs_per_row, y_hi = (s1 - 1) / segs_per_row;
+  const int rows = y_hi - y_lo + 7, pitch = segs_per_row * kF7Seg + 6, plane = rows_max * pitch;
+  {
+    // 98 * 128 = 49 * 256 weights: every thread issues its 49 loads before the first (transposing) store, otherwise
+    // the staging is 49 L2 round trips long and costs more than the convolution
+    float wv[49];
+#pragma unroll
+    for (int k = 0; k < 49; ++k) wv[k] = __ldg(weight + threadIdx.x + 256 * k);
+#pragma unroll
+    for (int k = 0; k < 49; ++k) {
+      const int i = threadIdx.x + 256 * k;
+      const int co = i / 98, tap = i - co * 98;  // tap = ci*49 + ky*7 + kx, the (ci,ky,kx) order of the weight tensor
+      sw[tap * kF7WStride + co] = wv[k];
+    }
   }
-  for (int i = threadIdx.x; i < 2 * rows * pitch; i += 256) {
-    const int ci = i / (rows * pitch), r = i - ci * rows * pitch;
-    const int ry = r / pitch, rx = r - ry * pitch;
-    const int yy = y_lo + ry - 3, xx = rx - 3;
-    sin[ci * plane + r] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(flow + ((size_t)(b * 2 + ci) * H + yy) * W + xx)
-                                                                  : 0.f;
+  const int n_in = 2 * rows * pitch;
+  for (int i0 = threadIdx.x; i0 < n_in; i0 += 4 * 256) {
+    float v[4];
+    int dst[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      const int ic = i < n_in ? i : 0;
+      const int ci = ic / (rows * pitch), r = ic - ci * rows * pitch;
+      const int ry = r / pitch, rx = r - ry * pitch;
+      const int yy = y_lo + ry - 3, xx = rx - 3;
+      dst[u] = i < n_in ? ci * plane + r : -1;
+      v[u] = (yy >= 0 && yy < H && xx >= 0 && xx < W) ? __ldg(flow + ((size_t)(b * 2 + ci) * H + yy) * W + xx) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (dst[u] >= 0) sin[dst[u]] = v[u];
   }
   __syncthreads();
-  const int grp = threadIdx.x & 15, slot = threadIdx.x >> 4;   // a warp = 2 slots x 16 groups: 512-byte output stores
-  int base[kF7PerThread];
-#pragma unroll
-  for (int j = 0; j < kF7PerThread; ++j) {
-    const int p = p0 + slot + kF7Slots * j;
-    const int pc = p < p1 ? p : p0;              // out-of-run slots compute a valid pixel again and store nothing
-    const int y = pc / W, x = pc - y * W;
-    base[j] = (y - y_lo) * pitch + x;            // staged row of input (y + ky - 3) is (y - y_lo + ky), column x + kx
-  }
-  float acc[kF7PerThread][8];
+  const int grp = threadIdx.x & 15, slot = threadIdx.x >> 4;   // a warp = 2 segments x 16 groups
+  const bool active = slot < segs_per_cta && s0 + slot < s1;
+  const int seg = active ? s0 + slot : s0;       // idle slots recompute the first segment and store nothing
+  const int y = seg / segs_per_row, x0 = (seg - y * segs_per_row) * kF7Seg;
+  float acc[kF7Seg][8];
   {
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias) + grp * 2);
-    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias) + grp * 2 + 1);
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias) + grp);
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias) + 16 + grp);
 #pragma unroll
-    for (int j = 0; j < kF7PerThread; ++j) {
+    for (int j = 0; j < kF7Seg; ++j) {
       acc[j][0] = b0.x; acc[j][1] = b0.y; acc[j][2] = b0.z; acc[j][3] = b0.w;
       acc[j][4] = b1.x; acc[j][5] = b1.y; acc[j][6] = b1.z; acc[j][7] = b1.w;
     }
   }
   for (int ci = 0; ci < 2; ++ci)
+#pragma unroll 1
     for (int ky = 0; ky < 7; ++ky) {
-      const float* srow = sin + ci * plane + ky * pitch;
-      const float* wrow = sw + (ci * 49 + ky * 7) * kF7WStride + grp * 8;
+      // staged row of input row (y + ky - 3) is (y - y_lo + ky); staged column of input column (x - 3) is x
+      const float* srow = sin + ci * plane + (y - y_lo + ky) * pitch + x0;
+      float v[kF7Seg + 6];
+#pragma unroll
+      for (int i = 0; i < kF7Seg + 6; ++i) v[i] = srow[i];
+      const float4* wrow = reinterpret_cast<const float4*>(sw + (ci * 49 + ky * 7) * kF7WStride) + grp;
 #pragma unroll
       for (int kx = 0; kx < 7; ++kx) {
-        const float4 w0 = *reinterpret_cast<const float4*>(wrow + kx * kF7WStride);
-        const float4 w1 = *reinterpret_cast<const float4*>(wrow + kx * kF7WStride + 4);
+        const float4 w0 = wrow[kx * (kF7WStride / 4)];
+        const float4 w1 = wrow[kx * (kF7WStride / 4) + 16];
 #pragma unroll
-        for (int j = 0; j < kF7PerThread; ++j) {
-          const float v = srow[base[j] + kx];
-          acc[j][0] = fmaf(v, w0.x, acc[j][0]); acc[j][1] = fmaf(v, w0.y, acc[j][1]);
-          acc[j][2] = fmaf(v, w0.z, acc[j][2]); acc[j][3] = fmaf(v, w0.w, acc[j][3]);
-          acc[j][4] = fmaf(v, w1.x, acc[j][4]); acc[j][5] = fmaf(v, w1.y, acc[j][5]);
-          acc[j][6] = fmaf(v, w1.z, acc[j][6]); acc[j][7] = fmaf(v, w1.w, acc[j][7]);
+        for (int j = 0; j < kF7Seg; ++j) {
+          const float u = v[j + kx];
+          acc[j][0] = fmaf(u, w0.x, acc[j][0]); acc[j][1] = fmaf(u, w0.y, acc[j][1]);
+          acc[j][2] = fmaf(u, w0.z, acc[j][2]); acc[j][3] = fmaf(u, w0.w, acc[j][3]);
+          acc[j][4] = fmaf(u, w1.x, acc[j][4]); acc[j][5] = fmaf(u, w1.y, acc[j][5]);
+          acc[j][6] = fmaf(u, w1.z, acc[j][6]); acc[j][7] = fmaf(u, w1.w, acc[j][7]);
         }
       }
     }
+  if (!active) return;
 #pragma unroll
-  for (int j = 0; j < kF7PerThread; ++j) {
-    const int p = p0 + slot + kF7Slots * j;
-    if (p < p1) {
-      float4* o = reinterpret_cast<float4*>(out + ((size_t)b * H * W + p) * kF7Cout + grp * 8);
-      o[0] = make_float4(fmaxf(acc[j][0], 0.f), fmaxf(acc[j][1], 0.f), fmaxf(acc[j][2], 0.f), fmaxf(acc[j][3], 0.f));
-      o[1] = make_float4(fmaxf(acc[j][4], 0.f), fmaxf(acc[j][5], 0.f), fmaxf(acc[j][6], 0.f), fmaxf(acc[j][7], 0.f));
+  for (int j = 0; j < kF7Seg; ++j) {
+    if (x0 + j < W) {
+      float4* o = reinterpret_cast<float4*>(out + (((size_t)b * H + y) * W + x0 + j) * kF7Cout);
+      o[grp] = make_float4(fmaxf(acc[j][0], 0.f), fmaxf(acc[j][1], 0.f), fmaxf(acc[j][2], 0.f), fmaxf(acc[j][3], 0.f));
+      o[16 + grp] = make_float4(fmaxf(acc[j][4], 0.f), fmaxf(acc[j][5], 0.f), fmaxf(acc[j][6], 0.f), fmaxf(acc[j][7], 0.f));
     }
   }
 }
@@ -167,65 +191,90 @@ __global__ void __launch_bounds__(256) flow_out3x3_kernel(const float* __restric
 }
 
 // ---- flow head output in two steps -------------------------------------------------------------------------------
-constexpr int kTapPix = 128;     // pixels per CTA: 4 groups of 32 (one lane per pixel) x 4 channel quarters = 16 warps
+constexpr int kTapPix = 128;     // pixels per CTA: a lane owns 4 of them (l, l+32, l+64, l+96)
+constexpr int kTapSlices = 8;    // warps per CTA, each taking 1/8 of the input channels
 constexpr int kTapW = 20;        // floats per channel in the staged weights: 18 (tap, o) products padded to 5 float4
 
-__global__ void __launch_bounds__(512) flow_head_taps_kernel(const float* __restrict__ in,      // (pixels, C)
+// Weights are read from shared memory as warp-wide broadcasts; an LDS.128 costs the LSU 4 cycles however few distinct
+// addresses it has, so each weight vector has to feed many FMAs: 4 pixels per lane make that 5 loads per 72 FMAs.
+__global__ void __launch_bounds__(256) flow_head_taps_kernel(const float* __restrict__ in,      // (pixels, C)
                                                              const float* __restrict__ weight,  // (2, C, 3, 3)
                                                              float* __restrict__ taps,          // (pixels, 9, 2)
                                                              int pixels, int C) {
   extern __shared__ __align__(16) float smt[];
   float* sw = smt;                       // [C][20]
-  float* red = smt + (size_t)C * kTapW;  // [3][128][19] partial sums of channel quarters 1..3
-  for (int i = threadIdx.x; i < C * 18; i += 512) {
-    const int c = i / 18, n = i - c * 18;
-    sw[c * kTapW + n] = __ldg(weight + ((size_t)(n & 1) * C + c) * 9 + (n >> 1));
+  float* red = smt + (size_t)C * kTapW;  // [8 slices][128 * 18] partial sums
+  for (int i0 = threadIdx.x; i0 < C * 18; i0 += 4 * 256) {
+    float v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      const int ic = i < C * 18 ? i : 0;
+      const int c = ic / 18, n = ic - c * 18;
+      v[u] = __ldg(weight + ((size_t)(n & 1) * C + c) * 9 + (n >> 1));
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      if (i < C * 18) sw[(i / 18) * kTapW + i % 18] = v[u];
+    }
   }
   __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int quarter = warp >> 2, pl = (warp & 3) * 32 + lane;
-  const int p = blockIdx.x * kTapPix + pl;
-  const int pc = p < pixels ? p : pixels - 1;
-  const int cq = C >> 2;
-  const float4* src = reinterpret_cast<const float4*>(in + (size_t)pc * C + quarter * cq);
-  const float* wq = sw + (size_t)quarter * cq * kTapW;
-  float acc[kTapW];
+  const int slice = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int cs = C / kTapSlices;         // channels per slice, a multiple of 4
+  const int pbase = blockIdx.x * kTapPix;
+  const float4* src[4];
 #pragma unroll
-  for (int n = 0; n < kTapW; ++n) acc[n] = 0.f;
-  for (int c4 = 0; c4 < (cq >> 2); ++c4) {
-    const float4 v4 = __ldg(src + c4);
-    const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+  for (int q = 0; q < 4; ++q) {
+    const int p = min(pbase + lane + 32 * q, pixels - 1);
+    src[q] = reinterpret_cast<const float4*>(in + (size_t)p * C + slice * cs);
+  }
+  const float* wq = sw + (size_t)slice * cs * kTapW;
+  float acc[4][18];
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int n = 0; n < 18; ++n) acc[q][n] = 0.f;
+  float4 cur[4], nxt[4];
+#pragma unroll
+  for (int q = 0; q < 4; ++q) cur[q] = __ldg(src[q]);
+  const int n4 = cs >> 2;
+  for (int c4 = 0; c4 < n4; ++c4) {
+    if (c4 + 1 < n4) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) nxt[q] = __ldg(src[q] + c4 + 1);
+    }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float4* wv = reinterpret_cast<const float4*>(wq + (c4 * 4 + k) * kTapW);
+      float w[kTapW];
 #pragma unroll
       for (int j = 0; j < 5; ++j) {
-        const float4 w = wv[j];
-        acc[4 * j] = fmaf(v[k], w.x, acc[4 * j]);
-        acc[4 * j + 1] = fmaf(v[k], w.y, acc[4 * j + 1]);
-        if (j < 4) {   // the fifth vector carries products 16 and 17 only
-          acc[4 * j + 2] = fmaf(v[k], w.z, acc[4 * j + 2]);
-          acc[4 * j + 3] = fmaf(v[k], w.w, acc[4 * j + 3]);
-        }
+        const float4 t = wv[j];
+        w[4 * j] = t.x; w[4 * j + 1] = t.y; w[4 * j + 2] = t.z; w[4 * j + 3] = t.w;
+      }
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float v = k == 0 ? cur[q].x : (k == 1 ? cur[q].y : (k == 2 ? cur[q].z : cur[q].w));
+#pragma unroll
+        for (int n = 0; n < 18; ++n) acc[q][n] = fmaf(v, w[n], acc[q][n]);
       }
     }
-  }
-  if (quarter > 0) {
-    float* r = red + ((size_t)(quarter - 1) * kTapPix + pl) * 19;
 #pragma unroll
-    for (int n = 0; n < 18; ++n) r[n] = acc[n];
+    for (int q = 0; q < 4; ++q) cur[q] = nxt[q];
   }
+  float* r = red + (size_t)slice * (kTapPix * 18);
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int n = 0; n < 18; ++n) r[(lane + 32 * q) * 18 + n] = acc[q][n];
   __syncthreads();
-  if (quarter == 0 && p < pixels) {
+  const int n_out = min(kTapPix, pixels - pbase) * 18;
+  for (int o = threadIdx.x; o < n_out; o += 256) {
+    float t = 0.f;
 #pragma unroll
-    for (int q = 0; q < 3; ++q) {
-      const float* r = red + ((size_t)q * kTapPix + pl) * 19;
-#pragma unroll
-      for (int n = 0; n < 18; ++n) acc[n] += r[n];
-    }
-    float2* o = reinterpret_cast<float2*>(taps + (size_t)p * 18);
-#pragma unroll
-    for (int t = 0; t < 9; ++t) o[t] = make_float2(acc[2 * t], acc[2 * t + 1]);
+    for (int sl = 0; sl < kTapSlices; ++sl) t += red[sl * (kTapPix * 18) + o];
+    taps[(size_t)pbase * 18 + o] = t;
   }
 }
 
@@ -278,18 +327,18 @@ extern "C" int woft_flow_conv7x7_relu(const float* flow, const float* weight, co
   using namespace woft;
   WOFT_REQUIRE(flow && weight && bias && out_nhwc, "woft_flow_conv7x7_relu: null pointer");
   WOFT_REQUIRE(batch > 0 && height > 0 && width > 0 && batch < 65536, "woft_flow_conv7x7_relu: bad extent");
-  // runs of consecutive pixels: a multiple of 148 CTAs per image batch when the map is large enough, <= 112 pixels each
-  const int hw = height * width;
-  const int waves = ceil_div(hw * batch, kF7MaxRun * 148);
-  int run = ceil_div(hw, ceil_div(148 * waves, batch));
-  run = run < kF7Slots ? kF7Slots : (run > kF7MaxRun ? kF7MaxRun : run);
-  const int rows_max = (run - 1) / width + 2 + 6;   // rows a run can touch, plus the halo
-  const size_t smem = (size_t)(98 * kF7WStride + 2 * rows_max * (width + 6)) * sizeof(float);
+  // segments of 7 pixels, up to 16 per CTA, a multiple of 148 CTAs per batch when the map is large enough
+  const int segs_per_row = ceil_div(width, kF7Seg), total = segs_per_row * height;
+  const int waves = ceil_div(total * batch, kF7Slots * 148);
+  int spc = ceil_div(total, ceil_div(148 * waves, batch));
+  spc = spc < 1 ? 1 : (spc > kF7Slots ? kF7Slots : spc);
+  const int rows_max = (spc - 1) / segs_per_row + 2 + 6;   // rows the segments of a CTA can touch, plus the halo
+  const size_t smem = (size_t)(98 * kF7WStride + 2 * rows_max * (segs_per_row * kF7Seg + 6)) * sizeof(float);
   WOFT_REQUIRE(smem <= 200 * 1024, "woft_flow_conv7x7_relu: width %d needs more shared memory than a CTA has", width);
   WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_conv7x7_relu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  dim3 grid(ceil_div(hw, run), batch);
+  dim3 grid(ceil_div(total, spc), batch);
   flow_conv7x7_relu_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(flow, weight, bias, out_nhwc, height,
-                                                                                  width, run, rows_max);
+                                                                                  width, spc, rows_max);
   return launch_status("flow_conv7x7_relu_kernel");
 }
 
@@ -320,7 +369,7 @@ extern "C" int woft_flow_head_step(const float* in_nhwc, const float* weight, co
   using namespace woft;
   WOFT_REQUIRE(in_nhwc && weight && bias && scratch, "woft_flow_head_step: null pointer");
   WOFT_REQUIRE(batch > 0 && height > 0 && width > 0, "woft_flow_head_step: bad extent");
-  WOFT_REQUIRE(channels % 16 == 0 && channels <= 1024, "woft_flow_head_step: channels must be a multiple of 16, <= 1024");
+  WOFT_REQUIRE(channels % 32 == 0 && channels <= 1024, "woft_flow_head_step: channels must be a multiple of 32, <= 1024");
   WOFT_REQUIRE(delta_nchw || coords, "woft_flow_head_step: no output requested");
   WOFT_REQUIRE(!coords || coords0, "woft_flow_head_step: coords needs coords0");
   const long long pixels = (long long)batch * height * width;
@@ -329,9 +378,9 @@ extern "C" int woft_flow_head_step(const float* in_nhwc, const float* weight, co
     return fail(WOFT_ERR_WORKSPACE, "woft_flow_head_step: scratch too small");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   float* taps = static_cast<float*>(scratch);
-  const size_t smem = ((size_t)channels * kTapW + 3 * kTapPix * 19) * sizeof(float);
+  const size_t smem = ((size_t)channels * kTapW + kTapSlices * kTapPix * 18) * sizeof(float);
   WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_head_taps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  flow_head_taps_kernel<<<(unsigned)ceil_div((int)pixels, kTapPix), 512, smem, s>>>(in_nhwc, weight, taps, (int)pixels,
+  flow_head_taps_kernel<<<(unsigned)ceil_div((int)pixels, kTapPix), 256, smem, s>>>(in_nhwc, weight, taps, (int)pixels,
                                                                                    channels);
   flow_head_gather_kernel<<<(unsigned)ceil_div((int)pixels, 128), 128, 0, s>>>(taps, bias, batch, height, width, delta_nchw,
                                                                                coords, coords0, flow_nchw, flow_nhwc);

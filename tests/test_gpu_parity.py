@@ -299,6 +299,24 @@ def test_flow_wrapper_matches_reference_wrapper(golden, graph):
     assert np.abs(w2 - gw["flow_w"]).max() <= 5e-3
 
 
+def test_flow_wrapper_mixed_precision(golden):
+    """class_params.mixed_precision=True (optical_flow/raft.py:35): fp16 autocast where the reference has it.  No shipped
+    config sets it and the CPU oracle cannot autocast to fp16, so the check is against the fp32 golden flow with a
+    tolerance stated for half precision: mean EPE 0.1 px, weights 0.05."""
+    from types import SimpleNamespace
+    from woft_b200.optical_flow import RAFTWrapper
+    g, gw = golden("net_small"), golden("wrapper_small")
+    conf = SimpleNamespace(raft_type="weighted", model=None, seeded_weights=0, iters=12, padding_mode="nopad",
+                           class_params=SimpleNamespace(small=False, alternate_corr=False, mixed_precision=True))
+    wrapper = RAFTWrapper(conf, device=DEV)
+    assert wrapper.mixed_precision and not wrapper.fused
+    for _ in range(2):
+        src, dst, w = wrapper.compute_flow(g["img1_bgr"], g["img2_bgr"], mode="TC", do_sigmoid=True)
+    assert dst.dtype == torch.float32 and w.dtype == torch.float32
+    assert (dst.cpu() - torch.from_numpy(gw["tc_dst"])).norm(dim=0).mean().item() <= 0.1
+    assert np.abs(w.cpu().numpy() - gw["tc_w"]).max() <= 0.05
+
+
 def test_tracker_runs_and_masks_like_the_reference():
     from types import SimpleNamespace
     import cv2

@@ -150,6 +150,12 @@ class RAFTWrapper:
             # cuDNN's sm_100 convolution kernels are NHWC: keep weights and activations channels-last so it does not
             # wrap every convolution in a pair of layout-conversion kernels
             self.net = self.net.to(memory_format=torch.channels_last)
+        # class_params.mixed_precision (raft.py:35): the reference's fp16 autocast regions, honoured on the layer-by-layer
+        # mirror; the fused schedule computes in fp32 / TF32 only
+        self.mixed_precision = bool(_cfg(params, "mixed_precision", False))
+        self.net.mixed_precision = self.mixed_precision
+        if self.mixed_precision:
+            fused = self.fused = False
         # fused inference schedule (fast_net.py) unless the layer-by-layer mirror is asked for
         if fused and not channels_last:
             from .fast_net import FastWeightedRAFT

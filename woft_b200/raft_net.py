@@ -205,16 +205,28 @@ class WeightedRAFT(nn.Module):
         self.cnet = BasicEncoder(self.hidden_dim + self.context_dim, "batch")
         self.update_block = BasicUpdateBlock(self.corr_levels, self.corr_radius, self.hidden_dim)
         self.with_weights = with_weights
+        # class_params.mixed_precision (optical_flow/raft.py:35): fp16 autocast around the two encoders and the update
+        # block exactly where the reference has it (weighted_raft.py:204, 215, 233); the correlation, the coordinate
+        # arithmetic, the upsampling and the weight head stay fp32.  False in every shipped config.
+        self.mixed_precision = False
         if with_weights:
             self.weight_head = WeightHead(weight_head_structure, self.corr_levels)
+
+    def _autocast(self, device):
+        return torch.autocast(device_type=device.type, dtype=torch.float16,
+                              enabled=self.mixed_precision and device.type == "cuda")
 
     def encode(self, image1, image2):
         """weighted_raft.py:194-219: scale to [-1,1], feature maps of both frames, context of frame 1."""
         image1 = 2 * (image1 / 255.0) - 1.0   # memory format (NCHW or channels-last) is kept as given
         image2 = 2 * (image2 / 255.0) - 1.0
-        fmap1, fmap2 = self.fnet(torch.cat([image1, image2], dim=0)).float().chunk(2, dim=0)
-        net, inp = torch.split(self.cnet(image1), [self.hidden_dim, self.context_dim], dim=1)
-        return fmap1.contiguous(), fmap2.contiguous(), torch.tanh(net), torch.relu(inp)
+        with self._autocast(image1.device):
+            fmaps = self.fnet(torch.cat([image1, image2], dim=0))
+        fmap1, fmap2 = fmaps.float().chunk(2, dim=0)
+        with self._autocast(image1.device):
+            net, inp = torch.split(self.cnet(image1), [self.hidden_dim, self.context_dim], dim=1)
+            net, inp = torch.tanh(net), torch.relu(inp)
+        return fmap1.contiguous(), fmap2.contiguous(), net, inp
 
     def forward(self, image1, image2, iters=12, flow_init=None, test_mode=True, corr_block=None):
         if not test_mode:
@@ -233,9 +245,12 @@ class WeightedRAFT(nn.Module):
         up_mask = None
         for it in range(iters):
             corr = corr_fn(coords1)
-            net, up_mask, dflow = self.update_block(net, inp, corr, coords1 - coords0,
-                                                    need_mask=(it == iters - 1))
-            coords1 = coords1 + dflow
+            with self._autocast(image1.device):
+                net, up_mask, dflow = self.update_block(net, inp, corr, coords1 - coords0,
+                                                        need_mask=(it == iters - 1))
+            coords1 = coords1 + dflow   # fp32 + fp16 promotes to fp32, as in the reference
+        if up_mask is not None:
+            up_mask = up_mask.float()
         flow_low = coords1 - coords0
         flow_up = convex_upsample(flow_low, up_mask)
         if not self.with_weights:

@@ -7,6 +7,8 @@ pytracking/tracker/YAOF_tracker_single_control.py:57-170 (global branch):
   cv2 pre-warp (:89-95) -> RAFTWrapper.compute_flow 'TC' on CPU (optical_flow/raft.py:113-218) ->
   _mask_coords (:287-312) -> Sobol subsample (config :31-53) -> find_homography_nonhomogeneous_QR ->
   redet_success_fn (config :14-21) -> compose_H.
+`track_frame_local` is the branch taken when that test fails (:178-204, 314-327): flow from the previous frame,
+template mask warped into the previous frame, Sobol subsample, fit, composition with the previous homography.
 """
 import cv2
 import numpy as np
@@ -53,3 +55,21 @@ def track_frame(net, template_bgr, frame_bgr, template_mask, prewarp_H, iters=12
     ok = wo.redet_success(H, t_coords, c_coords)
     H_global = np.dot(H[0].double().numpy(), prewarp_H)
     return H_global / H_global[2, 2], ok, t_coords.shape[1]
+
+
+def track_frame_local(net, prev_bgr, frame_bgr, template_mask, prev_H2init, iters=12):
+    """The lost branch of YAOF_tracker_single_control.py:178-204.  Returns (H_local_cur2init (3,3) float64, number of
+    fitted correspondences)."""
+    h, w = frame_bgr.shape[:2]
+    p_coords, c_coords, weights = compute_flow_tc(net, prev_bgr, frame_bgr, iters)
+    # _mask_coords_flow (:314-327): the template mask seen from the previous frame, nearest-neighbour warp
+    prev_mask = cv2.warpPerspective(template_mask, np.linalg.inv(prev_H2init), (w, h), flags=cv2.INTER_NEAREST) > 0
+    keep = torch.from_numpy(prev_mask)[p_coords[1], p_coords[0]]
+    p_coords, c_coords, weights = p_coords[:, keep].float(), c_coords[:, keep], weights[:, keep]
+    pick = wo.sobol_subsample_mask(p_coords.shape[1])
+    if pick is not None:
+        p_coords, c_coords, weights = p_coords[:, pick], c_coords[:, pick], weights[:, pick]
+    H_flow = wo.find_homography_nonhomogeneous_QR(c_coords.T[None].contiguous(), p_coords.T[None].contiguous(), weights)
+    # compose_H(H_flow, prev_H2init) multiplies in reverse order (geom_utils.py:365-373)
+    H_local = np.dot(prev_H2init, H_flow[0].double().numpy())
+    return H_local / H_local[2, 2], p_coords.shape[1]

@@ -590,6 +590,44 @@ def test_tracked_frame_matches_cpu_pipeline():
         assert err <= 0.05, f"tracked-frame homography differs from the CPU pipeline by {err} px at the corners"
 
 
+def test_lost_branch_matches_cpu_pipeline():
+    """A frame whose global fit fails the inlier test (YAOF_tracker_single_control.py:167-204): the tracker must chain a
+    local homography from the previous frame.  The failure is forced through the config's own hook
+    (redet_success_fn), the local homography is compared with the oracle's restatement of that branch."""
+    from types import SimpleNamespace
+    from oracle import cpu_pipeline
+    from oracle.gen_golden import make_frames
+    from woft_b200 import tracker
+    from woft_b200.corr import CorrBlock
+    from woft_b200.optical_flow import RAFTWrapper
+    H, W = 256, 320
+    img0, img1 = make_frames(H, W, 33)
+    mask = np.zeros((H, W), np.uint8)
+    mask[48:208, 64:256] = 255
+    net = cpu_pipeline.make_net(0)
+    torch.set_num_threads(8)
+    flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False), model=None,
+                                seeded_weights=0, iters=12, padding_mode="nopad")
+    for device_prewarp in (False, True):
+        conf = tracker.default_config(flow_conf, device_prewarp=device_prewarp)
+        conf.fused_select = False                      # the fused path has the default success test built in
+        conf.redet_success_fn = lambda *a, **k: torch.zeros((), dtype=torch.bool, device=DEV)
+        flower = RAFTWrapper(flow_conf, device=DEV, corr_block=functools.partial(CorrBlock, mode="tf32x3"))
+        trk = tracker.PlanarTracker(conf, flower=flower)
+        trk.init(img0, mask)
+        H_gpu, meta = trk.track(img1)
+        assert meta.lost and meta.N_lost == 1 and not meta.global_H_success and trk.flow_passes == 2
+        H_cpu, n_cpu = cpu_pipeline.track_frame_local(net, img0, img1, mask, np.eye(3), 12)
+        err = wo.corner_error(torch.from_numpy(meta.H_local_cur2init), torch.from_numpy(H_cpu), W, H)
+        assert err <= 0.05, f"local-branch homography differs from the CPU pipeline by {err} px at the corners"
+        assert np.array_equal(H_gpu, meta.H_local_cur2init)
+        # second lost frame chains onto the first one's result and the pre-warp keeps using the last good homography
+        H2, meta2 = trk.track(img0)
+        assert meta2.N_lost == 2 and np.all(np.isfinite(H2))
+        H_cpu2, _ = cpu_pipeline.track_frame_local(net, img1, img0, mask, H_gpu, 12)
+        assert wo.corner_error(torch.from_numpy(H2), torch.from_numpy(H_cpu2), W, H) <= 0.1
+
+
 def test_fused_select_fit_check_matches_reference_pieces():
     """woft_select_correspondences + woft_homography_fit_n + woft_inlier_fraction against the oracle's restatement of
     _mask_coords, the Sobol subsampler, find_homography_nonhomogeneous_QR and redet_success_fn."""

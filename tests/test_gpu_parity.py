@@ -510,6 +510,58 @@ def test_thin_convolution_kernels():
         torch.backends.cudnn.allow_tf32 = old
 
 
+def test_thin_kernels_stay_inside_their_outputs():
+    """Outputs embedded in sentinel-filled buffers: nothing may be written before or after them (ragged shapes, where
+    tiles, row segments and pixel groups are partial)."""
+    from woft_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(12)
+    st = _lib.current_stream(torch.device(DEV))
+    PAD = 4096
+
+    def guarded(n):
+        big = torch.full((n + 2 * PAD,), 12345.0, device=DEV)
+        return big, big[PAD:PAD + n]
+
+    def intact(big, n):
+        return bool((big[:PAD] == 12345.0).all() and (big[PAD + n:] == 12345.0).all())
+
+    for (B, H, W) in ((1, 9, 7), (2, 17, 23), (1, 90, 160), (3, 16, 41)):
+        flow = (torch.randn((B, 2, H, W), generator=g) * 3).to(DEV)
+        w7 = (torch.randn((128, 2, 7, 7), generator=g) * 0.1).to(DEV)
+        b7 = torch.randn((128,), generator=g).to(DEV)
+        n = B * H * W * 128
+        big, out = guarded(n)
+        assert lib.woft_flow_conv7x7_relu(_lib.ptr(flow), _lib.ptr(w7), _lib.ptr(b7), B, H, W, _lib.ptr(out), st) == 0
+        want = F.relu(F.conv2d(flow, w7, b7, padding=3)).permute(0, 2, 3, 1).reshape(-1)
+        assert intact(big, n) and torch.allclose(out, want, atol=2e-5)
+
+        x = torch.randn((B, H, W, 64), generator=g).to(DEV)          # channels-last storage, C = 64
+        w3 = (torch.randn((2, 64, 3, 3), generator=g) * 0.05).to(DEV)
+        b3 = torch.randn((2,), generator=g).to(DEV)
+        nb = lib.woft_flow_head_scratch_bytes(B, H, W)
+        bigs, scratch = guarded(nb // 4)
+        bigd, delta = guarded(B * 2 * H * W)
+        bigc, coords = guarded(B * 2 * H * W)
+        bign, fn = guarded(B * 2 * H * W)
+        bigh, fh = guarded(B * 2 * H * W)
+        c0 = torch.randn((B, 2, H, W), generator=g).to(DEV)
+        coords.copy_(c0.reshape(-1))
+        rc = lib.woft_flow_head_step(_lib.ptr(x), _lib.ptr(w3), _lib.ptr(b3), B, H, W, 64, _lib.ptr(scratch), nb,
+                                     _lib.ptr(delta), _lib.ptr(coords), _lib.ptr(c0), _lib.ptr(fn), _lib.ptr(fh), st)
+        assert rc == 0
+        want = F.conv2d(x.permute(0, 3, 1, 2), w3, b3, padding=1)
+        assert all(intact(b_, n_) for b_, n_ in ((bigs, nb // 4), (bigd, B * 2 * H * W), (bigc, B * 2 * H * W),
+                                                  (bign, B * 2 * H * W), (bigh, B * 2 * H * W)))
+        assert torch.allclose(delta.view(B, 2, H, W), want, atol=5e-5)
+        assert torch.allclose(coords.view(B, 2, H, W), c0 + want, atol=1e-4)
+        assert torch.allclose(fh.view(B, H, W, 2).permute(0, 3, 1, 2), fn.view(B, 2, H, W))
+    with pytest.raises(AssertionError):   # channel count the product kernel cannot split
+        from woft_b200 import fast_net
+        fast_net.flow_head_step(torch.randn((1, 24, 8, 8), device=DEV), torch.randn((2, 24, 3, 3), device=DEV),
+                                torch.randn((2,), device=DEV))
+
+
 def test_convex_upsample_kernel():
     from woft_b200.fast_net import convex_upsample_both
     from woft_b200.raft_net import convex_upsample

@@ -187,7 +187,7 @@ int woft_flow_out3x3(const float* in_nhwc, const float* weight, const float* bia
 /* FlowHead.conv2 and the step of the refinement loop that follows it (raft_core/weighted_raft.py:244-246:
  * coords1 = coords1 + delta_flow; next iteration's flow = coords1 - coords0) in two launches that read every input
  * value once: per input pixel the 18 (tap, output) products, then per output pixel the sum of 9 shifted products.
- *   in (B,H,W,C) channels-last, C a multiple of 32; weight (2,C,3,3); bias (2)
+ *   in (B,H,W,C) channels-last, 16-byte aligned, C a multiple of 32 and <= 320; weight (2,C,3,3); bias (2)
  *   scratch: woft_flow_head_scratch_bytes(B,H,W) bytes
  *   delta_nchw (B,2,H,W) or NULL: the convolution's result, as woft_flow_out3x3 gives it
  *   coords (B,2,H,W) or NULL: updated IN PLACE by the delta; with it coords0 (B,2,H,W) is required and

@@ -15,6 +15,7 @@
 //                              the 9 shifted taps + bias, fused with the coordinate update that follows the flow
 //                              head in the refinement loop (weighted_raft.py:244-246: coords1 = coords1 + delta_flow).
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace woft {
 
@@ -78,14 +79,14 @@ __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __r
   const bool active = slot < segs_per_cta && s0 + slot < s1;
   const int seg = active ? s0 + slot : s0;       // idle slots recompute the first segment and store nothing
   const int y = seg / segs_per_row, x0 = (seg - y * segs_per_row) * kF7Seg;
-  float acc[kF7Seg][8];
+  unsigned long long acc[kF7Seg][4];   // 8 channels as 4 packed pairs: FFMA2 halves the issue slots of the 5488 FMAs
   {
     const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias) + grp);
     const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias) + 16 + grp);
 #pragma unroll
     for (int j = 0; j < kF7Seg; ++j) {
-      acc[j][0] = b0.x; acc[j][1] = b0.y; acc[j][2] = b0.z; acc[j][3] = b0.w;
-      acc[j][4] = b1.x; acc[j][5] = b1.y; acc[j][6] = b1.z; acc[j][7] = b1.w;
+      acc[j][0] = ptx::pack_f32x2(b0.x, b0.y); acc[j][1] = ptx::pack_f32x2(b0.z, b0.w);
+      acc[j][2] = ptx::pack_f32x2(b1.x, b1.y); acc[j][3] = ptx::pack_f32x2(b1.z, b1.w);
     }
   }
   for (int ci = 0; ci < 2; ++ci)
@@ -101,13 +102,15 @@ __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __r
       for (int kx = 0; kx < 7; ++kx) {
         const float4 w0 = wrow[kx * (kF7WStride / 4)];
         const float4 w1 = wrow[kx * (kF7WStride / 4) + 16];
+        const unsigned long long p0 = ptx::pack_f32x2(w0.x, w0.y), p1 = ptx::pack_f32x2(w0.z, w0.w);
+        const unsigned long long p2 = ptx::pack_f32x2(w1.x, w1.y), p3 = ptx::pack_f32x2(w1.z, w1.w);
 #pragma unroll
         for (int j = 0; j < kF7Seg; ++j) {
           const float u = v[j + kx];
-          acc[j][0] = fmaf(u, w0.x, acc[j][0]); acc[j][1] = fmaf(u, w0.y, acc[j][1]);
-          acc[j][2] = fmaf(u, w0.z, acc[j][2]); acc[j][3] = fmaf(u, w0.w, acc[j][3]);
-          acc[j][4] = fmaf(u, w1.x, acc[j][4]); acc[j][5] = fmaf(u, w1.y, acc[j][5]);
-          acc[j][6] = fmaf(u, w1.z, acc[j][6]); acc[j][7] = fmaf(u, w1.w, acc[j][7]);
+          ptx::ffma2_bcast(acc[j][0], u, p0);
+          ptx::ffma2_bcast(acc[j][1], u, p1);
+          ptx::ffma2_bcast(acc[j][2], u, p2);
+          ptx::ffma2_bcast(acc[j][3], u, p3);
         }
       }
     }
@@ -115,9 +118,12 @@ __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __r
 #pragma unroll
   for (int j = 0; j < kF7Seg; ++j) {
     if (x0 + j < W) {
+      float a[8];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) ptx::unpack_f32x2(acc[j][k], a[2 * k], a[2 * k + 1]);
       float4* o = reinterpret_cast<float4*>(out + (((size_t)b * H + y) * W + x0 + j) * kF7Cout);
-      o[grp] = make_float4(fmaxf(acc[j][0], 0.f), fmaxf(acc[j][1], 0.f), fmaxf(acc[j][2], 0.f), fmaxf(acc[j][3], 0.f));
-      o[16 + grp] = make_float4(fmaxf(acc[j][4], 0.f), fmaxf(acc[j][5], 0.f), fmaxf(acc[j][6], 0.f), fmaxf(acc[j][7], 0.f));
+      o[grp] = make_float4(fmaxf(a[0], 0.f), fmaxf(a[1], 0.f), fmaxf(a[2], 0.f), fmaxf(a[3], 0.f));
+      o[16 + grp] = make_float4(fmaxf(a[4], 0.f), fmaxf(a[5], 0.f), fmaxf(a[6], 0.f), fmaxf(a[7], 0.f));
     }
   }
 }
@@ -194,16 +200,32 @@ __global__ void __launch_bounds__(256) flow_out3x3_kernel(const float* __restric
 constexpr int kTapPix = 128;     // pixels per CTA: a lane owns 4 of them (l, l+32, l+64, l+96)
 constexpr int kTapSlices = 8;    // warps per CTA, each taking 1/8 of the input channels
 constexpr int kTapW = 20;        // floats per channel in the staged weights: 18 (tap, o) products padded to 5 float4
+constexpr int kTapMaxC = 320;    // weights + a 128-pixel tile of C + 4 floats per row must fit in shared memory
 
-// Weights are read from shared memory as warp-wide broadcasts; an LDS.128 costs the LSU 4 cycles however few distinct
-// addresses it has, so each weight vector has to feed many FMAs: 4 pixels per lane make that 5 loads per 72 FMAs.
+// The CTA's 128 input pixels are one contiguous block of global memory (channels-last), brought in by 128 bulk copies
+// of one pixel row each into rows of C + 4 floats: with that pitch a lane-per-pixel LDS.128 is conflict free.  Weights
+// are read as warp-wide broadcasts; an LDS.128 costs the LSU 4 cycles however few distinct addresses it has, so each
+// weight vector has to feed many FMAs: 4 pixels per lane make that 5 loads per 72 FMAs.
 __global__ void __launch_bounds__(256) flow_head_taps_kernel(const float* __restrict__ in,      // (pixels, C)
                                                              const float* __restrict__ weight,  // (2, C, 3, 3)
                                                              float* __restrict__ taps,          // (pixels, 9, 2)
                                                              int pixels, int C) {
-  extern __shared__ __align__(16) float smt[];
-  float* sw = smt;                       // [C][20]
-  float* red = smt + (size_t)C * kTapW;  // [8 slices][128 * 18] partial sums
+  extern __shared__ __align__(128) float smt[];
+  __shared__ __align__(8) uint64_t bar;
+  float* sw = smt;                        // [C][20]
+  float* tile = smt + (size_t)C * kTapW;  // [128][C + 4]; reused as [8 slices][128 * 18] partial sums afterwards
+  const int pitch = C + 4;
+  const int pbase = blockIdx.x * kTapPix;
+  const int n_pix = min(kTapPix, pixels - pbase);
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(&bar, 1);
+    ptx::fence_mbar_init();
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) ptx::mbar_arrive_expect_tx(&bar, uint32_t(n_pix) * uint32_t(C) * 4u);
+  __syncthreads();   // the expectation is posted before any copy can complete
+  if (threadIdx.x < n_pix)
+    ptx::bulk_load_1d(tile + (size_t)threadIdx.x * pitch, in + (size_t)(pbase + threadIdx.x) * C, uint32_t(C) * 4u, &bar);
   for (int i0 = threadIdx.x; i0 < C * 18; i0 += 4 * 256) {
     float v[4];
 #pragma unroll
@@ -220,57 +242,52 @@ __global__ void __launch_bounds__(256) flow_head_taps_kernel(const float* __rest
     }
   }
   __syncthreads();
+  for (unsigned spins = 0; !ptx::mbar_try_wait(&bar, 0); ++spins)
+    if (spins > (1u << 24)) __trap();   // a copy that never lands must end the kernel, not hang the device
   const int slice = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int cs = C / kTapSlices;         // channels per slice, a multiple of 4
-  const int pbase = blockIdx.x * kTapPix;
-  const float4* src[4];
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    const int p = min(pbase + lane + 32 * q, pixels - 1);
-    src[q] = reinterpret_cast<const float4*>(in + (size_t)p * C + slice * cs);
-  }
   const float* wq = sw + (size_t)slice * cs * kTapW;
-  float acc[4][18];
+  const float* tq = tile + (size_t)lane * pitch + slice * cs;   // rows of pixels beyond n_pix hold stale data: never stored
+  unsigned long long acc[4][9];   // (tap, o = 0 / 1) pairs, packed for FFMA2
 #pragma unroll
   for (int q = 0; q < 4; ++q)
 #pragma unroll
-    for (int n = 0; n < 18; ++n) acc[q][n] = 0.f;
-  float4 cur[4], nxt[4];
+    for (int n = 0; n < 9; ++n) acc[q][n] = 0ull;
+  for (int c4 = 0; c4 < (cs >> 2); ++c4) {
+    float4 x[4];
 #pragma unroll
-  for (int q = 0; q < 4; ++q) cur[q] = __ldg(src[q]);
-  const int n4 = cs >> 2;
-  for (int c4 = 0; c4 < n4; ++c4) {
-    if (c4 + 1 < n4) {
-#pragma unroll
-      for (int q = 0; q < 4; ++q) nxt[q] = __ldg(src[q] + c4 + 1);
-    }
+    for (int q = 0; q < 4; ++q) x[q] = *reinterpret_cast<const float4*>(tq + (size_t)(32 * q) * pitch + c4 * 4);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
       const float4* wv = reinterpret_cast<const float4*>(wq + (c4 * 4 + k) * kTapW);
-      float w[kTapW];
+      unsigned long long w[10];
 #pragma unroll
       for (int j = 0; j < 5; ++j) {
         const float4 t = wv[j];
-        w[4 * j] = t.x; w[4 * j + 1] = t.y; w[4 * j + 2] = t.z; w[4 * j + 3] = t.w;
+        w[2 * j] = ptx::pack_f32x2(t.x, t.y);
+        w[2 * j + 1] = ptx::pack_f32x2(t.z, t.w);
       }
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const float v = k == 0 ? cur[q].x : (k == 1 ? cur[q].y : (k == 2 ? cur[q].z : cur[q].w));
+        const float v = k == 0 ? x[q].x : (k == 1 ? x[q].y : (k == 2 ? x[q].z : x[q].w));
 #pragma unroll
-        for (int n = 0; n < 18; ++n) acc[q][n] = fmaf(v, w[n], acc[q][n]);
+        for (int n = 0; n < 9; ++n) ptx::ffma2_bcast(acc[q][n], v, w[n]);
       }
     }
-#pragma unroll
-    for (int q = 0; q < 4; ++q) cur[q] = nxt[q];
   }
+  __syncthreads();   // every warp is done with the tile: its memory now takes the partial sums
+  float* red = tile;
   float* r = red + (size_t)slice * (kTapPix * 18);
 #pragma unroll
   for (int q = 0; q < 4; ++q)
 #pragma unroll
-    for (int n = 0; n < 18; ++n) r[(lane + 32 * q) * 18 + n] = acc[q][n];
+    for (int n = 0; n < 9; ++n) {
+      float lo, hi;
+      ptx::unpack_f32x2(acc[q][n], lo, hi);
+      *reinterpret_cast<float2*>(r + (lane + 32 * q) * 18 + 2 * n) = make_float2(lo, hi);
+    }
   __syncthreads();
-  const int n_out = min(kTapPix, pixels - pbase) * 18;
-  for (int o = threadIdx.x; o < n_out; o += 256) {
+  for (int o = threadIdx.x; o < n_pix * 18; o += 256) {
     float t = 0.f;
 #pragma unroll
     for (int sl = 0; sl < kTapSlices; ++sl) t += red[sl * (kTapPix * 18) + o];
@@ -369,7 +386,8 @@ extern "C" int woft_flow_head_step(const float* in_nhwc, const float* weight, co
   using namespace woft;
   WOFT_REQUIRE(in_nhwc && weight && bias && scratch, "woft_flow_head_step: null pointer");
   WOFT_REQUIRE(batch > 0 && height > 0 && width > 0, "woft_flow_head_step: bad extent");
-  WOFT_REQUIRE(channels % 32 == 0 && channels <= 1024, "woft_flow_head_step: channels must be a multiple of 32, <= 1024");
+  WOFT_REQUIRE(channels % 32 == 0 && channels <= kTapMaxC, "woft_flow_head_step: channels must be a multiple of 32, <= 320");
+  WOFT_REQUIRE(reinterpret_cast<uintptr_t>(in_nhwc) % 16 == 0, "woft_flow_head_step: input must be 16-byte aligned");
   WOFT_REQUIRE(delta_nchw || coords, "woft_flow_head_step: no output requested");
   WOFT_REQUIRE(!coords || coords0, "woft_flow_head_step: coords needs coords0");
   const long long pixels = (long long)batch * height * width;
@@ -378,7 +396,8 @@ extern "C" int woft_flow_head_step(const float* in_nhwc, const float* weight, co
     return fail(WOFT_ERR_WORKSPACE, "woft_flow_head_step: scratch too small");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   float* taps = static_cast<float*>(scratch);
-  const size_t smem = ((size_t)channels * kTapW + kTapSlices * kTapPix * 18) * sizeof(float);
+  const size_t tile_floats = (size_t)kTapPix * (channels + 4), red_floats = (size_t)kTapSlices * kTapPix * 18;
+  const size_t smem = ((size_t)channels * kTapW + (tile_floats > red_floats ? tile_floats : red_floats)) * sizeof(float);
   WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_head_taps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   flow_head_taps_kernel<<<(unsigned)ceil_div((int)pixels, kTapPix), 256, smem, s>>>(in_nhwc, weight, taps, (int)pixels,
                                                                                    channels);

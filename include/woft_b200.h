@@ -263,6 +263,13 @@ int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int hw, int chan
                                      float* y, void* scratch, size_t scratch_bytes, void* stream);
 int woft_add_relu(const float* a, const float* b, long long n, float* y, void* stream);
 
+/* The flow network's input from the two uint8 frames in one launch: BGR -> RGB, 2 * (v / 255) - 1
+ * (pytracking/optical_flow/raft.py:113-120, raft_core/weighted_raft.py:197-198), both frames stacked as the batch the
+ * feature encoder takes (extractor.py:171-174), channels-last.
+ *   img1_bgr, img2_bgr (H,W,3) uint8 -> out (2,H,W,3) fp32, i.e. a (2,3,H,W) tensor in channels-last memory format */
+int woft_images_to_input(const uint8_t* img1_bgr, const uint8_t* img2_bgr, int height, int width, float* out_nhwc,
+                         void* stream);
+
 #ifdef __cplusplus
 }
 #endif

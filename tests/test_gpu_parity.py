@@ -407,6 +407,31 @@ def test_fused_schedule_matches_layer_by_layer(golden):
     assert ref_epe <= 0.01, f"fused schedule vs reference network: mean EPE {ref_epe} px"
 
 
+def test_u8_input_path_is_the_float_path(golden):
+    """woft_images_to_input against the torch expressions it replaces (bit for bit), and the fused schedule fed with
+    uint8 frames against the same schedule fed the reference's way."""
+    from woft_b200 import _lib
+    from woft_b200.fast_net import FastWeightedRAFT
+    from woft_b200.raft_net import WeightedRAFT, seeded_state_dict
+    g = golden("net_small")
+    a = torch.from_numpy(g["img1_bgr"]).to(DEV)
+    b = torch.from_numpy(g["img2_bgr"]).to(DEV)
+    H, W, _ = a.shape
+    pair = torch.empty((2, 3, H, W), device=DEV).contiguous(memory_format=torch.channels_last)
+    rc = _lib.load().woft_images_to_input(_lib.ptr(a), _lib.ptr(b), H, W, _lib.ptr(pair),
+                                          _lib.current_stream(torch.device(DEV)))
+    assert rc == 0
+    f = [t.flip(-1).permute(2, 0, 1).float()[None] for t in (a, b)]
+    want = torch.cat([2 * (t / 255.0) - 1.0 for t in f], dim=0)
+    assert torch.equal(pair, want)
+    net = WeightedRAFT().eval()
+    net.load_state_dict(seeded_state_dict(net, 0))
+    fast = FastWeightedRAFT(net.to(DEV).requires_grad_(False))
+    out_f = fast(f[0], f[1], iters=4)
+    out_u = fast.run_u8(a, b, iters=4)
+    assert torch.equal(out_f[1], out_u[1]) and torch.equal(out_f[4], out_u[4])
+
+
 def test_device_prewarp_matches_opencv():
     """woft_warp_perspective_u8 against cv2.warpPerspective (YAOF_tracker_single_control.py:89-95)."""
     import cv2

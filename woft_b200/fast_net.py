@@ -437,12 +437,34 @@ class FastWeightedRAFT:
 
     @torch.no_grad()
     def __call__(self, image1, image2, iters=12, flow_init=None, test_mode=True, corr_block=None):
+        image1 = 2 * (image1 / 255.0) - 1.0
+        image2 = 2 * (image2 / 255.0) - 1.0
+        return self._run(torch.cat([image1, image2], dim=0), iters, flow_init, corr_block)
+
+    @torch.no_grad()
+    def run_u8(self, img1_bgr, img2_bgr, iters=12, flow_init=None, test_mode=True, corr_block=None):
+        """The same pass from two (H,W,3) uint8 BGR device tensors: one kernel (woft_images_to_input) forms the scaled
+        RGB pair in channels-last memory instead of flips, casts, three scalings per image, a cat and layout copies."""
+        _lib.require_cuda(img1_bgr, img2_bgr)
+        if img1_bgr.dtype != torch.uint8 or img1_bgr.shape != img2_bgr.shape or img1_bgr.dim() != 3 \
+                or img1_bgr.shape[2] != 3:
+            raise AssertionError("run_u8 takes two (H,W,3) uint8 tensors of equal shape")
+        H, W, _ = img1_bgr.shape
+        img1_bgr, img2_bgr = img1_bgr.contiguous(), img2_bgr.contiguous()
+        pair = torch.empty((2, 3, H, W), device=img1_bgr.device, dtype=torch.float32, memory_format=torch.channels_last)
+        with torch.cuda.device(pair.device):
+            rc = _lib.load().woft_images_to_input(_lib.ptr(img1_bgr), _lib.ptr(img2_bgr), H, W, _lib.ptr(pair),
+                                                  _lib.current_stream(pair.device))
+        _lib.check(rc, "woft_images_to_input")
+        return self._run(pair, iters, flow_init, corr_block)
+
+    def _run(self, images, iters, flow_init, corr_block):
+        """`images`: (2B,3,H,W), first the B source frames then the B target frames, scaled to [-1, 1]."""
         net_ = self.net
         if corr_block is None:
             from .corr import CorrBlock as corr_block
-        image1 = 2 * (image1 / 255.0) - 1.0
-        image2 = 2 * (image2 / 255.0) - 1.0
-        fmap1, fmap2 = self._features(torch.cat([image1, image2], dim=0)).chunk(2, dim=0)
+        image1 = images[:images.shape[0] // 2]
+        fmap1, fmap2 = self._features(images).chunk(2, dim=0)
         corr_fn = corr_block(fmap1.contiguous(), fmap2.contiguous(), num_levels=net_.corr_levels, radius=net_.corr_radius)
         net, inp = torch.split(self._context(image1), [net_.hidden_dim, net_.context_dim], dim=1)
         net, inp = torch.tanh(net), torch.relu(inp)

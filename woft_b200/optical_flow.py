@@ -160,8 +160,10 @@ class RAFTWrapper:
         if fused and not channels_last:
             from .fast_net import FastWeightedRAFT
             self._run = FastWeightedRAFT(self.net)
+            self._u8_input = True
         else:
             self._run = self.net
+            self._u8_input = False
         self.iters = int(_cfg(config, "iters", 12))
         self.use_cuda_graph = use_cuda_graph
         self.corr_block = corr_block
@@ -216,11 +218,13 @@ class RAFTWrapper:
         """uint8 BGR (H,W,3) -> float RGB (1,3,H,W) on the device (raft.py:113-120, conversion moved to the device)."""
         return self.upload_u8(img, slot).flip(-1).permute(2, 0, 1).float()[None]
 
-    def _forward(self, src, dst):
+    def _forward(self, src, dst, u8=False):
+        """`u8`: src / dst are (H,W,3) uint8 BGR device tensors and the fused schedule converts them itself."""
         kwargs = dict(iters=self.iters, test_mode=True, corr_block=self.corr_block)
+        run = self._run.run_u8 if u8 else self._run
         if not self.use_cuda_graph:
-            return self._run(src, dst, **kwargs)
-        key = tuple(src.shape)
+            return run(src, dst, **kwargs)
+        key = (u8,) + tuple(src.shape)
         entry = self._graphs.get(key)
         if entry is None:
             s_in, d_in = torch.empty_like(src), torch.empty_like(dst)
@@ -230,11 +234,11 @@ class RAFTWrapper:
             side.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(side):  # warm-up outside capture: cuDNN autotune, workspace allocation
                 for _ in range(2):
-                    self._run(s_in, d_in, **kwargs)
+                    run(s_in, d_in, **kwargs)
             torch.cuda.current_stream(self.device).wait_stream(side)
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph):
-                out = self._run(s_in, d_in, **kwargs)
+                out = run(s_in, d_in, **kwargs)
             entry = (graph, s_in, d_in, out)
             self._graphs[key] = entry
         graph, s_in, d_in, out = entry
@@ -251,15 +255,21 @@ class RAFTWrapper:
         assert mode in ["flow", "TC"]
         assert src_img.shape == dst_img.shape
         with torch.cuda.device(self.device):
-            src = self._upload(src_img, 0)
-            dst = self._upload(dst_img, 1)
             padding_mode = _cfg(self.C, "padding_mode", "nopad")
             if padding_mode not in _PADDERS:
                 raise ValueError(f"invalid padding_mode '{padding_mode}'")
-            padder = _PADDERS[padding_mode](dst.shape)
-            src, dst = padder.pad(src, dst)
-            fmt = torch.channels_last if self.channels_last else torch.contiguous_format
-            out = self._forward(src.contiguous(memory_format=fmt), dst.contiguous(memory_format=fmt))
+            h_img, w_img = src_img.shape[:2]
+            if self._u8_input and padding_mode == "nopad" and h_img % 8 == 0 and w_img % 8 == 0:
+                # nothing to pad: the uint8 frames go to the fused schedule as they are (one conversion kernel)
+                padder = _PADDERS[padding_mode]((1, 3, h_img, w_img))
+                out = self._forward(self.upload_u8(src_img, 0), self.upload_u8(dst_img, 1), u8=True)
+            else:
+                src = self._upload(src_img, 0)
+                dst = self._upload(dst_img, 1)
+                padder = _PADDERS[padding_mode](dst.shape)
+                src, dst = padder.pad(src, dst)
+                fmt = torch.channels_last if self.channels_last else torch.contiguous_format
+                out = self._forward(src.contiguous(memory_format=fmt), dst.contiguous(memory_format=fmt))
             if self.raft_type == "orig":
                 flow_up, weights_up = out[1], None
             else:

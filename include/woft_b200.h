@@ -270,6 +270,13 @@ int woft_add_relu(const float* a, const float* b, long long n, float* y, void* s
 int woft_images_to_input(const uint8_t* img1_bgr, const uint8_t* img2_bgr, int height, int width, float* out_nhwc,
                          void* stream);
 
+/* First layer of the two encoders (raft_core/extractor.py:131, 171-178): 7x7, stride 2, pad 3, 3 -> 64 channels, as an
+ * implicit GEMM on the tensor cores (mma.sync, TF32 operands rounded to nearest, fp32 accumulation).
+ *   in (B,H,W,3) fp32 channels-last; weight (64,3,7,7); bias (64) or NULL; relu != 0 applies ReLU
+ *   -> out (B,(H-1)/2+1,(W-1)/2+1,64) fp32 channels-last */
+int woft_stem_conv7x7(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
+                      int relu, float* out_nhwc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

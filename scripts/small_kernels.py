@@ -31,7 +31,12 @@ buf1 = torch.zeros((B, 384, H, W), device=dev).contiguous(memory_format=cl)
 buf2 = torch.zeros_like(buf1)
 big = torch.empty(64 << 20, device=dev)  # 256 MiB, flushes L2 between timed launches
 
+img2 = (torch.rand((2, 3, 720, 1280), generator=g) * 2 - 1).to(dev).contiguous(memory_format=cl)
+wst, bst = (torch.randn((64, 3, 7, 7), generator=g) * 0.05).to(dev), torch.randn((64,), generator=g).to(dev)
+
 cases = {
+    "stem_conv7x7 pair (fnet)": lambda: fast_net.stem_conv7x7(img2, wst),
+    "stem_conv7x7 one frame + bias + relu": lambda: fast_net.stem_conv7x7(img2[:1], wst, bst, relu=True),
     "flow_conv7x7_relu": lambda: fast_net.flow_conv7x7_relu(flow, w7, b7),
     "flow_out3x3 (one launch)": lambda: fast_net.flow_out3x3(x256, w3, b3),
     "flow_head_step (taps + gather)": lambda: fast_net.flow_head_step(x256, w3, b3, coords=coords, coords0=c0,

@@ -587,6 +587,28 @@ def test_thin_kernels_stay_inside_their_outputs():
                                 torch.randn((2,), device=DEV))
 
 
+def test_stem_convolution_kernel():
+    """woft_stem_conv7x7 (TF32 tensor cores) against the fp32 convolution: the error of 147 products with operands
+    rounded to 11 bits, 1e-3 at these magnitudes; ragged sizes exercise the partial tiles and the zero padding."""
+    from woft_b200 import fast_net
+    g = torch.Generator().manual_seed(14)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        for (B, H, W) in ((1, 64, 96), (2, 45, 83), (3, 720, 1280), (1, 17, 9)):
+            x = (torch.rand((B, 3, H, W), generator=g) * 2 - 1).to(DEV).contiguous(memory_format=torch.channels_last)
+            w = (torch.randn((64, 3, 7, 7), generator=g) * 0.05).to(DEV)
+            b = torch.randn((64,), generator=g).to(DEV)
+            want = F.conv2d(x, w, None, stride=2, padding=3)
+            got = fast_net.stem_conv7x7(x, w)
+            assert got.shape == want.shape and got.is_contiguous(memory_format=torch.channels_last)
+            assert (got - want).abs().max().item() <= 2e-3
+            got = fast_net.stem_conv7x7(x, w, b, relu=True)
+            assert (got - F.relu(want + b.view(1, -1, 1, 1))).abs().max().item() <= 2e-3
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+
+
 def test_convex_upsample_kernel():
     from woft_b200.fast_net import convex_upsample_both
     from woft_b200.raft_net import convex_upsample

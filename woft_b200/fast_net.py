@@ -15,6 +15,8 @@ concatenations and the three-pass instance norm around the cuDNN convolutions (p
 
 Results agree with the layer-by-layer schedule to fp32 rounding (tests/test_gpu_parity.py).
 """
+import os
+
 import torch
 import torch.nn.functional as F
 
@@ -155,6 +157,21 @@ def flow_out3x3(x_cl, weight, bias):
     return out
 
 
+def stem_conv7x7(x_cl, weight, bias=None, relu=False):
+    """channels-last (B,3,H,W) -> 7x7 stride-2 pad-3 convolution to 64 channels, channels-last; woft_stem_conv7x7
+    (TF32 tensor-core implicit GEMM).  `weight` is the (64,3,7,7) tensor in its plain contiguous layout."""
+    x_cl = _cl(x_cl)
+    B, C, H, W = x_cl.shape
+    if C != 3 or tuple(weight.shape) != (64, 3, 7, 7) or not weight.is_contiguous():
+        raise AssertionError("stem_conv7x7 takes a 3-channel input and a contiguous (64,3,7,7) weight")
+    out = _empty_cl(B, 64, (H - 1) // 2 + 1, (W - 1) // 2 + 1, x_cl)
+    with torch.cuda.device(x_cl.device):
+        rc = _lib.load().woft_stem_conv7x7(_lib.ptr(x_cl), _lib.ptr(weight), _lib.ptr(bias), B, H, W, int(relu),
+                                           _lib.ptr(out), _lib.current_stream(x_cl.device))
+    _lib.check(rc, "woft_stem_conv7x7")
+    return out
+
+
 def flow_head_step(x_cl, weight, bias, coords=None, coords0=None, flow_nchw=None, flow_nhwc=None, want_delta=False):
     """FlowHead.conv2 on a channels-last (B,C,H,W) tensor; woft_flow_head_step.  With `coords` the refinement step is
     fused: coords += delta in place, flow_nchw / flow_nhwc (preallocated, optional) = coords - coords0.  Returns the
@@ -219,6 +236,8 @@ class FastWeightedRAFT:
             # channels-last copies of the update block's weights: with NHWC activations cuDNN's sm_100 kernels run
             # without the NCHW<->NHWC conversion kernels that otherwise wrap every convolution
             self.nhwc = nhwc_update
+            # both encoders' 3-channel first layer through woft_stem_conv7x7 instead of cuDNN's sm_80 fallback
+            self.own_stem = os.environ.get("WOFT_OWN_STEM", "1") == "1"
             if nhwc_update:
                 fn = net.fnet
                 self.fw = {"stem": _cl(fn.conv1.weight), "out": (_cl(fn.conv2.weight), fn.conv2.bias), "blocks": []}
@@ -228,6 +247,7 @@ class FastWeightedRAFT:
                                                   "stride": blk.conv1.stride,
                                                   "down": _cl(blk.downsample[0].weight) if blk.downsample is not None else None})
                 c = self.cnet  # folded context-encoder weights, channels-last as well
+                c["stem_plain"] = (c["stem"][0].contiguous(), c["stem"][1].contiguous())  # for woft_stem_conv7x7
                 c["stem"] = (_cl(c["stem"][0]), c["stem"][1])
                 c["out"] = (_cl(c["out"][0]), c["out"][1])
                 for d in c["blocks"]:
@@ -283,7 +303,10 @@ class FastWeightedRAFT:
         c = self.cnet
         if self.nhwc:
             x = _cl(x)
-        x = _conv_relu(x, *c["stem"], stride=(2, 2), padding=(3, 3))
+        if self.nhwc and self.own_stem:
+            x = stem_conv7x7(x, *c["stem_plain"], relu=True)
+        else:
+            x = _conv_relu(x, *c["stem"], stride=(2, 2), padding=(3, 3))
         for d in c["blocks"]:
             y = _conv_relu(x, *d["c1"], stride=d["stride"], padding=(1, 1))
             y = _conv_relu(y, *d["c2"], padding=(1, 1))
@@ -311,7 +334,8 @@ class FastWeightedRAFT:
     def _features_nhwc(self, x):
         """Same encoder with channels-last activations and weights (no cuDNN layout conversions)."""
         w = self.fw
-        x = instance_norm_relu_nhwc(F.conv2d(_cl(x), w["stem"], None, stride=2, padding=3))
+        x = instance_norm_relu_nhwc(stem_conv7x7(x, self.net.fnet.conv1.weight) if self.own_stem else
+                                    F.conv2d(_cl(x), w["stem"], None, stride=2, padding=3))
         for d in w["blocks"]:
             y = instance_norm_relu_nhwc(F.conv2d(x, d["c1"], None, stride=d["stride"], padding=1))
             if d["down"] is not None:

@@ -156,8 +156,10 @@ __global__ void __launch_bounds__(kHThreads, 2) homography_fit_kernel(const HPar
   const float2* __restrict__ P2 = reinterpret_cast<const float2*>(prm.p2) + (size_t)b * N;
   const float* __restrict__ Wt = prm.w ? prm.w + (size_t)b * N : nullptr;
 
-  // ---- pass 1: means
-  double m[4] = {0.0, 0.0, 0.0, 0.0};
+  // ---- pass 1: means.  A thread's share (N / 256 points) is summed in fp32 and only the per-thread sums go to fp64:
+  // the transform built from the means and scales is applied and undone consistently, so the solution does not depend
+  // on their last bits, and fp32 -> fp64 conversions run on the 16-lane XU pipe (they were a third of this kernel).
+  float mf[4] = {0.f, 0.f, 0.f, 0.f};
   for (int i0 = threadIdx.x; i0 < N; i0 += kHThreads * kHUnroll) {
     float2 a[kHUnroll], c[kHUnroll];
 #pragma unroll
@@ -168,35 +170,39 @@ __global__ void __launch_bounds__(kHThreads, 2) homography_fit_kernel(const HPar
     }
 #pragma unroll
     for (int u = 0; u < kHUnroll; ++u) {
-      m[0] += a[u].x; m[1] += a[u].y; m[2] += c[u].x; m[3] += c[u].y;
+      mf[0] += a[u].x; mf[1] += a[u].y; mf[2] += c[u].x; mf[3] += c[u].y;
     }
   }
+  double m[4] = {double(mf[0]), double(mf[1]), double(mf[2]), double(mf[3])};
   block_sum<4>(m, scratch);
   const double inv_n = 1.0 / double(N);
   const double mx1 = m[0] * inv_n, my1 = m[1] * inv_n, mx2 = m[2] * inv_n, my2 = m[3] * inv_n;
 
-  // ---- pass 2: mean distance to the mean -> isotropic scale sqrt(2) / (dist + eps)
-  double d[2] = {0.0, 0.0};
-  for (int i0 = threadIdx.x; i0 < N; i0 += kHThreads * kHUnroll) {
-    float2 a[kHUnroll], c[kHUnroll];
-    bool live[kHUnroll];
+  // ---- pass 2: mean distance to the mean -> isotropic scale sqrt(2) / (dist + eps), fp32 per thread as above
+  // (the reference's normalize_points works in fp32 throughout)
+  float df[2] = {0.f, 0.f};
+  {
+    const float fx1 = float(mx1), fy1 = float(my1), fx2 = float(mx2), fy2 = float(my2);
+    for (int i0 = threadIdx.x; i0 < N; i0 += kHThreads * kHUnroll) {
+      float2 a[kHUnroll], c[kHUnroll];
+      bool live[kHUnroll];
 #pragma unroll
-    for (int u = 0; u < kHUnroll; ++u) {
-      const int i = i0 + u * kHThreads;
-      live[u] = i < N;
-      a[u] = live[u] ? __ldg(P1 + i) : make_float2(0.f, 0.f);
-      c[u] = live[u] ? __ldg(P2 + i) : make_float2(0.f, 0.f);
-    }
+      for (int u = 0; u < kHUnroll; ++u) {
+        const int i = i0 + u * kHThreads;
+        live[u] = i < N;
+        a[u] = live[u] ? __ldg(P1 + i) : make_float2(0.f, 0.f);
+        c[u] = live[u] ? __ldg(P2 + i) : make_float2(0.f, 0.f);
+      }
 #pragma unroll
-    for (int u = 0; u < kHUnroll; ++u) {
-      if (!live[u]) continue;
-      // differences in fp64, the square root in fp32 (1e-7 relative on a quantity that only sets the scale)
-      const float ax = float(a[u].x - mx1), ay = float(a[u].y - my1);
-      const float cx = float(c[u].x - mx2), cy = float(c[u].y - my2);
-      d[0] += double(sqrtf(ax * ax + ay * ay));
-      d[1] += double(sqrtf(cx * cx + cy * cy));
+      for (int u = 0; u < kHUnroll; ++u) {
+        if (!live[u]) continue;
+        const float ax = a[u].x - fx1, ay = a[u].y - fy1, cx = c[u].x - fx2, cy = c[u].y - fy2;
+        df[0] += sqrtf(ax * ax + ay * ay);
+        df[1] += sqrtf(cx * cx + cy * cy);
+      }
     }
   }
+  double d[2] = {double(df[0]), double(df[1])};
   block_sum<2>(d, scratch);
   const double s1 = 1.4142135623730951 / (d[0] * inv_n + 1e-8);
   const double s2 = 1.4142135623730951 / (d[1] * inv_n + 1e-8);

@@ -235,6 +235,16 @@ int woft_select_correspondences(const float* flow_up, const float* weights_up, c
                                 const uint8_t* pw_mask, int height, int width, const float* sobol_sorted, int to_draw,
                                 int apply_sigmoid, float* pts_template, float* pts_cur, float* weights_out,
                                 int* n_selected, void* scratch, size_t scratch_bytes, void* stream);
+/* The same for the tracker's lost branch (YAOF_tracker_single_control.py:178-204, 314-327): flow_up runs from the
+ * previous frame to the current one and a previous-frame pixel is kept iff the template mask covers it when seen
+ * through prev_H2init (HOST, 9 doubles, row-major): template_mask[round(prev_H2init (x, y, 1))], zero outside -- what
+ * cv2.warpPerspective(template_mask, inv(prev_H2init), flags=INTER_NEAREST) > 0 gives.  No bounds test on the targets.
+ * pts_prev receives the previous-frame pixels, pts_cur = pixel + flow. */
+int woft_select_correspondences_local(const float* flow_up, const float* weights_up, const uint8_t* template_mask,
+                                      const double* prev_to_template_host, int height, int width,
+                                      const float* sobol_sorted, int to_draw, int apply_sigmoid, float* pts_prev,
+                                      float* pts_cur, float* weights_out, int* n_selected, void* scratch,
+                                      size_t scratch_bytes, void* stream);
 int woft_homography_fit_n(const float* points1, const float* points2, const float* weights, const int* n_points_dev,
                           int max_points, int method, int n_iter, float huber_k, float* H_out, void* stream);
 int woft_inlier_fraction(const float* H, const float* pts_a, const float* pts_b, const int* n_points_dev, float threshold,

@@ -725,6 +725,28 @@ def test_lost_branch_matches_cpu_pipeline():
         assert meta2.N_lost == 2 and np.all(np.isfinite(H2))
         H_cpu2, _ = cpu_pipeline.track_frame_local(net, img1, img0, mask, H_gpu, 12)
         assert wo.corner_error(torch.from_numpy(H2), torch.from_numpy(H_cpu2), W, H) <= 0.1
+    # the same branch with everything after the flow on the device (woft_select_correspondences_local): the global
+    # stage's inlier fraction is zeroed on its way back to force the branch
+    conf = tracker.default_config(flow_conf, device_prewarp=True)
+    assert conf.fused_select
+    flower = RAFTWrapper(flow_conf, device=DEV, corr_block=functools.partial(CorrBlock, mode="tf32x3"))
+    trk = tracker.PlanarTracker(conf, flower=flower)
+    trk.init(img0, mask)
+    fused = trk.estimate_global_fused
+
+    def fail_global(*a):
+        res = fused(*a).clone()
+        res[9] = 0.0
+        return res
+
+    trk.estimate_global_fused = fail_global
+    H_gpu, meta = trk.track(img1)
+    assert meta.lost and trk.flow_passes == 2
+    H_cpu, _ = cpu_pipeline.track_frame_local(net, img0, img1, mask, np.eye(3), 12)
+    assert wo.corner_error(torch.from_numpy(H_gpu), torch.from_numpy(H_cpu), W, H) <= 0.05
+    H2, meta2 = trk.track(img0)
+    H_cpu2, _ = cpu_pipeline.track_frame_local(net, img1, img0, mask, H_gpu, 12)
+    assert meta2.N_lost == 2 and wo.corner_error(torch.from_numpy(H2), torch.from_numpy(H_cpu2), W, H) <= 0.1
 
 
 def test_fused_select_fit_check_matches_reference_pieces():

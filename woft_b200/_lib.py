@@ -67,6 +67,9 @@ SIGNATURES = {
     "woft_select_scratch_bytes": (c_size_t, [c_int, c_int]),
     "woft_select_correspondences": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
                                             c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "woft_select_correspondences_local": (c_int, [c_void_p, c_void_p, c_void_p, POINTER(ctypes.c_double), c_int, c_int,
+                                                  c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                                  c_size_t, c_void_p]),
     "woft_homography_fit_n": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_void_p,
                                       c_void_p]),
     "woft_inlier_fraction": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_float, c_void_p, c_void_p,

@@ -53,6 +53,43 @@ __global__ void __launch_bounds__(kSelBlock) select_flag_kernel(const float* __r
   }
 }
 
+// Lost branch (YAOF_tracker_single_control.py:314-327, _mask_coords_flow): the flow runs from the previous frame, and
+// a pixel of it is kept iff the template mask, seen from the previous frame, covers it:
+//   prev_mask = cv2.warpPerspective(template_mask, inv(prev_H2init), (W, H), flags=INTER_NEAREST) > 0
+// i.e. prev_mask(x, y) = template_mask(round(prev_H2init (x, y, 1))), zero outside.  No bounds test on the targets.
+struct LocalMap {
+  double m[9];   // prev_H2init: previous-frame pixel -> template pixel
+};
+
+__global__ void __launch_bounds__(kSelBlock) select_flag_local_kernel(const uint8_t* __restrict__ tmask, const LocalMap map,
+                                                                     uint8_t* __restrict__ keep,
+                                                                     int* __restrict__ counts, int H, int W) {
+  __shared__ int warp_cnt[kSelBlock / 32];
+  const int i = blockIdx.x * kSelBlock + threadIdx.x;
+  bool k = false;
+  if (i < H * W) {
+    const int y = i / W, x = i - y * W;
+    // OpenCV's warpPerspective, nearest: fp64 homogeneous coordinates, division by W (0 if W == 0), cvRound
+    const double X0 = map.m[0] * x + map.m[1] * y + map.m[2];
+    const double Y0 = map.m[3] * x + map.m[4] * y + map.m[5];
+    double Wd = map.m[6] * x + map.m[7] * y + map.m[8];
+    Wd = Wd != 0.0 ? 1.0 / Wd : 0.0;
+    const int sx = __double2int_rn(fmax(-2147483648.0, fmin(2147483647.0, X0 * Wd)));
+    const int sy = __double2int_rn(fmax(-2147483648.0, fmin(2147483647.0, Y0 * Wd)));
+    k = sx >= 0 && sx < W && sy >= 0 && sy < H && __ldg(tmask + (size_t)sy * W + sx) != 0;
+    keep[i] = k ? 1 : 0;
+  }
+  const unsigned b = __ballot_sync(0xffffffffu, k);
+  if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = __popc(b);
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    int v = warp_cnt[threadIdx.x];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0) counts[blockIdx.x] = v;
+  }
+}
+
 // counts -> exclusive offsets (in place), n_kept, and the list of selected ranks (sorted, unique).
 __global__ void __launch_bounds__(1024) select_plan_kernel(int* __restrict__ counts, int nblocks,
                                                            const float* __restrict__ u_sorted, int to_draw,
@@ -198,11 +235,10 @@ extern "C" size_t woft_select_scratch_bytes(int height, int width) {
   return ((hw + 255) / 256 * 256) + ((nblocks * 4 + 255) / 256 * 256) + woft::kSelMaxDraw * 4 + 256;
 }
 
-extern "C" int woft_select_correspondences(const float* flow_up, const float* weights_up, const uint8_t* template_mask,
-                                           const uint8_t* pw_mask, int height, int width, const float* sobol_sorted,
-                                           int to_draw, int apply_sigmoid, float* pts_template, float* pts_cur,
-                                           float* weights_out, int* n_selected, void* scratch, size_t scratch_bytes,
-                                           void* stream) {
+static int select_impl(const float* flow_up, const float* weights_up, const uint8_t* template_mask, const uint8_t* pw_mask,
+                       const double* prev_to_template_host, int height, int width, const float* sobol_sorted, int to_draw,
+                       int apply_sigmoid, float* pts_template, float* pts_cur, float* weights_out, int* n_selected,
+                       void* scratch, size_t scratch_bytes, void* stream) {
   using namespace woft;
   WOFT_REQUIRE(flow_up && template_mask && sobol_sorted && pts_template && pts_cur && weights_out && n_selected && scratch,
                "woft_select_correspondences: null pointer");
@@ -220,11 +256,37 @@ extern "C" int woft_select_correspondences(const float* flow_up, const float* we
   int* ranks = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(counts) + ((size_t)nblocks * 4 + 255) / 256 * 256);
   int* n_kept = ranks + kSelMaxDraw;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  select_flag_kernel<<<nblocks, kSelBlock, 0, s>>>(flow_up, template_mask, pw_mask, keep, counts, height, width);
+  if (prev_to_template_host) {
+    LocalMap map;
+    for (int k = 0; k < 9; ++k) map.m[k] = prev_to_template_host[k];
+    select_flag_local_kernel<<<nblocks, kSelBlock, 0, s>>>(template_mask, map, keep, counts, height, width);
+  } else {
+    select_flag_kernel<<<nblocks, kSelBlock, 0, s>>>(flow_up, template_mask, pw_mask, keep, counts, height, width);
+  }
   select_plan_kernel<<<1, 1024, 0, s>>>(counts, nblocks, sobol_sorted, to_draw, ranks, n_selected, n_kept);
   select_gather_kernel<<<to_draw, kSelBlock, 0, s>>>(flow_up, weights_up, keep, counts, nblocks, ranks, n_selected, height,
                                                      width, apply_sigmoid, pts_template, pts_cur, weights_out);
   return launch_status("select kernels");
+}
+
+extern "C" int woft_select_correspondences(const float* flow_up, const float* weights_up, const uint8_t* template_mask,
+                                           const uint8_t* pw_mask, int height, int width, const float* sobol_sorted,
+                                           int to_draw, int apply_sigmoid, float* pts_template, float* pts_cur,
+                                           float* weights_out, int* n_selected, void* scratch, size_t scratch_bytes,
+                                           void* stream) {
+  return select_impl(flow_up, weights_up, template_mask, pw_mask, nullptr, height, width, sobol_sorted, to_draw,
+                     apply_sigmoid, pts_template, pts_cur, weights_out, n_selected, scratch, scratch_bytes, stream);
+}
+
+extern "C" int woft_select_correspondences_local(const float* flow_up, const float* weights_up,
+                                                 const uint8_t* template_mask, const double* prev_to_template_host,
+                                                 int height, int width, const float* sobol_sorted, int to_draw,
+                                                 int apply_sigmoid, float* pts_prev, float* pts_cur, float* weights_out,
+                                                 int* n_selected, void* scratch, size_t scratch_bytes, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(prev_to_template_host, "woft_select_correspondences_local: null matrix");
+  return select_impl(flow_up, weights_up, template_mask, nullptr, prev_to_template_host, height, width, sobol_sorted,
+                     to_draw, apply_sigmoid, pts_prev, pts_cur, weights_out, n_selected, scratch, scratch_bytes, stream);
 }
 
 extern "C" int woft_inlier_fraction(const float* H, const float* pts_a, const float* pts_b, const int* n_points_dev,

@@ -79,11 +79,15 @@ def find_homography(pts_A, pts_B, weights=None):
 _SOBOL_DEV = {}
 
 
-def select_fit_check(flow_up, weight_logits, template_mask, pw_mask, to_draw=500, thr=5.0, min_frac=0.2):
+def select_fit_check(flow_up, weight_logits, template_mask, pw_mask, to_draw=500, thr=5.0, min_frac=0.2,
+                     prev_to_template=None):
     """The default config's post-flow stage as five launches and no host round trip: correspondence mask + Sobol pick
     (woft_select_correspondences), weighted fit (woft_homography_fit_n), inlier test (woft_inlier_fraction).
     flow_up (2,H,W), weight_logits (1,H,W) before the sigmoid, masks (H,W) bool/uint8 -- all on the device.
-    Returns a device tensor of 12 floats: H row-major in [0:9], inlier fraction in [9], number of points in [10]."""
+    Returns a device tensor of 12 floats: H row-major in [0:9], inlier fraction in [9], number of points in [10].
+    With `prev_to_template` (3x3, host: the previous frame's homography to the template) this is the lost branch:
+    the flow starts in the previous frame and its pixels are masked by the template mask seen through that matrix
+    (woft_select_correspondences_local); H then maps current points onto previous-frame points."""
     from . import _lib
     lib = _lib.load()
     dev = flow_up.device
@@ -103,9 +107,19 @@ def select_fit_check(flow_up, weight_logits, template_mask, pw_mask, to_draw=500
     scratch = torch.empty((nbytes,), device=dev, dtype=torch.uint8)
     with torch.cuda.device(dev):
         st = _lib.current_stream(dev)
-        rc = lib.woft_select_correspondences(_lib.ptr(flow_up), _lib.ptr(weight_logits), _lib.ptr(template_mask),
-                                             _lib.ptr(pw_mask), H, W, _lib.ptr(_SOBOL_DEV[key]), to_draw, 1, _lib.ptr(pts_t),
-                                             _lib.ptr(pts_c), _lib.ptr(w), _lib.ptr(n), _lib.ptr(scratch), nbytes, st)
+        if prev_to_template is None:
+            rc = lib.woft_select_correspondences(_lib.ptr(flow_up), _lib.ptr(weight_logits), _lib.ptr(template_mask),
+                                                 _lib.ptr(pw_mask), H, W, _lib.ptr(_SOBOL_DEV[key]), to_draw, 1,
+                                                 _lib.ptr(pts_t), _lib.ptr(pts_c), _lib.ptr(w), _lib.ptr(n),
+                                                 _lib.ptr(scratch), nbytes, st)
+        else:
+            import ctypes
+            m = np.ascontiguousarray(np.asarray(prev_to_template, dtype=np.float64).reshape(9))
+            rc = lib.woft_select_correspondences_local(_lib.ptr(flow_up), _lib.ptr(weight_logits), _lib.ptr(template_mask),
+                                                       m.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), H, W,
+                                                       _lib.ptr(_SOBOL_DEV[key]), to_draw, 1, _lib.ptr(pts_t),
+                                                       _lib.ptr(pts_c), _lib.ptr(w), _lib.ptr(n), _lib.ptr(scratch),
+                                                       nbytes, st)
         _lib.check(rc, "woft_select_correspondences")
         # H maps the current (pre-warped) points onto the template points (tracker :152-155)
         rc = lib.woft_homography_fit_n(_lib.ptr(pts_c), _lib.ptr(pts_t), _lib.ptr(w), _lib.ptr(n), to_draw,
@@ -210,6 +224,17 @@ class PlanarTracker:
             self.N_lost += 1
             if _cfg(self.C, "no_local_H", False):
                 H_cur2init = H_global
+            elif _cfg(self.C, "fused_select", False) and on_device:
+                # local flow (T-1 -> T), mask, Sobol pick and fit on the device; one 48-byte copy back (:178-204)
+                flow, w_logits = self.flower.compute_flow(self.prev_dev, frame_dev, mode="flow", do_sigmoid=False)
+                self.flow_passes += 1
+                res, _ = select_fit_check(flow, w_logits, self.template_mask, None, prev_to_template=self.prev_H2init)
+                H_flow = res[:9].cpu().numpy().reshape(3, 3).astype(np.float64)
+                H_local = compose_H(H_flow, self.prev_H2init) if np.all(np.isfinite(H_flow)) else None
+                if H_local is None or not np.all(np.isfinite(H_local)):
+                    H_local = self.prev_H2init   # fewer than 4 points or a degenerate fit: the reference's except branch
+                meta.H_local_cur2init = H_local.copy()
+                H_cur2init = H_local
             else:
                 p_coords, c2_coords, w2 = self.flower.compute_flow(self.prev_dev if on_device else self.prev_img,
                                                                    frame_dev if on_device else input_img, mode="TC",

@@ -749,6 +749,47 @@ def test_lost_branch_matches_cpu_pipeline():
     assert meta2.N_lost == 2 and wo.corner_error(torch.from_numpy(H2), torch.from_numpy(H_cpu2), W, H) <= 0.1
 
 
+def test_tracker_1080p_with_a_lost_frame():
+    """BASELINE config 5 in small: 1920x1080 frames (a 32 400-query volume, 5.6 GB pyramid) through the whole tracker with
+    one frame forced into the lost branch.  The weights are seeded random ones, so there is no known answer at this size
+    (parity with the CPU pipeline is checked at 256x320): every homography must be finite and normalised and the pass
+    counts must match the branches taken."""
+    from types import SimpleNamespace
+    from oracle.gen_golden import make_frames
+    from woft_b200 import tracker
+    from woft_b200.optical_flow import RAFTWrapper
+    H, W = 1080, 1920
+    img0, img1 = make_frames(H, W, 5)
+    mask = np.zeros((H, W), np.uint8)
+    mask[300:800, 500:1400] = 255
+    flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False), model=None,
+                                seeded_weights=0, iters=12, padding_mode="nopad")
+    trk = tracker.PlanarTracker(tracker.default_config(flow_conf), flower=RAFTWrapper(flow_conf, device=DEV))
+    trk.init(img0, mask)
+    fused = trk.estimate_global_fused
+    lose = {"now": False}
+
+    def maybe_fail(*a):
+        res = fused(*a)
+        if lose["now"]:
+            res = res.clone()
+            res[9] = 0.0
+        return res
+
+    trk.estimate_global_fused = maybe_fail
+    H_first, meta = trk.track(img0)
+    assert np.all(np.isfinite(H_first)) and trk.flow_passes >= 1
+    passes = trk.flow_passes
+    lose["now"] = True
+    H_lost, meta = trk.track(img1)
+    assert meta.lost and trk.flow_passes == passes + 2 and np.all(np.isfinite(H_lost))
+    lose["now"] = False
+    H_next, meta = trk.track(img1)
+    assert np.all(np.isfinite(H_next)) and H_next[2, 2] == pytest.approx(1.0)
+    del trk
+    torch.cuda.empty_cache()
+
+
 def test_fused_select_fit_check_matches_reference_pieces():
     """woft_select_correspondences + woft_homography_fit_n + woft_inlier_fraction against the oracle's restatement of
     _mask_coords, the Sobol subsampler, find_homography_nonhomogeneous_QR and redet_success_fn."""

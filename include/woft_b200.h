@@ -287,6 +287,15 @@ int woft_images_to_input(const uint8_t* img1_bgr, const uint8_t* img2_bgr, int h
 int woft_stem_conv7x7(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
                       int relu, float* out_nhwc, void* stream);
 
+/* First layer of the weight head (raft_core/weighted_raft.py:319-339, 347-384) with its input assembly: per query pixel
+ * the 9x9x4 correlation window (the channels-last lookup output read as (hp, wp, level), :267-272) and the mean
+ * response broadcast as a fifth channel (:358-361) -> conv3x3(5 -> 128, pad 1) + bias + ReLU, on the tensor cores
+ * (mma.sync, TF32 operands, fp32 accumulation).
+ *   window_nhwc (n, 9*9*4); mean_response (n); weight (128,5,3,3); bias (128)
+ *   -> out (n, 9, 9, 128) channels-last.  patch, levels, channels_out must be 9, 4, 128 (the shipped head). */
+int woft_weight_head_conv1(const float* window_nhwc, const float* mean_response, const float* weight, const float* bias,
+                           long long n_images, int patch, int levels, int channels_out, float* out_nhwc, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -34,7 +34,22 @@ big = torch.empty(64 << 20, device=dev)  # 256 MiB, flushes L2 between timed lau
 img2 = (torch.rand((2, 3, 720, 1280), generator=g) * 2 - 1).to(dev).contiguous(memory_format=cl)
 wst, bst = (torch.randn((64, 3, 7, 7), generator=g) * 0.05).to(dev), torch.randn((64,), generator=g).to(dev)
 
+from woft_b200 import _lib  # noqa: E402
+nq = 14400
+win = torch.randn((nq, 324), generator=g).to(dev)
+mresp = torch.randn((nq,), generator=g).to(dev)
+wh_w, wh_b = (torch.randn((128, 5, 3, 3), generator=g) * 0.2).to(dev), torch.randn((128,), generator=g).to(dev)
+wh_out = torch.empty((nq, 128, 9, 9), device=dev).contiguous(memory_format=cl)
+
+
+def head_conv1():
+    rc = _lib.load().woft_weight_head_conv1(_lib.ptr(win), _lib.ptr(mresp), _lib.ptr(wh_w), _lib.ptr(wh_b), nq, 9, 4, 128,
+                                            _lib.ptr(wh_out), _lib.current_stream(dev))
+    assert rc == 0
+
+
 cases = {
+    "weight_head_conv1 (14400 windows)": head_conv1,
     "stem_conv7x7 pair (fnet)": lambda: fast_net.stem_conv7x7(img2, wst),
     "stem_conv7x7 one frame + bias + relu": lambda: fast_net.stem_conv7x7(img2[:1], wst, bst, relu=True),
     "flow_conv7x7_relu": lambda: fast_net.flow_conv7x7_relu(flow, w7, b7),

@@ -609,6 +609,35 @@ def test_stem_convolution_kernel():
         torch.backends.cudnn.allow_tf32 = old
 
 
+def test_weight_head_first_layer_kernel():
+    """woft_weight_head_conv1 against the reference's formulation: scramble the lookup channels into (level, hp, wp),
+    append the broadcast mean response, conv3x3(5 -> 128) + ReLU in fp32 (weighted_raft.py:267-272, 347-384).
+    Tolerance: TF32 operands on 45 products of O(1) values."""
+    from woft_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(15)
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        for n in (1, 37, 1000):   # 81 * n rows: partial last step, steps that straddle two images
+            window = torch.randn((n, 81 * 4), generator=g).to(DEV)
+            mr = torch.randn((n,), generator=g).to(DEV)
+            w = (torch.randn((128, 5, 3, 3), generator=g) * 0.2).to(DEV)
+            b = torch.randn((128,), generator=g).to(DEV)
+            out = torch.full((n * 81 * 128 + 256,), 777.0, device=DEV)
+            rc = lib.woft_weight_head_conv1(_lib.ptr(window), _lib.ptr(mr), _lib.ptr(w), _lib.ptr(b), n, 9, 4, 128,
+                                            _lib.ptr(out), _lib.current_stream(torch.device(DEV)))
+            assert rc == 0 and (out[n * 81 * 128:] == 777.0).all()
+            x = torch.cat([window.view(n, 9, 9, 4).permute(0, 3, 1, 2), mr.view(n, 1, 1, 1).expand(n, 1, 9, 9)], dim=1)
+            want = F.relu(F.conv2d(x, w, b, padding=1)).permute(0, 2, 3, 1).reshape(-1)
+            assert (out[:n * 81 * 128] - want).abs().max().item() <= 1e-2
+            assert (out[:n * 81 * 128] - want).abs().mean().item() <= 1e-3
+        assert lib.woft_weight_head_conv1(_lib.ptr(window), _lib.ptr(mr), _lib.ptr(w), _lib.ptr(b), n, 7, 4, 128,
+                                          _lib.ptr(out), _lib.current_stream(torch.device(DEV))) == _lib.ERR_INVALID_ARGUMENT
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+
+
 def test_convex_upsample_kernel():
     from woft_b200.fast_net import convex_upsample_both
     from woft_b200.raft_net import convex_upsample

@@ -1,0 +1,177 @@
+// First layer of the weight head (raft_core/weighted_raft.py:319-339, 347-384): for every query pixel a 9 x 9 "image"
+// with 5 channels -- the 4 pyramid levels of its correlation window (the lookup's channels read as (hp, wp, level),
+// :267-272) and the mean response of its correlation plane broadcast over the patch (:358-361) -- goes through
+// conv3x3(5 -> 128, pad 1) + ReLU.  That is 14 400 tiny images at 1280x720; cuDNN runs it as an fp32 direct
+// convolution (206 us) after three ATen kernels have assembled the 5-channel input.  Here the assembly is the staging
+// step of an implicit GEMM on the tensor cores (mma.sync m16n8k8, TF32 operands rounded to nearest, fp32 accumulation):
+//   M = 81 pixels per image, images back to back; N = 128; K = 9 taps x 5 channels = 45, padded to 48.
+// A CTA takes 64 consecutive (image, pixel) rows per step, which touch at most two images; those are staged as
+// zero-bordered 11 x 11 x 5 tiles and the A fragments gathered through a k -> offset table.  The 48 x 128 weight matrix
+// never leaves the registers: a warp owns 32 rows x 32 output channels and keeps its 6 x 4 B fragments for the whole
+// kernel.  Output (n, 9, 9, 128) channels-last, 597 MB at 1280x720 -- the kernel is bound by writing it.
+#include "common.cuh"
+
+namespace woft {
+
+constexpr int kWhP = 9, kWhPix = kWhP * kWhP, kWhL = 4, kWhCin = kWhL + 1, kWhCout = 128;
+constexpr int kWhK = 9 * kWhCin, kWhKP = 48, kWhRows = 64;
+constexpr int kWhTile = 11 * 11 * kWhCin;   // 605 floats per zero-bordered image
+
+__device__ __forceinline__ float wh_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+__device__ __forceinline__ void wh_mma(float (&d)[4], const float (&a)[4], float b0, float b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
+        "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+
+__global__ void __launch_bounds__(256, 2) weight_head_conv1_kernel(const float* __restrict__ window,   // (n, 81 * 4)
+                                                                   const float* __restrict__ mean_resp, // (n)
+                                                                   const float* __restrict__ weight,    // (128, 5, 3, 3)
+                                                                   const float* __restrict__ bias,      // (128)
+                                                                   float* __restrict__ out,             // (n * 81, 128)
+                                                                   int n_img, int total_tiles) {
+  __shared__ float tiles[2][2 * kWhTile];   // double buffered: the next step's images load while this one multiplies
+  __shared__ int koff[kWhKP];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int rg = warp >> 2, cq = warp & 3;   // 2 row groups of 32 rows x 4 channel quarters of 32
+  for (int i = tid; i < 4 * kWhTile; i += 256) (&tiles[0][0])[i] = 0.f;   // borders stay zero for the whole kernel
+  if (tid < kWhKP) {
+    const int tap = tid / kWhCin, ci = tid - tap * kWhCin, ky = tap / 3, kx = tap - ky * 3;
+    koff[tid] = tid < kWhK ? (ky * 11 + kx) * kWhCin + ci : 0;
+  }
+  // B fragments of this warp: b0 = W[k = ks*8 + t][n], b1 = W[k + 4][n], n = cq*32 + nt*8 + g; k = tap*5 + ci
+  float bf[6][4][2];
+#pragma unroll
+  for (int ks = 0; ks < 6; ++ks)
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int k = ks * 8 + t + 4 * h;
+      const int tap = k / kWhCin, ci = k - tap * kWhCin;
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        const int n = cq * 32 + nt * 8 + g;
+        bf[ks][nt][h] = k < kWhK ? wh_tf32(__ldg(weight + ((size_t)n * kWhCin + ci) * 9 + tap)) : 0.f;
+      }
+    }
+  float bv[4][2];
+#pragma unroll
+  for (int nt = 0; nt < 4; ++nt) {
+    bv[nt][0] = __ldg(bias + cq * 32 + nt * 8 + 2 * t);
+    bv[nt][1] = __ldg(bias + cq * 32 + nt * 8 + 2 * t + 1);
+  }
+  const int total_rows = n_img * kWhPix;   // < 2^31, checked by the entry point
+
+  // a step's input: 2 images x 81 pixels x 5 channels = 810 values, at most 4 per thread, held in registers between
+  // the load (issued one step ahead) and the store into the step's buffer.  Which value a thread handles does not
+  // depend on the step: source and destination offsets are worked out once.
+  constexpr int kPer = (2 * kWhPix * kWhCin + 255) / 256;
+  int src_off[kPer], dst_off[kPer], slot[kPer];   // src_off < 0: the mean response of image `slot`
+#pragma unroll
+  for (int u = 0; u < kPer; ++u) {
+    const int i = tid + u * 256;
+    const int sl = i / (kWhPix * kWhCin), r = i - sl * kWhPix * kWhCin;
+    const int p = r / kWhCin, ci = r - p * kWhCin;
+    const int y = p / kWhP, x = p - y * kWhP;
+    slot[u] = i < 2 * kWhPix * kWhCin ? sl : -1;
+    src_off[u] = ci < kWhL ? sl * (kWhPix * kWhL) + p * kWhL + ci : -1;
+    dst_off[u] = sl * kWhTile + ((y + 1) * 11 + x + 1) * kWhCin + ci;
+  }
+  float pv[kPer];
+  auto prefetch = [&](int tile) {
+    const int img0 = (tile * kWhRows) / kWhPix;
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+      pv[u] = 0.f;
+      if (slot[u] >= 0 && img0 + slot[u] < n_img)
+        pv[u] = src_off[u] >= 0 ? __ldg(window + (size_t)img0 * (kWhPix * kWhL) + src_off[u])
+                                : __ldg(mean_resp + img0 + slot[u]);
+    }
+  };
+  int buf = 0;
+  if ((int)blockIdx.x < total_tiles) prefetch(blockIdx.x);
+  __syncthreads();   // zeroed borders and the offset table are in place before any step writes its images
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, buf ^= 1) {
+    const int row0 = tile * kWhRows;
+    const int img0 = row0 / kWhPix;
+    float* tl = tiles[buf];
+#pragma unroll
+    for (int u = 0; u < kPer; ++u)
+      if (slot[u] >= 0) tl[dst_off[u]] = wh_tf32(pv[u]);
+    __syncthreads();   // this buffer was last read two steps ago, before the previous step's barrier
+    if (tile + (int)gridDim.x < total_tiles) prefetch(tile + gridDim.x);
+
+    int base[2][2], grow[2][2];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        int r = row0 + rg * 32 + mt * 16 + g + 8 * h;
+        grow[mt][h] = r;
+        if (r >= total_rows) r = total_rows - 1;   // clamp for the gather, never stored
+        const int img = r / kWhPix, p = r - img * kWhPix;
+        const int y = p / kWhP, x = p - y * kWhP;
+        base[mt][h] = (img - img0) * kWhTile + (y * 11 + x) * kWhCin;
+      }
+    float acc[2][4][4];
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        acc[mt][nt][0] = bv[nt][0]; acc[mt][nt][1] = bv[nt][1];
+        acc[mt][nt][2] = bv[nt][0]; acc[mt][nt][3] = bv[nt][1];
+      }
+#pragma unroll
+    for (int ks = 0; ks < 6; ++ks) {
+      const int o0 = koff[ks * 8 + t], o1 = koff[ks * 8 + t + 4];
+      float a[2][4];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt) {
+        a[mt][0] = tl[base[mt][0] + o0];
+        a[mt][1] = tl[base[mt][1] + o0];
+        a[mt][2] = tl[base[mt][0] + o1];
+        a[mt][3] = tl[base[mt][1] + o1];
+      }
+#pragma unroll
+      for (int nt = 0; nt < 4; ++nt) {
+        wh_mma(acc[0][nt], a[0], bf[ks][nt][0], bf[ks][nt][1]);
+        wh_mma(acc[1][nt], a[1], bf[ks][nt][0], bf[ks][nt][1]);
+      }
+    }
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        if (grow[mt][h] >= total_rows) continue;
+        float* o = out + (size_t)grow[mt][h] * kWhCout + cq * 32 + 2 * t;
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+          *reinterpret_cast<float2*>(o + nt * 8) =
+              make_float2(fmaxf(acc[mt][nt][2 * h], 0.f), fmaxf(acc[mt][nt][2 * h + 1], 0.f));
+      }
+  }
+}
+
+}  // namespace woft
+
+extern "C" int woft_weight_head_conv1(const float* window_nhwc, const float* mean_response, const float* weight,
+                                      const float* bias, long long n_images, int patch, int levels, int channels_out,
+                                      float* out_nhwc, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(window_nhwc && mean_response && weight && bias && out_nhwc, "woft_weight_head_conv1: null pointer");
+  WOFT_REQUIRE(patch == kWhP && levels == kWhL && channels_out == kWhCout,
+               "woft_weight_head_conv1: built for 9x9 patches, 4 levels and 128 output channels");
+  WOFT_REQUIRE(n_images > 0 && n_images * kWhPix + kWhRows < (1LL << 31), "woft_weight_head_conv1: bad image count");
+  const long long tiles = (n_images * kWhPix + kWhRows - 1) / kWhRows;
+  WOFT_REQUIRE(tiles < (1LL << 31) && n_images < (1LL << 31), "woft_weight_head_conv1: too many images");
+  const int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
+  weight_head_conv1_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      window_nhwc, mean_response, weight, bias, out_nhwc, (int)n_images, (int)tiles);
+  return launch_status("weight_head_conv1_kernel");
+}

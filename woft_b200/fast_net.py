@@ -238,6 +238,7 @@ class FastWeightedRAFT:
             self.nhwc = nhwc_update
             # both encoders' 3-channel first layer through woft_stem_conv7x7 instead of cuDNN's sm_80 fallback
             self.own_stem = os.environ.get("WOFT_OWN_STEM", "1") == "1"
+            self.own_head_conv1 = os.environ.get("WOFT_OWN_HEAD_CONV1", "1") == "1"
             if nhwc_update:
                 fn = net.fnet
                 self.fw = {"stem": _cl(fn.conv1.weight), "out": (_cl(fn.conv2.weight), fn.conv2.bias), "blocks": []}
@@ -444,14 +445,29 @@ class FastWeightedRAFT:
         n = B * H1 * W1
         # NHWC buffer (n, P, P, L+1): CNN input [lvl', hp, wp] is lookup channel hp*P*L + wp*L + lvl'
         # (the reference's reinterpretation of the lookup channels, weighted_raft.py:267-272)
-        buf = torch.empty((n, P, P, L + 1), device=window.device, dtype=window.dtype)
-        if window.is_contiguous(memory_format=torch.channels_last) and not window.is_contiguous():
-            buf[..., :L] = window.permute(0, 2, 3, 1).reshape(n, P, P, L)  # NHWC lookup: already (n, hp, wp, lvl')
+        nhwc_window = window.is_contiguous(memory_format=torch.channels_last) and not window.is_contiguous()
+        first = self.net.weight_head.net[0]
+        rest = self.head[:-1]
+        if (self.own_head_conv1 and nhwc_window and (P, L) == (9, 4) and tuple(first.weight.shape) == (128, 5, 3, 3)
+                and first.weight.is_contiguous()):
+            # first layer and its input assembly in one kernel (woft_weight_head_conv1)
+            x = torch.empty((n, 128, P, P), device=window.device, dtype=torch.float32, memory_format=torch.channels_last)
+            mr = mean_response.contiguous()
+            with torch.cuda.device(window.device):
+                rc = _lib.load().woft_weight_head_conv1(_lib.ptr(window), _lib.ptr(mr), _lib.ptr(first.weight),
+                                                        _lib.ptr(first.bias), n, P, L, 128, _lib.ptr(x),
+                                                        _lib.current_stream(window.device))
+            _lib.check(rc, "woft_weight_head_conv1")
+            rest = rest[1:]
         else:
-            buf[..., :L] = window.view(B, P, P, L, H1, W1).permute(0, 4, 5, 1, 2, 3).reshape(n, P, P, L)
-        buf[..., L] = mean_response.reshape(n, 1, 1)
-        x = buf.permute(0, 3, 1, 2)  # logical NCHW, channels-last in memory
-        for w, b, pad in self.head[:-1]:
+            buf = torch.empty((n, P, P, L + 1), device=window.device, dtype=window.dtype)
+            if nhwc_window:
+                buf[..., :L] = window.permute(0, 2, 3, 1).reshape(n, P, P, L)  # NHWC lookup: already (n, hp, wp, lvl')
+            else:
+                buf[..., :L] = window.view(B, P, P, L, H1, W1).permute(0, 4, 5, 1, 2, 3).reshape(n, P, P, L)
+            buf[..., L] = mean_response.reshape(n, 1, 1)
+            x = buf.permute(0, 3, 1, 2)  # logical NCHW, channels-last in memory
+        for w, b, pad in rest:
             x = _conv_relu(x, w, b, padding=pad)
         w, b, _ = self.head[-1]
         # mean over the patch of a 1x1 convolution = 1x1 convolution of the patch mean

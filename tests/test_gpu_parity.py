@@ -405,6 +405,9 @@ def test_fused_schedule_matches_layer_by_layer(golden):
     assert (fast[4] - slow[4]).abs().max().item() <= 2e-3
     ref_epe = (fast[1].cpu() - torch.from_numpy(g["it12_flow_up"])).norm(dim=1).mean().item()
     assert ref_epe <= 0.01, f"fused schedule vs reference network: mean EPE {ref_epe} px"
+    # the channel-first variant of the schedule (kept for callers whose correlation operator is not this library's)
+    nchw = FastWeightedRAFT(net, nhwc_update=False)(t1, t2, iters=12, corr_block=blk)
+    assert (nchw[1] - slow[1]).norm(dim=1).mean().item() <= 2e-3 and (nchw[4] - slow[4]).abs().max().item() <= 2e-3
 
 
 def test_u8_input_path_is_the_float_path(golden):

@@ -272,6 +272,10 @@ int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels
 int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int hw, int channels, float eps, const float* residual,
                                      float* y, void* scratch, size_t scratch_bytes, void* stream);
 int woft_add_relu(const float* a, const float* b, long long n, float* y, void* stream);
+/* x = scale * (x + bias[c]) in place on a channels-last (pixels, channels) tensor, optional ReLU: the bias of the
+ * convolutions that have no activation behind them (encoder outputs, extractor.py:150; downsampling 1x1s, :36-37; the
+ * upsampling-mask head with its 0.25, update.py:122-125, 135). */
+int woft_bias_act_nhwc(float* x, const float* bias, long long pixels, int channels, float scale, int relu, void* stream);
 
 /* The flow network's input from the two uint8 frames in one launch: BGR -> RGB, 2 * (v / 255) - 1
  * (pytracking/optical_flow/raft.py:113-120, raft_core/weighted_raft.py:197-198), both frames stacked as the batch the

@@ -126,3 +126,16 @@ def test_lookup_against_oracle(b, h, w, nhwc, seed):
     levels = [lv.cpu() for lv in blk.corr_pyramid]
     want = wo.corr_lookup(levels, coords, radius=4)
     assert torch.allclose(got.cpu(), want, atol=2e-5)
+
+
+@FUZZ
+@given(b=st.integers(1, 2), h=st.integers(1, 20), w=st.integers(1, 30), cin=st.sampled_from([4, 16]),
+       cout=st.sampled_from([4, 8, 96, 576]), scale=st.sampled_from([1.0, 0.25]), nhwc=st.booleans(),
+       seed=st.integers(0, 10**6))
+def test_conv_bias(b, h, w, cin, cout, scale, nhwc, seed):
+    from woft_b200 import fast_net
+    x, wt, bs = _rand((b, cin, h, w), seed), _rand((cout, cin, 1, 1), seed + 1, 0.3), _rand((cout,), seed + 2)
+    if nhwc:
+        x, wt = x.contiguous(memory_format=CL), wt.contiguous(memory_format=CL)
+    got = fast_net.conv_bias_nhwc(x, wt, bs, scale=scale)
+    assert torch.allclose(got, scale * F.conv2d(x, wt, bs), atol=1e-5)

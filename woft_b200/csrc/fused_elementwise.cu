@@ -311,6 +311,21 @@ __global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* _
   }
 }
 
+// x[pix][c] = scale * (x[pix][c] + bias[c]) in place, optional ReLU: the bias of a convolution whose cuDNN call has no
+// fused epilogue (ATen adds a broadcast bias to a channels-last tensor with its slow, non-vectorised kernel)
+__global__ void bias_act_nhwc_kernel(float* __restrict__ x, const float* __restrict__ bias, unsigned C4, float scale,
+                                     int relu, unsigned total4) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias) + i % C4);
+    float4 v = reinterpret_cast<float4*>(x)[i];
+    v.x = scale * (v.x + b.x); v.y = scale * (v.y + b.y); v.z = scale * (v.z + b.z); v.w = scale * (v.w + b.w);
+    if (relu) {
+      v.x = fmaxf(v.x, 0.f); v.y = fmaxf(v.y, 0.f); v.z = fmaxf(v.z, 0.f); v.w = fmaxf(v.w, 0.f);
+    }
+    reinterpret_cast<float4*>(x)[i] = v;
+  }
+}
+
 __global__ void add_relu_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ y,
                                 long long total4) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
@@ -517,4 +532,16 @@ extern "C" int woft_add_relu(const float* a, const float* b, long long n, float*
   WOFT_REQUIRE(n > 0 && n % 4 == 0, "woft_add_relu: element count must be a positive multiple of 4");
   add_relu_kernel<<<ew_grid(n / 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(a, b, y, n / 4);
   return launch_status("add_relu_kernel");
+}
+
+extern "C" int woft_bias_act_nhwc(float* x, const float* bias, long long pixels, int channels, float scale, int relu,
+                                  void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(x && bias, "woft_bias_act_nhwc: null pointer");
+  WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0, "woft_bias_act_nhwc: channels must be a positive multiple of 4");
+  const long long total4 = pixels * (channels / 4);
+  WOFT_REQUIRE(total4 <= kMaxElems32, "woft_bias_act_nhwc: more than 2^31 - 1 vectors");
+  bias_act_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, bias, channels / 4, scale, relu,
+                                                                                      unsigned(total4));
+  return launch_status("bias_act_nhwc_kernel");
 }

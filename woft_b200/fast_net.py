@@ -66,6 +66,23 @@ def instance_norm_relu_nhwc(x, relu=True, eps=1e-5, residual=None):
     return y
 
 
+def conv_bias_nhwc(x, weight, bias, scale=1.0, **kw):
+    """scale * (conv2d(x, weight) + bias) for channels-last operands, the bias through woft_bias_act_nhwc (in place on
+    the convolution's output) instead of ATen's broadcast add; anything else goes the ATen way."""
+    y = F.conv2d(x, weight, None, **kw)
+    if bias is None:
+        return y if scale == 1.0 else y * scale
+    B, C, H, W = y.shape
+    if C % 4 or not y.is_contiguous(memory_format=torch.channels_last):
+        y = y + bias.view(1, -1, 1, 1)
+        return y if scale == 1.0 else y * scale
+    with torch.cuda.device(y.device):
+        rc = _lib.load().woft_bias_act_nhwc(_lib.ptr(y), _lib.ptr(bias), B * H * W, C, float(scale), 0,
+                                            _lib.current_stream(y.device))
+    _lib.check(rc, "woft_bias_act_nhwc")
+    return y
+
+
 def _dense(t):
     return t.is_contiguous() or (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last))
 
@@ -312,9 +329,9 @@ class FastWeightedRAFT:
             y = _conv_relu(x, *d["c1"], stride=d["stride"], padding=(1, 1))
             y = _conv_relu(y, *d["c2"], padding=(1, 1))
             if d["down"] is not None:
-                x = F.conv2d(x, d["down"][0], d["down"][1], stride=d["stride"])
+                x = conv_bias_nhwc(x, d["down"][0], d["down"][1], stride=d["stride"])
             x = add_relu(x, y) if x.stride() == y.stride() and _dense(x) else F.relu(x + y)
-        return F.conv2d(x, *c["out"])
+        return conv_bias_nhwc(x, *c["out"])
 
     # ---- feature encoder: bias-free conv + fused instance norm / ReLU --------------------------------------
     def _features(self, x):
@@ -342,7 +359,7 @@ class FastWeightedRAFT:
             if d["down"] is not None:
                 x = instance_norm_relu_nhwc(F.conv2d(x, d["down"], None, stride=d["stride"]), relu=False)
             x = instance_norm_relu_nhwc(F.conv2d(y, d["c2"], None, padding=1), residual=x)  # relu(x + relu(norm(..)))
-        return F.conv2d(x, w["out"][0], w["out"][1])
+        return conv_bias_nhwc(x, w["out"][0], w["out"][1])
 
     # ---- update block ---------------------------------------------------------------------------------------
     def _gru_half(self, h, x, tag):
@@ -434,7 +451,7 @@ class FastWeightedRAFT:
                        coords0=st["coords0"], flow_nchw=st["flow"], flow_nhwc=st["flow_cl"])
         mask = None
         if need_mask:
-            mask = 0.25 * F.conv2d(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"])
+            mask = conv_bias_nhwc(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"], scale=0.25)
         return mask
 
     # ---- weight head, channels-last -----------------------------------------------------------------------------

@@ -275,6 +275,11 @@ int woft_add_relu(const float* a, const float* b, long long n, float* y, void* s
 /* x = scale * (x + bias[c]) in place on a channels-last (pixels, channels) tensor, optional ReLU: the bias of the
  * convolutions that have no activation behind them (encoder outputs, extractor.py:150; downsampling 1x1s, :36-37; the
  * upsampling-mask head with its 0.25, update.py:122-125, 135). */
+/* Tail of the context encoder (raft_core/weighted_raft.py:215-219): y (pixels, 2C) is cnet's output without its bias;
+ * h = tanh(y[:, :C] + b[:C]) goes to h_dense (pixels, C) and to channels [0, C) of buf1, the context
+ * relu(y[:, C:] + b[C:]) to channels [C, 2C) of buf1 and buf2 (both (pixels, buf_stride)). */
+int woft_context_split_nhwc(const float* y, const float* bias, long long pixels, int channels, float* h_dense, float* buf1,
+                            float* buf2, int buf_stride, void* stream);
 int woft_bias_act_nhwc(float* x, const float* bias, long long pixels, int channels, float scale, int relu, void* stream);
 
 /* The flow network's input from the two uint8 frames in one launch: BGR -> RGB, 2 * (v / 255) - 1

@@ -504,6 +504,26 @@ def test_nhwc_gru_and_concat_kernels():
     assert torch.equal(buf1[:, C:], tail)
 
 
+def test_context_split_kernel():
+    """woft_context_split_nhwc: tanh / relu halves of the context encoder's output written into the GRU buffers."""
+    from woft_b200 import _lib
+    g = torch.Generator().manual_seed(16)
+    B, C, H, W = 2, 128, 9, 13
+    cl = torch.channels_last
+    y = torch.randn((B, 2 * C, H, W), generator=g).to(DEV).contiguous(memory_format=cl)
+    b = torch.randn((2 * C,), generator=g).to(DEV)
+    h = torch.empty((B, C, H, W), device=DEV).contiguous(memory_format=cl)
+    buf1 = torch.full((B, 3 * C, H, W), -3.0, device=DEV).contiguous(memory_format=cl)
+    buf2 = torch.full((B, 3 * C, H, W), -3.0, device=DEV).contiguous(memory_format=cl)
+    rc = _lib.load().woft_context_split_nhwc(_lib.ptr(y), _lib.ptr(b), B * H * W, C, _lib.ptr(h), _lib.ptr(buf1),
+                                             _lib.ptr(buf2), 3 * C, _lib.current_stream(torch.device(DEV)))
+    assert rc == 0
+    yb = y + b.view(1, -1, 1, 1)
+    assert torch.allclose(h, torch.tanh(yb[:, :C]), atol=2e-6) and torch.equal(buf1[:, :C], h)
+    assert torch.equal(buf1[:, C:2 * C], F.relu(yb[:, C:])) and torch.equal(buf2[:, C:2 * C], buf1[:, C:2 * C])
+    assert (buf1[:, 2 * C:] == -3).all() and (buf2[:, :C] == -3).all() and (buf2[:, 2 * C:] == -3).all()
+
+
 def test_thin_convolution_kernels():
     from woft_b200 import fast_net
     g = torch.Generator().manual_seed(8)

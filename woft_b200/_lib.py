@@ -67,6 +67,8 @@ SIGNATURES = {
     "woft_weight_head_conv1": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_int, c_int, c_int,
                                        c_void_p, c_void_p]),
     "woft_bias_act_nhwc": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_float, c_int, c_void_p]),
+    "woft_context_split_nhwc": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_void_p, c_void_p, c_void_p, c_int,
+                                        c_void_p]),
     "woft_select_scratch_bytes": (c_size_t, [c_int, c_int]),
     "woft_select_correspondences": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
                                             c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),

@@ -326,6 +326,29 @@ __global__ void bias_act_nhwc_kernel(float* __restrict__ x, const float* __restr
   }
 }
 
+// Tail of the context encoder (raft_core/weighted_raft.py:215-219): cnet's output + bias split into the GRU's initial
+// hidden state tanh(.) and the context features relu(.), written where the update block wants them: h dense and at the
+// head of the [h | x] buffer, the context at channel offset C of both GRU buffers.
+__global__ void context_split_nhwc_kernel(const float* __restrict__ y, const float* __restrict__ bias, unsigned C4,
+                                          float* __restrict__ h_dense, float* __restrict__ buf1, float* __restrict__ buf2,
+                                          int ld, unsigned total4) {
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
+    const unsigned pix = i / (2 * C4), c4 = i - pix * 2 * C4;
+    const float4 b = __ldg(reinterpret_cast<const float4*>(bias) + c4);
+    float4 v = __ldg(reinterpret_cast<const float4*>(y) + i);
+    v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;
+    if (c4 < C4) {
+      v = make_float4(tanhf(v.x), tanhf(v.y), tanhf(v.z), tanhf(v.w));
+      reinterpret_cast<float4*>(h_dense)[pix * C4 + c4] = v;
+      reinterpret_cast<float4*>(buf1 + (size_t)pix * ld)[c4] = v;
+    } else {
+      v = make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+      reinterpret_cast<float4*>(buf1 + (size_t)pix * ld)[c4] = v;
+      reinterpret_cast<float4*>(buf2 + (size_t)pix * ld)[c4] = v;
+    }
+  }
+}
+
 __global__ void add_relu_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ y,
                                 long long total4) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total4;
@@ -544,4 +567,17 @@ extern "C" int woft_bias_act_nhwc(float* x, const float* bias, long long pixels,
   bias_act_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(x, bias, channels / 4, scale, relu,
                                                                                       unsigned(total4));
   return launch_status("bias_act_nhwc_kernel");
+}
+
+extern "C" int woft_context_split_nhwc(const float* y, const float* bias, long long pixels, int channels, float* h_dense,
+                                       float* buf1, float* buf2, int buf_stride, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(y && bias && h_dense && buf1 && buf2, "woft_context_split_nhwc: null pointer");
+  WOFT_REQUIRE(pixels > 0 && channels > 0 && channels % 4 == 0 && buf_stride % 4 == 0 && buf_stride >= 2 * channels,
+               "woft_context_split_nhwc: channels and stride must be multiples of 4, stride >= 2 * channels");
+  const long long total4 = pixels * (channels / 2);
+  WOFT_REQUIRE(total4 <= kMaxElems32, "woft_context_split_nhwc: more than 2^31 - 1 vectors");
+  context_split_nhwc_kernel<<<ew_grid(total4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      y, bias, channels / 4, h_dense, buf1, buf2, buf_stride, unsigned(total4));
+  return launch_status("context_split_nhwc_kernel");
 }

@@ -317,7 +317,7 @@ class FastWeightedRAFT:
                 out["blocks"].append(d)
         return out
 
-    def _context(self, x):
+    def _context(self, x, raw_tail=False):
         c = self.cnet
         if self.nhwc:
             x = _cl(x)
@@ -331,6 +331,8 @@ class FastWeightedRAFT:
             if d["down"] is not None:
                 x = conv_bias_nhwc(x, d["down"][0], d["down"][1], stride=d["stride"])
             x = add_relu(x, y) if x.stride() == y.stride() and _dense(x) else F.relu(x + y)
+        if raw_tail:   # the caller adds the bias while splitting into hidden state and context (woft_context_split_nhwc)
+            return F.conv2d(x, c["out"][0], None), c["out"][1]
         return conv_bias_nhwc(x, *c["out"])
 
     # ---- feature encoder: bias-free conv + fused instance norm / ReLU --------------------------------------
@@ -389,15 +391,22 @@ class FastWeightedRAFT:
         return net, mask, dflow
 
     # ---- update block with channels-last activations and no torch.cat -----------------------------------------------
-    def _nhwc_state(self, net, inp, coords0, coords1):
-        B, C, H, W = net.shape
+    def _nhwc_state(self, ctx_out, ctx_bias, coords0, coords1):
+        """State of the channels-last update block from the context encoder's output (B, 2C, H, W), bias not yet added:
+        buf1 = [h | x], buf2 = [r*h | x] with x = [inp | motion | flow]; inp is the same every iteration."""
+        ctx_out = _cl(ctx_out)
+        B, C2, H, W = ctx_out.shape
+        C = C2 // 2
         flow = (coords1 - coords0).contiguous()
-        st = {"inp": _cl(inp), "h": _cl(net).clone(), "z": _empty_cl(B, C, H, W, net),
-              "buf1": _empty_cl(B, C + 2 * C, H, W, net), "buf2": _empty_cl(B, C + 2 * C, H, W, net), "C": C,
+        st = {"ci": C, "h": _empty_cl(B, C, H, W, ctx_out), "z": _empty_cl(B, C, H, W, ctx_out),
+              "buf1": _empty_cl(B, 3 * C, H, W, ctx_out), "buf2": _empty_cl(B, 3 * C, H, W, ctx_out), "C": C,
               "pixels": B * H * W, "coords0": coords0.contiguous(), "coords1": coords1.contiguous().clone(),
               "flow": flow, "flow_cl": _cl(flow).clone()}   # flow_cl: logical (B,2,H,W), stored (B,H,W,2)
-        concat_nhwc([st["h"]], st["buf1"], 0)  # buf1 = [h | x], buf2 = [r*h | x]
-        concat_nhwc([st["inp"]], st["buf1"], C, st["buf2"], C)  # x = [inp | motion | flow]: inp is the same every iteration
+        with torch.cuda.device(ctx_out.device):
+            rc = _lib.load().woft_context_split_nhwc(_lib.ptr(ctx_out), _lib.ptr(ctx_bias), B * H * W, C, _lib.ptr(st["h"]),
+                                                     _lib.ptr(st["buf1"]), _lib.ptr(st["buf2"]), 3 * C,
+                                                     _lib.current_stream(ctx_out.device))
+        _lib.check(rc, "woft_context_split_nhwc")
         return st
 
     def _gru_half_nhwc(self, st, tag):
@@ -438,7 +447,7 @@ class FastWeightedRAFT:
         cf = _empty_cl(B, cor.shape[1] + flo.shape[1], H, W, cor)
         concat_nhwc([_cl(cor), _cl(flo)], cf, 0)
         out = _cl(_conv_relu(cf, *w["conv"], padding=(1, 1)))      # 126 motion channels + `conv_pad` zero channels
-        C, ci = st["C"], st["inp"].shape[1]
+        C, ci = st["C"], st["ci"]
         # x = [inp | motion | flow]: inp sits in both GRU buffers since _nhwc_state; the motion features go in without
         # the padding channels of their convolution, the flow behind them (update.py:97)
         concat_nhwc([out, st["flow_cl"]], st["buf1"], C + ci, st["buf2"], C + ci,
@@ -523,18 +532,20 @@ class FastWeightedRAFT:
         image1 = images[:images.shape[0] // 2]
         fmap1, fmap2 = self._features(images).chunk(2, dim=0)
         corr_fn = corr_block(fmap1.contiguous(), fmap2.contiguous(), num_levels=net_.corr_levels, radius=net_.corr_radius)
-        net, inp = torch.split(self._context(image1), [net_.hidden_dim, net_.context_dim], dim=1)
-        net, inp = torch.tanh(net), torch.relu(inp)
-
+        nhwc = self.nhwc and isinstance(corr_fn, _CorrBlock) and net_.hidden_dim == net_.context_dim
         B, _, H, W = image1.shape
         coords0 = pixel_grid(B, H // 8, W // 8, image1.device)
         coords1 = coords0.clone()
         if flow_init is not None:
             coords1 = coords1 + flow_init
         up_mask = None
-        nhwc = self.nhwc and isinstance(corr_fn, _CorrBlock)
         lookup_flags = 8 if nhwc else 0
-        state = self._nhwc_state(net, inp, coords0, coords1) if nhwc else None
+        if nhwc:
+            state = self._nhwc_state(*self._context(image1, raw_tail=True), coords0, coords1)
+        else:
+            net, inp = torch.split(self._context(image1), [net_.hidden_dim, net_.context_dim], dim=1)
+            net, inp = torch.tanh(net), torch.relu(inp)
+            state = None
         for it in range(iters):
             last = it == iters - 1
             if nhwc:

@@ -46,6 +46,9 @@ enum woft_corr_mode {
   WOFT_CORR_FP16X3 = 5     /* tcgen05 kind::f16, error-compensated split into fp16 hi + lo (hi*hi + hi*lo + lo*hi): the
                               fp32-class result of WOFT_CORR_TF32X3 at half its operand traffic */
 };
+/* OR-ed into `mode` of woft_corr_pyramid[_static] (tensor-core modes only): fmap1 / fmap2 are channels-last
+ * (B, H, W, C) instead of (B, C, H, W), as a channels-last encoder leaves them; the result is the same volume. */
+#define WOFT_CORR_FMAPS_NHWC 0x100
 
 /* Estimators of pytracking/utils/least_squares_H.py served by woft_homography_fit (K4). */
 enum woft_h_method {

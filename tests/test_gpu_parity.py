@@ -91,6 +91,32 @@ def test_corr_pyramid_vs_oracle_ragged_shapes(shape, mode):
                                    err_msg=f"{shape} {mode} level {l}")
 
 
+@pytest.mark.parametrize("mode", ["fp16", "tf32x3", "bf16"])
+def test_corr_block_takes_channels_last_feature_maps(mode):
+    """Channels-last feature maps (WOFT_CORR_FMAPS_NHWC) give the volume the contiguous ones give, bit for bit (the
+    packed operands are the same numbers); the mean response is summed in another order, hence a tolerance."""
+    from woft_b200.corr import CorrBlock
+    g = torch.Generator().manual_seed(21)
+    for (B, C, H, W) in ((1, 256, 24, 40), (2, 40, 17, 23)):
+        f1 = torch.randn((B, C, H, W), generator=g).to(DEV)
+        f2 = torch.randn((B, C, H, W), generator=g).to(DEV)
+        a = CorrBlock(f1, f2, mode=mode)
+        b = CorrBlock(f1.contiguous(memory_format=torch.channels_last), f2.contiguous(memory_format=torch.channels_last),
+                      mode=mode)
+        b.check()
+        for la, lb in zip(a.corr_pyramid, b.corr_pyramid):
+            assert torch.equal(la, lb)
+        assert torch.allclose(a.mean_response(), b.mean_response(), atol=1e-5)
+    with pytest.raises(AssertionError):   # the CUDA-core mode reads (B,C,H,W) only; the Python class converts, the ABI refuses
+        from woft_b200 import _lib
+        lib = _lib.load()
+        lv, keep = _lib.ptr_array(a.corr_pyramid)
+        ws = torch.empty(1 << 20, dtype=torch.uint8, device=DEV)
+        _lib.check(lib.woft_corr_pyramid(_lib.ptr(f1), _lib.ptr(f2), B, C, H, W, 4, lv, None, _lib.ptr(ws), 1 << 20,
+                                         _lib.CORR_FP32_SIMT | _lib.CORR_FMAPS_NHWC, _lib.current_stream(torch.device(DEV))),
+                   "woft_corr_pyramid")
+
+
 def test_corr_block_rejects_what_the_reference_turns_into_nan():
     from woft_b200.corr import CorrBlock
     f = torch.randn(1, 16, 8, 12, device=DEV)  # coarsest level would be 1x1 -> reference returns NaN

@@ -45,7 +45,13 @@ class CorrBlock:
         self.mode = mode or DEFAULT_MODE
         if self.mode not in _lib.CORR_MODES:
             raise ValueError(f"unknown correlation mode '{self.mode}', expected one of {sorted(_lib.CORR_MODES)}")
-        fmap1, fmap2 = _as_f32c(fmap1), _as_f32c(fmap2)
+        # channels-last feature maps (what the channels-last encoder produces) are packed as they are by the
+        # tensor-core modes; anything else is brought to contiguous (B,C,H,W)
+        cl = torch.channels_last
+        nhwc = (self.mode != "fp32" and fmap1.dtype == fmap2.dtype == torch.float32 and fmap1.shape[1] > 1
+                and all(t.is_contiguous(memory_format=cl) and not t.is_contiguous() for t in (fmap1, fmap2)))
+        if not nhwc:
+            fmap1, fmap2 = _as_f32c(fmap1), _as_f32c(fmap2)
         B, C, H, W = fmap1.shape
         self.shape = (B, C, H, W)
         dev = fmap1.device
@@ -57,7 +63,7 @@ class CorrBlock:
         with torch.cuda.device(dev):
             self.corr_pyramid = [torch.empty((B * H * W, 1, h, w), device=dev, dtype=torch.float32) for h, w in sizes]
             self._row_mean = torch.empty((B, H, W), device=dev, dtype=torch.float32)
-            mode_id = _lib.CORR_MODES[self.mode]
+            mode_id = _lib.CORR_MODES[self.mode] | (_lib.CORR_FMAPS_NHWC if nhwc else 0)
             nbytes = lib.woft_corr_workspace_bytes(B, C, H, W, mode_id)
             self._workspace = torch.empty((nbytes,), device=dev, dtype=torch.uint8)
             levels, keep = _lib.ptr_array(self.corr_pyramid)

@@ -21,7 +21,7 @@ int fail(int code, const char* fmt, ...) {
 int corr_pyramid_simt(const float*, const float*, int, int, int, int, int, float* const*, cudaStream_t);
 int corr_pyramid_tc(const float*, const float*, int, int, int, int, int, float* const*, void*, int, cudaStream_t);
 size_t corr_tc_workspace_bytes(int, int, int, int);
-int launch_row_mean(const float*, const float*, int, int, int, float*, float*, cudaStream_t);
+int launch_row_mean(const float*, const float*, int, int, int, float*, float*, float*, cudaStream_t);
 
 static size_t simt_workspace_bytes(int B, int C) { return 256 + ((size_t)B * C * 4 + 255) / 256 * 256; }
 
@@ -33,6 +33,7 @@ extern "C" const char* woft_last_error(void) { return woft::last_error_buffer();
 
 extern "C" size_t woft_corr_workspace_bytes(int batch, int channels, int height, int width, int mode) {
   if (batch <= 0 || channels <= 0 || height <= 0 || width <= 0) return 0;
+  mode &= ~WOFT_CORR_FMAPS_NHWC;
   if (mode == WOFT_CORR_FP32_SIMT) return woft::simt_workspace_bytes(batch, channels);
   return woft::corr_tc_workspace_bytes(batch, channels, height * width, mode);
 }
@@ -45,7 +46,12 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
   WOFT_REQUIRE(batch > 0 && channels > 0 && height > 0 && width > 0, "woft_corr_pyramid: non-positive extent");
   WOFT_REQUIRE(num_levels >= 1 && num_levels <= kMaxLevels, "woft_corr_pyramid: num_levels %d not in [1,%d]",
                num_levels, kMaxLevels);
+  const bool fmaps_nhwc = (mode & WOFT_CORR_FMAPS_NHWC) != 0;
+  const int mode_flags = mode;
+  mode &= ~WOFT_CORR_FMAPS_NHWC;
   WOFT_REQUIRE(mode >= WOFT_CORR_FP32_SIMT && mode <= WOFT_CORR_FP16X3, "woft_corr_pyramid: unknown mode %d", mode);
+  WOFT_REQUIRE(!(fmaps_nhwc && mode == WOFT_CORR_FP32_SIMT),
+               "woft_corr_pyramid: channels-last feature maps need one of the tensor-core modes");
   WOFT_REQUIRE((long long)batch * height * width < (1ll << 31), "woft_corr_pyramid: too many query pixels");
   for (int l = 0, h = height, w = width; l < num_levels; ++l, h /= 2, w /= 2) {
     WOFT_REQUIRE(h >= 1 && w >= 1, "woft_corr_pyramid: level %d is empty", l);
@@ -62,12 +68,18 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
   if (mode == WOFT_CORR_FP32_SIMT) {
     rc = corr_pyramid_simt(fmap1, fmap2, batch, channels, height, width, num_levels, levels, s);
   } else {
-    rc = corr_pyramid_tc(fmap1, fmap2, batch, channels, height, width, num_levels, levels, workspace, mode, s);
+    rc = corr_pyramid_tc(fmap1, fmap2, batch, channels, height, width, num_levels, levels, workspace, mode_flags, s);
   }
   if (rc != WOFT_OK) return rc;
   if (row_mean) {
     float* mean2 = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) + 256);
-    rc = launch_row_mean(fmap1, fmap2, batch, channels, height * width, row_mean, mean2, s);
+    // channels-last maps: the per-strip partial sums go where the packed operands were (the GEMM is done with them);
+    // that region starts at the first 1 KiB boundary behind mean2 and is far larger than strips * B * C floats
+    float* scratch = nullptr;
+    if (fmaps_nhwc)
+      scratch = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) +
+                                         (256 + (size_t)batch * channels * 4 + 1023) / 1024 * 1024);
+    rc = launch_row_mean(fmap1, fmap2, batch, channels, height * width, row_mean, mean2, scratch, s);
   }
   return rc;
 }

@@ -130,8 +130,65 @@ __global__ void __launch_bounds__(256) row_mean_kernel(const float* __restrict__
   }
 }
 
+// The kernels for channels-last feature maps (B, HW, C).
+// mean2[b, c] in two steps: per-strip partial sums (a CTA walks its strip of pixels, threads over channels: every pixel
+// is one coalesced row), then one CTA per image adds the strips in a fixed order.
+__global__ void __launch_bounds__(256) channel_partial_nhwc_kernel(const float* __restrict__ f2, float* __restrict__ partial,
+                                                                   int C, int HW, int strips) {
+  const int b = blockIdx.y, strip = blockIdx.x;
+  const int len = (HW + strips - 1) / strips;
+  const int p0 = strip * len, p1 = min(p0 + len, HW);
+  for (int c = threadIdx.x; c < C; c += 256) {
+    const float* src = f2 + ((size_t)b * HW) * C + c;
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    int p = p0;
+    for (; p + 3 < p1; p += 4) {
+      s0 += __ldg(src + (size_t)p * C);
+      s1 += __ldg(src + (size_t)(p + 1) * C);
+      s2 += __ldg(src + (size_t)(p + 2) * C);
+      s3 += __ldg(src + (size_t)(p + 3) * C);
+    }
+    for (; p < p1; ++p) s0 += __ldg(src + (size_t)p * C);
+    partial[((size_t)b * strips + strip) * C + c] = (s0 + s1) + (s2 + s3);
+  }
+}
+
+__global__ void __launch_bounds__(256) channel_finalize_nhwc_kernel(const float* __restrict__ partial, float* __restrict__ mean,
+                                                                    int C, int HW, int strips) {
+  const int b = blockIdx.x;
+  for (int c = threadIdx.x; c < C; c += 256) {
+    float t = 0.f;
+    for (int s = 0; s < strips; ++s) t += partial[((size_t)b * strips + s) * C + c];
+    mean[(size_t)b * C + c] = t / float(HW);
+  }
+}
+
+// row_mean[b, q]: one warp per query, lanes over channels
+__global__ void __launch_bounds__(256) row_mean_nhwc_kernel(const float* __restrict__ f1, const float* __restrict__ mean2,
+                                                            float* __restrict__ row_mean, int C, int HW, int B,
+                                                            float denom) {
+  const long long q = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (q >= (long long)B * HW) return;
+  const int b = int(q / HW), lane = threadIdx.x & 31;
+  const float* a = f1 + (size_t)q * C;
+  const float* m = mean2 + (size_t)b * C;
+  float s = 0.f;
+  for (int c = lane; c < C; c += 32) s = fmaf(__ldg(a + c), __ldg(m + c), s);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) row_mean[q] = s / denom;
+}
+
 int launch_row_mean(const float* fmap1, const float* fmap2, int B, int C, int HW, float* row_mean, float* mean2,
-                    cudaStream_t stream) {
+                    float* nhwc_scratch, cudaStream_t stream) {
+  if (nhwc_scratch) {   // channels-last maps; scratch holds strips * B * C floats (strips = min(128, HW / 2))
+    const int strips = HW / 2 < 128 ? (HW / 2 > 0 ? HW / 2 : 1) : 128;
+    channel_partial_nhwc_kernel<<<dim3(strips, B), 256, 0, stream>>>(fmap2, nhwc_scratch, C, HW, strips);
+    channel_finalize_nhwc_kernel<<<B, 256, 0, stream>>>(nhwc_scratch, mean2, C, HW, strips);
+    row_mean_nhwc_kernel<<<(unsigned)(((long long)B * HW + 7) / 8), 256, 0, stream>>>(fmap1, mean2, row_mean, C, HW, B,
+                                                                                     sqrtf(float(C)));
+    return launch_status("row_mean kernels (channels-last)");
+  }
   channel_mean_kernel<<<B * C, 256, 0, stream>>>(fmap2, mean2, HW);
   dim3 grid(ceil_div(HW, 32), B);
   row_mean_kernel<<<grid, 256, 0, stream>>>(fmap1, mean2, row_mean, C, HW, sqrtf(float(C)));

@@ -132,6 +132,34 @@ __global__ void __launch_bounds__(256) pack_kernel(const float* __restrict__ src
   }
 }
 
+// The same packing for channels-last feature maps (B, HW, C): the K-major rows are already there, only the rounding /
+// splitting and the padding of C to Kp remain.  One thread per packed element, consecutive threads along K.
+template <int MODE>
+__global__ void __launch_bounds__(256) pack_nhwc_kernel(const float* __restrict__ src1, const float* __restrict__ src2,
+                                                        void* __restrict__ dst1, void* __restrict__ dst2, int C, int Kp,
+                                                        size_t rows, size_t plane_elems, int* flag) {
+  if (flag && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) *flag = 0;
+  const float* __restrict__ src = blockIdx.y ? src2 : src1;
+  void* __restrict__ dst = blockIdx.y ? dst2 : dst1;
+  const size_t total = rows * Kp;
+  for (size_t o = (size_t)blockIdx.x * 256 + threadIdx.x; o < total; o += (size_t)gridDim.x * 256) {
+    const size_t row = o / Kp;
+    const int c = int(o - row * Kp);
+    const float v = c < C ? __ldg(src + row * C + c) : 0.f;
+    if (MODE == 3) {
+      reinterpret_cast<__nv_bfloat16*>(dst)[o] = __float2bfloat16_rn(v);
+    } else if (MODE == 4 || MODE == 5) {
+      const __half hi = __float2half_rn(fminf(fmaxf(v, -65504.f), 65504.f));
+      reinterpret_cast<__half*>(dst)[o] = hi;
+      if (MODE == 5) reinterpret_cast<__half*>(dst)[plane_elems + o] = __float2half_rn(v - __half2float(hi));
+    } else {
+      const float hi = round_tf32(v);
+      reinterpret_cast<float*>(dst)[o] = hi;
+      if (MODE == 2) reinterpret_cast<float*>(dst)[plane_elems + o] = round_tf32(v - hi);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------
 // GEMM + pooled epilogue
 // ---------------------------------------------------------------------------------------------------
@@ -590,6 +618,8 @@ TcLayout tc_layout(int B, int C, int HW, int mode) {
 
 int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H, int W, int num_levels,
                     float* const* levels, void* workspace, int mode, cudaStream_t stream) {
+  const bool fmaps_nhwc = (mode & WOFT_CORR_FMAPS_NHWC) != 0;
+  mode &= ~WOFT_CORR_FMAPS_NHWC;
   if (num_levels > kMaxTcLevels)
     return fail(WOFT_ERR_UNSUPPORTED, "tensor-core correlation supports at most %d levels (8x32 pooling tile)",
                 kMaxTcLevels);
@@ -608,7 +638,22 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   void* packB = ws + L.off_b;
 
   // ---- pack both fmaps into K-major planes (also clears the abort flag)
-  {
+  if (fmaps_nhwc) {
+    const size_t plane_elems = L.plane_bytes / L.elem_bytes, rows = (size_t)B * HW;
+    dim3 grid(148 * 8, 2);
+    if (mode == WOFT_CORR_BF16)
+      pack_nhwc_kernel<3><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, C, L.Kp, rows, plane_elems, flag);
+    else if (mode == WOFT_CORR_FP16)
+      pack_nhwc_kernel<4><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, C, L.Kp, rows, plane_elems, flag);
+    else if (mode == WOFT_CORR_FP16X3)
+      pack_nhwc_kernel<5><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, C, L.Kp, rows, plane_elems, flag);
+    else if (mode == WOFT_CORR_TF32X3)
+      pack_nhwc_kernel<2><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, C, L.Kp, rows, plane_elems, flag);
+    else
+      pack_nhwc_kernel<1><<<grid, 256, 0, stream>>>(fmap1, fmap2, packA, packB, C, L.Kp, rows, plane_elems, flag);
+    int rc = launch_status("pack_nhwc_kernel");
+    if (rc != WOFT_OK) return rc;
+  } else {
     dim3 grid(ceil_div(HW, 32), L.Kp / 32, 2 * B);
     const size_t plane_elems = L.plane_bytes / L.elem_bytes;
     if (mode == WOFT_CORR_BF16)

@@ -531,7 +531,10 @@ class FastWeightedRAFT:
             from .corr import CorrBlock as corr_block
         image1 = images[:images.shape[0] // 2]
         fmap1, fmap2 = self._features(images).chunk(2, dim=0)
-        corr_fn = corr_block(fmap1.contiguous(), fmap2.contiguous(), num_levels=net_.corr_levels, radius=net_.corr_radius)
+        if not (self.nhwc and os.environ.get("WOFT_NHWC_FMAPS", "1") == "1"
+                and (corr_block is _CorrBlock or getattr(corr_block, "func", None) is _CorrBlock)):
+            fmap1, fmap2 = fmap1.contiguous(), fmap2.contiguous()   # this library's CorrBlock takes channels-last maps as is
+        corr_fn = corr_block(fmap1, fmap2, num_levels=net_.corr_levels, radius=net_.corr_radius)
         nhwc = self.nhwc and isinstance(corr_fn, _CorrBlock) and net_.hidden_dim == net_.context_dim
         B, _, H, W = image1.shape
         coords0 = pixel_grid(B, H // 8, W // 8, image1.device)

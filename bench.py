@@ -17,6 +17,7 @@ Under torchrun each rank tracks its own synthetic sequence (weak scaling, no dat
 taken on the device and reduced with MAX over ranks.
 """
 import argparse
+import contextlib
 import json
 import os
 import subprocess
@@ -333,7 +334,9 @@ def run_woft(args, rank, world, local):
         barrier()
         start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         passes0 = trk.flow_passes
-        with ClockSampler(local) as sampler:
+        # clocks are sampled (nvidia-smi in a side thread) while the device-resident loop runs; the end-to-end loop is
+        # host-latency sensitive and runs right after it on the same clocks, without the sampler's subprocesses
+        with (ClockSampler(local) if name == "device" else contextlib.nullcontext()) as sampler:
             if name == "device":
                 torch.cuda.profiler.start()  # `ncu --profile-from-start off` then lists exactly the timed steps
             start.record()

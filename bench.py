@@ -377,12 +377,12 @@ def run_woft(args, rank, world, local):
                 "h2d_bytes_per_step": HEIGHT * WIDTH * 3, "d2h_bytes_per_step": 48,
                 "flow_passes_per_frame": results["e2e"]["flow_passes"] / args.steps,
                 "api": "woft_b200.tracker.PlanarTracker.track(host uint8 frame) -> 3x3 homography on the host"},
-        # hand-written kernels per tracked frame (profiles/r1_bench_launches_summary.md counts the same 191):
-        # input conversion, 2 first-layer convolutions, the weight head's first layer, pack + GEMM + 2 row-mean, 13 lookups,
+        # hand-written kernels per tracked frame (profiles/r1_bench_launches_summary.md counts the same 192):
+        # input conversion, 2 first-layer convolutions, the weight head's first layer, pack + GEMM + 3 row-mean, 13 lookups,
         # 15 instance norms x 3, 6 add+ReLU, per iteration 1 + 2 + 2 + 2 + 2 (7x7 flow conv, concats, GRU gates, GRU updates,
         # flow head products + gather) + the 2 initial concats, convex upsampling, 3 selection kernels, homography fit,
         # inlier fraction, 4 bias kernels, the context split (it replaces the 2 initial concats)
-        "gpu_launches": int(args.steps * (1 + 2 + 1 + 4 + 1 + 4 + (ITERS + 1) + 45 + 6 + ITERS * 9 + 1 + 3 + 2)),
+        "gpu_launches": int(args.steps * (1 + 2 + 1 + 4 + 1 + 5 + (ITERS + 1) + 45 + 6 + ITERS * 9 + 1 + 3 + 2)),
         "clocks": clocks,
         "roofline": k3,
         "kernels": kernels,

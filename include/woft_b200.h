@@ -9,7 +9,8 @@
  *   - all pointers are DEVICE pointers unless the parameter comment says "host"; tensors are dense, row-major
  *     (C-contiguous) fp32 in exactly the layout the reference uses at that seam;
  *   - the caller (PyTorch in this repo) owns every buffer, including workspaces; the library never allocates,
- *     frees or keeps a pointer after the call returns;
+ *     frees or keeps a pointer after the call returns (two stated exceptions: woft_corr_pyramid_static uses a
+ *     fixed scratch array inside the library, woft_corr_set_trace_buffer keeps the debug pointer it is given);
  *   - `stream` is a cudaStream_t passed as void*; work is enqueued on it and the call returns without
  *     synchronising;
  *   - return value: WOFT_OK or a negative-free error code below; `woft_last_error()` gives a thread-local,
@@ -86,7 +87,8 @@ int woft_corr_pyramid(const float* fmap1, const float* fmap2, int batch, int cha
  * Arguments are those of woft_corr_pyramid without the workspace: the scratch lives in a fixed 32 MiB device
  * array inside the library (held by every GPU that loads the library, until the process exits).
  *   - Shapes/modes whose woft_corr_workspace_bytes() exceeds 32 MiB are refused with WOFT_ERR_WORKSPACE; one
- *     1280x720 frame pair (90x160x256 feature maps) fits in the fp32, tf32 and bf16 modes, 3xTF32 does not.
+ *     1280x720 frame pair (90x160x256 feature maps) fits in the fp32, tf32, bf16, fp16 and fp16x3 modes (14.1 to
+ *     28.2 MiB), 3xTF32 (56.3 MiB) does not.
  *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress); make that first
  *     call with the device current and outside any stream capture.
  *   - All calls on a device share the one array.  Calls whose GPU work can overlap (different streams, or
@@ -98,8 +100,17 @@ int woft_corr_pyramid_static(const float* fmap1, const float* fmap2, int batch, 
 
 /* Synchronises `stream` and reports whether the last woft_corr_pyramid on `workspace` ran to completion.  The
  * tensor-core kernel bounds every pipeline wait (2 s) and raises a flag in the workspace instead of hanging;
- * this reads the flag back (one 4-byte device-to-host copy).  No counterpart in the reference. */
+ * this reads the flag back (one 4-byte device-to-host copy).  No counterpart in the reference.
+ * woft_corr_check_static is the same check after woft_corr_pyramid_static (whose scratch the caller never sees),
+ * on the current device. */
 int woft_corr_check(const void* workspace, void* stream);
+int woft_corr_check_static(void* stream);
+
+/* Debug aid, no counterpart in the reference: per-role timestamps (TMA producer / MMA issuer / epilogue) of the first
+ * four CTAs of the tensor-core correlation kernel.  `device_buffer` is caller-allocated, zeroed device memory of
+ * 4 * 64 * 6 unsigned long long (tile-major, nanoseconds of %globaltimer), or NULL to switch tracing off; the library
+ * keeps the pointer until it is replaced.  Every later woft_corr_pyramid[_static] on any stream writes into it. */
+void woft_corr_set_trace_buffer(unsigned long long* device_buffer);
 
 /* K3.  Replaces CorrBlock.__call__ + bilinear_sampler (corr.py:29-59, raft_core/utils/utils.py:59-73):
  * for every query pixel and level l a (2r+1)^2 window of level l, centred at coords / 2^l, bilinear,
@@ -212,8 +223,9 @@ int woft_instance_norm_relu(const float* x, int planes, int hw, float eps, int r
  *   src, dst   : (H, W, C) uint8, C <= 4           valid_mask : (H, W) uint8 0/1, may be NULL
  *   inv_matrix_host : HOST pointer to 9 doubles, row-major, mapping destination (x, y, 1) to source -- the inverse of
  *                     the matrix cv2.warpPerspective is given (it inverts it unless WARP_INVERSE_MAP is set)
- * Coordinates are quantised to 1/32 px as OpenCV does; pixel values differ from OpenCV's fixed-point blend by at
- * most one grey level. */
+ *                     (formed by cv::invert's cofactor formula, woft_b200.tracker.invert3x3_opencv, for identical bits)
+ * Integer arithmetic of OpenCV's remap throughout (1/32-px coordinates, 15-bit weight table, (v + 2^14) >> 15):
+ * frame and mask are bit-identical to cv2's. */
 int woft_warp_perspective_u8(const uint8_t* src, int height, int width, int channels, const double* inv_matrix_host,
                              uint8_t* dst, uint8_t* valid_mask, void* stream);
 

@@ -174,6 +174,24 @@ def gen_net(ref):
         flow, w2 = wrapper.compute_flow(img1, img2, mode="flow", do_sigmoid=False)
         wout["flow_flow"], wout["flow_w"] = _np(flow), _np(w2)
         wout["last_flow_shape"] = np.array([wrapper.last_flow_shape[k] for k in ("batch", "delta", "H", "W")])
+        # the padders (optical_flow/raft.py:221-271, raft_core/utils/utils.py:7-26) on a frame size that is not a
+        # multiple of 8: replicate padding, bilinear resize and crop, each through the reference wrapper
+        oimg1, oimg2 = make_frames(125, 163, 6)
+        wout["odd_img1_bgr"], wout["odd_img2_bgr"] = oimg1, oimg2
+        for pmode in ("RAFT", "crop"):
+            conf.padding_mode = pmode
+            flow, w2 = wrapper.compute_flow(oimg1, oimg2, mode="flow", do_sigmoid=False)
+            wout[f"pad_{pmode}_flow"], wout[f"pad_{pmode}_w"] = _np(flow), _np(w2)
+        conf.padding_mode = "nopad"
+        # 'Michal' cannot run through the reference wrapper with raft_type 'weighted': raft.py:150 unpads a mask that
+        # only the 'weighted_masked' network produces (AttributeError on None).  Its padder class is recorded directly.
+        mp = ref.flow.MichalPadder((1, 3, 125, 163))
+        g = torch.Generator().manual_seed(21)
+        a, b = torch.rand((1, 3, 125, 163), generator=g) * 255, torch.rand((1, 3, 125, 163), generator=g) * 255
+        pa, pb = mp.pad(a, b)
+        fl = torch.randn((1, 2, 128, 168), generator=g) * 3
+        wout["michal_in_a"], wout["michal_in_b"], wout["michal_pad_a"], wout["michal_pad_b"] = _np(a), _np(b), _np(pa), _np(pb)
+        wout["michal_flow_in"], wout["michal_flow_out"] = _np(fl), _np(mp.unpad(fl))
     np.savez_compressed(OUT / "wrapper_small.npz", **wout)
     print("wrapper_small", {k: v.shape for k, v in wout.items()})
 

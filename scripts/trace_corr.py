@@ -1,5 +1,6 @@
-"""Per-role timeline of corr_tc_kernel (debug): WOFT_CORR_TRACE=<file> makes the library dump globaltimer stamps of the
-first 4 CTAs: [producer tile begin, producer tile end, MMA begin, MMA issue end, epilogue begin, epilogue end]."""
+"""Per-role timeline of corr_tc_kernel (debug): woft_corr_set_trace_buffer hands the library a zeroed device buffer into
+which the first 4 CTAs write globaltimer stamps per tile:
+[producer tile begin, producer tile end, MMA begin, MMA issue end, epilogue begin, epilogue end]."""
 import os
 import sys
 from pathlib import Path
@@ -8,6 +9,7 @@ import numpy as np
 import torch
 
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+from woft_b200 import _lib  # noqa: E402
 from woft_b200.corr import CorrBlock  # noqa: E402
 
 dev = "cuda:0"
@@ -17,12 +19,13 @@ f2 = torch.randn((1, 256, 90, 160), generator=g, device=dev)
 for mode in sys.argv[1:] or ["bf16", "tf32", "tf32x3"]:
     CorrBlock(f1, f2, mode=mode)
     torch.cuda.synchronize()
-    path = f"gpurun_out/trace_{mode}.txt"
-    os.environ["WOFT_CORR_TRACE"] = path
+    buf = torch.zeros(4 * 64 * 6, dtype=torch.int64, device=dev)
+    _lib.load().woft_corr_set_trace_buffer(_lib.ptr(buf))
     CorrBlock(f1, f2, mode=mode)
     torch.cuda.synchronize()
-    del os.environ["WOFT_CORR_TRACE"]
-    rows = np.loadtxt(path, dtype=np.int64)
+    _lib.load().woft_corr_set_trace_buffer(None)
+    st_all = buf.cpu().numpy().reshape(4, 64, 6)
+    rows = np.array([[c, t, *st_all[c, t]] for c in range(4) for t in range(64) if st_all[c, t].any()], dtype=np.int64)
     rows = rows[rows[:, 0] == 0]
     t0 = rows[0, 2]
     st = (rows[:, 2:] - t0) / 1e3  # us

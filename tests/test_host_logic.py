@@ -90,3 +90,31 @@ def test_host_side_result_gather_two_ranks(tmp_path):
     port = 29500 + (os.getpid() % 2000)
     mp.spawn(_gather_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     assert (tmp_path / "ok").exists()
+
+
+def test_padders_match_reference_values(golden):
+    """Padder classes on CPU tensors against outputs of the reference classes (tests/golden/wrapper_small.npz)."""
+    import torch
+    from woft_b200.optical_flow import CropPadder, InputPadder, MichalPadder
+    gw = golden("wrapper_small")
+    a, b = torch.from_numpy(gw["michal_in_a"]), torch.from_numpy(gw["michal_in_b"])
+    mp = MichalPadder(a.shape)
+    pa, pb = mp.pad(a, b)
+    np.testing.assert_array_equal(pa.numpy(), gw["michal_pad_a"])
+    np.testing.assert_array_equal(pb.numpy(), gw["michal_pad_b"])
+    np.testing.assert_array_equal(mp.unpad(torch.from_numpy(gw["michal_flow_in"])).numpy(), gw["michal_flow_out"])
+    ip = InputPadder(a.shape)
+    xa, xb = ip.pad(a, b)
+    assert tuple(xa.shape[-2:]) == (128, 168) and torch.equal(ip.unpad(xa), a) and torch.equal(ip.unpad(xb), b)
+    assert torch.equal(xa[..., 0, :], xa[..., 1, :])   # replicate padding: 1 row on top, 2 at the bottom (sintel centring)
+    ca, cb = CropPadder(a.shape).pad(a, b)
+    assert tuple(ca.shape[-2:]) == (120, 160) and torch.equal(ca, a[..., :120, :160])
+
+
+def test_opencv_order_inverse_is_bit_identical_to_cv_invert():
+    import cv2
+    from woft_b200.tracker import invert3x3_opencv
+    rng = np.random.RandomState(0)
+    for _ in range(2000):
+        M = np.eye(3) + rng.randn(3, 3) * np.array([[0.2, 0.2, 50], [0.2, 0.2, 50], [1e-4, 1e-4, 0.05]])
+        np.testing.assert_array_equal(invert3x3_opencv(M), cv2.invert(M)[1])

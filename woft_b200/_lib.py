@@ -31,6 +31,8 @@ SIGNATURES = {
     "woft_corr_pyramid_static": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, _FLOATP_ARRAY, c_void_p,
                                          c_int, c_void_p]),
     "woft_corr_check": (c_int, [c_void_p, c_void_p]),
+    "woft_corr_check_static": (c_int, [c_void_p]),
+    "woft_corr_set_trace_buffer": (None, [c_void_p]),
     "woft_corr_lookup": (c_int, [_FLOATP_ARRAY, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                  c_int, c_void_p]),
     "woft_alt_corr_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,

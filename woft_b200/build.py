@@ -48,7 +48,7 @@ def build(force=False, verbose=False):
         if LIB.exists():
             return LIB  # GPU box without a toolkit: use the library that travelled with the tree
         raise RuntimeError("nvcc not found and no prebuilt libwoft_b200.so present")
-    cmd = [nvcc, "-O3", "-std=c++17", *ARCH_FLAGS, "-lineinfo", "-Xcompiler", "-fPIC", "-shared",
+    cmd = [nvcc, "-O3", "-std=c++17", "--threads", "0", *ARCH_FLAGS, "-lineinfo", "-Xcompiler", "-fPIC", "-shared",
            "-I", str(PKG.parent / "include"), "-o", str(LIB)]
     if verbose:
         cmd += ["-Xptxas", "-v"]

@@ -21,6 +21,7 @@ int fail(int code, const char* fmt, ...) {
 int corr_pyramid_simt(const float*, const float*, int, int, int, int, int, float* const*, cudaStream_t);
 int corr_pyramid_tc(const float*, const float*, int, int, int, int, int, float* const*, void*, int, cudaStream_t);
 size_t corr_tc_workspace_bytes(int, int, int, int);
+void corr_tc_set_trace_buffer(unsigned long long*);
 int launch_row_mean(const float*, const float*, int, int, int, float*, float*, float*, cudaStream_t);
 
 static size_t simt_workspace_bytes(int B, int C) { return 256 + ((size_t)B * C * 4 + 255) / 256 * 256; }
@@ -82,6 +83,10 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
     rc = launch_row_mean(fmap1, fmap2, batch, channels, height * width, row_mean, mean2, scratch, s);
   }
   return rc;
+}
+
+extern "C" void woft_corr_set_trace_buffer(unsigned long long* device_buffer) {
+  woft::corr_tc_set_trace_buffer(device_buffer);
 }
 
 extern "C" int woft_corr_check(const void* workspace, void* stream) {

@@ -9,7 +9,8 @@
 
 namespace woft {
 
-// thread-local message behind woft_last_error(); no other mutable library state exists
+// thread-local message behind woft_last_error().  The only other mutable library state: the per-device address of
+// the built-in scratch of woft_corr_pyramid_static (corr_static.cu) and the debug trace pointer of corr_tc.cu.
 char* last_error_buffer();
 int fail(int code, const char* fmt, ...);
 

@@ -58,3 +58,14 @@ extern "C" int woft_corr_pyramid_static(const float* fmap1, const float* fmap2, 
   return woft_corr_pyramid(fmap1, fmap2, batch, channels, height, width, num_levels, levels, row_mean, scratch,
                            kStaticScratchBytes, mode, stream);
 }
+
+// The tensor-core kernel bounds its pipeline waits and raises a status word at the head of its scratch instead of
+// hanging; woft_corr_check reads that word back but needs the scratch pointer, which a caller of the _static variant
+// never sees.  This is the same check on the built-in scratch of the current device.
+extern "C" int woft_corr_check_static(void* stream) {
+  using namespace woft;
+  void* scratch = nullptr;
+  const int rc = static_scratch_pointer(&scratch);
+  if (rc != WOFT_OK) return rc;
+  return woft_corr_check(scratch, stream);
+}

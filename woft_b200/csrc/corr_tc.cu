@@ -197,6 +197,16 @@ __device__ __forceinline__ void store_ring_wait(int nslot) {
     ptx::tma_store_wait_read<0>();
 }
 
+struct TcKnobs {
+  int tma_levels;
+  bool a_resident;
+  int unit;
+};
+const TcKnobs& tc_knobs();
+// Per-role timeline buffer (woft_corr_set_trace_buffer): caller-allocated device memory, null = tracing off.
+static unsigned long long* g_trace_buffer = nullptr;
+void corr_tc_set_trace_buffer(unsigned long long* buf) { __atomic_store_n(&g_trace_buffer, buf, __ATOMIC_RELEASE); }
+
 struct TileCoord {
   int b, m0, h0, w0;
 };
@@ -698,8 +708,7 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
                                             : CU_TENSOR_MAP_SWIZZLE_NONE;
     cuuint64_t dims[4] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)HW, (cuuint64_t)B};
     cuuint32_t box[4] = {(cuuint32_t)(TW >> l), 1, BM, 1};
-    const char* env_pool = getenv("WOFT_CORR_POOL_TMA");  // bit l set => level l may use TMA stores
-    const int tma_levels = env_pool ? atoi(env_pool) : 0xF;
+    const int tma_levels = tc_knobs().tma_levels;  // bit l set => level l may use TMA stores
     p.tma_ok[l] = (((tma_levels >> l) & 1) && h > 0 && w > 0 && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0 &&
                    encode(enc, &p.tmOut[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, 4, levels[l], dims, box, swz))
                       ? 1
@@ -731,8 +740,7 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   p.unit = 1;
   p.stages = 3;
   p.nslot = 3;
-  const char* env_res = getenv("WOFT_CORR_A_RESIDENT");
-  const bool want_res = p.n_pairs == 1 && env_res && env_res[0] == '1';  // off by default: measured slower
+  const bool want_res = p.n_pairs == 1 && tc_knobs().a_resident;  // off by default: measured slower
   if (want_res) {
     const int a_bytes = p.k_blocks * A_STAGE;
     if (a_bytes + 3 * B_STAGE + 3 * SLOT + fixed <= TC_SMEM_LIMIT) {
@@ -743,9 +751,8 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
       p.nslot = 2;
     }
     if (p.a_resident) {
-      const char* env_unit = getenv("WOFT_CORR_UNIT");
       const int n_tiles = p.h_tiles * p.w_tiles;
-      int unit = env_unit ? atoi(env_unit) : 6;
+      int unit = tc_knobs().unit;
       if (unit < 1) unit = 1;
       // units must not straddle M tiles more than necessary: prefer a divisor of the N-tile count near `unit`
       for (int u = unit; u >= 1; --u)
@@ -763,13 +770,9 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   const int chunks = ceil_div(p.total_tiles, p.unit);
   const int grid = chunks < sms ? chunks : sms;
-  const char* trace_path = getenv("WOFT_CORR_TRACE");  // debug aid: per-role timestamps of the first 4 CTAs
-  p.trace = nullptr;
-  const size_t trace_bytes = 4 * 64 * 6 * sizeof(unsigned long long);
-  if (trace_path) {
-    WOFT_CUDA_CHECK(cudaMalloc(&p.trace, trace_bytes));
-    WOFT_CUDA_CHECK(cudaMemsetAsync(p.trace, 0, trace_bytes, stream));
-  }
+  // debug aid: per-role timestamps of the first 4 CTAs into a buffer the caller handed over beforehand
+  // (4 * 64 * 6 unsigned long long, zeroed by the caller); the library itself never allocates
+  p.trace = __atomic_load_n(&g_trace_buffer, __ATOMIC_ACQUIRE);
   const bool debug = p.a_resident || p.trace != nullptr || p.stages != 3 || p.nslot != 3 || p.unit != 1;
   if (debug) {
     WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
@@ -778,21 +781,23 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
     corr_tc_kernel<false><<<grid, TC_THREADS, smem_bytes, stream>>>(p);
   }
   int rc = launch_status("corr_tc_kernel");
-  if (trace_path && rc == WOFT_OK) {
-    static unsigned long long host_trace[4 * 64 * 6];
-    WOFT_CUDA_CHECK(cudaMemcpyAsync(host_trace, p.trace, trace_bytes, cudaMemcpyDeviceToHost, stream));
-    WOFT_CUDA_CHECK(cudaStreamSynchronize(stream));
-    WOFT_CUDA_CHECK(cudaFree(p.trace));
-    if (FILE* f = fopen(trace_path, "w")) {
-      for (int c = 0; c < 4; ++c)
-        for (int t = 0; t < 64; ++t) {
-          const unsigned long long* r = host_trace + (c * 64 + t) * 6;
-          if (r[0] || r[2] || r[4]) fprintf(f, "%d %d %llu %llu %llu %llu %llu %llu\n", c, t, r[0], r[1], r[2], r[3], r[4], r[5]);
-        }
-      fclose(f);
-    }
-  }
   return rc;
+}
+
+// Debug knobs of the experiments in DESIGN.md 4, read from the environment ONCE per process (never on the launch path):
+//   WOFT_CORR_POOL_TMA (bit l: level l may use TMA stores), WOFT_CORR_A_RESIDENT=1, WOFT_CORR_UNIT=<tiles per unit>
+const TcKnobs& tc_knobs() {
+  static const TcKnobs k = [] {
+    TcKnobs v;
+    const char* e = getenv("WOFT_CORR_POOL_TMA");
+    v.tma_levels = e ? atoi(e) : 0xF;
+    e = getenv("WOFT_CORR_A_RESIDENT");
+    v.a_resident = e && e[0] == '1';
+    e = getenv("WOFT_CORR_UNIT");
+    v.unit = e ? atoi(e) : 6;
+    return v;
+  }();
+  return k;
 }
 
 size_t corr_tc_workspace_bytes(int B, int C, int HW, int mode) { return tc_layout(B, C, HW, mode).total; }

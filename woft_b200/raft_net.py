@@ -274,7 +274,8 @@ def seeded_state_dict(model, seed=0):
     Values depend only on (seed, parameter name, shape), not on construction order or torch's global RNG,
     so the reference model and this one can be given identical weights.  Distributions follow what the
     reference's constructors would draw: encoder convs ~ N(0, 2/fan_out) (extractor.py:143-145), every other
-    conv and all biases ~ U(+-1/sqrt(fan_in)) (torch's Conv2d default), norm layers identity."""
+    conv and all biases ~ U(+-1/sqrt(fan_in)) (torch's Conv2d default); BatchNorm layers get weight ~ U(0.8, 1.2),
+    bias and running_mean ~ N(0, 0.1), running_var ~ U(0.5, 1.5) as a trained checkpoint would hold some."""
     import hashlib
 
     ref_sd = model.state_dict()
@@ -283,12 +284,17 @@ def seeded_state_dict(model, seed=0):
         digest = hashlib.sha256(f"{seed}:{name}".encode()).digest()
         g = torch.Generator().manual_seed(int.from_bytes(digest[:8], "little") % (2 ** 63))
         is_norm = "norm" in name or "downsample.1" in name
-        if name.endswith(("num_batches_tracked", "running_mean")):
+        if name.endswith("num_batches_tracked"):
             t = torch.zeros_like(ref)
+        elif name.endswith("running_mean"):
+            t = torch.randn(ref.shape, generator=g) * 0.1
         elif name.endswith("running_var"):
-            t = torch.ones_like(ref)
+            t = 0.5 + torch.rand(ref.shape, generator=g)
         elif is_norm:
-            t = torch.ones_like(ref) if name.endswith("weight") else torch.zeros_like(ref)
+            # eval-mode BatchNorm of the context encoder (extractor.py:118-192): non-trivial affine parameters and
+            # statistics, so that folding them into the convolutions is exercised by every parity test
+            t = 0.8 + 0.4 * torch.rand(ref.shape, generator=g) if name.endswith("weight") else \
+                torch.randn(ref.shape, generator=g) * 0.1
         elif ref.dim() == 4 and name.startswith(("fnet.", "cnet.")):
             fan_out = ref.shape[0] * ref.shape[2] * ref.shape[3]
             t = torch.randn(ref.shape, generator=g) * (2.0 / fan_out) ** 0.5

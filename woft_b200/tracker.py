@@ -145,6 +145,28 @@ def default_config(flow_config, device_prewarp=True):
                            fused_select=device_prewarp)
 
 
+def invert3x3_opencv(H):
+    """Inverse of a 3x3 matrix by the cofactor formula in the order of operations of cv::invert (the matrix
+    cv2.warpPerspective inverts internally), so that the device pre-warp sees bit-identical coefficients."""
+    S = np.asarray(H, dtype=np.float64)
+    d = (S[0, 0] * (S[1, 1] * S[2, 2] - S[1, 2] * S[2, 1]) - S[0, 1] * (S[1, 0] * S[2, 2] - S[1, 2] * S[2, 0])
+         + S[0, 2] * (S[1, 0] * S[2, 1] - S[1, 1] * S[2, 0]))
+    if d == 0.0:
+        raise np.linalg.LinAlgError("singular pre-warp homography")
+    d = 1.0 / d
+    t = np.empty((3, 3), dtype=np.float64)
+    t[0, 0] = (S[1, 1] * S[2, 2] - S[1, 2] * S[2, 1]) * d
+    t[0, 1] = (S[0, 2] * S[2, 1] - S[0, 1] * S[2, 2]) * d
+    t[0, 2] = (S[0, 1] * S[1, 2] - S[0, 2] * S[1, 1]) * d
+    t[1, 0] = (S[1, 2] * S[2, 0] - S[1, 0] * S[2, 2]) * d
+    t[1, 1] = (S[0, 0] * S[2, 2] - S[0, 2] * S[2, 0]) * d
+    t[1, 2] = (S[0, 2] * S[1, 0] - S[0, 0] * S[1, 2]) * d
+    t[2, 0] = (S[1, 0] * S[2, 1] - S[1, 1] * S[2, 0]) * d
+    t[2, 1] = (S[0, 1] * S[2, 0] - S[0, 0] * S[2, 1]) * d
+    t[2, 2] = (S[0, 0] * S[1, 1] - S[0, 1] * S[1, 0]) * d
+    return t
+
+
 def prewarp_on_device(frame_u8, H, want_mask=True):
     """(H,W,3) uint8 device tensor warped by the 3x3 matrix `H` the way cv2.warpPerspective(frame, H, (W,H),
     flags=INTER_LINEAR) does, and the `> 0` mask of an image of ones warped alike (:89-95)."""
@@ -154,7 +176,7 @@ def prewarp_on_device(frame_u8, H, want_mask=True):
     frame_u8 = frame_u8.contiguous()
     out = torch.empty_like(frame_u8)
     mask = torch.empty((h, w), dtype=torch.uint8, device=frame_u8.device) if want_mask else None
-    inv = np.ascontiguousarray(np.linalg.inv(np.asarray(H, dtype=np.float64)))
+    inv = invert3x3_opencv(H)
     with torch.cuda.device(frame_u8.device):
         rc = _lib.load().woft_warp_perspective_u8(_lib.ptr(frame_u8), h, w, c,
                                                   inv.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), _lib.ptr(out),

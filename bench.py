@@ -35,6 +35,11 @@ sys.path.insert(0, str(ROOT))
 HEIGHT, WIDTH, ITERS = 720, 1280, 12
 METRIC = "tracked frames/s @1280x720"
 LOOKUP_BYTES_PER_QUERY = 4 * 10 * 10 * 4 + 8 + 324 * 4  # 2904 B per query pixel per call
+# one string for both arms: the driver compares the two `config.workload` fields
+WORKLOAD = ("configs[1]: single RAFT flow+uncertainty pass on a synthetic 1280x720 frame pair (160x90x256 feature maps, "
+            "12 GRU iters, 13 lookups) + correspondence mask + 500-point Sobol pick + weighted homography fit + inlier "
+            "test, one independent sequence per GPU")
+WEIGHTS = "seeded random init (WOFT checkpoints not shipped)"
 
 
 def make_sequence(n_frames, seed):
@@ -58,7 +63,7 @@ def make_sequence(n_frames, seed):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while a timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms while a timed region runs."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
@@ -69,7 +74,7 @@ class ClockSampler:
     def __enter__(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._pump, daemon=True).start()
         except OSError:
@@ -280,96 +285,135 @@ def run_reference(args, rank, world):
     dt = time.perf_counter() - t0
     fps = done / dt
     cores = torch.get_num_threads()
-    sample = (f"{done} full 1280x720 frames ({ITERS} iters) per the oracle port of the reference's CPU path, "
-              f"{cores} threads" + ("" if done == args.steps and warm == args.warmup else
+    sample = (f"{done} full 1280x720 frames ({ITERS} iters) per the oracle port of the reference's CPU path "
+              f"(oracle/cpu_pipeline.py driving the layer-by-layer mirror of the reference network on CPU; the mirror "
+              f"evaluates the upsampling-mask head on the last iteration only, the reference on all 12, so the port is "
+              f"slightly faster than the reference would be), {cores} threads" + ("" if done == args.steps and warm == args.warmup else
                                     f"; stopped early by the {budget:.0f} s budget (asked {args.steps} steps, {args.warmup} warm-up)"))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": round(fps, 4), "unit": "frames/s", "n_gpus": args.gpus,
         "steps": done, "warmup": warm, "ms_per_step": round(1e3 * dt / done, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "configs[1]: single RAFT flow+uncertainty pass on a synthetic 1280x720 frame pair "
-                               "(160x90x256 feature maps, 12 GRU iters) + 500-point weighted homography fit",
-                   "weights": "seeded random init (WOFT checkpoints not shipped)"},
+        "config": {"workload": WORKLOAD, "weights": WEIGHTS},
         "cpu_baseline": {"value": round(fps, 4), "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": round(fps, 4), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}), flush=True)
+
+
+def count_launches(torch, step, dev):
+    """Kernels launched by one step, counted from the CUPTI activity records of one profiled (untimed) step:
+    (kernels of this library, all kernels).  Works for CUDA-graph replays too (kernel records carry the names)."""
+    from torch.profiler import ProfilerActivity, profile
+    torch.cuda.synchronize(dev)
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        step(0)
+        torch.cuda.synchronize(dev)
+    own = total = 0
+    for ev in prof.events():
+        if ev.device_type == torch.autograd.DeviceType.CUDA and not ev.name.lower().startswith(("memcpy", "memset")):
+            total += 1
+            own += "woft::" in ev.name
+    return own, total
+
+
+def time_tracker(torch, args, rank, world, local, corr_mode, tf32_convs, with_clocks):
+    """Device-resident and end-to-end frames/s of the tracker in one arithmetic configuration."""
+    import functools
+    from woft_b200 import tracker as wtracker
+    from woft_b200.corr import CorrBlock
+    from woft_b200.optical_flow import RAFTWrapper
+    from woft_b200.sharding import max_over_ranks
+    dev = torch.device("cuda", local)
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = tf32_convs
+    try:
+        flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False, alternate_corr=False),
+                                    model=None, seeded_weights=0, iters=ITERS, padding_mode="nopad")
+        flower = RAFTWrapper(flow_conf, device=dev, use_cuda_graph=True,
+                             corr_block=functools.partial(CorrBlock, mode=corr_mode), tf32=tf32_convs)
+        trk = wtracker.PlanarTracker(wtracker.default_config(flow_conf), flower=flower)
+        n_seq_frames = 8
+        base, frames, mask = make_sequence(n_seq_frames, seed=rank)
+        trk.init(base, mask)
+        base_dev = torch.from_numpy(base).to(dev)
+        frames_dev = [torch.from_numpy(f).to(dev) for f in frames]
+        pw_all = torch.ones((HEIGHT, WIDTH), dtype=torch.bool, device=dev)
+
+        def device_step(i):
+            return trk.estimate_global_fused(base_dev, frames_dev[i % n_seq_frames], pw_all)
+
+        def e2e_step(i):
+            return trk.track(frames[i % n_seq_frames])
+
+        results, clocks = {}, None
+        for name, step in (("device", device_step), ("e2e", e2e_step)):
+            for i in range(args.warmup):
+                step(i)
+            torch.cuda.synchronize(dev)
+            barrier()
+            start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            passes0 = trk.flow_passes
+            # clocks are sampled (nvidia-smi in a side thread) while the device-resident loop runs; the end-to-end loop
+            # is host-latency sensitive and runs right after it on the same clocks, without the sampler's subprocesses
+            sample = with_clocks and name == "device"
+            with (ClockSampler(local) if sample else contextlib.nullcontext()) as sampler:
+                if sample:
+                    torch.cuda.profiler.start()  # `ncu --profile-from-start off` then lists exactly the timed steps
+                start.record()
+                for i in range(args.steps):
+                    step(i)
+                stop.record()
+                torch.cuda.synchronize(dev)
+                if sample:
+                    torch.cuda.profiler.stop()
+            barrier()
+            seconds = max_over_ranks(start.elapsed_time(stop) * 1e-3, device=dev)
+            results[name] = {"seconds": seconds, "flow_passes": trk.flow_passes - passes0}
+            if sample:
+                clocks = sampler.summary()
+        results["launches"] = count_launches(torch, device_step, dev) if rank == 0 else (0, 0)
+        return results, clocks
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
 
 
 def run_woft(args, rank, world, local):
     import torch
     from woft_b200 import build as wbuild
     wbuild.build()
-    from woft_b200 import tracker as wtracker
-    from woft_b200.corr import CorrBlock
-    from woft_b200.optical_flow import RAFTWrapper
-    import functools
-
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
     peaks = load_peaks()
-    flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False, alternate_corr=False),
-                                model=None, seeded_weights=0, iters=ITERS, padding_mode="nopad")
-    flower = RAFTWrapper(flow_conf, device=dev, use_cuda_graph=True,
-                         corr_block=functools.partial(CorrBlock, mode=args.corr_mode))
-    trk = wtracker.PlanarTracker(wtracker.default_config(flow_conf), flower=flower)
-    n_seq_frames = 8
-    base, frames, mask = make_sequence(n_seq_frames, seed=rank)
-    trk.init(base, mask)
-    base_dev = torch.from_numpy(base).to(dev)
-    frames_dev = [torch.from_numpy(f).to(dev) for f in frames]
-    pw_all = torch.ones((HEIGHT, WIDTH), dtype=torch.bool, device=dev)
-
-    def device_step(i):
-        return trk.estimate_global_fused(base_dev, frames_dev[i % n_seq_frames], pw_all)
-
-    def e2e_step(i):
-        return trk.track(frames[i % n_seq_frames])
-
-    results = {}
-    clocks = None
-    for name, step in (("device", device_step), ("e2e", e2e_step)):
-        for i in range(args.warmup):
-            step(i)
-        torch.cuda.synchronize(dev)
-        barrier()
-        start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        passes0 = trk.flow_passes
-        # clocks are sampled (nvidia-smi in a side thread) while the device-resident loop runs; the end-to-end loop is
-        # host-latency sensitive and runs right after it on the same clocks, without the sampler's subprocesses
-        with (ClockSampler(local) if name == "device" else contextlib.nullcontext()) as sampler:
-            if name == "device":
-                torch.cuda.profiler.start()  # `ncu --profile-from-start off` then lists exactly the timed steps
-            start.record()
-            for i in range(args.steps):
-                step(i)
-            stop.record()
-            torch.cuda.synchronize(dev)
-            if name == "device":
-                torch.cuda.profiler.stop()
-        barrier()
-        from woft_b200.sharding import max_over_ranks
-        seconds = max_over_ranks(start.elapsed_time(stop) * 1e-3, device=dev)
-        results[name] = {"seconds": seconds, "flow_passes": trk.flow_passes - passes0}
-        if name == "device":
-            clocks = sampler.summary()
+    results, clocks = time_tracker(torch, args, rank, world, local, args.corr_mode, True, True)
+    # the same frames in the reference's precision class: error-compensated correlation GEMM (fp32-class result) and
+    # convolutions with TF32 switched off; every rank takes part (barriers inside), rank 0 reports
+    fp32 = None
+    if not args.no_fp32_class:
+        fp32, _ = time_tracker(torch, args, rank, world, local, "fp16x3", False, False)
 
     if rank != 0:
         return
     k3, kernels, peak_src = kernel_rooflines(torch, dev, args.corr_mode, peaks)
     k3["peak_source"] = f"MEASURED_PEAKS.json ({peak_src})"
+    own, total = results["launches"]
     out = {
         "metric": METRIC,
         "value": round(world * args.steps / results["device"]["seconds"], 3),
         "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(1e3 * results["device"]["seconds"] / args.steps, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": {"tf32": "tf32", "tf32x3": "f32 (3xTF32)", "bf16": "bf16", "fp16": "f16", "fp16x3": "f32 (3xFP16)", "fp32": "f32"}[args.corr_mode],
+        "dtype": "tf32 (convolution operands; correlation GEMM operands " + args.corr_mode + "; fp32 accumulation)",
         "data": "synthetic",
-        "config": {"workload": "configs[1]: single RAFT flow+uncertainty pass on a synthetic 1280x720 frame pair "
-                               "(160x90x256 feature maps, 12 GRU iters, 13 lookups) + correspondence mask + 500-point "
-                               "Sobol pick + weighted homography fit + inlier test, one independent sequence per GPU",
-                   "corr_mode": args.corr_mode, "weights": "seeded random init (WOFT checkpoints not shipped)",
-                   "convolutions": "cuDNN, torch defaults (TF32 allowed)", "cuda_graph": True,
+        "config": {"workload": WORKLOAD,
+                   "corr_mode": args.corr_mode, "weights": WEIGHTS,
+                   "convolutions": "TF32 tensor cores (hand-written tcgen05 implicit GEMMs where fast_net.py uses them, "
+                                   "cuDNN with TF32 allowed elsewhere)", "cuda_graph": True,
+                   "precision": "stated-tolerance mode (flow within 0.05 px of the fp32 reference, "
+                                "tests/test_gpu_parity.py::test_benched_configuration_parity_720p); the fp32-class "
+                                "figures of the same workload are under `fp32_class`",
+                   "device_loop": "`value` times PlanarTracker.estimate_global_fused on frames resident in HBM: no "
+                                  "pre-warp (identity) and an all-ones pre-warp mask; `e2e` runs the whole of "
+                                  "PlanarTracker.track including the device pre-warp by the last good homography",
                    "l2": "step working set (1.1 GB correlation pyramid) exceeds the 126 MB L2, no flush between "
                          "steps; per-kernel roofline launches are preceded by a 256 MiB L2 flush",
                    "flow_passes_per_frame": results["device"]["flow_passes"] / args.steps},
@@ -377,21 +421,31 @@ def run_woft(args, rank, world, local):
                 "h2d_bytes_per_step": HEIGHT * WIDTH * 3, "d2h_bytes_per_step": 48,
                 "flow_passes_per_frame": results["e2e"]["flow_passes"] / args.steps,
                 "api": "woft_b200.tracker.PlanarTracker.track(host uint8 frame) -> 3x3 homography on the host"},
-        # hand-written kernels per tracked frame (profiles/r1_bench_launches_summary.md counts the same 192):
-        # input conversion, 2 first-layer convolutions, the weight head's first layer, pack + GEMM + 3 row-mean, 13 lookups,
-        # 15 instance norms x 3, 6 add+ReLU, per iteration 1 + 2 + 2 + 2 + 2 (7x7 flow conv, concats, GRU gates, GRU updates,
-        # flow head products + gather) + the 2 initial concats, convex upsampling, 3 selection kernels, homography fit,
-        # inlier fraction, 4 bias kernels, the context split (it replaces the 2 initial concats)
-        "gpu_launches": int(args.steps * (1 + 2 + 1 + 4 + 1 + 5 + (ITERS + 1) + 45 + 6 + ITERS * 9 + 1 + 3 + 2)),
+        # counted, not derived: kernel activity records of one profiled step of the timed loop (count_launches)
+        "gpu_launches": int(own * args.steps),
+        "gpu_launches_per_step": {"this_library": own, "all_kernels": total,
+                                  "how": "CUPTI kernel records of one extra, untimed step of the device loop"},
         "clocks": clocks,
         "roofline": k3,
         "kernels": kernels,
     }
+    if fp32 is not None:
+        out["fp32_class"] = {
+            "value": round(world * args.steps / fp32["device"]["seconds"], 3), "unit": "frames/s",
+            "ms_per_step": round(1e3 * fp32["device"]["seconds"] / args.steps, 3),
+            "e2e": round(world * args.steps / fp32["e2e"]["seconds"], 3),
+            "config": "correlation fp16x3 (error-compensated, fp32-class), torch.backends.cudnn.allow_tf32=False, "
+                      "hand-written TF32 convolution kernels off; flow within 0.01 px of the fp32 reference",
+            "gpu_launches_per_step": {"this_library": fp32["launches"][0], "all_kernels": fp32["launches"][1]}}
     if world == 1 and not args.no_cpu_baseline:
-        times, cores = cpu_frame_seconds(2)
-        out["cpu_baseline"] = {"value": round(1.0 / min(times), 4), "unit": "frames/s", "cores": cores, "kind": "port",
-                               "sample": f"2 full 1280x720 frames (12 iters) through the oracle port of the reference's "
-                                         f"CPU path, best of 2: {min(times):.2f} s/frame on {cores} threads"}
+        n_cpu = 5
+        times, cores = cpu_frame_seconds(n_cpu)
+        rest = times[1:]
+        out["cpu_baseline"] = {"value": round(len(rest) / sum(rest), 4), "unit": "frames/s", "cores": cores, "kind": "port",
+                               "sample": f"{n_cpu} full 1280x720 frames (12 iters) through the oracle port of the "
+                                         f"reference's CPU path (oracle/cpu_pipeline.py), first frame discarded as "
+                                         f"warm-up, mean of the other {len(rest)}: {sum(rest) / len(rest):.2f} s/frame "
+                                         f"on {cores} threads"}
     print(json.dumps(out), flush=True)
 
 
@@ -404,6 +458,7 @@ def main():
     ap.add_argument("--corr-mode", default=os.environ.get("WOFT_CORR_MODE", "fp16"),
                     choices=["tf32", "tf32x3", "bf16", "fp16", "fp16x3", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fp32-class", action="store_true", help="skip the second, fp32-class timing of the same workload")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "woft" else args.warmup
     if args.impl == "reference":

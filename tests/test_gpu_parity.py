@@ -192,6 +192,35 @@ def test_alt_corr_forward_vs_oracle():
     np.testing.assert_allclose(a.cpu().numpy(), m.cpu().numpy(), atol=2e-4)
 
 
+def test_alt_corr_forward_vs_reference_extension():
+    """Row a8 pinned by the reference itself: `alt_cuda_corr` compiled from the reference's own two source files
+    (oracle/build_ref.py -> oracle/_ref/alt_cuda_corr.so, built in the container, shipped with the tree) runs here as
+    the oracle of woft_alt_corr_forward and of the pure-torch restatement woft_oracle.alt_corr_forward, on batched,
+    multi-coordinate and out-of-bounds inputs (alt_cuda_corr/correlation.cpp:23-33, correlation_kernel.cu:18-119)."""
+    from oracle import build_ref
+    from woft_b200.corr import alt_cuda_corr
+    ref = build_ref.load()
+    if ref is None:
+        pytest.skip("oracle/_ref/alt_cuda_corr.so was not built (python -m oracle.build_ref in the build container): "
+                    "PARITY OF alt_corr_forward IS NOT PINNED BY THE REFERENCE IN THIS RUN")
+    g = torch.Generator().manual_seed(7)
+    for (B, C, H1, W1, H2, W2, N, r, spread) in ((2, 64, 16, 24, 8, 12, 1, 4, 1.0), (1, 256, 12, 20, 12, 20, 2, 4, 1.0),
+                                                 (1, 32, 9, 13, 5, 7, 1, 3, 1.0), (1, 96, 8, 8, 8, 8, 1, 4, 3.0)):
+        f1 = torch.randn((B, H1, W1, C), generator=g)
+        f2 = torch.randn((B, H2, W2, C), generator=g)
+        # `spread` 3: a third of the windows start outside the map
+        coords = (torch.rand((B, N, H1, W1, 2), generator=g) * spread - (spread - 1) / 2) * torch.tensor([W2 - 1.0, H2 - 1.0])
+        f1d, f2d, cd = f1.to(DEV), f2.to(DEV), coords.to(DEV)
+        want, = ref.forward(f1d, f2d, cd, r)
+        torch.cuda.synchronize()
+        got, = alt_cuda_corr.forward(f1d, f2d, cd, r)
+        assert got.shape == want.shape
+        scale = C ** 0.5
+        np.testing.assert_allclose(got.cpu().numpy() / scale, want.cpu().numpy() / scale, atol=2e-5)
+        np.testing.assert_allclose(wo.alt_corr_forward(f1, f2, coords, r).numpy() / scale, want.cpu().numpy() / scale,
+                                   atol=2e-5)
+
+
 # ----------------------------------------------------------------------------------------------------
 # K4 homography
 # ----------------------------------------------------------------------------------------------------
@@ -800,6 +829,56 @@ def test_tracked_frame_matches_cpu_pipeline():
         assert meta.global_H_success == ok_cpu
         err = wo.corner_error(torch.from_numpy(H_gpu), torch.from_numpy(H_cpu), W, H)
         assert err <= 0.05, f"tracked-frame homography differs from the CPU pipeline by {err} px at the corners"
+
+
+@pytest.fixture(scope="module")
+def cpu_frame_720p():
+    """One 1280x720 pair of bench.py's synthetic sequence through the CPU oracle pipeline (about 5 s of host time)."""
+    import bench
+    from oracle import cpu_pipeline
+    base, frames, mask = bench.make_sequence(1, 0)
+    net = cpu_pipeline.make_net(0)
+    torch.set_num_threads(max(1, min(16, torch.get_num_threads())))
+    t1 = torch.from_numpy(base[:, :, ::-1].copy()).permute(2, 0, 1).float()[None]
+    t2 = torch.from_numpy(frames[0][:, :, ::-1].copy()).permute(2, 0, 1).float()[None]
+    _, flow_up, _, w_up = wo.flow_pass(net, t1, t2, iters=12)
+    H_cpu, ok_cpu, _ = cpu_pipeline.track_frame(net, base, frames[0], mask, np.eye(3), 12)
+    return base, frames[0], mask, flow_up, w_up, H_cpu, ok_cpu
+
+
+@pytest.mark.parametrize("corr_mode,tf32,epe_tol,corner_tol", [("fp16", True, 0.05, 0.05), ("fp16x3", False, 0.01, 0.05)])
+def test_benched_configuration_parity_720p(cpu_frame_720p, corr_mode, tf32, epe_tol, corner_tol):
+    """What bench.py times, checked: the same constructor arguments (CUDA graph, fused channels-last schedule, correlation
+    mode, TF32 convolutions allowed / forbidden) on a 1280x720 pair of bench.make_sequence, against the CPU oracle.
+    ("fp16", TF32 on) is the headline configuration with its stated tolerance; ("fp16x3", TF32 off) the fp32-class one
+    under the north star's budgets (0.01 px mean EPE, 0.05 px corner error)."""
+    from types import SimpleNamespace
+    from woft_b200 import tracker
+    from woft_b200.corr import CorrBlock
+    from woft_b200.optical_flow import RAFTWrapper
+    base, frame, mask, flow_cpu, w_cpu, H_cpu, ok_cpu = cpu_frame_720p
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = tf32
+    try:
+        flow_conf = SimpleNamespace(raft_type="weighted", class_params=SimpleNamespace(small=False, alternate_corr=False),
+                                    model=None, seeded_weights=0, iters=12, padding_mode="nopad")
+        flower = RAFTWrapper(flow_conf, device=DEV, use_cuda_graph=True,
+                             corr_block=functools.partial(CorrBlock, mode=corr_mode), tf32=tf32)
+        trk = tracker.PlanarTracker(tracker.default_config(flow_conf), flower=flower)
+        trk.init(base, mask)
+        for _ in range(2):   # the second call replays the captured graph, as every timed step does
+            flow, w = flower.compute_flow(base, frame, mode="flow", do_sigmoid=False)
+        H_gpu, meta = trk.track(frame)
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+    epe = (flow.cpu().view(2, 720, 1280) - flow_cpu[0]).norm(dim=0).mean().item()
+    w_err = (w.cpu().view(720, 1280) - w_cpu[0, 0]).abs().max().item()
+    corner = wo.corner_error(torch.from_numpy(H_gpu), torch.from_numpy(H_cpu), 1280, 720)
+    print(f"\nbenched configuration {corr_mode}, TF32 convolutions {tf32}: mean EPE {epe:.5f} px, "
+          f"weight-logit max error {w_err:.4f}, homography corner error {corner:.5f} px")
+    assert meta.global_H_success == ok_cpu
+    assert epe <= epe_tol, f"mean EPE {epe} px"
+    assert corner <= corner_tol, f"corner error {corner} px"
 
 
 def test_lost_branch_matches_cpu_pipeline():

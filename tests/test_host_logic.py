@@ -70,10 +70,10 @@ def _gather_worker(rank, world, port, out_dir):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     sys.path.insert(0, str(ROOT))
     import torch.distributed as dist
-    from woft_b200.sharding import gather_results, shard_sequences
+    from woft_b200.sharding import gather_results, max_over_ranks, shard_sequences
     dist.init_process_group("gloo", rank=rank, world_size=world)
     mine = {s: np.full((3, 3, 3), float(s)) for s in shard_sequences(5, rank, world)}
-    elapsed = gather_results.max_over_ranks(0.5 + rank)
+    elapsed = max_over_ranks(0.5 + rank)
     merged = gather_results(mine)
     if rank == 0:
         assert sorted(merged) == [0, 1, 2, 3, 4]

@@ -18,12 +18,14 @@ import torch.nn.functional as F
 from . import _lib
 
 #: arithmetic of the all-pairs GEMM, all with fp32 accumulation:
-#:   "fp16"   tensor cores, operands rounded to fp16 (10-bit mantissa like tf32, half the operand bytes) -- default
+#:   "fp16x3" tensor cores, error-compensated fp16 hi/lo split (3 MMAs), fp32-class result -- default: the reference
+#:            multiplies in fp32 (corr.py:67), and the split keeps full accuracy whatever the feature magnitudes are
+#:   "fp16"   tensor cores, operands rounded once to fp16 (10-bit mantissa like tf32, half the operand bytes, inputs
+#:            saturated at +-65504): opt-in, 0.05 px tolerance class
 #:   "tf32"   tensor cores, operands rounded to tf32        "bf16"  tensor cores, 7-bit mantissa
-#:   "fp16x3" tensor cores, error-compensated fp16 hi/lo split (3 MMAs), fp32-class result
 #:   "tf32x3" tensor cores, the same with tf32 hi/lo planes (twice the operand bytes)
 #:   "fp32"   CUDA cores, the reference's own precision class
-DEFAULT_MODE = os.environ.get("WOFT_CORR_MODE", "fp16")
+DEFAULT_MODE = os.environ.get("WOFT_CORR_MODE", "fp16x3")
 
 
 def _as_f32c(t):

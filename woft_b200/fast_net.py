@@ -232,8 +232,9 @@ def convex_upsample_both(flow_low, weights_low, mask, sigmoid=False):
 class FastWeightedRAFT:
     """Callable with the signature of WeightedRAFT.forward; built from a WeightedRAFT that already sits on the GPU."""
 
-    def __init__(self, net, nhwc_update=True):
+    def __init__(self, net, nhwc_update=True, tf32=True):
         self.net = net
+        self.tf32 = tf32   # False: no hand-written TF32 convolution kernel is used, cuDNN obeys torch's allow_tf32
         self.with_weights = net.with_weights
         dev = next(net.parameters()).device
         if dev.type != "cuda":

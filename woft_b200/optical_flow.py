@@ -120,7 +120,10 @@ def sigmoid(xs):
 
 class RAFTWrapper:
     def __init__(self, config, device="cuda", use_cuda_graph=True, corr_block=None, channels_last=False,
-                 cudnn_benchmark=True, fused=True):
+                 cudnn_benchmark=True, fused=True, tf32=None):
+        """`tf32`: may the convolutions round their operands to TF32 (the hand-written tensor-core convolution kernels
+        of the fused schedule do)?  None follows torch.backends.cudnn.allow_tf32 at construction; False keeps every
+        convolution in fp32 (the reference's precision class)."""
         self.C = config
         self.channels_last = channels_last
         self.fused = fused
@@ -159,7 +162,8 @@ class RAFTWrapper:
         # fused inference schedule (fast_net.py) unless the layer-by-layer mirror is asked for
         if fused and not channels_last:
             from .fast_net import FastWeightedRAFT
-            self._run = FastWeightedRAFT(self.net)
+            self.tf32 = bool(torch.backends.cudnn.allow_tf32 if tf32 is None else tf32)
+            self._run = FastWeightedRAFT(self.net, tf32=self.tf32)
             self._u8_input = True
         else:
             self._run = self.net

@@ -44,5 +44,3 @@ def max_over_ranks(value, device=None):
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
 
-
-gather_results.max_over_ranks = max_over_ranks

@@ -65,7 +65,10 @@ def subsampler(coords_a, coords_b, weights, to_draw=500):
     return coords_a[:, idx], coords_b[:, idx], weights[:, idx]
 
 
-def redet_success_fn(H, template_coords, cur_coords, weights=None, thr=5.0, min_frac=0.2):
+REDET_THRESHOLD_PX, REDET_MIN_FRACTION = 5.0, 0.2   # config :14-21
+
+
+def redet_success_fn(H, template_coords, cur_coords, weights=None, thr=REDET_THRESHOLD_PX, min_frac=REDET_MIN_FRACTION):
     """config :14-21: fraction of correspondences reprojecting within `thr` px must exceed `min_frac`."""
     errs = lsq.torch_proj_errors(H, cur_coords[None], template_coords[None])
     return torch.mean((errs <= thr).float()) > min_frac
@@ -79,7 +82,8 @@ def find_homography(pts_A, pts_B, weights=None):
 _SOBOL_DEV = {}
 
 
-def select_fit_check(flow_up, weight_logits, template_mask, pw_mask, to_draw=500, thr=5.0, min_frac=0.2,
+def select_fit_check(flow_up, weight_logits, template_mask, pw_mask, to_draw=500, thr=REDET_THRESHOLD_PX,
+                     min_frac=REDET_MIN_FRACTION,
                      prev_to_template=None):
     """The default config's post-flow stage as five launches and no host round trip: correspondence mask + Sobol pick
     (woft_select_correspondences), weighted fit (woft_homography_fit_n), inlier test (woft_inlier_fraction).
@@ -96,7 +100,7 @@ def select_fit_check(flow_up, weight_logits, template_mask, pw_mask, to_draw=500
     if key not in _SOBOL_DEV:
         _SOBOL_DEV[key] = torch.from_numpy(np.sort(sobol_positions(to_draw)).astype(np.float32)).to(dev)
     flow_up = flow_up.contiguous()
-    weight_logits = weight_logits.contiguous()
+    weight_logits = weight_logits.contiguous() if weight_logits is not None else None   # None: unit weights
     pts_t = torch.empty((to_draw, 2), device=dev, dtype=torch.float32)
     pts_c = torch.empty((to_draw, 2), device=dev, dtype=torch.float32)
     w = torch.empty((to_draw,), device=dev, dtype=torch.float32)
@@ -227,11 +231,12 @@ class PlanarTracker:
             pw_mask = torch.from_numpy(pw_mask > 0).to(self.device, non_blocking=True)
             template = self.template_img
 
-        if _cfg(self.C, "fused_select", False) and on_device:
+        fused = on_device and self._fused_select_applies()
+        if fused:
             # mask + Sobol pick + fit + inlier test stay on the device; ONE 48-byte copy brings H and the flag back
             res = self.estimate_global_fused(template, prewarped, pw_mask).cpu().numpy()
             H_np = res[:9].reshape(3, 3).astype(np.float64)
-            ok = bool(res[9] > 0.2)
+            ok = bool(res[9] > REDET_MIN_FRACTION)
         else:
             H_pw2init, ok, t_coords, c_coords, weights = self.estimate_global(template, prewarped, pw_mask)
             H_np = H_pw2init.detach().cpu().numpy()[0].astype(np.float64)   # D2H of the 3x3 (reference :156)
@@ -246,7 +251,7 @@ class PlanarTracker:
             self.N_lost += 1
             if _cfg(self.C, "no_local_H", False):
                 H_cur2init = H_global
-            elif _cfg(self.C, "fused_select", False) and on_device:
+            elif fused:
                 # local flow (T-1 -> T), mask, Sobol pick and fit on the device; one 48-byte copy back (:178-204)
                 flow, w_logits = self.flower.compute_flow(self.prev_dev, frame_dev, mode="flow", do_sigmoid=False)
                 self.flow_passes += 1
@@ -285,6 +290,14 @@ class PlanarTracker:
             self.last_good_H2init = H_cur2init.copy()
         meta.lost, meta.N_lost, meta.global_H_success = self.lost, self.N_lost, bool(ok)
         return H_cur2init, meta
+
+    def _fused_select_applies(self):
+        """The fused post-flow stage (woft_select_correspondences + fit + inlier test) IS the default config's three
+        plug-ins; a config that swapped any of them (wIRLSq, plainLSq, cvransac, alwayswarp variants of the reference)
+        goes through the plug-ins themselves."""
+        C = self.C
+        return bool(_cfg(C, "fused_select", False)) and getattr(C, "H_estimator", None) is find_homography \
+            and getattr(C, "subsampler_fn", None) is subsampler and getattr(C, "redet_success_fn", None) is redet_success_fn
 
     def estimate_global_fused(self, template_img, prewarped_img, pw_mask):
         """estimate_global for the default config's plug-ins, without boolean indexing or host round trips."""

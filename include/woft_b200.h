@@ -320,6 +320,58 @@ int woft_stem_conv7x7(const float* in_nhwc, const float* weight, const float* bi
 int woft_weight_head_conv1(const float* window_nhwc, const float* mean_response, const float* weight, const float* bias,
                            long long n_images, int patch, int levels, int channels_out, float* out_nhwc, void* stream);
 
+/* The wide convolutions of the update block and of the weight head as ONE implicit-GEMM kernel on the tcgen05 tensor
+ * cores, with the element-wise stage that follows each of them in the reference fused into the epilogue.  Replaces the
+ * nn.Conv2d calls (stride 1, zero padding) of BasicMotionEncoder, SepConvGRU, FlowHead.conv1 and the mask head
+ * (pytracking/external/RAFT/raft_core/update.py:6-14, 33-60, 79-97, 122-125) and layers 2-3 + the 1x1 and patch mean of
+ * WeightHead (raft_core/weighted_raft.py:318-339, 347-384).
+ *   in            (N, H, W, in_stride) channels-last, fp32 or fp16 (in_f16); the first `cin` channels of every pixel
+ *                 are convolved, so `in` may be a channel slice of a wider buffer
+ *   weight_packed [kh*kw][cout_pad][cin_pad] in the input's type, tap = ky*kw + kx, zero padded; cin_pad = cin rounded
+ *                 up to 32 (fp32) / 64 (fp16), cout_pad a multiple of 32.  fp32 operands are used as TF32 (the tensor
+ *                 core reads the top 19 bits): round the weights to TF32 beforehand for round-to-nearest
+ *   box_w, box_h  tile of output pixels, box_w * box_h in [96, 128]; 0 = chosen by the library
+ *   epilogue      WOFT_CONV_BIAS_ACT : out[pix][c] = scale * act(acc + bias[c]), act = ReLU when `relu`; fp32 or fp16
+ *                                      (out_f16); `out2` (optional) receives the same values; strides in elements
+ *                 WOFT_CONV_GRU_ZR   : cout = 2C stacked convz|convr filters; z[pix][c] = sigmoid(acc[c] + bias[c]);
+ *                                      out[pix][c] = sigmoid(acc[C+c] + bias[C+c]) * h[pix][c]      (update.py:47-52)
+ *                 WOFT_CONV_GRU_Q    : cout = C; out[pix][c] = (1 - z) * h + z * tanh(acc + bias); out may alias h;
+ *                                      out2 optional second copy                                     (update.py:53-54)
+ *                 WOFT_CONV_HEAD_MEAN: images of row_valid x W pixels stacked along H every row_period rows (batch 1);
+ *                                      head_out[image] = head_bias + mean over the image of w1x1 . relu(acc + bias)
+ *   row_period, row_valid: when row_period > 0, rows y with y % row_period >= row_valid separate stacked images: the
+ *                 BIAS_ACT epilogue stores zeros there (they are the next layer's zero padding between images)
+ * One launch (two for HEAD_MEAN: the logits are cleared first).  woft_conv_tc_check synchronises the stream and reports
+ * whether any convolution kernel gave up on a pipeline wait (2 s bound) since the library was loaded. */
+enum woft_conv_epilogue { WOFT_CONV_BIAS_ACT = 0, WOFT_CONV_GRU_ZR = 1, WOFT_CONV_GRU_Q = 2, WOFT_CONV_HEAD_MEAN = 3 };
+typedef struct woft_conv_tc_args {
+  const void* in;
+  long long in_stride;
+  int in_f16;
+  int batch, height, width, cin, cin_pad;
+  const void* weight_packed;
+  int cout, cout_pad, kh, kw, pad_h, pad_w;
+  int box_w, box_h;
+  int epilogue, relu;
+  float scale;
+  const float* bias;
+  void* out;
+  long long out_stride;
+  int out_f16;
+  void* out2;
+  long long out2_stride;
+  const float* h;
+  long long h_stride;
+  float* z;
+  long long z_stride;
+  const float* w1x1;
+  float* head_out;
+  float head_bias;
+  int row_period, row_valid;
+} woft_conv_tc_args;
+int woft_conv_tc(const woft_conv_tc_args* args, void* stream);
+int woft_conv_tc_check(void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -176,7 +176,8 @@ def gen_net(ref):
         wout["last_flow_shape"] = np.array([wrapper.last_flow_shape[k] for k in ("batch", "delta", "H", "W")])
         # the padders (optical_flow/raft.py:221-271, raft_core/utils/utils.py:7-26) on a frame size that is not a
         # multiple of 8: replicate padding, bilinear resize and crop, each through the reference wrapper
-        oimg1, oimg2 = make_frames(125, 163, 6)
+        oimg1, oimg2 = make_frames(133, 171, 6)   # RAFT pads to 136x176, crop cuts to 128x168 (a 15x20 feature map
+        # would leave a 1x2 coarsest level, on which the reference's bilinear sampler divides by zero: all-NaN flow)
         wout["odd_img1_bgr"], wout["odd_img2_bgr"] = oimg1, oimg2
         for pmode in ("RAFT", "crop"):
             conf.padding_mode = pmode
@@ -185,7 +186,7 @@ def gen_net(ref):
         conf.padding_mode = "nopad"
         # 'Michal' cannot run through the reference wrapper with raft_type 'weighted': raft.py:150 unpads a mask that
         # only the 'weighted_masked' network produces (AttributeError on None).  Its padder class is recorded directly.
-        mp = ref.flow.MichalPadder((1, 3, 125, 163))
+        mp = ref.flow.MichalPadder((1, 3, 125, 163))  # -> 128x168
         g = torch.Generator().manual_seed(21)
         a, b = torch.rand((1, 3, 125, 163), generator=g) * 255, torch.rand((1, 3, 125, 163), generator=g) * 255
         pa, pb = mp.pad(a, b)

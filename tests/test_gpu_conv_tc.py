@@ -1,0 +1,190 @@
+"""woft_conv_tc (tcgen05 implicit-GEMM convolution with fused epilogues) against plain PyTorch expressions of the layers
+it replaces (raft_core/update.py:6-14, 33-60, 79-97, 122-125; raft_core/weighted_raft.py:318-339, 347-384).
+
+Two references per case:
+  exact   the same operand rounding as the kernel (activations truncated to TF32 as the tensor core reads them, filters
+          rounded to nearest TF32 by pack_conv) convolved in fp64: only the fp32 accumulation order differs -> 2e-4
+          relative to the output scale; this is the layout / indexing / padding check
+  fp32    torch's fp32 convolution (TF32 off) of the unrounded operands: TF32-class tolerance 4e-3 of the output scale
+"""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _exact_convs():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def trunc_tf32(t):
+    return (t.contiguous().view(torch.int32) & ~0x1FFF).view(torch.float32)
+
+
+def cl(t):
+    return t.contiguous(memory_format=torch.channels_last)
+
+
+def make(B, cin, cout, H, W, kh, kw, seed, ctot=None, off=0):
+    g = torch.Generator().manual_seed(seed)
+    ctot = ctot or cin
+    x = cl(torch.randn((B, ctot, H, W), generator=g)).to(DEV)
+    w = (torch.randn((cout, cin, kh, kw), generator=g) / (cin * kh * kw) ** 0.5).to(DEV)
+    b = (torch.randn((cout,), generator=g) * 0.1).to(DEV)
+    return x, w, b
+
+
+def refs(x, w, b, pad):
+    from woft_b200.conv_tc import round_to_tf32
+    exact = F.conv2d(trunc_tf32(x).double(), round_to_tf32(w).double(), b.double(), padding=pad).float()
+    plain = F.conv2d(x, w, b, padding=pad)
+    return exact, plain
+
+
+def check(got, exact, plain, what):
+    scale = plain.abs().max().item()
+    e1 = (got - exact).abs().max().item() / scale
+    e2 = (got - plain).abs().max().item() / scale
+    assert e1 <= 2e-4, f"{what}: differs from the same-rounding reference by {e1:.2e} of the output scale"
+    assert e2 <= 4e-3, f"{what}: differs from the fp32 convolution by {e2:.2e} of the output scale"
+
+
+@pytest.mark.parametrize("shape", [
+    # B, cin, cout, H, W, kh, kw, pad
+    (1, 256, 192, 90, 160, 3, 3, (1, 1)),    # convc2 at 1280x720
+    (1, 324, 256, 90, 160, 1, 1, (0, 0)),    # convc1: Cin not a multiple of 32 (zero-filled by TMA)
+    (1, 128, 64, 90, 160, 3, 3, (1, 1)),     # convf2
+    (2, 64, 126, 13, 21, 3, 3, (1, 1)),      # ragged pixel grid, batch 2, 126 of 128 output channels stored
+    (1, 256, 576, 24, 40, 1, 1, (0, 0)),     # mask head 1x1: three output-channel tiles
+    (1, 96, 32, 17, 9, 5, 1, (2, 0)),        # vertical 5x1
+    (1, 96, 32, 9, 33, 1, 5, (0, 2)),        # horizontal 1x5
+])
+def test_conv_bias_relu_matches_torch(shape):
+    from woft_b200 import _lib, conv_tc
+    B, cin, cout, H, W, kh, kw, pad = shape
+    x, w, b = make(B, cin, cout, H, W, kh, kw, seed=cin + cout)
+    pc = conv_tc.PackedConv(w, b, pad)
+    out = cl(torch.full((B, cout + 8, H, W), 7.0, device=DEV))   # written at channel offset 4 of a wider buffer
+    out2 = cl(torch.full((B, cout, H, W), 7.0, device=DEV))
+    conv_tc.run(pc, x, relu=True, out=out, out_off=4, out2=out2)
+    conv_tc.check(DEV)
+    exact, plain = refs(x, w, b, pad)
+    check(out[:, 4:4 + cout], exact.relu(), plain.relu(), f"{shape}")
+    assert torch.equal(out[:, 4:4 + cout], out2)
+    assert (out[:, :4] == 7.0).all() and (out[:, 4 + cout:] == 7.0).all(), "wrote outside its channel slice"
+
+
+def test_conv_reads_a_channel_slice_and_scales():
+    from woft_b200 import conv_tc
+    x, w, b = make(1, 128, 64, 30, 44, 3, 3, seed=3, ctot=384)
+    pc = conv_tc.PackedConv(w, b, 1)
+    out = cl(torch.empty((1, 64, 30, 44), device=DEV))
+    conv_tc.run(pc, x, x_off=128, relu=False, scale=0.25, out=out)
+    exact, plain = refs(x[:, 128:256], w, b, 1)
+    check(out, exact * 0.25, plain * 0.25, "slice")
+
+
+@pytest.mark.parametrize("kh,kw", [(1, 5), (5, 1)])
+@pytest.mark.parametrize("H,W", [(90, 160), (11, 27)])
+def test_gru_half_step_matches_torch(kh, kw, H, W):
+    """SepConvGRU half step (update.py:45-60) as two launches: stacked convz|convr with the gate epilogue, convq with the
+    blend epilogue, on the persistent [h | x] / [r*h | x] buffers of the fused schedule."""
+    from woft_b200 import _lib, conv_tc
+    C, X = 128, 256
+    g = torch.Generator().manual_seed(kh * 10 + W)
+    pad = (kh // 2, kw // 2)
+    buf1 = cl(torch.randn((1, C + X, H, W), generator=g)).to(DEV)
+    buf1[:, :C] = torch.tanh(buf1[:, :C])
+    buf2 = buf1.clone(memory_format=torch.channels_last)
+    wz, wr, wq = ((torch.randn((C, C + X, kh, kw), generator=g) / ((C + X) * 5) ** 0.5).to(DEV) for _ in range(3))
+    bz, br, bq = ((torch.randn((C,), generator=g) * 0.1).to(DEV) for _ in range(3))
+    h0 = buf1[:, :C].clone()
+    # reference, fp32
+    hx = buf1.clone()
+    zt = torch.sigmoid(F.conv2d(hx, wz, bz, padding=pad))
+    rt = torch.sigmoid(F.conv2d(hx, wr, br, padding=pad))
+    qt = torch.tanh(F.conv2d(torch.cat([rt * h0, hx[:, C:]], 1), wq, bq, padding=pad))
+    h_ref = (1 - zt) * h0 + zt * qt
+    pzr = conv_tc.PackedConv(torch.cat([wz, wr], 0), torch.cat([bz, br], 0), pad)
+    pq = conv_tc.PackedConv(wq, bq, pad)
+    z = torch.empty((H * W, C), device=DEV)
+    conv_tc.run(pzr, buf1, epilogue=_lib.CONV_GRU_ZR, h=buf1, z=z, out=buf2)
+    conv_tc.run(pq, buf2, epilogue=_lib.CONV_GRU_Q, h=buf1, z=z, out=buf1)
+    conv_tc.check(DEV)
+    assert (z.view(1, H, W, C).permute(0, 3, 1, 2) - zt).abs().max().item() <= 2e-3
+    assert (buf2[:, :C] - rt * h0).abs().max().item() <= 2e-3
+    assert torch.equal(buf2[:, C:], hx[:, C:]) and torch.equal(buf1[:, C:], hx[:, C:])
+    assert (buf1[:, :C] - h_ref).abs().max().item() <= 3e-3
+
+
+def test_fp16_operands_and_output():
+    from woft_b200 import conv_tc
+    x, w, b = make(1, 128, 128, 40, 56, 3, 3, seed=9)
+    xh = cl(x.half())
+    pc = conv_tc.PackedConv(w, b, 1, f16=True)
+    out = cl(torch.empty((1, 128, 40, 56), device=DEV, dtype=torch.float16))
+    conv_tc.run(pc, xh, relu=True, out=out)
+    exact = F.conv2d(xh.double(), w.half().double(), b.double(), padding=1).relu()
+    scale = exact.abs().max().item()
+    assert (out.double() - exact).abs().max().item() / scale <= 1.5e-3   # fp16 rounding of the stored result
+
+
+@pytest.mark.parametrize("f16", [False, True])
+def test_weight_head_layers_on_stacked_images(f16):
+    """Layers 2-3 of the weight head + 1x1 + patch mean (weighted_raft.py:318-339, 380-384) on 9x9 images stacked along H
+    with one zero row between them: conv+ReLU writes zeros into the separator rows, the last layer reduces each image."""
+    from woft_b200 import _lib, conv_tc
+    n, P, C = 53, 9, 128
+    g = torch.Generator().manual_seed(1)
+    imgs = torch.randn((n, C, P, P), generator=g).relu().to(DEV)
+    w2, w3 = ((torch.randn((C, C, 3, 3), generator=g) / (C * 9) ** 0.5).to(DEV) for _ in range(2))
+    b2, b3 = ((torch.randn((C,), generator=g) * 0.1).to(DEV) for _ in range(2))
+    w1 = (torch.randn((C,), generator=g) / C ** 0.5).to(DEV)
+    b1 = 0.3
+    dt = torch.float16 if f16 else torch.float32
+    if f16:
+        imgs = imgs.half().float()
+    want2 = F.conv2d(imgs, w2.half().float() if f16 else w2, b2, padding=1).relu()
+    x3 = want2.half().float() if f16 else want2
+    want3 = F.conv2d(x3, w3.half().float() if f16 else w3, b3, padding=1).relu()
+    want = (want3 * w1.view(1, C, 1, 1)).sum(1).mean(dim=(1, 2)) + b1
+    # stacked layout: (1, C, n*10, 9) channels-last, row 9 of every image zero
+    stacked = torch.zeros((n, P + 1, P, C), device=DEV, dtype=dt)
+    stacked[:, :P] = imgs.permute(0, 2, 3, 1).to(dt)
+    x = stacked.view(1, n * (P + 1), P, C).permute(0, 3, 1, 2)
+    mid = torch.full((1, n * (P + 1), P, C), 5.0, device=DEV, dtype=dt).permute(0, 3, 1, 2)
+    p2, p3 = conv_tc.PackedConv(w2, b2, 1, f16=f16), conv_tc.PackedConv(w3, b3, 1, f16=f16)
+    conv_tc.run(p2, x, relu=True, out=mid, row_period=P + 1, row_valid=P, box=(9, 14))
+    logits = torch.full((n,), 9.0, device=DEV)
+    conv_tc.run(p3, mid, epilogue=_lib.CONV_HEAD_MEAN, w1x1=w1, head_out=logits, head_bias=b1, row_period=P + 1,
+                row_valid=P, box=(9, 14))
+    conv_tc.check(DEV)
+    got2 = mid.permute(0, 2, 3, 1).reshape(n, P + 1, P, C)
+    assert (got2[:, P] == 0).all(), "separator rows must be zero"
+    tol = 4e-3 if f16 else 3e-3
+    s2 = want2.abs().max().item()
+    assert (got2[:, :P].permute(0, 3, 1, 2).float() - want2).abs().max().item() / s2 <= tol
+    assert (logits - want).abs().max().item() <= tol * max(1.0, want.abs().max().item())
+    # deterministic: a second run gives the same bits
+    logits2 = torch.empty_like(logits)
+    conv_tc.run(p3, mid, epilogue=_lib.CONV_HEAD_MEAN, w1x1=w1, head_out=logits2, head_bias=b1, row_period=P + 1,
+                row_valid=P, box=(9, 14))
+    assert torch.equal(logits, logits2)
+
+
+def test_conv_tc_argument_errors():
+    from woft_b200 import conv_tc
+    x, w, b = make(1, 32, 32, 8, 8, 3, 3, seed=0)
+    pc = conv_tc.PackedConv(w, b, 1)
+    with pytest.raises(AssertionError):
+        conv_tc.run(pc, x.contiguous(), out=x)            # not channels-last
+    with pytest.raises(AssertionError):
+        conv_tc.run(pc, x, out=None)                       # no output

@@ -513,7 +513,7 @@ def test_device_prewarp_matches_opencv():
 @pytest.mark.parametrize("pmode", ["RAFT", "crop"])
 def test_flow_wrapper_padders_match_reference_wrapper(golden, pmode):
     """Frame sizes that are not multiples of 8 through the padders (optical_flow/raft.py:122-150, 221-271;
-    raft_core/utils/utils.py:7-26), against the reference wrapper's output on the same 125x163 pair."""
+    raft_core/utils/utils.py:7-26), against the reference wrapper's output on the same 133x171 pair."""
     from types import SimpleNamespace
     from woft_b200.optical_flow import RAFTWrapper
     from woft_b200.corr import CorrBlock

@@ -21,6 +21,22 @@ CORR_MODES = {"fp32": CORR_FP32_SIMT, "tf32": CORR_TF32, "tf32x3": CORR_TF32X3, 
 
 _FLOATP_ARRAY = POINTER(c_void_p)
 
+
+class ConvTcArgs(ctypes.Structure):
+    """woft_conv_tc_args (include/woft_b200.h), field for field."""
+    _fields_ = [("in_", c_void_p), ("in_stride", ctypes.c_longlong), ("in_f16", c_int),
+                ("batch", c_int), ("height", c_int), ("width", c_int), ("cin", c_int), ("cin_pad", c_int),
+                ("weight_packed", c_void_p),
+                ("cout", c_int), ("cout_pad", c_int), ("kh", c_int), ("kw", c_int), ("pad_h", c_int), ("pad_w", c_int),
+                ("box_w", c_int), ("box_h", c_int), ("epilogue", c_int), ("relu", c_int), ("scale", c_float),
+                ("bias", c_void_p), ("out", c_void_p), ("out_stride", ctypes.c_longlong), ("out_f16", c_int),
+                ("out2", c_void_p), ("out2_stride", ctypes.c_longlong), ("h", c_void_p), ("h_stride", ctypes.c_longlong),
+                ("z", c_void_p), ("z_stride", ctypes.c_longlong), ("w1x1", c_void_p), ("head_out", c_void_p),
+                ("head_bias", c_float), ("row_period", c_int), ("row_valid", c_int)]
+
+
+CONV_BIAS_ACT, CONV_GRU_ZR, CONV_GRU_Q, CONV_HEAD_MEAN = range(4)
+
 # name -> (restype, argtypes); kept in step with include/woft_b200.h (tests/test_abi.py checks both ways)
 SIGNATURES = {
     "woft_abi_version": (c_int, []),
@@ -85,6 +101,8 @@ SIGNATURES = {
     "woft_convex_upsample": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                      c_void_p]),
     "woft_instance_norm_relu": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p]),
+    "woft_conv_tc": (c_int, [POINTER(ConvTcArgs), c_void_p]),
+    "woft_conv_tc_check": (c_int, [c_void_p]),
 }
 
 _lib = None

@@ -1,0 +1,597 @@
+// Convolutions of the flow network on the Blackwell tensor cores: an implicit GEMM on tcgen05/TMEM fed by TMA, with the
+// element-wise stage that follows each convolution in the reference fused into the epilogue.
+//
+// Replaces, in the fused channels-last schedule (woft_b200/fast_net.py), the cuDNN convolutions of
+//   BasicMotionEncoder  convc1, convc2, convf2, conv        (raft_core/update.py:79-97)
+//   SepConvGRU          convz|convr stacked, convq, both halves, with the gate arithmetic (update.py:33-60)
+//   FlowHead.conv1, the mask head                            (update.py:6-14, 122-125)
+//   WeightHead          layers 2 and 3 with the 1x1 + patch mean (raft_core/weighted_raft.py:318-339, 347-384)
+//
+// Formulation.  Activations are channels-last (N, H, W, C) -- possibly a channel slice of a wider buffer: the tensor map
+// carries the pixel stride.  For a tile of BW x BH = 128 output pixels and one filter tap (dy, dx), the A operand of the
+// GEMM is the BW x BH box of input pixels shifted by (dy, dx), 32 fp32 (or 64 fp16) channels deep: ONE 4-D TMA box
+// over (C, W, H, N) whose 128 rows land in shared memory K-major with the 128-byte swizzle tcgen05 reads.  Rows that
+// fall outside the image are zero-filled by TMA -- that is the convolution's zero padding and the ragged edge of the
+// tile grid at once, so there is no im2col buffer and no border code.  The B operand is the tap's (Cout, Cin) weight
+// matrix, repacked once on the host to [tap][Cout][Cin] (rounded to tf32 / fp16).  The accumulator (128 pixels x up to
+// 256 output channels, fp32) lives in TMEM across all taps and channel blocks: K = taps * Cin.
+//
+// Warp roles (192 threads, persistent CTAs over tiles), as in corr_tc.cu: warp 0 TMA producer, warp 1 MMA issuer (two
+// accumulators in TMEM, so tile i+1 multiplies while tile i drains), warps 2-5 epilogue (one output pixel per thread,
+// 32 channels per tcgen05.ld).  Epilogues:
+//   BIAS_ACT  y = scale * act(acc + bias), fp32 or fp16, to one or two (strided) destinations -- writing straight into
+//             the concatenation buffers of the next layer (torch.cat at update.py:96-97, 129 disappears)
+//   GRU_ZR    z = sigmoid(acc[:, :C] + bz) -> z;  r*h = sigmoid(acc[:, C:] + br) * h -> the q convolution's input
+//   GRU_Q     h' = (1 - z) * h + z * tanh(acc + bq), written over h
+//   HEAD_MEAN relu(acc + bias) . w1x1, averaged over the 81 pixels of each 9x9 patch image (+ b1x1): the weight logit
+// Every mbarrier wait is bounded (2 s) and raises a status word instead of hanging (woft_conv_tc_check).
+//
+// Work per launch at 1280x720 (14 400 pixels): 2 * 14400 * taps * Cin * Cout flop; the 1x5 GRU gate pair
+// (K = 5 * 384, N = 256) is 14.2 GFLOP.  Bound: tensor pipe (tf32: 4096 flop/clk/SM), on 113..115 of 148 SMs because
+// 14 400 pixels are 112.5 tiles.
+#include <cuda.h>
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "ptx.cuh"
+
+namespace woft {
+
+constexpr int CT_THREADS = 192, CT_EPI_THREADS = 128;
+constexpr int CT_A_STAGE = 128 * 128;       // 128 pixel rows x one 128-byte K row
+constexpr int CT_MAX_STAGES = 8;
+constexpr int CT_MAX_TAPS = 25;
+constexpr int CT_SMEM_LIMIT = 232448;
+constexpr int CT_MAX_BIAS = 1024;
+
+enum { CT_EPI_BIAS_ACT = 0, CT_EPI_GRU_ZR = 1, CT_EPI_GRU_Q = 2, CT_EPI_HEAD_MEAN = 3 };
+
+struct ConvTcParams {
+  CUtensorMap tmA;  // (Cin, W, H, N) box (k_elems, bw, bh, 1)
+  CUtensorMap tmB;  // (Cin_pad, Cout_pad, taps) box (k_elems, bn, 1)
+  int W, H, NB;
+  int bw, bh;
+  int x_tiles, y_tiles, n_tiles, total_tiles;
+  int taps, k_chunks, k_elems, f16;
+  int bn, stages, a_bytes, b_bytes;
+  signed char dx[CT_MAX_TAPS], dy[CT_MAX_TAPS];
+  int cout, relu;
+  float scale;
+  const float* bias;
+  void* out;
+  long long out_stride;
+  int out_f16;
+  void* out2;
+  long long out2_stride;
+  const float* h;
+  long long h_stride;
+  float* z;
+  long long z_stride;
+  const float* w1x1;
+  float* head_out;
+  float head_scale, head_bias;
+  int row_period, row_valid;  // rows y with (y % row_period) >= row_valid are separators: stored as zeros, not averaged
+};
+
+// status word of the conv kernels (a pipeline wait timed out); read back by woft_conv_tc_check
+__device__ int g_conv_abort = 0;
+
+__device__ __forceinline__ bool ct_wait(uint64_t* bar, uint32_t parity) {
+  if (ptx::mbar_try_wait(bar, parity)) return true;
+  const uint64_t t0 = ptx::globaltimer_ns();
+  uint32_t spins = 0;
+  while (!ptx::mbar_try_wait(bar, parity)) {
+    if ((++spins & 63u) == 0) {
+      if (*reinterpret_cast<volatile int*>(&g_conv_abort) != 0) return false;
+      if (ptx::globaltimer_ns() - t0 > 2000000000ull) {
+        atomicExch(&g_conv_abort, 1);
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint64_t ct_desc(uint32_t saddr) {  // K-major, 128-byte swizzle, 8-row groups 1024 B apart
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+struct CtTile {
+  int n, x0, y0, c0;
+};
+__device__ __forceinline__ CtTile ct_decode(const ConvTcParams& p, int t) {
+  CtTile c;
+  const int nt = t % p.n_tiles;
+  t /= p.n_tiles;
+  const int xt = t % p.x_tiles;
+  t /= p.x_tiles;
+  const int yt = t % p.y_tiles;
+  c.n = t / p.y_tiles;
+  c.x0 = xt * p.bw;
+  c.y0 = yt * p.bh;
+  c.c0 = nt * p.bn;
+  return c;
+}
+
+__device__ __forceinline__ float ct_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+// 32 consecutive channels of one pixel, fp32 or fp16 destination; `nv` < 32 only in the last channel block
+__device__ __forceinline__ void ct_store_row(void* base, long long stride, long long pix, int col, const float* v, int nv,
+                                             bool f16) {
+  if (f16) {
+    __half* o = reinterpret_cast<__half*>(base) + pix * stride + col;
+    if (nv == 32) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        __half2 a = __floats2half2_rn(v[j], v[j + 1]), b = __floats2half2_rn(v[j + 2], v[j + 3]);
+        __half2 c = __floats2half2_rn(v[j + 4], v[j + 5]), d = __floats2half2_rn(v[j + 6], v[j + 7]);
+        uint4 u;
+        u.x = *reinterpret_cast<uint32_t*>(&a);
+        u.y = *reinterpret_cast<uint32_t*>(&b);
+        u.z = *reinterpret_cast<uint32_t*>(&c);
+        u.w = *reinterpret_cast<uint32_t*>(&d);
+        *reinterpret_cast<uint4*>(o + j) = u;
+      }
+    } else {
+      for (int j = 0; j < nv; ++j) o[j] = __float2half_rn(v[j]);
+    }
+  } else {
+    float* o = reinterpret_cast<float*>(base) + pix * stride + col;
+    if (nv == 32) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    } else {
+      for (int j = 0; j < nv; ++j) o[j] = v[j];
+    }
+  }
+}
+
+__device__ __forceinline__ void ct_load_row(const float* base, long long stride, long long pix, int col, float* v) {
+  const float4* s = reinterpret_cast<const float4*>(base + pix * stride + col);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const float4 t = s[j];
+    v[4 * j] = t.x;
+    v[4 * j + 1] = t.y;
+    v[4 * j + 2] = t.z;
+    v[4 * j + 3] = t.w;
+  }
+}
+
+template <int EPI>
+__global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
+  extern __shared__ uint8_t ct_smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ct_smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + p.stages * CT_A_STAGE;
+  float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
+  float* s_red = s_bias + CT_MAX_BIAS;                                   // 128 floats (HEAD_MEAN)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_red + 128);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + CT_MAX_STAGES;
+  uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
+  volatile int* epi_go = reinterpret_cast<volatile int*>(tmem_ptr + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) {
+      ptx::mbar_init(full + s, 1);
+      ptx::mbar_init(empty + s, 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(tfull + i, 1);
+      ptx::mbar_init(tempty + i, CT_EPI_THREADS);
+    }
+    ptx::fence_mbar_init();
+    ptx::prefetch_tmap(&p.tmA);
+    ptx::prefetch_tmap(&p.tmB);
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_ptr, 512);
+  {
+    const int nb = p.n_tiles * p.bn;
+    for (int i = threadIdx.x; i < nb && i < CT_MAX_BIAS; i += CT_THREADS) {
+      float b = (p.bias && i < p.cout) ? __ldg(p.bias + i) : 0.f;
+      s_bias[i] = b;
+    }
+  }
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+  const int k_steps = p.taps * p.k_chunks;
+
+  if (warp == 0) {
+    // ================================ TMA producer ================================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      bool alive = true;
+      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x) {
+        const CtTile tc = ct_decode(p, t);
+        for (int tap = 0; tap < p.taps && alive; ++tap) {
+          const int xs = tc.x0 + p.dx[tap], ys = tc.y0 + p.dy[tap];
+          for (int kc = 0; kc < p.k_chunks; ++kc) {
+            if (!ct_wait(empty + stage, phase ^ 1u)) {
+              alive = false;
+              break;
+            }
+            ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.a_bytes + p.b_bytes));
+            ptx::tma_load_4d(sA + stage * CT_A_STAGE, &p.tmA, full + stage, kc * p.k_elems, xs, ys, tc.n);
+            ptx::tma_load_3d(sB + stage * p.b_bytes, &p.tmB, full + stage, kc * p.k_elems, tc.c0, tap);
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ MMA issuer ================================
+    if (lane == 0) {
+      const uint32_t fmt = p.f16 ? 0u : 2u;  // F16 = 0, TF32 = 2
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(p.bn >> 3) << 17) | (uint32_t(128 >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      bool alive = true;
+      int it = 0;
+      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x, ++it) {
+        const int buf = it & 1;
+        const uint32_t use = uint32_t(it >> 1);
+        if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
+        ptx::tc_fence_after_sync();
+        const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
+        for (int ks = 0; ks < k_steps; ++ks) {
+          if (!ct_wait(full + stage, phase)) {
+            alive = false;
+            break;
+          }
+          ptx::tc_fence_after_sync();
+          const uint64_t da = ct_desc(ptx::smem_u32(sA + stage * CT_A_STAGE));
+          const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row
+            const uint32_t acc = (ks > 0 || k > 0) ? 1u : 0u;
+            if (p.f16)
+              ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+            else
+              ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+          }
+          ptx::mma_commit(empty + stage);
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        if (alive) ptx::mma_commit(tfull + buf);
+      }
+    }
+  } else {
+    // ================================ epilogue ================================
+    const int et = threadIdx.x - 64;  // 0..127
+    const bool leader = (et == 0);
+    const int m = (warp & 3) * 32 + lane;  // TMEM lane == pixel row of the tile
+    const uint32_t lane_base = uint32_t((warp & 3) * 32) << 16;
+    const int xi = m % p.bw, yj = m / p.bw;
+    const int chunks = p.bn >> 5;
+    int it = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+      const CtTile tc = ct_decode(p, t);
+      const int buf = it & 1;
+      const uint32_t use = uint32_t(it >> 1);
+      if (leader) *epi_go = ct_wait(tfull + buf, use & 1u) ? 1 : 0;
+      ptx::named_bar_sync(1, CT_EPI_THREADS);
+      if (*epi_go == 0) break;
+      ptx::tc_fence_after_sync();
+      const int x = tc.x0 + xi, y = tc.y0 + yj;
+      const bool valid = yj < p.bh && x < p.W && y < p.H;
+      const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
+      const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
+      float head_sum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < chunks; ++c) {
+        float v[32];
+        ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * 256 + c * 32), v);
+        if (c == chunks - 1) {  // accumulator fully read: hand it back to the MMA warp
+          ptx::tc_fence_before_sync();
+          ptx::mbar_arrive(tempty + buf);
+        }
+        const int col = tc.c0 + c * 32;  // output channel of v[0]
+        if (EPI == CT_EPI_BIAS_ACT) {
+          const int nv = min(32, p.cout - col);
+          if (valid && nv > 0) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              float a = v[j] + s_bias[col + j];
+              if (p.relu) a = fmaxf(a, 0.f);
+              v[j] = separator ? 0.f : a * p.scale;
+            }
+            ct_store_row(p.out, p.out_stride, pix, col, v, nv, p.out_f16 != 0);
+            if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, nv, p.out_f16 != 0);
+          }
+        } else if (EPI == CT_EPI_GRU_ZR) {
+          const int hid = p.bn >> 1;
+          if (valid) {
+            if (col < hid) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + s_bias[col + j]);
+              ct_store_row(p.z, p.z_stride, pix, col, v, 32, false);
+            } else {
+              float hv[32];
+              ct_load_row(p.h, p.h_stride, pix, col - hid, hv);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + s_bias[col + j]) * hv[j];
+              ct_store_row(p.out, p.out_stride, pix, col - hid, v, 32, false);
+            }
+          }
+        } else if (EPI == CT_EPI_GRU_Q) {
+          if (valid) {
+            float hv[32], zv[32];
+            ct_load_row(p.h, p.h_stride, pix, col, hv);
+            ct_load_row(p.z, p.z_stride, pix, col, zv);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = (1.f - zv[j]) * hv[j] + zv[j] * tanhf(v[j] + s_bias[col + j]);
+            ct_store_row(p.out, p.out_stride, pix, col, v, 32, false);
+            if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, 32, false);
+          }
+        } else {  // CT_EPI_HEAD_MEAN
+#pragma unroll
+          for (int j = 0; j < 32; ++j) head_sum = fmaf(fmaxf(v[j] + s_bias[col + j], 0.f), __ldg(p.w1x1 + col + j), head_sum);
+        }
+      }
+      if (EPI == CT_EPI_HEAD_MEAN) {
+        // rows of the tile are (row_period) image rows apart per image: sum the pixels of each image in a fixed order
+        s_red[m] = (valid && !separator) ? head_sum : 0.f;
+        ptx::named_bar_sync(1, CT_EPI_THREADS);
+        const int img_first = tc.y0 / p.row_period;
+        const int img = img_first + et;
+        const int y_lo = max(img * p.row_period, tc.y0), y_hi = min(min(img * p.row_period + p.row_valid, tc.y0 + p.bh), p.H);
+        if (et < 4 && y_lo < y_hi) {
+          float s = 0.f;
+          for (int r = (y_lo - tc.y0) * p.bw; r < (y_hi - tc.y0) * p.bw; ++r) s += s_red[r];
+          s *= p.head_scale;
+          if (y_lo == img * p.row_period) s += p.head_bias;  // the tile holding the image's first row brings the 1x1 bias
+          // at most two tiles hold pixels of one image and the destination starts at zero: 0 + a + b == 0 + b + a
+          atomicAdd(p.head_out + img, s);
+        }
+        ptx::named_bar_sync(1, CT_EPI_THREADS);
+      }
+    }
+  }
+
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after_sync();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+__global__ void fill_kernel(float* dst, float value, long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dst[i] = value;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------
+typedef CUresult (*CtEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static CtEncodeFn ct_encode_fn() {
+  static CtEncodeFn cached = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      fn = nullptr;
+    return reinterpret_cast<CtEncodeFn>(fn);
+  }();
+  return cached;
+}
+
+template <int EPI>
+static int ct_launch(const ConvTcParams& p, int grid, int smem, cudaStream_t s) {
+  WOFT_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_LIMIT));
+  conv_tc_kernel<EPI><<<grid, CT_THREADS, smem, s>>>(p);
+  return launch_status("conv_tc_kernel");
+}
+
+}  // namespace woft
+
+extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(a, "woft_conv_tc: null argument block");
+  WOFT_REQUIRE(a->in && a->weight_packed, "woft_conv_tc: null input or weight pointer");
+  WOFT_REQUIRE(a->batch > 0 && a->height > 0 && a->width > 0 && a->cin > 0 && a->cout > 0, "woft_conv_tc: bad extent");
+  WOFT_REQUIRE(a->kh >= 1 && a->kw >= 1 && a->kh * a->kw <= CT_MAX_TAPS, "woft_conv_tc: at most %d filter taps", CT_MAX_TAPS);
+  WOFT_REQUIRE(a->epilogue >= CT_EPI_BIAS_ACT && a->epilogue <= CT_EPI_HEAD_MEAN, "woft_conv_tc: unknown epilogue %d",
+               a->epilogue);
+  const int esz = a->in_f16 ? 2 : 4;
+  const int k_elems = 128 / esz;
+  const int cin_pad = (a->cin + k_elems - 1) / k_elems * k_elems;
+  WOFT_REQUIRE(a->cin_pad == cin_pad, "woft_conv_tc: weights must be packed with Cin padded to %d (got %d)", cin_pad,
+               a->cin_pad);
+  WOFT_REQUIRE(a->cout_pad % 16 == 0 && a->cout_pad >= a->cout && a->cout_pad <= CT_MAX_BIAS,
+               "woft_conv_tc: Cout must be padded to a multiple of 16 (at most %d)", CT_MAX_BIAS);
+  WOFT_REQUIRE((reinterpret_cast<uintptr_t>(a->in) & 15) == 0 && ((long long)a->in_stride * esz) % 16 == 0,
+               "woft_conv_tc: input must be 16-byte aligned with a pixel stride that is a multiple of 16 bytes");
+  WOFT_REQUIRE(a->in_stride >= a->cin, "woft_conv_tc: input pixel stride smaller than Cin");
+  int dev = 0, major = 0;
+  WOFT_CUDA_CHECK(cudaGetDevice(&dev));
+  WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+  if (major != 10) return fail(WOFT_ERR_UNSUPPORTED, "tcgen05 path needs sm_100; device is sm_%d*", major);
+  CtEncodeFn enc = ct_encode_fn();
+  if (!enc) return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+
+  ConvTcParams p{};
+  // N tile: the whole of Cout when it fits one accumulator, else the largest of 256/192/128/... dividing it
+  int bn = a->cout_pad;
+  if (bn > 256) {
+    bn = 0;
+    for (int c = 256; c >= 16; c -= 16)
+      if (a->cout_pad % c == 0) {
+        bn = c;
+        break;
+      }
+  }
+  WOFT_REQUIRE(bn >= 16 && bn % 32 == 0, "woft_conv_tc: Cout tile %d (need a multiple of 32 dividing the padded Cout)", bn);
+  p.bn = bn;
+  p.n_tiles = a->cout_pad / bn;
+  // pixel box: bw x bh = 128 (or the caller's own, e.g. 9 x 14 rows of stacked 9-wide images)
+  int bw = a->box_w, bh = a->box_h;
+  if (bw <= 0 || bh <= 0) {
+    long long best = -1;
+    for (int cand = 128; cand >= 8; cand >>= 1) {
+      const int cw = cand, ch = 128 / cand;
+      const long long tiles = (long long)ceil_div(a->width, cw) * ceil_div(a->height, ch);
+      if (best < 0 || tiles < best) {
+        best = tiles;
+        bw = cw;
+        bh = ch;
+      }
+    }
+  }
+  WOFT_REQUIRE(bw >= 1 && bh >= 1 && bw <= 256 && bh <= 256 && bw * bh <= 128 && bw * bh >= 96,
+               "woft_conv_tc: pixel box %d x %d must cover 96..128 pixels", bw, bh);
+  p.bw = bw;
+  p.bh = bh;
+  p.W = a->width;
+  p.H = a->height;
+  p.NB = a->batch;
+  p.x_tiles = ceil_div(a->width, bw);
+  p.y_tiles = ceil_div(a->height, bh);
+  const long long total = (long long)p.x_tiles * p.y_tiles * a->batch * p.n_tiles;
+  WOFT_REQUIRE(total < (1LL << 31), "woft_conv_tc: too many tiles");
+  p.total_tiles = (int)total;
+  p.taps = a->kh * a->kw;
+  for (int ky = 0; ky < a->kh; ++ky)
+    for (int kx = 0; kx < a->kw; ++kx) {
+      p.dx[ky * a->kw + kx] = (signed char)(kx - a->pad_w);
+      p.dy[ky * a->kw + kx] = (signed char)(ky - a->pad_h);
+    }
+  p.k_elems = k_elems;
+  p.k_chunks = cin_pad / k_elems;
+  p.f16 = a->in_f16 ? 1 : 0;
+  p.a_bytes = bw * bh * 128;
+  p.b_bytes = bn * 128;
+  p.cout = a->cout;
+  p.relu = a->relu;
+  p.scale = a->scale;
+  p.bias = a->bias;
+  p.out = a->out;
+  p.out_stride = a->out_stride;
+  p.out_f16 = a->out_f16;
+  p.out2 = a->out2;
+  p.out2_stride = a->out2_stride;
+  p.h = a->h;
+  p.h_stride = a->h_stride;
+  p.z = a->z;
+  p.z_stride = a->z_stride;
+  p.w1x1 = a->w1x1;
+  p.head_out = a->head_out;
+  p.row_period = a->row_period;
+  p.row_valid = a->row_valid;
+
+  const int oesz = a->out_f16 ? 2 : 4;
+  if (a->epilogue == CT_EPI_BIAS_ACT) {
+    WOFT_REQUIRE(a->out && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0 && (a->out_stride * oesz) % 16 == 0,
+                 "woft_conv_tc: output must be 16-byte aligned with a 16-byte multiple pixel stride");
+    WOFT_REQUIRE(!a->out2 || ((reinterpret_cast<uintptr_t>(a->out2) & 15) == 0 && (a->out2_stride * oesz) % 16 == 0),
+                 "woft_conv_tc: second output must be 16-byte aligned with a 16-byte multiple pixel stride");
+  } else if (a->epilogue == CT_EPI_GRU_ZR) {
+    WOFT_REQUIRE(p.n_tiles == 1 && bn % 64 == 0 && a->cout == bn, "woft_conv_tc: GRU gate epilogue takes the stacked z|r "
+                 "filters as one tile (Cout = 2 * hidden, a multiple of 64, at most 256)");
+    WOFT_REQUIRE(a->h && a->z && a->out && !a->out_f16, "woft_conv_tc: GRU gate epilogue needs h, z and the r*h output (fp32)");
+    WOFT_REQUIRE(((reinterpret_cast<uintptr_t>(a->h) | reinterpret_cast<uintptr_t>(a->z) | reinterpret_cast<uintptr_t>(a->out)) & 15) == 0 &&
+                 a->h_stride % 4 == 0 && a->z_stride % 4 == 0 && a->out_stride % 4 == 0, "woft_conv_tc: GRU operands must be 16-byte aligned");
+  } else if (a->epilogue == CT_EPI_GRU_Q) {
+    WOFT_REQUIRE(p.n_tiles == 1 && a->cout == bn, "woft_conv_tc: GRU update epilogue takes Cout = hidden as one tile");
+    WOFT_REQUIRE(a->h && a->z && a->out && !a->out_f16, "woft_conv_tc: GRU update epilogue needs h, z and the output (fp32)");
+    WOFT_REQUIRE(((reinterpret_cast<uintptr_t>(a->h) | reinterpret_cast<uintptr_t>(a->z) | reinterpret_cast<uintptr_t>(a->out) |
+                   reinterpret_cast<uintptr_t>(a->out2)) & 15) == 0 &&
+                 a->h_stride % 4 == 0 && a->z_stride % 4 == 0 && a->out_stride % 4 == 0 && a->out2_stride % 4 == 0,
+                 "woft_conv_tc: GRU operands must be 16-byte aligned");
+  } else {
+    WOFT_REQUIRE(p.n_tiles == 1 && a->w1x1 && a->head_out && a->row_period > 0 && a->row_valid > 0 &&
+                 a->row_valid <= a->row_period, "woft_conv_tc: patch-mean epilogue needs w1x1, head_out and the row period");
+    WOFT_REQUIRE(a->batch == 1 && a->height % a->row_period == 0, "woft_conv_tc: patch-mean epilogue takes the images "
+                 "stacked along H (batch 1, H = images * row_period)");
+    WOFT_REQUIRE(ceil_div(bh, a->row_period) + 1 <= 4, "woft_conv_tc: pixel box spans too many images");
+    p.head_scale = 1.0f / float(a->row_valid * a->width);
+    p.head_bias = a->head_bias;
+  }
+  if (a->bias == nullptr) p.bias = nullptr;
+
+  const CUtensorMapDataType dt = a->in_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  {
+    cuuint64_t dims[4] = {(cuuint64_t)a->cin, (cuuint64_t)a->width, (cuuint64_t)a->height, (cuuint64_t)a->batch};
+    cuuint64_t strides[3] = {(cuuint64_t)a->in_stride * esz, (cuuint64_t)a->in_stride * esz * a->width,
+                             (cuuint64_t)a->in_stride * esz * a->width * a->height};
+    cuuint32_t box[4] = {(cuuint32_t)k_elems, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    if (enc(&p.tmA, dt, 4, const_cast<void*>(a->in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the activation operand");
+  }
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)cin_pad, (cuuint64_t)a->cout_pad, (cuuint64_t)p.taps};
+    cuuint64_t strides[2] = {(cuuint64_t)cin_pad * esz, (cuuint64_t)cin_pad * esz * a->cout_pad};
+    cuuint32_t box[3] = {(cuuint32_t)k_elems, (cuuint32_t)bn, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&p.tmB, dt, 3, const_cast<void*>(a->weight_packed), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight operand");
+  }
+
+  const int fixed = 1024 + (CT_MAX_BIAS + 128) * 4 + 256;
+  int stages = (CT_SMEM_LIMIT - fixed) / (CT_A_STAGE + p.b_bytes);
+  if (stages > CT_MAX_STAGES) stages = CT_MAX_STAGES;
+  WOFT_REQUIRE(stages >= 2, "woft_conv_tc: tile does not fit shared memory");
+  p.stages = stages;
+  // always more than half of the SM's shared memory: one CTA per SM, which owns all 512 TMEM columns
+  int smem = stages * (CT_A_STAGE + p.b_bytes) + fixed;
+  if (smem < 120 * 1024) smem = 120 * 1024;
+
+  int sms = 0;
+  WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (a->epilogue) {
+    case CT_EPI_BIAS_ACT:
+      return ct_launch<CT_EPI_BIAS_ACT>(p, grid, smem, s);
+    case CT_EPI_GRU_ZR:
+      return ct_launch<CT_EPI_GRU_ZR>(p, grid, smem, s);
+    case CT_EPI_GRU_Q:
+      return ct_launch<CT_EPI_GRU_Q>(p, grid, smem, s);
+    default: {
+      // the logits start at zero; the kernel adds each image's patch mean in (at most) two parts
+      const long long n_img = a->height / a->row_period;
+      fill_kernel<<<(unsigned)((n_img + 255) / 256), 256, 0, s>>>(a->head_out, 0.f, n_img);
+      int rc = launch_status("fill_kernel");
+      if (rc != WOFT_OK) return rc;
+      return ct_launch<CT_EPI_HEAD_MEAN>(p, grid, smem, s);
+    }
+  }
+}
+
+extern "C" int woft_conv_tc_check(void* stream) {
+  using namespace woft;
+  int flag = 0;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  WOFT_CUDA_CHECK(cudaMemcpyFromSymbolAsync(&flag, g_conv_abort, sizeof(int), 0, cudaMemcpyDeviceToHost, s));
+  WOFT_CUDA_CHECK(cudaStreamSynchronize(s));
+  if (flag != 0) return fail(WOFT_ERR_CUDA, "convolution kernel aborted: a pipeline barrier timed out (flag=%d)", flag);
+  return WOFT_OK;
+}

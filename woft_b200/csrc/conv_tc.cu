@@ -126,7 +126,7 @@ __device__ __forceinline__ void ct_store_row(void* base, long long stride, long 
                                              bool f16) {
   if (f16) {
     __half* o = reinterpret_cast<__half*>(base) + pix * stride + col;
-    if (nv == 32) {
+    if (nv == 32 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
 #pragma unroll
       for (int j = 0; j < 32; j += 8) {
         __half2 a = __floats2half2_rn(v[j], v[j + 1]), b = __floats2half2_rn(v[j + 2], v[j + 3]);
@@ -143,7 +143,7 @@ __device__ __forceinline__ void ct_store_row(void* base, long long stride, long 
     }
   } else {
     float* o = reinterpret_cast<float*>(base) + pix * stride + col;
-    if (nv == 32) {
+    if (nv == 32 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
 #pragma unroll
       for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
     } else {
@@ -506,10 +506,11 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
 
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {
-    WOFT_REQUIRE(a->out && (reinterpret_cast<uintptr_t>(a->out) & 15) == 0 && (a->out_stride * oesz) % 16 == 0,
-                 "woft_conv_tc: output must be 16-byte aligned with a 16-byte multiple pixel stride");
-    WOFT_REQUIRE(!a->out2 || ((reinterpret_cast<uintptr_t>(a->out2) & 15) == 0 && (a->out2_stride * oesz) % 16 == 0),
-                 "woft_conv_tc: second output must be 16-byte aligned with a 16-byte multiple pixel stride");
+    // rows that are not 16-byte aligned (odd strides / offsets) are stored element by element
+    WOFT_REQUIRE(a->out && (reinterpret_cast<uintptr_t>(a->out) % oesz) == 0 && a->out_stride >= a->cout,
+                 "woft_conv_tc: output missing, misaligned or narrower than Cout");
+    WOFT_REQUIRE(!a->out2 || ((reinterpret_cast<uintptr_t>(a->out2) % oesz) == 0 && a->out2_stride >= a->cout),
+                 "woft_conv_tc: second output misaligned or narrower than Cout");
   } else if (a->epilogue == CT_EPI_GRU_ZR) {
     WOFT_REQUIRE(p.n_tiles == 1 && bn % 64 == 0 && a->cout == bn, "woft_conv_tc: GRU gate epilogue takes the stacked z|r "
                  "filters as one tile (Cout = 2 * hidden, a multiple of 64, at most 256)");

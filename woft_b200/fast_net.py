@@ -20,7 +20,7 @@ import os
 import torch
 import torch.nn.functional as F
 
-from . import _lib
+from . import _lib, conv_tc
 from .corr import CorrBlock as _CorrBlock
 from .raft_net import pixel_grid
 
@@ -254,6 +254,7 @@ class FastWeightedRAFT:
             # channels-last copies of the update block's weights: with NHWC activations cuDNN's sm_100 kernels run
             # without the NCHW<->NHWC conversion kernels that otherwise wrap every convolution
             self.nhwc = nhwc_update
+            self.own_convs = self.own_head = False
             # both encoders' 3-channel first layer through woft_stem_conv7x7 instead of cuDNN's sm_80 fallback
             self.own_stem = os.environ.get("WOFT_OWN_STEM", "1") == "1"
             self.own_head_conv1 = os.environ.get("WOFT_OWN_HEAD_CONV1", "1") == "1"
@@ -287,6 +288,33 @@ class FastWeightedRAFT:
                 self.conv_pad = pad
                 self.ubw["conv"] = (_cl(torch.cat([wc, wc.new_zeros((pad,) + tuple(wc.shape[1:]))], 0)),
                                     torch.cat([bc, bc.new_zeros(pad)], 0).contiguous())
+                # the update block's and the weight head's wide convolutions on woft_conv_tc (tcgen05 implicit GEMM with
+                # the element-wise stage of each layer in its epilogue) instead of cuDNN: TF32 operands, so only when
+                # the caller allows TF32-class convolutions
+                self.own_convs = (self.tf32 and os.environ.get("WOFT_OWN_CONVS", "1") == "1"
+                                  and net.hidden_dim == net.context_dim == 128 and e.conv.weight.shape[0] == 126)
+                if self.own_convs:
+                    P = conv_tc.PackedConv
+                    self.tc = {name: P(m.weight, m.bias, m.padding) for name, m in (
+                        ("convc1", e.convc1), ("convc2", e.convc2), ("convf2", e.convf2), ("conv", e.conv),
+                        ("fh1", ub.flow_head.conv1), ("m0", ub.mask[0]), ("m2", ub.mask[2]))}
+                    for tag in ("1", "2"):
+                        gt = self.gru[tag]
+                        self.tc["zr" + tag] = P(gt["w_zr"], gt["b_zr"], gt["padding"])
+                        self.tc["q" + tag] = P(gt["w_q"], gt["b_q"], gt["padding"])
+                    self.own_head = False
+                    if self.with_weights and os.environ.get("WOFT_OWN_HEAD", "1") == "1":
+                        convs = [m for m in net.weight_head.net if isinstance(m, torch.nn.Conv2d)]
+                        if (len(convs) == 4 and tuple(convs[0].weight.shape) == (128, 5, 3, 3)
+                                and all(tuple(c.weight.shape) == (128, 128, 3, 3) for c in convs[1:3])
+                                and tuple(convs[3].weight.shape) == (1, 128, 1, 1)):
+                            # layers 2 and 3 read and write fp16 activations (10-bit mantissa like TF32, half the
+                            # 2.6 GB the three layers would otherwise move), fp32 accumulation
+                            self.tc["head2"] = P(convs[1].weight, convs[1].bias, 1, f16=True)
+                            self.tc["head3"] = P(convs[2].weight, convs[2].bias, 1, f16=True)
+                            self.head_w1x1 = convs[3].weight.detach().reshape(-1).float().contiguous()
+                            self.head_b1x1 = float(convs[3].bias.detach().item())
+                            self.own_head = True
                 for tag in ("1", "2"):
                     gt = self.gru[tag]
                     gt["w_zr"], gt["w_q"] = _cl(gt["w_zr"]), _cl(gt["w_q"])
@@ -403,6 +431,8 @@ class FastWeightedRAFT:
               "buf1": _empty_cl(B, 3 * C, H, W, ctx_out), "buf2": _empty_cl(B, 3 * C, H, W, ctx_out), "C": C,
               "pixels": B * H * W, "coords0": coords0.contiguous(), "coords1": coords1.contiguous().clone(),
               "flow": flow, "flow_cl": _cl(flow).clone()}   # flow_cl: logical (B,2,H,W), stored (B,H,W,2)
+        if self.own_convs:
+            st["cor1"], st["cf"], st["fh"] = (_empty_cl(B, 256, H, W, ctx_out) for _ in range(3))
         with torch.cuda.device(ctx_out.device):
             rc = _lib.load().woft_context_split_nhwc(_lib.ptr(ctx_out), _lib.ptr(ctx_bias), B * H * W, C, _lib.ptr(st["h"]),
                                                      _lib.ptr(st["buf1"]), _lib.ptr(st["buf2"]), 3 * C,
@@ -441,6 +471,8 @@ class FastWeightedRAFT:
         w = self.ubw
         e = self.net.update_block.encoder
         flo = flow_conv7x7_relu(st["flow"], e.convf1.weight, e.convf1.bias)   # NCHW flow in, channels-last out
+        if self.own_convs:
+            return self._update_own(st, corr, flo, need_mask)
         cor = _conv_relu(corr, *w["convc1"])
         cor = _conv_relu(cor, *w["convc2"], padding=(1, 1))
         flo = _conv_relu(flo, *w["convf2"], padding=(1, 1))
@@ -462,6 +494,33 @@ class FastWeightedRAFT:
         mask = None
         if need_mask:
             mask = conv_bias_nhwc(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"], scale=0.25)
+        return mask
+
+    def _update_own(self, st, corr, flo, need_mask):
+        """The iteration on woft_conv_tc: every wide convolution is one launch that also applies its bias / ReLU / GRU gate
+        arithmetic and writes where the next layer reads (no concatenation, no separate element-wise kernels)."""
+        tc, C, ci = self.tc, st["C"], st["ci"]
+        buf1, buf2, cf = st["buf1"], st["buf2"], st["cf"]
+        conv_tc.run(tc["convc1"], corr, relu=True, out=st["cor1"])
+        conv_tc.run(tc["convc2"], st["cor1"], relu=True, out=cf)                        # cf = [cor (192) | flo (64)]
+        conv_tc.run(tc["convf2"], flo, relu=True, out=cf, out_off=tc["convc2"].cout)
+        # x = [inp | motion (126) | flow (2)] behind h resp. r*h in both GRU buffers (update.py:96-97)
+        conv_tc.run(tc["conv"], cf, relu=True, out=buf1, out_off=C + ci, out2=buf2, out2_off=C + ci)
+        concat_nhwc([st["flow_cl"]], buf1, C + ci + tc["conv"].cout, buf2, C + ci + tc["conv"].cout)
+        for tag in ("1", "2"):
+            conv_tc.run(tc["zr" + tag], buf1, epilogue=_lib.CONV_GRU_ZR, h=buf1, z=st["z"], out=buf2)
+            conv_tc.run(tc["q" + tag], buf2, epilogue=_lib.CONV_GRU_Q, h=buf1, z=st["z"], out=buf1)
+        conv_tc.run(tc["fh1"], buf1, relu=True, out=st["fh"])                           # reads the h slice of buf1
+        fh = self.net.update_block.flow_head
+        flow_head_step(st["fh"], fh.conv2.weight, fh.conv2.bias, coords=st["coords1"], coords0=st["coords0"],
+                       flow_nchw=st["flow"], flow_nhwc=st["flow_cl"])
+        mask = None
+        if need_mask:
+            B, _, H, W = buf1.shape
+            m = _empty_cl(B, tc["m0"].cout, H, W, buf1)
+            conv_tc.run(tc["m0"], buf1, relu=True, out=m)
+            mask = _empty_cl(B, tc["m2"].cout, H, W, buf1)
+            conv_tc.run(tc["m2"], m, relu=False, scale=0.25, out=mask)
         return mask
 
     # ---- weight head, channels-last -----------------------------------------------------------------------------

@@ -119,7 +119,9 @@ void woft_corr_set_trace_buffer(unsigned long long* device_buffer);
  *   coords : (B, 2, H1, W1), channel 0 = x, channel 1 = y
  *   out    : (B, num_levels*(2r+1)^2, H1, W1); channel = l*(2r+1)^2 + (xoff+r)*(2r+1) + (yoff+r)
  *   flags  : bit 0 = scalar loads (testing); bit 3 (8) = write `out` channels-last, (B, H1, W1, channels), for an
- *            NHWC consumer (same values)
+ *            NHWC consumer (same values); bit 4 (16, with bit 3) = `out` holds fp16 with the channels of a query padded
+ *            to a multiple of 8 (328 for 4 levels of radius 4; the padding is not written): the operand of an fp16
+ *            tensor-core convolution, whose TMA loads need 16-byte multiples between pixels
  * Level maps narrower than 2 pixels make the reference return NaN (division by W-1 = 0, utils.py:63-64);
  * this call rejects them with WOFT_ERR_INVALID_ARGUMENT instead.
  */
@@ -197,6 +199,15 @@ int woft_flow_conv7x7_relu(const float* flow, const float* weight, const float* 
                            float* out_nhwc, void* stream);
 int woft_flow_out3x3(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
                      int channels, float* out_nchw, void* stream);
+/* woft_flow_conv7x7_relu with an fp16 output tensor (B,H,W,128): the operand of an fp16 tensor-core convolution. */
+int woft_flow_conv7x7_relu_f16(const float* flow, const float* weight, const float* bias, int batch, int height,
+                               int width, void* out_nhwc_f16, void* stream);
+/* fp32 channels-last values (pixels, src_stride), the first `channels` of every pixel, rounded to fp16 into channel
+ * slice [dst_offset, dst_offset + channels) of one or two fp16 tensors (pixels, dst_stride): fills the fp16 operand
+ * buffers of woft_conv_tc from fp32 producers (context features, hidden state, the flow behind the motion features,
+ * update.py:97).  Even channel counts, strides and offsets. */
+int woft_cast_nhwc_f16(const float* src, int src_stride, int channels, long long pixels, void* dst, int dst_stride,
+                       int dst_offset, void* dst2, int dst2_stride, int dst2_offset, void* stream);
 
 /* FlowHead.conv2 and the step of the refinement loop that follows it (raft_core/weighted_raft.py:244-246:
  * coords1 = coords1 + delta_flow; next iteration's flow = coords1 - coords0) in two launches that read every input
@@ -319,6 +330,11 @@ int woft_stem_conv7x7(const float* in_nhwc, const float* weight, const float* bi
  *   -> out (n, 9, 9, 128) channels-last.  patch, levels, channels_out must be 9, 4, 128 (the shipped head). */
 int woft_weight_head_conv1(const float* window_nhwc, const float* mean_response, const float* weight, const float* bias,
                            long long n_images, int patch, int levels, int channels_out, float* out_nhwc, void* stream);
+/* The same layer writing fp16 in the layout woft_conv_tc takes for layers 2 and 3: (n, 10, 9, 128), every image's 9 rows
+ * of 9 pixels followed by one all-zero row (the vertical zero padding between the images stacked along H). */
+int woft_weight_head_conv1_stacked_f16(const float* window_nhwc, const float* mean_response, const float* weight,
+                                       const float* bias, long long n_images, int patch, int levels, int channels_out,
+                                       void* out_stacked_f16, void* stream);
 
 /* The wide convolutions of the update block and of the weight head as ONE implicit-GEMM kernel on the tcgen05 tensor
  * cores, with the element-wise stage that follows each of them in the reference fused into the epilogue.  Replaces the
@@ -335,8 +351,9 @@ int woft_weight_head_conv1(const float* window_nhwc, const float* mean_response,
  *                                      (out_f16); `out2` (optional) receives the same values; strides in elements
  *                 WOFT_CONV_GRU_ZR   : cout = 2C stacked convz|convr filters; z[pix][c] = sigmoid(acc[c] + bias[c]);
  *                                      out[pix][c] = sigmoid(acc[C+c] + bias[C+c]) * h[pix][c]      (update.py:47-52)
- *                 WOFT_CONV_GRU_Q    : cout = C; out[pix][c] = (1 - z) * h + z * tanh(acc + bias); out may alias h;
- *                                      out2 optional second copy                                     (update.py:53-54)
+ *                 WOFT_CONV_GRU_Q    : cout = C; out[pix][c] = (1 - z) * h + z * tanh(acc + bias), fp32, may alias h;
+ *                                      out2 optional second copy, fp32 or fp16 (out2_f16)            (update.py:53-54)
+ *                 (h and z are fp32; in GRU_ZR the r*h output may be fp16 (out_f16): it is a convolution operand)
  *                 WOFT_CONV_HEAD_MEAN: images of row_valid x W pixels stacked along H every row_period rows (batch 1);
  *                                      head_out[image] = head_bias + mean over the image of w1x1 . relu(acc + bias)
  *   row_period, row_valid: when row_period > 0, rows y with y % row_period >= row_valid separate stacked images: the
@@ -360,6 +377,7 @@ typedef struct woft_conv_tc_args {
   int out_f16;
   void* out2;
   long long out2_stride;
+  int out2_f16;
   const float* h;
   long long h_stride;
   float* z;

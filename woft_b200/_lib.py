@@ -30,7 +30,7 @@ class ConvTcArgs(ctypes.Structure):
                 ("cout", c_int), ("cout_pad", c_int), ("kh", c_int), ("kw", c_int), ("pad_h", c_int), ("pad_w", c_int),
                 ("box_w", c_int), ("box_h", c_int), ("epilogue", c_int), ("relu", c_int), ("scale", c_float),
                 ("bias", c_void_p), ("out", c_void_p), ("out_stride", ctypes.c_longlong), ("out_f16", c_int),
-                ("out2", c_void_p), ("out2_stride", ctypes.c_longlong), ("h", c_void_p), ("h_stride", ctypes.c_longlong),
+                ("out2", c_void_p), ("out2_stride", ctypes.c_longlong), ("out2_f16", c_int), ("h", c_void_p), ("h_stride", ctypes.c_longlong),
                 ("z", c_void_p), ("z_stride", ctypes.c_longlong), ("w1x1", c_void_p), ("head_out", c_void_p),
                 ("head_bias", c_float), ("row_period", c_int), ("row_valid", c_int)]
 
@@ -85,6 +85,8 @@ SIGNATURES = {
     "woft_stem_conv7x7": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_weight_head_conv1": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_int, c_int, c_int,
                                        c_void_p, c_void_p]),
+    "woft_weight_head_conv1_stacked_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, ctypes.c_longlong, c_int, c_int,
+                                                   c_int, c_void_p, c_void_p]),
     "woft_bias_act_nhwc": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_float, c_int, c_void_p]),
     "woft_context_split_nhwc": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_void_p, c_void_p, c_void_p, c_int,
                                         c_void_p]),
@@ -102,6 +104,9 @@ SIGNATURES = {
                                      c_void_p]),
     "woft_instance_norm_relu": (c_int, [c_void_p, c_int, c_int, c_float, c_int, c_void_p, c_void_p]),
     "woft_conv_tc": (c_int, [POINTER(ConvTcArgs), c_void_p]),
+    "woft_flow_conv7x7_relu_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "woft_cast_nhwc_f16": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
+                                   c_void_p]),
     "woft_conv_tc_check": (c_int, [c_void_p]),
 }
 

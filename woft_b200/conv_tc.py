@@ -75,6 +75,7 @@ def run(pc, x, x_off=0, epilogue=_lib.CONV_BIAS_ACT, relu=False, scale=1.0, out=
     a.out, a.out_stride = _slice(out, out_off)
     a.out_f16 = int(out is not None and out.dtype == torch.float16)
     a.out2, a.out2_stride = _slice(out2, out2_off)
+    a.out2_f16 = int(out2 is not None and out2.dtype == torch.float16)
     a.h, a.h_stride = _slice(h, h_off)
     a.z, a.z_stride = _slice(z, 0)
     a.w1x1 = _lib.ptr(w1x1)

@@ -84,9 +84,14 @@ class CorrBlock:
             raise AssertionError(f"coords must be ({B},2,{H},{W}), got {tuple(coords.shape)}")
         P = 2 * self.radius + 1
         dev = coords.device
-        # flags bit 3: channels-last output for an NHWC consumer (same logical shape and values)
+        # flags bit 3: channels-last output for an NHWC consumer (same logical shape and values); bit 4 (with bit 3):
+        # fp16, channels padded to a multiple of 8 (the padding is never written) -- the operand of woft_conv_tc
         fmt = torch.channels_last if flags & 8 else torch.contiguous_format
-        out = torch.empty((B, self.num_levels * P * P, H, W), device=dev, dtype=torch.float32, memory_format=fmt)
+        ch = self.num_levels * P * P
+        if flags & 16:
+            out = torch.empty((B, (ch + 7) // 8 * 8, H, W), device=dev, dtype=torch.float16, memory_format=fmt)
+        else:
+            out = torch.empty((B, ch, H, W), device=dev, dtype=torch.float32, memory_format=fmt)
         with torch.cuda.device(dev):
             levels, keep = _lib.ptr_array(self.corr_pyramid)
             rc = _lib.load().woft_corr_lookup(levels, self.num_levels, _lib.ptr(coords), B, H, W, H, W, self.radius,

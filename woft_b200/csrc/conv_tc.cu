@@ -63,6 +63,7 @@ struct ConvTcParams {
   int out_f16;
   void* out2;
   long long out2_stride;
+  int out2_f16;
   const float* h;
   long long h_stride;
   float* z;
@@ -317,7 +318,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               v[j] = separator ? 0.f : a * p.scale;
             }
             ct_store_row(p.out, p.out_stride, pix, col, v, nv, p.out_f16 != 0);
-            if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, nv, p.out_f16 != 0);
+            if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, nv, p.out2_f16 != 0);
           }
         } else if (EPI == CT_EPI_GRU_ZR) {
           const int hid = p.bn >> 1;
@@ -331,7 +332,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               ct_load_row(p.h, p.h_stride, pix, col - hid, hv);
 #pragma unroll
               for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + s_bias[col + j]) * hv[j];
-              ct_store_row(p.out, p.out_stride, pix, col - hid, v, 32, false);
+              ct_store_row(p.out, p.out_stride, pix, col - hid, v, 32, p.out_f16 != 0);
             }
           }
         } else if (EPI == CT_EPI_GRU_Q) {
@@ -342,7 +343,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = (1.f - zv[j]) * hv[j] + zv[j] * tanhf(v[j] + s_bias[col + j]);
             ct_store_row(p.out, p.out_stride, pix, col, v, 32, false);
-            if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, 32, false);
+            if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, 32, p.out2_f16 != 0);
           }
         } else {  // CT_EPI_HEAD_MEAN
 #pragma unroll
@@ -495,6 +496,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.out_f16 = a->out_f16;
   p.out2 = a->out2;
   p.out2_stride = a->out2_stride;
+  p.out2_f16 = a->out2_f16;
   p.h = a->h;
   p.h_stride = a->h_stride;
   p.z = a->z;
@@ -506,6 +508,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
 
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {
+    WOFT_REQUIRE(!a->out2 || a->out2_f16 == a->out_f16, "woft_conv_tc: both outputs of this epilogue share one type");
     // rows that are not 16-byte aligned (odd strides / offsets) are stored element by element
     WOFT_REQUIRE(a->out && (reinterpret_cast<uintptr_t>(a->out) % oesz) == 0 && a->out_stride >= a->cout,
                  "woft_conv_tc: output missing, misaligned or narrower than Cout");
@@ -514,15 +517,14 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   } else if (a->epilogue == CT_EPI_GRU_ZR) {
     WOFT_REQUIRE(p.n_tiles == 1 && bn % 64 == 0 && a->cout == bn, "woft_conv_tc: GRU gate epilogue takes the stacked z|r "
                  "filters as one tile (Cout = 2 * hidden, a multiple of 64, at most 256)");
-    WOFT_REQUIRE(a->h && a->z && a->out && !a->out_f16, "woft_conv_tc: GRU gate epilogue needs h, z and the r*h output (fp32)");
-    WOFT_REQUIRE(((reinterpret_cast<uintptr_t>(a->h) | reinterpret_cast<uintptr_t>(a->z) | reinterpret_cast<uintptr_t>(a->out)) & 15) == 0 &&
-                 a->h_stride % 4 == 0 && a->z_stride % 4 == 0 && a->out_stride % 4 == 0, "woft_conv_tc: GRU operands must be 16-byte aligned");
+    WOFT_REQUIRE(a->h && a->z && a->out, "woft_conv_tc: GRU gate epilogue needs h, z and the r*h output");
+    WOFT_REQUIRE(((reinterpret_cast<uintptr_t>(a->h) | reinterpret_cast<uintptr_t>(a->z)) & 15) == 0 &&
+                 a->h_stride % 4 == 0 && a->z_stride % 4 == 0, "woft_conv_tc: GRU operands must be 16-byte aligned");
   } else if (a->epilogue == CT_EPI_GRU_Q) {
     WOFT_REQUIRE(p.n_tiles == 1 && a->cout == bn, "woft_conv_tc: GRU update epilogue takes Cout = hidden as one tile");
     WOFT_REQUIRE(a->h && a->z && a->out && !a->out_f16, "woft_conv_tc: GRU update epilogue needs h, z and the output (fp32)");
-    WOFT_REQUIRE(((reinterpret_cast<uintptr_t>(a->h) | reinterpret_cast<uintptr_t>(a->z) | reinterpret_cast<uintptr_t>(a->out) |
-                   reinterpret_cast<uintptr_t>(a->out2)) & 15) == 0 &&
-                 a->h_stride % 4 == 0 && a->z_stride % 4 == 0 && a->out_stride % 4 == 0 && a->out2_stride % 4 == 0,
+    WOFT_REQUIRE(((reinterpret_cast<uintptr_t>(a->h) | reinterpret_cast<uintptr_t>(a->z) | reinterpret_cast<uintptr_t>(a->out)) & 15) == 0 &&
+                 a->h_stride % 4 == 0 && a->z_stride % 4 == 0 && a->out_stride % 4 == 0,
                  "woft_conv_tc: GRU operands must be 16-byte aligned");
   } else {
     WOFT_REQUIRE(p.n_tiles == 1 && a->w1x1 && a->head_out && a->row_period > 0 && a->row_valid > 0 &&

@@ -10,6 +10,8 @@
 //   instance_norm_relu_kernel  one CTA per (n, c) plane: mean / biased variance, then (x - mean) * rstd, ReLU
 //                              (eps 1e-5, no affine: nn.InstanceNorm2d defaults), second read served by L2.
 // All tensors NCHW fp32 contiguous.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace woft {
@@ -368,6 +370,22 @@ static int ew_grid(long long total4) {
   return int(blocks < 148 * 16 ? (blocks > 0 ? blocks : 1) : 148 * 16);
 }
 
+// fp32 channels (pixels, src_stride) -> fp16 channel slices of one or two (pixels, dst_stride) tensors: feeds the fp16
+// operand buffers of the tensor-core convolutions (context features, hidden state, the 2-channel flow) from fp32 producers.
+__global__ void cast_nhwc_f16_kernel(const float* __restrict__ src, int src_stride, int channels, unsigned total,
+                                     __half* __restrict__ d1, int d1_stride, int d1_off, __half* __restrict__ d2,
+                                     int d2_stride, int d2_off) {
+  const unsigned per_pixel = unsigned(channels) / 2;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const unsigned pix = i / per_pixel;
+    const int c = int(i - pix * per_pixel) * 2;
+    const float2 v = __ldg(reinterpret_cast<const float2*>(src + (size_t)pix * src_stride + c));
+    const __half2 hv = __floats2half2_rn(v.x, v.y);
+    *reinterpret_cast<__half2*>(d1 + (size_t)pix * d1_stride + d1_off + c) = hv;
+    if (d2) *reinterpret_cast<__half2*>(d2 + (size_t)pix * d2_stride + d2_off + c) = hv;
+  }
+}
+
 }  // namespace woft
 
 extern "C" int woft_gru_gates(const float* zr, const float* bias_zr, const float* h, int batch, int channels, int hw,
@@ -508,6 +526,22 @@ extern "C" int woft_concat_nhwc_strided(const float* const* srcs, const int* cha
   WOFT_REQUIRE(src_strides, "woft_concat_nhwc_strided: null stride array");
   return concat_nhwc_impl(srcs, channels, src_strides, n_src, pixels, dst, dst_stride, dst_offset, dst2, dst2_stride,
                           dst2_offset, stream);
+}
+
+extern "C" int woft_cast_nhwc_f16(const float* src, int src_stride, int channels, long long pixels, void* dst,
+                                  int dst_stride, int dst_offset, void* dst2, int dst2_stride, int dst2_offset, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(src && dst && pixels > 0 && channels > 0, "woft_cast_nhwc_f16: null pointer or empty tensor");
+  WOFT_REQUIRE(channels % 2 == 0 && src_stride % 2 == 0 && dst_stride % 2 == 0 && dst_offset % 2 == 0 &&
+               dst2_stride % 2 == 0 && dst2_offset % 2 == 0 && (reinterpret_cast<uintptr_t>(src) & 7) == 0 &&
+               (reinterpret_cast<uintptr_t>(dst) & 3) == 0 && (reinterpret_cast<uintptr_t>(dst2) & 3) == 0,
+               "woft_cast_nhwc_f16: channel counts, strides and offsets must be even and the pointers aligned to a pair");
+  const long long total = pixels * (channels / 2);
+  WOFT_REQUIRE(total <= kMaxElems32, "woft_cast_nhwc_f16: more than 2^31 - 1 pairs");
+  cast_nhwc_f16_kernel<<<ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      src, src_stride, channels, unsigned(total), static_cast<__half*>(dst), dst_stride, dst_offset,
+      static_cast<__half*>(dst2), dst2_stride, dst2_offset);
+  return launch_status("cast_nhwc_f16_kernel");
 }
 
 extern "C" size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels) {

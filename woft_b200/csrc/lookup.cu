@@ -20,6 +20,8 @@
 //                  i.e. two full 64-byte segments per store instruction in the reference's channel-first layout.
 // Algorithmic bytes per query pixel (r=4, 4 levels): 4*10*10*4 B read + 8 B coords + 324*4 B written = 2904 B.
 // DRAM moves more than that: a 40-byte row at a random offset costs one or two 64-byte sectors pairs.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace woft {
@@ -33,6 +35,8 @@ struct LookupParams {
   float* out;           // (B, L*P*P, H1, W1)
   int nq;               // B*H1*W1
   int hw1;              // H1*W1
+  int out_f16;          // channels-last output holds __half (flag 16): the A operand of an fp16 tensor-core convolution
+  int out_stride;       // channels-last output: elements between consecutive queries (channels, rounded up to 8 for fp16)
 };
 
 constexpr int kLookupThreads = 128;
@@ -160,9 +164,16 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
         float h[4];
 #pragma unroll
         for (int r = 0; r < 4; ++r) h[r] = fmaf(ax, c[r * WIN + 1], bx * c[r * WIN]);
-        float* o = p.out + (size_t)q * channels + (size_t)lvl * P * P + xo * P + y3;
+        const size_t oi = (size_t)q * p.out_stride + (size_t)lvl * P * P + xo * P + y3;
+        if (p.out_f16) {
+          __half* o = reinterpret_cast<__half*>(p.out) + oi;
 #pragma unroll
-        for (int j = 0; j < 3; ++j) o[j] = fmaf(ay, h[j + 1], by * h[j]);
+          for (int j = 0; j < 3; ++j) o[j] = __float2half_rn(fmaf(ay, h[j + 1], by * h[j]));
+        } else {
+          float* o = p.out + oi;
+#pragma unroll
+          for (int j = 0; j < 3; ++j) o[j] = fmaf(ay, h[j + 1], by * h[j]);
+        }
       }
     } else if (NHWC) {
       // channels-last output, any radius: lanes take consecutive taps, 4-tap bilinear weights
@@ -182,12 +193,16 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
         const float* my = win + pair * STRIDE;
         const float ax = s_ax[pair], ay = s_ay[pair];
         const float w00 = (1.f - ax) * (1.f - ay), w01 = ax * (1.f - ay), w10 = (1.f - ax) * ay, w11 = ax * ay;
-        float* o = p.out + (size_t)q * channels + (size_t)lvl * P * P + lane;
+        const size_t oi = (size_t)q * p.out_stride + (size_t)lvl * P * P + lane;
 #pragma unroll
         for (int k = 0; k < ROUNDS; ++k) {
           if (tap_off[k] >= 0) {
             const float* c = my + tap_off[k];
-            o[32 * k] = c[0] * w00 + c[1] * w01 + c[WIN] * w10 + c[WIN + 1] * w11;
+            const float r = c[0] * w00 + c[1] * w01 + c[WIN] * w10 + c[WIN + 1] * w11;
+            if (p.out_f16)
+              reinterpret_cast<__half*>(p.out)[oi + 32 * k] = __float2half_rn(r);
+            else
+              p.out[oi + 32 * k] = r;
           }
         }
       }
@@ -274,6 +289,12 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   p.num_levels = num_levels;
   p.coords = coords;
   p.out = out;
+  {
+    const int P = 2 * radius + 1, channels = num_levels * P * P;
+    p.out_f16 = (flags & 16) != 0;
+    WOFT_REQUIRE(!p.out_f16 || nhwc, "woft_corr_lookup: the fp16 output (flag 16) exists for the channels-last layout (flag 8)");
+    p.out_stride = p.out_f16 ? (channels + 7) / 8 * 8 : channels;
+  }
   p.nq = batch * h1 * w1;
   p.hw1 = h1 * w1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);

@@ -14,6 +14,8 @@
 //                              pixels per lane, eight warps splitting the channels), then per output pixel the sum of
 //                              the 9 shifted taps + bias, fused with the coordinate update that follows the flow
 //                              head in the refinement loop (weighted_raft.py:244-246: coords1 = coords1 + delta_flow).
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -30,10 +32,11 @@ namespace woft {
 constexpr int kF7Seg = 7, kF7Slots = 16;
 constexpr int kF7Cout = 128, kF7WStride = 132;
 
+template <bool F16OUT>   // F16OUT: the output tensor holds __half (input of an fp16 tensor-core convolution)
 __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __restrict__ flow,   // (B,2,H,W)
                                                                 const float* __restrict__ weight, // (128,2,7,7)
                                                                 const float* __restrict__ bias,   // (128)
-                                                                float* __restrict__ out,          // (B,H,W,128)
+                                                                void* __restrict__ out_any,       // (B,H,W,128)
                                                                 int H, int W, int segs_per_cta, int rows_max) {
   extern __shared__ __align__(16) float sm[];
   float* sw = sm;                                // [98 taps][132]
@@ -121,9 +124,21 @@ __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __r
       float a[8];
 #pragma unroll
       for (int k = 0; k < 4; ++k) ptx::unpack_f32x2(acc[j][k], a[2 * k], a[2 * k + 1]);
-      float4* o = reinterpret_cast<float4*>(out + (((size_t)b * H + y) * W + x0 + j) * kF7Cout);
-      o[grp] = make_float4(fmaxf(a[0], 0.f), fmaxf(a[1], 0.f), fmaxf(a[2], 0.f), fmaxf(a[3], 0.f));
-      o[16 + grp] = make_float4(fmaxf(a[4], 0.f), fmaxf(a[5], 0.f), fmaxf(a[6], 0.f), fmaxf(a[7], 0.f));
+      const size_t pix = ((size_t)b * H + y) * W + x0 + j;
+      if (F16OUT) {
+        __half2* o = reinterpret_cast<__half2*>(reinterpret_cast<__half*>(out_any) + pix * kF7Cout);
+        uint2 lo, hi;
+        __half2 t0 = __floats2half2_rn(fmaxf(a[0], 0.f), fmaxf(a[1], 0.f)), t1 = __floats2half2_rn(fmaxf(a[2], 0.f), fmaxf(a[3], 0.f));
+        __half2 t2 = __floats2half2_rn(fmaxf(a[4], 0.f), fmaxf(a[5], 0.f)), t3 = __floats2half2_rn(fmaxf(a[6], 0.f), fmaxf(a[7], 0.f));
+        lo.x = *reinterpret_cast<uint32_t*>(&t0); lo.y = *reinterpret_cast<uint32_t*>(&t1);
+        hi.x = *reinterpret_cast<uint32_t*>(&t2); hi.y = *reinterpret_cast<uint32_t*>(&t3);
+        reinterpret_cast<uint2*>(o)[grp] = lo;        // channels 4g..4g+3
+        reinterpret_cast<uint2*>(o)[16 + grp] = hi;   // channels 64+4g..64+4g+3
+      } else {
+        float4* o = reinterpret_cast<float4*>(reinterpret_cast<float*>(out_any) + pix * kF7Cout);
+        o[grp] = make_float4(fmaxf(a[0], 0.f), fmaxf(a[1], 0.f), fmaxf(a[2], 0.f), fmaxf(a[3], 0.f));
+        o[16 + grp] = make_float4(fmaxf(a[4], 0.f), fmaxf(a[5], 0.f), fmaxf(a[6], 0.f), fmaxf(a[7], 0.f));
+      }
     }
   }
 }
@@ -339,8 +354,8 @@ __global__ void flow_head_gather_kernel(const float* __restrict__ taps, const fl
 
 }  // namespace woft
 
-extern "C" int woft_flow_conv7x7_relu(const float* flow, const float* weight, const float* bias, int batch, int height,
-                                      int width, float* out_nhwc, void* stream) {
+static int flow_conv7x7_impl(const float* flow, const float* weight, const float* bias, int batch, int height, int width,
+                             void* out_nhwc, bool f16, void* stream) {
   using namespace woft;
   WOFT_REQUIRE(flow && weight && bias && out_nhwc, "woft_flow_conv7x7_relu: null pointer");
   WOFT_REQUIRE(batch > 0 && height > 0 && width > 0 && batch < 65536, "woft_flow_conv7x7_relu: bad extent");
@@ -352,11 +367,26 @@ extern "C" int woft_flow_conv7x7_relu(const float* flow, const float* weight, co
   const int rows_max = (spc - 1) / segs_per_row + 2 + 6;   // rows the segments of a CTA can touch, plus the halo
   const size_t smem = (size_t)(98 * kF7WStride + 2 * rows_max * (segs_per_row * kF7Seg + 6)) * sizeof(float);
   WOFT_REQUIRE(smem <= 200 * 1024, "woft_flow_conv7x7_relu: width %d needs more shared memory than a CTA has", width);
-  WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_conv7x7_relu_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(ceil_div(total, spc), batch);
-  flow_conv7x7_relu_kernel<<<grid, 256, smem, static_cast<cudaStream_t>(stream)>>>(flow, weight, bias, out_nhwc, height,
-                                                                                  width, spc, rows_max);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (f16) {
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_conv7x7_relu_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    flow_conv7x7_relu_kernel<true><<<grid, 256, smem, s>>>(flow, weight, bias, out_nhwc, height, width, spc, rows_max);
+  } else {
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_conv7x7_relu_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    flow_conv7x7_relu_kernel<false><<<grid, 256, smem, s>>>(flow, weight, bias, out_nhwc, height, width, spc, rows_max);
+  }
   return launch_status("flow_conv7x7_relu_kernel");
+}
+
+extern "C" int woft_flow_conv7x7_relu(const float* flow, const float* weight, const float* bias, int batch, int height,
+                                      int width, float* out_nhwc, void* stream) {
+  return flow_conv7x7_impl(flow, weight, bias, batch, height, width, out_nhwc, false, stream);
+}
+
+extern "C" int woft_flow_conv7x7_relu_f16(const float* flow, const float* weight, const float* bias, int batch, int height,
+                                          int width, void* out_nhwc_f16, void* stream) {
+  return flow_conv7x7_impl(flow, weight, bias, batch, height, width, out_nhwc_f16, true, stream);
 }
 
 extern "C" int woft_flow_out3x3(const float* in_nhwc, const float* weight, const float* bias, int batch, int height,

@@ -9,6 +9,8 @@
 // zero-bordered 11 x 11 x 5 tiles and the A fragments gathered through a k -> offset table.  The 48 x 128 weight matrix
 // never leaves the registers: a warp owns 32 rows x 32 output channels and keeps its 6 x 4 B fragments for the whole
 // kernel.  Output (n, 9, 9, 128) channels-last, 597 MB at 1280x720 -- the kernel is bound by writing it.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace woft {
@@ -31,11 +33,14 @@ __device__ __forceinline__ void wh_mma(float (&d)[4], const float (&a)[4], float
         "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
 }
 
+// STACKED: the output is fp16 and every image takes 10 rows of 9 pixels, the tenth all zero -- the layout in which
+// woft_conv_tc runs the next two layers (the zero row is the vertical padding between stacked images).
+template <bool STACKED>
 __global__ void __launch_bounds__(256, 2) weight_head_conv1_kernel(const float* __restrict__ window,   // (n, 81 * 4)
                                                                    const float* __restrict__ mean_resp, // (n)
                                                                    const float* __restrict__ weight,    // (128, 5, 3, 3)
                                                                    const float* __restrict__ bias,      // (128)
-                                                                   float* __restrict__ out,             // (n * 81, 128)
+                                                                   void* __restrict__ out_any,          // (n * 81, 128)
                                                                    int n_img, int total_tiles) {
   __shared__ float tiles[2][2 * kWhTile];   // double buffered: the next step's images load while this one multiplies
   __shared__ int koff[kWhKP];
@@ -149,12 +154,30 @@ __global__ void __launch_bounds__(256, 2) weight_head_conv1_kernel(const float* 
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         if (grow[mt][h] >= total_rows) continue;
-        float* o = out + (size_t)grow[mt][h] * kWhCout + cq * 32 + 2 * t;
+        if (STACKED) {
+          const int img = grow[mt][h] / kWhPix, pp = grow[mt][h] - img * kWhPix;
+          __half* o = reinterpret_cast<__half*>(out_any) + ((size_t)img * (kWhPix + kWhP) + pp) * kWhCout + cq * 32 + 2 * t;
 #pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
-          *reinterpret_cast<float2*>(o + nt * 8) =
-              make_float2(fmaxf(acc[mt][nt][2 * h], 0.f), fmaxf(acc[mt][nt][2 * h + 1], 0.f));
+          for (int nt = 0; nt < 4; ++nt)
+            *reinterpret_cast<__half2*>(o + nt * 8) =
+                __floats2half2_rn(fmaxf(acc[mt][nt][2 * h], 0.f), fmaxf(acc[mt][nt][2 * h + 1], 0.f));
+        } else {
+          float* o = reinterpret_cast<float*>(out_any) + (size_t)grow[mt][h] * kWhCout + cq * 32 + 2 * t;
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt)
+            *reinterpret_cast<float2*>(o + nt * 8) =
+                make_float2(fmaxf(acc[mt][nt][2 * h], 0.f), fmaxf(acc[mt][nt][2 * h + 1], 0.f));
+        }
       }
+    if (STACKED) {
+      // the image whose first pixel lies in this tile (at most one: 81 rows per image, 64 per tile) gets its zero row
+      const int img_s = (row0 + kWhPix - 1) / kWhPix;
+      if (img_s < n_img && img_s * kWhPix < row0 + kWhRows) {
+        uint32_t* z = reinterpret_cast<uint32_t*>(reinterpret_cast<__half*>(out_any) +
+                                                  ((size_t)img_s * (kWhPix + kWhP) + kWhPix) * kWhCout);
+        for (int i = tid; i < kWhP * kWhCout / 2; i += 256) z[i] = 0u;
+      }
+    }
   }
 }
 
@@ -171,7 +194,24 @@ extern "C" int woft_weight_head_conv1(const float* window_nhwc, const float* mea
   const long long tiles = (n_images * kWhPix + kWhRows - 1) / kWhRows;
   WOFT_REQUIRE(tiles < (1LL << 31) && n_images < (1LL << 31), "woft_weight_head_conv1: too many images");
   const int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
-  weight_head_conv1_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  weight_head_conv1_kernel<false><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       window_nhwc, mean_response, weight, bias, out_nhwc, (int)n_images, (int)tiles);
+  return launch_status("weight_head_conv1_kernel");
+}
+
+extern "C" int woft_weight_head_conv1_stacked_f16(const float* window_nhwc, const float* mean_response, const float* weight,
+                                                  const float* bias, long long n_images, int patch, int levels,
+                                                  int channels_out, void* out_stacked_f16, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(window_nhwc && mean_response && weight && bias && out_stacked_f16,
+               "woft_weight_head_conv1_stacked_f16: null pointer");
+  WOFT_REQUIRE(patch == kWhP && levels == kWhL && channels_out == kWhCout,
+               "woft_weight_head_conv1_stacked_f16: built for 9x9 patches, 4 levels and 128 output channels");
+  WOFT_REQUIRE(n_images > 0 && n_images * (kWhPix + kWhP) + kWhRows < (1LL << 31),
+               "woft_weight_head_conv1_stacked_f16: bad image count");
+  const long long tiles = (n_images * kWhPix + kWhRows - 1) / kWhRows;
+  const int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
+  weight_head_conv1_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      window_nhwc, mean_response, weight, bias, out_stacked_f16, (int)n_images, (int)tiles);
   return launch_status("weight_head_conv1_kernel");
 }

@@ -162,6 +162,30 @@ def flow_conv7x7_relu(flow, weight, bias):
     return out
 
 
+def flow_conv7x7_relu_f16(flow, weight, bias):
+    """The same with an fp16 output tensor; woft_flow_conv7x7_relu_f16."""
+    flow = flow.contiguous()
+    B, _, H, W = flow.shape
+    out = torch.empty((B, weight.shape[0], H, W), device=flow.device, dtype=torch.float16,
+                      memory_format=torch.channels_last)
+    with torch.cuda.device(flow.device):
+        rc = _lib.load().woft_flow_conv7x7_relu_f16(_lib.ptr(flow), _lib.ptr(weight), _lib.ptr(bias), B, H, W, _lib.ptr(out),
+                                                    _lib.current_stream(flow.device))
+    _lib.check(rc, "woft_flow_conv7x7_relu_f16")
+    return out
+
+
+def cast_nhwc_f16(src, channels, dst, dst_off, dst2=None, dst2_off=0):
+    """The first `channels` channels of the channels-last fp32 tensor `src`, rounded to fp16, into channel slice
+    [dst_off, ...) of the channels-last fp16 tensor `dst` (and of `dst2`); woft_cast_nhwc_f16."""
+    B, _, H, W = src.shape
+    with torch.cuda.device(src.device):
+        rc = _lib.load().woft_cast_nhwc_f16(_lib.ptr(src), src.shape[1], channels, B * H * W, _lib.ptr(dst), dst.shape[1],
+                                            dst_off, _lib.ptr(dst2), dst2.shape[1] if dst2 is not None else 0, dst2_off,
+                                            _lib.current_stream(src.device))
+    _lib.check(rc, "woft_cast_nhwc_f16")
+
+
 def flow_out3x3(x_cl, weight, bias):
     """channels-last (B,C,H,W) -> conv3x3 to 2 channels, NCHW (B,2,H,W); woft_flow_out3x3."""
     x_cl = _cl(x_cl)
@@ -232,9 +256,11 @@ def convex_upsample_both(flow_low, weights_low, mask, sigmoid=False):
 class FastWeightedRAFT:
     """Callable with the signature of WeightedRAFT.forward; built from a WeightedRAFT that already sits on the GPU."""
 
-    def __init__(self, net, nhwc_update=True, tf32=True):
+    def __init__(self, net, nhwc_update=True, tf32=None):
         self.net = net
-        self.tf32 = tf32   # False: no hand-written TF32 convolution kernel is used, cuDNN obeys torch's allow_tf32
+        # may convolution operands be rounded to 10-bit mantissas (TF32 / fp16 with fp32 accumulation)?  None follows
+        # torch.backends.cudnn.allow_tf32; False keeps every convolution in fp32 on cuDNN (the reference's class)
+        self.tf32 = bool(torch.backends.cudnn.allow_tf32 if tf32 is None else tf32)
         self.with_weights = net.with_weights
         dev = next(net.parameters()).device
         if dev.type != "cuda":
@@ -294,7 +320,11 @@ class FastWeightedRAFT:
                 self.own_convs = (self.tf32 and os.environ.get("WOFT_OWN_CONVS", "1") == "1"
                                   and net.hidden_dim == net.context_dim == 128 and e.conv.weight.shape[0] == 126)
                 if self.own_convs:
-                    P = conv_tc.PackedConv
+                    # fp16 operands (the 10-bit mantissa of TF32 at half the bytes; every tensor that feeds a convolution
+                    # is bounded: ReLU / tanh / sigmoid outputs, correlation values, flow in pixels), fp32 accumulation;
+                    # the recurrent state h and the gate z stay fp32
+                    def P(w, b, pad):
+                        return conv_tc.PackedConv(w, b, pad, f16=True)
                     self.tc = {name: P(m.weight, m.bias, m.padding) for name, m in (
                         ("convc1", e.convc1), ("convc2", e.convc2), ("convf2", e.convf2), ("conv", e.conv),
                         ("fh1", ub.flow_head.conv1), ("m0", ub.mask[0]), ("m2", ub.mask[2]))}
@@ -310,8 +340,8 @@ class FastWeightedRAFT:
                                 and tuple(convs[3].weight.shape) == (1, 128, 1, 1)):
                             # layers 2 and 3 read and write fp16 activations (10-bit mantissa like TF32, half the
                             # 2.6 GB the three layers would otherwise move), fp32 accumulation
-                            self.tc["head2"] = P(convs[1].weight, convs[1].bias, 1, f16=True)
-                            self.tc["head3"] = P(convs[2].weight, convs[2].bias, 1, f16=True)
+                            self.tc["head2"] = P(convs[1].weight, convs[1].bias, 1)
+                            self.tc["head3"] = P(convs[2].weight, convs[2].bias, 1)
                             self.head_w1x1 = convs[3].weight.detach().reshape(-1).float().contiguous()
                             self.head_b1x1 = float(convs[3].bias.detach().item())
                             self.own_head = True
@@ -432,7 +462,12 @@ class FastWeightedRAFT:
               "pixels": B * H * W, "coords0": coords0.contiguous(), "coords1": coords1.contiguous().clone(),
               "flow": flow, "flow_cl": _cl(flow).clone()}   # flow_cl: logical (B,2,H,W), stored (B,H,W,2)
         if self.own_convs:
-            st["cor1"], st["cf"], st["fh"] = (_empty_cl(B, 256, H, W, ctx_out) for _ in range(3))
+            def half_cl(c):
+                return torch.empty((B, c, H, W), device=ctx_out.device, dtype=torch.float16, memory_format=torch.channels_last)
+            st["cor1"], st["cf"], st["fh"] = half_cl(256), half_cl(256), _empty_cl(B, 256, H, W, ctx_out)
+            # fp16 copies of the two GRU operand buffers [h | inp | motion | flow] and [r*h | inp | motion | flow]
+            st["buf1h"], st["buf2h"] = half_cl(3 * C), half_cl(3 * C)
+            cast_nhwc_f16(st["buf1"], 2 * C, st["buf1h"], 0, st["buf2h"], 0)
         with torch.cuda.device(ctx_out.device):
             rc = _lib.load().woft_context_split_nhwc(_lib.ptr(ctx_out), _lib.ptr(ctx_bias), B * H * W, C, _lib.ptr(st["h"]),
                                                      _lib.ptr(st["buf1"]), _lib.ptr(st["buf2"]), 3 * C,
@@ -471,8 +506,6 @@ class FastWeightedRAFT:
         w = self.ubw
         e = self.net.update_block.encoder
         flo = flow_conv7x7_relu(st["flow"], e.convf1.weight, e.convf1.bias)   # NCHW flow in, channels-last out
-        if self.own_convs:
-            return self._update_own(st, corr, flo, need_mask)
         cor = _conv_relu(corr, *w["convc1"])
         cor = _conv_relu(cor, *w["convc2"], padding=(1, 1))
         flo = _conv_relu(flo, *w["convf2"], padding=(1, 1))
@@ -496,32 +529,59 @@ class FastWeightedRAFT:
             mask = conv_bias_nhwc(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"], scale=0.25)
         return mask
 
-    def _update_own(self, st, corr, flo, need_mask):
+    def _update_own(self, st, corr):
         """The iteration on woft_conv_tc: every wide convolution is one launch that also applies its bias / ReLU / GRU gate
-        arithmetic and writes where the next layer reads (no concatenation, no separate element-wise kernels)."""
+        arithmetic and writes where the next layer reads (no concatenation, no separate element-wise kernels).  `corr` is
+        the fp16 channels-last lookup (flags 8 | 16)."""
         tc, C, ci = self.tc, st["C"], st["ci"]
-        buf1, buf2, cf = st["buf1"], st["buf2"], st["cf"]
+        buf1, buf2, cf, h, z = st["buf1h"], st["buf2h"], st["cf"], st["h"], st["z"]
+        e = self.net.update_block.encoder
+        flo = flow_conv7x7_relu_f16(st["flow"], e.convf1.weight, e.convf1.bias)
         conv_tc.run(tc["convc1"], corr, relu=True, out=st["cor1"])
         conv_tc.run(tc["convc2"], st["cor1"], relu=True, out=cf)                        # cf = [cor (192) | flo (64)]
         conv_tc.run(tc["convf2"], flo, relu=True, out=cf, out_off=tc["convc2"].cout)
         # x = [inp | motion (126) | flow (2)] behind h resp. r*h in both GRU buffers (update.py:96-97)
         conv_tc.run(tc["conv"], cf, relu=True, out=buf1, out_off=C + ci, out2=buf2, out2_off=C + ci)
-        concat_nhwc([st["flow_cl"]], buf1, C + ci + tc["conv"].cout, buf2, C + ci + tc["conv"].cout)
+        cast_nhwc_f16(st["flow_cl"], 2, buf1, C + ci + tc["conv"].cout, buf2, C + ci + tc["conv"].cout)
         for tag in ("1", "2"):
-            conv_tc.run(tc["zr" + tag], buf1, epilogue=_lib.CONV_GRU_ZR, h=buf1, z=st["z"], out=buf2)
-            conv_tc.run(tc["q" + tag], buf2, epilogue=_lib.CONV_GRU_Q, h=buf1, z=st["z"], out=buf1)
+            conv_tc.run(tc["zr" + tag], buf1, epilogue=_lib.CONV_GRU_ZR, h=h, z=z, out=buf2)
+            conv_tc.run(tc["q" + tag], buf2, epilogue=_lib.CONV_GRU_Q, h=h, z=z, out=h, out2=buf1)
         conv_tc.run(tc["fh1"], buf1, relu=True, out=st["fh"])                           # reads the h slice of buf1
         fh = self.net.update_block.flow_head
         flow_head_step(st["fh"], fh.conv2.weight, fh.conv2.bias, coords=st["coords1"], coords0=st["coords0"],
                        flow_nchw=st["flow"], flow_nhwc=st["flow_cl"])
-        mask = None
-        if need_mask:
-            B, _, H, W = buf1.shape
-            m = _empty_cl(B, tc["m0"].cout, H, W, buf1)
-            conv_tc.run(tc["m0"], buf1, relu=True, out=m)
-            mask = _empty_cl(B, tc["m2"].cout, H, W, buf1)
-            conv_tc.run(tc["m2"], m, relu=False, scale=0.25, out=mask)
+
+    def _mask_own(self, st):
+        """The upsampling-mask head (update.py:122-125, 135) on the final hidden state."""
+        tc, buf1 = self.tc, st["buf1h"]
+        B, _, H, W = buf1.shape
+        m = torch.empty((B, tc["m0"].cout, H, W), device=buf1.device, dtype=torch.float16, memory_format=torch.channels_last)
+        conv_tc.run(tc["m0"], buf1, relu=True, out=m)
+        mask = _empty_cl(B, tc["m2"].cout, H, W, st["h"])
+        conv_tc.run(tc["m2"], m, relu=False, scale=0.25, out=mask)
         return mask
+
+    def _weights_own(self, window, mean_response):
+        """The weight head on woft_weight_head_conv1_stacked_f16 + two woft_conv_tc launches: layer 1 writes the 14 400
+        9x9x128 images stacked along H with a zero row between them (fp16), layer 2 is a plain 3x3 convolution over that
+        stack, layer 3 ends in the 1x1 convolution and the patch mean (weighted_raft.py:318-339, 380-384)."""
+        B, ch, H1, W1 = window.shape
+        n, P = B * H1 * W1, 9
+        first = self.net.weight_head.net[0]
+        dev = window.device
+        x1 = torch.empty((1, n * (P + 1), P, 128), device=dev, dtype=torch.float16).permute(0, 3, 1, 2)
+        x2 = torch.empty((1, n * (P + 1), P, 128), device=dev, dtype=torch.float16).permute(0, 3, 1, 2)
+        mr = mean_response.contiguous()
+        with torch.cuda.device(dev):
+            rc = _lib.load().woft_weight_head_conv1_stacked_f16(_lib.ptr(window), _lib.ptr(mr), _lib.ptr(first.weight),
+                                                                _lib.ptr(first.bias), n, P, 4, 128, _lib.ptr(x1),
+                                                                _lib.current_stream(dev))
+        _lib.check(rc, "woft_weight_head_conv1_stacked_f16")
+        conv_tc.run(self.tc["head2"], x1, relu=True, out=x2, row_period=P + 1, row_valid=P, box=(P, 14))
+        logits = torch.empty((n,), device=dev, dtype=torch.float32)
+        conv_tc.run(self.tc["head3"], x2, epilogue=_lib.CONV_HEAD_MEAN, w1x1=self.head_w1x1, head_out=logits,
+                    head_bias=self.head_b1x1, row_period=P + 1, row_valid=P, box=(P, 14))
+        return logits.view(B, H1, W1).unsqueeze(1)
 
     # ---- weight head, channels-last -----------------------------------------------------------------------------
     def _weights(self, window, mean_response):
@@ -611,8 +671,13 @@ class FastWeightedRAFT:
             state = None
         for it in range(iters):
             last = it == iters - 1
-            if nhwc:
+            if nhwc and self.own_convs:
                 coords1 = state["coords1"]  # advanced in place by the flow head's last kernel
+                self._update_own(state, corr_fn(coords1, flags=lookup_flags | 16))
+                if last:
+                    up_mask = self._mask_own(state)
+            elif nhwc:
+                coords1 = state["coords1"]
                 corr = corr_fn(coords1, flags=lookup_flags)
                 up_mask = self._update_nhwc(state, corr, need_mask=last)
             else:
@@ -623,6 +688,9 @@ class FastWeightedRAFT:
         if not self.with_weights:
             return flow_low, convex_upsample_both(flow_low, None, up_mask)[0]
         window = corr_fn(coords1, flags=lookup_flags) if nhwc else corr_fn(coords1)
-        weights = self._weights(window, corr_fn.mean_response())
+        if nhwc and self.own_head and tuple(window.shape[1:2]) == (324,):
+            weights = self._weights_own(window, corr_fn.mean_response())
+        else:
+            weights = self._weights(window, corr_fn.mean_response())
         flow_up, weights_up = convex_upsample_both(flow_low, weights, up_mask)  # one kernel, softmax computed once
         return flow_low, flow_up, corr_fn.corr_pyramid[0], weights, weights_up

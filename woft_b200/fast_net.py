@@ -467,12 +467,13 @@ class FastWeightedRAFT:
             st["cor1"], st["cf"], st["fh"] = half_cl(256), half_cl(256), _empty_cl(B, 256, H, W, ctx_out)
             # fp16 copies of the two GRU operand buffers [h | inp | motion | flow] and [r*h | inp | motion | flow]
             st["buf1h"], st["buf2h"] = half_cl(3 * C), half_cl(3 * C)
-            cast_nhwc_f16(st["buf1"], 2 * C, st["buf1h"], 0, st["buf2h"], 0)
         with torch.cuda.device(ctx_out.device):
             rc = _lib.load().woft_context_split_nhwc(_lib.ptr(ctx_out), _lib.ptr(ctx_bias), B * H * W, C, _lib.ptr(st["h"]),
                                                      _lib.ptr(st["buf1"]), _lib.ptr(st["buf2"]), 3 * C,
                                                      _lib.current_stream(ctx_out.device))
         _lib.check(rc, "woft_context_split_nhwc")
+        if self.own_convs:
+            cast_nhwc_f16(st["buf1"], 2 * C, st["buf1h"], 0, st["buf2h"], 0)   # [h | inp] into both operand buffers
         return st
 
     def _gru_half_nhwc(self, st, tag):

@@ -386,6 +386,9 @@ typedef struct woft_conv_tc_args {
   float* head_out;
   float head_bias;
   int row_period, row_valid;
+  void* debug_trace; /* NULL, or device memory of 8 * 148 unsigned long long: per-CTA %globaltimer stamps (kernel entry,
+                        set-up done, first operands landed, last MMA issued, accumulator ready, epilogue done, exit) */
+  int debug_flags;   /* 0; experiments only */
 } woft_conv_tc_args;
 int woft_conv_tc(const woft_conv_tc_args* args, void* stream);
 int woft_conv_tc_check(void* stream);

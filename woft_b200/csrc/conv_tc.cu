@@ -16,9 +16,9 @@
 // matrix, repacked once on the host to [tap][Cout][Cin] (rounded to tf32 / fp16).  The accumulator (128 pixels x up to
 // 256 output channels, fp32) lives in TMEM across all taps and channel blocks: K = taps * Cin.
 //
-// Warp roles (192 threads, persistent CTAs over tiles), as in corr_tc.cu: warp 0 TMA producer, warp 1 MMA issuer (two
-// accumulators in TMEM, so tile i+1 multiplies while tile i drains), warps 2-5 epilogue (one output pixel per thread,
-// 32 channels per tcgen05.ld).  Epilogues:
+// Warp roles (320 threads, persistent CTAs over tiles), as in corr_tc.cu: warp 0 TMA producer, warp 1 MMA issuer (two
+// accumulators in TMEM, so tile i+1 multiplies while tile i drains), warps 2-9 epilogue (one output pixel per thread,
+// 32 channels per tcgen05.ld, the two warps of a TMEM lane quadrant taking alternate chunks).  Epilogues:
 //   BIAS_ACT  y = scale * act(acc + bias), fp32 or fp16, to one or two (strided) destinations -- writing straight into
 //             the concatenation buffers of the next layer (torch.cat at update.py:96-97, 129 disappears)
 //   GRU_ZR    z = sigmoid(acc[:, :C] + bz) -> z;  r*h = sigmoid(acc[:, C:] + br) * h -> the q convolution's input
@@ -37,7 +37,7 @@
 
 namespace woft {
 
-constexpr int CT_THREADS = 192, CT_EPI_THREADS = 128;
+constexpr int CT_THREADS = 320, CT_EPI_THREADS = 256;   // TMA warp, MMA warp, 8 epilogue warps
 constexpr int CT_A_STAGE = 128 * 128;       // 128 pixel rows x one 128-byte K row
 constexpr int CT_MAX_STAGES = 8;
 constexpr int CT_MAX_TAPS = 25;
@@ -72,7 +72,12 @@ struct ConvTcParams {
   float* head_out;
   float head_scale, head_bias;
   int row_period, row_valid;  // rows y with (y % row_period) >= row_valid are separators: stored as zeros, not averaged
+  unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA, or null
 };
+
+__device__ __forceinline__ void ct_stamp(const ConvTcParams& p, int slot) {
+  if (p.trace) p.trace[blockIdx.x * 8 + slot] = ptx::globaltimer_ns();
+}
 
 // status word of the conv kernels (a pipeline wait timed out); read back by woft_conv_tc_check
 __device__ int g_conv_abort = 0;
@@ -120,7 +125,10 @@ __device__ __forceinline__ CtTile ct_decode(const ConvTcParams& p, int t) {
   return c;
 }
 
-__device__ __forceinline__ float ct_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }
+// exp through ex2.approx and the division through rcp.approx (about 2 ulp each): a handful of instructions where expf,
+// tanhf and the IEEE division are dozens with a slow-path call -- the epilogue is issue-bound, not accuracy-bound
+__device__ __forceinline__ float ct_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float ct_tanh(float x) { return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x)); }
 
 // 32 consecutive channels of one pixel, fp32 or fp16 destination; `nv` < 32 only in the last channel block
 __device__ __forceinline__ void ct_store_row(void* base, long long stride, long long pix, int col, const float* v, int nv,
@@ -140,7 +148,9 @@ __device__ __forceinline__ void ct_store_row(void* base, long long stride, long 
         *reinterpret_cast<uint4*>(o + j) = u;
       }
     } else {
-      for (int j = 0; j < nv; ++j) o[j] = __float2half_rn(v[j]);
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < nv) o[j] = __float2half_rn(v[j]);
     }
   } else {
     float* o = reinterpret_cast<float*>(base) + pix * stride + col;
@@ -148,7 +158,9 @@ __device__ __forceinline__ void ct_store_row(void* base, long long stride, long 
 #pragma unroll
       for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
     } else {
-      for (int j = 0; j < nv; ++j) o[j] = v[j];
+#pragma unroll
+      for (int j = 0; j < 32; ++j)
+        if (j < nv) o[j] = v[j];
     }
   }
 }
@@ -168,12 +180,13 @@ __device__ __forceinline__ void ct_load_row(const float* base, long long stride,
 template <int EPI>
 __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ uint8_t ct_smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ct_smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1 KiB alignment by an offset into the array (a cast through an integer would turn every later access generic)
+  uint8_t* smem = ct_smem_raw + ((1024u - (ptx::smem_u32(ct_smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = sA + p.stages * CT_A_STAGE;
   float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
-  float* s_red = s_bias + CT_MAX_BIAS;                                   // 128 floats (HEAD_MEAN)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_red + 128);
+  float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_red + 256);
   uint64_t* full = bars;
   uint64_t* empty = bars + CT_MAX_STAGES;
   uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
@@ -185,6 +198,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   const int lane = threadIdx.x & 31;
 
   if (threadIdx.x == 0) {
+    ct_stamp(p, 0);
     for (int s = 0; s < p.stages; ++s) {
       ptx::mbar_init(full + s, 1);
       ptx::mbar_init(empty + s, 1);
@@ -210,6 +224,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
   const int k_steps = p.taps * p.k_chunks;
+  if (threadIdx.x == 0) ct_stamp(p, 1);
 
   if (warp == 0) {
     // ================================ TMA producer ================================
@@ -258,6 +273,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
             break;
           }
           ptx::tc_fence_after_sync();
+          if (ks == 0 && it == 0) ct_stamp(p, 2);
           const uint64_t da = ct_desc(ptx::smem_u32(sA + stage * CT_A_STAGE));
           const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
 #pragma unroll
@@ -275,13 +291,17 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           }
         }
         if (alive) ptx::mma_commit(tfull + buf);
+        if (it == 0) ct_stamp(p, 3);
       }
     }
   } else {
     // ================================ epilogue ================================
-    const int et = threadIdx.x - 64;  // 0..127
-    const bool leader = (et == 0);
-    const int m = (warp & 3) * 32 + lane;  // TMEM lane == pixel row of the tile
+    // Eight warps: two per TMEM lane quadrant (a warp reaches lanes 32 * (warp % 4) ...), the pair splitting the tile's
+    // 32-column chunks by parity.  One warp per scheduler cannot hide the latency of its own dependent instructions;
+    // two can, and each has half the work.
+    const bool leader = (threadIdx.x == 64);
+    const int half = (warp - 2) >> 2;                 // which chunks of the tile this warp takes
+    const int m = (warp & 3) * 32 + lane;             // TMEM lane == pixel row of the tile
     const uint32_t lane_base = uint32_t((warp & 3) * 32) << 16;
     const int xi = m % p.bw, yj = m / p.bw;
     const int chunks = p.bn >> 5;
@@ -294,26 +314,48 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       ptx::named_bar_sync(1, CT_EPI_THREADS);
       if (*epi_go == 0) break;
       ptx::tc_fence_after_sync();
+      if (leader && it == 0) ct_stamp(p, 4);
       const int x = tc.x0 + xi, y = tc.y0 + yj;
       const bool valid = yj < p.bh && x < p.W && y < p.H;
       const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
       const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
       float head_sum = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < chunks; ++c) {
-        float v[32];
+      for (int c = half; c < chunks; c += 2) {
+        const int col = tc.c0 + c * 32;  // output channel of v[0]
+        float v[32], bv[32];
+        // operands of this chunk that do not depend on the accumulator are requested before the TMEM read is waited for
+        float hv[32], zv[32];
+        if (EPI == CT_EPI_GRU_ZR) {
+          if (valid && col >= (p.bn >> 1)) ct_load_row(p.h, p.h_stride, pix, col - (p.bn >> 1), hv);
+        } else if (EPI == CT_EPI_GRU_Q) {
+          if (valid) {
+            ct_load_row(p.h, p.h_stride, pix, col, hv);
+            ct_load_row(p.z, p.z_stride, pix, col, zv);
+          }
+        } else if (EPI == CT_EPI_HEAD_MEAN) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 w4 = __ldg(reinterpret_cast<const float4*>(p.w1x1 + col) + j);
+            hv[4 * j] = w4.x; hv[4 * j + 1] = w4.y; hv[4 * j + 2] = w4.z; hv[4 * j + 3] = w4.w;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float4 b4 = reinterpret_cast<const float4*>(s_bias + col)[j];
+          bv[4 * j] = b4.x; bv[4 * j + 1] = b4.y; bv[4 * j + 2] = b4.z; bv[4 * j + 3] = b4.w;
+        }
         ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * 256 + c * 32), v);
-        if (c == chunks - 1) {  // accumulator fully read: hand it back to the MMA warp
+        if (c + 2 >= chunks) {  // this warp's last chunk: its share of the accumulator is read, hand it back
           ptx::tc_fence_before_sync();
           ptx::mbar_arrive(tempty + buf);
         }
-        const int col = tc.c0 + c * 32;  // output channel of v[0]
         if (EPI == CT_EPI_BIAS_ACT) {
           const int nv = min(32, p.cout - col);
           if (valid && nv > 0) {
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              float a = v[j] + s_bias[col + j];
+              float a = v[j] + bv[j];
               if (p.relu) a = fmaxf(a, 0.f);
               v[j] = separator ? 0.f : a * p.scale;
             }
@@ -325,41 +367,42 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           if (valid) {
             if (col < hid) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + s_bias[col + j]);
+              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]);
               ct_store_row(p.z, p.z_stride, pix, col, v, 32, false);
             } else {
-              float hv[32];
-              ct_load_row(p.h, p.h_stride, pix, col - hid, hv);
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + s_bias[col + j]) * hv[j];
+              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]) * hv[j];
               ct_store_row(p.out, p.out_stride, pix, col - hid, v, 32, p.out_f16 != 0);
             }
           }
         } else if (EPI == CT_EPI_GRU_Q) {
           if (valid) {
-            float hv[32], zv[32];
-            ct_load_row(p.h, p.h_stride, pix, col, hv);
-            ct_load_row(p.z, p.z_stride, pix, col, zv);
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = (1.f - zv[j]) * hv[j] + zv[j] * tanhf(v[j] + s_bias[col + j]);
+            for (int j = 0; j < 32; ++j) v[j] = (1.f - zv[j]) * hv[j] + zv[j] * ct_tanh(v[j] + bv[j]);
             ct_store_row(p.out, p.out_stride, pix, col, v, 32, false);
             if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, 32, p.out2_f16 != 0);
           }
         } else {  // CT_EPI_HEAD_MEAN
 #pragma unroll
-          for (int j = 0; j < 32; ++j) head_sum = fmaf(fmaxf(v[j] + s_bias[col + j], 0.f), __ldg(p.w1x1 + col + j), head_sum);
+          for (int j = 0; j < 32; ++j) head_sum = fmaf(fmaxf(v[j] + bv[j], 0.f), hv[j], head_sum);
         }
       }
+      if (chunks <= half) {  // a one-chunk tile leaves the second warp of each pair without work
+        ptx::tc_fence_before_sync();
+        ptx::mbar_arrive(tempty + buf);
+      }
       if (EPI == CT_EPI_HEAD_MEAN) {
-        // rows of the tile are (row_period) image rows apart per image: sum the pixels of each image in a fixed order
-        s_red[m] = (valid && !separator) ? head_sum : 0.f;
+        // the two warps of a lane quadrant hold the even / odd chunks of the same pixels; the pixels of each image are
+        // then summed in a fixed order
+        s_red[half * 128 + m] = (valid && !separator) ? head_sum : 0.f;
         ptx::named_bar_sync(1, CT_EPI_THREADS);
+        const int et = threadIdx.x - 64;
         const int img_first = tc.y0 / p.row_period;
         const int img = img_first + et;
         const int y_lo = max(img * p.row_period, tc.y0), y_hi = min(min(img * p.row_period + p.row_valid, tc.y0 + p.bh), p.H);
         if (et < 4 && y_lo < y_hi) {
           float s = 0.f;
-          for (int r = (y_lo - tc.y0) * p.bw; r < (y_hi - tc.y0) * p.bw; ++r) s += s_red[r];
+          for (int r = (y_lo - tc.y0) * p.bw; r < (y_hi - tc.y0) * p.bw; ++r) s += s_red[r] + s_red[128 + r];
           s *= p.head_scale;
           if (y_lo == img * p.row_period) s += p.head_bias;  // the tile holding the image's first row brings the 1x1 bias
           // at most two tiles hold pixels of one image and the destination starts at zero: 0 + a + b == 0 + b + a
@@ -367,6 +410,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         }
         ptx::named_bar_sync(1, CT_EPI_THREADS);
       }
+      if (leader && it == 0) ct_stamp(p, 5);
     }
   }
 
@@ -376,6 +420,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     ptx::tc_fence_after_sync();
     ptx::tmem_dealloc(tmem_base, 512);
   }
+  if (threadIdx.x == 0) ct_stamp(p, 6);
 }
 
 __global__ void fill_kernel(float* dst, float value, long long n) {
@@ -505,6 +550,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.head_out = a->head_out;
   p.row_period = a->row_period;
   p.row_valid = a->row_valid;
+  p.trace = static_cast<unsigned long long*>(a->debug_trace);
 
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {
@@ -558,7 +604,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight operand");
   }
 
-  const int fixed = 1024 + (CT_MAX_BIAS + 128) * 4 + 256;
+  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 256;
   int stages = (CT_SMEM_LIMIT - fixed) / (CT_A_STAGE + p.b_bytes);
   if (stages > CT_MAX_STAGES) stages = CT_MAX_STAGES;
   WOFT_REQUIRE(stages >= 2, "woft_conv_tc: tile does not fit shared memory");

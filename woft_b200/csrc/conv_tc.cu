@@ -42,7 +42,7 @@ constexpr int CT_A_STAGE = 128 * 128;       // 128 pixel rows x one 128-byte K r
 constexpr int CT_MAX_STAGES = 8;
 constexpr int CT_MAX_TAPS = 25;
 constexpr int CT_SMEM_LIMIT = 232448;
-constexpr int CT_MAX_BIAS = 1024;
+constexpr int CT_MAX_BIAS = 640;   // padded Cout of one launch (the mask head's 576 is the largest)
 
 enum { CT_EPI_BIAS_ACT = 0, CT_EPI_GRU_ZR = 1, CT_EPI_GRU_Q = 2, CT_EPI_HEAD_MEAN = 3 };
 
@@ -73,6 +73,7 @@ struct ConvTcParams {
   float head_scale, head_bias;
   int row_period, row_valid;  // rows y with (y % row_period) >= row_valid are separators: stored as zeros, not averaged
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA, or null
+  int coalesce;               // every epilogue operand is 16-byte aligned with 16-byte multiple strides: staged accesses
 };
 
 __device__ __forceinline__ void ct_stamp(const ConvTcParams& p, int slot) {
@@ -177,6 +178,109 @@ __device__ __forceinline__ void ct_load_row(const float* base, long long stride,
   }
 }
 
+// ---- coalescing through shared memory -------------------------------------------------------------------------------
+// In the epilogue a thread owns one pixel (a TMEM lane), so a plain vector store touches 32 different 128-byte lines per
+// warp instruction and the L1 spends 32 tag cycles on it: at 1280x720 that alone was 5-8 us per convolution.  Instead a
+// warp passes blocks of 32 rows x 64 bytes through a private 2 KB staging buffer (16-byte pieces XOR-swizzled so that
+// both the row-per-thread side and the transposed side are bank-conflict free) and touches global memory with 4 lanes
+// per row: 8 lines per instruction, every byte of a 64-byte segment used.  rp[i] is the pixel index of row
+// (lane >> 2) + 8 i of the warp's 32 rows, or -1 outside the image.
+__device__ __forceinline__ uint8_t* ct_stage_own(uint8_t* stg, int lane, int j) {
+  return stg + lane * 64 + ((j ^ ((lane >> 1) & 3)) << 4);
+}
+__device__ __forceinline__ uint8_t* ct_stage_row(uint8_t* stg, int r, int q) {
+  return stg + r * 64 + ((q ^ ((r >> 1) & 3)) << 4);
+}
+
+__device__ __forceinline__ void ct_store_tile(void* base, long long stride, int col, const float* v, int nv, bool f16,
+                                              uint8_t* stg, int lane, const int* rp) {
+  const int q = lane & 3;
+  if (f16) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      __half2 a = __floats2half2_rn(v[8 * j], v[8 * j + 1]), b = __floats2half2_rn(v[8 * j + 2], v[8 * j + 3]);
+      __half2 c = __floats2half2_rn(v[8 * j + 4], v[8 * j + 5]), d = __floats2half2_rn(v[8 * j + 6], v[8 * j + 7]);
+      uint4 u;
+      u.x = *reinterpret_cast<uint32_t*>(&a);
+      u.y = *reinterpret_cast<uint32_t*>(&b);
+      u.z = *reinterpret_cast<uint32_t*>(&c);
+      u.w = *reinterpret_cast<uint32_t*>(&d);
+      *reinterpret_cast<uint4*>(ct_stage_own(stg, lane, j)) = u;
+    }
+    __syncwarp();
+    const int left = nv - q * 8;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = (lane >> 2) + 8 * i;
+      if (rp[i] >= 0 && left > 0) {
+        const uint4 t = *reinterpret_cast<const uint4*>(ct_stage_row(stg, r, q));
+        __half* o = reinterpret_cast<__half*>(base) + (long long)rp[i] * stride + col + q * 8;
+        if (left >= 8) {
+          *reinterpret_cast<uint4*>(o) = t;
+        } else {
+          const __half* hsrc = reinterpret_cast<const __half*>(&t);
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            if (e < left) o[e] = hsrc[e];
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+#pragma unroll
+    for (int hb = 0; hb < 2; ++hb) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        *reinterpret_cast<float4*>(ct_stage_own(stg, lane, j)) =
+            make_float4(v[16 * hb + 4 * j], v[16 * hb + 4 * j + 1], v[16 * hb + 4 * j + 2], v[16 * hb + 4 * j + 3]);
+      __syncwarp();
+      const int left = nv - 16 * hb - q * 4;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = (lane >> 2) + 8 * i;
+        if (rp[i] >= 0 && left > 0) {
+          const float4 t = *reinterpret_cast<const float4*>(ct_stage_row(stg, r, q));
+          float* o = reinterpret_cast<float*>(base) + (long long)rp[i] * stride + col + 16 * hb + q * 4;
+          if (left >= 4) {
+            *reinterpret_cast<float4*>(o) = t;
+          } else {
+            o[0] = t.x;
+            if (left > 1) o[1] = t.y;
+            if (left > 2) o[2] = t.z;
+          }
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// 32 fp32 channels [col, col + 32) of the warp's 32 pixels, each thread ending up with its own pixel's values
+__device__ __forceinline__ void ct_load_tile(const float* base, long long stride, int col, float* v, uint8_t* stg, int lane,
+                                             const int* rp) {
+  const int q = lane & 3;
+#pragma unroll
+  for (int hb = 0; hb < 2; ++hb) {
+    float4 t[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      t[i] = rp[i] >= 0 ? __ldg(reinterpret_cast<const float4*>(base + (long long)rp[i] * stride + col + 16 * hb + q * 4))
+                        : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(ct_stage_row(stg, (lane >> 2) + 8 * i, q)) = t[i];
+    __syncwarp();
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float4 u = *reinterpret_cast<const float4*>(ct_stage_own(stg, lane, j));
+      v[16 * hb + 4 * j] = u.x;
+      v[16 * hb + 4 * j + 1] = u.y;
+      v[16 * hb + 4 * j + 2] = u.z;
+      v[16 * hb + 4 * j + 3] = u.w;
+    }
+    __syncwarp();
+  }
+}
+
 template <int EPI>
 __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ uint8_t ct_smem_raw[];
@@ -186,7 +290,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   uint8_t* sB = sA + p.stages * CT_A_STAGE;
   float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
   float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_red + 256);
+  uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_red + 256);            // 8 warps x 2 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stage + 8 * 2048);
   uint64_t* full = bars;
   uint64_t* empty = bars + CT_MAX_STAGES;
   uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
@@ -319,6 +424,11 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       const bool valid = yj < p.bh && x < p.W && y < p.H;
       const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
       const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
+      uint8_t* stg = s_stage + (warp - 2) * 2048;
+      int rp[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) rp[i] = __shfl_sync(0xffffffffu, valid ? int(pix) : -1, (lane >> 2) + 8 * i);
+      const bool co = p.coalesce != 0;
       float head_sum = 0.f;
 #pragma unroll 1
       for (int c = half; c < chunks; c += 2) {
@@ -327,9 +437,17 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         // operands of this chunk that do not depend on the accumulator are requested before the TMEM read is waited for
         float hv[32], zv[32];
         if (EPI == CT_EPI_GRU_ZR) {
-          if (valid && col >= (p.bn >> 1)) ct_load_row(p.h, p.h_stride, pix, col - (p.bn >> 1), hv);
+          if (col >= (p.bn >> 1)) {
+            if (co)
+              ct_load_tile(p.h, p.h_stride, col - (p.bn >> 1), hv, stg, lane, rp);
+            else if (valid)
+              ct_load_row(p.h, p.h_stride, pix, col - (p.bn >> 1), hv);
+          }
         } else if (EPI == CT_EPI_GRU_Q) {
-          if (valid) {
+          if (co) {
+            ct_load_tile(p.h, p.h_stride, col, hv, stg, lane, rp);
+            ct_load_tile(p.z, p.z_stride, col, zv, stg, lane, rp);
+          } else if (valid) {
             ct_load_row(p.h, p.h_stride, pix, col, hv);
             ct_load_row(p.z, p.z_stride, pix, col, zv);
           }
@@ -352,33 +470,43 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         }
         if (EPI == CT_EPI_BIAS_ACT) {
           const int nv = min(32, p.cout - col);
-          if (valid && nv > 0) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              float a = v[j] + bv[j];
-              if (p.relu) a = fmaxf(a, 0.f);
-              v[j] = separator ? 0.f : a * p.scale;
-            }
+          for (int j = 0; j < 32; ++j) {
+            float a = v[j] + bv[j];
+            if (p.relu) a = fmaxf(a, 0.f);
+            v[j] = separator ? 0.f : a * p.scale;
+          }
+          if (co && nv > 0) {   // warp-uniform
+            ct_store_tile(p.out, p.out_stride, col, v, nv, p.out_f16 != 0, stg, lane, rp);
+            if (p.out2) ct_store_tile(p.out2, p.out2_stride, col, v, nv, p.out2_f16 != 0, stg, lane, rp);
+          } else if (valid && nv > 0) {
             ct_store_row(p.out, p.out_stride, pix, col, v, nv, p.out_f16 != 0);
             if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, nv, p.out2_f16 != 0);
           }
         } else if (EPI == CT_EPI_GRU_ZR) {
           const int hid = p.bn >> 1;
-          if (valid) {
-            if (col < hid) {
+          if (col < hid) {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]);
+            for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]);
+            if (co)
+              ct_store_tile(p.z, p.z_stride, col, v, 32, false, stg, lane, rp);
+            else if (valid)
               ct_store_row(p.z, p.z_stride, pix, col, v, 32, false);
-            } else {
+          } else {
 #pragma unroll
-              for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]) * hv[j];
+            for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]) * hv[j];
+            if (co)
+              ct_store_tile(p.out, p.out_stride, col - hid, v, 32, p.out_f16 != 0, stg, lane, rp);
+            else if (valid)
               ct_store_row(p.out, p.out_stride, pix, col - hid, v, 32, p.out_f16 != 0);
-            }
           }
         } else if (EPI == CT_EPI_GRU_Q) {
-          if (valid) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = (1.f - zv[j]) * hv[j] + zv[j] * ct_tanh(v[j] + bv[j]);
+          for (int j = 0; j < 32; ++j) v[j] = (1.f - zv[j]) * hv[j] + zv[j] * ct_tanh(v[j] + bv[j]);
+          if (co) {
+            ct_store_tile(p.out, p.out_stride, col, v, 32, false, stg, lane, rp);
+            if (p.out2) ct_store_tile(p.out2, p.out2_stride, col, v, 32, p.out2_f16 != 0, stg, lane, rp);
+          } else if (valid) {
             ct_store_row(p.out, p.out_stride, pix, col, v, 32, false);
             if (p.out2) ct_store_row(p.out2, p.out2_stride, pix, col, v, 32, p.out2_f16 != 0);
           }
@@ -582,6 +710,14 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     p.head_bias = a->head_bias;
   }
   if (a->bias == nullptr) p.bias = nullptr;
+  {
+    auto ok = [](const void* ptr, long long stride, int esz) {
+      return ptr == nullptr || ((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (stride * esz) % 16 == 0);
+    };
+    p.coalesce = ok(a->out, a->out_stride, oesz) && ok(a->out2, a->out2_stride, a->out2_f16 ? 2 : 4) &&
+                 ok(a->h, a->h_stride, 4) && ok(a->z, a->z_stride, 4);
+    WOFT_REQUIRE((long long)a->batch * a->height * a->width < (1LL << 31), "woft_conv_tc: too many pixels");
+  }
 
   const CUtensorMapDataType dt = a->in_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
   {
@@ -604,7 +740,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight operand");
   }
 
-  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 256;
+  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 256;
   int stages = (CT_SMEM_LIMIT - fixed) / (CT_A_STAGE + p.b_bytes);
   if (stages > CT_MAX_STAGES) stages = CT_MAX_STAGES;
   WOFT_REQUIRE(stages >= 2, "woft_conv_tc: tile does not fit shared memory");

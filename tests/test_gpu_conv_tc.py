@@ -137,8 +137,8 @@ def test_fp16_operands_and_output():
     assert (out.double() - exact).abs().max().item() / scale <= 1.5e-3   # fp16 rounding of the stored result
 
 
-@pytest.mark.parametrize("f16", [False, True])
-def test_weight_head_layers_on_stacked_images(f16):
+@pytest.mark.parametrize("f16,halo", [(False, False), (True, False), (True, True)])
+def test_weight_head_layers_on_stacked_images(f16, halo):
     """Layers 2-3 of the weight head + 1x1 + patch mean (weighted_raft.py:318-339, 380-384) on 9x9 images stacked along H
     with one zero row between them: conv+ReLU writes zeros into the separator rows, the last layer reduces each image."""
     from woft_b200 import _lib, conv_tc
@@ -162,10 +162,12 @@ def test_weight_head_layers_on_stacked_images(f16):
     x = stacked.view(1, n * (P + 1), P, C).permute(0, 3, 1, 2)
     mid = torch.full((1, n * (P + 1), P, C), 5.0, device=DEV, dtype=dt).permute(0, 3, 1, 2)
     p2, p3 = conv_tc.PackedConv(w2, b2, 1, f16=f16), conv_tc.PackedConv(w3, b3, 1, f16=f16)
-    conv_tc.run(p2, x, relu=True, out=mid, row_period=P + 1, row_valid=P, box=(9, 14))
+    # halo: one image per tile, filters resident in shared memory, all nine taps read one 11 x 12 activation box
+    kw = dict(box=(9, 10), halo=True) if halo else dict(box=(9, 14))
+    conv_tc.run(p2, x, relu=True, out=mid, row_period=P + 1, row_valid=P, **kw)
     logits = torch.full((n,), 9.0, device=DEV)
     conv_tc.run(p3, mid, epilogue=_lib.CONV_HEAD_MEAN, w1x1=w1, head_out=logits, head_bias=b1, row_period=P + 1,
-                row_valid=P, box=(9, 14))
+                row_valid=P, **kw)
     conv_tc.check(DEV)
     got2 = mid.permute(0, 2, 3, 1).reshape(n, P + 1, P, C)
     assert (got2[:, P] == 0).all(), "separator rows must be zero"
@@ -176,7 +178,7 @@ def test_weight_head_layers_on_stacked_images(f16):
     # deterministic: a second run gives the same bits
     logits2 = torch.empty_like(logits)
     conv_tc.run(p3, mid, epilogue=_lib.CONV_HEAD_MEAN, w1x1=w1, head_out=logits2, head_bias=b1, row_period=P + 1,
-                row_valid=P, box=(9, 14))
+                row_valid=P, **kw)
     assert torch.equal(logits, logits2)
 
 

@@ -38,7 +38,7 @@
 namespace woft {
 
 constexpr int CT_THREADS = 320, CT_EPI_THREADS = 256;   // TMA warp, MMA warp, 8 epilogue warps
-constexpr int CT_A_STAGE = 128 * 128;       // 128 pixel rows x one 128-byte K row
+constexpr int CT_A_STAGE = 128 * 128;       // 128 pixel rows x one 128-byte K row (a_stage; more rows in halo mode)
 constexpr int CT_MAX_STAGES = 8;
 constexpr int CT_MAX_TAPS = 25;
 constexpr int CT_SMEM_LIMIT = 232448;
@@ -54,6 +54,11 @@ struct ConvTcParams {
   int x_tiles, y_tiles, n_tiles, total_tiles;
   int taps, k_chunks, k_elems, f16;
   int bn, stages, a_bytes, b_bytes;
+  // halo mode (weights resident in shared memory): ONE activation box of pw x hh pixels per channel block serves every
+  // filter tap -- the tap's operand starts tap_row[tap] rows into the box; output pixel (i, j) of the tile is GEMM row
+  // j * pw + i, rows with i >= bw are junk.  pw == bw and halo == 0 otherwise.
+  int halo, pw, hh, a_stage;
+  short tap_row[CT_MAX_TAPS];
   signed char dx[CT_MAX_TAPS], dy[CT_MAX_TAPS];
   int cout, relu;
   float scale;
@@ -74,6 +79,7 @@ struct ConvTcParams {
   int row_period, row_valid;  // rows y with (y % row_period) >= row_valid are separators: stored as zeros, not averaged
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA, or null
   int coalesce;               // every epilogue operand is 16-byte aligned with 16-byte multiple strides: staged accesses
+  int dbg;                    // experiments (woft_conv_tc_args.debug_flags)
 };
 
 __device__ __forceinline__ void ct_stamp(const ConvTcParams& p, int slot) {
@@ -287,8 +293,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   // 1 KiB alignment by an offset into the array (a cast through an integer would turn every later access generic)
   uint8_t* smem = ct_smem_raw + ((1024u - (ptx::smem_u32(ct_smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
-  uint8_t* sB = sA + p.stages * CT_A_STAGE;
-  float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
+  uint8_t* sB = sA + p.stages * p.a_stage;
+  // streamed weights: one b_bytes block per stage; halo mode: all taps * k_chunks blocks of this CTA's Cout tile
+  float* s_bias = reinterpret_cast<float*>(sB + (p.halo ? p.taps * p.k_chunks : p.stages) * p.b_bytes);   // CT_MAX_BIAS floats
   float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
   uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_red + 256);            // 8 warps x 2 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_stage + 8 * 2048);
@@ -296,7 +303,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   uint64_t* empty = bars + CT_MAX_STAGES;
   uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
   uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint64_t* b_full = tempty + 2;   // resident weights landed (halo mode)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(b_full + 1);
   volatile int* epi_go = reinterpret_cast<volatile int*>(tmem_ptr + 1);
 
   const int warp = threadIdx.x >> 5;
@@ -312,6 +320,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       ptx::mbar_init(tfull + i, 1);
       ptx::mbar_init(tempty + i, CT_EPI_THREADS);
     }
+    ptx::mbar_init(b_full, 1);
     ptx::fence_mbar_init();
     ptx::prefetch_tmap(&p.tmA);
     ptx::prefetch_tmap(&p.tmB);
@@ -337,7 +346,30 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       int stage = 0;
       uint32_t phase = 0;
       bool alive = true;
-      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x) {
+      if (p.halo) {
+        // every tile of this CTA has the same Cout tile (grid and tile order are arranged so): its weights load once
+        const int c0 = (int(blockIdx.x) % p.n_tiles) * p.bn;
+        ptx::mbar_arrive_expect_tx(b_full, uint32_t(p.taps * p.k_chunks * p.b_bytes));
+        for (int tap = 0; tap < p.taps; ++tap)
+          for (int kc = 0; kc < p.k_chunks; ++kc)
+            ptx::tma_load_3d(sB + (tap * p.k_chunks + kc) * p.b_bytes, &p.tmB, b_full, kc * p.k_elems, c0, tap);
+        for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x) {
+          const CtTile tc = ct_decode(p, t);
+          for (int kc = 0; kc < p.k_chunks; ++kc) {
+            if (!ct_wait(empty + stage, phase ^ 1u)) {
+              alive = false;
+              break;
+            }
+            ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.a_bytes));
+            ptx::tma_load_4d(sA + stage * p.a_stage, &p.tmA, full + stage, kc * p.k_elems, tc.x0 + p.dx[0], tc.y0 + p.dy[0], tc.n);
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+        }
+      }
+      for (int t = blockIdx.x; t < p.total_tiles && alive && !p.halo; t += gridDim.x) {
         const CtTile tc = ct_decode(p, t);
         for (int tap = 0; tap < p.taps && alive; ++tap) {
           const int xs = tc.x0 + p.dx[tap], ys = tc.y0 + p.dy[tap];
@@ -347,7 +379,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               break;
             }
             ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.a_bytes + p.b_bytes));
-            ptx::tma_load_4d(sA + stage * CT_A_STAGE, &p.tmA, full + stage, kc * p.k_elems, xs, ys, tc.n);
+            ptx::tma_load_4d(sA + stage * p.a_stage, &p.tmA, full + stage, kc * p.k_elems, xs, ys, tc.n);
             ptx::tma_load_3d(sB + stage * p.b_bytes, &p.tmB, full + stage, kc * p.k_elems, tc.c0, tap);
             if (++stage == p.stages) {
               stage = 0;
@@ -372,6 +404,40 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
         ptx::tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
+        if (p.halo) {
+          if (it == 0 && !ct_wait(b_full, 0)) break;
+          for (int kc = 0; kc < p.k_chunks && alive; ++kc) {
+            if (!ct_wait(full + stage, phase)) {
+              alive = false;
+              break;
+            }
+            ptx::tc_fence_after_sync();
+            if (kc == 0 && it == 0) ct_stamp(p, 2);
+            const uint32_t a_base = ptx::smem_u32(sA + stage * p.a_stage);
+            for (int tap = 0; tap < p.taps; ++tap) {
+              // the tap's operand is the same box read from tap_row[tap] rows further in: the 128-byte swizzle is a
+              // function of the shared-memory address, so a descriptor may start on any row of the tile
+              const uint64_t da = ct_desc(a_base + uint32_t(p.tap_row[tap]) * 128u);
+              const uint64_t db = ct_desc(ptx::smem_u32(sB + (tap * p.k_chunks + kc) * p.b_bytes));
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t acc = (kc > 0 || tap > 0 || k > 0) ? 1u : 0u;
+                if (p.f16)
+                  ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+                else
+                  ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+              }
+            }
+            ptx::mma_commit(empty + stage);
+            if (++stage == p.stages) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+          if (alive) ptx::mma_commit(tfull + buf);
+          if (it == 0) ct_stamp(p, 3);
+          continue;
+        }
         for (int ks = 0; ks < k_steps; ++ks) {
           if (!ct_wait(full + stage, phase)) {
             alive = false;
@@ -379,7 +445,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           }
           ptx::tc_fence_after_sync();
           if (ks == 0 && it == 0) ct_stamp(p, 2);
-          const uint64_t da = ct_desc(ptx::smem_u32(sA + stage * CT_A_STAGE));
+          const uint64_t da = ct_desc(ptx::smem_u32(sA + stage * p.a_stage));
           const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
 #pragma unroll
           for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row
@@ -408,7 +474,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     const int half = (warp - 2) >> 2;                 // which chunks of the tile this warp takes
     const int m = (warp & 3) * 32 + lane;             // TMEM lane == pixel row of the tile
     const uint32_t lane_base = uint32_t((warp & 3) * 32) << 16;
-    const int xi = m % p.bw, yj = m / p.bw;
+    const int xi = m % p.pw, yj = m / p.pw;   // halo mode: GEMM rows run over the box pitch, columns >= bw are junk
     const int chunks = p.bn >> 5;
     int it = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
@@ -421,7 +487,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       ptx::tc_fence_after_sync();
       if (leader && it == 0) ct_stamp(p, 4);
       const int x = tc.x0 + xi, y = tc.y0 + yj;
-      const bool valid = yj < p.bh && x < p.W && y < p.H;
+      const bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H;
       const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
       const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
       uint8_t* stg = s_stage + (warp - 2) * 2048;
@@ -530,9 +596,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         const int y_lo = max(img * p.row_period, tc.y0), y_hi = min(min(img * p.row_period + p.row_valid, tc.y0 + p.bh), p.H);
         if (et < 4 && y_lo < y_hi) {
           float s = 0.f;
-          for (int r = (y_lo - tc.y0) * p.bw; r < (y_hi - tc.y0) * p.bw; ++r) s += s_red[r] + s_red[128 + r];
+          for (int r = (y_lo - tc.y0) * p.pw; r < (y_hi - tc.y0) * p.pw; ++r) s += s_red[r] + s_red[128 + r];
           s *= p.head_scale;
-          if (y_lo == img * p.row_period) s += p.head_bias;  // the tile holding the image's first row brings the 1x1 bias
+          if (y_lo == img * p.row_period && tc.c0 == 0) s += p.head_bias;  // one contributor brings the 1x1 bias
           // at most two tiles hold pixels of one image and the destination starts at zero: 0 + a + b == 0 + b + a
           atomicAdd(p.head_out + img, s);
         }
@@ -620,9 +686,34 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
         break;
       }
   }
+  const int taps = a->kh * a->kw;
+  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 256;
+  int a_stage = CT_A_STAGE;
+  if (a->halo) {
+    // one activation box per channel block serves all taps, the filters stay in shared memory: the Cout tile is the
+    // largest whose taps * k_chunks weight blocks fit beside two activation stages
+    WOFT_REQUIRE(a->box_w > 0 && a->box_h > 0, "woft_conv_tc: halo mode takes the output tile in box_w, box_h");
+    const int pw = a->box_w + a->kw - 1, hh = a->box_h + a->kh - 1;
+    WOFT_REQUIRE(pw * a->box_h <= 128 && pw <= 256 && hh <= 256, "woft_conv_tc: halo tile %d x %d does not fit 128 GEMM rows",
+                 a->box_w, a->box_h);
+    const int rows = 128 + (a->kh - 1) * pw + (a->kw - 1) > pw * hh ? 128 + (a->kh - 1) * pw + (a->kw - 1) : pw * hh;
+    a_stage = (rows * 128 + 1023) / 1024 * 1024;
+    const int budget = CT_SMEM_LIMIT - fixed - 2 * a_stage;
+    bn = 0;
+    for (int d = 1; d <= 8; d *= 2) {
+      const int c = a->cout_pad / d;
+      if (a->cout_pad % d == 0 && c % 32 == 0 && taps * (cin_pad / k_elems) * c * 128 <= budget) {
+        bn = c;
+        break;
+      }
+    }
+    WOFT_REQUIRE(bn > 0, "woft_conv_tc: the filters do not fit shared memory (halo mode)");
+  }
   WOFT_REQUIRE(bn >= 16 && bn % 32 == 0, "woft_conv_tc: Cout tile %d (need a multiple of 32 dividing the padded Cout)", bn);
   p.bn = bn;
   p.n_tiles = a->cout_pad / bn;
+  p.halo = a->halo ? 1 : 0;
+  p.a_stage = a_stage;
   // pixel box: bw x bh = 128 (or the caller's own, e.g. 9 x 14 rows of stacked 9-wide images)
   int bw = a->box_w, bh = a->box_h;
   if (bw <= 0 || bh <= 0) {
@@ -637,10 +728,12 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       }
     }
   }
-  WOFT_REQUIRE(bw >= 1 && bh >= 1 && bw <= 256 && bh <= 256 && bw * bh <= 128 && bw * bh >= 96,
+  WOFT_REQUIRE(bw >= 1 && bh >= 1 && bw <= 256 && bh <= 256 && bw * bh <= 128 && (a->halo || bw * bh >= 96),
                "woft_conv_tc: pixel box %d x %d must cover 96..128 pixels", bw, bh);
   p.bw = bw;
   p.bh = bh;
+  p.pw = a->halo ? bw + a->kw - 1 : bw;
+  p.hh = a->halo ? bh + a->kh - 1 : bh;
   p.W = a->width;
   p.H = a->height;
   p.NB = a->batch;
@@ -649,16 +742,17 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   const long long total = (long long)p.x_tiles * p.y_tiles * a->batch * p.n_tiles;
   WOFT_REQUIRE(total < (1LL << 31), "woft_conv_tc: too many tiles");
   p.total_tiles = (int)total;
-  p.taps = a->kh * a->kw;
+  p.taps = taps;
   for (int ky = 0; ky < a->kh; ++ky)
     for (int kx = 0; kx < a->kw; ++kx) {
       p.dx[ky * a->kw + kx] = (signed char)(kx - a->pad_w);
       p.dy[ky * a->kw + kx] = (signed char)(ky - a->pad_h);
+      p.tap_row[ky * a->kw + kx] = (short)(ky * p.pw + kx);
     }
   p.k_elems = k_elems;
   p.k_chunks = cin_pad / k_elems;
   p.f16 = a->in_f16 ? 1 : 0;
-  p.a_bytes = bw * bh * 128;
+  p.a_bytes = p.pw * p.hh * 128;
   p.b_bytes = bn * 128;
   p.cout = a->cout;
   p.relu = a->relu;
@@ -679,6 +773,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.row_period = a->row_period;
   p.row_valid = a->row_valid;
   p.trace = static_cast<unsigned long long*>(a->debug_trace);
+  p.dbg = a->debug_flags;
 
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {
@@ -701,8 +796,12 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
                  a->h_stride % 4 == 0 && a->z_stride % 4 == 0 && a->out_stride % 4 == 0,
                  "woft_conv_tc: GRU operands must be 16-byte aligned");
   } else {
-    WOFT_REQUIRE(p.n_tiles == 1 && a->w1x1 && a->head_out && a->row_period > 0 && a->row_valid > 0 &&
-                 a->row_valid <= a->row_period, "woft_conv_tc: patch-mean epilogue needs w1x1, head_out and the row period");
+    WOFT_REQUIRE(a->w1x1 && a->head_out && a->row_period > 0 && a->row_valid > 0 && a->row_valid <= a->row_period,
+                 "woft_conv_tc: patch-mean epilogue needs w1x1, head_out and the row period");
+    // every image may receive at most two partial sums (their order then does not matter): either one Cout tile and
+    // tiles that straddle images, or image-aligned tiles and two Cout tiles
+    WOFT_REQUIRE(p.n_tiles == 1 || (p.n_tiles == 2 && bh == a->row_period),
+                 "woft_conv_tc: patch-mean epilogue with split filters needs one image per tile (box_h == row_period)");
     WOFT_REQUIRE(a->batch == 1 && a->height % a->row_period == 0, "woft_conv_tc: patch-mean epilogue takes the images "
                  "stacked along H (batch 1, H = images * row_period)");
     WOFT_REQUIRE(ceil_div(bh, a->row_period) + 1 <= 4, "woft_conv_tc: pixel box spans too many images");
@@ -724,7 +823,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     cuuint64_t dims[4] = {(cuuint64_t)a->cin, (cuuint64_t)a->width, (cuuint64_t)a->height, (cuuint64_t)a->batch};
     cuuint64_t strides[3] = {(cuuint64_t)a->in_stride * esz, (cuuint64_t)a->in_stride * esz * a->width,
                              (cuuint64_t)a->in_stride * esz * a->width * a->height};
-    cuuint32_t box[4] = {(cuuint32_t)k_elems, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+    cuuint32_t box[4] = {(cuuint32_t)k_elems, (cuuint32_t)p.pw, (cuuint32_t)p.hh, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     if (enc(&p.tmA, dt, 4, const_cast<void*>(a->in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -740,18 +839,20 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight operand");
   }
 
-  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 256;
-  int stages = (CT_SMEM_LIMIT - fixed) / (CT_A_STAGE + p.b_bytes);
+  const int b_resident = p.halo ? taps * p.k_chunks * p.b_bytes : 0;
+  int stages = p.halo ? (CT_SMEM_LIMIT - fixed - b_resident) / a_stage : (CT_SMEM_LIMIT - fixed) / (a_stage + p.b_bytes);
   if (stages > CT_MAX_STAGES) stages = CT_MAX_STAGES;
   WOFT_REQUIRE(stages >= 2, "woft_conv_tc: tile does not fit shared memory");
   p.stages = stages;
   // always more than half of the SM's shared memory: one CTA per SM, which owns all 512 TMEM columns
-  int smem = stages * (CT_A_STAGE + p.b_bytes) + fixed;
+  int smem = (p.halo ? stages * a_stage + b_resident : stages * (a_stage + p.b_bytes)) + fixed;
   if (smem < 120 * 1024) smem = 120 * 1024;
 
   int sms = 0;
   WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  if (p.halo) grid = grid / p.n_tiles * p.n_tiles;   // tile t has Cout tile t % n_tiles: a CTA keeps one set of filters
+  WOFT_REQUIRE(grid >= 1, "woft_conv_tc: empty grid");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (a->epilogue) {
     case CT_EPI_BIAS_ACT:

@@ -578,11 +578,13 @@ class FastWeightedRAFT:
                                                                 _lib.ptr(first.bias), n, P, 4, 128, _lib.ptr(x1),
                                                                 _lib.current_stream(dev))
         _lib.check(rc, "woft_weight_head_conv1_stacked_f16")
-        # one image per tile, filters resident in shared memory, every tap reading the same 11 x 12 activation box
-        conv_tc.run(self.tc["head2"], x1, relu=True, out=x2, row_period=P + 1, row_valid=P, box=(P, P + 1), halo=True)
+        # tiles of 14 stacked rows (126 of the 128 GEMM rows).  The halo mode of woft_conv_tc (filters resident in shared
+        # memory as two 64-channel halves, one 11 x 12 activation box per image) was measured slower here, 0.81 ms against
+        # 0.50 ms per layer: with 64-column MMAs the tensor core waits on shared-memory operand reads
+        conv_tc.run(self.tc["head2"], x1, relu=True, out=x2, row_period=P + 1, row_valid=P, box=(P, 14))
         logits = torch.empty((n,), device=dev, dtype=torch.float32)
         conv_tc.run(self.tc["head3"], x2, epilogue=_lib.CONV_HEAD_MEAN, w1x1=self.head_w1x1, head_out=logits,
-                    head_bias=self.head_b1x1, row_period=P + 1, row_valid=P, box=(P, P + 1), halo=True)
+                    head_bias=self.head_b1x1, row_period=P + 1, row_valid=P, box=(P, 14))
         return logits.view(B, H1, W1).unsqueeze(1)
 
     # ---- weight head, channels-last -----------------------------------------------------------------------------

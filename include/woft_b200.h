@@ -389,9 +389,10 @@ typedef struct woft_conv_tc_args {
   void* debug_trace; /* NULL, or device memory of 8 * 148 unsigned long long: per-CTA %globaltimer stamps (kernel entry,
                         set-up done, first operands landed, last MMA issued, accumulator ready, epilogue done, exit) */
   int debug_flags;   /* 0; experiments only */
-  int halo;          /* 1: keep the filters resident in shared memory and fetch ONE activation box per channel block and
-                        tile, which every filter tap reads at its own row offset (for many small images: the weight
-                        head).  box_w x box_h is then the tile of OUTPUT pixels, (box_w + kw - 1) * box_h <= 128 */
+  int halo;          /* 1: fetch ONE activation box per tile and channel block -- the output tile plus its filter halo --
+                        which every filter tap reads at its own row offset, instead of one shifted box per tap (kh * kw
+                        times less activation traffic; the filters stream as before).  box_w x box_h is then the tile of
+                        OUTPUT pixels, with (box_w + kw - 1) * box_h <= 128 */
 } woft_conv_tc_args;
 int woft_conv_tc(const woft_conv_tc_args* args, void* stream);
 int woft_conv_tc_check(void* stream);

@@ -137,7 +137,7 @@ def test_fp16_operands_and_output():
     assert (out.double() - exact).abs().max().item() / scale <= 1.5e-3   # fp16 rounding of the stored result
 
 
-@pytest.mark.parametrize("f16,halo", [(False, False), (True, False), (True, True)])
+@pytest.mark.parametrize("f16,halo", [(False, False), (True, False), (True, True), (False, True)])
 def test_weight_head_layers_on_stacked_images(f16, halo):
     """Layers 2-3 of the weight head + 1x1 + patch mean (weighted_raft.py:318-339, 380-384) on 9x9 images stacked along H
     with one zero row between them: conv+ReLU writes zeros into the separator rows, the last layer reduces each image."""
@@ -162,8 +162,8 @@ def test_weight_head_layers_on_stacked_images(f16, halo):
     x = stacked.view(1, n * (P + 1), P, C).permute(0, 3, 1, 2)
     mid = torch.full((1, n * (P + 1), P, C), 5.0, device=DEV, dtype=dt).permute(0, 3, 1, 2)
     p2, p3 = conv_tc.PackedConv(w2, b2, 1, f16=f16), conv_tc.PackedConv(w3, b3, 1, f16=f16)
-    # halo: one image per tile, filters resident in shared memory, all nine taps read one 11 x 12 activation box
-    kw = dict(box=(9, 10), halo=True) if halo else dict(box=(9, 14))
+    # halo: all nine taps read one 11 x 13 activation box (11 output rows of 9 pixels per tile) at their own row offsets
+    kw = dict(box=(9, 11), halo=True) if halo else dict(box=(9, 14))
     conv_tc.run(p2, x, relu=True, out=mid, row_period=P + 1, row_valid=P, **kw)
     logits = torch.full((n,), 9.0, device=DEV)
     conv_tc.run(p3, mid, epilogue=_lib.CONV_HEAD_MEAN, w1x1=w1, head_out=logits, head_bias=b1, row_period=P + 1,

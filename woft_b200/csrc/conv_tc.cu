@@ -54,10 +54,10 @@ struct ConvTcParams {
   int x_tiles, y_tiles, n_tiles, total_tiles;
   int taps, k_chunks, k_elems, f16;
   int bn, stages, a_bytes, b_bytes;
-  // halo mode (weights resident in shared memory): ONE activation box of pw x hh pixels per channel block serves every
-  // filter tap -- the tap's operand starts tap_row[tap] rows into the box; output pixel (i, j) of the tile is GEMM row
-  // j * pw + i, rows with i >= bw are junk.  pw == bw and halo == 0 otherwise.
-  int halo, pw, hh, a_stage;
+  // halo mode: ONE activation box of pw x hh pixels per channel block serves every filter tap -- the tap's operand
+  // starts tap_row[tap] rows into the box -- while the filters stream through their own ring; output pixel (i, j) of the
+  // tile is GEMM row j * pw + i, rows with i >= bw are junk.  pw == bw, halo == 0 and one ring for both otherwise.
+  int halo, pw, hh, a_stage, a_stages;
   short tap_row[CT_MAX_TAPS];
   signed char dx[CT_MAX_TAPS], dy[CT_MAX_TAPS];
   int cout, relu;
@@ -293,9 +293,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   // 1 KiB alignment by an offset into the array (a cast through an integer would turn every later access generic)
   uint8_t* smem = ct_smem_raw + ((1024u - (ptx::smem_u32(ct_smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
-  uint8_t* sB = sA + p.stages * p.a_stage;
-  // streamed weights: one b_bytes block per stage; halo mode: all taps * k_chunks blocks of this CTA's Cout tile
-  float* s_bias = reinterpret_cast<float*>(sB + (p.halo ? p.taps * p.k_chunks : p.stages) * p.b_bytes);   // CT_MAX_BIAS floats
+  uint8_t* sB = sA + p.a_stages * p.a_stage;   // a_stages == stages unless the activations have their own ring (halo)
+  float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
   float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
   uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_red + 256);            // 8 warps x 2 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_stage + 8 * 2048);
@@ -303,8 +302,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   uint64_t* empty = bars + CT_MAX_STAGES;
   uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
   uint64_t* tempty = tfull + 2;
-  uint64_t* b_full = tempty + 2;   // resident weights landed (halo mode)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(b_full + 1);
+  uint64_t* a_full = tempty + 2;   // [4] activation ring of the halo mode
+  uint64_t* a_empty = a_full + 4;  // [4]
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(a_empty + 4);
   volatile int* epi_go = reinterpret_cast<volatile int*>(tmem_ptr + 1);
 
   const int warp = threadIdx.x >> 5;
@@ -320,7 +320,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       ptx::mbar_init(tfull + i, 1);
       ptx::mbar_init(tempty + i, CT_EPI_THREADS);
     }
-    ptx::mbar_init(b_full, 1);
+    for (int i = 0; i < 4; ++i) {
+      ptx::mbar_init(a_full + i, 1);
+      ptx::mbar_init(a_empty + i, 1);
+    }
     ptx::fence_mbar_init();
     ptx::prefetch_tmap(&p.tmA);
     ptx::prefetch_tmap(&p.tmB);
@@ -347,24 +350,34 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       uint32_t phase = 0;
       bool alive = true;
       if (p.halo) {
-        // every tile of this CTA has the same Cout tile (grid and tile order are arranged so): its weights load once
-        const int c0 = (int(blockIdx.x) % p.n_tiles) * p.bn;
-        ptx::mbar_arrive_expect_tx(b_full, uint32_t(p.taps * p.k_chunks * p.b_bytes));
-        for (int tap = 0; tap < p.taps; ++tap)
-          for (int kc = 0; kc < p.k_chunks; ++kc)
-            ptx::tma_load_3d(sB + (tap * p.k_chunks + kc) * p.b_bytes, &p.tmB, b_full, kc * p.k_elems, c0, tap);
+        // two rings, filled in the order the MMA warp drains them: the activation box of a channel block, then the
+        // filters of every tap for that block
+        int a_st = 0;
+        uint32_t a_ph = 0;
         for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x) {
           const CtTile tc = ct_decode(p, t);
-          for (int kc = 0; kc < p.k_chunks; ++kc) {
-            if (!ct_wait(empty + stage, phase ^ 1u)) {
+          for (int kc = 0; kc < p.k_chunks && alive; ++kc) {
+            if (!ct_wait(a_empty + a_st, a_ph ^ 1u)) {
               alive = false;
               break;
             }
-            ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.a_bytes));
-            ptx::tma_load_4d(sA + stage * p.a_stage, &p.tmA, full + stage, kc * p.k_elems, tc.x0 + p.dx[0], tc.y0 + p.dy[0], tc.n);
-            if (++stage == p.stages) {
-              stage = 0;
-              phase ^= 1u;
+            ptx::mbar_arrive_expect_tx(a_full + a_st, uint32_t(p.a_bytes));
+            ptx::tma_load_4d(sA + a_st * p.a_stage, &p.tmA, a_full + a_st, kc * p.k_elems, tc.x0 + p.dx[0], tc.y0 + p.dy[0], tc.n);
+            if (++a_st == p.a_stages) {
+              a_st = 0;
+              a_ph ^= 1u;
+            }
+            for (int tap = 0; tap < p.taps; ++tap) {
+              if (!ct_wait(empty + stage, phase ^ 1u)) {
+                alive = false;
+                break;
+              }
+              ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.b_bytes));
+              ptx::tma_load_3d(sB + stage * p.b_bytes, &p.tmB, full + stage, kc * p.k_elems, tc.c0, tap);
+              if (++stage == p.stages) {
+                stage = 0;
+                phase ^= 1u;
+              }
             }
           }
         }
@@ -394,8 +407,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     if (lane == 0) {
       const uint32_t fmt = p.f16 ? 0u : 2u;  // F16 = 0, TF32 = 2
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(p.bn >> 3) << 17) | (uint32_t(128 >> 4) << 24);
-      int stage = 0;
-      uint32_t phase = 0;
+      int stage = 0, a_st = 0;
+      uint32_t phase = 0, a_ph = 0;
       bool alive = true;
       int it = 0;
       for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x, ++it) {
@@ -405,20 +418,23 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         ptx::tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
         if (p.halo) {
-          if (it == 0 && !ct_wait(b_full, 0)) break;
           for (int kc = 0; kc < p.k_chunks && alive; ++kc) {
-            if (!ct_wait(full + stage, phase)) {
+            if (!ct_wait(a_full + a_st, a_ph)) {
               alive = false;
               break;
             }
-            ptx::tc_fence_after_sync();
-            if (kc == 0 && it == 0) ct_stamp(p, 2);
-            const uint32_t a_base = ptx::smem_u32(sA + stage * p.a_stage);
+            const uint32_t a_base = ptx::smem_u32(sA + a_st * p.a_stage);
             for (int tap = 0; tap < p.taps; ++tap) {
+              if (!ct_wait(full + stage, phase)) {
+                alive = false;
+                break;
+              }
+              ptx::tc_fence_after_sync();
+              if (kc == 0 && tap == 0 && it == 0) ct_stamp(p, 2);
               // the tap's operand is the same box read from tap_row[tap] rows further in: the 128-byte swizzle is a
               // function of the shared-memory address, so a descriptor may start on any row of the tile
               const uint64_t da = ct_desc(a_base + uint32_t(p.tap_row[tap]) * 128u);
-              const uint64_t db = ct_desc(ptx::smem_u32(sB + (tap * p.k_chunks + kc) * p.b_bytes));
+              const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 const uint32_t acc = (kc > 0 || tap > 0 || k > 0) ? 1u : 0u;
@@ -427,11 +443,16 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
                 else
                   ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
               }
+              ptx::mma_commit(empty + stage);
+              if (++stage == p.stages) {
+                stage = 0;
+                phase ^= 1u;
+              }
             }
-            ptx::mma_commit(empty + stage);
-            if (++stage == p.stages) {
-              stage = 0;
-              phase ^= 1u;
+            if (alive) ptx::mma_commit(a_empty + a_st);   // every MMA reading this activation box has been issued
+            if (++a_st == p.a_stages) {
+              a_st = 0;
+              a_ph ^= 1u;
             }
           }
           if (alive) ptx::mma_commit(tfull + buf);
@@ -690,24 +711,13 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 256;
   int a_stage = CT_A_STAGE;
   if (a->halo) {
-    // one activation box per channel block serves all taps, the filters stay in shared memory: the Cout tile is the
-    // largest whose taps * k_chunks weight blocks fit beside two activation stages
+    // one activation box per channel block serves all taps: it must hold the 128 GEMM rows behind the last tap's offset
     WOFT_REQUIRE(a->box_w > 0 && a->box_h > 0, "woft_conv_tc: halo mode takes the output tile in box_w, box_h");
     const int pw = a->box_w + a->kw - 1, hh = a->box_h + a->kh - 1;
     WOFT_REQUIRE(pw * a->box_h <= 128 && pw <= 256 && hh <= 256, "woft_conv_tc: halo tile %d x %d does not fit 128 GEMM rows",
                  a->box_w, a->box_h);
     const int rows = 128 + (a->kh - 1) * pw + (a->kw - 1) > pw * hh ? 128 + (a->kh - 1) * pw + (a->kw - 1) : pw * hh;
     a_stage = (rows * 128 + 1023) / 1024 * 1024;
-    const int budget = CT_SMEM_LIMIT - fixed - 2 * a_stage;
-    bn = 0;
-    for (int d = 1; d <= 8; d *= 2) {
-      const int c = a->cout_pad / d;
-      if (a->cout_pad % d == 0 && c % 32 == 0 && taps * (cin_pad / k_elems) * c * 128 <= budget) {
-        bn = c;
-        break;
-      }
-    }
-    WOFT_REQUIRE(bn > 0, "woft_conv_tc: the filters do not fit shared memory (halo mode)");
   }
   WOFT_REQUIRE(bn >= 16 && bn % 32 == 0, "woft_conv_tc: Cout tile %d (need a multiple of 32 dividing the padded Cout)", bn);
   p.bn = bn;
@@ -801,7 +811,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     // every image may receive at most two partial sums (their order then does not matter): either one Cout tile and
     // tiles that straddle images, or image-aligned tiles and two Cout tiles
     WOFT_REQUIRE(p.n_tiles == 1 || (p.n_tiles == 2 && bh == a->row_period),
-                 "woft_conv_tc: patch-mean epilogue with split filters needs one image per tile (box_h == row_period)");
+                 "woft_conv_tc: patch-mean epilogue with two filter tiles needs one image per tile (box_h == row_period)");
     WOFT_REQUIRE(a->batch == 1 && a->height % a->row_period == 0, "woft_conv_tc: patch-mean epilogue takes the images "
                  "stacked along H (batch 1, H = images * row_period)");
     WOFT_REQUIRE(ceil_div(bh, a->row_period) + 1 <= 4, "woft_conv_tc: pixel box spans too many images");
@@ -839,19 +849,20 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight operand");
   }
 
-  const int b_resident = p.halo ? taps * p.k_chunks * p.b_bytes : 0;
-  int stages = p.halo ? (CT_SMEM_LIMIT - fixed - b_resident) / a_stage : (CT_SMEM_LIMIT - fixed) / (a_stage + p.b_bytes);
+  // halo mode: 3 activation stages (one box feeds `taps` MMA groups) and as many filter stages as fit beside them
+  const int a_stages_halo = 3;
+  int stages = p.halo ? (CT_SMEM_LIMIT - fixed - a_stages_halo * a_stage) / p.b_bytes : (CT_SMEM_LIMIT - fixed) / (a_stage + p.b_bytes);
   if (stages > CT_MAX_STAGES) stages = CT_MAX_STAGES;
   WOFT_REQUIRE(stages >= 2, "woft_conv_tc: tile does not fit shared memory");
   p.stages = stages;
+  p.a_stages = p.halo ? a_stages_halo : stages;
   // always more than half of the SM's shared memory: one CTA per SM, which owns all 512 TMEM columns
-  int smem = (p.halo ? stages * a_stage + b_resident : stages * (a_stage + p.b_bytes)) + fixed;
+  int smem = p.a_stages * a_stage + stages * p.b_bytes + fixed;
   if (smem < 120 * 1024) smem = 120 * 1024;
 
   int sms = 0;
   WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   int grid = p.total_tiles < sms ? p.total_tiles : sms;
-  if (p.halo) grid = grid / p.n_tiles * p.n_tiles;   // tile t has Cout tile t % n_tiles: a CTA keeps one set of filters
   WOFT_REQUIRE(grid >= 1, "woft_conv_tc: empty grid");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (a->epilogue) {

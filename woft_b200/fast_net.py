@@ -345,6 +345,7 @@ class FastWeightedRAFT:
                             self.head_w1x1 = convs[3].weight.detach().reshape(-1).float().contiguous()
                             self.head_b1x1 = float(convs[3].bias.detach().item())
                             self.own_head = True
+                            self.head_halo = os.environ.get("WOFT_HEAD_HALO", "1") == "1"
                 for tag in ("1", "2"):
                     gt = self.gru[tag]
                     gt["w_zr"], gt["w_q"] = _cl(gt["w_zr"]), _cl(gt["w_q"])
@@ -578,13 +579,13 @@ class FastWeightedRAFT:
                                                                 _lib.ptr(first.bias), n, P, 4, 128, _lib.ptr(x1),
                                                                 _lib.current_stream(dev))
         _lib.check(rc, "woft_weight_head_conv1_stacked_f16")
-        # tiles of 14 stacked rows (126 of the 128 GEMM rows).  The halo mode of woft_conv_tc (filters resident in shared
-        # memory as two 64-channel halves, one 11 x 12 activation box per image) was measured slower here, 0.81 ms against
-        # 0.50 ms per layer: with 64-column MMAs the tensor core waits on shared-memory operand reads
-        conv_tc.run(self.tc["head2"], x1, relu=True, out=x2, row_period=P + 1, row_valid=P, box=(P, 14))
+        # halo mode: tiles of 11 stacked rows of 9 pixels; one 11 x 13 activation box per tile and channel block serves all
+        # nine taps (each reads it from its own row offset), so the layer fetches a ninth of the activation bytes
+        tile = dict(box=(P, 11), halo=True) if self.head_halo else dict(box=(P, 14))
+        conv_tc.run(self.tc["head2"], x1, relu=True, out=x2, row_period=P + 1, row_valid=P, **tile)
         logits = torch.empty((n,), device=dev, dtype=torch.float32)
         conv_tc.run(self.tc["head3"], x2, epilogue=_lib.CONV_HEAD_MEAN, w1x1=self.head_w1x1, head_out=logits,
-                    head_bias=self.head_b1x1, row_period=P + 1, row_valid=P, box=(P, 14))
+                    head_bias=self.head_b1x1, row_period=P + 1, row_valid=P, **tile)
         return logits.view(B, H1, W1).unsqueeze(1)
 
     # ---- weight head, channels-last -----------------------------------------------------------------------------

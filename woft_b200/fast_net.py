@@ -345,7 +345,7 @@ class FastWeightedRAFT:
                             self.head_w1x1 = convs[3].weight.detach().reshape(-1).float().contiguous()
                             self.head_b1x1 = float(convs[3].bias.detach().item())
                             self.own_head = True
-                            self.head_halo = os.environ.get("WOFT_HEAD_HALO", "1") == "1"
+                            self.head_halo = os.environ.get("WOFT_HEAD_HALO", "0") == "1"
                 for tag in ("1", "2"):
                     gt = self.gru[tag]
                     gt["w_zr"], gt["w_q"] = _cl(gt["w_zr"]), _cl(gt["w_q"])
@@ -579,8 +579,10 @@ class FastWeightedRAFT:
                                                                 _lib.ptr(first.bias), n, P, 4, 128, _lib.ptr(x1),
                                                                 _lib.current_stream(dev))
         _lib.check(rc, "woft_weight_head_conv1_stacked_f16")
-        # halo mode: tiles of 11 stacked rows of 9 pixels; one 11 x 13 activation box per tile and channel block serves all
-        # nine taps (each reads it from its own row offset), so the layer fetches a ninth of the activation bytes
+        # default: tiles of 14 stacked rows (126 of the 128 GEMM rows), one shifted box per tap.  The halo mode (WOFT_HEAD_HALO=1:
+        # tiles of 11 rows, one 11 x 13 activation box per tile and channel block read by all nine taps at their own row
+        # offsets) fetches a ninth of the activation bytes yet measured slower, 0.64 ms against 0.50 ms per layer: MMAs whose
+        # operand starts off an 8-row boundary of the swizzled tile run about three times longer
         tile = dict(box=(P, 11), halo=True) if self.head_halo else dict(box=(P, 14))
         conv_tc.run(self.tc["head2"], x1, relu=True, out=x2, row_period=P + 1, row_valid=P, **tile)
         logits = torch.empty((n,), device=dev, dtype=torch.float32)

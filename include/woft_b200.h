@@ -393,6 +393,8 @@ typedef struct woft_conv_tc_args {
                         which every filter tap reads at its own row offset, instead of one shifted box per tap (kh * kw
                         times less activation traffic; the filters stream as before).  box_w x box_h is then the tile of
                         OUTPUT pixels, with (box_w + kw - 1) * box_h <= 128 */
+  int pair;          /* 1: clusters of two CTAs share each filter tile (tcgen05 cta_group::2, M = 256): every CTA fetches its
+                        own activation box and half of the filter rows; ignored in halo mode */
 } woft_conv_tc_args;
 int woft_conv_tc(const woft_conv_tc_args* args, void* stream);
 int woft_conv_tc_check(void* stream);

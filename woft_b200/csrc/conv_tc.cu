@@ -58,6 +58,9 @@ struct ConvTcParams {
   // starts tap_row[tap] rows into the box -- while the filters stream through their own ring; output pixel (i, j) of the
   // tile is GEMM row j * pw + i, rows with i >= bw are junk.  pw == bw, halo == 0 and one ring for both otherwise.
   int halo, pw, hh, a_stage, a_stages;
+  // pair mode (cta_group::2): a cluster of two CTAs takes two pixel tiles that share the filters; each CTA fetches its own
+  // activation box and HALF of the filter rows, the leader's MMA warp multiplies both tiles against both halves
+  int pair, pix_tiles, pair_tiles;
   short tap_row[CT_MAX_TAPS];
   signed char dx[CT_MAX_TAPS], dy[CT_MAX_TAPS];
   int cout, relu;
@@ -130,6 +133,32 @@ __device__ __forceinline__ CtTile ct_decode(const ConvTcParams& p, int t) {
   c.y0 = yt * p.bh;
   c.c0 = nt * p.bn;
   return c;
+}
+
+// the it-th tile of this CTA (false when there is none).  Pair mode: the cluster walks pair-tiles; rank r of the pair takes
+// pixel tile 2 * pp + r, a tile past the end is a dummy outside the batch (its loads are zero-filled, nothing is stored)
+__device__ __forceinline__ bool ct_tile_at(const ConvTcParams& p, int it, uint32_t rank, CtTile& c) {
+  if (!p.pair) {
+    const int t = blockIdx.x + it * gridDim.x;
+    if (t >= p.total_tiles) return false;
+    c = ct_decode(p, t);
+    return true;
+  }
+  const int pt = int(blockIdx.x >> 1) + it * int(gridDim.x >> 1);
+  if (pt >= p.pair_tiles) return false;
+  const int nt = pt % p.n_tiles, pix = 2 * (pt / p.n_tiles) + int(rank);
+  c.c0 = nt * p.bn;
+  if (pix >= p.pix_tiles) {
+    c.n = p.NB;
+    c.x0 = 0;
+    c.y0 = 0;
+  } else {
+    const int xt = pix % p.x_tiles, r = pix / p.x_tiles;
+    c.x0 = xt * p.bw;
+    c.y0 = (r % p.y_tiles) * p.bh;
+    c.n = r / p.y_tiles;
+  }
+  return true;
 }
 
 // exp through ex2.approx and the division through rcp.approx (about 2 ulp each): a handful of instructions where expf,
@@ -287,7 +316,8 @@ __device__ __forceinline__ void ct_load_tile(const float* base, long long stride
   }
 }
 
-template <int EPI>
+// PAIR instantiations contain cluster / cta_group::2 instructions and can only be launched as clusters of two
+template <int EPI, bool PAIR>
 __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ uint8_t ct_smem_raw[];
   // 1 KiB alignment by an offset into the array (a cast through an integer would turn every later access generic)
@@ -313,12 +343,12 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   if (threadIdx.x == 0) {
     ct_stamp(p, 0);
     for (int s = 0; s < p.stages; ++s) {
-      ptx::mbar_init(full + s, 1);
+      ptx::mbar_init(full + s, PAIR ? 2 : 1);   // pair: the leader's barrier counts both producers
       ptx::mbar_init(empty + s, 1);
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(tfull + i, 1);
-      ptx::mbar_init(tempty + i, CT_EPI_THREADS);
+      ptx::mbar_init(tempty + i, PAIR ? 2 * CT_EPI_THREADS : CT_EPI_THREADS);   // pair: both CTAs' epilogues
     }
     for (int i = 0; i < 4; ++i) {
       ptx::mbar_init(a_full + i, 1);
@@ -328,7 +358,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     ptx::prefetch_tmap(&p.tmA);
     ptx::prefetch_tmap(&p.tmB);
   }
-  if (warp == 1) ptx::tmem_alloc(tmem_ptr, 512);
+  const uint32_t rank = PAIR ? ptx::cluster_ctarank() : 0u;
+  if (warp == 1) {
+    if (PAIR)
+      ptx::tmem_alloc_2sm(tmem_ptr, 512);
+    else
+      ptx::tmem_alloc(tmem_ptr, 512);
+  }
   {
     const int nb = p.n_tiles * p.bn;
     for (int i = threadIdx.x; i < nb && i < CT_MAX_BIAS; i += CT_THREADS) {
@@ -337,7 +373,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     }
   }
   ptx::tc_fence_before_sync();
-  __syncthreads();
+  if (PAIR)
+    ptx::cluster_sync();   // the peer's barriers must be initialised before anything is signalled on them
+  else
+    __syncthreads();
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
   const int k_steps = p.taps * p.k_chunks;
@@ -354,8 +393,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         // filters of every tap for that block
         int a_st = 0;
         uint32_t a_ph = 0;
-        for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x) {
-          const CtTile tc = ct_decode(p, t);
+        CtTile tc;
+        for (int it = 0; alive && ct_tile_at(p, it, rank, tc); ++it) {
           for (int kc = 0; kc < p.k_chunks && alive; ++kc) {
             if (!ct_wait(a_empty + a_st, a_ph ^ 1u)) {
               alive = false;
@@ -382,8 +421,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           }
         }
       }
-      for (int t = blockIdx.x; t < p.total_tiles && alive && !p.halo; t += gridDim.x) {
-        const CtTile tc = ct_decode(p, t);
+      CtTile tc;
+      for (int it = 0; alive && !p.halo && ct_tile_at(p, it, rank, tc); ++it) {
         for (int tap = 0; tap < p.taps && alive; ++tap) {
           const int xs = tc.x0 + p.dx[tap], ys = tc.y0 + p.dy[tap];
           for (int kc = 0; kc < p.k_chunks; ++kc) {
@@ -391,9 +430,20 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               alive = false;
               break;
             }
-            ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.a_bytes + p.b_bytes));
-            ptx::tma_load_4d(sA + stage * p.a_stage, &p.tmA, full + stage, kc * p.k_elems, xs, ys, tc.n);
-            ptx::tma_load_3d(sB + stage * p.b_bytes, &p.tmB, full + stage, kc * p.k_elems, tc.c0, tap);
+            if (PAIR) {
+              // both CTAs' bytes are counted on the LEADER's barrier: the leader announces the sum, the peer only arrives
+              const uint32_t lead_full = ptx::mapa(full + stage, 0);
+              if (rank == 0)
+                ptx::mbar_arrive_expect_tx(full + stage, 2u * uint32_t(p.a_bytes + p.b_bytes));
+              else
+                ptx::mbar_arrive_cluster(lead_full);
+              ptx::tma_load_4d_2sm(sA + stage * p.a_stage, &p.tmA, lead_full, kc * p.k_elems, xs, ys, tc.n);
+              ptx::tma_load_3d_2sm(sB + stage * p.b_bytes, &p.tmB, lead_full, kc * p.k_elems, tc.c0 + int(rank) * (p.bn >> 1), tap);
+            } else {
+              ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.a_bytes + p.b_bytes));
+              ptx::tma_load_4d(sA + stage * p.a_stage, &p.tmA, full + stage, kc * p.k_elems, xs, ys, tc.n);
+              ptx::tma_load_3d(sB + stage * p.b_bytes, &p.tmB, full + stage, kc * p.k_elems, tc.c0, tap);
+            }
             if (++stage == p.stages) {
               stage = 0;
               phase ^= 1u;
@@ -404,14 +454,16 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (lane == 0) {
+    if (lane == 0 && rank == 0) {   // pair mode: the leader CTA issues for both SMs
       const uint32_t fmt = p.f16 ? 0u : 2u;  // F16 = 0, TF32 = 2
-      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(p.bn >> 3) << 17) | (uint32_t(128 >> 4) << 24);
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(p.bn >> 3) << 17) |
+                             (uint32_t((PAIR ? 256 : 128) >> 4) << 24);
       int stage = 0, a_st = 0;
       uint32_t phase = 0, a_ph = 0;
       bool alive = true;
       int it = 0;
-      for (int t = blockIdx.x; t < p.total_tiles && alive; t += gridDim.x, ++it) {
+      CtTile tc_unused;
+      for (; alive && ct_tile_at(p, it, rank, tc_unused); ++it) {
         const int buf = it & 1;
         const uint32_t use = uint32_t(it >> 1);
         if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
@@ -471,18 +523,32 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
           for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row
             const uint32_t acc = (ks > 0 || k > 0) ? 1u : 0u;
-            if (p.f16)
+            if (PAIR) {
+              if (p.f16)
+                ptx::mma_f16_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+              else
+                ptx::mma_tf32_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+            } else if (p.f16) {
               ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-            else
+            } else {
               ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+            }
           }
-          ptx::mma_commit(empty + stage);
+          if (PAIR)
+            ptx::mma_commit_2sm(empty + stage, 3);   // frees the stage in both CTAs
+          else
+            ptx::mma_commit(empty + stage);
           if (++stage == p.stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        if (alive) ptx::mma_commit(tfull + buf);
+        if (alive) {
+          if (PAIR)
+            ptx::mma_commit_2sm(tfull + buf, 3);
+          else
+            ptx::mma_commit(tfull + buf);
+        }
         if (it == 0) ct_stamp(p, 3);
       }
     }
@@ -498,8 +564,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     const int xi = m % p.pw, yj = m / p.pw;   // halo mode: GEMM rows run over the box pitch, columns >= bw are junk
     const int chunks = p.bn >> 5;
     int it = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-      const CtTile tc = ct_decode(p, t);
+    CtTile tc;
+    const uint32_t lead_tempty[2] = {PAIR ? ptx::mapa(tempty, 0) : 0u, PAIR ? ptx::mapa(tempty + 1, 0) : 0u};
+    for (; ct_tile_at(p, it, rank, tc); ++it) {
       const int buf = it & 1;
       const uint32_t use = uint32_t(it >> 1);
       if (leader) *epi_go = ct_wait(tfull + buf, use & 1u) ? 1 : 0;
@@ -508,7 +575,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       ptx::tc_fence_after_sync();
       if (leader && it == 0) ct_stamp(p, 4);
       const int x = tc.x0 + xi, y = tc.y0 + yj;
-      const bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H;
+      const bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H && tc.n < p.NB;
       const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
       const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
       uint8_t* stg = s_stage + (warp - 2) * 2048;
@@ -553,7 +620,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * 256 + c * 32), v);
         if (c + 2 >= chunks) {  // this warp's last chunk: its share of the accumulator is read, hand it back
           ptx::tc_fence_before_sync();
-          ptx::mbar_arrive(tempty + buf);
+          if (PAIR)
+            ptx::mbar_arrive_cluster(lead_tempty[buf]);   // the leader's MMA warp waits for both CTAs' epilogues
+          else
+            ptx::mbar_arrive(tempty + buf);
         }
         if (EPI == CT_EPI_BIAS_ACT) {
           const int nv = min(32, p.cout - col);
@@ -604,7 +674,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       }
       if (chunks <= half) {  // a one-chunk tile leaves the second warp of each pair without work
         ptx::tc_fence_before_sync();
-        ptx::mbar_arrive(tempty + buf);
+        if (PAIR)
+          ptx::mbar_arrive_cluster(lead_tempty[buf]);
+        else
+          ptx::mbar_arrive(tempty + buf);
       }
       if (EPI == CT_EPI_HEAD_MEAN) {
         // the two warps of a lane quadrant hold the even / odd chunks of the same pixels; the pixels of each image are
@@ -615,7 +688,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         const int img_first = tc.y0 / p.row_period;
         const int img = img_first + et;
         const int y_lo = max(img * p.row_period, tc.y0), y_hi = min(min(img * p.row_period + p.row_valid, tc.y0 + p.bh), p.H);
-        if (et < 4 && y_lo < y_hi) {
+        if (et < 4 && y_lo < y_hi && tc.n < p.NB) {
           float s = 0.f;
           for (int r = (y_lo - tc.y0) * p.pw; r < (y_hi - tc.y0) * p.pw; ++r) s += s_red[r] + s_red[128 + r];
           s *= p.head_scale;
@@ -630,10 +703,16 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   }
 
   ptx::tc_fence_before_sync();
-  __syncthreads();
+  if (PAIR)
+    ptx::cluster_sync();   // neither CTA may leave while the other can still read its shared memory or signal its barriers
+  else
+    __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after_sync();
-    ptx::tmem_dealloc(tmem_base, 512);
+    if (PAIR)
+      ptx::tmem_dealloc_2sm(tmem_base, 512);
+    else
+      ptx::tmem_dealloc(tmem_base, 512);
   }
   if (threadIdx.x == 0) ct_stamp(p, 6);
 }
@@ -664,8 +743,26 @@ static CtEncodeFn ct_encode_fn() {
 
 template <int EPI>
 static int ct_launch(const ConvTcParams& p, int grid, int smem, cudaStream_t s) {
-  WOFT_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_LIMIT));
-  conv_tc_kernel<EPI><<<grid, CT_THREADS, smem, s>>>(p);
+  if (p.pair)
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_LIMIT));
+  else
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_LIMIT));
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(CT_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = p.pair ? 2 : 1;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = p.pair ? 1 : 0;
+  if (p.pair)
+    WOFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_tc_kernel<EPI, true>, p));
+  else
+    WOFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_tc_kernel<EPI, false>, p));
   return launch_status("conv_tc_kernel");
 }
 
@@ -752,6 +849,10 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   const long long total = (long long)p.x_tiles * p.y_tiles * a->batch * p.n_tiles;
   WOFT_REQUIRE(total < (1LL << 31), "woft_conv_tc: too many tiles");
   p.total_tiles = (int)total;
+  // pair mode: two CTAs of a cluster share the filter tile, each loading half of its rows (cta_group::2 MMA, M = 256)
+  p.pair = (a->pair && !p.halo && bn % 32 == 0) ? 1 : 0;
+  p.pix_tiles = p.x_tiles * p.y_tiles * a->batch;
+  p.pair_tiles = (p.pix_tiles + 1) / 2 * p.n_tiles;
   p.taps = taps;
   for (int ky = 0; ky < a->kh; ++ky)
     for (int kx = 0; kx < a->kw; ++kx) {
@@ -763,7 +864,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.k_chunks = cin_pad / k_elems;
   p.f16 = a->in_f16 ? 1 : 0;
   p.a_bytes = p.pw * p.hh * 128;
-  p.b_bytes = bn * 128;
+  p.b_bytes = (p.pair ? bn / 2 : bn) * 128;
   p.cout = a->cout;
   p.relu = a->relu;
   p.scale = a->scale;
@@ -842,7 +943,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   {
     cuuint64_t dims[3] = {(cuuint64_t)cin_pad, (cuuint64_t)a->cout_pad, (cuuint64_t)p.taps};
     cuuint64_t strides[2] = {(cuuint64_t)cin_pad * esz, (cuuint64_t)cin_pad * esz * a->cout_pad};
-    cuuint32_t box[3] = {(cuuint32_t)k_elems, (cuuint32_t)bn, 1};
+    cuuint32_t box[3] = {(cuuint32_t)k_elems, (cuuint32_t)(p.pair ? bn / 2 : bn), 1};
     cuuint32_t estr[3] = {1, 1, 1};
     if (enc(&p.tmB, dt, 3, const_cast<void*>(a->weight_packed), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
@@ -863,6 +964,10 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   int sms = 0;
   WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  if (p.pair) {
+    const int pairs = p.pair_tiles < sms / 2 ? p.pair_tiles : sms / 2;
+    grid = 2 * pairs;
+  }
   WOFT_REQUIRE(grid >= 1, "woft_conv_tc: empty grid");
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (a->epilogue) {

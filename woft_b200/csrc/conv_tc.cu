@@ -317,7 +317,7 @@ __device__ __forceinline__ void ct_load_tile(const float* base, long long stride
 }
 
 // PAIR instantiations contain cluster / cta_group::2 instructions and can only be launched as clusters of two
-template <int EPI, bool PAIR>
+template <int EPI, bool PAIR, bool F16>
 __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_constant__ ConvTcParams p) {
   extern __shared__ uint8_t ct_smem_raw[];
   // 1 KiB alignment by an offset into the array (a cast through an integer would turn every later access generic)
@@ -343,7 +343,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   if (threadIdx.x == 0) {
     ct_stamp(p, 0);
     for (int s = 0; s < p.stages; ++s) {
-      ptx::mbar_init(full + s, PAIR ? 2 : 1);   // pair: the leader's barrier counts both producers
+      ptx::mbar_init(full + s, 1);   // pair: only the leader arrives (announcing both CTAs' bytes); the peer's loads just complete
       ptx::mbar_init(empty + s, 1);
     }
     for (int i = 0; i < 2; ++i) {
@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
 
   if (warp == 0) {
     // ================================ TMA producer ================================
-    if (lane == 0) {
+    if (ptx::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       bool alive = true;
@@ -431,12 +431,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               break;
             }
             if (PAIR) {
-              // both CTAs' bytes are counted on the LEADER's barrier: the leader announces the sum, the peer only arrives
+              // both CTAs' bytes are counted on the LEADER's barrier, which the leader arms with the sum.  The peer does not
+              // arrive (a remote release-arrive per stage paced the whole pipeline at 0.74 us per step): its bytes may land
+              // before the leader has armed the phase, which only drives the pending count negative for a while -- the
+              // phase cannot complete before the leader's arrival, and the peer cannot reach the next use of this stage
+              // before the leader's MMAs have drained it
               const uint32_t lead_full = ptx::mapa(full + stage, 0);
-              if (rank == 0)
-                ptx::mbar_arrive_expect_tx(full + stage, 2u * uint32_t(p.a_bytes + p.b_bytes));
-              else
-                ptx::mbar_arrive_cluster(lead_full);
+              if (rank == 0) ptx::mbar_arrive_expect_tx(full + stage, 2u * uint32_t(p.a_bytes + p.b_bytes));
               ptx::tma_load_4d_2sm(sA + stage * p.a_stage, &p.tmA, lead_full, kc * p.k_elems, xs, ys, tc.n);
               ptx::tma_load_3d_2sm(sB + stage * p.b_bytes, &p.tmB, lead_full, kc * p.k_elems, tc.c0 + int(rank) * (p.bn >> 1), tap);
             } else {
@@ -454,8 +455,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (lane == 0 && rank == 0) {   // pair mode: the leader CTA issues for both SMs
-      const uint32_t fmt = p.f16 ? 0u : 2u;  // F16 = 0, TF32 = 2
+    if (rank == 0 && ptx::elect_one()) {   // one elected lane; pair mode: the leader CTA issues for both SMs
+      const uint32_t fmt = F16 ? 0u : 2u;  // F16 = 0, TF32 = 2
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(p.bn >> 3) << 17) |
                              (uint32_t((PAIR ? 256 : 128) >> 4) << 24);
       int stage = 0, a_st = 0;
@@ -490,7 +491,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 const uint32_t acc = (kc > 0 || tap > 0 || k > 0) ? 1u : 0u;
-                if (p.f16)
+                if (F16)
                   ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
                 else
                   ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
@@ -524,11 +525,11 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row
             const uint32_t acc = (ks > 0 || k > 0) ? 1u : 0u;
             if (PAIR) {
-              if (p.f16)
+              if (F16)
                 ptx::mma_f16_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
               else
                 ptx::mma_tf32_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-            } else if (p.f16) {
+            } else if (F16) {
               ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
             } else {
               ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
@@ -743,10 +744,10 @@ static CtEncodeFn ct_encode_fn() {
 
 template <int EPI>
 static int ct_launch(const ConvTcParams& p, int grid, int smem, cudaStream_t s) {
-  if (p.pair)
-    WOFT_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_LIMIT));
-  else
-    WOFT_CUDA_CHECK(cudaFuncSetAttribute(conv_tc_kernel<EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_LIMIT));
+  void (*kern)(const ConvTcParams) =
+      p.pair ? (p.f16 ? conv_tc_kernel<EPI, true, true> : conv_tc_kernel<EPI, true, false>)
+             : (p.f16 ? conv_tc_kernel<EPI, false, true> : conv_tc_kernel<EPI, false, false>);
+  WOFT_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, CT_SMEM_LIMIT));
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(CT_THREADS);
@@ -759,10 +760,7 @@ static int ct_launch(const ConvTcParams& p, int grid, int smem, cudaStream_t s) 
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = p.pair ? 1 : 0;
-  if (p.pair)
-    WOFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_tc_kernel<EPI, true>, p));
-  else
-    WOFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, conv_tc_kernel<EPI, false>, p));
+  WOFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p));
   return launch_status("conv_tc_kernel");
 }
 

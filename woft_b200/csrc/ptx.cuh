@@ -161,6 +161,14 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, float (&v)[32]) {
 }
 
 
+// One lane of a converged warp: the compiler recognises elect.sync and emits the uniform-datapath instructions behind it
+// (UTMALDG, UTCHMMA, UTCBAR) straight, instead of the ELECT / BRA.U.ANY loops it wraps around them under `lane == 0`.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- thread-block clusters and the two-SM (cta_group::2) forms ------------------------------------------------------
 __device__ __forceinline__ uint32_t cluster_ctarank() {
   uint32_t r;

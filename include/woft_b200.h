@@ -395,6 +395,9 @@ typedef struct woft_conv_tc_args {
                         OUTPUT pixels, with (box_w + kw - 1) * box_h <= 128 */
   int pair;          /* 1: clusters of two CTAs share each filter tile (tcgen05 cta_group::2, M = 256): every CTA fetches its
                         own activation box and half of the filter rows; ignored in halo mode */
+  int pdl;           /* 1: programmatic dependent launch -- the kernel may be scheduled while its predecessor in the stream
+                        still runs; it sets up (barriers, TMEM, filters' tensor map) and then waits for the predecessor
+                        to complete before touching any tensor */
 } woft_conv_tc_args;
 int woft_conv_tc(const woft_conv_tc_args* args, void* stream);
 int woft_conv_tc_check(void* stream);

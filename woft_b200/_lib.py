@@ -32,7 +32,7 @@ class ConvTcArgs(ctypes.Structure):
                 ("bias", c_void_p), ("out", c_void_p), ("out_stride", ctypes.c_longlong), ("out_f16", c_int),
                 ("out2", c_void_p), ("out2_stride", ctypes.c_longlong), ("out2_f16", c_int), ("h", c_void_p), ("h_stride", ctypes.c_longlong),
                 ("z", c_void_p), ("z_stride", ctypes.c_longlong), ("w1x1", c_void_p), ("head_out", c_void_p),
-                ("head_bias", c_float), ("row_period", c_int), ("row_valid", c_int), ("debug_trace", c_void_p), ("debug_flags", c_int), ("halo", c_int), ("pair", c_int)]
+                ("head_bias", c_float), ("row_period", c_int), ("row_valid", c_int), ("debug_trace", c_void_p), ("debug_flags", c_int), ("halo", c_int), ("pair", c_int), ("pdl", c_int)]
 
 
 CONV_BIAS_ACT, CONV_GRU_ZR, CONV_GRU_Q, CONV_HEAD_MEAN = range(4)

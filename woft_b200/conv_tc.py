@@ -17,6 +17,8 @@ from . import _lib
 
 #: two-CTA mode (tcgen05 cta_group::2) unless a call says otherwise; WOFT_CONV_PAIR=0 switches it off
 PAIR_DEFAULT = os.environ.get("WOFT_CONV_PAIR", "0") == "1"
+#: programmatic dependent launch of the convolution kernels (WOFT_CONV_PDL=0 switches it off)
+PDL_DEFAULT = os.environ.get("WOFT_CONV_PDL", "1") == "1"
 
 
 def round_to_tf32(t):
@@ -89,6 +91,7 @@ def run(pc, x, x_off=0, epilogue=_lib.CONV_BIAS_ACT, relu=False, scale=1.0, out=
     a.row_period, a.row_valid = row_period, row_valid
     a.debug_flags = debug_flags
     a.pair = int(PAIR_DEFAULT if pair is None else pair)   # two-CTA clusters sharing the filter tile (cta_group::2)
+    a.pdl = int(PDL_DEFAULT)
     a.halo = int(halo)   # filters resident in shared memory, one activation box per tile and channel block (box = output tile)
     a.debug_trace = _lib.ptr(trace)   # debug: int64 tensor of 8 * 148 per-CTA time stamps
     with torch.cuda.device(x.device):

@@ -1,4 +1,5 @@
 // C-ABI glue: error reporting, woft_corr_pyramid dispatch over the arithmetic modes, workspace sizing.
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -23,6 +24,14 @@ int corr_pyramid_tc(const float*, const float*, int, int, int, int, int, float* 
 size_t corr_tc_workspace_bytes(int, int, int, int);
 void corr_tc_set_trace_buffer(unsigned long long*);
 int launch_row_mean(const float*, const float*, int, int, int, float*, float*, float*, cudaStream_t);
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("WOFT_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
 
 static size_t simt_workspace_bytes(int B, int C) { return 256 + ((size_t)B * C * 4 + 255) / 256 * 256; }
 

@@ -83,6 +83,7 @@ struct ConvTcParams {
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA, or null
   int coalesce;               // every epilogue operand is 16-byte aligned with 16-byte multiple strides: staged accesses
   int dbg;                    // experiments (woft_conv_tc_args.debug_flags)
+  int pdl;                    // host only: launch with programmatic stream serialization
 };
 
 __device__ __forceinline__ void ct_stamp(const ConvTcParams& p, int slot) {
@@ -378,6 +379,11 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   else
     __syncthreads();
   ptx::tc_fence_after_sync();
+  // Everything above (barriers, TMEM, tensor-map prefetch, bias) is independent of the previous kernel in the stream; from
+  // here on its output is read and buffers it may still be reading are written.  Launched with programmatic
+  // serialization this kernel's set-up overlaps the predecessor's tail, and the successor's overlaps this kernel's.
+  ptx::griddep_wait();
+  ptx::griddep_launch();
   const uint32_t tmem_base = *tmem_ptr;
   const int k_steps = p.taps * p.k_chunks;
   if (threadIdx.x == 0) ct_stamp(p, 1);
@@ -753,13 +759,22 @@ static int ct_launch(const ConvTcParams& p, int grid, int smem, cudaStream_t s) 
   cfg.blockDim = dim3(CT_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = s;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = p.pair ? 2 : 1;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (p.pair) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = 2;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (p.pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = p.pair ? 1 : 0;
+  cfg.numAttrs = na;
   WOFT_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, p));
   return launch_status("conv_tc_kernel");
 }
@@ -883,6 +898,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.row_valid = a->row_valid;
   p.trace = static_cast<unsigned long long*>(a->debug_trace);
   p.dbg = a->debug_flags;
+  p.pdl = (a->pdl && pdl_enabled()) ? 1 : 0;
 
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {

@@ -376,6 +376,7 @@ __global__ void cast_nhwc_f16_kernel(const float* __restrict__ src, int src_stri
                                      __half* __restrict__ d1, int d1_stride, int d1_off, __half* __restrict__ d2,
                                      int d2_stride, int d2_off) {
   const unsigned per_pixel = unsigned(channels) / 2;
+  pdl_sync();
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const unsigned pix = i / per_pixel;
     const int c = int(i - pix * per_pixel) * 2;
@@ -538,9 +539,9 @@ extern "C" int woft_cast_nhwc_f16(const float* src, int src_stride, int channels
                "woft_cast_nhwc_f16: channel counts, strides and offsets must be even and the pointers aligned to a pair");
   const long long total = pixels * (channels / 2);
   WOFT_REQUIRE(total <= kMaxElems32, "woft_cast_nhwc_f16: more than 2^31 - 1 pairs");
-  cast_nhwc_f16_kernel<<<ew_grid(total), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      src, src_stride, channels, unsigned(total), static_cast<__half*>(dst), dst_stride, dst_offset,
-      static_cast<__half*>(dst2), dst2_stride, dst2_offset);
+  WOFT_CUDA_CHECK(launch_pdl(cast_nhwc_f16_kernel, dim3(ew_grid(total)), dim3(256), 0, static_cast<cudaStream_t>(stream), src,
+                             src_stride, channels, unsigned(total), static_cast<__half*>(dst), dst_stride, dst_offset,
+                             static_cast<__half*>(dst2), dst2_stride, dst2_offset));
   return launch_status("cast_nhwc_f16_kernel");
 }
 

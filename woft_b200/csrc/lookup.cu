@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
   __shared__ float win[kLevelsPerPass * kQueriesPerCta * STRIDE];
   __shared__ int s_x0[kLevelsPerPass * kQueriesPerCta], s_y0[kLevelsPerPass * kQueriesPerCta];
   __shared__ float s_ax[kLevelsPerPass * kQueriesPerCta], s_ay[kLevelsPerPass * kQueriesPerCta];
+  pdl_sync();   // the coordinates come from the previous kernel of the iteration
 
   const int tid = threadIdx.x;
   const int q0 = blockIdx.x * kQueriesPerCta;
@@ -248,15 +249,17 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
 
 template <int R>
 static int launch_lookup(const LookupParams& p, bool vec, bool nhwc, cudaStream_t stream) {
-  const int grid = ceil_div(p.nq, kQueriesPerCta);
+  const dim3 grid(ceil_div(p.nq, kQueriesPerCta)), block(kLookupThreads);
+  cudaError_t e;
   if (vec && nhwc)
-    corr_lookup_kernel<R, true, true><<<grid, kLookupThreads, 0, stream>>>(p);
+    e = launch_pdl(corr_lookup_kernel<R, true, true>, grid, block, 0, stream, p);
   else if (vec)
-    corr_lookup_kernel<R, true, false><<<grid, kLookupThreads, 0, stream>>>(p);
+    e = launch_pdl(corr_lookup_kernel<R, true, false>, grid, block, 0, stream, p);
   else if (nhwc)
-    corr_lookup_kernel<R, false, true><<<grid, kLookupThreads, 0, stream>>>(p);
+    e = launch_pdl(corr_lookup_kernel<R, false, true>, grid, block, 0, stream, p);
   else
-    corr_lookup_kernel<R, false, false><<<grid, kLookupThreads, 0, stream>>>(p);
+    e = launch_pdl(corr_lookup_kernel<R, false, false>, grid, block, 0, stream, p);
+  if (e != cudaSuccess) return fail(WOFT_ERR_CUDA, "corr_lookup_kernel launch failed: %s", cudaGetErrorString(e));
   return launch_status("corr_lookup_kernel");
 }
 

@@ -161,6 +161,12 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, float (&v)[32]) {
 }
 
 
+// Programmatic dependent launch: a kernel launched with the programmatic-serialization attribute may start while its
+// predecessor in the stream still runs; griddep_wait blocks until the predecessor has completed and its writes are visible,
+// griddep_launch lets the successor's CTAs be scheduled from here on (they stop at their own griddep_wait).
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // One lane of a converged warp: the compiler recognises elect.sync and emits the uniform-datapath instructions behind it
 // (UTMALDG, UTCHMMA, UTCBAR) straight, instead of the ELECT / BRA.U.ANY loops it wraps around them under `lane == 0`.
 __device__ __forceinline__ bool elect_one() {

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(256) flow_conv7x7_relu_kernel(const float* __r
     }
   }
   const int n_in = 2 * rows * pitch;
+  pdl_sync();   // the filters above are constants; the flow is the previous kernel's output
   for (int i0 = threadIdx.x; i0 < n_in; i0 += 4 * 256) {
     float v[4];
     int dst[4];
@@ -238,6 +239,7 @@ __global__ void __launch_bounds__(256) flow_head_taps_kernel(const float* __rest
   }
   __syncthreads();
   if (threadIdx.x == 0) ptx::mbar_arrive_expect_tx(&bar, uint32_t(n_pix) * uint32_t(C) * 4u);
+  pdl_sync();        // `in` is the previous kernel's output
   __syncthreads();   // the expectation is posted before any copy can complete
   if (threadIdx.x < n_pix)
     ptx::bulk_load_1d(tile + (size_t)threadIdx.x * pitch, in + (size_t)(pbase + threadIdx.x) * C, uint32_t(C) * 4u, &bar);
@@ -317,6 +319,7 @@ __global__ void flow_head_gather_kernel(const float* __restrict__ taps, const fl
                                         float* __restrict__ flow_nchw, float* __restrict__ flow_nhwc) {
   const int hw = H * W;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  pdl_sync();
   if (i >= B * hw) return;
   const int b = i / hw, r = i - b * hw;
   const int y = r / W, x = r - y * W;
@@ -371,10 +374,12 @@ static int flow_conv7x7_impl(const float* flow, const float* weight, const float
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (f16) {
     WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_conv7x7_relu_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    flow_conv7x7_relu_kernel<true><<<grid, 256, smem, s>>>(flow, weight, bias, out_nhwc, height, width, spc, rows_max);
+    WOFT_CUDA_CHECK(launch_pdl(flow_conv7x7_relu_kernel<true>, grid, dim3(256), smem, s, flow, weight, bias, out_nhwc, height,
+                               width, spc, rows_max));
   } else {
     WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_conv7x7_relu_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    flow_conv7x7_relu_kernel<false><<<grid, 256, smem, s>>>(flow, weight, bias, out_nhwc, height, width, spc, rows_max);
+    WOFT_CUDA_CHECK(launch_pdl(flow_conv7x7_relu_kernel<false>, grid, dim3(256), smem, s, flow, weight, bias, out_nhwc, height,
+                               width, spc, rows_max));
   }
   return launch_status("flow_conv7x7_relu_kernel");
 }
@@ -429,9 +434,9 @@ extern "C" int woft_flow_head_step(const float* in_nhwc, const float* weight, co
   const size_t tile_floats = (size_t)kTapPix * (channels + 4), red_floats = (size_t)kTapSlices * kTapPix * 18;
   const size_t smem = ((size_t)channels * kTapW + (tile_floats > red_floats ? tile_floats : red_floats)) * sizeof(float);
   WOFT_CUDA_CHECK(cudaFuncSetAttribute(flow_head_taps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  flow_head_taps_kernel<<<(unsigned)ceil_div((int)pixels, kTapPix), 256, smem, s>>>(in_nhwc, weight, taps, (int)pixels,
-                                                                                   channels);
-  flow_head_gather_kernel<<<(unsigned)ceil_div((int)pixels, 128), 128, 0, s>>>(taps, bias, batch, height, width, delta_nchw,
-                                                                               coords, coords0, flow_nchw, flow_nhwc);
+  WOFT_CUDA_CHECK(launch_pdl(flow_head_taps_kernel, dim3((unsigned)ceil_div((int)pixels, kTapPix)), dim3(256), smem, s, in_nhwc,
+                             weight, taps, (int)pixels, channels));
+  WOFT_CUDA_CHECK(launch_pdl(flow_head_gather_kernel, dim3((unsigned)ceil_div((int)pixels, 128)), dim3(128), 0, s,
+                             (const float*)taps, bias, batch, height, width, delta_nchw, coords, coords0, flow_nchw, flow_nhwc));
   return launch_status("flow head kernels");
 }

@@ -298,6 +298,11 @@ int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels
 int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int hw, int channels, float eps, const float* residual,
                                      float* y, void* scratch, size_t scratch_bytes, void* stream);
 int woft_add_relu(const float* a, const float* b, long long n, float* y, void* stream);
+/* The channels-last instance norm on fp16 tensors (statistics and arithmetic in fp32): the form the encoders take when
+ * their convolutions run on woft_conv_tc with fp16 operands.  y = act(norm(x)), act = ReLU when `relu`; with `residual`
+ * (fp16, same shape; relu must be set) y = relu(residual + relu(norm(x))).  x, y: (batch, HW, channels) fp16. */
+int woft_instance_norm_relu_nhwc_f16(const void* x, int batch, int hw, int channels, float eps, int relu,
+                                     const void* residual, void* y, void* scratch, size_t scratch_bytes, void* stream);
 /* x = scale * (x + bias[c]) in place on a channels-last (pixels, channels) tensor, optional ReLU: the bias of the
  * convolutions that have no activation behind them (encoder outputs, extractor.py:150; downsampling 1x1s, :36-37; the
  * upsampling-mask head with its 0.25, update.py:122-125, 135). */
@@ -321,6 +326,9 @@ int woft_images_to_input(const uint8_t* img1_bgr, const uint8_t* img2_bgr, int h
  *   -> out (B,(H-1)/2+1,(W-1)/2+1,64) fp32 channels-last */
 int woft_stem_conv7x7(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
                       int relu, float* out_nhwc, void* stream);
+/* The same with an fp16 output tensor, for encoders whose residual stages run on woft_conv_tc with fp16 operands. */
+int woft_stem_conv7x7_f16(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
+                          int relu, void* out_nhwc_f16, void* stream);
 
 /* First layer of the weight head (raft_core/weighted_raft.py:319-339, 347-384) with its input assembly: per query pixel
  * the 9x9x4 correlation window (the channels-last lookup output read as (hp, wp, level), :267-272) and the mean
@@ -338,7 +346,8 @@ int woft_weight_head_conv1_stacked_f16(const float* window_nhwc, const float* me
 
 /* The wide convolutions of the update block and of the weight head as ONE implicit-GEMM kernel on the tcgen05 tensor
  * cores, with the element-wise stage that follows each of them in the reference fused into the epilogue.  Replaces the
- * nn.Conv2d calls (stride 1, zero padding) of BasicMotionEncoder, SepConvGRU, FlowHead.conv1 and the mask head
+ * nn.Conv2d calls (stride 1 or 2, zero padding) of the two encoders' residual stages (raft_core/extractor.py:6-57,
+ * 118-192), of BasicMotionEncoder, SepConvGRU, FlowHead.conv1 and the mask head
  * (pytracking/external/RAFT/raft_core/update.py:6-14, 33-60, 79-97, 122-125) and layers 2-3 + the 1x1 and patch mean of
  * WeightHead (raft_core/weighted_raft.py:318-339, 347-384).
  *   in            (N, H, W, in_stride) channels-last, fp32 or fp16 (in_f16); the first `cin` channels of every pixel
@@ -398,6 +407,11 @@ typedef struct woft_conv_tc_args {
   int pdl;           /* 1: programmatic dependent launch -- the kernel may be scheduled while its predecessor in the stream
                         still runs; it sets up (barriers, TMEM, filters' tensor map) and then waits for the predecessor
                         to complete before touching any tensor */
+  int stride;        /* 0 / 1, or 2: output pixel (x, y) reads input pixels (2x + kx - pad_w, 2y + ky - pad_h); height and
+                        width are the INPUT extents, the outputs have (H + 2 pad - k) / stride + 1 rows / columns */
+  const void* residual; /* BIAS_ACT only, or NULL: fp16 tensor laid out like `out`; out = relu(residual + act(acc + bias)),
+                           the tail of a residual block (raft_core/extractor.py:45-56) */
+  long long residual_stride;
 } woft_conv_tc_args;
 int woft_conv_tc(const woft_conv_tc_args* args, void* stream);
 int woft_conv_tc_check(void* stream);

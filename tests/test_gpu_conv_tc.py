@@ -190,3 +190,41 @@ def test_conv_tc_argument_errors():
         conv_tc.run(pc, x.contiguous(), out=x)            # not channels-last
     with pytest.raises(AssertionError):
         conv_tc.run(pc, x, out=None)                       # no output
+
+
+@pytest.mark.parametrize("shape", [
+    # B, cin, cout, H, W, k, pad
+    (2, 64, 96, 72, 128, 3, 1),     # first convolution of the encoders' second stage (stride 2), two images
+    (1, 96, 128, 45, 80, 3, 1),     # third stage, odd input height
+    (2, 64, 96, 72, 128, 1, 0),     # the 1x1 stride-2 projection of the shortcut
+    (1, 64, 64, 37, 51, 3, 1),      # ragged, odd x odd
+])
+def test_stride_two_convolution_fp16(shape):
+    """Stride-2 convolutions of the encoders (raft_core/extractor.py:16-24, 36-37): TMA boxes with an element stride of 2."""
+    from woft_b200 import conv_tc
+    B, cin, cout, H, W, k, pad = shape
+    x, w, b = make(B, cin, cout, H, W, k, k, seed=H + cout)
+    xh = cl(x.half())
+    pc = conv_tc.PackedConv(w, b, pad, f16=True)
+    Ho, Wo = (H + 2 * pad - k) // 2 + 1, (W + 2 * pad - k) // 2 + 1
+    out = cl(torch.full((B, cout, Ho, Wo), 7.0, device=DEV, dtype=torch.float16))
+    conv_tc.run(pc, xh, relu=True, out=out, stride=2)
+    conv_tc.check(DEV)
+    want = F.conv2d(xh.double(), w.half().double(), b.double(), stride=2, padding=pad).relu()
+    assert tuple(want.shape) == tuple(out.shape)
+    scale = want.abs().max().item()
+    assert (out.double() - want).abs().max().item() / scale <= 1.5e-3
+
+
+def test_residual_tail_in_the_epilogue():
+    """relu(x + relu(conv(y) + b)): the tail of a batch-norm residual block (extractor.py:45-56, norm folded) in one launch."""
+    from woft_b200 import conv_tc
+    x, w, b = make(2, 64, 64, 45, 80, 3, 3, seed=4)
+    xh = cl(x.half())
+    res = cl(torch.randn((2, 64, 45, 80), generator=torch.Generator().manual_seed(5)).half().to(DEV))
+    pc = conv_tc.PackedConv(w, b, 1, f16=True)
+    out = cl(torch.empty((2, 64, 45, 80), device=DEV, dtype=torch.float16))
+    conv_tc.run(pc, xh, relu=True, out=out, residual=res)
+    want = (res.double() + F.conv2d(xh.double(), w.half().double(), b.double(), padding=1).relu()).relu()
+    scale = want.abs().max().item()
+    assert (out.double() - want).abs().max().item() / scale <= 1.5e-3

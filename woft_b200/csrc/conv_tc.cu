@@ -61,6 +61,9 @@ struct ConvTcParams {
   // pair mode (cta_group::2): a cluster of two CTAs takes two pixel tiles that share the filters; each CTA fetches its own
   // activation box and HALF of the filter rows, the leader's MMA warp multiplies both tiles against both halves
   int pair, pix_tiles, pair_tiles;
+  int stride;        // 1 or 2: output pixel (x, y) reads input (stride * x + dx, stride * y + dy); W, H are OUTPUT extents
+  const void* residual;      // BIAS_ACT: out = relu(residual + act(acc + bias)), fp16, laid out like `out` (the tail of a
+  long long residual_stride; // residual block, raft_core/extractor.py:45-56), or null
   short tap_row[CT_MAX_TAPS];
   signed char dx[CT_MAX_TAPS], dy[CT_MAX_TAPS];
   int cout, relu;
@@ -430,7 +433,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       CtTile tc;
       for (int it = 0; alive && !p.halo && ct_tile_at(p, it, rank, tc); ++it) {
         for (int tap = 0; tap < p.taps && alive; ++tap) {
-          const int xs = tc.x0 + p.dx[tap], ys = tc.y0 + p.dy[tap];
+          const int xs = p.stride * tc.x0 + p.dx[tap], ys = p.stride * tc.y0 + p.dy[tap];
           for (int kc = 0; kc < p.k_chunks; ++kc) {
             if (!ct_wait(empty + stage, phase ^ 1u)) {
               alive = false;
@@ -640,6 +643,20 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
             if (p.relu) a = fmaxf(a, 0.f);
             v[j] = separator ? 0.f : a * p.scale;
           }
+          if (p.residual && valid && nv == 32) {   // fp16 residual, 64 contiguous bytes of this thread's pixel
+            const uint4* rs = reinterpret_cast<const uint4*>(reinterpret_cast<const __half*>(p.residual) + pix * p.residual_stride + col);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint4 u = __ldg(rs + j);
+              const __half2* hp = reinterpret_cast<const __half2*>(&u);
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float2 f = __half22float2(hp[e]);
+                v[8 * j + 2 * e] = fmaxf(v[8 * j + 2 * e] + f.x, 0.f);
+                v[8 * j + 2 * e + 1] = fmaxf(v[8 * j + 2 * e + 1] + f.y, 0.f);
+              }
+            }
+          }
           if (co && nv > 0) {   // warp-uniform
             ct_store_tile(p.out, p.out_stride, col, v, nv, p.out_f16 != 0, stg, lane, rp);
             if (p.out2) ct_store_tile(p.out2, p.out2_stride, col, v, nv, p.out2_f16 != 0, stg, lane, rp);
@@ -840,7 +857,9 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     long long best = -1;
     for (int cand = 128; cand >= 8; cand >>= 1) {
       const int cw = cand, ch = 128 / cand;
-      const long long tiles = (long long)ceil_div(a->width, cw) * ceil_div(a->height, ch);
+      const int s_ = a->stride > 1 ? a->stride : 1;
+      const long long tiles = (long long)ceil_div((a->width + 2 * a->pad_w - a->kw) / s_ + 1, cw) *
+                              ceil_div((a->height + 2 * a->pad_h - a->kh) / s_ + 1, ch);
       if (best < 0 || tiles < best) {
         best = tiles;
         bw = cw;
@@ -854,11 +873,16 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.bh = bh;
   p.pw = a->halo ? bw + a->kw - 1 : bw;
   p.hh = a->halo ? bh + a->kh - 1 : bh;
-  p.W = a->width;
-  p.H = a->height;
+  const int stride = a->stride > 1 ? a->stride : 1;
+  WOFT_REQUIRE(stride <= 2 && !(a->halo && stride != 1), "woft_conv_tc: stride 1 or 2 (1 in halo mode)");
+  const int wo = (a->width + 2 * a->pad_w - a->kw) / stride + 1, ho = (a->height + 2 * a->pad_h - a->kh) / stride + 1;
+  WOFT_REQUIRE(wo >= 1 && ho >= 1, "woft_conv_tc: empty output");
+  p.stride = stride;
+  p.W = wo;   // the tile grid, the validity tests and the pixel indices of the epilogue run over OUTPUT pixels
+  p.H = ho;
   p.NB = a->batch;
-  p.x_tiles = ceil_div(a->width, bw);
-  p.y_tiles = ceil_div(a->height, bh);
+  p.x_tiles = ceil_div(wo, bw);
+  p.y_tiles = ceil_div(ho, bh);
   const long long total = (long long)p.x_tiles * p.y_tiles * a->batch * p.n_tiles;
   WOFT_REQUIRE(total < (1LL << 31), "woft_conv_tc: too many tiles");
   p.total_tiles = (int)total;
@@ -897,12 +921,17 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.row_period = a->row_period;
   p.row_valid = a->row_valid;
   p.trace = static_cast<unsigned long long*>(a->debug_trace);
+  p.residual = a->residual;
+  p.residual_stride = a->residual_stride;
   p.dbg = a->debug_flags;
   p.pdl = (a->pdl && pdl_enabled()) ? 1 : 0;
 
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {
     WOFT_REQUIRE(!a->out2 || a->out2_f16 == a->out_f16, "woft_conv_tc: both outputs of this epilogue share one type");
+    WOFT_REQUIRE(!a->residual || ((reinterpret_cast<uintptr_t>(a->residual) & 15) == 0 && a->residual_stride % 8 == 0 &&
+                                  a->cout % 32 == 0),
+                 "woft_conv_tc: the residual is fp16, 16-byte aligned, with Cout a multiple of 32");
     // rows that are not 16-byte aligned (odd strides / offsets) are stored element by element
     WOFT_REQUIRE(a->out && (reinterpret_cast<uintptr_t>(a->out) % oesz) == 0 && a->out_stride >= a->cout,
                  "woft_conv_tc: output missing, misaligned or narrower than Cout");
@@ -948,8 +977,9 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     cuuint64_t dims[4] = {(cuuint64_t)a->cin, (cuuint64_t)a->width, (cuuint64_t)a->height, (cuuint64_t)a->batch};
     cuuint64_t strides[3] = {(cuuint64_t)a->in_stride * esz, (cuuint64_t)a->in_stride * esz * a->width,
                              (cuuint64_t)a->in_stride * esz * a->width * a->height};
-    cuuint32_t box[4] = {(cuuint32_t)k_elems, (cuuint32_t)p.pw, (cuuint32_t)p.hh, 1};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
+    // with an element stride the box extent is given in input pixels: every stride-th one is fetched
+    cuuint32_t box[4] = {(cuuint32_t)k_elems, (cuuint32_t)(p.pw * stride), (cuuint32_t)(p.hh * stride), 1};
+    cuuint32_t estr[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
     if (enc(&p.tmA, dt, 4, const_cast<void*>(a->in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the activation operand");

@@ -218,9 +218,32 @@ __global__ void concat_nhwc_kernel(const __grid_constant__ ConcatParams p, unsig
 }
 
 // ---- instance norm + ReLU on channels-last tensors (N, HW, C): per-strip partial sums, a tiny finalise, then apply
+// element type of the channels-last instance-norm kernels: fp32, or fp16 for the encoders that feed the fp16 tensor-core
+// convolutions (statistics and arithmetic stay fp32)
+template <typename T> __device__ __forceinline__ float4 ld4(const T* p, size_t i4);
+template <> __device__ __forceinline__ float4 ld4<float>(const float* p, size_t i4) {
+  return __ldg(reinterpret_cast<const float4*>(p) + i4);
+}
+template <> __device__ __forceinline__ float4 ld4<__half>(const __half* p, size_t i4) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2*>(p) + i4);
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void st4(float* p, size_t i4, float4 v) { reinterpret_cast<float4*>(p)[i4] = v; }
+__device__ __forceinline__ void st4(__half* p, size_t i4, float4 v) {
+  const __half2 a = __floats2half2_rn(v.x, v.y), b = __floats2half2_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<const uint32_t*>(&a);
+  u.y = *reinterpret_cast<const uint32_t*>(&b);
+  reinterpret_cast<uint2*>(p)[i4] = u;
+}
+__device__ __forceinline__ float ld1(const float* p, size_t i) { return __ldg(p + i); }
+__device__ __forceinline__ float ld1(const __half* p, size_t i) { return __half2float(p[i]); }
+
 constexpr int kInStrips = 256;  // (strips x batch) CTAs in the partial-sum pass: enough to fill 148 SMs at batch 1-2
 
-__global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __restrict__ x, float* __restrict__ partial,
+template <typename T>
+__global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const T* __restrict__ x, float* __restrict__ partial,
                                                               int HW, int C) {
   __shared__ float4 s_sum[256], s_sq[256];
   const int n = blockIdx.y, strip = blockIdx.x;
@@ -228,10 +251,10 @@ __global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __res
   const int cq = threadIdx.x % c4n, pl = threadIdx.x / c4n;
   const int len = (HW + kInStrips - 1) / kInStrips;
   const int p0 = strip * len, p1 = min(p0 + len, HW);
-  const float4* base = reinterpret_cast<const float4*>(x + (size_t)n * HW * C);
+  const T* base = x + (size_t)n * HW * C;
   float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
   if (pl < ppb) {
-    const float4 pv = __ldg(base + cq);  // pivot: the plane's first pixel, keeps the variance well conditioned
+    const float4 pv = ld4<T>(base, cq);  // pivot: the plane's first pixel, keeps the variance well conditioned
     auto add = [&](const float4 v) {
       const float a = v.x - pv.x, b = v.y - pv.y, c = v.z - pv.z, d = v.w - pv.w;
       s.x += a; s.y += b; s.z += c; s.w += d;
@@ -239,13 +262,13 @@ __global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __res
     };
     int p = p0 + pl;
     for (; p + 3 * ppb < p1; p += 4 * ppb) {  // four loads in flight per thread: the pass is latency bound otherwise
-      const float4 v0 = __ldg(base + (size_t)p * c4n + cq);
-      const float4 v1 = __ldg(base + (size_t)(p + ppb) * c4n + cq);
-      const float4 v2 = __ldg(base + (size_t)(p + 2 * ppb) * c4n + cq);
-      const float4 v3 = __ldg(base + (size_t)(p + 3 * ppb) * c4n + cq);
+      const float4 v0 = ld4<T>(base, (size_t)p * c4n + cq);
+      const float4 v1 = ld4<T>(base, (size_t)(p + ppb) * c4n + cq);
+      const float4 v2 = ld4<T>(base, (size_t)(p + 2 * ppb) * c4n + cq);
+      const float4 v3 = ld4<T>(base, (size_t)(p + 3 * ppb) * c4n + cq);
       add(v0); add(v1); add(v2); add(v3);
     }
-    for (; p < p1; p += ppb) add(__ldg(base + (size_t)p * c4n + cq));
+    for (; p < p1; p += ppb) add(ld4<T>(base, (size_t)p * c4n + cq));
   }
   s_sum[threadIdx.x] = s;
   s_sq[threadIdx.x] = q;
@@ -263,7 +286,8 @@ __global__ void __launch_bounds__(256) in_partial_nhwc_kernel(const float* __res
 }
 
 // one warp per channel: lanes add up the strips, 8 channels per CTA
-__global__ void __launch_bounds__(256) in_finalize_nhwc_kernel(const float* __restrict__ x,
+template <typename T>
+__global__ void __launch_bounds__(256) in_finalize_nhwc_kernel(const T* __restrict__ x,
                                                                const float* __restrict__ partial,
                                                                float* __restrict__ stats, int HW, int C, float eps) {
   const int n = blockIdx.y;
@@ -282,14 +306,15 @@ __global__ void __launch_bounds__(256) in_finalize_nhwc_kernel(const float* __re
   }
   if (lane == 0) {
     const double m = s / HW, var = q / HW - m * m;
-    stats[(size_t)n * 2 * C + c] = float(m) + __ldg(x + (size_t)n * HW * C + c);
+    stats[(size_t)n * 2 * C + c] = float(m) + ld1(x, (size_t)n * HW * C + c);
     stats[(size_t)n * 2 * C + C + c] = rsqrtf(fmaxf(float(var), 0.f) + eps);
   }
 }
 
 // `residual` (optional): y = relu(residual + act(norm(x))), the tail of a residual block (extractor.py:56) in one pass
-__global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* __restrict__ stats,
-                                     const float* __restrict__ residual, float* __restrict__ y, unsigned HW, unsigned C,
+template <typename T>
+__global__ void in_apply_nhwc_kernel(const T* __restrict__ x, const float* __restrict__ stats,
+                                     const T* __restrict__ residual, T* __restrict__ y, unsigned HW, unsigned C,
                                      int relu, unsigned total4) {
   const unsigned c4n = C >> 2;
   const unsigned per_image = HW * c4n;
@@ -297,7 +322,7 @@ __global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* _
   for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += gridDim.x * blockDim.x) {
     const unsigned cq = i % c4n;
     const unsigned n = i / per_image;
-    const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    const float4 v = ld4<T>(x, i);
     const float4 m = __ldg(reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C) + cq);
     const float4 r = __ldg(reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C + C) + cq);
     float4 o;
@@ -306,10 +331,10 @@ __global__ void in_apply_nhwc_kernel(const float* __restrict__ x, const float* _
     o.z = fmaxf((v.z - m.z) * r.z, floor_);
     o.w = fmaxf((v.w - m.w) * r.w, floor_);
     if (residual) {
-      const float4 a = __ldg(reinterpret_cast<const float4*>(residual) + i);
+      const float4 a = ld4<T>(residual, i);
       o.x = fmaxf(a.x + o.x, 0.f); o.y = fmaxf(a.y + o.y, 0.f); o.z = fmaxf(a.z + o.z, 0.f); o.w = fmaxf(a.w + o.w, 0.f);
     }
-    reinterpret_cast<float4*>(y)[i] = o;
+    st4(y, i, o);
   }
 }
 
@@ -550,8 +575,9 @@ extern "C" size_t woft_instance_norm_nhwc_scratch_bytes(int batch, int channels)
   return (size_t)batch * channels * 2 * (woft::kInStrips + 1) * sizeof(float);
 }
 
-static int instance_norm_nhwc_impl(const char* who, const float* x, int batch, int hw, int channels, float eps, int relu,
-                                   const float* residual, float* y, void* scratch, size_t scratch_bytes, void* stream) {
+template <typename T>
+static int instance_norm_nhwc_impl(const char* who, const T* x, int batch, int hw, int channels, float eps, int relu,
+                                   const T* residual, T* y, void* scratch, size_t scratch_bytes, void* stream) {
   using namespace woft;
   WOFT_REQUIRE(x && y && scratch, "instance norm (NHWC): null pointer");
   WOFT_REQUIRE(batch > 0 && hw > 0 && channels > 0 && channels % 4 == 0 && channels <= 1024 && batch < 65536,
@@ -561,18 +587,26 @@ static int instance_norm_nhwc_impl(const char* who, const float* x, int batch, i
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   float* partial = static_cast<float*>(scratch);
   float* stats = partial + (size_t)batch * kInStrips * 2 * channels;
-  in_partial_nhwc_kernel<<<dim3(kInStrips, batch), 256, 0, s>>>(x, partial, hw, channels);
-  in_finalize_nhwc_kernel<<<dim3(ceil_div(channels, 8), batch), 256, 0, s>>>(x, partial, stats, hw, channels, eps);
+  in_partial_nhwc_kernel<T><<<dim3(kInStrips, batch), 256, 0, s>>>(x, partial, hw, channels);
+  in_finalize_nhwc_kernel<T><<<dim3(ceil_div(channels, 8), batch), 256, 0, s>>>(x, partial, stats, hw, channels, eps);
   const long long total4 = (long long)batch * hw * (channels / 4);
   WOFT_REQUIRE(total4 <= kMaxElems32, "instance norm (NHWC): more than 2^31 - 1 vectors");
-  in_apply_nhwc_kernel<<<ew_grid(total4), 256, 0, s>>>(x, stats, residual, y, hw, channels, relu, unsigned(total4));
+  in_apply_nhwc_kernel<T><<<ew_grid(total4), 256, 0, s>>>(x, stats, residual, y, hw, channels, relu, unsigned(total4));
   return launch_status("instance norm (NHWC) kernels");
 }
 
 extern "C" int woft_instance_norm_relu_nhwc(const float* x, int batch, int hw, int channels, float eps, int relu,
                                             float* y, void* scratch, size_t scratch_bytes, void* stream) {
-  return instance_norm_nhwc_impl("woft_instance_norm_relu_nhwc", x, batch, hw, channels, eps, relu, nullptr, y, scratch,
-                                 scratch_bytes, stream);
+  return instance_norm_nhwc_impl<float>("woft_instance_norm_relu_nhwc", x, batch, hw, channels, eps, relu, nullptr, y,
+                                        scratch, scratch_bytes, stream);
+}
+
+extern "C" int woft_instance_norm_relu_nhwc_f16(const void* x, int batch, int hw, int channels, float eps, int relu,
+                                                const void* residual, void* y, void* scratch, size_t scratch_bytes,
+                                                void* stream) {
+  return instance_norm_nhwc_impl<__half>("woft_instance_norm_relu_nhwc_f16", static_cast<const __half*>(x), batch, hw,
+                                         channels, eps, relu, static_cast<const __half*>(residual), static_cast<__half*>(y),
+                                         scratch, scratch_bytes, stream);
 }
 
 extern "C" int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int hw, int channels, float eps,
@@ -580,8 +614,8 @@ extern "C" int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int h
                                                 void* stream) {
   using namespace woft;
   WOFT_REQUIRE(residual, "woft_instance_norm_relu_add_nhwc: null residual");
-  return instance_norm_nhwc_impl("woft_instance_norm_relu_add_nhwc", x, batch, hw, channels, eps, 1, residual, y, scratch,
-                                 scratch_bytes, stream);
+  return instance_norm_nhwc_impl<float>("woft_instance_norm_relu_add_nhwc", x, batch, hw, channels, eps, 1, residual, y,
+                                        scratch, scratch_bytes, stream);
 }
 
 extern "C" int woft_add_relu(const float* a, const float* b, long long n, float* y, void* stream) {

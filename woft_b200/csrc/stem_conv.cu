@@ -9,6 +9,8 @@
 // and the A fragments are gathered from it through a k -> patch-offset table.  4 warps, each 2 m16 tiles x 8 n8 tiles.
 // Input (n, H, W, 3) fp32 channels-last (woft_images_to_input), output (n, H/2, W/2, 64) channels-last, optional
 // bias + ReLU (the context encoder's folded batch norm).
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace woft {
@@ -32,10 +34,11 @@ __device__ __forceinline__ void mma_tf32_16x8x8(float (&d)[4], const float (&a)[
         "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
 }
 
+template <bool F16OUT>   // F16OUT: `out_any` holds __half (input of the fp16 tensor-core convolutions)
 __global__ void __launch_bounds__(128) stem_conv7x7_kernel(const float* __restrict__ in,      // (n, H, W, 3)
                                                            const float* __restrict__ weight,  // (64, 3, 7, 7)
                                                            const float* __restrict__ bias,    // (64) or null
-                                                           float* __restrict__ out,           // (n, Ho, Wo, 64)
+                                                           void* __restrict__ out_any,        // (n, Ho, Wo, 64)
                                                            int H, int W, int Ho, int Wo, int tiles_x, int tiles_y,
                                                            int total_tiles, int relu) {
   extern __shared__ __align__(16) float sm[];
@@ -132,7 +135,7 @@ __global__ void __launch_bounds__(128) stem_conv7x7_kernel(const float* __restri
       for (int h = 0; h < 2; ++h) {
         const int ox = ox0 + g + 8 * h;
         if (ox >= Wo) continue;
-        float* o = out + (((size_t)img * Ho + oy) * Wo + ox) * kStN + 2 * t;
+        const size_t obase = (((size_t)img * Ho + oy) * Wo + ox) * kStN + 2 * t;
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
           float x = acc[mt][nt][2 * h], y = acc[mt][nt][2 * h + 1];
@@ -144,7 +147,10 @@ __global__ void __launch_bounds__(128) stem_conv7x7_kernel(const float* __restri
             x = fmaxf(x, 0.f);
             y = fmaxf(y, 0.f);
           }
-          *reinterpret_cast<float2*>(o + nt * 8) = make_float2(x, y);
+          if (F16OUT)
+            *reinterpret_cast<__half2*>(reinterpret_cast<__half*>(out_any) + obase + nt * 8) = __floats2half2_rn(x, y);
+          else
+            *reinterpret_cast<float2*>(reinterpret_cast<float*>(out_any) + obase + nt * 8) = make_float2(x, y);
         }
       }
     }
@@ -153,8 +159,8 @@ __global__ void __launch_bounds__(128) stem_conv7x7_kernel(const float* __restri
 
 }  // namespace woft
 
-extern "C" int woft_stem_conv7x7(const float* in_nhwc, const float* weight, const float* bias, int batch, int height,
-                                 int width, int relu, float* out_nhwc, void* stream) {
+static int stem_conv7x7_impl(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
+                             int relu, void* out_nhwc, bool f16, void* stream) {
   using namespace woft;
   WOFT_REQUIRE(in_nhwc && weight && out_nhwc, "woft_stem_conv7x7: null pointer");
   WOFT_REQUIRE(batch > 0 && height > 0 && width > 0, "woft_stem_conv7x7: bad extent");
@@ -164,9 +170,26 @@ extern "C" int woft_stem_conv7x7(const float* in_nhwc, const float* weight, cons
   const long long total = (long long)tiles_x * tiles_y * batch;
   WOFT_REQUIRE(total < (1LL << 31), "woft_stem_conv7x7: too many tiles");
   const size_t smem = ((size_t)kStKP * kStWPitch + ((kStPatch + 3) & ~3)) * sizeof(float) + kStKP * sizeof(int);
-  WOFT_CUDA_CHECK(cudaFuncSetAttribute(stem_conv7x7_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int grid = (int)(total < 148 * 4 ? total : 148 * 4);
-  stem_conv7x7_kernel<<<grid, 128, smem, static_cast<cudaStream_t>(stream)>>>(
-      in_nhwc, weight, bias, out_nhwc, height, width, Ho, Wo, tiles_x, tiles_y, (int)total, relu);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (f16) {
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(stem_conv7x7_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    stem_conv7x7_kernel<true><<<grid, 128, smem, s>>>(in_nhwc, weight, bias, out_nhwc, height, width, Ho, Wo, tiles_x, tiles_y,
+                                                      (int)total, relu);
+  } else {
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(stem_conv7x7_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    stem_conv7x7_kernel<false><<<grid, 128, smem, s>>>(in_nhwc, weight, bias, out_nhwc, height, width, Ho, Wo, tiles_x, tiles_y,
+                                                       (int)total, relu);
+  }
   return launch_status("stem_conv7x7_kernel");
+}
+
+extern "C" int woft_stem_conv7x7(const float* in_nhwc, const float* weight, const float* bias, int batch, int height,
+                                 int width, int relu, float* out_nhwc, void* stream) {
+  return stem_conv7x7_impl(in_nhwc, weight, bias, batch, height, width, relu, out_nhwc, false, stream);
+}
+
+extern "C" int woft_stem_conv7x7_f16(const float* in_nhwc, const float* weight, const float* bias, int batch, int height,
+                                     int width, int relu, void* out_nhwc_f16, void* stream) {
+  return stem_conv7x7_impl(in_nhwc, weight, bias, batch, height, width, relu, out_nhwc_f16, true, stream);
 }

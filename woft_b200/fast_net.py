@@ -213,6 +213,43 @@ def stem_conv7x7(x_cl, weight, bias=None, relu=False):
     return out
 
 
+def stem_conv7x7_f16(x_cl, weight, bias=None, relu=False):
+    """woft_stem_conv7x7_f16: the same first layer with an fp16 output tensor."""
+    x_cl = _cl(x_cl)
+    B, C, H, W = x_cl.shape
+    out = torch.empty((B, 64, (H - 1) // 2 + 1, (W - 1) // 2 + 1), device=x_cl.device, dtype=torch.float16,
+                      memory_format=torch.channels_last)
+    with torch.cuda.device(x_cl.device):
+        rc = _lib.load().woft_stem_conv7x7_f16(_lib.ptr(x_cl), _lib.ptr(weight), _lib.ptr(bias), B, H, W, int(relu),
+                                               _lib.ptr(out), _lib.current_stream(x_cl.device))
+    _lib.check(rc, "woft_stem_conv7x7_f16")
+    return out
+
+
+def instance_norm_relu_f16(x, relu=True, eps=1e-5, residual=None):
+    """Channels-last fp16 tensor -> same; woft_instance_norm_relu_nhwc_f16 (with `residual`: relu(residual + relu(norm)))."""
+    N, C, H, W = x.shape
+    y = torch.empty_like(x)
+    lib = _lib.load()
+    nbytes = lib.woft_instance_norm_nhwc_scratch_bytes(N, C)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = lib.woft_instance_norm_relu_nhwc_f16(_lib.ptr(x), N, H * W, C, eps, int(relu), _lib.ptr(residual), _lib.ptr(y),
+                                                  _lib.ptr(scratch), nbytes, _lib.current_stream(x.device))
+    _lib.check(rc, "woft_instance_norm_relu_nhwc_f16")
+    return y
+
+
+def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float16):
+    """One woft_conv_tc launch on a channels-last fp16 tensor; returns the new channels-last tensor."""
+    B, _, H, W = x.shape
+    Ho = (H + 2 * pc.pad_h - pc.kh) // stride + 1
+    Wo = (W + 2 * pc.pad_w - pc.kw) // stride + 1
+    out = torch.empty((B, pc.cout, Ho, Wo), device=x.device, dtype=out_dtype, memory_format=torch.channels_last)
+    conv_tc.run(pc, x, relu=relu, out=out, stride=stride, residual=residual)
+    return out
+
+
 def flow_head_step(x_cl, weight, bias, coords=None, coords0=None, flow_nchw=None, flow_nhwc=None, want_delta=False):
     """FlowHead.conv2 on a channels-last (B,C,H,W) tensor; woft_flow_head_step.  With `coords` the refinement step is
     fused: coords += delta in place, flow_nchw / flow_nhwc (preallocated, optional) = coords - coords0.  Returns the
@@ -280,7 +317,7 @@ class FastWeightedRAFT:
             # channels-last copies of the update block's weights: with NHWC activations cuDNN's sm_100 kernels run
             # without the NCHW<->NHWC conversion kernels that otherwise wrap every convolution
             self.nhwc = nhwc_update
-            self.own_convs = self.own_head = False
+            self.own_convs = self.own_head = self.own_encoders = False
             # both encoders' 3-channel first layer through woft_stem_conv7x7 instead of cuDNN's sm_80 fallback
             self.own_stem = os.environ.get("WOFT_OWN_STEM", "1") == "1"
             self.own_head_conv1 = os.environ.get("WOFT_OWN_HEAD_CONV1", "1") == "1"
@@ -332,6 +369,26 @@ class FastWeightedRAFT:
                         gt = self.gru[tag]
                         self.tc["zr" + tag] = P(gt["w_zr"], gt["b_zr"], gt["padding"])
                         self.tc["q" + tag] = P(gt["w_q"], gt["b_q"], gt["padding"])
+                    # both encoders' residual stages on the same kernel (stride-2 convolutions through TMA element
+                    # strides, fp16 activations between the layers, the batch-norm encoder's block tails in the epilogue)
+                    self.own_encoders = os.environ.get("WOFT_OWN_ENCODERS", "1") == "1" and self.own_stem
+                    if self.own_encoders:
+                        fn = net.fnet
+                        self.enc_f = {"blocks": [], "out": P(fn.conv2.weight, fn.conv2.bias, 0)}
+                        for layer in (fn.layer1, fn.layer2, fn.layer3):
+                            for blk in layer:
+                                self.enc_f["blocks"].append({
+                                    "c1": P(blk.conv1.weight, None, 1), "c2": P(blk.conv2.weight, None, 1),
+                                    "stride": blk.conv1.stride[0],
+                                    "down": P(blk.downsample[0].weight, None, 0) if blk.downsample is not None else None})
+                        folded = self._fold_encoder(net.cnet)   # plain (w, b) pairs, batch norm folded in
+                        self.enc_c = {"stem": (folded["stem"][0].contiguous(), folded["stem"][1].contiguous()),
+                                      "blocks": [], "out": (P(folded["out"][0], None, 0), folded["out"][1])}
+                        for d in folded["blocks"]:
+                            self.enc_c["blocks"].append({
+                                "c1": P(d["c1"][0], d["c1"][1], 1), "c2": P(d["c2"][0], d["c2"][1], 1),
+                                "stride": d["stride"][0],
+                                "down": P(d["down"][0], d["down"][1], 0) if d["down"] is not None else None})
                     self.own_head = False
                     if self.with_weights and os.environ.get("WOFT_OWN_HEAD", "1") == "1":
                         convs = [m for m in net.weight_head.net if isinstance(m, torch.nn.Conv2d)]
@@ -411,8 +468,33 @@ class FastWeightedRAFT:
                 x = F.relu(x + y)
         return F.conv2d(x, enc.conv2.weight, enc.conv2.bias)
 
+    def _features_tc(self, x):
+        """Feature encoder (extractor.py:118-192, instance norm) on woft_conv_tc: fp16 activations, bias-free convolutions
+        (a per-channel constant cancels in the norm), the residual tails fused into the norm pass."""
+        x = instance_norm_relu_f16(stem_conv7x7_f16(x, self.net.fnet.conv1.weight))
+        for d in self.enc_f["blocks"]:
+            y = instance_norm_relu_f16(_conv_f16(d["c1"], x, stride=d["stride"]))
+            if d["down"] is not None:
+                x = instance_norm_relu_f16(_conv_f16(d["down"], x, stride=d["stride"]), relu=False)
+            x = instance_norm_relu_f16(_conv_f16(d["c2"], y), residual=x)   # relu(x + relu(norm(conv2(y))))
+        return _conv_f16(self.enc_f["out"], x, out_dtype=torch.float32)
+
+    def _context_tc(self, x):
+        """Context encoder (batch norm folded into the filters) on woft_conv_tc; returns the last convolution WITHOUT its
+        bias (fp32) and the bias, for woft_context_split_nhwc."""
+        c = self.enc_c
+        x = stem_conv7x7_f16(_cl(x), *c["stem"], relu=True)
+        for d in c["blocks"]:
+            y = _conv_f16(d["c1"], x, stride=d["stride"], relu=True)
+            if d["down"] is not None:
+                x = _conv_f16(d["down"], x, stride=d["stride"])
+            x = _conv_f16(d["c2"], y, relu=True, residual=x)                 # relu(x + relu(conv2(y) + b))
+        return _conv_f16(c["out"][0], x, out_dtype=torch.float32), c["out"][1]
+
     def _features_nhwc(self, x):
         """Same encoder with channels-last activations and weights (no cuDNN layout conversions)."""
+        if self.own_encoders:
+            return self._features_tc(x)
         w = self.fw
         x = instance_norm_relu_nhwc(stem_conv7x7(x, self.net.fnet.conv1.weight) if self.own_stem else
                                     F.conv2d(_cl(x), w["stem"], None, stride=2, padding=3))
@@ -671,7 +753,8 @@ class FastWeightedRAFT:
         up_mask = None
         lookup_flags = 8 if nhwc else 0
         if nhwc:
-            state = self._nhwc_state(*self._context(image1, raw_tail=True), coords0, coords1)
+            ctx = self._context_tc(image1) if self.own_encoders else self._context(image1, raw_tail=True)
+            state = self._nhwc_state(*ctx, coords0, coords1)
         else:
             net, inp = torch.split(self._context(image1), [net_.hidden_dim, net_.context_dim], dim=1)
             net, inp = torch.tanh(net), torch.relu(inp)

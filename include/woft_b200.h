@@ -303,6 +303,12 @@ int woft_add_relu(const float* a, const float* b, long long n, float* y, void* s
  * (fp16, same shape; relu must be set) y = relu(residual + relu(norm(x))).  x, y: (batch, HW, channels) fp16. */
 int woft_instance_norm_relu_nhwc_f16(const void* x, int batch, int hw, int channels, float eps, int relu,
                                      const void* residual, void* y, void* scratch, size_t scratch_bytes, void* stream);
+/* The same norm with the statistics taken from the partial sums woft_conv_tc gathered while it wrote x (`stats` of its
+ * argument block: (rows, batch, 2, channels) fp32): two launches (combine, apply) instead of three, and x is read once.
+ * scratch: batch * 2 * channels floats. */
+int woft_instance_norm_from_sums_f16(const void* x, const float* partial, int rows, int batch, int hw, int channels,
+                                     float eps, int relu, const void* residual, void* y, void* scratch,
+                                     size_t scratch_bytes, void* stream);
 /* x = scale * (x + bias[c]) in place on a channels-last (pixels, channels) tensor, optional ReLU: the bias of the
  * convolutions that have no activation behind them (encoder outputs, extractor.py:150; downsampling 1x1s, :36-37; the
  * upsampling-mask head with its 0.25, update.py:122-125, 135). */
@@ -412,6 +418,11 @@ typedef struct woft_conv_tc_args {
   const void* residual; /* BIAS_ACT only, or NULL: fp16 tensor laid out like `out`; out = relu(residual + act(acc + bias)),
                            the tail of a residual block (raft_core/extractor.py:45-56) */
   long long residual_stride;
+  float* stats;      /* BIAS_ACT with one fp16 output and at most two images, or NULL: (stats_ctas, batch, 2, cout) fp32; CTA k
+                        writes the sums and sums of squares of the values it stored, per image and channel, into row k
+                        (rows of CTAs the launch does not have are cleared): the statistics of an instance norm that
+                        follows (woft_instance_norm_from_sums_f16), without a pass over the tensor */
+  int stats_ctas;    /* rows of `stats`; at least the SM count (148) */
 } woft_conv_tc_args;
 int woft_conv_tc(const woft_conv_tc_args* args, void* stream);
 int woft_conv_tc_check(void* stream);

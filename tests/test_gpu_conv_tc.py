@@ -228,3 +228,23 @@ def test_residual_tail_in_the_epilogue():
     want = (res.double() + F.conv2d(xh.double(), w.half().double(), b.double(), padding=1).relu()).relu()
     scale = want.abs().max().item()
     assert (out.double() - want).abs().max().item() / scale <= 1.5e-3
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 64, 90, 160, 1), (2, 64, 96, 90, 160, 2), (1, 96, 96, 23, 37, 1)])
+def test_convolution_gathers_instance_norm_statistics(shape):
+    """conv -> InstanceNorm -> ReLU (-> residual add) of the feature encoder (extractor.py:30-32, 45-56) with the norm's
+    statistics gathered in the convolution's epilogue, against torch on the convolution's own fp16 output."""
+    from woft_b200 import fast_net
+    from woft_b200 import conv_tc
+    B, cin, cout, H, W, stride = shape
+    x, w, _ = make(B, cin, cout, H, W, 3, 3, seed=cout + stride)
+    xh = cl((x * 1.7 + 0.4).half())
+    pc = conv_tc.PackedConv(w, None, 1, f16=True)
+    y = fast_net._conv_f16(pc, xh, stride=stride)                    # the plain convolution, fp16
+    got = fast_net.conv_instance_norm_f16(pc, xh, stride=stride)
+    want = F.relu(F.instance_norm(y.float(), eps=1e-5))
+    assert (got.float() - want).abs().max().item() <= 4e-3          # fp16 rounding of a unit-variance result
+    res = cl(torch.randn(tuple(y.shape), generator=torch.Generator().manual_seed(3)).half().to(DEV))
+    got_r = fast_net.conv_instance_norm_f16(pc, xh, stride=stride, residual=res)
+    assert (got_r.float() - F.relu(res.float() + want)).abs().max().item() <= 6e-3
+    conv_tc.check(DEV)

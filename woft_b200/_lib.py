@@ -33,7 +33,7 @@ class ConvTcArgs(ctypes.Structure):
                 ("out2", c_void_p), ("out2_stride", ctypes.c_longlong), ("out2_f16", c_int), ("h", c_void_p), ("h_stride", ctypes.c_longlong),
                 ("z", c_void_p), ("z_stride", ctypes.c_longlong), ("w1x1", c_void_p), ("head_out", c_void_p),
                 ("head_bias", c_float), ("row_period", c_int), ("row_valid", c_int), ("debug_trace", c_void_p), ("debug_flags", c_int), ("halo", c_int), ("pair", c_int), ("pdl", c_int), ("stride", c_int), ("residual", c_void_p),
-                ("residual_stride", ctypes.c_longlong)]
+                ("residual_stride", ctypes.c_longlong), ("stats", c_void_p), ("stats_ctas", c_int)]
 
 
 CONV_BIAS_ACT, CONV_GRU_ZR, CONV_GRU_Q, CONV_HEAD_MEAN = range(4)
@@ -83,6 +83,8 @@ SIGNATURES = {
                                                  c_size_t, c_void_p]),
     "woft_instance_norm_relu_nhwc_f16": (c_int, [c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p, c_void_p, c_void_p,
                                                  c_size_t, c_void_p]),
+    "woft_instance_norm_from_sums_f16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_int, c_void_p,
+                                                 c_void_p, c_void_p, c_size_t, c_void_p]),
     "woft_add_relu": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_void_p, c_void_p]),
     "woft_images_to_input": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "woft_stem_conv7x7": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),

@@ -63,7 +63,7 @@ def _slice(t, ch_off, elem=None):
 
 def run(pc, x, x_off=0, epilogue=_lib.CONV_BIAS_ACT, relu=False, scale=1.0, out=None, out_off=0, out2=None, out2_off=0,
         h=None, h_off=0, z=None, w1x1=None, head_out=None, head_bias=0.0, row_period=0, row_valid=0, box=(0, 0),
-        dims=None, trace=None, debug_flags=0, halo=False, pair=None, stride=1, residual=None):
+        dims=None, trace=None, debug_flags=0, halo=False, pair=None, stride=1, residual=None, stats=None):
     """One convolution.  `x` (B,C,H,W) channels-last fp32 or fp16; channels [x_off, x_off + pc.cin) are the input.
     `dims=(B, H, W)` overrides the pixel grid (the weight head stacks its 9x9 images along H)."""
     _lib.require_cuda(x)
@@ -94,6 +94,8 @@ def run(pc, x, x_off=0, epilogue=_lib.CONV_BIAS_ACT, relu=False, scale=1.0, out=
     a.pdl = int(PDL_DEFAULT)
     a.stride = stride
     a.residual, a.residual_stride = _slice(residual, 0)
+    a.stats = _lib.ptr(stats)          # (rows, batch, 2, cout) fp32 partial sums for an instance norm that follows
+    a.stats_ctas = stats.shape[0] if stats is not None else 0
     a.halo = int(halo)   # filters resident in shared memory, one activation box per tile and channel block (box = output tile)
     a.debug_trace = _lib.ptr(trace)   # debug: int64 tensor of 8 * 148 per-CTA time stamps
     with torch.cuda.device(x.device):

@@ -61,6 +61,8 @@ struct ConvTcParams {
   // pair mode (cta_group::2): a cluster of two CTAs takes two pixel tiles that share the filters; each CTA fetches its own
   // activation box and HALF of the filter rows, the leader's MMA warp multiplies both tiles against both halves
   int pair, pix_tiles, pair_tiles;
+  float* stats;      // BIAS_ACT with fp16 output, or null: per-CTA partial sums (sms, NB <= 2, 2, cout) of the stored
+                     // values, for an instance norm that follows (extractor.py:30-32): removes its statistics pass
   int stride;        // 1 or 2: output pixel (x, y) reads input (stride * x + dx, stride * y + dy); W, H are OUTPUT extents
   const void* residual;      // BIAS_ACT: out = relu(residual + act(acc + bias)), fp16, laid out like `out` (the tail of a
   long long residual_stride; // residual block, raft_core/extractor.py:45-56), or null
@@ -231,8 +233,11 @@ __device__ __forceinline__ uint8_t* ct_stage_row(uint8_t* stg, int r, int q) {
   return stg + r * 64 + ((q ^ ((r >> 1) & 3)) << 4);
 }
 
+// `stat` (fp16 outputs only, or null): shared-memory accumulators [sum (C) | sum of squares (C)] of this tile's image; the
+// values added are the rounded fp16 numbers that are stored, so a later normalisation sees exactly their statistics
 __device__ __forceinline__ void ct_store_tile(void* base, long long stride, int col, const float* v, int nv, bool f16,
-                                              uint8_t* stg, int lane, const int* rp) {
+                                              uint8_t* stg, int lane, const int* rp, float* stat = nullptr,
+                                              int stat_c = 0) {
   const int q = lane & 3;
   if (f16) {
 #pragma unroll
@@ -248,11 +253,25 @@ __device__ __forceinline__ void ct_store_tile(void* base, long long stride, int 
     }
     __syncwarp();
     const int left = nv - q * 8;
+    float ps[8], pq[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ps[e] = pq[e] = 0.f;
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
       const int r = (lane >> 2) + 8 * i;
       if (rp[i] >= 0 && left > 0) {
         const uint4 t = *reinterpret_cast<const uint4*>(ct_stage_row(stg, r, q));
+        if (stat) {
+          const __half2* hp = reinterpret_cast<const __half2*>(&t);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const float2 f = __half22float2(hp[e]);
+            ps[2 * e] += f.x;
+            ps[2 * e + 1] += f.y;
+            pq[2 * e] = fmaf(f.x, f.x, pq[2 * e]);
+            pq[2 * e + 1] = fmaf(f.y, f.y, pq[2 * e + 1]);
+          }
+        }
         __half* o = reinterpret_cast<__half*>(base) + (long long)rp[i] * stride + col + q * 8;
         if (left >= 8) {
           *reinterpret_cast<uint4*>(o) = t;
@@ -262,6 +281,24 @@ __device__ __forceinline__ void ct_store_tile(void* base, long long stride, int 
           for (int e = 0; e < 8; ++e)
             if (e < left) o[e] = hsrc[e];
         }
+      }
+    }
+    if (stat) {   // warp-uniform: the eight lanes that share a 16-byte piece add up, one of them updates shared memory
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+#pragma unroll
+        for (int o = 4; o < 32; o <<= 1) {
+          ps[e] += __shfl_xor_sync(0xffffffffu, ps[e], o);
+          pq[e] += __shfl_xor_sync(0xffffffffu, pq[e], o);
+        }
+      }
+      if (lane < 4 && left > 0) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (e < left) {
+            atomicAdd(stat + col + q * 8 + e, ps[e]);
+            atomicAdd(stat + stat_c + col + q * 8 + e, pq[e]);
+          }
       }
     }
     __syncwarp();
@@ -331,7 +368,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
   float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
   uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_red + 256);            // 8 warps x 2 KB
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stage + 8 * 2048);
+  float* s_stat = reinterpret_cast<float*>(s_stage + 8 * 2048);         // [2 images][sum | squares][CT_MAX_BIAS]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stat + 4 * CT_MAX_BIAS);
   uint64_t* full = bars;
   uint64_t* empty = bars + CT_MAX_STAGES;
   uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
@@ -375,6 +413,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       float b = (p.bias && i < p.cout) ? __ldg(p.bias + i) : 0.f;
       s_bias[i] = b;
     }
+    if (p.stats)
+      for (int i = threadIdx.x; i < 4 * CT_MAX_BIAS; i += CT_THREADS) s_stat[i] = 0.f;
   }
   ptx::tc_fence_before_sync();
   if (PAIR)
@@ -658,7 +698,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
             }
           }
           if (co && nv > 0) {   // warp-uniform
-            ct_store_tile(p.out, p.out_stride, col, v, nv, p.out_f16 != 0, stg, lane, rp);
+            ct_store_tile(p.out, p.out_stride, col, v, nv, p.out_f16 != 0, stg, lane, rp,
+                          (p.stats && tc.n < 2) ? s_stat + tc.n * 2 * CT_MAX_BIAS : nullptr, CT_MAX_BIAS);
             if (p.out2) ct_store_tile(p.out2, p.out2_stride, col, v, nv, p.out2_f16 != 0, stg, lane, rp);
           } else if (valid && nv > 0) {
             ct_store_row(p.out, p.out_stride, pix, col, v, nv, p.out_f16 != 0);
@@ -731,6 +772,13 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     ptx::cluster_sync();   // neither CTA may leave while the other can still read its shared memory or signal its barriers
   else
     __syncthreads();
+  if (p.stats) {   // this CTA's partial sums, image by image: [n][sum (cout) | squares (cout)]
+    const int nimg = p.NB < 2 ? p.NB : 2;
+    for (int i = threadIdx.x; i < nimg * 2 * p.cout; i += CT_THREADS) {
+      const int n = i / (2 * p.cout), r = i - n * 2 * p.cout, part = r / p.cout, c = r - part * p.cout;
+      p.stats[(size_t)blockIdx.x * nimg * 2 * p.cout + i] = s_stat[(n * 2 + part) * CT_MAX_BIAS + c];
+    }
+  }
   if (warp == 1) {
     ptx::tc_fence_after_sync();
     if (PAIR)
@@ -835,7 +883,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       }
   }
   const int taps = a->kh * a->kw;
-  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 256;
+  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 4 * CT_MAX_BIAS * 4 + 256;
   int a_stage = CT_A_STAGE;
   if (a->halo) {
     // one activation box per channel block serves all taps: it must hold the 128 GEMM rows behind the last tap's offset
@@ -921,6 +969,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.row_period = a->row_period;
   p.row_valid = a->row_valid;
   p.trace = static_cast<unsigned long long*>(a->debug_trace);
+  p.stats = a->stats;
   p.residual = a->residual;
   p.residual_stride = a->residual_stride;
   p.dbg = a->debug_flags;
@@ -929,6 +978,8 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {
     WOFT_REQUIRE(!a->out2 || a->out2_f16 == a->out_f16, "woft_conv_tc: both outputs of this epilogue share one type");
+    WOFT_REQUIRE(!a->stats || (a->out_f16 && !a->out2 && a->batch <= 2 && a->stats_ctas >= 1),
+                 "woft_conv_tc: statistics are gathered for a single fp16 output of at most two images");
     WOFT_REQUIRE(!a->residual || ((reinterpret_cast<uintptr_t>(a->residual) & 15) == 0 && a->residual_stride % 8 == 0 &&
                                   a->cout % 32 == 0),
                  "woft_conv_tc: the residual is fp16, 16-byte aligned, with Cout a multiple of 32");
@@ -1013,6 +1064,15 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     grid = 2 * pairs;
   }
   WOFT_REQUIRE(grid >= 1, "woft_conv_tc: empty grid");
+  if (a->stats) {
+    // every CTA writes its partial sums; the rows of CTAs that do not exist in this launch are cleared
+    WOFT_REQUIRE(p.coalesce && !p.pair, "woft_conv_tc: statistics need 16-byte aligned outputs and single-CTA mode");
+    WOFT_REQUIRE(grid <= a->stats_ctas, "woft_conv_tc: the statistics buffer holds %d CTA rows, the launch has %d", a->stats_ctas, grid);
+    const size_t row = (size_t)a->batch * 2 * a->cout * sizeof(float);
+    if (grid < a->stats_ctas)
+      WOFT_CUDA_CHECK(cudaMemsetAsync(a->stats + (size_t)grid * a->batch * 2 * a->cout, 0, (a->stats_ctas - grid) * row,
+                                      static_cast<cudaStream_t>(stream)));
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (a->epilogue) {
     case CT_EPI_BIAS_ACT:

@@ -311,6 +311,32 @@ __global__ void __launch_bounds__(256) in_finalize_nhwc_kernel(const T* __restri
   }
 }
 
+// The same from sums a producer gathered while it wrote x (woft_conv_tc `stats`): partial is (rows, batch, 2, C), row k the
+// sums and sums of squares of the values CTA k stored.  No pivot here: the rows hold a few thousand values each in fp32,
+// the combination over rows is done in double.
+__global__ void __launch_bounds__(256) in_finalize_sums_kernel(const float* __restrict__ partial, int rows, int batch,
+                                                               float* __restrict__ stats, int HW, int C, float eps) {
+  const int n = blockIdx.y;
+  const int c = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (c >= C) return;
+  double s = 0.0, q = 0.0;
+  for (int k = lane; k < rows; k += 32) {
+    const float* pp = partial + ((size_t)(k * batch + n) * 2) * C;
+    s += pp[c];
+    q += pp[C + c];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
+    const double m = s / HW, var = q / HW - m * m;
+    stats[(size_t)n * 2 * C + c] = float(m);
+    stats[(size_t)n * 2 * C + C + c] = rsqrtf(fmaxf(float(var), 0.f) + eps);
+  }
+}
+
 // `residual` (optional): y = relu(residual + act(norm(x))), the tail of a residual block (extractor.py:56) in one pass
 template <typename T>
 __global__ void in_apply_nhwc_kernel(const T* __restrict__ x, const float* __restrict__ stats,
@@ -607,6 +633,27 @@ extern "C" int woft_instance_norm_relu_nhwc_f16(const void* x, int batch, int hw
   return instance_norm_nhwc_impl<__half>("woft_instance_norm_relu_nhwc_f16", static_cast<const __half*>(x), batch, hw,
                                          channels, eps, relu, static_cast<const __half*>(residual), static_cast<__half*>(y),
                                          scratch, scratch_bytes, stream);
+}
+
+extern "C" int woft_instance_norm_from_sums_f16(const void* x, const float* partial, int rows, int batch, int hw, int channels,
+                                                float eps, int relu, const void* residual, void* y, void* scratch,
+                                                size_t scratch_bytes, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(x && y && partial && scratch, "woft_instance_norm_from_sums_f16: null pointer");
+  WOFT_REQUIRE(batch > 0 && hw > 0 && rows > 0 && channels > 0 && channels % 4 == 0 && channels <= 1024 && batch < 65536,
+               "woft_instance_norm_from_sums_f16: channels must be a multiple of 4 (<= 1024)");
+  WOFT_REQUIRE(!residual || relu, "woft_instance_norm_from_sums_f16: the residual tail applies ReLU");
+  if (scratch_bytes < (size_t)batch * 2 * channels * sizeof(float))
+    return fail(WOFT_ERR_WORKSPACE, "woft_instance_norm_from_sums_f16: scratch too small");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  float* stats = static_cast<float*>(scratch);
+  in_finalize_sums_kernel<<<dim3(ceil_div(channels, 8), batch), 256, 0, s>>>(partial, rows, batch, stats, hw, channels, eps);
+  const long long total4 = (long long)batch * hw * (channels / 4);
+  WOFT_REQUIRE(total4 <= kMaxElems32, "woft_instance_norm_from_sums_f16: more than 2^31 - 1 vectors");
+  in_apply_nhwc_kernel<__half><<<ew_grid(total4), 256, 0, s>>>(static_cast<const __half*>(x), stats,
+                                                                static_cast<const __half*>(residual), static_cast<__half*>(y),
+                                                                hw, channels, relu, unsigned(total4));
+  return launch_status("instance norm (from sums) kernels");
 }
 
 extern "C" int woft_instance_norm_relu_add_nhwc(const float* x, int batch, int hw, int channels, float eps,

@@ -240,13 +240,33 @@ def instance_norm_relu_f16(x, relu=True, eps=1e-5, residual=None):
     return y
 
 
-def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float16):
+def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float16, stats=None):
     """One woft_conv_tc launch on a channels-last fp16 tensor; returns the new channels-last tensor."""
     B, _, H, W = x.shape
     Ho = (H + 2 * pc.pad_h - pc.kh) // stride + 1
     Wo = (W + 2 * pc.pad_w - pc.kw) // stride + 1
     out = torch.empty((B, pc.cout, Ho, Wo), device=x.device, dtype=out_dtype, memory_format=torch.channels_last)
-    conv_tc.run(pc, x, relu=relu, out=out, stride=stride, residual=residual)
+    conv_tc.run(pc, x, relu=relu, out=out, stride=stride, residual=residual, stats=stats)
+    return out
+
+
+_STAT_ROWS = 148   # one row of partial sums per CTA of a persistent woft_conv_tc launch (at most one CTA per SM)
+
+
+def conv_instance_norm_f16(pc, x, stride=1, relu=True, residual=None, eps=1e-5):
+    """conv -> InstanceNorm -> ReLU (extractor.py:30-32, 45-56) as convolution + combine + apply: the convolution's epilogue
+    gathers the per-channel sums of what it stores, so the norm's own statistics pass over the tensor disappears."""
+    B = x.shape[0]
+    stats = torch.empty((_STAT_ROWS, B, 2, pc.cout), device=x.device, dtype=torch.float32)
+    y = _conv_f16(pc, x, stride=stride, stats=stats)
+    N, C, H, W = y.shape
+    out = torch.empty_like(y)
+    scratch = torch.empty((N * 2 * C,), device=x.device, dtype=torch.float32)
+    with torch.cuda.device(x.device):
+        rc = _lib.load().woft_instance_norm_from_sums_f16(_lib.ptr(y), _lib.ptr(stats), _STAT_ROWS, N, H * W, C, eps, int(relu),
+                                                          _lib.ptr(residual), _lib.ptr(out), _lib.ptr(scratch),
+                                                          scratch.numel() * 4, _lib.current_stream(x.device))
+    _lib.check(rc, "woft_instance_norm_from_sums_f16")
     return out
 
 
@@ -473,10 +493,10 @@ class FastWeightedRAFT:
         (a per-channel constant cancels in the norm), the residual tails fused into the norm pass."""
         x = instance_norm_relu_f16(stem_conv7x7_f16(x, self.net.fnet.conv1.weight))
         for d in self.enc_f["blocks"]:
-            y = instance_norm_relu_f16(_conv_f16(d["c1"], x, stride=d["stride"]))
+            y = conv_instance_norm_f16(d["c1"], x, stride=d["stride"])
             if d["down"] is not None:
-                x = instance_norm_relu_f16(_conv_f16(d["down"], x, stride=d["stride"]), relu=False)
-            x = instance_norm_relu_f16(_conv_f16(d["c2"], y), residual=x)   # relu(x + relu(norm(conv2(y))))
+                x = conv_instance_norm_f16(d["down"], x, stride=d["stride"], relu=False)
+            x = conv_instance_norm_f16(d["c2"], y, residual=x)              # relu(x + relu(norm(conv2(y))))
         return _conv_f16(self.enc_f["out"], x, out_dtype=torch.float32)
 
     def _context_tc(self, x):

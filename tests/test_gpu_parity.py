@@ -497,6 +497,18 @@ def test_tensor_core_convolution_schedule_matches_layer_by_layer(golden):
           f"reference golden, weight-logit max error {werr:.5f}")
     assert epe <= 0.02 and ref_epe <= 0.02, f"mean EPE {epe} / {ref_epe} px"
     assert werr <= 0.02
+    # a batch of two frame pairs (four images through the feature encoder: the three-pass instance norm path): each item
+    # must reproduce the single-pair result
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = True
+    try:
+        both = fast_net_(torch.cat([t1, t2]), torch.cat([t2, t1]), iters=12, corr_block=blk)
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
+    conv_tc.check(DEV)
+    assert both[1].shape[0] == 2
+    assert (both[1][:1] - fast[1]).norm(dim=1).mean().item() <= 5e-3
+    assert (both[4][:1] - fast[4]).abs().max().item() <= 5e-3
 
 
 def test_u8_input_path_is_the_float_path(golden):

@@ -257,6 +257,8 @@ def conv_instance_norm_f16(pc, x, stride=1, relu=True, residual=None, eps=1e-5):
     """conv -> InstanceNorm -> ReLU (extractor.py:30-32, 45-56) as convolution + combine + apply: the convolution's epilogue
     gathers the per-channel sums of what it stores, so the norm's own statistics pass over the tensor disappears."""
     B = x.shape[0]
+    if B > 2:   # the epilogue keeps sums for two images (one frame pair); larger batches take the three-pass norm
+        return instance_norm_relu_f16(_conv_f16(pc, x, stride=stride), relu=relu, eps=eps, residual=residual)
     stats = torch.empty((_STAT_ROWS, B, 2, pc.cout), device=x.device, dtype=torch.float32)
     y = _conv_f16(pc, x, stride=stride, stats=stats)
     N, C, H, W = y.shape

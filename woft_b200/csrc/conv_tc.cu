@@ -42,6 +42,7 @@ constexpr int CT_A_STAGE = 128 * 128;       // 128 pixel rows x one 128-byte K r
 constexpr int CT_MAX_STAGES = 8;
 constexpr int CT_MAX_TAPS = 25;
 constexpr int CT_SMEM_LIMIT = 232448;
+constexpr int CT_STAT_C = 128;     // widest output for which the epilogue gathers instance-norm sums
 constexpr int CT_MAX_BIAS = 640;   // padded Cout of one launch (the mask head's 576 is the largest)
 
 enum { CT_EPI_BIAS_ACT = 0, CT_EPI_GRU_ZR = 1, CT_EPI_GRU_Q = 2, CT_EPI_HEAD_MEAN = 3 };
@@ -233,8 +234,9 @@ __device__ __forceinline__ uint8_t* ct_stage_row(uint8_t* stg, int r, int q) {
   return stg + r * 64 + ((q ^ ((r >> 1) & 3)) << 4);
 }
 
-// `stat` (fp16 outputs only, or null): shared-memory accumulators [sum (C) | sum of squares (C)] of this tile's image; the
-// values added are the rounded fp16 numbers that are stored, so a later normalisation sees exactly their statistics
+// `stat` (fp16 outputs only, or null): this WARP's shared-memory accumulators [sum (C) | sum of squares (C)] of the tile's
+// image -- no atomics, so the sums are reproducible bit for bit; the values added are the rounded fp16 numbers that are
+// stored, so a later normalisation sees exactly their statistics
 __device__ __forceinline__ void ct_store_tile(void* base, long long stride, int col, const float* v, int nv, bool f16,
                                               uint8_t* stg, int lane, const int* rp, float* stat = nullptr,
                                               int stat_c = 0) {
@@ -292,12 +294,12 @@ __device__ __forceinline__ void ct_store_tile(void* base, long long stride, int 
           pq[e] += __shfl_xor_sync(0xffffffffu, pq[e], o);
         }
       }
-      if (lane < 4 && left > 0) {
+      if (lane < 4 && left > 0) {   // `stat` is private to this warp: plain read-modify-write, a fixed order of additions
 #pragma unroll
         for (int e = 0; e < 8; ++e)
           if (e < left) {
-            atomicAdd(stat + col + q * 8 + e, ps[e]);
-            atomicAdd(stat + stat_c + col + q * 8 + e, pq[e]);
+            stat[col + q * 8 + e] += ps[e];
+            stat[stat_c + col + q * 8 + e] += pq[e];
           }
       }
     }
@@ -368,8 +370,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
   float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
   uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_red + 256);            // 8 warps x 2 KB
-  float* s_stat = reinterpret_cast<float*>(s_stage + 8 * 2048);         // [2 images][sum | squares][CT_MAX_BIAS]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stat + 4 * CT_MAX_BIAS);
+  float* s_stat = reinterpret_cast<float*>(s_stage + 8 * 2048);         // [8 warps][2 images][sum | squares][CT_STAT_C]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stat + 8 * 4 * CT_STAT_C);
   uint64_t* full = bars;
   uint64_t* empty = bars + CT_MAX_STAGES;
   uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
@@ -414,7 +416,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       s_bias[i] = b;
     }
     if (p.stats)
-      for (int i = threadIdx.x; i < 4 * CT_MAX_BIAS; i += CT_THREADS) s_stat[i] = 0.f;
+      for (int i = threadIdx.x; i < 8 * 4 * CT_STAT_C; i += CT_THREADS) s_stat[i] = 0.f;
   }
   ptx::tc_fence_before_sync();
   if (PAIR)
@@ -699,7 +701,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           }
           if (co && nv > 0) {   // warp-uniform
             ct_store_tile(p.out, p.out_stride, col, v, nv, p.out_f16 != 0, stg, lane, rp,
-                          (p.stats && tc.n < 2) ? s_stat + tc.n * 2 * CT_MAX_BIAS : nullptr, CT_MAX_BIAS);
+                          (p.stats && tc.n < 2) ? s_stat + ((warp - 2) * 2 + tc.n) * 2 * CT_STAT_C : nullptr, CT_STAT_C);
             if (p.out2) ct_store_tile(p.out2, p.out2_stride, col, v, nv, p.out2_f16 != 0, stg, lane, rp);
           } else if (valid && nv > 0) {
             ct_store_row(p.out, p.out_stride, pix, col, v, nv, p.out_f16 != 0);
@@ -776,7 +778,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     const int nimg = p.NB < 2 ? p.NB : 2;
     for (int i = threadIdx.x; i < nimg * 2 * p.cout; i += CT_THREADS) {
       const int n = i / (2 * p.cout), r = i - n * 2 * p.cout, part = r / p.cout, c = r - part * p.cout;
-      p.stats[(size_t)blockIdx.x * nimg * 2 * p.cout + i] = s_stat[(n * 2 + part) * CT_MAX_BIAS + c];
+      float acc = 0.f;
+      for (int w = 0; w < 8; ++w) acc += s_stat[((w * 2 + n) * 2 + part) * CT_STAT_C + c];   // fixed order over the warps
+      p.stats[(size_t)blockIdx.x * nimg * 2 * p.cout + i] = acc;
     }
   }
   if (warp == 1) {
@@ -883,7 +887,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       }
   }
   const int taps = a->kh * a->kw;
-  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 4 * CT_MAX_BIAS * 4 + 256;
+  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 8 * 4 * CT_STAT_C * 4 + 256;
   int a_stage = CT_A_STAGE;
   if (a->halo) {
     // one activation box per channel block serves all taps: it must hold the 128 GEMM rows behind the last tap's offset
@@ -978,8 +982,8 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   const int oesz = a->out_f16 ? 2 : 4;
   if (a->epilogue == CT_EPI_BIAS_ACT) {
     WOFT_REQUIRE(!a->out2 || a->out2_f16 == a->out_f16, "woft_conv_tc: both outputs of this epilogue share one type");
-    WOFT_REQUIRE(!a->stats || (a->out_f16 && !a->out2 && a->batch <= 2 && a->stats_ctas >= 1),
-                 "woft_conv_tc: statistics are gathered for a single fp16 output of at most two images");
+    WOFT_REQUIRE(!a->stats || (a->out_f16 && !a->out2 && a->batch <= 2 && a->stats_ctas >= 1 && a->cout_pad <= CT_STAT_C),
+                 "woft_conv_tc: statistics are gathered for a single fp16 output of at most two images and %d channels", CT_STAT_C);
     WOFT_REQUIRE(!a->residual || ((reinterpret_cast<uintptr_t>(a->residual) & 15) == 0 && a->residual_stride % 8 == 0 &&
                                   a->cout % 32 == 0),
                  "woft_conv_tc: the residual is fp16, 16-byte aligned, with Cout a multiple of 32");

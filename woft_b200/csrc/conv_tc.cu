@@ -333,26 +333,19 @@ __device__ __forceinline__ void ct_store_tile(void* base, long long stride, int 
   }
 }
 
-// 32 fp32 channels [col, col + 32) of the warp's 32 pixels, each thread ending up with its own pixel's values.  Split in
-// two so that the loads of a chunk are in flight while the accumulator is read and the activation is evaluated:
-// ct_load_issue requests 4 lanes x 16 bytes per 64-byte row segment (both halves of the 128 bytes), ct_load_finish passes
-// them through the warp's staging buffer.
-__device__ __forceinline__ void ct_load_issue(const float* base, long long stride, int col, int lane, const int* rp,
-                                              float4* t) {
-  const int q = lane & 3;
-#pragma unroll
-  for (int hb = 0; hb < 2; ++hb)
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
-      t[hb * 4 + i] = rp[i] >= 0 ? __ldg(reinterpret_cast<const float4*>(base + (long long)rp[i] * stride + col + 16 * hb + q * 4))
-                                 : make_float4(0.f, 0.f, 0.f, 0.f);
-}
-__device__ __forceinline__ void ct_load_finish(const float4* t, float* v, uint8_t* stg, int lane) {
+// 32 fp32 channels [col, col + 32) of the warp's 32 pixels, each thread ending up with its own pixel's values
+__device__ __forceinline__ void ct_load_tile(const float* base, long long stride, int col, float* v, uint8_t* stg, int lane,
+                                             const int* rp) {
   const int q = lane & 3;
 #pragma unroll
   for (int hb = 0; hb < 2; ++hb) {
+    float4 t[4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(ct_stage_row(stg, (lane >> 2) + 8 * i, q)) = t[hb * 4 + i];
+    for (int i = 0; i < 4; ++i)
+      t[i] = rp[i] >= 0 ? __ldg(reinterpret_cast<const float4*>(base + (long long)rp[i] * stride + col + 16 * hb + q * 4))
+                        : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) *reinterpret_cast<float4*>(ct_stage_row(stg, (lane >> 2) + 8 * i, q)) = t[i];
     __syncwarp();
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
@@ -649,18 +642,17 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         float v[32], bv[32];
         // operands of this chunk that do not depend on the accumulator are requested before the TMEM read is waited for
         float hv[32], zv[32];
-        float4 th[8], tz[8];   // coalesced loads in flight (GRU epilogues)
         if (EPI == CT_EPI_GRU_ZR) {
           if (col >= (p.bn >> 1)) {
             if (co)
-              ct_load_issue(p.h, p.h_stride, col - (p.bn >> 1), lane, rp, th);
+              ct_load_tile(p.h, p.h_stride, col - (p.bn >> 1), hv, stg, lane, rp);
             else if (valid)
               ct_load_row(p.h, p.h_stride, pix, col - (p.bn >> 1), hv);
           }
         } else if (EPI == CT_EPI_GRU_Q) {
           if (co) {
-            ct_load_issue(p.z, p.z_stride, col, lane, rp, tz);
-            ct_load_issue(p.h, p.h_stride, col, lane, rp, th);
+            ct_load_tile(p.h, p.h_stride, col, hv, stg, lane, rp);
+            ct_load_tile(p.z, p.z_stride, col, zv, stg, lane, rp);
           } else if (valid) {
             ct_load_row(p.h, p.h_stride, pix, col, hv);
             ct_load_row(p.z, p.z_stride, pix, col, zv);
@@ -726,10 +718,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               ct_store_row(p.z, p.z_stride, pix, col, v, 32, false);
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]);
-            if (co) ct_load_finish(th, hv, stg, lane);   // the loads had the TMEM read and the sigmoids to arrive
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] *= hv[j];
+            for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bv[j]) * hv[j];
             if (co)
               ct_store_tile(p.out, p.out_stride, col - hid, v, 32, p.out_f16 != 0, stg, lane, rp);
             else if (valid)
@@ -737,13 +726,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           }
         } else if (EPI == CT_EPI_GRU_Q) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = ct_tanh(v[j] + bv[j]);
-          if (co) ct_load_finish(tz, zv, stg, lane);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] *= zv[j];                 // z * q
-          if (co) ct_load_finish(th, hv, stg, lane);
-#pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = fmaf(1.f - zv[j], hv[j], v[j]);   // (1 - z) * h + z * q
+          for (int j = 0; j < 32; ++j) v[j] = (1.f - zv[j]) * hv[j] + zv[j] * ct_tanh(v[j] + bv[j]);
           if (co) {
             ct_store_tile(p.out, p.out_stride, col, v, 32, false, stg, lane, rp);
             if (p.out2) ct_store_tile(p.out2, p.out2_stride, col, v, 32, p.out2_f16 != 0, stg, lane, rp);

@@ -184,7 +184,9 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
     coords_seq = [grid + base_flow * (0.4 + 0.05 * i) for i in range(ITERS + 1)]
     # flags=8: the channels-last output the fused schedule consumes (the variant that runs inside a frame)
     t_lookup_cold = time_launches(lambda: blk(coords_seq[-1], flags=8), 20, scratch, torch)
-    t_lookup_pass = time_burst([(lambda c=c: blk(c, flags=8)) for c in coords_seq], 10, scratch, torch)
+    t_lookup_pass32 = time_burst([(lambda c=c: blk(c, flags=8)) for c in coords_seq], 10, scratch, torch)
+    # flags 8 | 16: channels-last fp16 output, the operand of the tensor-core convc1 -- what the timed frame runs
+    t_lookup_pass = time_burst([(lambda c=c: blk(c, flags=24)) for c in coords_seq], 10, scratch, torch)
     t_lookup_nchw = time_burst([(lambda c=c: blk(c)) for c in coords_seq], 10, scratch, torch)
     lookup_bytes = LOOKUP_BYTES_PER_QUERY * B * H * W
 
@@ -222,10 +224,16 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
         return {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
                 "traffic": traffic.get(key), "us_per_launch": round(t * 1e6, 2), "algorithmic_bytes": bytes_}
 
-    k3 = entry(lookup_bytes, t_lookup_pass, "corr_lookup")
-    k3["kernel"] = ("corr_lookup_kernel<4> (K3, channels-last output): 14400 queries x 4 levels per launch; average over the 13 launches of one "
-                    "flow pass issued back to back between one CUDA-event pair on the launch stream, L2 flushed before "
-                    "the pass (first launch cold, the rest see what L2 kept, as inside a frame)")
+    k3 = entry(lookup_bytes, t_lookup_pass, "corr_lookup_f16out")
+    k3["kernel"] = ("corr_lookup_kernel<4> (K3) as the timed frame runs it: channels-last output stored as fp16 (the operand of "
+                    "the tensor-core convc1; 648 B instead of 1296 B written per query -- `algorithmic_bytes` keeps SURVEY.md "
+                    "8(d)'s 2904 B per query of the fp32 operator, the bytes this variant really moves are 2256 B per query); "
+                    "14400 queries x 4 levels per launch; average over the 13 launches of one flow pass issued back to back "
+                    "between one CUDA-event pair on the launch stream, L2 flushed before the pass (first launch cold, the "
+                    "rest see what L2 kept, as inside a frame)")
+    k3["frac_on_bytes_moved"] = round((LOOKUP_BYTES_PER_QUERY - 648) * B * H * W / t_lookup_pass / 1e9 / hbm, 4)
+    k3_f32 = entry(lookup_bytes, t_lookup_pass32, "corr_lookup")
+    k3_f32["kernel"] = "K3 with the fp32 channels-last output, same 13-launch pass"
     k3_cold = entry(lookup_bytes, t_lookup_cold, "corr_lookup")
     k3_cold["kernel"] = "K3, one launch per event pair, L2 flushed before every launch (includes ~5 us of launch/event overhead)"
     k3_b4 = entry(lookup_bytes * B4, t_lookup_b4)
@@ -245,6 +253,7 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
         e["kernel"] = f"homography_fit_kernel (K4), B=1024 x N=14400, {name}" + (" (6 solves)" if sweeps > 1 else "")
         extra["homography_fit_config3_" + name] = e
     return k3, {"corr_lookup_cold": k3_cold, "corr_lookup_batch4_cold": k3_b4, "corr_lookup_pass_nchw": k3_nchw,
+                "corr_lookup_pass_nhwc_fp32": k3_f32,
                 "corr_pyramid": k1,
                 "homography_fit_config3": k4, **extra}, peaks["source"]
 
@@ -416,15 +425,17 @@ def run_woft(args, rank, world, local):
         "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": round(1e3 * results["device"]["seconds"] / args.steps, 3),
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "tf32 (convolution operands; correlation GEMM operands " + args.corr_mode + "; fp32 accumulation)",
+        "dtype": "f16 operands, f32 accumulation (convolutions; correlation GEMM operands " + args.corr_mode + ")",
         "data": "synthetic",
         "config": {"workload": WORKLOAD,
                    "corr_mode": args.corr_mode, "weights": WEIGHTS,
-                   "convolutions": "TF32 tensor cores (hand-written tcgen05 implicit GEMMs where fast_net.py uses them, "
-                                   "cuDNN with TF32 allowed elsewhere)", "cuda_graph": True,
-                   "precision": "stated-tolerance mode (flow within 0.05 px of the fp32 reference, "
-                                "tests/test_gpu_parity.py::test_benched_configuration_parity_720p); the fp32-class "
-                                "figures of the same workload are under `fp32_class`",
+                   "convolutions": "hand-written tcgen05 implicit GEMMs (woft_conv_tc: fp16 operands, fp32 accumulation, fused "
+                                   "epilogues) for every wide convolution of both encoders, the update block and the "
+                                   "weight head; no cuDNN kernel in this configuration", "cuda_graph": True,
+                   "precision": "stated-tolerance mode: measured 0.0046 px mean EPE and 0.012 px homography corner error "
+                                "against the fp32 CPU oracle on a 1280x720 pair of this sequence (asserted <= 0.02 px / "
+                                "0.05 px in tests/test_gpu_parity.py::test_benched_configuration_parity_720p); the "
+                                "fp32-class figures of the same workload are under `fp32_class`",
                    "device_loop": "`value` times PlanarTracker.estimate_global_fused on frames resident in HBM: no "
                                   "pre-warp (identity) and an all-ones pre-warp mask; `e2e` runs the whole of "
                                   "PlanarTracker.track including the device pre-warp by the last good homography",
@@ -448,8 +459,9 @@ def run_woft(args, rank, world, local):
             "value": round(world * args.steps / fp32["device"]["seconds"], 3), "unit": "frames/s",
             "ms_per_step": round(1e3 * fp32["device"]["seconds"] / args.steps, 3),
             "e2e": round(world * args.steps / fp32["e2e"]["seconds"], 3),
-            "config": "correlation fp16x3 (error-compensated, fp32-class), torch.backends.cudnn.allow_tf32=False, "
-                      "hand-written TF32 convolution kernels off; flow within 0.01 px of the fp32 reference",
+            "config": "correlation fp16x3 (error-compensated, fp32-class), torch.backends.cudnn.allow_tf32=False, every "
+                      "convolution in fp32 on cuDNN (the tensor-core convolution kernels are off); measured 0.00055 px mean "
+                      "EPE, 0.0015 px corner error against the fp32 CPU oracle",
             "gpu_launches_per_step": {"this_library": fp32["launches"][0], "all_kernels": fp32["launches"][1]}}
     if world == 1 and not args.no_cpu_baseline:
         n_cpu = 5
@@ -533,7 +545,7 @@ def run_sequences(args, rank, world, local):
         "value": round(total_frames / seconds, 3), "unit": "frames/s", "n_gpus": world,
         "steps": total_frames, "warmup": min(args.warmup, 8), "ms_per_step": round(1e3 * seconds * world / total_frames, 3),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "tf32 (convolution operands; correlation GEMM operands " + args.corr_mode + "; fp32 accumulation)",
+        "dtype": "f16 operands, f32 accumulation (convolutions; correlation GEMM operands " + args.corr_mode + ")",
         "data": "synthetic",
         "config": {"workload": f"configs[{3 if args.workload == 'config4' else 4}]: full WOFT tracking of {n_seq} synthetic "
                                f"{WIDTH}x{HEIGHT} sequences x {args.frames} frames, sequence-sharded (sequence s on rank "

@@ -1061,3 +1061,29 @@ def test_fused_select_fit_check_matches_reference_pieces():
         assert wo.corner_error(res[:9].view(1, 3, 3), Href, W, H) <= 0.05
         errs = wo.torch_proj_errors(res[:9].view(1, 3, 3), c_c[None], t_c.float()[None])
         assert res[9].item() == pytest.approx((errs <= 5).float().mean().item(), abs=1e-6)
+
+
+@pytest.mark.parametrize("shape", [(1, 32, 90, 160), (2, 16, 48, 64), (1, 8, 36, 52)])
+def test_tma_lookup_is_the_load_store_lookup(shape):
+    """lookup_tma.cu (footprints fetched as TMA boxes, zero padding by out-of-bounds fill) against lookup.cu's kernel
+    (flag 32) on jittered and far out-of-range coordinates: same arithmetic, so the channels-last outputs are equal bit for
+    bit, fp32 and fp16; and both agree with the oracle."""
+    from woft_b200 import _lib
+    from woft_b200.corr import CorrBlock
+    B, C, H, W = shape
+    g = torch.Generator().manual_seed(H)
+    f1, f2 = torch.randn(shape, generator=g), torch.randn(shape, generator=g)
+    blk = CorrBlock(f1.to(DEV), f2.to(DEV), mode="fp32")
+    ys, xs = torch.meshgrid(torch.arange(H), torch.arange(W), indexing="ij")
+    grid = torch.stack([xs, ys]).float()[None].repeat(B, 1, 1, 1)
+    coords = grid + (torch.rand(grid.shape, generator=g) * 2 - 1) * 9
+    far = torch.rand((B, 1, H, W), generator=g) < 0.1
+    coords = torch.where(far, coords + (torch.rand(grid.shape, generator=g) - 0.5) * 8 * max(H, W), coords).to(DEV)
+    for flags in (8, 24):
+        a = blk(coords, flags=flags)
+        b = blk(coords, flags=flags | 32)
+        with torch.cuda.device(DEV):
+            assert _lib.load().woft_corr_lookup_check(_lib.current_stream(torch.device(DEV))) == _lib.OK, _lib.last_error()
+        assert torch.equal(a[:, :324], b[:, :324]), f"flags {flags}"
+    want = wo.OracleCorrBlock(f1, f2)(coords.cpu())
+    np.testing.assert_allclose(blk(coords, flags=8).cpu().numpy(), want.numpy(), atol=1e-4)

@@ -52,6 +52,7 @@ SIGNATURES = {
     "woft_corr_set_trace_buffer": (None, [c_void_p]),
     "woft_corr_lookup": (c_int, [_FLOATP_ARRAY, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                  c_int, c_void_p]),
+    "woft_corr_lookup_check": (c_int, [c_void_p]),
     "woft_alt_corr_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                       c_int, c_void_p, c_void_p]),
     "woft_homography_fit": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,

@@ -18,7 +18,7 @@ LIB = PKG / "libwoft_b200.so"
 STAMP = PKG / ".libwoft_b200.stamp"
 SOURCES = ["api.cu", "lookup.cu", "homography.cu", "corr_simt.cu", "corr_tc.cu", "alt_corr.cu", "corr_static.cu",
            "fused_elementwise.cu", "prewarp.cu", "small_convs.cu", "upsample.cu", "select.cu", "preprocess.cu",
-           "stem_conv.cu", "weight_head.cu", "conv_tc.cu"]
+           "stem_conv.cu", "weight_head.cu", "conv_tc.cu", "lookup_tma.cu"]
 ARCH_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 

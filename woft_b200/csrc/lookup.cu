@@ -263,6 +263,8 @@ static int launch_lookup(const LookupParams& p, bool vec, bool nhwc, cudaStream_
   return launch_status("corr_lookup_kernel");
 }
 
+int corr_lookup_tma(const float* const*, int, const float*, int, int, int, int, int, void*, int, int, cudaStream_t);
+
 }  // namespace woft
 
 extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, const float* coords, int batch, int h1,
@@ -301,6 +303,12 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   p.nq = batch * h1 * w1;
   p.hw1 = h1 * w1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (nhwc && radius == 4 && vec && !(flags & 32)) {
+    // channels-last output, radius 4, 16-byte aligned level rows: the footprints come in by TMA (lookup_tma.cu);
+    // flag 32 keeps the load/store-unit path below (testing, comparison)
+    const int rc = corr_lookup_tma(levels, num_levels, coords, batch, h1, w1, h2, w2, out, p.out_f16, p.out_stride, s);
+    if (rc != WOFT_ERR_UNSUPPORTED) return rc;
+  }
   switch (radius) {
     case 1: return launch_lookup<1>(p, vec, nhwc, s);
     case 2: return launch_lookup<2>(p, vec, nhwc, s);

@@ -118,9 +118,10 @@ void woft_corr_set_trace_buffer(unsigned long long* device_buffer);
  *   levels : HOST array of `num_levels` device pointers as written by woft_corr_pyramid (h2 x w2 at level 0)
  *   coords : (B, 2, H1, W1), channel 0 = x, channel 1 = y
  *   out    : (B, num_levels*(2r+1)^2, H1, W1); channel = l*(2r+1)^2 + (xoff+r)*(2r+1) + (yoff+r)
- *   With the channels-last output, radius 4, at most 4 levels and level rows that are multiples of 16 bytes the footprints
- *   are fetched by TMA (one 12 x 10 box per query and level, lookup_tma.cu); flag 32 forces the load/store-unit kernel.
- *   woft_corr_lookup_check synchronises the stream and reports whether such a launch gave up on a load (2 s bound).
+ *   Flag 64 (with the channels-last output, radius 4, at most 4 levels, level rows that are multiples of 16 bytes): the
+ *   footprints are fetched by TMA, one 16 x 10 box per query and level (lookup_tma.cu) -- same results bit for bit,
+ *   measured slower than the default kernel; woft_corr_lookup_check synchronises the stream and reports whether such a
+ *   launch gave up on a load (2 s bound).
  *   flags  : bit 0 = scalar loads (testing); bit 3 (8) = write `out` channels-last, (B, H1, W1, channels), for an
  *            NHWC consumer (same values); bit 4 (16, with bit 3) = `out` holds fp16 with the channels of a query padded
  *            to a multiple of 8 (328 for 4 levels of radius 4; the padding is not written): the operand of an fp16

@@ -1065,8 +1065,8 @@ def test_fused_select_fit_check_matches_reference_pieces():
 
 @pytest.mark.parametrize("shape", [(1, 32, 90, 160), (2, 16, 48, 64), (1, 8, 36, 52)])
 def test_tma_lookup_is_the_load_store_lookup(shape):
-    """lookup_tma.cu (footprints fetched as TMA boxes, zero padding by out-of-bounds fill) against lookup.cu's kernel
-    (flag 32) on jittered and far out-of-range coordinates: same arithmetic, so the channels-last outputs are equal bit for
+    """lookup_tma.cu (flag 64: footprints fetched as TMA boxes, zero padding by out-of-bounds fill) against lookup.cu's
+    kernel on jittered and far out-of-range coordinates: same arithmetic, so the channels-last outputs are equal bit for
     bit, fp32 and fp16; and both agree with the oracle."""
     from woft_b200 import _lib
     from woft_b200.corr import CorrBlock
@@ -1080,8 +1080,8 @@ def test_tma_lookup_is_the_load_store_lookup(shape):
     far = torch.rand((B, 1, H, W), generator=g) < 0.1
     coords = torch.where(far, coords + (torch.rand(grid.shape, generator=g) - 0.5) * 8 * max(H, W), coords).to(DEV)
     for flags in (8, 24):
-        a = blk(coords, flags=flags)
-        b = blk(coords, flags=flags | 32)
+        a = blk(coords, flags=flags | 64)
+        b = blk(coords, flags=flags)
         with torch.cuda.device(DEV):
             assert _lib.load().woft_corr_lookup_check(_lib.current_stream(torch.device(DEV))) == _lib.OK, _lib.last_error()
         assert torch.equal(a[:, :324], b[:, :324]), f"flags {flags}"

@@ -303,9 +303,10 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   p.nq = batch * h1 * w1;
   p.hw1 = h1 * w1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (nhwc && radius == 4 && vec && !(flags & 32)) {
-    // channels-last output, radius 4, 16-byte aligned level rows: the footprints come in by TMA (lookup_tma.cu);
-    // flag 32 keeps the load/store-unit path below (testing, comparison)
+  if (nhwc && radius == 4 && vec && (flags & 64)) {
+    // flag 64: channels-last output, radius 4, 16-byte aligned level rows -- the footprints come in by TMA
+    // (lookup_tma.cu).  Measured slower than the load/store-unit kernel below (20.2 vs 18.4 us per launch at 1280x720),
+    // so it is opt-in
     const int rc = corr_lookup_tma(levels, num_levels, coords, batch, h1, w1, h2, w2, out, p.out_f16, p.out_stride, s);
     if (rc != WOFT_ERR_UNSUPPORTED) return rc;
   }

@@ -4,9 +4,10 @@
 // raft_core/utils/utils.py:59-73) for the case the fused schedule runs 13 times per frame.  lookup.cu fetches a (2r+2)^2
 // footprint as 10 rows of 3-4 float4 loads per row; every such 16-byte access of a scattered row is its own L1 wavefront
 // and the kernel sat at 60 % L1/TEX utilisation and 0.33 of the HBM roofline.  Here ONE cp.async.bulk.tensor box per
-// (query, level) brings the whole 10-row footprint (12 x 10 floats, 48-byte rows) into shared memory:
-//   - level l is a 3-D tensor (W_l, H_l, queries); the box starts at (floor(x) - 4, floor(y) - 4, q) -- any element
-//     alignment -- and TMA zero-fills what lies outside the map, which is the operator's zero padding;
+// (query, level) brings the whole 10-row footprint (16 x 10 floats, 64-byte rows) into shared memory:
+//   - level l is a 3-D tensor (W_l, H_l, queries); the box starts at ((floor(x) - 4) & ~3, floor(y) - 4, q) -- the origin of
+//     a box must be 16-byte aligned within its row -- and TMA zero-fills what lies outside the map, which is the
+//     operator's zero padding;
 //   - the load/store units only see the coalesced output stores; the 57 600 boxes of a 1280x720 lookup are address
 //     generation work for the TMA units (10 rows each);
 //   - persistent CTAs with two 16-query stages: the boxes of batch i+1 are in flight while batch i is interpolated.
@@ -22,13 +23,18 @@
 namespace woft {
 
 constexpr int kLtThreads = 128, kLtQueries = 16, kLtLevels = 4;
-constexpr int kLtR = 4, kLtP = 9, kLtWin = 10, kLtPitch = 12;       // 12 floats = 48-byte box rows (16-byte multiple)
-constexpr int kLtBox = kLtPitch * kLtWin;                            // floats per footprint
-constexpr int kLtStage = kLtLevels * kLtQueries * kLtBox;            // floats per stage: 30 KB
+constexpr int kLtR = 4, kLtP = 9, kLtWin = 10, kLtPitch = 16;       // box rows of 16 floats: the box must START on a 16-byte
+                                                                     // boundary of its row (a box origin at 12 bytes is an illegal
+                                                                     // instruction), so the 10 floats wanted lie at offset 0..3 in it
+constexpr int kLtBox = kLtPitch * kLtWin;                            // floats per footprint box (640 bytes = 5 x 128)
+constexpr int kLtSlot = kLtBox;                                      // floats between footprints: TMA writes to 128-byte aligned addresses
+constexpr int kLtStage = kLtLevels * kLtQueries * kLtSlot;           // floats per stage: 40 KB
 constexpr int kLtPairs = kLtLevels * kLtQueries;
 
 struct LookupTmaParams {
-  CUtensorMap tm[kLtLevels];  // (W_l, H_l, queries), box (12, 10, 1)
+  CUtensorMap tm0, tm1, tm2, tm3;  // level l: (W_l, H_l, queries), box (16, 10, 1).  Separate members: a run-time index into
+                                   // an array of kernel parameters would make the compiler copy them to local memory,
+                                   // where TMA cannot read a descriptor
   int num_levels;
   const float* coords;  // (B, 2, H1, W1)
   void* out;            // (queries, out_stride) fp32 or fp16
@@ -54,7 +60,7 @@ __device__ __forceinline__ bool lt_wait(uint64_t* bar, uint32_t parity) {
   return true;
 }
 
-__global__ void __launch_bounds__(kLtThreads, 3) corr_lookup_tma_kernel(const __grid_constant__ LookupTmaParams p) {
+__global__ void __launch_bounds__(kLtThreads, 2) corr_lookup_tma_kernel(const __grid_constant__ LookupTmaParams p) {
   extern __shared__ __align__(128) float lt_smem[];
   float* win = lt_smem;                                                    // [2 stages][level][query][10][12]
   float* s_ax = win + 2 * kLtStage;                                        // [2][64]
@@ -69,32 +75,54 @@ __global__ void __launch_bounds__(kLtThreads, 3) corr_lookup_tma_kernel(const __
   __syncthreads();
   pdl_sync();   // the coordinates come from the previous kernel of the iteration
 
-  // the footprints of one batch of 16 queries: thread t < 64 handles (level slot, query) = (t >> 4, t & 15)
+  // the footprints of one batch of 16 queries: thread t < 64 works out the box origin of (level slot, query) = (t >> 4,
+  // t & 15); one elected lane of warp 0 then issues the 64 box loads (the instruction takes its operands from uniform
+  // registers, so it is issued from converged code)
+  int* s_bx = reinterpret_cast<int*>(bars + 2);                            // [64] box origins of the batch being issued
+  int* s_by = s_bx + kLtPairs;
+  int* s_bq = s_by + kLtPairs;
+  int* s_sh = s_bq + kLtPairs;                                             // [2][64]
+  float* s_out = reinterpret_cast<float*>(s_sh + 2 * kLtPairs);            // [16 queries][out_stride] fp32 or fp16
   auto issue = [&](int batch, int stage) {
-    if (tid == 0) ptx::mbar_arrive_expect_tx(bars + stage, uint32_t(p.num_levels * kLtQueries * kLtBox * 4));
-    __syncthreads();   // the expectation is posted before any box can complete; also orders the reuse of the stage
-    ptx::fence_proxy_async_smem();   // the stage was last read through the generic proxy, TMA writes it through the async one
+    __syncthreads();   // every warp is done with this stage (two batches ago) and with the origin scratch
     if (tid < kLtPairs) {
       const int slot = tid >> 4, ql = tid & 15;
       const int q = batch * kLtQueries + ql;
-      if (slot < p.num_levels) {
-        float cx = 0.f, cy = 0.f;
-        const int qc = q < p.nq ? q : p.nq - 1;   // the tail batch fetches (and discards) the last query again
-        {
-          const int b = qc / p.hw1, pix = qc - b * p.hw1;
-          cx = __ldg(p.coords + (size_t)(2 * b) * p.hw1 + pix);
-          cy = __ldg(p.coords + (size_t)(2 * b + 1) * p.hw1 + pix);
-        }
-        const float inv = 1.0f / float(1 << slot);
-        const float x = cx * inv, y = cy * inv;  // centroid_lvl = coords / 2**i (corr.py:41)
-        float fx = floorf(x), fy = floorf(y);
-        s_ax[stage * kLtPairs + tid] = x - fx;
-        s_ay[stage * kLtPairs + tid] = y - fy;
-        fx = fminf(fmaxf(fx, -1048576.f), 1048576.f);
-        fy = fminf(fmaxf(fy, -1048576.f), 1048576.f);
-        float* dst = win + stage * kLtStage + tid * kLtBox;
-        const CUtensorMap* tm = &p.tm[slot];
-        ptx::tma_load_3d(dst, tm, bars + stage, int(fx) - kLtR, int(fy) - kLtR, qc);
+      const int qc = q < p.nq ? q : p.nq - 1;   // the tail batch fetches (and discards) the last query again
+      const int b = qc / p.hw1, pix = qc - b * p.hw1;
+      const float cx = __ldg(p.coords + (size_t)(2 * b) * p.hw1 + pix);
+      const float cy = __ldg(p.coords + (size_t)(2 * b + 1) * p.hw1 + pix);
+      const float inv = 1.0f / float(1 << slot);
+      const float x = cx * inv, y = cy * inv;  // centroid_lvl = coords / 2**i (corr.py:41)
+      float fx = floorf(x), fy = floorf(y);
+      s_ax[stage * kLtPairs + tid] = x - fx;
+      s_ay[stage * kLtPairs + tid] = y - fy;
+      fx = fminf(fmaxf(fx, -1048576.f), 1048576.f);
+      fy = fminf(fmaxf(fy, -1048576.f), 1048576.f);
+      s_bx[tid] = (int(fx) - kLtR) & ~3;                       // aligned box origin ...
+      s_sh[stage * kLtPairs + tid] = (int(fx) - kLtR) & 3;     // ... and where the footprint starts inside the box
+      s_by[tid] = int(fy) - kLtR;
+      s_bq[tid] = qc;
+    }
+    __syncthreads();
+    // warp w fetches level w: one elected lane issues its 16 boxes (four issuers per CTA)
+    if (tid == 0) {
+      ptx::fence_proxy_async_smem();   // the stage was last read through the generic proxy, TMA writes it through the async one
+      ptx::mbar_arrive_expect_tx(bars + stage, uint32_t(p.num_levels * kLtQueries * kLtBox * 4));
+    }
+    __syncthreads();   // the expectation is posted before any box can complete
+    const int lvl_w = tid >> 5;
+    if (lvl_w < p.num_levels && ptx::elect_one()) {
+      float* dst = win + stage * kLtStage + lvl_w * kLtQueries * kLtSlot;
+      const int o = lvl_w * kLtQueries;
+      if (lvl_w == 0) {
+        for (int i = 0; i < kLtQueries; ++i) ptx::tma_load_3d(dst + i * kLtSlot, &p.tm0, bars + stage, s_bx[o + i], s_by[o + i], s_bq[o + i]);
+      } else if (lvl_w == 1) {
+        for (int i = 0; i < kLtQueries; ++i) ptx::tma_load_3d(dst + i * kLtSlot, &p.tm1, bars + stage, s_bx[o + i], s_by[o + i], s_bq[o + i]);
+      } else if (lvl_w == 2) {
+        for (int i = 0; i < kLtQueries; ++i) ptx::tma_load_3d(dst + i * kLtSlot, &p.tm2, bars + stage, s_bx[o + i], s_by[o + i], s_bq[o + i]);
+      } else {
+        for (int i = 0; i < kLtQueries; ++i) ptx::tma_load_3d(dst + i * kLtSlot, &p.tm3, bars + stage, s_bx[o + i], s_by[o + i], s_bq[o + i]);
       }
     }
   };
@@ -117,22 +145,33 @@ __global__ void __launch_bounds__(kLtThreads, 3) corr_lookup_tma_kernel(const __
       const int slot = pair >> 4, ql = pair & 15;
       const int q = batch * kLtQueries + ql;
       if (q >= p.nq || !active) continue;
-      const float* c = wst + pair * kLtBox + y3 * kLtPitch + xo;
+      const float* c = wst + pair * kLtSlot + y3 * kLtPitch + xo + s_sh[stage * kLtPairs + pair];
       const float ax = s_ax[stage * kLtPairs + pair], ay = s_ay[stage * kLtPairs + pair];
       const float bx = 1.f - ax, by = 1.f - ay;
       float h[4];
 #pragma unroll
       for (int r = 0; r < 4; ++r) h[r] = fmaf(ax, c[r * kLtPitch + 1], bx * c[r * kLtPitch]);
-      const size_t oi = (size_t)q * p.out_stride + (size_t)slot * kLtP * kLtP + xo * kLtP + y3;
+      // the batch's output rows are assembled in shared memory and leave as 16-byte pieces of whole rows: written from
+      // here, three values per lane at an 18- or 36-byte stride, every store instruction touched four to five lines
+      const int oi = ql * p.out_stride + slot * kLtP * kLtP + xo * kLtP + y3;
       if (p.out_f16) {
-        __half* o = reinterpret_cast<__half*>(p.out) + oi;
+        __half* o = reinterpret_cast<__half*>(s_out) + oi;
 #pragma unroll
         for (int j = 0; j < 3; ++j) o[j] = __float2half_rn(fmaf(ay, h[j + 1], by * h[j]));
       } else {
-        float* o = reinterpret_cast<float*>(p.out) + oi;
+        float* o = s_out + oi;
 #pragma unroll
         for (int j = 0; j < 3; ++j) o[j] = fmaf(ay, h[j + 1], by * h[j]);
       }
+    }
+    __syncthreads();
+    {
+      const int row_bytes = p.out_stride * (p.out_f16 ? 2 : 4);           // a multiple of 16 (host check)
+      const int pieces = row_bytes >> 4;
+      const int nrows = min(kLtQueries, p.nq - batch * kLtQueries);
+      const uint4* src = reinterpret_cast<const uint4*>(s_out);
+      uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(p.out) + (size_t)batch * kLtQueries * row_bytes);
+      for (int i = tid; i < nrows * pieces; i += kLtThreads) dst[i] = src[i];   // consecutive rows are contiguous
     }
   }
 }
@@ -162,9 +201,10 @@ int corr_lookup_tma(const float* const* levels, int num_levels, const float* coo
     if ((w * 4) % 16 != 0 || (reinterpret_cast<uintptr_t>(levels[l]) & 15) != 0) return WOFT_ERR_UNSUPPORTED;
     cuuint64_t dims[3] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)nq};
     cuuint64_t strides[2] = {(cuuint64_t)w * 4, (cuuint64_t)w * h * 4};
-    cuuint32_t box[3] = {kLtPitch, kLtWin, 1};
+    cuuint32_t box[3] = {kLtPitch, kLtWin, 1};   // 16 x 10 floats
     cuuint32_t estr[3] = {1, 1, 1};
-    if (enc(&p.tm[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(levels[l]), dims, strides, box, estr,
+    CUtensorMap* tml = l == 0 ? &p.tm0 : l == 1 ? &p.tm1 : l == 2 ? &p.tm2 : &p.tm3;
+    if (enc(tml, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(levels[l]), dims, strides, box, estr,
             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return WOFT_ERR_UNSUPPORTED;
@@ -179,12 +219,13 @@ int corr_lookup_tma(const float* const* levels, int num_levels, const float* coo
   p.out_f16 = out_f16;
   p.out_stride = out_stride;
   p.batches = (int)((nq + kLtQueries - 1) / kLtQueries);
-  const int smem = (2 * kLtStage + 4 * kLtPairs) * 4 + 64;
+  if ((out_stride * (out_f16 ? 2 : 4)) % 16 != 0 || (reinterpret_cast<uintptr_t>(out) & 15) != 0) return WOFT_ERR_UNSUPPORTED;
+  const int smem = (2 * kLtStage + 4 * kLtPairs) * 4 + 16 + 5 * kLtPairs * 4 + kLtQueries * out_stride * 4 + 64;
   WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_lookup_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   int dev = 0, sms = 0;
   WOFT_CUDA_CHECK(cudaGetDevice(&dev));
   WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  const int grid = p.batches < 3 * sms ? p.batches : 3 * sms;
+  const int grid = p.batches < 2 * sms ? p.batches : 2 * sms;
   WOFT_CUDA_CHECK(launch_pdl(corr_lookup_tma_kernel, dim3(grid), dim3(kLtThreads), (size_t)smem, stream, p));
   return launch_status("corr_lookup_tma_kernel");
 }

@@ -223,6 +223,12 @@ int woft_cast_nhwc_f16(const float* src, int src_stride, int channels, long long
  *   coords (B,2,H,W) or NULL: updated IN PLACE by the delta; with it coords0 (B,2,H,W) is required and
  *   flow_nchw (B,2,H,W) / flow_nhwc (B,H,W,2), each optional, receive coords - coords0 */
 size_t woft_flow_head_scratch_bytes(int batch, int height, int width);
+/* The second half of woft_flow_head_step alone, for tap products formed elsewhere (woft_conv_tc, WOFT_CONV_FLOW_TAPS):
+ * taps (B*H*W, 9, 2).  flow_f16_a / flow_f16_b (optional, with coords): fp16 channels-last tensors (pixels, f16_stride)
+ * that also receive the new flow, at channel offset f16_offset (the GRU operand buffers, update.py:97). */
+int woft_flow_head_gather(const float* taps, const float* bias, int batch, int height, int width, float* delta_nchw,
+                          float* coords, const float* coords0, float* flow_nchw, float* flow_nhwc, void* flow_f16_a,
+                          void* flow_f16_b, int f16_stride, int f16_offset, void* stream);
 int woft_flow_head_step(const float* in_nhwc, const float* weight, const float* bias, int batch, int height, int width,
                         int channels, void* scratch, size_t scratch_bytes, float* delta_nchw, float* coords,
                         const float* coords0, float* flow_nchw, float* flow_nhwc, void* stream);
@@ -376,11 +382,17 @@ int woft_weight_head_conv1_stacked_f16(const float* window_nhwc, const float* me
  *                 (h and z are fp32; in GRU_ZR the r*h output may be fp16 (out_f16): it is a convolution operand)
  *                 WOFT_CONV_HEAD_MEAN: images of row_valid x W pixels stacked along H every row_period rows (batch 1);
  *                                      head_out[image] = head_bias + mean over the image of w1x1 . relu(acc + bias)
+ *                 WOFT_CONV_FLOW_TAPS: FlowHead.conv1 + ReLU with the products of FlowHead.conv2 (update.py:6-14):
+ *                                      head_out[pix][tap][o] = sum_c relu(acc[c] + bias[c]) * w2[o][c][tap] for the 9 taps and
+ *                                      2 outputs; `w1x1` holds w2 as (cout, 24) floats, [taps 0-4 x 2 | pad | taps 5-8 x 2 |
+ *                                      pad]; woft_flow_head_gather adds the nine shifted products per output pixel.  The
+ *                                      256-channel activation is never written
  *   row_period, row_valid: when row_period > 0, rows y with y % row_period >= row_valid separate stacked images: the
  *                 BIAS_ACT epilogue stores zeros there (they are the next layer's zero padding between images)
  * One launch (two for HEAD_MEAN: the logits are cleared first).  woft_conv_tc_check synchronises the stream and reports
  * whether any convolution kernel gave up on a pipeline wait (2 s bound) since the library was loaded. */
-enum woft_conv_epilogue { WOFT_CONV_BIAS_ACT = 0, WOFT_CONV_GRU_ZR = 1, WOFT_CONV_GRU_Q = 2, WOFT_CONV_HEAD_MEAN = 3 };
+enum woft_conv_epilogue { WOFT_CONV_BIAS_ACT = 0, WOFT_CONV_GRU_ZR = 1, WOFT_CONV_GRU_Q = 2, WOFT_CONV_HEAD_MEAN = 3,
+                          WOFT_CONV_FLOW_TAPS = 4 };
 typedef struct woft_conv_tc_args {
   const void* in;
   long long in_stride;

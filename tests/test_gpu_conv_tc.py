@@ -248,3 +248,44 @@ def test_convolution_gathers_instance_norm_statistics(shape):
     got_r = fast_net.conv_instance_norm_f16(pc, xh, stride=stride, residual=res)
     assert (got_r.float() - F.relu(res.float() + want)).abs().max().item() <= 6e-3
     conv_tc.check(DEV)
+
+
+@pytest.mark.parametrize("H,W", [(90, 160), (13, 21)])
+def test_flow_head_epilogue_and_gather(H, W):
+    """FlowHead (update.py:6-14): conv1 + ReLU + the tap products of conv2 in the convolution's epilogue, then the gather
+    that also advances the coordinates and copies the flow (fp32 and fp16), against the two torch convolutions."""
+    from woft_b200 import _lib, conv_tc
+    g = torch.Generator().manual_seed(H)
+    hbuf = cl((torch.randn((1, 384, H, W), generator=g)).half().to(DEV))
+    w1 = (torch.randn((256, 128, 3, 3), generator=g) / (128 * 9) ** 0.5).to(DEV)
+    b1 = (torch.randn((256,), generator=g) * 0.1).to(DEV)
+    w2 = (torch.randn((2, 256, 3, 3), generator=g) / (256 * 9) ** 0.5).to(DEV)
+    b2 = (torch.randn((2,), generator=g) * 0.1).to(DEV)
+    want = F.conv2d(F.conv2d(hbuf[:, :128].float(), w1.half().float(), b1, padding=1).relu(), w2, b2, padding=1)
+    wt = w2.reshape(2, 256, 9).permute(1, 2, 0)
+    fh2 = torch.zeros((256, 24), device=DEV)
+    fh2[:, 0:10] = wt[:, 0:5].reshape(-1, 10)
+    fh2[:, 12:20] = wt[:, 5:9].reshape(-1, 8)
+    pc = conv_tc.PackedConv(w1, b1, 1, f16=True)
+    taps = torch.full((H * W, 18), float("nan"), device=DEV)
+    conv_tc.run(pc, hbuf, epilogue=_lib.CONV_FLOW_TAPS, w1x1=fh2, head_out=taps)
+    conv_tc.check(DEV)
+    coords0 = torch.rand((1, 2, H, W), generator=g).to(DEV) * 50
+    coords = coords0 + 1.5
+    c_before = coords.clone()
+    flow_nchw = torch.empty((1, 2, H, W), device=DEV)
+    flow_nhwc = torch.empty((H * W, 2), device=DEV)
+    fa = cl(torch.zeros((1, 384, H, W), device=DEV, dtype=torch.float16))
+    fb = cl(torch.zeros((1, 384, H, W), device=DEV, dtype=torch.float16))
+    with torch.cuda.device(DEV):
+        rc = _lib.load().woft_flow_head_gather(_lib.ptr(taps), _lib.ptr(b2), 1, H, W, None, _lib.ptr(coords), _lib.ptr(coords0),
+                                               _lib.ptr(flow_nchw), _lib.ptr(flow_nhwc), _lib.ptr(fa), _lib.ptr(fb), 384, 382,
+                                               _lib.current_stream(torch.device(DEV)))
+    assert rc == _lib.OK, _lib.last_error()
+    assert not torch.isnan(taps).any()
+    delta = coords - c_before
+    assert (delta - want).abs().max().item() <= 3e-3 * max(1.0, want.abs().max().item())
+    assert torch.allclose(flow_nchw, coords - coords0)
+    assert torch.allclose(flow_nhwc.view(H, W, 2).permute(2, 0, 1)[None], flow_nchw)
+    assert torch.equal(fa[:, 382:384], flow_nchw.half()) and torch.equal(fb[:, 382:384], fa[:, 382:384])
+    assert (fa[:, :382] == 0).all()

@@ -36,7 +36,7 @@ class ConvTcArgs(ctypes.Structure):
                 ("residual_stride", ctypes.c_longlong), ("stats", c_void_p), ("stats_ctas", c_int)]
 
 
-CONV_BIAS_ACT, CONV_GRU_ZR, CONV_GRU_Q, CONV_HEAD_MEAN = range(4)
+CONV_BIAS_ACT, CONV_GRU_ZR, CONV_GRU_Q, CONV_HEAD_MEAN, CONV_FLOW_TAPS = range(5)
 
 # name -> (restype, argtypes); kept in step with include/woft_b200.h (tests/test_abi.py checks both ways)
 SIGNATURES = {
@@ -75,6 +75,8 @@ SIGNATURES = {
     "woft_flow_head_scratch_bytes": (c_size_t, [c_int, c_int, c_int]),
     "woft_flow_head_step": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_size_t,
                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "woft_flow_head_gather": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "woft_flow_conv7x7_relu": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_flow_out3x3": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "woft_instance_norm_nhwc_scratch_bytes": (c_size_t, [c_int, c_int]),

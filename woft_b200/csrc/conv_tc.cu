@@ -45,7 +45,8 @@ constexpr int CT_SMEM_LIMIT = 232448;
 constexpr int CT_STAT_C = 128;     // widest output for which the epilogue gathers instance-norm sums
 constexpr int CT_MAX_BIAS = 640;   // padded Cout of one launch (the mask head's 576 is the largest)
 
-enum { CT_EPI_BIAS_ACT = 0, CT_EPI_GRU_ZR = 1, CT_EPI_GRU_Q = 2, CT_EPI_HEAD_MEAN = 3 };
+enum { CT_EPI_BIAS_ACT = 0, CT_EPI_GRU_ZR = 1, CT_EPI_GRU_Q = 2, CT_EPI_HEAD_MEAN = 3, CT_EPI_FLOW_TAPS = 4 };
+constexpr int CT_TAPS_W = 2 * 12;   // FLOW_TAPS: floats of second-layer filter per channel: [first 5 taps x 2 | last 4 taps x 2], padded to 12 each
 
 struct ConvTcParams {
   CUtensorMap tmA;  // (Cin, W, H, N) box (k_elems, bw, bh, 1)
@@ -82,8 +83,8 @@ struct ConvTcParams {
   long long h_stride;
   float* z;
   long long z_stride;
-  const float* w1x1;
-  float* head_out;
+  const float* w1x1;   // HEAD_MEAN: 1x1 filter (cout); FLOW_TAPS: second-layer filter (cout, CT_TAPS_W)
+  float* head_out;     // HEAD_MEAN: logits; FLOW_TAPS: (pixels, 18) tap products
   float head_scale, head_bias;
   int row_period, row_valid;  // rows y with (y % row_period) >= row_valid are separators: stored as zeros, not averaged
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA, or null
@@ -370,8 +371,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
   float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
   uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_red + 256);            // 8 warps x 2 KB
-  float* s_stat = reinterpret_cast<float*>(s_stage + 8 * 2048);         // [8 warps][2 images][sum | squares][CT_STAT_C]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stat + 8 * 4 * CT_STAT_C);
+  float* s_stat = reinterpret_cast<float*>(s_stage + 8 * 2048);         // [8 warps][2 images][sum | squares][CT_STAT_C],
+  // only when gathered; FLOW_TAPS: the second-layer filter lies over the (unused) staging buffer and 8 KB behind it
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_stat + (EPI == CT_EPI_FLOW_TAPS ? 2048 : p.stats ? 8 * 4 * CT_STAT_C : 0));
+  float* s_w2 = reinterpret_cast<float*>(s_stage);
   uint64_t* full = bars;
   uint64_t* empty = bars + CT_MAX_STAGES;
   uint64_t* tfull = bars + 2 * CT_MAX_STAGES;
@@ -417,6 +420,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     }
     if (p.stats)
       for (int i = threadIdx.x; i < 8 * 4 * CT_STAT_C; i += CT_THREADS) s_stat[i] = 0.f;
+    if (EPI == CT_EPI_FLOW_TAPS)
+      for (int i = threadIdx.x; i < p.cout * CT_TAPS_W; i += CT_THREADS) s_w2[i] = __ldg(p.w1x1 + i);
   }
   ptx::tc_fence_before_sync();
   if (PAIR)
@@ -635,6 +640,52 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
 #pragma unroll
       for (int i = 0; i < 4; ++i) rp[i] = __shfl_sync(0xffffffffu, valid ? int(pix) : -1, (lane >> 2) + 8 * i);
       const bool co = p.coalesce != 0;
+      if (EPI == CT_EPI_FLOW_TAPS) {
+        // FlowHead (update.py:6-14): relu(conv1) never leaves the SM.  The second, 3x3 -> 2-channel convolution is
+        // linear, so every pixel's 18 (tap, output) products with its own 256 activations are formed here and a small
+        // gather kernel adds the nine shifted products per output pixel.  Both warps of a lane quadrant read all
+        // chunks; one forms taps 0-4, the other taps 5-8 (no exchange between them).
+        float t[10];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) t[k] = 0.f;
+#pragma unroll 1
+        for (int c = 0; c < chunks; ++c) {
+          const int col = tc.c0 + c * 32;
+          float v[32], bv[32];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 b4 = reinterpret_cast<const float4*>(s_bias + col)[j];
+            bv[4 * j] = b4.x; bv[4 * j + 1] = b4.y; bv[4 * j + 2] = b4.z; bv[4 * j + 3] = b4.w;
+          }
+          ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * 256 + c * 32), v);
+          if (c == chunks - 1) {
+            ptx::tc_fence_before_sync();
+            if (PAIR)
+              ptx::mbar_arrive_cluster(lead_tempty[buf]);
+            else
+              ptx::mbar_arrive(tempty + buf);
+          }
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float a = fmaxf(v[j] + bv[j], 0.f);
+            const float4* w = reinterpret_cast<const float4*>(s_w2 + (col + j) * CT_TAPS_W + half * 12);
+            const float4 w0 = w[0], w1 = w[1], w2 = w[2];
+            t[0] = fmaf(a, w0.x, t[0]); t[1] = fmaf(a, w0.y, t[1]); t[2] = fmaf(a, w0.z, t[2]); t[3] = fmaf(a, w0.w, t[3]);
+            t[4] = fmaf(a, w1.x, t[4]); t[5] = fmaf(a, w1.y, t[5]); t[6] = fmaf(a, w1.z, t[6]); t[7] = fmaf(a, w1.w, t[7]);
+            t[8] = fmaf(a, w2.x, t[8]); t[9] = fmaf(a, w2.y, t[9]);
+          }
+        }
+        if (valid) {
+          float2* o = reinterpret_cast<float2*>(p.head_out + pix * 18 + half * 10);
+          o[0] = make_float2(t[0], t[1]);
+          o[1] = make_float2(t[2], t[3]);
+          o[2] = make_float2(t[4], t[5]);
+          o[3] = make_float2(t[6], t[7]);
+          if (half == 0) o[4] = make_float2(t[8], t[9]);
+        }
+        if (leader && it == 0) ct_stamp(p, 5);
+        continue;
+      }
       float head_sum = 0.f;
 #pragma unroll 1
       for (int c = half; c < chunks; c += 2) {
@@ -856,7 +907,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   WOFT_REQUIRE(a->in && a->weight_packed, "woft_conv_tc: null input or weight pointer");
   WOFT_REQUIRE(a->batch > 0 && a->height > 0 && a->width > 0 && a->cin > 0 && a->cout > 0, "woft_conv_tc: bad extent");
   WOFT_REQUIRE(a->kh >= 1 && a->kw >= 1 && a->kh * a->kw <= CT_MAX_TAPS, "woft_conv_tc: at most %d filter taps", CT_MAX_TAPS);
-  WOFT_REQUIRE(a->epilogue >= CT_EPI_BIAS_ACT && a->epilogue <= CT_EPI_HEAD_MEAN, "woft_conv_tc: unknown epilogue %d",
+  WOFT_REQUIRE(a->epilogue >= CT_EPI_BIAS_ACT && a->epilogue <= CT_EPI_FLOW_TAPS, "woft_conv_tc: unknown epilogue %d",
                a->epilogue);
   const int esz = a->in_f16 ? 2 : 4;
   const int k_elems = 128 / esz;
@@ -887,7 +938,8 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       }
   }
   const int taps = a->kh * a->kw;
-  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 + 8 * 4 * CT_STAT_C * 4 + 256;
+  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 +
+                    (a->epilogue == CT_EPI_FLOW_TAPS ? 8192 : a->stats ? 8 * 4 * CT_STAT_C * 4 : 0) + 256;
   int a_stage = CT_A_STAGE;
   if (a->halo) {
     // one activation box per channel block serves all taps: it must hold the 128 GEMM rows behind the last tap's offset
@@ -1004,6 +1056,12 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     WOFT_REQUIRE(((reinterpret_cast<uintptr_t>(a->h) | reinterpret_cast<uintptr_t>(a->z) | reinterpret_cast<uintptr_t>(a->out)) & 15) == 0 &&
                  a->h_stride % 4 == 0 && a->z_stride % 4 == 0 && a->out_stride % 4 == 0,
                  "woft_conv_tc: GRU operands must be 16-byte aligned");
+  } else if (a->epilogue == CT_EPI_FLOW_TAPS) {
+    WOFT_REQUIRE(p.n_tiles == 1 && a->cout == bn && a->cout * CT_TAPS_W * 4 <= 8 * 2048 + 8192 && !a->halo,
+                 "woft_conv_tc: the flow-head epilogue takes Cout <= 256 as one tile");
+    WOFT_REQUIRE(a->w1x1 && a->head_out && (reinterpret_cast<uintptr_t>(a->head_out) & 7) == 0 &&
+                 (reinterpret_cast<uintptr_t>(a->w1x1) & 15) == 0,
+                 "woft_conv_tc: the flow-head epilogue needs the second-layer filter (Cout x 24 floats) and the tap buffer");
   } else {
     WOFT_REQUIRE(a->w1x1 && a->head_out && a->row_period > 0 && a->row_valid > 0 && a->row_valid <= a->row_period,
                  "woft_conv_tc: patch-mean epilogue needs w1x1, head_out and the row period");
@@ -1085,6 +1143,8 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       return ct_launch<CT_EPI_GRU_ZR>(p, grid, smem, s);
     case CT_EPI_GRU_Q:
       return ct_launch<CT_EPI_GRU_Q>(p, grid, smem, s);
+    case CT_EPI_FLOW_TAPS:
+      return ct_launch<CT_EPI_FLOW_TAPS>(p, grid, smem, s);
     default: {
       // the logits start at zero; the kernel adds each image's patch mean in (at most) two parts
       const long long n_img = a->height / a->row_period;

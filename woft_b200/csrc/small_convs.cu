@@ -314,9 +314,12 @@ __global__ void __launch_bounds__(256) flow_head_taps_kernel(const float* __rest
 
 // delta[o](y,x) = bias[o] + sum over taps of t[(y+ky-1, x+kx-1)][ky*3+kx][o] (zero padding).  Optional fused outputs:
 // coords (B,2,H,W) updated in place, flow = coords - coords0 as NCHW and as (pixels, 2).
+// flow_h1 / flow_h2 (optional): fp16 channels-last tensors (pixels, stride) that receive the new flow at channel offset
+// `h_off` -- the two operand buffers of the GRU convolutions, where the flow sits behind the motion features
 __global__ void flow_head_gather_kernel(const float* __restrict__ taps, const float* __restrict__ bias, int B, int H,
                                         int W, float* __restrict__ delta, float* coords, const float* __restrict__ coords0,
-                                        float* __restrict__ flow_nchw, float* __restrict__ flow_nhwc) {
+                                        float* __restrict__ flow_nchw, float* __restrict__ flow_nhwc,
+                                        __half* __restrict__ flow_h1, __half* __restrict__ flow_h2, int h_stride, int h_off) {
   const int hw = H * W;
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   pdl_sync();
@@ -352,6 +355,9 @@ __global__ void flow_head_gather_kernel(const float* __restrict__ taps, const fl
       flow_nchw[iy] = fy;
     }
     if (flow_nhwc) reinterpret_cast<float2*>(flow_nhwc)[i] = make_float2(fx, fy);
+    const __half2 fh = __floats2half2_rn(fx, fy);
+    if (flow_h1) *reinterpret_cast<__half2*>(flow_h1 + (size_t)i * h_stride + h_off) = fh;
+    if (flow_h2) *reinterpret_cast<__half2*>(flow_h2 + (size_t)i * h_stride + h_off) = fh;
   }
 }
 
@@ -437,6 +443,27 @@ extern "C" int woft_flow_head_step(const float* in_nhwc, const float* weight, co
   WOFT_CUDA_CHECK(launch_pdl(flow_head_taps_kernel, dim3((unsigned)ceil_div((int)pixels, kTapPix)), dim3(256), smem, s, in_nhwc,
                              weight, taps, (int)pixels, channels));
   WOFT_CUDA_CHECK(launch_pdl(flow_head_gather_kernel, dim3((unsigned)ceil_div((int)pixels, 128)), dim3(128), 0, s,
-                             (const float*)taps, bias, batch, height, width, delta_nchw, coords, coords0, flow_nchw, flow_nhwc));
+                             (const float*)taps, bias, batch, height, width, delta_nchw, coords, coords0, flow_nchw, flow_nhwc,
+                             (__half*)nullptr, (__half*)nullptr, 0, 0));
   return launch_status("flow head kernels");
+}
+
+extern "C" int woft_flow_head_gather(const float* taps, const float* bias, int batch, int height, int width, float* delta_nchw,
+                                     float* coords, const float* coords0, float* flow_nchw, float* flow_nhwc,
+                                     void* flow_f16_a, void* flow_f16_b, int f16_stride, int f16_offset, void* stream) {
+  using namespace woft;
+  WOFT_REQUIRE(taps && bias, "woft_flow_head_gather: null pointer");
+  WOFT_REQUIRE(batch > 0 && height > 0 && width > 0, "woft_flow_head_gather: bad extent");
+  WOFT_REQUIRE(delta_nchw || coords, "woft_flow_head_gather: no output requested");
+  WOFT_REQUIRE(!coords || coords0, "woft_flow_head_gather: coords needs coords0");
+  WOFT_REQUIRE((!flow_f16_a && !flow_f16_b) || (coords && f16_stride % 2 == 0 && f16_offset % 2 == 0 &&
+                                                  ((reinterpret_cast<uintptr_t>(flow_f16_a) | reinterpret_cast<uintptr_t>(flow_f16_b)) & 3) == 0),
+               "woft_flow_head_gather: the fp16 flow copies need coords and even strides / offsets");
+  const long long pixels = (long long)batch * height * width;
+  WOFT_REQUIRE(pixels < (1LL << 30), "woft_flow_head_gather: too many pixels");
+  WOFT_CUDA_CHECK(launch_pdl(flow_head_gather_kernel, dim3((unsigned)ceil_div((int)pixels, 128)), dim3(128), 0,
+                             static_cast<cudaStream_t>(stream), taps, bias, batch, height, width, delta_nchw, coords, coords0,
+                             flow_nchw, flow_nhwc, static_cast<__half*>(flow_f16_a), static_cast<__half*>(flow_f16_b),
+                             f16_stride, f16_offset));
+  return launch_status("flow_head_gather_kernel");
 }

@@ -387,6 +387,15 @@ class FastWeightedRAFT:
                     self.tc = {name: P(m.weight, m.bias, m.padding) for name, m in (
                         ("convc1", e.convc1), ("convc2", e.convc2), ("convf2", e.convf2), ("conv", e.conv),
                         ("fh1", ub.flow_head.conv1), ("m0", ub.mask[0]), ("m2", ub.mask[2]))}
+                    # FlowHead.conv2 (2, 256, 3, 3) as (256, 24): [taps 0-4 x (dx, dy) | 2 pad | taps 5-8 x (dx, dy) | 4 pad],
+                    # the operand of the flow-head epilogue of woft_conv_tc
+                    w2 = ub.flow_head.conv2.weight.detach().float()
+                    wt = w2.reshape(2, w2.shape[1], 9).permute(1, 2, 0)            # (c, tap, o)
+                    self.fh2 = wt.new_zeros((w2.shape[1], 24))
+                    self.fh2[:, 0:10] = wt[:, 0:5].reshape(-1, 10)
+                    self.fh2[:, 12:20] = wt[:, 5:9].reshape(-1, 8)
+                    self.fh2 = self.fh2.contiguous()
+                    self.fh2_bias = ub.flow_head.conv2.bias.detach().float().contiguous()
                     for tag in ("1", "2"):
                         gt = self.gru[tag]
                         self.tc["zr" + tag] = P(gt["w_zr"], gt["b_zr"], gt["padding"])
@@ -648,14 +657,22 @@ class FastWeightedRAFT:
         conv_tc.run(tc["convf2"], flo, relu=True, out=cf, out_off=tc["convc2"].cout)
         # x = [inp | motion (126) | flow (2)] behind h resp. r*h in both GRU buffers (update.py:96-97)
         conv_tc.run(tc["conv"], cf, relu=True, out=buf1, out_off=C + ci, out2=buf2, out2_off=C + ci)
-        cast_nhwc_f16(st["flow_cl"], 2, buf1, C + ci + tc["conv"].cout, buf2, C + ci + tc["conv"].cout)
+        if "taps" not in st:   # first iteration: the flow head's last kernel writes the flow into both buffers afterwards
+            cast_nhwc_f16(st["flow_cl"], 2, buf1, C + ci + tc["conv"].cout, buf2, C + ci + tc["conv"].cout)
+            st["taps"] = torch.empty((st["pixels"], 18), device=h.device, dtype=torch.float32)
         for tag in ("1", "2"):
             conv_tc.run(tc["zr" + tag], buf1, epilogue=_lib.CONV_GRU_ZR, h=h, z=z, out=buf2)
             conv_tc.run(tc["q" + tag], buf2, epilogue=_lib.CONV_GRU_Q, h=h, z=z, out=h, out2=buf1)
-        conv_tc.run(tc["fh1"], buf1, relu=True, out=st["fh"])                           # reads the h slice of buf1
-        fh = self.net.update_block.flow_head
-        flow_head_step(st["fh"], fh.conv2.weight, fh.conv2.bias, coords=st["coords1"], coords0=st["coords0"],
-                       flow_nchw=st["flow"], flow_nhwc=st["flow_cl"])
+        # flow head: conv1 + ReLU + the 18 tap products of conv2 in one launch (reads the h slice of buf1), then the gather
+        # that sums the shifted products, advances the coordinates and writes the flow where the next iteration reads it
+        conv_tc.run(tc["fh1"], buf1, epilogue=_lib.CONV_FLOW_TAPS, w1x1=self.fh2, head_out=st["taps"])
+        B, _, H, W = buf1.shape
+        with torch.cuda.device(h.device):
+            rc = _lib.load().woft_flow_head_gather(_lib.ptr(st["taps"]), _lib.ptr(self.fh2_bias), B, H, W, None,
+                                                   _lib.ptr(st["coords1"]), _lib.ptr(st["coords0"]), _lib.ptr(st["flow"]),
+                                                   _lib.ptr(st["flow_cl"]), _lib.ptr(buf1), _lib.ptr(buf2), buf1.shape[1],
+                                                   C + ci + tc["conv"].cout, _lib.current_stream(h.device))
+        _lib.check(rc, "woft_flow_head_gather")
 
     def _mask_own(self, st):
         """The upsampling-mask head (update.py:122-125, 135) on the final hidden state."""

@@ -424,7 +424,10 @@ typedef struct woft_conv_tc_args {
   int halo;          /* 1: fetch ONE activation box per tile and channel block -- the output tile plus its filter halo --
                         which every filter tap reads at its own row offset, instead of one shifted box per tap (kh * kw
                         times less activation traffic; the filters stream as before).  box_w x box_h is then the tile of
-                        OUTPUT pixels, with (box_w + kw - 1) * box_h <= 128 */
+                        OUTPUT pixels, with (box_w + kw - 1) * box_h <= 128.
+                        2 ("row halo", box_w % 8 == 0, box_w * box_h <= 128): one box per channel block and filter COLUMN,
+                        with kh - 1 extra rows; the taps of that column read it ky * box_w rows further in, so every MMA
+                        operand starts on an 8-row boundary: kw instead of kh * kw activation fetches at full MMA speed */
   int pair;          /* 1: clusters of two CTAs share each filter tile (tcgen05 cta_group::2, M = 256): every CTA fetches its
                         own activation box and half of the filter rows; ignored in halo mode */
   int pdl;           /* 1: programmatic dependent launch -- the kernel may be scheduled while its predecessor in the stream

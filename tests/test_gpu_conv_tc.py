@@ -289,3 +289,25 @@ def test_flow_head_epilogue_and_gather(H, W):
     assert torch.allclose(flow_nhwc.view(H, W, 2).permute(2, 0, 1)[None], flow_nchw)
     assert torch.equal(fa[:, 382:384], flow_nchw.half()) and torch.equal(fb[:, 382:384], fa[:, 382:384])
     assert (fa[:, :382] == 0).all()
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 64, 45, 80, 3, 3), (1, 128, 256, 90, 160, 3, 3), (1, 384, 128, 90, 160, 5, 1),
+                                   (1, 96, 96, 23, 37, 3, 3)])
+@pytest.mark.parametrize("f16", [True, False])
+def test_row_halo_mode_is_the_plain_convolution(shape, f16):
+    """halo=2: one activation box per channel block and filter column, the column's taps reading it ky * box_w rows further
+    in (8-row aligned operand starts).  Same products in the same order per output: bit-identical to the default mode."""
+    from woft_b200 import conv_tc
+    B, cin, cout, H, W, kh, kw = shape
+    x, w, b = make(B, cin, cout, H, W, kh, kw, seed=cin + kh)
+    pad = (kh // 2, kw // 2)
+    if f16:
+        x = cl(x.half())
+    pc = conv_tc.PackedConv(w, b, pad, f16=f16)
+    outs = []
+    for kwargs in (dict(), dict(halo=2, box=(32, 4))):
+        out = cl(torch.full((B, cout, H, W), 7.0, device=DEV, dtype=x.dtype))
+        conv_tc.run(pc, x, relu=True, out=out, **kwargs)
+        outs.append(out)
+    conv_tc.check(DEV)
+    assert torch.equal(outs[0], outs[1])

@@ -96,7 +96,7 @@ def run(pc, x, x_off=0, epilogue=_lib.CONV_BIAS_ACT, relu=False, scale=1.0, out=
     a.residual, a.residual_stride = _slice(residual, 0)
     a.stats = _lib.ptr(stats)          # (rows, batch, 2, cout) fp32 partial sums for an instance norm that follows
     a.stats_ctas = stats.shape[0] if stats is not None else 0
-    a.halo = int(halo)   # filters resident in shared memory, one activation box per tile and channel block (box = output tile)
+    a.halo = int(halo)   # 1: one activation box per tile and channel block for all taps; 2: one per filter column (rows only)
     a.debug_trace = _lib.ptr(trace)   # debug: int64 tensor of 8 * 148 per-CTA time stamps
     with torch.cuda.device(x.device):
         rc = _lib.load().woft_conv_tc(ctypes.byref(a), _lib.current_stream(x.device))

@@ -60,6 +60,10 @@ struct ConvTcParams {
   // starts tap_row[tap] rows into the box -- while the filters stream through their own ring; output pixel (i, j) of the
   // tile is GEMM row j * pw + i, rows with i >= bw are junk.  pw == bw, halo == 0 and one ring for both otherwise.
   int halo, pw, hh, a_stage, a_stages;
+  // halo == 2 ("row halo"): one box per channel block AND filter column kx, holding the tile plus kh - 1 extra rows; the
+  // taps of that column read it ky * bw rows further in.  With bw a multiple of 8 every operand starts on an 8-row
+  // boundary of the swizzled tile (full MMA speed), and the activations are fetched kw instead of kh * kw times.
+  int kw;
   // pair mode (cta_group::2): a cluster of two CTAs takes two pixel tiles that share the filters; each CTA fetches its own
   // activation box and HALF of the filter rows, the leader's MMA warp multiplies both tiles against both halves
   int pair, pix_tiles, pair_tiles;
@@ -451,18 +455,21 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         uint32_t a_ph = 0;
         CtTile tc;
         for (int it = 0; alive && ct_tile_at(p, it, rank, tc); ++it) {
-          for (int kc = 0; kc < p.k_chunks && alive; ++kc) {
+          const int groups = p.halo == 2 ? p.kw : 1, tpg = p.taps / groups;
+          for (int kg = 0; kg < p.k_chunks * groups && alive; ++kg) {
+            const int kc = kg / groups, g = kg - kc * groups;   // g: filter column of a row-halo box (tap g is its first)
             if (!ct_wait(a_empty + a_st, a_ph ^ 1u)) {
               alive = false;
               break;
             }
             ptx::mbar_arrive_expect_tx(a_full + a_st, uint32_t(p.a_bytes));
-            ptx::tma_load_4d(sA + a_st * p.a_stage, &p.tmA, a_full + a_st, kc * p.k_elems, tc.x0 + p.dx[0], tc.y0 + p.dy[0], tc.n);
+            ptx::tma_load_4d(sA + a_st * p.a_stage, &p.tmA, a_full + a_st, kc * p.k_elems, tc.x0 + p.dx[g], tc.y0 + p.dy[g], tc.n);
             if (++a_st == p.a_stages) {
               a_st = 0;
               a_ph ^= 1u;
             }
-            for (int tap = 0; tap < p.taps; ++tap) {
+            for (int i = 0; i < tpg; ++i) {
+              const int tap = p.halo == 2 ? i * p.kw + g : i;
               if (!ct_wait(empty + stage, phase ^ 1u)) {
                 alive = false;
                 break;
@@ -527,26 +534,29 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         ptx::tc_fence_after_sync();
         const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
         if (p.halo) {
-          for (int kc = 0; kc < p.k_chunks && alive; ++kc) {
+          const int groups = p.halo == 2 ? p.kw : 1, tpg = p.taps / groups;
+          for (int kg = 0; kg < p.k_chunks * groups && alive; ++kg) {
+            const int g = kg % groups;
             if (!ct_wait(a_full + a_st, a_ph)) {
               alive = false;
               break;
             }
             const uint32_t a_base = ptx::smem_u32(sA + a_st * p.a_stage);
-            for (int tap = 0; tap < p.taps; ++tap) {
+            for (int i = 0; i < tpg; ++i) {
+              const int tap = p.halo == 2 ? i * p.kw + g : i;
               if (!ct_wait(full + stage, phase)) {
                 alive = false;
                 break;
               }
               ptx::tc_fence_after_sync();
-              if (kc == 0 && tap == 0 && it == 0) ct_stamp(p, 2);
+              if (kg == 0 && i == 0 && it == 0) ct_stamp(p, 2);
               // the tap's operand is the same box read from tap_row[tap] rows further in: the 128-byte swizzle is a
               // function of the shared-memory address, so a descriptor may start on any row of the tile
               const uint64_t da = ct_desc(a_base + uint32_t(p.tap_row[tap]) * 128u);
               const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
-                const uint32_t acc = (kc > 0 || tap > 0 || k > 0) ? 1u : 0u;
+                const uint32_t acc = (kg > 0 || i > 0 || k > 0) ? 1u : 0u;
                 if (F16)
                   ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
                 else
@@ -944,16 +954,19 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   if (a->halo) {
     // one activation box per channel block serves all taps: it must hold the 128 GEMM rows behind the last tap's offset
     WOFT_REQUIRE(a->box_w > 0 && a->box_h > 0, "woft_conv_tc: halo mode takes the output tile in box_w, box_h");
-    const int pw = a->box_w + a->kw - 1, hh = a->box_h + a->kh - 1;
+    WOFT_REQUIRE(a->halo == 1 || (a->halo == 2 && a->box_w % 8 == 0), "woft_conv_tc: the row-halo mode needs box_w % 8 == 0");
+    const int pw = a->halo == 2 ? a->box_w : a->box_w + a->kw - 1, hh = a->box_h + a->kh - 1;
     WOFT_REQUIRE(pw * a->box_h <= 128 && pw <= 256 && hh <= 256, "woft_conv_tc: halo tile %d x %d does not fit 128 GEMM rows",
                  a->box_w, a->box_h);
-    const int rows = 128 + (a->kh - 1) * pw + (a->kw - 1) > pw * hh ? 128 + (a->kh - 1) * pw + (a->kw - 1) : pw * hh;
+    const int last = (a->kh - 1) * pw + (a->halo == 2 ? 0 : a->kw - 1);   // row offset of the last tap's operand
+    const int rows = 128 + last > pw * hh ? 128 + last : pw * hh;
     a_stage = (rows * 128 + 1023) / 1024 * 1024;
   }
   WOFT_REQUIRE(bn >= 16 && bn % 32 == 0, "woft_conv_tc: Cout tile %d (need a multiple of 32 dividing the padded Cout)", bn);
   p.bn = bn;
   p.n_tiles = a->cout_pad / bn;
-  p.halo = a->halo ? 1 : 0;
+  p.halo = a->halo;
+  p.kw = a->kw;
   p.a_stage = a_stage;
   // pixel box: bw x bh = 128 (or the caller's own, e.g. 9 x 14 rows of stacked 9-wide images)
   int bw = a->box_w, bh = a->box_h;
@@ -975,7 +988,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
                "woft_conv_tc: pixel box %d x %d must cover 96..128 pixels", bw, bh);
   p.bw = bw;
   p.bh = bh;
-  p.pw = a->halo ? bw + a->kw - 1 : bw;
+  p.pw = a->halo == 1 ? bw + a->kw - 1 : bw;
   p.hh = a->halo ? bh + a->kh - 1 : bh;
   const int stride = a->stride > 1 ? a->stride : 1;
   WOFT_REQUIRE(stride <= 2 && !(a->halo && stride != 1), "woft_conv_tc: stride 1 or 2 (1 in halo mode)");
@@ -999,7 +1012,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     for (int kx = 0; kx < a->kw; ++kx) {
       p.dx[ky * a->kw + kx] = (signed char)(kx - a->pad_w);
       p.dy[ky * a->kw + kx] = (signed char)(ky - a->pad_h);
-      p.tap_row[ky * a->kw + kx] = (short)(ky * p.pw + kx);
+      p.tap_row[ky * a->kw + kx] = (short)(a->halo == 2 ? ky * p.pw : ky * p.pw + kx);
     }
   p.k_elems = k_elems;
   p.k_chunks = cin_pad / k_elems;

@@ -246,10 +246,13 @@ def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float1
     Ho = (H + 2 * pc.pad_h - pc.kh) // stride + 1
     Wo = (W + 2 * pc.pad_w - pc.kw) // stride + 1
     out = torch.empty((B, pc.cout, Ho, Wo), device=x.device, dtype=out_dtype, memory_format=torch.channels_last)
-    conv_tc.run(pc, x, relu=relu, out=out, stride=stride, residual=residual, stats=stats)
+    # stride-1 filters with more than one row: fetch the activations once per filter column instead of once per tap
+    tile = dict(halo=2, box=(32, 4)) if (_ROW_HALO and stride == 1 and pc.kh > 1) else {}
+    conv_tc.run(pc, x, relu=relu, out=out, stride=stride, residual=residual, stats=stats, **tile)
     return out
 
 
+_ROW_HALO = os.environ.get("WOFT_ROW_HALO", "1") == "1"
 _STAT_ROWS = 148   # one row of partial sums per CTA of a persistent woft_conv_tc launch (at most one CTA per SM)
 
 

@@ -296,7 +296,8 @@ def test_flow_head_epilogue_and_gather(H, W):
 @pytest.mark.parametrize("f16", [True, False])
 def test_row_halo_mode_is_the_plain_convolution(shape, f16):
     """halo=2: one activation box per channel block and filter column, the column's taps reading it ky * box_w rows further
-    in (8-row aligned operand starts).  Same products in the same order per output: bit-identical to the default mode."""
+    in (8-row aligned operand starts).  The products are summed in a different order (channel block, column, row instead
+    of tap, channel block), so the two modes agree to fp32 summation noise, and both with torch."""
     from woft_b200 import conv_tc
     B, cin, cout, H, W, kh, kw = shape
     x, w, b = make(B, cin, cout, H, W, kh, kw, seed=cin + kh)
@@ -310,4 +311,10 @@ def test_row_halo_mode_is_the_plain_convolution(shape, f16):
         conv_tc.run(pc, x, relu=True, out=out, **kwargs)
         outs.append(out)
     conv_tc.check(DEV)
-    assert torch.equal(outs[0], outs[1])
+    want = F.conv2d(x.double(), (w.half() if f16 else conv_tc.round_to_tf32(w)).double(), b.double(), padding=pad).relu()
+    if not f16:
+        want = F.conv2d(trunc_tf32(x).double(), conv_tc.round_to_tf32(w).double(), b.double(), padding=pad).relu()
+    scale = want.abs().max().item()
+    tol = 1.5e-3 if f16 else 2e-4          # fp16: rounding of the stored result
+    assert (outs[1].double() - want).abs().max().item() / scale <= tol
+    assert (outs[0].double() - outs[1].double()).abs().max().item() / scale <= tol

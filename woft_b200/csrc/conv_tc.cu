@@ -37,7 +37,8 @@
 
 namespace woft {
 
-constexpr int CT_THREADS = 320, CT_EPI_THREADS = 256;   // TMA warp, MMA warp, 8 epilogue warps
+constexpr int CT_THREADS = 384, CT_EPI_THREADS = 256;   // TMA warp, MMA warp, 8 epilogue warps, two more TMA warps
+constexpr int CT_MAX_PRODUCERS = 3;
 constexpr int CT_A_STAGE = 128 * 128;       // 128 pixel rows x one 128-byte K row (a_stage; more rows in halo mode)
 constexpr int CT_MAX_STAGES = 8;
 constexpr int CT_MAX_TAPS = 25;
@@ -94,11 +95,17 @@ struct ConvTcParams {
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA, or null
   int coalesce;               // every epilogue operand is 16-byte aligned with 16-byte multiple strides: staged accesses
   int dbg;                    // experiments (woft_conv_tc_args.debug_flags)
+  int producers;              // TMA-issuing warps of the plain mode (warp 0 and warps 10, 11): each takes every producers-th k-step
   int pdl;                    // host only: launch with programmatic stream serialization
 };
 
 __device__ __forceinline__ void ct_stamp(const ConvTcParams& p, int slot) {
-  if (p.trace) p.trace[blockIdx.x * 8 + slot] = ptx::globaltimer_ns();
+  if (p.trace && !(p.dbg & 16)) p.trace[blockIdx.x * 8 + slot] = ptx::globaltimer_ns();
+}
+
+// debug_flags bit 16: SM-clock stamps of CTA 0's roles for its first 18 tiles (8 slots per tile) instead of the phase stamps
+__device__ __forceinline__ void ct_tile_stamp(const ConvTcParams& p, int it, int slot) {
+  if ((p.dbg & 16) && p.trace && blockIdx.x == 0 && it < 18 && (threadIdx.x & 31) == 0) p.trace[it * 8 + slot] = clock64();
 }
 
 // status word of the conv kernels (a pipeline wait timed out); read back by woft_conv_tc_check
@@ -109,6 +116,22 @@ __device__ __forceinline__ bool ct_wait(uint64_t* bar, uint32_t parity) {
   const uint64_t t0 = ptx::globaltimer_ns();
   uint32_t spins = 0;
   while (!ptx::mbar_try_wait(bar, parity)) {
+    if ((++spins & 63u) == 0) {
+      if (*reinterpret_cast<volatile int*>(&g_conv_abort) != 0) return false;
+      if (ptx::globaltimer_ns() - t0 > 2000000000ull) {
+        atomicExch(&g_conv_abort, 1);
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
+// the slow path alone, on a barrier address (the caller has tried once)
+__device__ __noinline__ bool ct_wait_a(uint32_t bar, uint32_t parity) {
+  const uint64_t t0 = ptx::globaltimer_ns();
+  uint32_t spins = 0;
+  while (!ptx::mbar_try_wait_a(bar, parity)) {
     if ((++spins & 63u) == 0) {
       if (*reinterpret_cast<volatile int*>(&g_conv_abort) != 0) return false;
       if (ptx::globaltimer_ns() - t0 > 2000000000ull) {
@@ -442,15 +465,21 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   const int k_steps = p.taps * p.k_chunks;
   if (threadIdx.x == 0) ct_stamp(p, 1);
 
-  if (warp == 0) {
-    // ================================ TMA producer ================================
+  const int prod = warp == 0 ? 0 : warp - 9;   // warps 10 and 11: the second and third TMA warp of the plain mode
+  if (warp == 0 || (warp >= 10 && prod < p.producers)) {
+    // ================================ TMA producers ================================
+    // One elected lane per warp.  A k-step costs the issuing thread a few hundred cycles of dependent latency (barrier
+    // try-wait ~90, arrive, two TMA issues, coordinate arithmetic) -- more than the MMAs of a narrow tile take -- so in the
+    // plain mode the k-steps are dealt round-robin to `producers` warps: the stage sequence is fixed, each warp walks
+    // every producers-th stage of the ring.
     if (ptx::elect_one()) {
-      int stage = 0;
-      uint32_t phase = 0;
       bool alive = true;
       if (p.halo) {
+        {
         // two rings, filled in the order the MMA warp drains them: the activation box of a channel block, then the
         // filters of every tap for that block
+        int stage = 0;
+        uint32_t phase = 0;
         int a_st = 0;
         uint32_t a_ph = 0;
         CtTile tc;
@@ -483,143 +512,200 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
             }
           }
         }
-      }
-      CtTile tc;
-      for (int it = 0; alive && !p.halo && ct_tile_at(p, it, rank, tc); ++it) {
-        for (int tap = 0; tap < p.taps && alive; ++tap) {
-          const int xs = p.stride * tc.x0 + p.dx[tap], ys = p.stride * tc.y0 + p.dy[tap];
-          for (int kc = 0; kc < p.k_chunks; ++kc) {
+        }
+      } else {
+        const int np = p.producers, stages = p.stages, k_chunks = p.k_chunks, k_elems = p.k_elems, stride = p.stride;
+        const int a_stage = p.a_stage, b_bytes = p.b_bytes;
+        const bool load_a = !(p.dbg & 1), load_b = !(p.dbg & 2);   // dbg bits 1, 2: timing experiments without the loads
+        const uint32_t tx = uint32_t((load_a ? p.a_bytes : 0) + (load_b ? b_bytes : 0));
+        int stage = prod;   // host: producers <= stages
+        uint32_t phase = 0;
+        int ks = prod;      // this warp's next k-step of the current tile
+        CtTile tc;
+        for (int it = 0; alive && ct_tile_at(p, it, rank, tc); ++it) {
+          if (prod == 0) ct_tile_stamp(p, it, 0);
+          int tap = ks / k_chunks, kc = ks - tap * k_chunks;
+          const int xb = stride * tc.x0, yb = stride * tc.y0;
+          while (ks < k_steps) {
+            const int xs = xb + p.dx[tap], ys = yb + p.dy[tap];
             if (!ct_wait(empty + stage, phase ^ 1u)) {
               alive = false;
               break;
             }
-            if (PAIR) {
-              // both CTAs' bytes are counted on the LEADER's barrier, which the leader arms with the sum.  The peer does not
-              // arrive (a remote release-arrive per stage paced the whole pipeline at 0.74 us per step): its bytes may land
-              // before the leader has armed the phase, which only drives the pending count negative for a while -- the
-              // phase cannot complete before the leader's arrival, and the peer cannot reach the next use of this stage
-              // before the leader's MMAs have drained it
-              const uint32_t lead_full = ptx::mapa(full + stage, 0);
-              if (rank == 0) ptx::mbar_arrive_expect_tx(full + stage, 2u * uint32_t(p.a_bytes + p.b_bytes));
-              ptx::tma_load_4d_2sm(sA + stage * p.a_stage, &p.tmA, lead_full, kc * p.k_elems, xs, ys, tc.n);
-              ptx::tma_load_3d_2sm(sB + stage * p.b_bytes, &p.tmB, lead_full, kc * p.k_elems, tc.c0 + int(rank) * (p.bn >> 1), tap);
-            } else {
-              ptx::mbar_arrive_expect_tx(full + stage, uint32_t(p.a_bytes + p.b_bytes));
-              ptx::tma_load_4d(sA + stage * p.a_stage, &p.tmA, full + stage, kc * p.k_elems, xs, ys, tc.n);
-              ptx::tma_load_3d(sB + stage * p.b_bytes, &p.tmB, full + stage, kc * p.k_elems, tc.c0, tap);
+            {
+              if (PAIR) {
+                // both CTAs' bytes are counted on the LEADER's barrier, which the leader arms with the sum.  The peer does
+                // not arrive (a remote release-arrive per stage paced the whole pipeline at 0.74 us per step): its bytes may
+                // land before the leader has armed the phase, which only drives the pending count negative for a while --
+                // the phase cannot complete before the leader's arrival, and the peer cannot reach the next use of this
+                // stage before the leader's MMAs have drained it
+                const uint32_t lead_full = ptx::mapa(full + stage, 0);
+                if (rank == 0) ptx::mbar_arrive_expect_tx(full + stage, 2u * uint32_t(p.a_bytes + b_bytes));
+                ptx::tma_load_4d_2sm(sA + stage * a_stage, &p.tmA, lead_full, kc * k_elems, xs, ys, tc.n);
+                ptx::tma_load_3d_2sm(sB + stage * b_bytes, &p.tmB, lead_full, kc * k_elems, tc.c0 + int(rank) * (p.bn >> 1), tap);
+              } else {
+                ptx::mbar_arrive_expect_tx(full + stage, tx);
+                if (load_a) ptx::tma_load_4d(sA + stage * a_stage, &p.tmA, full + stage, kc * k_elems, xs, ys, tc.n);
+                if (load_b) ptx::tma_load_3d(sB + stage * b_bytes, &p.tmB, full + stage, kc * k_elems, tc.c0, tap);
+              }
             }
-            if (++stage == p.stages) {
-              stage = 0;
+            stage += np;
+            if (stage >= stages) {
+              stage -= stages;
               phase ^= 1u;
             }
+            ks += np;
+            kc += np;
+            while (kc >= k_chunks) {
+              kc -= k_chunks;
+              ++tap;
+            }
           }
+          ks -= k_steps;
+          if (prod == 0) ct_tile_stamp(p, it, 1);
         }
       }
     }
   } else if (warp == 1) {
     // ================================ MMA issuer ================================
-    if (rank == 0 && ptx::elect_one()) {   // one elected lane; pair mode: the leader CTA issues for both SMs
+    // pair mode: the leader CTA issues for both SMs
+    if (rank == 0 && ptx::elect_one()) {   // one elected lane runs the whole loop
       const uint32_t fmt = F16 ? 0u : 2u;  // F16 = 0, TF32 = 2
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | (uint32_t(p.bn >> 3) << 17) |
                              (uint32_t((PAIR ? 256 : 128) >> 4) << 24);
-      int stage = 0, a_st = 0;
-      uint32_t phase = 0, a_ph = 0;
+      // this CTA's (pair's) tile count: the issuing warp has no use for tile coordinates
+      const int my_tiles = p.pair ? (p.pair_tiles - int(blockIdx.x >> 1) + int(gridDim.x >> 1) - 1) / int(gridDim.x >> 1)
+                                  : (p.total_tiles - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);
+      int stage = 0;
+      uint32_t phase = 0;
       bool alive = true;
-      int it = 0;
-      CtTile tc_unused;
-      for (; alive && ct_tile_at(p, it, rank, tc_unused); ++it) {
-        const int buf = it & 1;
-        const uint32_t use = uint32_t(it >> 1);
-        if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
-        ptx::tc_fence_after_sync();
-        const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
-        if (p.halo) {
-          const int groups = p.halo == 2 ? p.kw : 1, tpg = p.taps / groups;
-          for (int kg = 0; kg < p.k_chunks * groups && alive; ++kg) {
-            const int g = kg % groups;
-            if (!ct_wait(a_full + a_st, a_ph)) {
-              alive = false;
-              break;
-            }
-            const uint32_t a_base = ptx::smem_u32(sA + a_st * p.a_stage);
-            for (int i = 0; i < tpg; ++i) {
-              const int tap = p.halo == 2 ? i * p.kw + g : i;
-              if (!ct_wait(full + stage, phase)) {
+      if (p.halo) {
+        {
+          int a_st = 0;
+          uint32_t a_ph = 0;
+          for (int it = 0; alive && it < my_tiles; ++it) {
+            const int buf = it & 1;
+            const uint32_t use = uint32_t(it >> 1);
+            if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
+            ptx::tc_fence_after_sync();
+            const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
+              const int groups = p.halo == 2 ? p.kw : 1, tpg = p.taps / groups;
+              for (int kg = 0; kg < p.k_chunks * groups && alive; ++kg) {
+                const int g = kg % groups;
+                if (!ct_wait(a_full + a_st, a_ph)) {
+                  alive = false;
+                  break;
+                }
+                const uint32_t a_base = ptx::smem_u32(sA + a_st * p.a_stage);
+                for (int i = 0; i < tpg; ++i) {
+                  const int tap = p.halo == 2 ? i * p.kw + g : i;
+                  if (!ct_wait(full + stage, phase)) {
+                    alive = false;
+                    break;
+                  }
+                  ptx::tc_fence_after_sync();
+                  if (kg == 0 && i == 0 && it == 0) ct_stamp(p, 2);
+                  // the tap's operand is the same box read from tap_row[tap] rows further in: the 128-byte swizzle is a
+                  // function of the shared-memory address, so a descriptor may start on any row of the tile
+                  const uint64_t da = ct_desc(a_base + uint32_t(p.tap_row[tap]) * 128u);
+                  const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
+    #pragma unroll
+                  for (int k = 0; k < 4; ++k) {
+                    const uint32_t acc = (kg > 0 || i > 0 || k > 0) ? 1u : 0u;
+                    if (F16)
+                      ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+                    else
+                      ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+                  }
+                  ptx::mma_commit(empty + stage);
+                  if (++stage == p.stages) {
+                    stage = 0;
+                    phase ^= 1u;
+                  }
+                }
+                if (alive) ptx::mma_commit(a_empty + a_st);   // every MMA reading this activation box has been issued
+                if (++a_st == p.a_stages) {
+                  a_st = 0;
+                  a_ph ^= 1u;
+                }
+              }
+              if (alive) ptx::mma_commit(tfull + buf);
+              if (it == 0) ct_stamp(p, 3);
+          }
+        }
+      } else {
+        // Plain mode.  The issuing thread is latency bound (about 5 cycles per instruction, every one dependent on the
+        // last through the loop state), so the k-step is kept to the barrier wait, four MMAs and the commit: descriptors
+        // and barrier addresses are running 32-bit values (the descriptors' high words never change), and the ring wrap
+        // is a loop boundary, not a select chain.
+        const int stages = p.stages;
+        const uint64_t da0 = ct_desc(ptx::smem_u32(sA)), db0 = ct_desc(ptx::smem_u32(sB));
+        const uint32_t desc_hi = uint32_t(da0 >> 32);
+        const uint32_t a_lo0 = uint32_t(da0), b_lo0 = uint32_t(db0);
+        const uint32_t a_step = uint32_t(p.a_stage >> 4), b_step = uint32_t(p.b_bytes >> 4);
+        const uint32_t full0 = ptx::smem_u32(full), empty0 = ptx::smem_u32(empty);
+        uint32_t a_lo = a_lo0, b_lo = b_lo0, full_a = full0, empty_a = empty0;
+        for (int it = 0; alive && it < my_tiles; ++it) {
+          const int buf = it & 1;
+          const uint32_t use = uint32_t(it >> 1);
+          if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
+          ptx::tc_fence_after_sync();
+          ct_tile_stamp(p, it, 2);
+          const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
+          uint32_t started = 0;   // 0: the tile's first MMA overwrites the accumulator
+          int left = k_steps;
+          while (left > 0 && alive) {
+            int n = stages - stage;   // k-steps up to the end of the ring or of the tile
+            if (n > left) n = left;
+            left -= n;
+            stage += n;
+            for (; n > 0; --n) {
+              if (!ptx::mbar_try_wait_a(full_a, phase) && !ct_wait_a(full_a, phase)) {
                 alive = false;
                 break;
               }
               ptx::tc_fence_after_sync();
-              if (kg == 0 && i == 0 && it == 0) ct_stamp(p, 2);
-              // the tap's operand is the same box read from tap_row[tap] rows further in: the 128-byte swizzle is a
-              // function of the shared-memory address, so a descriptor may start on any row of the tile
-              const uint64_t da = ct_desc(a_base + uint32_t(p.tap_row[tap]) * 128u);
-              const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
+              if (PAIR) {
+                const uint64_t da = (uint64_t(desc_hi) << 32) | a_lo, db = (uint64_t(desc_hi) << 32) | b_lo;
 #pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const uint32_t acc = (kg > 0 || i > 0 || k > 0) ? 1u : 0u;
-                if (F16)
-                  ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-                else
-                  ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+                for (int k = 0; k < 4; ++k) {
+                  if (F16)
+                    ptx::mma_f16_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, k ? 1u : started);
+                  else
+                    ptx::mma_tf32_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, k ? 1u : started);
+                }
+                ptx::mma_commit_2sm(empty + (stage - n), 3);   // frees the stage in both CTAs
+              } else {
+                ptx::mma_row4<F16>(d_tmem, a_lo, b_lo, desc_hi, idesc, started);
+                ptx::mma_commit_a(empty_a);
               }
-              ptx::mma_commit(empty + stage);
-              if (++stage == p.stages) {
-                stage = 0;
-                phase ^= 1u;
-              }
+              started = 1;
+              a_lo += a_step;
+              b_lo += b_step;
+              full_a += 8;
+              empty_a += 8;
             }
-            if (alive) ptx::mma_commit(a_empty + a_st);   // every MMA reading this activation box has been issued
-            if (++a_st == p.a_stages) {
-              a_st = 0;
-              a_ph ^= 1u;
+            if (stage == stages) {
+              stage = 0;
+              phase ^= 1u;
+              a_lo = a_lo0;
+              b_lo = b_lo0;
+              full_a = full0;
+              empty_a = empty0;
             }
           }
-          if (alive) ptx::mma_commit(tfull + buf);
+          if (alive) {
+            if (PAIR)
+              ptx::mma_commit_2sm(tfull + buf, 3);
+            else
+              ptx::mma_commit(tfull + buf);
+          }
           if (it == 0) ct_stamp(p, 3);
-          continue;
+          ct_tile_stamp(p, it, 3);
         }
-        for (int ks = 0; ks < k_steps; ++ks) {
-          if (!ct_wait(full + stage, phase)) {
-            alive = false;
-            break;
-          }
-          ptx::tc_fence_after_sync();
-          if (ks == 0 && it == 0) ct_stamp(p, 2);
-          const uint64_t da = ct_desc(ptx::smem_u32(sA + stage * p.a_stage));
-          const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
-#pragma unroll
-          for (int k = 0; k < 4; ++k) {  // 4 x 32 bytes of K per 128-byte row
-            const uint32_t acc = (ks > 0 || k > 0) ? 1u : 0u;
-            if (PAIR) {
-              if (F16)
-                ptx::mma_f16_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-              else
-                ptx::mma_tf32_2sm(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-            } else if (F16) {
-              ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-            } else {
-              ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-            }
-          }
-          if (PAIR)
-            ptx::mma_commit_2sm(empty + stage, 3);   // frees the stage in both CTAs
-          else
-            ptx::mma_commit(empty + stage);
-          if (++stage == p.stages) {
-            stage = 0;
-            phase ^= 1u;
-          }
-        }
-        if (alive) {
-          if (PAIR)
-            ptx::mma_commit_2sm(tfull + buf, 3);
-          else
-            ptx::mma_commit(tfull + buf);
-        }
-        if (it == 0) ct_stamp(p, 3);
       }
     }
-  } else {
+  } else if (warp < 10) {   // warps 10, 11 that are not producers have nothing to do
     // ================================ epilogue ================================
     // Eight warps: two per TMEM lane quadrant (a warp reaches lanes 32 * (warp % 4) ...), the pair splitting the tile's
     // 32-column chunks by parity.  One warp per scheduler cannot hide the latency of its own dependent instructions;
@@ -637,9 +723,11 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       const int buf = it & 1;
       const uint32_t use = uint32_t(it >> 1);
       if (leader) *epi_go = ct_wait(tfull + buf, use & 1u) ? 1 : 0;
+      if (leader) ct_tile_stamp(p, it, 4);
       ptx::named_bar_sync(1, CT_EPI_THREADS);
       if (*epi_go == 0) break;
       ptx::tc_fence_after_sync();
+      if (leader) ct_tile_stamp(p, it, 5);
       if (leader && it == 0) ct_stamp(p, 4);
       const int x = tc.x0 + xi, y = tc.y0 + yj;
       const bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H && tc.n < p.NB;
@@ -760,7 +848,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               }
             }
           }
-          if (co && nv > 0) {   // warp-uniform
+          if (p.dbg & 8) {   // timing experiment: nothing is stored
+          } else if (co && nv > 0) {   // warp-uniform
             ct_store_tile(p.out, p.out_stride, col, v, nv, p.out_f16 != 0, stg, lane, rp,
                           (p.stats && tc.n < 2) ? s_stat + ((warp - 2) * 2 + tc.n) * 2 * CT_STAT_C : nullptr, CT_STAT_C);
             if (p.out2) ct_store_tile(p.out2, p.out2_stride, col, v, nv, p.out2_f16 != 0, stg, lane, rp);
@@ -827,6 +916,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         ptx::named_bar_sync(1, CT_EPI_THREADS);
       }
       if (leader && it == 0) ct_stamp(p, 5);
+      if (leader) ct_tile_stamp(p, it, 6);
     }
   }
 
@@ -1127,6 +1217,12 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   WOFT_REQUIRE(stages >= 2, "woft_conv_tc: tile does not fit shared memory");
   p.stages = stages;
   p.a_stages = p.halo ? a_stages_halo : stages;
+  static const int producers_env = [] {   // WOFT_CONV_PRODUCERS: TMA-issuing warps of the plain mode (1..3)
+    const char* e = getenv("WOFT_CONV_PRODUCERS");
+    const int v = e ? atoi(e) : CT_MAX_PRODUCERS;
+    return v < 1 ? 1 : v > CT_MAX_PRODUCERS ? CT_MAX_PRODUCERS : v;
+  }();
+  p.producers = p.halo ? 1 : (producers_env < stages ? producers_env : stages);
   // always more than half of the SM's shared memory: one CTA per SM, which owns all 512 TMEM columns
   int smem = p.a_stages * a_stage + stages * p.b_bytes + fixed;
   if (smem < 120 * 1024) smem = 120 * 1024;

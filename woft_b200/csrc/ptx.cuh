@@ -89,6 +89,13 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const void* tmap, ui
       "r"(c3)
       : "memory");
 }
+// L2 prefetch of a 4-D box (no shared-memory destination, no barrier): the lines are in L2 when the load that follows asks
+__device__ __forceinline__ void tma_prefetch_4d(const void* tmap, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(
+                   reinterpret_cast<uint64_t>(tmap)),
+               "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+               : "memory");
+}
 __device__ __forceinline__ void tma_store_4d(const void* tmap, const void* smem_src, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(
                    reinterpret_cast<uint64_t>(tmap)),
@@ -128,6 +135,56 @@ __device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t desc_a, uint64
       "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// Four K = 16 (fp16) / K = 8 (tf32) MMAs over one 128-byte operand row: the descriptors' start-address fields advance by
+// 32 bytes (2 units of 16 B) per MMA; `first` = 0 makes the first of the four overwrite the accumulator.  The descriptors
+// come as their low words plus the common high word, so a k-step costs one 32-bit add per operand.
+template <bool F16>
+__device__ __forceinline__ void mma_row4(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc,
+                                         uint32_t first) {
+  if (F16)
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t.reg .b32 t;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\tsetp.eq.b32 q, %4, %4;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n\t"
+        "add.u32 t, %1, 2;\n\tmov.b64 da, {t, %3};\n\tadd.u32 t, %2, 2;\n\tmov.b64 db, {t, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, q;\n\t"
+        "add.u32 t, %1, 4;\n\tmov.b64 da, {t, %3};\n\tadd.u32 t, %2, 4;\n\tmov.b64 db, {t, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, q;\n\t"
+        "add.u32 t, %1, 6;\n\tmov.b64 da, {t, %3};\n\tadd.u32 t, %2, 6;\n\tmov.b64 db, {t, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, q;\n\t}"
+        ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(first)
+        : "memory");
+  else
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 da, db;\n\t.reg .b32 t;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\tsetp.eq.b32 q, %4, %4;\n\t"
+        "mov.b64 da, {%1, %3};\n\tmov.b64 db, {%2, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, p;\n\t"
+        "add.u32 t, %1, 2;\n\tmov.b64 da, {t, %3};\n\tadd.u32 t, %2, 2;\n\tmov.b64 db, {t, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, q;\n\t"
+        "add.u32 t, %1, 4;\n\tmov.b64 da, {t, %3};\n\tadd.u32 t, %2, 4;\n\tmov.b64 db, {t, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, q;\n\t"
+        "add.u32 t, %1, 6;\n\tmov.b64 da, {t, %3};\n\tadd.u32 t, %2, 6;\n\tmov.b64 db, {t, %3};\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], da, db, %4, q;\n\t}"
+        ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(hi), "r"(idesc), "r"(first)
+        : "memory");
+}
+// try_wait / commit on a barrier given by its shared-memory address (loops that keep running barrier addresses)
+__device__ __forceinline__ bool mbar_try_wait_a(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mma_commit_a(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
 // arrives on the mbarrier once every MMA issued so far by this thread has completed
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {

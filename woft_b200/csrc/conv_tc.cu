@@ -665,6 +665,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
                 break;
               }
               ptx::tc_fence_after_sync();
+              if (started == 0 && it == 0) ct_stamp(p, 2);
               if (PAIR) {
                 const uint64_t da = (uint64_t(desc_hi) << 32) | a_lo, db = (uint64_t(desc_hi) << 32) | b_lo;
 #pragma unroll

@@ -162,12 +162,13 @@ def flow_conv7x7_relu(flow, weight, bias):
     return out
 
 
-def flow_conv7x7_relu_f16(flow, weight, bias):
-    """The same with an fp16 output tensor; woft_flow_conv7x7_relu_f16."""
+def flow_conv7x7_relu_f16(flow, weight, bias, out=None):
+    """The same with an fp16 output tensor (`out` reuses one); woft_flow_conv7x7_relu_f16."""
     flow = flow.contiguous()
     B, _, H, W = flow.shape
-    out = torch.empty((B, weight.shape[0], H, W), device=flow.device, dtype=torch.float16,
-                      memory_format=torch.channels_last)
+    if out is None:
+        out = torch.empty((B, weight.shape[0], H, W), device=flow.device, dtype=torch.float16,
+                          memory_format=torch.channels_last)
     with torch.cuda.device(flow.device):
         rc = _lib.load().woft_flow_conv7x7_relu_f16(_lib.ptr(flow), _lib.ptr(weight), _lib.ptr(bias), B, H, W, _lib.ptr(out),
                                                     _lib.current_stream(flow.device))
@@ -252,6 +253,7 @@ def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float1
     return out
 
 
+_TWO_STREAMS = os.environ.get("WOFT_TWO_STREAMS", "1") == "1"   # independent branches of the schedule on a second stream
 _ROW_HALO = os.environ.get("WOFT_ROW_HALO", "0") == "1"   # measured: no gain on the encoders (205.9 vs 208.7 frames/s)
 _STAT_ROWS = 148   # one row of partial sums per CTA of a persistent woft_conv_tc launch (at most one CTA per SM)
 
@@ -324,6 +326,7 @@ class FastWeightedRAFT:
         # torch.backends.cudnn.allow_tf32; False keeps every convolution in fp32 on cuDNN (the reference's class)
         self.tf32 = bool(torch.backends.cudnn.allow_tf32 if tf32 is None else tf32)
         self.with_weights = net.with_weights
+        self._side = {}   # device index -> second stream (see _update_own)
         dev = next(net.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("FastWeightedRAFT needs the network on a CUDA device")
@@ -647,17 +650,37 @@ class FastWeightedRAFT:
             mask = conv_bias_nhwc(_conv_relu(h, *w["m0"], padding=(1, 1)), *w["m2"], scale=0.25)
         return mask
 
-    def _update_own(self, st, corr):
+    def _side_stream(self, device):
+        """The second stream of the two-branch sections (one per device, created on first use)."""
+        key = torch.device(device).index
+        if key not in self._side:
+            self._side[key] = torch.cuda.Stream(device=device)
+        return self._side[key]
+
+    def _update_own(self, st, lookup):
         """The iteration on woft_conv_tc: every wide convolution is one launch that also applies its bias / ReLU / GRU gate
-        arithmetic and writes where the next layer reads (no concatenation, no separate element-wise kernels).  `corr` is
-        the fp16 channels-last lookup (flags 8 | 16)."""
+        arithmetic and writes where the next layer reads (no concatenation, no separate element-wise kernels).  `lookup()`
+        returns the fp16 channels-last correlation lookup (flags 8 | 16).
+
+        The motion encoder's two branches (update.py:88-95) are independent until `conv`: the flow branch (7x7 + 3x3) runs
+        on a second stream beside the correlation branch (lookup + 1x1 + 3x3), which leaves 33 SMs and every prologue and
+        epilogue bubble of its one-tile-per-CTA launches free.  Under graph capture the fork and join become graph edges."""
         tc, C, ci = self.tc, st["C"], st["ci"]
         buf1, buf2, cf, h, z = st["buf1h"], st["buf2h"], st["cf"], st["h"], st["z"]
         e = self.net.update_block.encoder
-        flo = flow_conv7x7_relu_f16(st["flow"], e.convf1.weight, e.convf1.bias)
+        main = torch.cuda.current_stream(h.device)
+        side = self._side_stream(h.device) if _TWO_STREAMS else main
+        if side is not main:
+            side.wait_stream(main)
+        with torch.cuda.stream(side):
+            flo = flow_conv7x7_relu_f16(st["flow"], e.convf1.weight, e.convf1.bias, out=st.get("flo"))
+            st["flo"] = flo
+            conv_tc.run(tc["convf2"], flo, relu=True, out=cf, out_off=tc["convc2"].cout)
+        corr = lookup()
         conv_tc.run(tc["convc1"], corr, relu=True, out=st["cor1"])
         conv_tc.run(tc["convc2"], st["cor1"], relu=True, out=cf)                        # cf = [cor (192) | flo (64)]
-        conv_tc.run(tc["convf2"], flo, relu=True, out=cf, out_off=tc["convc2"].cout)
+        if side is not main:
+            main.wait_stream(side)
         # x = [inp | motion (126) | flow (2)] behind h resp. r*h in both GRU buffers (update.py:96-97)
         conv_tc.run(tc["conv"], cf, relu=True, out=buf1, out_off=C + ci, out2=buf2, out2_off=C + ci)
         if "taps" not in st:   # first iteration: the flow head's last kernel writes the flow into both buffers afterwards
@@ -792,7 +815,7 @@ class FastWeightedRAFT:
         coords1 = coords0.clone()
         if flow_init is not None:
             coords1 = coords1 + flow_init
-        up_mask = None
+        up_mask, mask_join = None, None
         lookup_flags = 8 if nhwc else 0
         if nhwc:
             ctx = self._context_tc(image1) if self.own_encoders else self._context(image1, raw_tail=True)
@@ -805,8 +828,15 @@ class FastWeightedRAFT:
             last = it == iters - 1
             if nhwc and self.own_convs:
                 coords1 = state["coords1"]  # advanced in place by the flow head's last kernel
-                self._update_own(state, corr_fn(coords1, flags=lookup_flags | 16))
-                if last:
+                self._update_own(state, lambda: corr_fn(coords1, flags=lookup_flags | 16))
+                if last and _TWO_STREAMS:   # the mask head runs beside the last lookup and the weight head
+                    main, side = torch.cuda.current_stream(image1.device), self._side_stream(image1.device)
+                    side.wait_stream(main)
+                    with torch.cuda.stream(side):
+                        up_mask = self._mask_own(state)
+                    up_mask.record_stream(main)
+                    mask_join = (main, side)
+                elif last:
                     up_mask = self._mask_own(state)
             elif nhwc:
                 coords1 = state["coords1"]
@@ -818,11 +848,15 @@ class FastWeightedRAFT:
                 coords1 = coords1 + dflow
         flow_low = coords1 - coords0
         if not self.with_weights:
+            if mask_join:
+                mask_join[0].wait_stream(mask_join[1])
             return flow_low, convex_upsample_both(flow_low, None, up_mask)[0]
         window = corr_fn(coords1, flags=lookup_flags) if nhwc else corr_fn(coords1)
         if nhwc and self.own_head and tuple(window.shape[1:2]) == (324,):
             weights = self._weights_own(window, corr_fn.mean_response())
         else:
             weights = self._weights(window, corr_fn.mean_response())
+        if mask_join:
+            mask_join[0].wait_stream(mask_join[1])
         flow_up, weights_up = convex_upsample_both(flow_low, weights, up_mask)  # one kernel, softmax computed once
         return flow_low, flow_up, corr_fn.corr_pyramid[0], weights, weights_up

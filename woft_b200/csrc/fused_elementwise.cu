@@ -364,6 +364,48 @@ __global__ void in_apply_nhwc_kernel(const T* __restrict__ x, const float* __res
   }
 }
 
+// fp16, channels a multiple of 8: 16 bytes per thread and access.  x and y may be the same tensor (the normalisation of
+// the encoders runs in place, so the tensor crosses L2 once instead of twice); neither is declared restrict.
+__global__ void in_apply_nhwc_h8_kernel(const __half* x, const float* __restrict__ stats, const __half* __restrict__ residual,
+                                        __half* y, unsigned HW, unsigned C, int relu, unsigned total8) {
+  const unsigned c8n = C >> 3;
+  const unsigned per_image = HW * c8n;
+  const float floor_ = relu ? 0.f : -3.4e38f;
+  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total8; i += gridDim.x * blockDim.x) {
+    const unsigned cq = i % c8n;
+    const unsigned n = i / per_image;
+    const uint4 u = reinterpret_cast<const uint4*>(x)[i];
+    const float4* mp = reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C) + 2 * cq;
+    const float4* rp = reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C + C) + 2 * cq;
+    const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), r0 = __ldg(rp), r1 = __ldg(rp + 1);
+    const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+    const float r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+    const __half2* hp = reinterpret_cast<const __half2*>(&u);
+    float o[8];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = __half22float2(hp[e]);
+      o[2 * e] = fmaxf((f.x - m[2 * e]) * r[2 * e], floor_);
+      o[2 * e + 1] = fmaxf((f.y - m[2 * e + 1]) * r[2 * e + 1], floor_);
+    }
+    if (residual) {
+      const uint4 a = __ldg(reinterpret_cast<const uint4*>(residual) + i);
+      const __half2* ap = reinterpret_cast<const __half2*>(&a);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __half22float2(ap[e]);
+        o[2 * e] = fmaxf(f.x + o[2 * e], 0.f);
+        o[2 * e + 1] = fmaxf(f.y + o[2 * e + 1], 0.f);
+      }
+    }
+    uint4 w;
+    __half2* wp = reinterpret_cast<__half2*>(&w);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) wp[e] = __floats2half2_rn(o[2 * e], o[2 * e + 1]);
+    reinterpret_cast<uint4*>(y)[i] = w;
+  }
+}
+
 // x[pix][c] = scale * (x[pix][c] + bias[c]) in place, optional ReLU: the bias of a convolution whose cuDNN call has no
 // fused epilogue (ATen adds a broadcast bias to a channels-last tensor with its slow, non-vectorised kernel)
 __global__ void bias_act_nhwc_kernel(float* __restrict__ x, const float* __restrict__ bias, unsigned C4, float scale,
@@ -650,9 +692,16 @@ extern "C" int woft_instance_norm_from_sums_f16(const void* x, const float* part
   in_finalize_sums_kernel<<<dim3(ceil_div(channels, 8), batch), 256, 0, s>>>(partial, rows, batch, stats, hw, channels, eps);
   const long long total4 = (long long)batch * hw * (channels / 4);
   WOFT_REQUIRE(total4 <= kMaxElems32, "woft_instance_norm_from_sums_f16: more than 2^31 - 1 vectors");
-  in_apply_nhwc_kernel<__half><<<ew_grid(total4), 256, 0, s>>>(static_cast<const __half*>(x), stats,
-                                                                static_cast<const __half*>(residual), static_cast<__half*>(y),
-                                                                hw, channels, relu, unsigned(total4));
+  const bool wide = channels % 8 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
+                                           reinterpret_cast<uintptr_t>(residual)) & 15) == 0;
+  if (wide)   // x == y allowed
+    in_apply_nhwc_h8_kernel<<<ew_grid(total4 / 2), 256, 0, s>>>(static_cast<const __half*>(x), stats,
+                                                                 static_cast<const __half*>(residual), static_cast<__half*>(y),
+                                                                 hw, channels, relu, unsigned(total4 / 2));
+  else
+    in_apply_nhwc_kernel<__half><<<ew_grid(total4), 256, 0, s>>>(static_cast<const __half*>(x), stats,
+                                                                  static_cast<const __half*>(residual), static_cast<__half*>(y),
+                                                                  hw, channels, relu, unsigned(total4));
   return launch_status("instance norm (from sums) kernels");
 }
 

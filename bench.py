@@ -175,7 +175,7 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
     t_build = time_launches(build, 5, scratch, torch)
     blk = holder["blk"]
     blk.check()
-    level_bytes = sum(l.numel() * 4 for l in blk.corr_pyramid)
+    level_bytes = sum(l.numel() * l.element_size() for l in blk.corr_pyramid)   # fp16 levels in the storage mode "fp16s"
     corr_bytes = 2 * f1.numel() * 4 + level_bytes
     ys, xs = torch.meshgrid(torch.arange(H, device=dev), torch.arange(W, device=dev), indexing="ij")
     grid = torch.stack([xs, ys]).float()[None]
@@ -231,7 +231,11 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
                     "14400 queries x 4 levels per launch; average over the 13 launches of one flow pass issued back to back "
                     "between one CUDA-event pair on the launch stream, L2 flushed before the pass (first launch cold, the "
                     "rest see what L2 kept, as inside a frame)")
-    k3["frac_on_bytes_moved"] = round((LOOKUP_BYTES_PER_QUERY - 648) * B * H * W / t_lookup_pass / 1e9 / hbm, 4)
+    # bytes this variant really moves per query: 4 levels x 10 x 10 footprint values (fp32, or fp16 in the storage mode),
+    # 8 B of coordinates, 324 fp16 outputs
+    moved = 4 * 100 * blk.corr_pyramid[0].element_size() + 8 + 648
+    k3["bytes_moved_per_query"] = moved
+    k3["frac_on_bytes_moved"] = round(moved * B * H * W / t_lookup_pass / 1e9 / hbm, 4)
     k3_f32 = entry(lookup_bytes, t_lookup_pass32, "corr_lookup")
     k3_f32["kernel"] = "K3 with the fp32 channels-last output, same 13-launch pass"
     k3_cold = entry(lookup_bytes, t_lookup_cold, "corr_lookup")
@@ -239,7 +243,8 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
     k3_b4 = entry(lookup_bytes * B4, t_lookup_b4)
     k3_b4["kernel"] = "K3 on a batch of 4 frame pairs (57600 queries, 4.4 GB pyramid), L2 flushed before every launch"
     k1 = entry(corr_bytes, t_build, "corr_pyramid_" + corr_mode)
-    k1["kernel"] = f"pack + corr_tc_kernel + row-mean (K1+K2), mode {corr_mode}; 106.2 GFLOP"
+    k1["kernel"] = (f"pack + corr_tc_kernel + row-mean (K1+K2), mode {corr_mode}; 106.2 GFLOP; algorithmic bytes = both feature "
+                    f"maps in + every level out once in the mode's storage format ({blk.corr_pyramid[0].element_size()} B per value)")
     k1["tflops"] = round(2.0 * (H * W) ** 2 * C / t_build / 1e12, 1)
     k4 = entry(h_bytes, t_h, "homography_fit_config3")
     k4["kernel"] = "homography_fit_kernel (K4), B=1024 x N=14400, nonhomogeneous"
@@ -568,7 +573,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["woft", "reference"], default="woft")
     ap.add_argument("--corr-mode", default=os.environ.get("WOFT_CORR_MODE", "fp16"),
-                    choices=["tf32", "tf32x3", "bf16", "fp16", "fp16x3", "fp32"])
+                    choices=["tf32", "tf32x3", "bf16", "fp16", "fp16s", "fp16x3", "fp32"])
     ap.add_argument("--workload", choices=["config2", "config4", "config5"], default="config2",
                     help="config2 (default): the headline frame-pair workload; config4 / config5: 8 sequences x --frames "
                          "frames at 1280x720 / 1920x1080 through the whole tracker, sequence-sharded over the ranks")

@@ -50,6 +50,11 @@ enum woft_corr_mode {
 /* OR-ed into `mode` of woft_corr_pyramid[_static] (tensor-core modes only): fmap1 / fmap2 are channels-last
  * (B, H, W, C) instead of (B, C, H, W), as a channels-last encoder leaves them; the result is the same volume. */
 #define WOFT_CORR_FMAPS_NHWC 0x100
+/* OR-ed into `mode` (tensor-core modes only): the pyramid levels are written as fp16 (IEEE half), each value rounded
+ * once from its fp32 accumulator / fp32 pooled mean -- half the bytes K1 writes and K3 gathers.  The `levels` pointers
+ * then address __half arrays of the same shapes; read them with woft_corr_lookup flag 32.  A stated-tolerance storage
+ * format (relative rounding 2^-11 per stored value), not the reference's fp32 volume. */
+#define WOFT_CORR_STORE_F16 0x200
 
 /* Estimators of pytracking/utils/least_squares_H.py served by woft_homography_fit (K4). */
 enum woft_h_method {
@@ -125,7 +130,8 @@ void woft_corr_set_trace_buffer(unsigned long long* device_buffer);
  *   flags  : bit 0 = scalar loads (testing); bit 3 (8) = write `out` channels-last, (B, H1, W1, channels), for an
  *            NHWC consumer (same values); bit 4 (16, with bit 3) = `out` holds fp16 with the channels of a query padded
  *            to a multiple of 8 (328 for 4 levels of radius 4; the padding is not written): the operand of an fp16
- *            tensor-core convolution, whose TMA loads need 16-byte multiples between pixels
+ *            tensor-core convolution, whose TMA loads need 16-byte multiples between pixels; bit 5 (32) = the levels hold
+ *            fp16 (written with WOFT_CORR_STORE_F16): interpolation in fp32 as before
  * Level maps narrower than 2 pixels make the reference return NaN (division by W-1 = 0, utils.py:63-64);
  * this call rejects them with WOFT_ERR_INVALID_ARGUMENT instead.
  */

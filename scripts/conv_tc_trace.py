@@ -7,7 +7,10 @@ import torch
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 from woft_b200 import _lib, conv_tc  # noqa: E402
 
+import os
+
 dev = "cuda:0"
+DBG = int(os.environ.get("CONV_DBG", "0"))
 H, W = 90, 160
 g = torch.Generator(device=dev).manual_seed(0)
 
@@ -39,7 +42,7 @@ for name, cin, cout, kh, kw, epi in (("convc1 1x1 324->256", 328, 256, 1, 1, 0),
     hbuf = cl(torch.randn((1, 128, H, W), generator=g, device=dev))
     z = cl(torch.rand((1, 128, H, W), generator=g, device=dev))
     tr = torch.zeros(8 * 148, dtype=torch.int64, device=dev)
-    kw_ = dict(trace=tr)
+    kw_ = dict(trace=tr, debug_flags=DBG)
     if epi == 0:
         kw_.update(relu=True, out=out)
     elif epi == 1:

@@ -22,6 +22,8 @@ from . import _lib
 #:            multiplies in fp32 (corr.py:67), and the split keeps full accuracy whatever the feature magnitudes are
 #:   "fp16"   tensor cores, operands rounded once to fp16 (10-bit mantissa like tf32, half the operand bytes, inputs
 #:            saturated at +-65504): opt-in, 0.05 px tolerance class
+#:   "fp16s"  the same arithmetic, and the pyramid itself is stored as fp16 (every level rounded once from fp32): half
+#:            the bytes K1 writes and K3 gathers; `corr_pyramid` then holds fp16 tensors
 #:   "tf32"   tensor cores, operands rounded to tf32        "bf16"  tensor cores, 7-bit mantissa
 #:   "tf32x3" tensor cores, the same with tf32 hi/lo planes (twice the operand bytes)
 #:   "fp32"   CUDA cores, the reference's own precision class
@@ -35,7 +37,8 @@ def _as_f32c(t):
 
 
 class CorrBlock:
-    """corr.py:12-69.  `corr_pyramid[l]` is a real (B*H*W, 1, H_l, W_l) fp32 tensor, as the weight head expects."""
+    """corr.py:12-69.  `corr_pyramid[l]` is a real (B*H*W, 1, H_l, W_l) tensor, as the weight head expects: fp32, or
+    fp16 in the storage mode "fp16s"."""
 
     def __init__(self, fmap1, fmap2, num_levels=4, radius=4, mode=None):
         _lib.require_cuda(fmap1, fmap2)
@@ -63,7 +66,9 @@ class CorrBlock:
             raise AssertionError(f"feature map {H}x{W} is too small for {num_levels} levels: "
                                  f"coarsest level would be {sizes[-1][0]}x{sizes[-1][1]}, need at least 2x2")
         with torch.cuda.device(dev):
-            self.corr_pyramid = [torch.empty((B * H * W, 1, h, w), device=dev, dtype=torch.float32) for h, w in sizes]
+            self.store_f16 = bool(_lib.CORR_MODES[self.mode] & _lib.CORR_STORE_F16)
+            level_dtype = torch.float16 if self.store_f16 else torch.float32
+            self.corr_pyramid = [torch.empty((B * H * W, 1, h, w), device=dev, dtype=level_dtype) for h, w in sizes]
             self._row_mean = torch.empty((B, H, W), device=dev, dtype=torch.float32)
             mode_id = _lib.CORR_MODES[self.mode] | (_lib.CORR_FMAPS_NHWC if nhwc else 0)
             nbytes = lib.woft_corr_workspace_bytes(B, C, H, W, mode_id)
@@ -95,7 +100,8 @@ class CorrBlock:
         with torch.cuda.device(dev):
             levels, keep = _lib.ptr_array(self.corr_pyramid)
             rc = _lib.load().woft_corr_lookup(levels, self.num_levels, _lib.ptr(coords), B, H, W, H, W, self.radius,
-                                              _lib.ptr(out), flags, _lib.current_stream(dev))
+                                              _lib.ptr(out), flags | (32 if self.corr_pyramid[0].dtype == torch.float16 else 0),
+                                              _lib.current_stream(dev))
             del keep
         _lib.check(rc, "woft_corr_lookup")
         return out

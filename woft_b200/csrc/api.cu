@@ -43,7 +43,7 @@ extern "C" const char* woft_last_error(void) { return woft::last_error_buffer();
 
 extern "C" size_t woft_corr_workspace_bytes(int batch, int channels, int height, int width, int mode) {
   if (batch <= 0 || channels <= 0 || height <= 0 || width <= 0) return 0;
-  mode &= ~WOFT_CORR_FMAPS_NHWC;
+  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16);
   if (mode == WOFT_CORR_FP32_SIMT) return woft::simt_workspace_bytes(batch, channels);
   return woft::corr_tc_workspace_bytes(batch, channels, height * width, mode);
 }
@@ -57,11 +57,12 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
   WOFT_REQUIRE(num_levels >= 1 && num_levels <= kMaxLevels, "woft_corr_pyramid: num_levels %d not in [1,%d]",
                num_levels, kMaxLevels);
   const bool fmaps_nhwc = (mode & WOFT_CORR_FMAPS_NHWC) != 0;
+  const bool store_f16 = (mode & WOFT_CORR_STORE_F16) != 0;
   const int mode_flags = mode;
-  mode &= ~WOFT_CORR_FMAPS_NHWC;
+  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16);
   WOFT_REQUIRE(mode >= WOFT_CORR_FP32_SIMT && mode <= WOFT_CORR_FP16X3, "woft_corr_pyramid: unknown mode %d", mode);
-  WOFT_REQUIRE(!(fmaps_nhwc && mode == WOFT_CORR_FP32_SIMT),
-               "woft_corr_pyramid: channels-last feature maps need one of the tensor-core modes");
+  WOFT_REQUIRE(!((fmaps_nhwc || store_f16) && mode == WOFT_CORR_FP32_SIMT),
+               "woft_corr_pyramid: channels-last feature maps and fp16 storage need one of the tensor-core modes");
   WOFT_REQUIRE((long long)batch * height * width < (1ll << 31), "woft_corr_pyramid: too many query pixels");
   for (int l = 0, h = height, w = width; l < num_levels; ++l, h /= 2, w /= 2) {
     WOFT_REQUIRE(h >= 1 && w >= 1, "woft_corr_pyramid: level %d is empty", l);

@@ -44,6 +44,7 @@ constexpr int CT_MAX_STAGES = 8;
 constexpr int CT_MAX_TAPS = 25;
 constexpr int CT_SMEM_LIMIT = 232448;
 constexpr int CT_STAT_C = 128;     // widest output for which the epilogue gathers instance-norm sums
+__host__ __device__ constexpr int ct_stage_bytes(int) { return 2048; }   // per epilogue warp
 constexpr int CT_MAX_BIAS = 640;   // padded Cout of one launch (the mask head's 576 is the largest)
 
 enum { CT_EPI_BIAS_ACT = 0, CT_EPI_GRU_ZR = 1, CT_EPI_GRU_Q = 2, CT_EPI_HEAD_MEAN = 3, CT_EPI_FLOW_TAPS = 4 };
@@ -200,6 +201,15 @@ __device__ __forceinline__ bool ct_tile_at(const ConvTcParams& p, int it, uint32
 // tanhf and the IEEE division are dozens with a slow-path call -- the epilogue is issue-bound, not accuracy-bound
 __device__ __forceinline__ float ct_sigmoid(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
 __device__ __forceinline__ float ct_tanh(float x) { return 1.0f - __fdividef(2.0f, 1.0f + __expf(2.0f * x)); }
+// one MUFU instruction (relative error 2^-11, the rounding of the fp16 operands these values become); sigmoid through
+// tanh: sigma(x) = 0.5 tanh(x / 2) + 0.5.  The GRU epilogues use them (p.dbg bit 64) unless WOFT_CONV_FAST_GATES=0:
+// same end-point error against the CPU oracle (0.0046 px at 1280x720), 1 % more frames per second
+__device__ __forceinline__ float ct_tanh_mufu(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ct_sigmoid_mufu(float x) { return fmaf(0.5f, ct_tanh_mufu(0.5f * x), 0.5f); }
 
 // 32 consecutive channels of one pixel, fp32 or fp16 destination; `nv` < 32 only in the last channel block
 __device__ __forceinline__ void ct_store_row(void* base, long long stride, long long pix, int col, const float* v, int nv,
@@ -361,6 +371,60 @@ __device__ __forceinline__ void ct_store_tile(void* base, long long stride, int 
   }
 }
 
+// ---- the GRU epilogues work in the coalesced layout itself ---------------------------------------------------------
+// A 32-pixel x 32-channel fp32 block is 32 rows of 128 bytes.  Lane l owns the 16-byte piece l & 7 of rows
+// (l >> 3) + 4 i, i = 0..7: a warp access covers four whole 128-byte lines.  Only the accumulator has to be brought into
+// this layout (two 16-row passes through the warp's 2 KB buffer, 16-byte pieces XOR-swizzled by the row); h, z and the results
+// are read and written by plain vector accesses whose latencies overlap, where the row-per-thread form needed a
+// shared-memory round trip (and two global round trips) per operand.  rp8[i]: pixel index of row (l >> 3) + 4 i or -1.
+__device__ __forceinline__ void ct_to_coalesced(float* v, uint8_t* stg, int lane) {
+  float o[32];
+#pragma unroll
+  for (int hb = 0; hb < 2; ++hb) {   // rows 16 hb .. 16 hb + 15 through the 2 KB buffer
+    if ((lane >> 4) == hb) {
+      const int r = lane & 15;
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(stg + r * 128 + ((j ^ (r & 7)) << 4)) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = (lane >> 3) + 4 * i;
+      const float4 t = *reinterpret_cast<const float4*>(stg + r * 128 + (((lane & 7) ^ (r & 7)) << 4));
+      o[16 * hb + 4 * i] = t.x; o[16 * hb + 4 * i + 1] = t.y; o[16 * hb + 4 * i + 2] = t.z; o[16 * hb + 4 * i + 3] = t.w;
+    }
+    __syncwarp();
+  }
+#pragma unroll
+  for (int j = 0; j < 32; ++j) v[j] = o[j];
+}
+__device__ __forceinline__ void ct_ld_coalesced(const float* base, long long stride, int col, const int* rp8, int lane, float* o) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (rp8[i] >= 0) t = *reinterpret_cast<const float4*>(base + (long long)rp8[i] * stride + col + (lane & 7) * 4);
+    o[4 * i] = t.x; o[4 * i + 1] = t.y; o[4 * i + 2] = t.z; o[4 * i + 3] = t.w;
+  }
+}
+__device__ __forceinline__ void ct_st_coalesced(void* base, long long stride, int col, const int* rp8, int lane, const float* v,
+                                                bool f16) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    if (rp8[i] < 0) continue;
+    if (f16) {
+      const __half2 a = __floats2half2_rn(v[4 * i], v[4 * i + 1]), b = __floats2half2_rn(v[4 * i + 2], v[4 * i + 3]);
+      uint2 u;
+      u.x = *reinterpret_cast<const uint32_t*>(&a);
+      u.y = *reinterpret_cast<const uint32_t*>(&b);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__half*>(base) + (long long)rp8[i] * stride + col + (lane & 7) * 4) = u;
+    } else {
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(base) + (long long)rp8[i] * stride + col + (lane & 7) * 4) =
+          make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+    }
+  }
+}
+
 // 32 fp32 channels [col, col + 32) of the warp's 32 pixels, each thread ending up with its own pixel's values
 __device__ __forceinline__ void ct_load_tile(const float* base, long long stride, int col, float* v, uint8_t* stg, int lane,
                                              const int* rp) {
@@ -398,7 +462,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
   float* s_bias = reinterpret_cast<float*>(sB + p.stages * p.b_bytes);   // CT_MAX_BIAS floats
   float* s_red = s_bias + CT_MAX_BIAS;                                   // 2 x 128 floats (HEAD_MEAN)
   uint8_t* s_stage = reinterpret_cast<uint8_t*>(s_red + 256);            // 8 warps x 2 KB
-  float* s_stat = reinterpret_cast<float*>(s_stage + 8 * 2048);         // [8 warps][2 images][sum | squares][CT_STAT_C],
+  float* s_stat = reinterpret_cast<float*>(s_stage + 8 * ct_stage_bytes(EPI));         // [8 warps][2 images][sum | squares][CT_STAT_C],
   // only when gathered; FLOW_TAPS: the second-layer filter lies over the (unused) staging buffer and 8 KB behind it
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_stat + (EPI == CT_EPI_FLOW_TAPS ? 2048 : p.stats ? 8 * 4 * CT_STAT_C : 0));
   float* s_w2 = reinterpret_cast<float*>(s_stage);
@@ -723,6 +787,27 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     for (; ct_tile_at(p, it, rank, tc); ++it) {
       const int buf = it & 1;
       const uint32_t use = uint32_t(it >> 1);
+      const int x = tc.x0 + xi, y = tc.y0 + yj;
+      const bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H && tc.n < p.NB;
+      const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
+      const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
+      uint8_t* stg = s_stage + (warp - 2) * ct_stage_bytes(EPI);
+      const bool co = p.coalesce != 0;
+      constexpr bool GRU = EPI == CT_EPI_GRU_ZR || EPI == CT_EPI_GRU_Q;
+      // GRU epilogues, coalesced layout: the first chunk's h (and z) are requested before the accumulator is waited for
+      int rp8[8];
+      float hc[32], zc[32];
+      const int hid = p.bn >> 1;
+      // gates: this warp's chunks in the order r, r, z, z (the r chunks need h); blend: ascending
+      const int first_c = EPI == CT_EPI_GRU_ZR ? half + 4 : half;
+      if (GRU && co) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) rp8[i] = __shfl_sync(0xffffffffu, valid ? int(pix) : -1, (lane >> 3) + 4 * i);
+        if (first_c < chunks && !(p.dbg & 32)) {   // dbg 32: experiment without the early request
+          ct_ld_coalesced(p.h, p.h_stride, tc.c0 + first_c * 32 - (EPI == CT_EPI_GRU_ZR ? hid : 0), rp8, lane, hc);
+          if (EPI == CT_EPI_GRU_Q) ct_ld_coalesced(p.z, p.z_stride, tc.c0 + first_c * 32, rp8, lane, zc);
+        }
+      }
       if (leader) *epi_go = ct_wait(tfull + buf, use & 1u) ? 1 : 0;
       if (leader) ct_tile_stamp(p, it, 4);
       ptx::named_bar_sync(1, CT_EPI_THREADS);
@@ -730,15 +815,86 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       ptx::tc_fence_after_sync();
       if (leader) ct_tile_stamp(p, it, 5);
       if (leader && it == 0) ct_stamp(p, 4);
-      const int x = tc.x0 + xi, y = tc.y0 + yj;
-      const bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H && tc.n < p.NB;
-      const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
-      const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
-      uint8_t* stg = s_stage + (warp - 2) * 2048;
+      if (GRU && co) {
+        const int q4 = (lane & 7) * 4;
+        const bool fast_gates = (p.dbg & 64) != 0;
+        const int mine = (chunks - half + 1) >> 1;   // chunks of this warp
+#pragma unroll 1
+        for (int ci = 0; ci < mine; ++ci) {
+          // gates with 8 chunks: order half+4, half+6, half, half+2; otherwise ascending
+          const int c = (EPI == CT_EPI_GRU_ZR && chunks == 8) ? half + 2 * ((ci + 2) & 3) : half + 2 * ci;
+          const int col = tc.c0 + c * 32;
+          float v[32];
+#define CT_ESTAMP(j) if ((p.dbg & 16) && p.trace && blockIdx.x == 0 && leader && it == 0) p.trace[64 + 8 * ci + (j)] = clock64();
+          CT_ESTAMP(0)
+          ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * 256 + c * 32), v);
+          CT_ESTAMP(1)
+          if (ci == mine - 1) {   // this warp's share of the accumulator is read, hand it back
+            ptx::tc_fence_before_sync();
+            if (PAIR)
+              ptx::mbar_arrive_cluster(lead_tempty[buf]);
+            else
+              ptx::mbar_arrive(tempty + buf);
+          }
+          ct_to_coalesced(v, stg, lane);
+          CT_ESTAMP(2)
+          const float4 b4 = *reinterpret_cast<const float4*>(s_bias + col + q4);
+          const float bb[4] = {b4.x, b4.y, b4.z, b4.w};
+          if (EPI == CT_EPI_GRU_ZR) {
+            if (col < hid) {
+              if (fast_gates) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid_mufu(v[j] + bb[j & 3]);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bb[j & 3]);
+              }
+              ct_st_coalesced(p.z, p.z_stride, col, rp8, lane, v, false);
+            } else {
+              if (c != first_c || (p.dbg & 32)) ct_ld_coalesced(p.h, p.h_stride, col - hid, rp8, lane, hc);
+              if (fast_gates) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid_mufu(v[j] + bb[j & 3]) * hc[j];
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = ct_sigmoid(v[j] + bb[j & 3]) * hc[j];
+              }
+              ct_st_coalesced(p.out, p.out_stride, col - hid, rp8, lane, v, p.out_f16 != 0);
+            }
+          } else {
+            if (c != first_c || (p.dbg & 32)) {
+              ct_ld_coalesced(p.h, p.h_stride, col, rp8, lane, hc);
+              ct_ld_coalesced(p.z, p.z_stride, col, rp8, lane, zc);
+            }
+            if (__float_as_int(hc[0]) == 0x7fc12345 && __float_as_int(zc[31]) == 0x7fc12345) CT_ESTAMP(7)   // forces the loads to have landed
+            CT_ESTAMP(3)
+            if (fast_gates) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = fmaf(zc[j], ct_tanh_mufu(v[j] + bb[j & 3]) - hc[j], hc[j]);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = (1.f - zc[j]) * hc[j] + zc[j] * ct_tanh(v[j] + bb[j & 3]);
+            }
+            CT_ESTAMP(4)
+            ct_st_coalesced(p.out, p.out_stride, col, rp8, lane, v, false);
+            if (p.out2) ct_st_coalesced(p.out2, p.out2_stride, col, rp8, lane, v, p.out2_f16 != 0);
+            CT_ESTAMP(5)
+          }
+        }
+        if (mine == 0) {
+          ptx::tc_fence_before_sync();
+          if (PAIR)
+            ptx::mbar_arrive_cluster(lead_tempty[buf]);
+          else
+            ptx::mbar_arrive(tempty + buf);
+        }
+        if (leader && it == 0) ct_stamp(p, 5);
+        if (leader) ct_tile_stamp(p, it, 6);
+        continue;
+      }
       int rp[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) rp[i] = __shfl_sync(0xffffffffu, valid ? int(pix) : -1, (lane >> 2) + 8 * i);
-      const bool co = p.coalesce != 0;
       if (EPI == CT_EPI_FLOW_TAPS) {
         // FlowHead (update.py:6-14): relu(conv1) never leaves the SM.  The second, 3x3 -> 2-channel convolution is
         // linear, so every pixel's 18 (tap, output) products with its own 256 activations are formed here and a small
@@ -1039,7 +1195,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       }
   }
   const int taps = a->kh * a->kw;
-  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * 2048 +
+  const int fixed = 1024 + (CT_MAX_BIAS + 256) * 4 + 8 * ct_stage_bytes(a->epilogue) +
                     (a->epilogue == CT_EPI_FLOW_TAPS ? 8192 : a->stats ? 8 * 4 * CT_STAT_C * 4 : 0) + 256;
   int a_stage = CT_A_STAGE;
   if (a->halo) {
@@ -1133,6 +1289,11 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   p.residual = a->residual;
   p.residual_stride = a->residual_stride;
   p.dbg = a->debug_flags;
+  static const bool fast_gates_env = [] {   // WOFT_CONV_FAST_GATES=0: ex2/rcp-based GRU gates instead of tanh.approx
+    const char* e = getenv("WOFT_CONV_FAST_GATES");
+    return !(e && e[0] == '0');
+  }();
+  if (fast_gates_env) p.dbg |= 64;
   p.pdl = (a->pdl && pdl_enabled()) ? 1 : 0;
 
   const int oesz = a->out_f16 ? 2 : 4;
@@ -1223,7 +1384,9 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     const int v = e ? atoi(e) : CT_MAX_PRODUCERS;
     return v < 1 ? 1 : v > CT_MAX_PRODUCERS ? CT_MAX_PRODUCERS : v;
   }();
-  p.producers = p.halo ? 1 : (producers_env < stages ? producers_env : stages);
+  // several TMA warps pay off when a CTA walks many tiles (the issue latency of one thread bounds the k-step rate); with
+  // one tile per CTA they only delay the first stage's arrival (three boxes share the start-up bandwidth): 0.3 us later
+  p.producers = 1;   // decided below, once the grid is known
   // always more than half of the SM's shared memory: one CTA per SM, which owns all 512 TMEM columns
   int smem = p.a_stages * a_stage + stages * p.b_bytes + fixed;
   if (smem < 120 * 1024) smem = 120 * 1024;
@@ -1236,6 +1399,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
     grid = 2 * pairs;
   }
   WOFT_REQUIRE(grid >= 1, "woft_conv_tc: empty grid");
+  if (!p.halo && p.total_tiles > grid) p.producers = producers_env < stages ? producers_env : stages;
   if (a->stats) {
     // every CTA writes its partial sums; the rows of CTAs that do not exist in this launch are cleared
     WOFT_REQUIRE(p.coalesce && !p.pair, "woft_conv_tc: statistics need 16-byte aligned outputs and single-CTA mode");

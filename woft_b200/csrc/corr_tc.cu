@@ -59,11 +59,12 @@ struct CorrTcParams {
   CUtensorMap tmA;                   // (Kp, HW, B*planes), box (Kblk, 128, 1)
   CUtensorMap tmB;                   // (Kp, W, H, B*planes), box (Kblk, 32, 8, 1)
   CUtensorMap tmOut[kMaxTcLevels];   // (W_l, H_l, HW, B), box (32 >> l, 1, 128, 1)
-  float* level[kMaxTcLevels];
+  float* level[kMaxTcLevels];   // __half* when out_f16
   int lh[kMaxTcLevels];
   int lw[kMaxTcLevels];
   int tma_ok[kMaxTcLevels];
   int num_levels;
+  int out_f16;   // levels stored as fp16 (WOFT_CORR_STORE_F16)
   int B, HW, H, W;
   int m_tiles, h_tiles, w_tiles, total_tiles;
   int k_blocks;   // 128-byte K rows per plane
@@ -226,6 +227,47 @@ __device__ __forceinline__ TileCoord decode_tile(const CorrTcParams& p, int t) {
 
 // swizzled staging of one pooled/unpooled row of NV fp32 values (NV*4 bytes per query) for a TMA store whose
 // box is (NV, 1, 128): 16-byte chunk index XOR-ed the way CU_TENSOR_MAP_SWIZZLE_{128,64,32}B expects.
+// the same for fp16 storage: NV halves = NV*2 bytes per query, 16-byte chunks of 8 values
+template <int NV>
+__device__ __forceinline__ void stage_row_h(uint8_t* sub_slot, int m, const float* v) {
+  constexpr int RB = NV * 2, CH = RB / 16;
+  uint8_t* row = sub_slot + m * RB;
+  const int x = (RB == 64) ? ((m >> 1) & 3) : (RB == 32) ? ((m >> 2) & 1) : 0;
+#pragma unroll
+  for (int c = 0; c < CH; ++c) {
+    uint4 u;
+    __half2 h0 = __floats2half2_rn(v[8 * c], v[8 * c + 1]), h1 = __floats2half2_rn(v[8 * c + 2], v[8 * c + 3]);
+    __half2 h2 = __floats2half2_rn(v[8 * c + 4], v[8 * c + 5]), h3 = __floats2half2_rn(v[8 * c + 6], v[8 * c + 7]);
+    u.x = *reinterpret_cast<uint32_t*>(&h0);
+    u.y = *reinterpret_cast<uint32_t*>(&h1);
+    u.z = *reinterpret_cast<uint32_t*>(&h2);
+    u.w = *reinterpret_cast<uint32_t*>(&h3);
+    *reinterpret_cast<uint4*>(row + ((c ^ x) << 4)) = u;
+  }
+}
+template <int NV>
+__device__ __forceinline__ void direct_row_h(float* level_, int lh, int lw, int HW, int b, int m, int h, int w0,
+                                             const float* v) {
+  if (m >= HW || h >= lh) return;
+  __half* dst = reinterpret_cast<__half*>(level_) + (((size_t)b * HW + m) * lh + h) * lw;
+  if ((lw & 3) == 0 && (reinterpret_cast<uintptr_t>(level_) & 7) == 0) {
+    // rows are 8-byte aligned and a 4-value chunk is wholly inside or outside the map
+#pragma unroll
+    for (int j = 0; j < NV; j += 4)
+      if (w0 + j < lw) {
+        __half2 a = __floats2half2_rn(v[j], v[j + 1]), c = __floats2half2_rn(v[j + 2], v[j + 3]);
+        uint2 u;
+        u.x = *reinterpret_cast<uint32_t*>(&a);
+        u.y = *reinterpret_cast<uint32_t*>(&c);
+        *reinterpret_cast<uint2*>(dst + w0 + j) = u;
+      }
+    return;
+  }
+#pragma unroll
+  for (int j = 0; j < NV; ++j)
+    if (w0 + j < lw) dst[w0 + j] = __float2half_rn(v[j]);
+}
+
 template <int NV>
 __device__ __forceinline__ void stage_row(uint8_t* sub_slot, int m, const float* v) {
   constexpr int CH = NV / 4;  // 16-byte chunks per query row
@@ -436,6 +478,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
     const int m = (warp & 3) * 32 + lane;         // TMEM lane == query row of the tile
     const uint32_t lane_base = uint32_t((warp & 3) * 32) << 16;
     const float scale = p.scale;
+    const bool f16o = p.out_f16 != 0;
     uint32_t ev = 0;  // ring event counter (identical in all epilogue threads)
     int it = 0;
     bool go = true;
@@ -469,8 +512,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
         for (int j = 0; j < 32; ++j) v[j] *= scale;
         uint8_t* slot = ring + (ev % NSLOT) * SLOT;
         if (p.tma_ok[0]) {
-          stage_row<32>(slot, m, v);
+          if (f16o)
+            stage_row_h<32>(slot, m, v);
+          else
+            stage_row<32>(slot, m, v);
           ptx::fence_proxy_async_smem();
+        } else if (f16o) {
+          direct_row_h<32>(p.level[0], p.lh[0], p.lw[0], p.HW, tc.b, mq, tc.h0 + r, tc.w0, v);
         } else {
           direct_row<32>(p.level[0], p.lh[0], p.lw[0], p.HW, tc.b, mq, tc.h0 + r, tc.w0, v);
         }
@@ -498,10 +546,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
 #pragma unroll
           for (int rr = 0; rr < 2; ++rr) {
             const int r1 = half * 2 + rr;
-            if (p.tma_ok[1])
-              stage_row<16>(slot + rr * 8192, m, l1[r1]);
-            else
+            if (p.tma_ok[1]) {
+              if (f16o)
+                stage_row_h<16>(slot + rr * 8192, m, l1[r1]);
+              else
+                stage_row<16>(slot + rr * 8192, m, l1[r1]);
+            } else if (f16o) {
+              direct_row_h<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, tc.h0 / 2 + r1, tc.w0 / 2, l1[r1]);
+            } else {
               direct_row<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, tc.h0 / 2 + r1, tc.w0 / 2, l1[r1]);
+            }
           }
           if (p.tma_ok[1]) {  // (kernel parameter: uniform) no ring event when the level goes out by direct stores
             ptx::fence_proxy_async_smem();
@@ -531,14 +585,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
         uint8_t* slot = ring + (ev % NSLOT) * SLOT;
 #pragma unroll
         for (int i = 0; i < 2; ++i) {
-          if (p.tma_ok[2])
-            stage_row<8>(slot + i * 4096, m, l2[i]);
-          else
+          if (p.tma_ok[2]) {
+            if (f16o)
+              stage_row_h<8>(slot + i * 4096, m, l2[i]);
+            else
+              stage_row<8>(slot + i * 4096, m, l2[i]);
+          } else if (f16o) {
+            direct_row_h<8>(p.level[2], p.lh[2], p.lw[2], p.HW, tc.b, mq, tc.h0 / 4 + i, tc.w0 / 4, l2[i]);
+          } else {
             direct_row<8>(p.level[2], p.lh[2], p.lw[2], p.HW, tc.b, mq, tc.h0 / 4 + i, tc.w0 / 4, l2[i]);
+          }
         }
         if (p.num_levels > 3) {
-          if (p.tma_ok[3])
+          if (p.tma_ok[3])   // never with fp16 storage: a 4-value row is 8 bytes, below TMA's 16-byte granule
             stage_row<4>(slot + 8192, m, l3);
+          else if (f16o)
+            direct_row_h<4>(p.level[3], p.lh[3], p.lw[3], p.HW, tc.b, mq, tc.h0 / 8, tc.w0 / 8, l3);
           else
             direct_row<4>(p.level[3], p.lh[3], p.lw[3], p.HW, tc.b, mq, tc.h0 / 8, tc.w0 / 8, l3);
         }
@@ -629,7 +691,8 @@ TcLayout tc_layout(int B, int C, int HW, int mode) {
 int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H, int W, int num_levels,
                     float* const* levels, void* workspace, int mode, cudaStream_t stream) {
   const bool fmaps_nhwc = (mode & WOFT_CORR_FMAPS_NHWC) != 0;
-  mode &= ~WOFT_CORR_FMAPS_NHWC;
+  const bool store_f16 = (mode & WOFT_CORR_STORE_F16) != 0;
+  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16);
   if (num_levels > kMaxTcLevels)
     return fail(WOFT_ERR_UNSUPPORTED, "tensor-core correlation supports at most %d levels (8x32 pooling tile)",
                 kMaxTcLevels);
@@ -702,21 +765,25 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
     p.level[l] = levels[l];
     p.lh[l] = h;
     p.lw[l] = w;
-    const CUtensorMapSwizzle swz = l == 0   ? CU_TENSOR_MAP_SWIZZLE_128B
-                                   : l == 1 ? CU_TENSOR_MAP_SWIZZLE_64B
-                                   : l == 2 ? CU_TENSOR_MAP_SWIZZLE_32B
-                                            : CU_TENSOR_MAP_SWIZZLE_NONE;
+    const int row_bytes = (TW >> l) * (store_f16 ? 2 : 4);   // one query's row of the tile at this level
+    const CUtensorMapSwizzle swz = row_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                                   : row_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                   : row_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                                     : CU_TENSOR_MAP_SWIZZLE_NONE;
     cuuint64_t dims[4] = {(cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)HW, (cuuint64_t)B};
     cuuint32_t box[4] = {(cuuint32_t)(TW >> l), 1, BM, 1};
     const int tma_levels = tc_knobs().tma_levels;  // bit l set => level l may use TMA stores
-    p.tma_ok[l] = (((tma_levels >> l) & 1) && h > 0 && w > 0 && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0 &&
-                   encode(enc, &p.tmOut[l], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, 4, levels[l], dims, box, swz))
+    p.tma_ok[l] = (((tma_levels >> l) & 1) && h > 0 && w > 0 && row_bytes >= 16 &&
+                   (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0 &&
+                   encode(enc, &p.tmOut[l], store_f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32,
+                          store_f16 ? 2 : 4, 4, levels[l], dims, box, swz))
                       ? 1
                       : 0;
     h /= 2;
     w /= 2;
   }
   p.num_levels = num_levels;
+  p.out_f16 = store_f16 ? 1 : 0;
   p.B = B;
   p.HW = HW;
   p.H = H;

@@ -27,7 +27,7 @@
 namespace woft {
 
 struct LookupParams {
-  const float* level[kMaxLevels];
+  const float* level[kMaxLevels];   // const __half* in the instantiations for fp16 storage (flag 32)
   int lh[kMaxLevels];
   int lw[kMaxLevels];
   int num_levels;
@@ -53,7 +53,18 @@ struct LookupGeom {
   static constexpr int ROWS_PER_THREAD = (ROWS + kLookupThreads - 1) / kLookupThreads;
 };
 
-template <int R, bool VEC, bool NHWC>
+// four consecutive level values at an index that is a multiple of 4 (16-byte / 8-byte aligned), and one value
+__device__ __forceinline__ float4 lk_ld4(const float* row, int x) { return __ldg(reinterpret_cast<const float4*>(row + x)); }
+__device__ __forceinline__ float4 lk_ld4(const __half* row, int x) {
+  const uint2 u = __ldg(reinterpret_cast<const uint2*>(row + x));
+  const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&u.x)), b = __half22float2(*reinterpret_cast<const __half2*>(&u.y));
+  return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ float lk_ld1(const float* row, int x) { return __ldg(row + x); }
+__device__ __forceinline__ float lk_ld1(const __half* row, int x) { return __half2float(row[x]); }
+
+// T: element type of the pyramid levels (float, or __half as written with WOFT_CORR_STORE_F16)
+template <int R, bool VEC, bool NHWC, typename T = float>
 __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __grid_constant__ LookupParams p) {
   using G = LookupGeom<R>;
   constexpr int P = G::P, WIN = G::WIN, STRIDE = G::STRIDE;
@@ -103,7 +114,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
       const int x0 = s_x0[sq & (kLevelsPerPass * kQueriesPerCta - 1)];
       const int y = s_y0[sq & (kLevelsPerPass * kQueriesPerCta - 1)] + r;
       const bool row_in = live && y >= 0 && y < H;
-      const float* row = p.level[lvc] + ((size_t)(q0 + ql) * H + (row_in ? y : 0)) * W;
+      const T* row = reinterpret_cast<const T*>(p.level[lvc]) + ((size_t)(q0 + ql) * H + (row_in ? y : 0)) * W;
       if (VEC) {
         const int xa = x0 & ~3;
         const int sh = x0 - xa;
@@ -112,7 +123,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
           const int xc = xa + 4 * k;
           const bool need = (4 * k < sh + WIN);  // the last chunk is only touched for the largest shifts
           float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (row_in && need && xc >= 0 && xc < W) c = __ldg(reinterpret_cast<const float4*>(row + xc));
+          if (row_in && need && xc >= 0 && xc < W) c = lk_ld4(row, xc);
           vals[j][4 * k] = c.x;
           vals[j][4 * k + 1] = c.y;
           vals[j][4 * k + 2] = c.z;
@@ -122,7 +133,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
 #pragma unroll
         for (int c = 0; c < WIN; ++c) {
           const int xx = x0 + c;
-          vals[j][c] = (row_in && xx >= 0 && xx < W) ? __ldg(row + xx) : 0.f;
+          vals[j][c] = (row_in && xx >= 0 && xx < W) ? lk_ld1(row, xx) : 0.f;
         }
       }
     }
@@ -248,10 +259,18 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
 }
 
 template <int R>
-static int launch_lookup(const LookupParams& p, bool vec, bool nhwc, cudaStream_t stream) {
+static int launch_lookup(const LookupParams& p, bool vec, bool nhwc, bool f16_levels, cudaStream_t stream) {
   const dim3 grid(ceil_div(p.nq, kQueriesPerCta)), block(kLookupThreads);
   cudaError_t e;
-  if (vec && nhwc)
+  if (f16_levels && vec && nhwc)
+    e = launch_pdl(corr_lookup_kernel<R, true, true, __half>, grid, block, 0, stream, p);
+  else if (f16_levels && vec)
+    e = launch_pdl(corr_lookup_kernel<R, true, false, __half>, grid, block, 0, stream, p);
+  else if (f16_levels && nhwc)
+    e = launch_pdl(corr_lookup_kernel<R, false, true, __half>, grid, block, 0, stream, p);
+  else if (f16_levels)
+    e = launch_pdl(corr_lookup_kernel<R, false, false, __half>, grid, block, 0, stream, p);
+  else if (vec && nhwc)
     e = launch_pdl(corr_lookup_kernel<R, true, true>, grid, block, 0, stream, p);
   else if (vec)
     e = launch_pdl(corr_lookup_kernel<R, true, false>, grid, block, 0, stream, p);
@@ -280,6 +299,8 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   int h = h2, w = w2;
   bool vec = (flags & 1) == 0;  // flags bit 0 forces the scalar load path (testing)
   const bool nhwc = (flags & 8) != 0;  // flags bit 3: channels-last output (B, H1, W1, L*P*P)
+  const bool f16_levels = (flags & 32) != 0;   // the levels hold fp16 (WOFT_CORR_STORE_F16)
+  WOFT_REQUIRE(!(f16_levels && (flags & 64)), "woft_corr_lookup: the TMA variant (flag 64) reads fp32 levels");
   for (int l = 0; l < num_levels; ++l) {
     // the reference divides by (W-1), (H-1) and returns NaN for 1-pixel maps (utils.py:63-64)
     WOFT_REQUIRE(h >= 2 && w >= 2, "woft_corr_lookup: level %d is %dx%d; every level must be at least 2x2", l, h, w);
@@ -287,7 +308,7 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
     p.level[l] = levels[l];
     p.lh[l] = h;
     p.lw[l] = w;
-    vec = vec && (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0);
+    vec = vec && (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(levels[l]) & (f16_levels ? 7 : 15)) == 0);
     h /= 2;
     w /= 2;
   }
@@ -311,9 +332,9 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
     if (rc != WOFT_ERR_UNSUPPORTED) return rc;
   }
   switch (radius) {
-    case 1: return launch_lookup<1>(p, vec, nhwc, s);
-    case 2: return launch_lookup<2>(p, vec, nhwc, s);
-    case 3: return launch_lookup<3>(p, vec, nhwc, s);
-    default: return launch_lookup<4>(p, vec, nhwc, s);
+    case 1: return launch_lookup<1>(p, vec, nhwc, f16_levels, s);
+    case 2: return launch_lookup<2>(p, vec, nhwc, f16_levels, s);
+    case 3: return launch_lookup<3>(p, vec, nhwc, f16_levels, s);
+    default: return launch_lookup<4>(p, vec, nhwc, f16_levels, s);
   }
 }

@@ -823,6 +823,30 @@ def test_weight_head_first_layer_kernel():
         torch.backends.cudnn.allow_tf32 = old
 
 
+def test_weight_head_first_layer_stacked_fp16():
+    """woft_weight_head_conv1_stacked_f16: the same layer written as fp16 into the stacked layout of the tensor-core layers
+    (ten rows of nine pixels per image, the tenth zero) -- it must be the fp32 kernel's result rounded once, nothing
+    outside the images' rows touched except the zero rows."""
+    from woft_b200 import _lib
+    lib = _lib.load()
+    g = torch.Generator().manual_seed(16)
+    for n in (1, 37, 1000):
+        window = torch.randn((n, 81 * 4), generator=g).to(DEV)
+        mr = torch.randn((n,), generator=g).to(DEV)
+        w = (torch.randn((128, 5, 3, 3), generator=g) * 0.2).to(DEV)
+        b = torch.randn((128,), generator=g).to(DEV)
+        ref = torch.empty((n, 81, 128), device=DEV)
+        assert lib.woft_weight_head_conv1(_lib.ptr(window), _lib.ptr(mr), _lib.ptr(w), _lib.ptr(b), n, 9, 4, 128,
+                                          _lib.ptr(ref), _lib.current_stream(torch.device(DEV))) == 0
+        out = torch.full((n * 90 * 128 + 256,), 7.0, device=DEV, dtype=torch.float16)
+        assert lib.woft_weight_head_conv1_stacked_f16(_lib.ptr(window), _lib.ptr(mr), _lib.ptr(w), _lib.ptr(b), n, 9, 4, 128,
+                                                      _lib.ptr(out), _lib.current_stream(torch.device(DEV))) == 0
+        assert (out[n * 90 * 128:] == 7.0).all()
+        st = out[:n * 90 * 128].view(n, 90, 128)
+        assert torch.equal(st[:, :81], ref.half())
+        assert (st[:, 81:] == 0).all()
+
+
 def test_convex_upsample_kernel():
     from woft_b200.fast_net import convex_upsample_both
     from woft_b200.raft_net import convex_upsample

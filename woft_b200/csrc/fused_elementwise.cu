@@ -366,43 +366,68 @@ __global__ void in_apply_nhwc_kernel(const T* __restrict__ x, const float* __res
 
 // fp16, channels a multiple of 8: 16 bytes per thread and access.  x and y may be the same tensor (the normalisation of
 // the encoders runs in place, so the tensor crosses L2 once instead of twice); neither is declared restrict.
-__global__ void in_apply_nhwc_h8_kernel(const __half* x, const float* __restrict__ stats, const __half* __restrict__ residual,
-                                        __half* y, unsigned HW, unsigned C, int relu, unsigned total8) {
+__global__ void __launch_bounds__(256) in_apply_nhwc_h8_kernel(const __half* x, const float* __restrict__ stats,
+                                                               const __half* __restrict__ residual, __half* y, unsigned HW,
+                                                               unsigned C, int relu, unsigned total8) {
   const unsigned c8n = C >> 3;
   const unsigned per_image = HW * c8n;
   const float floor_ = relu ? 0.f : -3.4e38f;
-  for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total8; i += gridDim.x * blockDim.x) {
-    const unsigned cq = i % c8n;
-    const unsigned n = i / per_image;
-    const uint4 u = reinterpret_cast<const uint4*>(x)[i];
-    const float4* mp = reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C) + 2 * cq;
-    const float4* rp = reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C + C) + 2 * cq;
-    const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), r0 = __ldg(rp), r1 = __ldg(rp + 1);
-    const float m[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-    const float r[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
-    const __half2* hp = reinterpret_cast<const __half2*>(&u);
-    float o[8];
+  const unsigned stride = gridDim.x * blockDim.x;
+  // the launch makes the grid stride a multiple of the channel octets, so a thread keeps one octet for the whole loop and
+  // its mean / inverse deviation stay in registers (reloading 64 bytes of statistics per 16 bytes of data made the L1 the
+  // busiest unit: 73 %); they are reloaded only when the loop crosses into the next image
+  const bool fixed = stride % c8n == 0;
+  unsigned i = blockIdx.x * blockDim.x + threadIdx.x;
+  unsigned cq = i % c8n, n_cur = 0xffffffffu;
+  float m[8], r[8];
+  constexpr int U = 4;   // vectors in flight per thread: one 16-byte load per thread and round trip left DRAM at 30 %
+  for (; i < total8; i += U * stride) {
+    uint4 u[U], a[U];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float2 f = __half22float2(hp[e]);
-      o[2 * e] = fmaxf((f.x - m[2 * e]) * r[2 * e], floor_);
-      o[2 * e + 1] = fmaxf((f.y - m[2 * e + 1]) * r[2 * e + 1], floor_);
-    }
-    if (residual) {
-      const uint4 a = __ldg(reinterpret_cast<const uint4*>(residual) + i);
-      const __half2* ap = reinterpret_cast<const __half2*>(&a);
-#pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 f = __half22float2(ap[e]);
-        o[2 * e] = fmaxf(f.x + o[2 * e], 0.f);
-        o[2 * e + 1] = fmaxf(f.y + o[2 * e + 1], 0.f);
+    for (int k = 0; k < U; ++k) {
+      const unsigned ik = i + k * stride;
+      if (ik < total8) {
+        u[k] = reinterpret_cast<const uint4*>(x)[ik];
+        if (residual) a[k] = __ldg(reinterpret_cast<const uint4*>(residual) + ik);
       }
     }
-    uint4 w;
-    __half2* wp = reinterpret_cast<__half2*>(&w);
 #pragma unroll
-    for (int e = 0; e < 4; ++e) wp[e] = __floats2half2_rn(o[2 * e], o[2 * e + 1]);
-    reinterpret_cast<uint4*>(y)[i] = w;
+    for (int k = 0; k < U; ++k) {
+      const unsigned ik = i + k * stride;
+      if (ik >= total8) break;
+      if (!fixed) cq = ik % c8n;
+      const unsigned n = ik / per_image;
+      if (n != n_cur || !fixed) {
+        const float4* mp = reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C) + 2 * cq;
+        const float4* rp = reinterpret_cast<const float4*>(stats + (size_t)n * 2 * C + C) + 2 * cq;
+        const float4 m0 = __ldg(mp), m1 = __ldg(mp + 1), r0 = __ldg(rp), r1 = __ldg(rp + 1);
+        m[0] = m0.x; m[1] = m0.y; m[2] = m0.z; m[3] = m0.w; m[4] = m1.x; m[5] = m1.y; m[6] = m1.z; m[7] = m1.w;
+        r[0] = r0.x; r[1] = r0.y; r[2] = r0.z; r[3] = r0.w; r[4] = r1.x; r[5] = r1.y; r[6] = r1.z; r[7] = r1.w;
+        n_cur = n;
+      }
+      const __half2* hp = reinterpret_cast<const __half2*>(&u[k]);
+      float o[8];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = __half22float2(hp[e]);
+        o[2 * e] = fmaxf((f.x - m[2 * e]) * r[2 * e], floor_);
+        o[2 * e + 1] = fmaxf((f.y - m[2 * e + 1]) * r[2 * e + 1], floor_);
+      }
+      if (residual) {
+        const __half2* ap = reinterpret_cast<const __half2*>(&a[k]);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 f = __half22float2(ap[e]);
+          o[2 * e] = fmaxf(f.x + o[2 * e], 0.f);
+          o[2 * e + 1] = fmaxf(f.y + o[2 * e + 1], 0.f);
+        }
+      }
+      uint4 w;
+      __half2* wp = reinterpret_cast<__half2*>(&w);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) wp[e] = __floats2half2_rn(o[2 * e], o[2 * e + 1]);
+      reinterpret_cast<uint4*>(y)[ik] = w;
+    }
   }
 }
 
@@ -694,14 +719,20 @@ extern "C" int woft_instance_norm_from_sums_f16(const void* x, const float* part
   WOFT_REQUIRE(total4 <= kMaxElems32, "woft_instance_norm_from_sums_f16: more than 2^31 - 1 vectors");
   const bool wide = channels % 8 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
                                            reinterpret_cast<uintptr_t>(residual)) & 15) == 0;
-  if (wide)   // x == y allowed
-    in_apply_nhwc_h8_kernel<<<ew_grid(total4 / 2), 256, 0, s>>>(static_cast<const __half*>(x), stats,
+  if (wide) {   // x == y allowed
+    // 8 CTAs per SM's worth of threads; the grid is a multiple of 3 so that 256 * grid is a multiple of 12 and 16 octets too
+    const long long total8 = total4 / 2;
+    int grid = 148 * 8 + 2;   // 1186 = 2 * 593; made a multiple of 3 below
+    grid = (grid + 2) / 3 * 3;
+    if ((long long)grid * 256 > total8) grid = int((total8 + 255) / 256);
+    in_apply_nhwc_h8_kernel<<<grid, 256, 0, s>>>(static_cast<const __half*>(x), stats,
                                                                  static_cast<const __half*>(residual), static_cast<__half*>(y),
                                                                  hw, channels, relu, unsigned(total4 / 2));
-  else
+  } else {
     in_apply_nhwc_kernel<__half><<<ew_grid(total4), 256, 0, s>>>(static_cast<const __half*>(x), stats,
                                                                   static_cast<const __half*>(residual), static_cast<__half*>(y),
                                                                   hw, channels, relu, unsigned(total4));
+  }
   return launch_status("instance norm (from sums) kernels");
 }
 

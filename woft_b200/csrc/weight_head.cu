@@ -44,6 +44,10 @@ __global__ void __launch_bounds__(256, 2) weight_head_conv1_kernel(const float* 
                                                                    int n_img, int total_tiles) {
   __shared__ float tiles[2][2 * kWhTile];   // double buffered: the next step's images load while this one multiplies
   __shared__ int koff[kWhKP];
+  // STACKED: a warp's 32 rows x 32 fp16 channels pass through 2 KB of staging so that a lane stores 16 contiguous bytes
+  // (the accumulator fragment gives a lane 4 bytes in each of four 16-byte groups: 16-byte stores of which a quarter is
+  // written made this kernel 193 us for 331 MB)
+  __shared__ __align__(16) uint32_t stg[STACKED ? 8 : 1][STACKED ? 32 * 16 : 1];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
   const int rg = warp >> 2, cq = warp & 3;   // 2 row groups of 32 rows x 4 channel quarters of 32
   for (int i = tid; i < 4 * kWhTile; i += 256) (&tiles[0][0])[i] = 0.f;   // borders stay zero for the whole kernel
@@ -149,18 +153,39 @@ __global__ void __launch_bounds__(256, 2) weight_head_conv1_kernel(const float* 
         wh_mma(acc[1][nt], a[1], bf[ks][nt][0], bf[ks][nt][1]);
       }
     }
+    if (STACKED) {
+      uint32_t* sw = stg[warp];
+#pragma unroll
+      for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int r = mt * 16 + h * 8 + g;   // row of the warp's 32; 16 words per row, 4-word pieces XOR-ed by the row
+#pragma unroll
+          for (int nt = 0; nt < 4; ++nt) {
+            const __half2 v = __floats2half2_rn(fmaxf(acc[mt][nt][2 * h], 0.f), fmaxf(acc[mt][nt][2 * h + 1], 0.f));
+            sw[r * 16 + (((nt ^ ((r >> 1) & 3)) << 2) | t)] = *reinterpret_cast<const uint32_t*>(&v);
+          }
+        }
+      __syncwarp();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = (lane >> 2) + 8 * i, q = lane & 3;
+        const int gr = row0 + rg * 32 + r;
+        if (gr < total_rows) {
+          const uint4 v = *reinterpret_cast<const uint4*>(sw + r * 16 + ((q ^ ((r >> 1) & 3)) << 2));
+          const int img = gr / kWhPix, pp = gr - img * kWhPix;
+          *reinterpret_cast<uint4*>(reinterpret_cast<__half*>(out_any) + ((size_t)img * (kWhPix + kWhP) + pp) * kWhCout +
+                                    cq * 32 + q * 8) = v;
+        }
+      }
+      __syncwarp();
+    }
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
         if (grow[mt][h] >= total_rows) continue;
         if (STACKED) {
-          const int img = grow[mt][h] / kWhPix, pp = grow[mt][h] - img * kWhPix;
-          __half* o = reinterpret_cast<__half*>(out_any) + ((size_t)img * (kWhPix + kWhP) + pp) * kWhCout + cq * 32 + 2 * t;
-#pragma unroll
-          for (int nt = 0; nt < 4; ++nt)
-            *reinterpret_cast<__half2*>(o + nt * 8) =
-                __floats2half2_rn(fmaxf(acc[mt][nt][2 * h], 0.f), fmaxf(acc[mt][nt][2 * h + 1], 0.f));
         } else {
           float* o = reinterpret_cast<float*>(out_any) + (size_t)grow[mt][h] * kWhCout + cq * 32 + 2 * t;
 #pragma unroll

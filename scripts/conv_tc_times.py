@@ -55,7 +55,7 @@ for name, cin, cout, kh, kw in (("convc1 1x1 324->256", 324, 256, 1, 1), ("convc
     wc = cl(w)
     t_ref = timeit(lambda: torch.cudnn_convolution_relu(x, wc, b, (1, 1), pad, (1, 1), 1)) if cout % 8 == 0 else float("nan")
     gf = 2.0 * H * W * cin * cout * kh * kw / 1e9
-    print(f"{name:34s} {gf:7.2f} {t_own:10.1f} {gf / t_own / 1e3:8.1f} {t_ref:9.1f}")
+    print(f"{name:34s} {gf:7.2f} {t_own:10.1f} {gf / t_own * 1e3:8.1f} {t_ref:9.1f}")
 conv_tc.check(dev)
 
 # weight head layers 2/3: 14 400 images of 9x9x128, stacked with a separator row
@@ -73,7 +73,7 @@ for f16 in (False, True):
     t3 = timeit(lambda: conv_tc.run(pc, x, epilogue=_lib.CONV_HEAD_MEAN, w1x1=w1, head_out=logits, head_bias=0.1,
                                     row_period=P + 1, row_valid=P, box=(9, 14)), n=3)
     gf = 2.0 * n * 81 * C * C * 9 / 1e9
-    print(f"weight head layer 2 ({'fp16' if f16 else 'tf32'}) {gf:7.1f} GFLOP {t2:8.1f} us {gf / t2 / 1e3:6.1f} TFLOP/s;  "
+    print(f"weight head layer 2 ({'fp16' if f16 else 'tf32'}) {gf:7.1f} GFLOP {t2:8.1f} us {gf / t2 * 1e3:6.1f} TFLOP/s;  "
           f"layer 3 + 1x1 + mean {t3:8.1f} us")
     if not f16:
         xi = cl(torch.randn((n, C, P, P), generator=g, device=dev))

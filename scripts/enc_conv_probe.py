@@ -74,7 +74,7 @@ for name, cin, cout, H, W, stride in (("layer1 64->64 360x640", 64, 64, 360, 640
                 except Exception as e:  # noqa: BLE001
                     print(f"   box {box} halo {halo} stats {st is not None}: {str(e)[:80]}")
                     continue
-                print(f"   box {str(box):9s} halo {halo} stats {int(st is not None)}: {t:7.1f} us warm  {tcold:7.1f} us cold  {gf / t / 1e3:6.1f} TFLOP/s  {mb / t / 1e3:5.2f} TB/s")
+                print(f"   box {str(box):9s} halo {halo} stats {int(st is not None)}: {t:7.1f} us warm  {tcold:7.1f} us cold  {gf / t * 1e3:6.1f} TFLOP/s  {mb / t:5.2f} TB/s")
 
 # weight head layer 2: 14 400 stacked 9x9x128 images
 n, P, C = 14400, 9, 128
@@ -86,4 +86,4 @@ pc = conv_tc.PackedConv(w, b, 1, f16=True)
 t, tcold = timeit(lambda: conv_tc.run(pc, x, relu=True, out=mid, row_period=P + 1, row_valid=P, box=(9, 14)), n=3)
 conv_tc.check(dev)
 gf = 2.0 * n * 81 * C * C * 9 / 1e9
-print(f"== weight head layer 2: {gf:.0f} GFLOP  {t:7.1f} us warm  {tcold:7.1f} us cold  {gf / t / 1e3:6.1f} TFLOP/s")
+print(f"== weight head layer 2: {gf:.0f} GFLOP  {t:7.1f} us warm  {tcold:7.1f} us cold  {gf / t * 1e3:6.1f} TFLOP/s")

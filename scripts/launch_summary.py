@@ -28,5 +28,5 @@ for name, (n, s) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print(f"| `{name}` | {n} | {s:.1f} | {100 * s / total:.1f}% |")
 own = [(n, s) for k, (n, s) in agg.items() if "woft::" in k]
 print(f"\nHand-written kernels (woft::*): {sum(n for n, _ in own)} launches ({sum(n for n, _ in own) // steps} per frame), "
-      f"{sum(s for _, s in own):.1f} us = {100 * sum(s for _, s in own) / total:.1f}% of the step; the rest is cuDNN "
-      "convolutions (TF32) and a few ATen element-wise kernels.")
+      f"{sum(s for _, s in own):.1f} us = {100 * sum(s for _, s in own) / total:.1f}% of the step; the rest is whatever "
+      "else the step launched (ATen element-wise / copy kernels; cuDNN / cuBLAS kernels would be listed above by name).")

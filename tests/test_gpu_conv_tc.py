@@ -318,3 +318,56 @@ def test_row_halo_mode_is_the_plain_convolution(shape, f16):
     tol = 1.5e-3 if f16 else 2e-4          # fp16: rounding of the stored result
     assert (outs[1].double() - want).abs().max().item() / scale <= tol
     assert (outs[0].double() - outs[1].double()).abs().max().item() / scale <= tol
+
+
+@pytest.mark.parametrize("shape", [(2, 64, 64, 45, 80, 1), (1, 96, 96, 23, 37, 1), (2, 64, 96, 90, 160, 2), (1, 128, 128, 33, 47, 1)])
+def test_two_tiles_per_k_step_is_the_same_convolution(shape):
+    """M = 256 per CTA (two pixel tiles share every filter tile; debug_flags 2048 forces the mode on a small problem,
+    1024 forbids it): every output pixel sees the same MMAs in the same order, so results are bit-identical -- with an odd
+    tile count (the second tile of the last pair lies outside the batch), stride 2, the residual tail and the
+    instance-norm sums (whose per-CTA rows are dealt differently, hence compared after the combination)."""
+    from woft_b200 import conv_tc
+    B, cin, cout, H, W, stride = shape
+    x, w, b = make(B, cin, cout, H, W, 3, 3, seed=cin + H)
+    xh = cl(x.half())
+    pc = conv_tc.PackedConv(w, b, 1, f16=True)
+    Ho, Wo = (H - 1) // stride + 1, (W - 1) // stride + 1
+    res = cl(torch.randn((B, cout, Ho, Wo), generator=torch.Generator().manual_seed(9)).half().to(DEV))
+    outs, sums = [], []
+    for flag in (1024, 2048):
+        out = cl(torch.full((B, cout, Ho, Wo), 3.0, device=DEV, dtype=torch.float16))
+        stats = torch.zeros((148, B, 2, cout), device=DEV)
+        conv_tc.run(pc, xh, relu=True, out=out, stride=stride, residual=res, stats=stats, debug_flags=flag)
+        outs.append(out)
+        sums.append(stats.double().sum(0))
+    conv_tc.check(DEV)
+    assert torch.equal(outs[0], outs[1])
+    assert torch.allclose(sums[0], sums[1], rtol=1e-6, atol=1e-3)
+    want = (res.double() + F.conv2d(xh.double(), w.half().double(), b.double(), padding=1, stride=stride).relu()).relu()
+    assert (outs[1].double() - want).abs().max().item() / want.abs().max().item() <= 1.5e-3
+
+
+def test_two_tiles_per_k_step_weight_head():
+    """The stacked weight-head layers (9 x 14 boxes, HEAD_MEAN epilogue) in the two-tile mode against the one-tile mode."""
+    from woft_b200 import _lib, conv_tc
+    n, P, C = 61, 9, 128
+    g = torch.Generator().manual_seed(2)
+    stacked = torch.zeros((n, P + 1, P, C), dtype=torch.float16)
+    stacked[:, :P] = torch.randn((n, P, P, C), generator=g).relu().half()
+    x = stacked.to(DEV).view(1, n * (P + 1), P, C).permute(0, 3, 1, 2)
+    w = (torch.randn((C, C, 3, 3), generator=g) / (C * 9) ** 0.5).to(DEV)
+    b = (torch.randn((C,), generator=g) * 0.1).to(DEV)
+    w1 = (torch.randn((C,), generator=g) / C ** 0.5).to(DEV)
+    pc = conv_tc.PackedConv(w, b, 1, f16=True)
+    mids, logits = [], []
+    for flag in (1024, 2048):
+        mid = torch.full((1, n * (P + 1), P, C), 5.0, device=DEV, dtype=torch.float16).permute(0, 3, 1, 2)
+        conv_tc.run(pc, x, relu=True, out=mid, row_period=P + 1, row_valid=P, box=(9, 14), debug_flags=flag)
+        lg = torch.zeros((n,), device=DEV)
+        conv_tc.run(pc, x, epilogue=_lib.CONV_HEAD_MEAN, w1x1=w1, head_out=lg, head_bias=0.2, row_period=P + 1,
+                    row_valid=P, box=(9, 14), debug_flags=flag)
+        mids.append(mid)
+        logits.append(lg)
+    conv_tc.check(DEV)
+    assert torch.equal(mids[0], mids[1])
+    assert torch.equal(logits[0], logits[1])

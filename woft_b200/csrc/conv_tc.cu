@@ -96,6 +96,7 @@ struct ConvTcParams {
   unsigned long long* trace;  // debug: 8 globaltimer stamps per CTA, or null
   int coalesce;               // every epilogue operand is 16-byte aligned with 16-byte multiple strides: staged accesses
   int dbg;                    // experiments (woft_conv_tc_args.debug_flags)
+  int mt2, super_tiles;       // two pixel tiles per k-step share one filter tile (M = 256 per CTA): persistent launches, bn <= 128
   int producers;              // TMA-issuing warps of the plain mode (warp 0 and warps 10, 11): each takes every producers-th k-step
   int pdl;                    // host only: launch with programmatic stream serialization
 };
@@ -174,6 +175,12 @@ __device__ __forceinline__ CtTile ct_decode(const ConvTcParams& p, int t) {
 // the it-th tile of this CTA (false when there is none).  Pair mode: the cluster walks pair-tiles; rank r of the pair takes
 // pixel tile 2 * pp + r, a tile past the end is a dummy outside the batch (its loads are zero-filled, nothing is stored)
 __device__ __forceinline__ bool ct_tile_at(const ConvTcParams& p, int it, uint32_t rank, CtTile& c) {
+  if (p.mt2) {   // the first pixel tile of the it-th super tile (n_tiles == 1); the second is ct_decode(p, 2 * st + 1),
+    const int st = blockIdx.x + it * gridDim.x;   // which lies outside the batch when the tile count is odd
+    if (st >= p.super_tiles) return false;
+    c = ct_decode(p, 2 * st);
+    return true;
+  }
   if (!p.pair) {
     const int t = blockIdx.x + it * gridDim.x;
     if (t >= p.total_tiles) return false;
@@ -581,7 +588,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         const int np = p.producers, stages = p.stages, k_chunks = p.k_chunks, k_elems = p.k_elems, stride = p.stride;
         const int a_stage = p.a_stage, b_bytes = p.b_bytes;
         const bool load_a = !(p.dbg & 1), load_b = !(p.dbg & 2);   // dbg bits 1, 2: timing experiments without the loads
-        const uint32_t tx = uint32_t((load_a ? p.a_bytes : 0) + (load_b ? b_bytes : 0));
+        const bool mt2 = p.mt2 != 0;
+        const uint32_t tx = uint32_t((load_a ? (mt2 ? 2 : 1) * p.a_bytes : 0) + (load_b ? b_bytes : 0));
         int stage = prod;   // host: producers <= stages
         uint32_t phase = 0;
         int ks = prod;      // this warp's next k-step of the current tile
@@ -590,6 +598,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           if (prod == 0) ct_tile_stamp(p, it, 0);
           int tap = ks / k_chunks, kc = ks - tap * k_chunks;
           const int xb = stride * tc.x0, yb = stride * tc.y0;
+          CtTile tc2 = tc;
+          if (mt2) tc2 = ct_decode(p, 2 * (int(blockIdx.x) + it * int(gridDim.x)) + 1);
+          const int xb2 = stride * tc2.x0, yb2 = stride * tc2.y0;
           while (ks < k_steps) {
             const int xs = xb + p.dx[tap], ys = yb + p.dy[tap];
             if (!ct_wait(empty + stage, phase ^ 1u)) {
@@ -610,6 +621,9 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               } else {
                 ptx::mbar_arrive_expect_tx(full + stage, tx);
                 if (load_a) ptx::tma_load_4d(sA + stage * a_stage, &p.tmA, full + stage, kc * k_elems, xs, ys, tc.n);
+                if (load_a && mt2)
+                  ptx::tma_load_4d(sA + stage * a_stage + CT_A_STAGE, &p.tmA, full + stage, kc * k_elems, xb2 + p.dx[tap],
+                                   yb2 + p.dy[tap], tc2.n);
                 if (load_b) ptx::tma_load_3d(sB + stage * b_bytes, &p.tmB, full + stage, kc * k_elems, tc.c0, tap);
               }
             }
@@ -639,7 +653,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
                              (uint32_t((PAIR ? 256 : 128) >> 4) << 24);
       // this CTA's (pair's) tile count: the issuing warp has no use for tile coordinates
       const int my_tiles = p.pair ? (p.pair_tiles - int(blockIdx.x >> 1) + int(gridDim.x >> 1) - 1) / int(gridDim.x >> 1)
-                                  : (p.total_tiles - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);
+                                  : ((p.mt2 ? p.super_tiles : p.total_tiles) - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);
       int stage = 0;
       uint32_t phase = 0;
       bool alive = true;
@@ -708,6 +722,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         const uint32_t a_lo0 = uint32_t(da0), b_lo0 = uint32_t(db0);
         const uint32_t a_step = uint32_t(p.a_stage >> 4), b_step = uint32_t(p.b_bytes >> 4);
         const uint32_t full0 = ptx::smem_u32(full), empty0 = ptx::smem_u32(empty);
+        const bool mt2 = p.mt2 != 0;   // second accumulator of the super tile: 128 columns further, second activation box
         uint32_t a_lo = a_lo0, b_lo = b_lo0, full_a = full0, empty_a = empty0;
         for (int it = 0; alive && it < my_tiles; ++it) {
           const int buf = it & 1;
@@ -742,6 +757,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
                 ptx::mma_commit_2sm(empty + (stage - n), 3);   // frees the stage in both CTAs
               } else {
                 ptx::mma_row4<F16>(d_tmem, a_lo, b_lo, desc_hi, idesc, started);
+                if (mt2) ptx::mma_row4<F16>(d_tmem + 128u, a_lo + uint32_t(CT_A_STAGE >> 4), b_lo, desc_hi, idesc, started);
                 ptx::mma_commit_a(empty_a);
               }
               started = 1;
@@ -787,10 +803,10 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     for (; ct_tile_at(p, it, rank, tc); ++it) {
       const int buf = it & 1;
       const uint32_t use = uint32_t(it >> 1);
-      const int x = tc.x0 + xi, y = tc.y0 + yj;
-      const bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H && tc.n < p.NB;
-      const bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
-      const long long pix = ((long long)tc.n * p.H + y) * p.W + x;
+      int x = tc.x0 + xi, y = tc.y0 + yj;
+      bool valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H && tc.n < p.NB;
+      bool separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
+      long long pix = ((long long)tc.n * p.H + y) * p.W + x;
       uint8_t* stg = s_stage + (warp - 2) * ct_stage_bytes(EPI);
       const bool co = p.coalesce != 0;
       constexpr bool GRU = EPI == CT_EPI_GRU_ZR || EPI == CT_EPI_GRU_Q;
@@ -892,6 +908,19 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         if (leader) ct_tile_stamp(p, it, 6);
         continue;
       }
+      // mt2: the super tile's two pixel tiles one after the other, their accumulators 128 TMEM columns apart
+      const int nsub = p.mt2 ? 2 : 1;
+      for (int sub = 0; sub < nsub; ++sub) {
+      if (sub == 1) {
+        tc = ct_decode(p, 2 * (int(blockIdx.x) + it * int(gridDim.x)) + 1);
+        x = tc.x0 + xi;
+        y = tc.y0 + yj;
+        valid = xi < p.bw && yj < p.bh && x < p.W && y < p.H && tc.n < p.NB;
+        separator = p.row_period > 0 && (y % p.row_period) >= p.row_valid;
+        pix = ((long long)tc.n * p.H + y) * p.W + x;
+      }
+      const uint32_t acc_col = uint32_t(buf * 256 + sub * 128);
+      const bool last_sub = sub == nsub - 1;
       int rp[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) rp[i] = __shfl_sync(0xffffffffu, valid ? int(pix) : -1, (lane >> 2) + 8 * i);
@@ -975,8 +1004,8 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           const float4 b4 = reinterpret_cast<const float4*>(s_bias + col)[j];
           bv[4 * j] = b4.x; bv[4 * j + 1] = b4.y; bv[4 * j + 2] = b4.z; bv[4 * j + 3] = b4.w;
         }
-        ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * 256 + c * 32), v);
-        if (c + 2 >= chunks) {  // this warp's last chunk: its share of the accumulator is read, hand it back
+        ptx::tmem_ld_32x32(tmem_base + lane_base + acc_col + uint32_t(c * 32), v);
+        if (c + 2 >= chunks && last_sub) {  // this warp's last chunk: its share of the accumulator is read, hand it back
           ptx::tc_fence_before_sync();
           if (PAIR)
             ptx::mbar_arrive_cluster(lead_tempty[buf]);   // the leader's MMA warp waits for both CTAs' epilogues
@@ -1046,7 +1075,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
           for (int j = 0; j < 32; ++j) head_sum = fmaf(fmaxf(v[j] + bv[j], 0.f), hv[j], head_sum);
         }
       }
-      if (chunks <= half) {  // a one-chunk tile leaves the second warp of each pair without work
+      if (chunks <= half && last_sub) {  // a one-chunk tile leaves the second warp of each pair without work
         ptx::tc_fence_before_sync();
         if (PAIR)
           ptx::mbar_arrive_cluster(lead_tempty[buf]);
@@ -1072,6 +1101,7 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
         }
         ptx::named_bar_sync(1, CT_EPI_THREADS);
       }
+      }   // sub
       if (leader && it == 0) ct_stamp(p, 5);
       if (leader) ct_tile_stamp(p, it, 6);
     }
@@ -1372,6 +1402,29 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
       return fail(WOFT_ERR_CUDA, "cuTensorMapEncodeTiled failed for the weight operand");
   }
 
+  int sms = 0;
+  WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  // Two pixel tiles per k-step (M = 256 per CTA) when the launch is persistent and the filter tile is narrow: one filter
+  // tile, one barrier round trip and one commit serve eight MMAs instead of four.  The many-tile launches are bound by
+  // L2 -> SM operand traffic (weight head: 32 KB per 384-cycle k-step on 148 SMs = 16.8 TB/s) and by the issue thread;
+  // this takes a quarter of the bytes and half of the waits away.  debug_flags 1024 / 2048 force it off / on (tests).
+  static const bool mt2_env = [] {
+    const char* e = getenv("WOFT_CONV_MT2");
+    return !(e && e[0] == '0');
+  }();
+  const bool mt2_fit = !p.halo && !p.pair && p.n_tiles == 1 && bn <= 128 &&
+                       (a->epilogue == CT_EPI_BIAS_ACT || a->epilogue == CT_EPI_HEAD_MEAN);
+  p.super_tiles = (p.total_tiles + 1) / 2;
+  // ... unless the pairing costs a round: a CTA's share is ceil(tiles / SMs) single tiles or ceil(pairs / SMs) pairs
+  // (encoder layer 1: 3 600 tiles = 25 rounds of one or 13 rounds of two -- measured 54.2 vs 53.8 us; the weight head's
+  // 10 286 tiles: 70 rounds either way, 361 -> 329 us)
+  const bool mt2_rounds = 2 * ceil_div(p.super_tiles, sms) <= ceil_div(p.total_tiles, sms);
+  p.mt2 = (mt2_fit && !(a->debug_flags & 1024) &&
+           ((mt2_env && p.total_tiles >= 2 * sms && mt2_rounds) || (a->debug_flags & 2048))) ? 1 : 0;
+  if (p.mt2) {
+    a_stage = 2 * CT_A_STAGE;
+    p.a_stage = a_stage;
+  }
   // halo mode: 3 activation stages (one box feeds `taps` MMA groups) and as many filter stages as fit beside them
   const int a_stages_halo = 3;
   int stages = p.halo ? (CT_SMEM_LIMIT - fixed - a_stages_halo * a_stage) / p.b_bytes : (CT_SMEM_LIMIT - fixed) / (a_stage + p.b_bytes);
@@ -1391,15 +1444,14 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   int smem = p.a_stages * a_stage + stages * p.b_bytes + fixed;
   if (smem < 120 * 1024) smem = 120 * 1024;
 
-  int sms = 0;
-  WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   int grid = p.total_tiles < sms ? p.total_tiles : sms;
+  if (p.mt2) grid = p.super_tiles < sms ? p.super_tiles : sms;
   if (p.pair) {
     const int pairs = p.pair_tiles < sms / 2 ? p.pair_tiles : sms / 2;
     grid = 2 * pairs;
   }
   WOFT_REQUIRE(grid >= 1, "woft_conv_tc: empty grid");
-  if (!p.halo && p.total_tiles > grid) p.producers = producers_env < stages ? producers_env : stages;
+  if (!p.halo && (p.mt2 ? p.super_tiles : p.total_tiles) > grid) p.producers = producers_env < stages ? producers_env : stages;
   if (a->stats) {
     // every CTA writes its partial sums; the rows of CTAs that do not exist in this launch are cleared
     WOFT_REQUIRE(p.coalesce && !p.pair, "woft_conv_tc: statistics need 16-byte aligned outputs and single-CTA mode");

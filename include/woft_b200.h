@@ -138,6 +138,16 @@ void woft_corr_set_trace_buffer(unsigned long long* device_buffer);
 int woft_corr_lookup(const float* const* levels, int num_levels, const float* coords, int batch, int h1, int w1,
                      int h2, int w2, int radius, float* out, int flags, void* stream);
 int woft_corr_lookup_check(void* stream);
+/* woft_corr_lookup preceded, in the same launch, by woft_flow_head_gather for the launch's own queries (the step between
+ * two refinement iterations, raft_core/weighted_raft.py:244-246 then :232-233): `coords` (B,2,H1,W1) is advanced IN PLACE
+ * by the flow head's delta (bias + the nine shifted tap products of `taps`, (B*H1*W1, 9, 2)), the new flow
+ * coords - coords0 goes to flow_nchw / flow_nhwc / the two fp16 operand buffers (each optional), and the lookup is taken at
+ * the new coordinates.  Bit for bit what the two separate calls give; one launch and one pass over the coordinates less
+ * per iteration.  Not with flag 64. */
+int woft_corr_lookup_gather(const float* const* levels, int num_levels, float* coords, int batch, int h1, int w1, int h2,
+                            int w2, int radius, float* out, int flags, const float* taps, const float* bias,
+                            const float* coords0, float* flow_nchw, float* flow_nhwc, void* flow_f16_a, void* flow_f16_b,
+                            int f16_stride, int f16_offset, void* stream);
 
 /* A''.  Replaces alt_cuda_corr.forward (alt_cuda_corr/correlation.cpp:23-33, correlation_kernel.cu:18-119,
  * 260-286), the reference's one native op: on-the-fly local correlation without a materialised volume.

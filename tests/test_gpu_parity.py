@@ -535,6 +535,56 @@ def test_tensor_core_convolution_schedule_matches_layer_by_layer(golden):
     assert both[1].shape[0] == 2
     assert (both[1][:1] - fast[1]).norm(dim=1).mean().item() <= 5e-3
     assert (both[4][:1] - fast[4]).abs().max().item() <= 5e-3
+    # the flow head's gather inside the next lookup (woft_corr_lookup_gather; an option, measured slower) and as its own
+    # launch after every iteration are the same arithmetic: every output bit for bit; likewise one stream instead of two
+    from woft_b200 import fast_net as fn_mod
+    saved = (fn_mod._FUSE_GATHER, fn_mod._TWO_STREAMS)
+    torch.backends.cudnn.allow_tf32 = True
+    try:
+        fn_mod._FUSE_GATHER, fn_mod._TWO_STREAMS = True, False
+        plain = fast_net_(t1, t2, iters=12, corr_block=blk)
+    finally:
+        fn_mod._FUSE_GATHER, fn_mod._TWO_STREAMS = saved
+        torch.backends.cudnn.allow_tf32 = old
+    for a, b in zip(fast, plain):
+        assert torch.equal(a, b)
+
+
+def test_lookup_with_the_flow_head_gather_in_the_same_launch():
+    """woft_corr_lookup_gather against woft_flow_head_gather followed by woft_corr_lookup: coordinates, every flow copy
+    and the lookup bit for bit, for both pyramid storage types and a ragged map."""
+    from woft_b200 import _lib
+    from woft_b200.corr import CorrBlock
+    g = torch.Generator().manual_seed(77)
+    for (B, H, W), mode in (((1, 24, 40), "fp16"), ((2, 17, 23), "fp16s")):
+        f1, f2 = torch.randn((B, 64, H, W), generator=g).to(DEV), torch.randn((B, 64, H, W), generator=g).to(DEV)
+        blk = CorrBlock(f1, f2, mode=mode)
+        ys, xs = torch.meshgrid(torch.arange(H, device=DEV), torch.arange(W, device=DEV), indexing="ij")
+        coords0 = torch.stack([xs, ys]).float()[None].repeat(B, 1, 1, 1).contiguous()
+        start = coords0 + torch.randn((B, 2, H, W), generator=g).to(DEV) * 3
+        taps = (torch.randn((B * H * W, 18), generator=g) * 0.3).to(DEV)
+        bias = torch.tensor([0.05, -0.02], device=DEV)
+        stride, off = 392, 382
+        outs = []
+        for fused in (False, True):
+            coords = start.clone()
+            flow, flow_cl = torch.zeros_like(coords), torch.zeros((B, H, W, 2), device=DEV)
+            ha = torch.zeros((B * H * W, stride), device=DEV, dtype=torch.float16)
+            hb = torch.zeros_like(ha)
+            gd = dict(taps=taps, bias=bias, coords0=coords0, flow_nchw=flow, flow_nhwc=flow_cl, f16_a=ha, f16_b=hb,
+                      f16_stride=stride, f16_offset=off)
+            if fused:
+                out = blk(coords, flags=24, gather=gd)
+            else:
+                rc = _lib.load().woft_flow_head_gather(_lib.ptr(taps), _lib.ptr(bias), B, H, W, None, _lib.ptr(coords),
+                                                       _lib.ptr(coords0), _lib.ptr(flow), _lib.ptr(flow_cl), _lib.ptr(ha),
+                                                       _lib.ptr(hb), stride, off, _lib.current_stream(torch.device(DEV)))
+                assert rc == 0
+                out = blk(coords, flags=24)
+            outs.append((coords, flow, flow_cl, ha, hb, out[:, :324]))
+        for a, b in zip(*outs):
+            assert torch.equal(a, b)
+        assert not torch.equal(outs[0][0], start)
 
 
 def test_u8_input_path_is_the_float_path(golden):

@@ -54,6 +54,9 @@ SIGNATURES = {
     "woft_corr_lookup": (c_int, [_FLOATP_ARRAY, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
                                  c_int, c_void_p]),
     "woft_corr_lookup_check": (c_int, [c_void_p]),
+    "woft_corr_lookup_gather": (c_int, [_FLOATP_ARRAY, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p,
+                                        c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                        c_int, c_void_p]),
     "woft_alt_corr_forward": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                       c_int, c_void_p, c_void_p]),
     "woft_homography_fit": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_float, c_void_p,

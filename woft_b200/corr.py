@@ -80,10 +80,16 @@ class CorrBlock:
             del keep
         _lib.check(rc, "woft_corr_pyramid")
 
-    def __call__(self, coords, flags=0):
-        """corr.py:29-59: coords (B,2,H1,W1) -> (B, L*(2r+1)^2, H1, W1) fp32 contiguous."""
+    def __call__(self, coords, flags=0, gather=None):
+        """corr.py:29-59: coords (B,2,H1,W1) -> (B, L*(2r+1)^2, H1, W1) fp32 contiguous.
+
+        `gather` (fused schedule only): dict(taps, bias, coords0, flow_nchw, flow_nhwc, f16_a, f16_b, f16_stride, f16_offset)
+        -- the flow head's 9-tap gather and coordinate update run in the same launch first (woft_corr_lookup_gather):
+        `coords` is then advanced IN PLACE and must be the contiguous fp32 tensor itself."""
         _lib.require_cuda(coords)
         B, C, H, W = self.shape
+        if gather is not None and not (coords.dtype == torch.float32 and coords.is_contiguous()):
+            raise AssertionError("the fused gather advances `coords` in place: contiguous fp32 needed")
         coords = _as_f32c(coords)
         if coords.shape[0] != B or coords.shape[1] != 2 or tuple(coords.shape[2:]) != (H, W):
             raise AssertionError(f"coords must be ({B},2,{H},{W}), got {tuple(coords.shape)}")
@@ -99,9 +105,17 @@ class CorrBlock:
             out = torch.empty((B, ch, H, W), device=dev, dtype=torch.float32, memory_format=fmt)
         with torch.cuda.device(dev):
             levels, keep = _lib.ptr_array(self.corr_pyramid)
-            rc = _lib.load().woft_corr_lookup(levels, self.num_levels, _lib.ptr(coords), B, H, W, H, W, self.radius,
-                                              _lib.ptr(out), flags | (32 if self.corr_pyramid[0].dtype == torch.float16 else 0),
-                                              _lib.current_stream(dev))
+            flags |= 32 if self.corr_pyramid[0].dtype == torch.float16 else 0
+            if gather is None:
+                rc = _lib.load().woft_corr_lookup(levels, self.num_levels, _lib.ptr(coords), B, H, W, H, W, self.radius,
+                                                  _lib.ptr(out), flags, _lib.current_stream(dev))
+            else:
+                g = gather
+                rc = _lib.load().woft_corr_lookup_gather(
+                    levels, self.num_levels, _lib.ptr(coords), B, H, W, H, W, self.radius, _lib.ptr(out), flags,
+                    _lib.ptr(g["taps"]), _lib.ptr(g["bias"]), _lib.ptr(g["coords0"]), _lib.ptr(g.get("flow_nchw")),
+                    _lib.ptr(g.get("flow_nhwc")), _lib.ptr(g.get("f16_a")), _lib.ptr(g.get("f16_b")),
+                    g.get("f16_stride", 0), g.get("f16_offset", 0), _lib.current_stream(dev))
             del keep
         _lib.check(rc, "woft_corr_lookup")
         return out

@@ -37,6 +37,18 @@ struct LookupParams {
   int hw1;              // H1*W1
   int out_f16;          // channels-last output holds __half (flag 16): the A operand of an fp16 tensor-core convolution
   int out_stride;       // channels-last output: elements between consecutive queries (channels, rounded up to 8 for fp16)
+  // Optional (woft_corr_lookup_gather): the flow head's 9-tap gather and coordinate update (flow_head_gather_kernel,
+  // weighted_raft.py:244-246) done by this launch for its own queries before it looks anything up.  `g_coords` is advanced
+  // in place; the new flow goes out as NCHW, as (pixels, 2) and as fp16 into the two GRU operand buffers.
+  const float* g_taps;     // (pixels, 18) or null
+  const float* g_bias;     // (2)
+  float* g_coords;         // (B, 2, H1, W1), read and written
+  const float* g_coords0;
+  float* g_flow_nchw;
+  float* g_flow_nhwc;
+  __half* g_h1;
+  __half* g_h2;
+  int g_stride, g_off, g_H, g_W;
 };
 
 constexpr int kLookupThreads = 128;
@@ -71,11 +83,51 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
   __shared__ float win[kLevelsPerPass * kQueriesPerCta * STRIDE];
   __shared__ int s_x0[kLevelsPerPass * kQueriesPerCta], s_y0[kLevelsPerPass * kQueriesPerCta];
   __shared__ float s_ax[kLevelsPerPass * kQueriesPerCta], s_ay[kLevelsPerPass * kQueriesPerCta];
+  __shared__ float s_cx[kQueriesPerCta], s_cy[kQueriesPerCta];
   pdl_sync();   // the coordinates come from the previous kernel of the iteration
 
   const int tid = threadIdx.x;
   const int q0 = blockIdx.x * kQueriesPerCta;
   const int channels = p.num_levels * P * P;
+  const bool gather = p.g_taps != nullptr;
+  if (gather) {
+    // the arithmetic of flow_head_gather_kernel, operation for operation (the two must agree bit for bit)
+    if (tid < kQueriesPerCta && q0 + tid < p.nq) {
+      const int i = q0 + tid, hw = p.hw1, H = p.g_H, W = p.g_W;
+      const int b = i / hw, r = i - b * hw;
+      const int y = r / W, x = r - y * W;
+      float dx = __ldg(p.g_bias), dy = __ldg(p.g_bias + 1);
+#pragma unroll
+      for (int ky = 0; ky < 3; ++ky) {
+        const int yy = y + ky - 1;
+        if (yy < 0 || yy >= H) continue;
+#pragma unroll
+        for (int kx = 0; kx < 3; ++kx) {
+          const int xx = x + kx - 1;
+          if (xx < 0 || xx >= W) continue;
+          const float2 t = __ldg(reinterpret_cast<const float2*>(p.g_taps + ((size_t)b * hw + yy * W + xx) * 18) + ky * 3 + kx);
+          dx += t.x;
+          dy += t.y;
+        }
+      }
+      const size_t ix = (size_t)(b * 2) * hw + r, iy = ix + hw;
+      const float cx = p.g_coords[ix] + dx, cy = p.g_coords[iy] + dy;
+      p.g_coords[ix] = cx;
+      p.g_coords[iy] = cy;
+      s_cx[tid] = cx;
+      s_cy[tid] = cy;
+      const float fx = cx - __ldg(p.g_coords0 + ix), fy = cy - __ldg(p.g_coords0 + iy);
+      if (p.g_flow_nchw) {
+        p.g_flow_nchw[ix] = fx;
+        p.g_flow_nchw[iy] = fy;
+      }
+      if (p.g_flow_nhwc) reinterpret_cast<float2*>(p.g_flow_nhwc)[i] = make_float2(fx, fy);
+      const __half2 fh = __floats2half2_rn(fx, fy);
+      if (p.g_h1) *reinterpret_cast<__half2*>(p.g_h1 + (size_t)i * p.g_stride + p.g_off) = fh;
+      if (p.g_h2) *reinterpret_cast<__half2*>(p.g_h2 + (size_t)i * p.g_stride + p.g_off) = fh;
+    }
+    __syncthreads();
+  }
 
   for (int lv0 = 0; lv0 < p.num_levels; lv0 += kLevelsPerPass) {
     // ---- window origins and fractions for (level slot, query): 64 threads
@@ -84,9 +136,14 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
       const int q = q0 + ql, lvl = lv0 + slot;
       float cx = 0.f, cy = 0.f;
       if (q < p.nq && lvl < p.num_levels) {
-        const int b = q / p.hw1, pix = q - b * p.hw1;
-        cx = __ldg(p.coords + (size_t)(2 * b) * p.hw1 + pix);
-        cy = __ldg(p.coords + (size_t)(2 * b + 1) * p.hw1 + pix);
+        if (gather) {
+          cx = s_cx[ql];
+          cy = s_cy[ql];
+        } else {
+          const int b = q / p.hw1, pix = q - b * p.hw1;
+          cx = __ldg(p.coords + (size_t)(2 * b) * p.hw1 + pix);
+          cy = __ldg(p.coords + (size_t)(2 * b + 1) * p.hw1 + pix);
+        }
       }
       const float inv = 1.0f / float(1 << (lvl & 31));
       const float x = cx * inv, y = cy * inv;  // centroid_lvl = coords / 2**i (corr.py:41)
@@ -286,9 +343,38 @@ int corr_lookup_tma(const float* const*, int, const float*, int, int, int, int, 
 
 }  // namespace woft
 
+namespace woft {
+struct LookupGather {   // the optional fused gather of woft_corr_lookup_gather
+  const float *taps, *bias, *coords0;
+  float *flow_nchw, *flow_nhwc;
+  void *f16_a, *f16_b;
+  int f16_stride, f16_offset;
+};
+static int corr_lookup_impl(const float* const* levels, int num_levels, const float* coords, int batch, int h1, int w1,
+                            int h2, int w2, int radius, float* out, int flags, const LookupGather* g, void* stream);
+}  // namespace woft
+
 extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, const float* coords, int batch, int h1,
                                 int w1, int h2, int w2, int radius, float* out, int flags, void* stream) {
+  return woft::corr_lookup_impl(levels, num_levels, coords, batch, h1, w1, h2, w2, radius, out, flags, nullptr, stream);
+}
+
+extern "C" int woft_corr_lookup_gather(const float* const* levels, int num_levels, float* coords, int batch, int h1, int w1,
+                                       int h2, int w2, int radius, float* out, int flags, const float* taps,
+                                       const float* bias, const float* coords0, float* flow_nchw, float* flow_nhwc,
+                                       void* flow_f16_a, void* flow_f16_b, int f16_stride, int f16_offset, void* stream) {
   using namespace woft;
+  WOFT_REQUIRE(taps && bias && coords0, "woft_corr_lookup_gather: null pointer");
+  WOFT_REQUIRE(!(flags & 64), "woft_corr_lookup_gather: not with the TMA variant (flag 64)");
+  WOFT_REQUIRE((!flow_f16_a && !flow_f16_b) || (f16_stride % 2 == 0 && f16_offset % 2 == 0 &&
+                                                  ((reinterpret_cast<uintptr_t>(flow_f16_a) | reinterpret_cast<uintptr_t>(flow_f16_b)) & 3) == 0),
+               "woft_corr_lookup_gather: the fp16 flow copies need even strides / offsets");
+  const LookupGather g{taps, bias, coords0, flow_nchw, flow_nhwc, flow_f16_a, flow_f16_b, f16_stride, f16_offset};
+  return corr_lookup_impl(levels, num_levels, coords, batch, h1, w1, h2, w2, radius, out, flags, &g, stream);
+}
+
+static int woft::corr_lookup_impl(const float* const* levels, int num_levels, const float* coords, int batch, int h1, int w1,
+                                  int h2, int w2, int radius, float* out, int flags, const LookupGather* g, void* stream) {
   WOFT_REQUIRE(levels && coords && out, "woft_corr_lookup: null pointer");
   WOFT_REQUIRE(num_levels >= 1 && num_levels <= kMaxLevels, "woft_corr_lookup: num_levels %d not in [1,%d]",
                num_levels, kMaxLevels);
@@ -323,6 +409,20 @@ extern "C" int woft_corr_lookup(const float* const* levels, int num_levels, cons
   }
   p.nq = batch * h1 * w1;
   p.hw1 = h1 * w1;
+  if (g) {
+    p.g_taps = g->taps;
+    p.g_bias = g->bias;
+    p.g_coords = const_cast<float*>(coords);   // woft_corr_lookup_gather takes it mutable
+    p.g_coords0 = g->coords0;
+    p.g_flow_nchw = g->flow_nchw;
+    p.g_flow_nhwc = g->flow_nhwc;
+    p.g_h1 = static_cast<__half*>(g->f16_a);
+    p.g_h2 = static_cast<__half*>(g->f16_b);
+    p.g_stride = g->f16_stride;
+    p.g_off = g->f16_offset;
+    p.g_H = h1;
+    p.g_W = w1;
+  }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (nhwc && radius == 4 && vec && (flags & 64)) {
     // flag 64: channels-last output, radius 4, 16-byte aligned level rows -- the footprints come in by TMA

@@ -253,6 +253,10 @@ def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float1
     return out
 
 
+# flow-head gather inside the next correlation lookup (woft_corr_lookup_gather): bit-identical, 12 launches fewer per frame,
+# and measured SLOWER (4.82 vs 4.64 ms per frame): the flow branch of the next iteration then starts behind the lookup
+# instead of beside it, and its 7x7 kernel finds the SMs taken by convc1's one-CTA-per-SM launch.  Off by default.
+_FUSE_GATHER = os.environ.get("WOFT_FUSE_GATHER", "0") == "1"
 _TWO_STREAMS = os.environ.get("WOFT_TWO_STREAMS", "1") == "1"   # independent branches of the schedule on a second stream
 _ROW_HALO = os.environ.get("WOFT_ROW_HALO", "0") == "1"   # measured: no gain on the encoders (205.9 vs 208.7 frames/s)
 _STAT_ROWS = 148   # one row of partial sums per CTA of a persistent woft_conv_tc launch (at most one CTA per SM)
@@ -670,13 +674,20 @@ class FastWeightedRAFT:
         e = self.net.update_block.encoder
         main = torch.cuda.current_stream(h.device)
         side = self._side_stream(h.device) if _TWO_STREAMS else main
+        corr = None
+        if st.get("pending_gather"):
+            # the previous iteration left its flow-head taps ungathered: this lookup sums them, advances the coordinates
+            # and writes the new flow first (woft_corr_lookup_gather), so the flow branch starts behind it
+            corr = lookup(self._gather_args(st, True))
+            st["pending_gather"] = False
         if side is not main:
             side.wait_stream(main)
         with torch.cuda.stream(side):
             flo = flow_conv7x7_relu_f16(st["flow"], e.convf1.weight, e.convf1.bias, out=st.get("flo"))
             st["flo"] = flo
             conv_tc.run(tc["convf2"], flo, relu=True, out=cf, out_off=tc["convc2"].cout)
-        corr = lookup()
+        if corr is None:
+            corr = lookup(None)
         conv_tc.run(tc["convc1"], corr, relu=True, out=st["cor1"])
         conv_tc.run(tc["convc2"], st["cor1"], relu=True, out=cf)                        # cf = [cor (192) | flo (64)]
         if side is not main:
@@ -692,13 +703,34 @@ class FastWeightedRAFT:
         # flow head: conv1 + ReLU + the 18 tap products of conv2 in one launch (reads the h slice of buf1), then the gather
         # that sums the shifted products, advances the coordinates and writes the flow where the next iteration reads it
         conv_tc.run(tc["fh1"], buf1, epilogue=_lib.CONV_FLOW_TAPS, w1x1=self.fh2, head_out=st["taps"])
+        if _FUSE_GATHER:
+            st["pending_gather"] = True   # the next lookup does it (or _flush_gather after the last iteration)
+        else:
+            self._flush_gather(st, True)
+
+    def _gather_args(self, st, write_operands):
+        """Arguments of the flow head's gather for CorrBlock.__call__(gather=...); `write_operands`: also write the fp16
+        flow into the two GRU operand buffers (not needed once the iterations are over)."""
+        buf1, buf2 = st["buf1h"], st["buf2h"]
+        off = st["C"] + st["ci"] + self.tc["conv"].cout
+        g = dict(taps=st["taps"], bias=self.fh2_bias, coords0=st["coords0"], flow_nchw=st["flow"], flow_nhwc=st["flow_cl"])
+        if write_operands:
+            g.update(f16_a=buf1, f16_b=buf2, f16_stride=buf1.shape[1], f16_offset=off)
+        return g
+
+    def _flush_gather(self, st, write_operands=False):
+        """The gather as its own launch (woft_flow_head_gather)."""
+        buf1, buf2, h = st["buf1h"], st["buf2h"], st["h"]
         B, _, H, W = buf1.shape
+        off = st["C"] + st["ci"] + self.tc["conv"].cout
         with torch.cuda.device(h.device):
             rc = _lib.load().woft_flow_head_gather(_lib.ptr(st["taps"]), _lib.ptr(self.fh2_bias), B, H, W, None,
                                                    _lib.ptr(st["coords1"]), _lib.ptr(st["coords0"]), _lib.ptr(st["flow"]),
-                                                   _lib.ptr(st["flow_cl"]), _lib.ptr(buf1), _lib.ptr(buf2), buf1.shape[1],
-                                                   C + ci + tc["conv"].cout, _lib.current_stream(h.device))
+                                                   _lib.ptr(st["flow_cl"]), _lib.ptr(buf1 if write_operands else None),
+                                                   _lib.ptr(buf2 if write_operands else None), buf1.shape[1], off,
+                                                   _lib.current_stream(h.device))
         _lib.check(rc, "woft_flow_head_gather")
+        st["pending_gather"] = False
 
     def _mask_own(self, st):
         """The upsampling-mask head (update.py:122-125, 135) on the final hidden state."""
@@ -828,7 +860,7 @@ class FastWeightedRAFT:
             last = it == iters - 1
             if nhwc and self.own_convs:
                 coords1 = state["coords1"]  # advanced in place by the flow head's last kernel
-                self._update_own(state, lambda: corr_fn(coords1, flags=lookup_flags | 16))
+                self._update_own(state, lambda g: corr_fn(coords1, flags=lookup_flags | 16, gather=g))
                 if last and _TWO_STREAMS:   # the mask head runs beside the last lookup and the weight head
                     main, side = torch.cuda.current_stream(image1.device), self._side_stream(image1.device)
                     side.wait_stream(main)
@@ -846,12 +878,20 @@ class FastWeightedRAFT:
                 corr = corr_fn(coords1)
                 net, up_mask, dflow = self._update(net, inp, corr, coords1 - coords0, need_mask=last)
                 coords1 = coords1 + dflow
-        flow_low = coords1 - coords0
+        pending = bool(state is not None and state.get("pending_gather"))
+        if pending and not self.with_weights:
+            self._flush_gather(state)
         if not self.with_weights:
+            flow_low = coords1 - coords0
             if mask_join:
                 mask_join[0].wait_stream(mask_join[1])
             return flow_low, convex_upsample_both(flow_low, None, up_mask)[0]
-        window = corr_fn(coords1, flags=lookup_flags) if nhwc else corr_fn(coords1)
+        if pending:   # the weight head's window lookup gathers the last iteration's taps first
+            window = corr_fn(coords1, flags=lookup_flags, gather=self._gather_args(state, False))
+            state["pending_gather"] = False
+        else:
+            window = corr_fn(coords1, flags=lookup_flags) if nhwc else corr_fn(coords1)
+        flow_low = coords1 - coords0
         if nhwc and self.own_head and tuple(window.shape[1:2]) == (324,):
             weights = self._weights_own(window, corr_fn.mean_response())
         else:

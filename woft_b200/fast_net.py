@@ -257,6 +257,7 @@ def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float1
 # and measured SLOWER (4.82 vs 4.64 ms per frame): the flow branch of the next iteration then starts behind the lookup
 # instead of beside it, and its 7x7 kernel finds the SMs taken by convc1's one-CTA-per-SM launch.  Off by default.
 _FUSE_GATHER = os.environ.get("WOFT_FUSE_GATHER", "0") == "1"
+_CTX_STREAM = os.environ.get("WOFT_CTX_STREAM", "1") == "1"   # context encoder beside the feature encoder
 _TWO_STREAMS = os.environ.get("WOFT_TWO_STREAMS", "1") == "1"   # independent branches of the schedule on a second stream
 _ROW_HALO = os.environ.get("WOFT_ROW_HALO", "0") == "1"   # measured: no gain on the encoders (205.9 vs 208.7 frames/s)
 _STAT_ROWS = 148   # one row of partial sums per CTA of a persistent woft_conv_tc launch (at most one CTA per SM)
@@ -836,6 +837,15 @@ class FastWeightedRAFT:
         if corr_block is None:
             from .corr import CorrBlock as corr_block
         image1 = images[:images.shape[0] // 2]
+        # the context encoder needs nothing from the feature encoder or the correlation: on the second stream its
+        # tensor-core convolutions fill the feature encoder's normalisation passes and vice versa (WOFT_CTX_STREAM)
+        ctx_early, ctx_join = None, None
+        if _CTX_STREAM and _TWO_STREAMS and self.nhwc and self.own_encoders:
+            main, side = torch.cuda.current_stream(images.device), self._side_stream(images.device)
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                ctx_early = self._context_tc(image1)
+            ctx_join = (main, side)
         fmap1, fmap2 = self._features(images).chunk(2, dim=0)
         if not (self.nhwc and os.environ.get("WOFT_NHWC_FMAPS", "1") == "1"
                 and (corr_block is _CorrBlock or getattr(corr_block, "func", None) is _CorrBlock)):
@@ -849,8 +859,14 @@ class FastWeightedRAFT:
             coords1 = coords1 + flow_init
         up_mask, mask_join = None, None
         lookup_flags = 8 if nhwc else 0
+        if ctx_join:
+            ctx_join[0].wait_stream(ctx_join[1])
+            for t in ctx_early:
+                if torch.is_tensor(t):
+                    t.record_stream(ctx_join[0])
         if nhwc:
-            ctx = self._context_tc(image1) if self.own_encoders else self._context(image1, raw_tail=True)
+            ctx = ctx_early if ctx_early is not None else (
+                self._context_tc(image1) if self.own_encoders else self._context(image1, raw_tail=True))
             state = self._nhwc_state(*ctx, coords0, coords1)
         else:
             net, inp = torch.split(self._context(image1), [net_.hidden_dim, net_.context_dim], dim=1)

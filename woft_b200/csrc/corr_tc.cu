@@ -500,10 +500,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
 
       float hs[16];      // horizontal pair sums of the even row
       float l1[4][16];   // level-1 rows of this tile
+      // the TMEM read of the next patch row is in flight while this one is staged, fenced, synchronised and stored
+      uint32_t ra[32], rb[32];
+      ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN), ra);
 #pragma unroll
       for (int r = 0; r < TH; ++r) {
         float v[32];
-        ptx::tmem_ld_32x32(tmem_base + lane_base + uint32_t(buf * BN + r * TW), v);
+        if ((r & 1) == 0) {
+          ptx::tmem_ld_32x32_wait(ra);
+          if (r + 1 < TH) ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN + (r + 1) * TW), rb);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(ra[j]);
+        } else {
+          ptx::tmem_ld_32x32_wait(rb);
+          if (r + 1 < TH) ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN + (r + 1) * TW), ra);
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rb[j]);
+        }
         if (r == TH - 1) {  // accumulator fully read: hand it back to the MMA warp
           ptx::tc_fence_before_sync();
           ptx::mbar_arrive(tempty + buf);

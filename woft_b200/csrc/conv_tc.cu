@@ -16,14 +16,18 @@
 // matrix, repacked once on the host to [tap][Cout][Cin] (rounded to tf32 / fp16).  The accumulator (128 pixels x up to
 // 256 output channels, fp32) lives in TMEM across all taps and channel blocks: K = taps * Cin.
 //
-// Warp roles (320 threads, persistent CTAs over tiles), as in corr_tc.cu: warp 0 TMA producer, warp 1 MMA issuer (two
+// Warp roles (384 threads, persistent CTAs over tiles), as in corr_tc.cu: warp 0 TMA producer, warp 1 MMA issuer (two
 // accumulators in TMEM, so tile i+1 multiplies while tile i drains), warps 2-9 epilogue (one output pixel per thread,
-// 32 channels per tcgen05.ld, the two warps of a TMEM lane quadrant taking alternate chunks).  Epilogues:
+// 32 channels per tcgen05.ld, the two warps of a TMEM lane quadrant taking alternate chunks), warps 10-11 two more TMA
+// producers for launches whose CTAs own several tiles (the k-steps are dealt round-robin: one issuing thread's dependent
+// instruction latency, not memory, bounds the k-step rate of a narrow tile).  Such launches with a filter tile of at
+// most 128 channels take two pixel tiles per k-step (M = 256 per CTA, one filter tile for eight MMAs).  Epilogues:
 //   BIAS_ACT  y = scale * act(acc + bias), fp32 or fp16, to one or two (strided) destinations -- writing straight into
 //             the concatenation buffers of the next layer (torch.cat at update.py:96-97, 129 disappears)
 //   GRU_ZR    z = sigmoid(acc[:, :C] + bz) -> z;  r*h = sigmoid(acc[:, C:] + br) * h -> the q convolution's input
 //   GRU_Q     h' = (1 - z) * h + z * tanh(acc + bq), written over h
 //   HEAD_MEAN relu(acc + bias) . w1x1, averaged over the 81 pixels of each 9x9 patch image (+ b1x1): the weight logit
+//   FLOW_TAPS relu(acc + bias) times the second flow-head layer's 18 (tap, output) filters: per-pixel tap products
 // Every mbarrier wait is bounded (2 s) and raises a status word instead of hanging (woft_conv_tc_check).
 //
 // Work per launch at 1280x720 (14 400 pixels): 2 * 14400 * taps * Cin * Cout flop; the 1x5 GRU gate pair
@@ -546,7 +550,6 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
     if (ptx::elect_one()) {
       bool alive = true;
       if (p.halo) {
-        {
         // two rings, filled in the order the MMA warp drains them: the activation box of a channel block, then the
         // filters of every tap for that block
         int stage = 0;
@@ -583,7 +586,6 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
             }
           }
         }
-        }
       } else {
         const int np = p.producers, stages = p.stages, k_chunks = p.k_chunks, k_elems = p.k_elems, stride = p.stride;
         const int a_stage = p.a_stage, b_bytes = p.b_bytes;
@@ -607,25 +609,23 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
               alive = false;
               break;
             }
-            {
-              if (PAIR) {
-                // both CTAs' bytes are counted on the LEADER's barrier, which the leader arms with the sum.  The peer does
-                // not arrive (a remote release-arrive per stage paced the whole pipeline at 0.74 us per step): its bytes may
-                // land before the leader has armed the phase, which only drives the pending count negative for a while --
-                // the phase cannot complete before the leader's arrival, and the peer cannot reach the next use of this
-                // stage before the leader's MMAs have drained it
-                const uint32_t lead_full = ptx::mapa(full + stage, 0);
-                if (rank == 0) ptx::mbar_arrive_expect_tx(full + stage, 2u * uint32_t(p.a_bytes + b_bytes));
-                ptx::tma_load_4d_2sm(sA + stage * a_stage, &p.tmA, lead_full, kc * k_elems, xs, ys, tc.n);
-                ptx::tma_load_3d_2sm(sB + stage * b_bytes, &p.tmB, lead_full, kc * k_elems, tc.c0 + int(rank) * (p.bn >> 1), tap);
-              } else {
-                ptx::mbar_arrive_expect_tx(full + stage, tx);
-                if (load_a) ptx::tma_load_4d(sA + stage * a_stage, &p.tmA, full + stage, kc * k_elems, xs, ys, tc.n);
-                if (load_a && mt2)
-                  ptx::tma_load_4d(sA + stage * a_stage + CT_A_STAGE, &p.tmA, full + stage, kc * k_elems, xb2 + p.dx[tap],
-                                   yb2 + p.dy[tap], tc2.n);
-                if (load_b) ptx::tma_load_3d(sB + stage * b_bytes, &p.tmB, full + stage, kc * k_elems, tc.c0, tap);
-              }
+            if (PAIR) {
+              // both CTAs' bytes are counted on the LEADER's barrier, which the leader arms with the sum.  The peer does
+              // not arrive (a remote release-arrive per stage paced the whole pipeline at 0.74 us per step): its bytes may
+              // land before the leader has armed the phase, which only drives the pending count negative for a while --
+              // the phase cannot complete before the leader's arrival, and the peer cannot reach the next use of this
+              // stage before the leader's MMAs have drained it
+              const uint32_t lead_full = ptx::mapa(full + stage, 0);
+              if (rank == 0) ptx::mbar_arrive_expect_tx(full + stage, 2u * uint32_t(p.a_bytes + b_bytes));
+              ptx::tma_load_4d_2sm(sA + stage * a_stage, &p.tmA, lead_full, kc * k_elems, xs, ys, tc.n);
+              ptx::tma_load_3d_2sm(sB + stage * b_bytes, &p.tmB, lead_full, kc * k_elems, tc.c0 + int(rank) * (p.bn >> 1), tap);
+            } else {
+              ptx::mbar_arrive_expect_tx(full + stage, tx);
+              if (load_a) ptx::tma_load_4d(sA + stage * a_stage, &p.tmA, full + stage, kc * k_elems, xs, ys, tc.n);
+              if (load_a && mt2)
+                ptx::tma_load_4d(sA + stage * a_stage + CT_A_STAGE, &p.tmA, full + stage, kc * k_elems, xb2 + p.dx[tap],
+                                 yb2 + p.dy[tap], tc2.n);
+              if (load_b) ptx::tma_load_3d(sB + stage * b_bytes, &p.tmB, full + stage, kc * k_elems, tc.c0, tap);
             }
             stage += np;
             if (stage >= stages) {
@@ -658,58 +658,56 @@ __global__ void __launch_bounds__(CT_THREADS, 1) conv_tc_kernel(const __grid_con
       uint32_t phase = 0;
       bool alive = true;
       if (p.halo) {
-        {
-          int a_st = 0;
-          uint32_t a_ph = 0;
-          for (int it = 0; alive && it < my_tiles; ++it) {
-            const int buf = it & 1;
-            const uint32_t use = uint32_t(it >> 1);
-            if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
-            ptx::tc_fence_after_sync();
-            const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
-              const int groups = p.halo == 2 ? p.kw : 1, tpg = p.taps / groups;
-              for (int kg = 0; kg < p.k_chunks * groups && alive; ++kg) {
-                const int g = kg % groups;
-                if (!ct_wait(a_full + a_st, a_ph)) {
-                  alive = false;
-                  break;
-                }
-                const uint32_t a_base = ptx::smem_u32(sA + a_st * p.a_stage);
-                for (int i = 0; i < tpg; ++i) {
-                  const int tap = p.halo == 2 ? i * p.kw + g : i;
-                  if (!ct_wait(full + stage, phase)) {
-                    alive = false;
-                    break;
-                  }
-                  ptx::tc_fence_after_sync();
-                  if (kg == 0 && i == 0 && it == 0) ct_stamp(p, 2);
-                  // the tap's operand is the same box read from tap_row[tap] rows further in: the 128-byte swizzle is a
-                  // function of the shared-memory address, so a descriptor may start on any row of the tile
-                  const uint64_t da = ct_desc(a_base + uint32_t(p.tap_row[tap]) * 128u);
-                  const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
-    #pragma unroll
-                  for (int k = 0; k < 4; ++k) {
-                    const uint32_t acc = (kg > 0 || i > 0 || k > 0) ? 1u : 0u;
-                    if (F16)
-                      ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-                    else
-                      ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
-                  }
-                  ptx::mma_commit(empty + stage);
-                  if (++stage == p.stages) {
-                    stage = 0;
-                    phase ^= 1u;
-                  }
-                }
-                if (alive) ptx::mma_commit(a_empty + a_st);   // every MMA reading this activation box has been issued
-                if (++a_st == p.a_stages) {
-                  a_st = 0;
-                  a_ph ^= 1u;
-                }
+        int a_st = 0;
+        uint32_t a_ph = 0;
+        for (int it = 0; alive && it < my_tiles; ++it) {
+          const int buf = it & 1;
+          const uint32_t use = uint32_t(it >> 1);
+          if (!ct_wait(tempty + buf, (use & 1u) ^ 1u)) break;
+          ptx::tc_fence_after_sync();
+          const uint32_t d_tmem = tmem_base + uint32_t(buf * 256);
+          const int groups = p.halo == 2 ? p.kw : 1, tpg = p.taps / groups;
+          for (int kg = 0; kg < p.k_chunks * groups && alive; ++kg) {
+            const int g = kg % groups;
+            if (!ct_wait(a_full + a_st, a_ph)) {
+              alive = false;
+              break;
+            }
+            const uint32_t a_base = ptx::smem_u32(sA + a_st * p.a_stage);
+            for (int i = 0; i < tpg; ++i) {
+              const int tap = p.halo == 2 ? i * p.kw + g : i;
+              if (!ct_wait(full + stage, phase)) {
+                alive = false;
+                break;
               }
-              if (alive) ptx::mma_commit(tfull + buf);
-              if (it == 0) ct_stamp(p, 3);
+              ptx::tc_fence_after_sync();
+              if (kg == 0 && i == 0 && it == 0) ct_stamp(p, 2);
+              // the tap's operand is the same box read from tap_row[tap] rows further in: the 128-byte swizzle is a
+              // function of the shared-memory address, so a descriptor may start on any row of the tile
+              const uint64_t da = ct_desc(a_base + uint32_t(p.tap_row[tap]) * 128u);
+              const uint64_t db = ct_desc(ptx::smem_u32(sB + stage * p.b_bytes));
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint32_t acc = (kg > 0 || i > 0 || k > 0) ? 1u : 0u;
+                if (F16)
+                  ptx::mma_f16(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+                else
+                  ptx::mma_tf32(d_tmem, da + uint64_t(2 * k), db + uint64_t(2 * k), idesc, acc);
+              }
+              ptx::mma_commit(empty + stage);
+              if (++stage == p.stages) {
+                stage = 0;
+                phase ^= 1u;
+              }
+            }
+            if (alive) ptx::mma_commit(a_empty + a_st);   // every MMA reading this activation box has been issued
+            if (++a_st == p.a_stages) {
+              a_st = 0;
+              a_ph ^= 1u;
+            }
           }
+          if (alive) ptx::mma_commit(tfull + buf);
+          if (it == 0) ct_stamp(p, 3);
         }
       } else {
         // Plain mode.  The issuing thread is latency bound (about 5 cycles per instruction, every one dependent on the

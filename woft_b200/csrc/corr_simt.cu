@@ -158,7 +158,15 @@ __global__ void __launch_bounds__(256) channel_finalize_nhwc_kernel(const float*
   const int b = blockIdx.x;
   for (int c = threadIdx.x; c < C; c += 256) {
     float t = 0.f;
-    for (int s = 0; s < strips; ++s) t += partial[((size_t)b * strips + s) * C + c];
+    int s = 0;
+    for (; s + 7 < strips; s += 8) {   // eight loads in flight, added in strip order (the sum is the same bit for bit)
+      float v[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = __ldg(partial + ((size_t)b * strips + s + k) * C + c);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t += v[k];
+    }
+    for (; s < strips; ++s) t += partial[((size_t)b * strips + s) * C + c];
     mean[(size_t)b * C + c] = t / float(HW);
   }
 }

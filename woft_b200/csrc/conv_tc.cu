@@ -1279,7 +1279,7 @@ extern "C" int woft_conv_tc(const woft_conv_tc_args* a, void* stream) {
   WOFT_REQUIRE(total < (1LL << 31), "woft_conv_tc: too many tiles");
   p.total_tiles = (int)total;
   // pair mode: two CTAs of a cluster share the filter tile, each loading half of its rows (cta_group::2 MMA, M = 256)
-  p.pair = (a->pair && !p.halo && bn % 32 == 0) ? 1 : 0;
+  p.pair = (a->pair && !p.halo && bn % 32 == 0 && !a->stats) ? 1 : 0;   // the statistics are gathered by single CTAs
   p.pix_tiles = p.x_tiles * p.y_tiles * a->batch;
   p.pair_tiles = (p.pix_tiles + 1) / 2 * p.n_tiles;
   p.taps = taps;

@@ -318,14 +318,14 @@ def run_reference(args, rank, world):
               f"evaluates the upsampling-mask head on the last iteration only, the reference on all 12, so the port is "
               f"slightly faster than the reference would be), {cores} threads" + ("" if done == args.steps and warm == args.warmup else
                                     f"; stopped early by the {budget:.0f} s budget (asked {args.steps} steps, {args.warmup} warm-up)"))
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": round(fps, 4), "unit": "frames/s", "n_gpus": args.gpus,
         "steps": done, "warmup": warm, "ms_per_step": round(1e3 * dt / done, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD, "weights": WEIGHTS},
         "cpu_baseline": {"value": round(fps, 4), "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": round(fps, 4), "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}), flush=True)
+        "gpu_launches": 0})
 
 
 def count_launches(torch, step, dev):
@@ -477,7 +477,7 @@ def run_woft(args, rank, world, local):
                                          f"reference's CPU path (oracle/cpu_pipeline.py), first frame discarded as "
                                          f"warm-up, mean of the other {len(rest)}: {sum(rest) / len(rest):.2f} s/frame "
                                          f"on {cores} threads"}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def run_sequences(args, rank, world, local):
@@ -545,7 +545,7 @@ def run_sequences(args, rank, world, local):
     again, _, _, _ = track_sequence(check_seq, args.frames)
     same = float(np.abs(again - merged[check_seq]).max())
     total_frames = n_seq * args.frames
-    print(json.dumps({
+    emit({
         "metric": METRIC if args.workload == "config4" else "tracked frames/s @1920x1080",
         "value": round(total_frames / seconds, 3), "unit": "frames/s", "n_gpus": world,
         "steps": total_frames, "warmup": min(args.warmup, 8), "ms_per_step": round(1e3 * seconds * world / total_frames, 3),
@@ -563,7 +563,12 @@ def run_sequences(args, rank, world, local):
         "e2e": {"value": round(total_frames / seconds, 3), "unit": "frames/s",
                 "h2d_bytes_per_step": HEIGHT * WIDTH * 3, "d2h_bytes_per_step": 48,
                 "api": "woft_b200.tracker.PlanarTracker.track(host uint8 frame) -> 3x3 homography on the host; the timed "
-                       "region is the whole sequence loop (device events), max over ranks"}}), flush=True)
+                       "region is the whole sequence loop (device events), max over ranks"}})
+
+
+def emit(obj):
+    """The one JSON line (main() replaces this with a version that owns the real stdout)."""
+    print(json.dumps(obj), flush=True)
 
 
 def main():
@@ -581,6 +586,20 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-fp32-class", action="store_true", help="skip the second, fp32-class timing of the same workload")
     args = ap.parse_args()
+    # The contract is ONE line on stdout.  Libraries write there too (NCCL prints its version banner on rank 0 when the
+    # environment sets NCCL_DEBUG): file descriptor 1 points at stderr while the benchmark runs and is handed back to
+    # `emit`, which prints the JSON line.
+    sys.stdout.flush()
+    _real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    global emit
+
+    def emit(obj):
+        sys.stdout.flush()
+        os.dup2(_real_stdout, 1)
+        print(json.dumps(obj), flush=True)
+        os.dup2(2, 1)
+
     args.warmup = max(args.warmup, 3) if args.impl == "woft" else args.warmup
     if args.impl == "reference":
         # no process group: rank 0 alone times the CPU path, the other ranks leave at once

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Benchmark of the WOFT per-frame hot path on B200: tracked frames/s at 1280x720.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl woft|reference] [--corr-mode tf32|tf32x3|bf16|fp32]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl woft|reference] [--corr-mode fp16s|fp16|fp16x3|tf32|tf32x3|bf16|fp32]
 
 A step is one tracked frame of BASELINE.json configs[1]: one WeightedRAFT flow + uncertainty pass on a synthetic
 1280x720 frame pair (160x90x256 feature maps, 12 GRU iterations, 13 correlation lookups), the correspondence
@@ -224,7 +224,8 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
         return {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
                 "traffic": traffic.get(key), "us_per_launch": round(t * 1e6, 2), "algorithmic_bytes": bytes_}
 
-    k3 = entry(lookup_bytes, t_lookup_pass, "corr_lookup_f16out")
+    f16_pyr = blk.corr_pyramid[0].element_size() == 2
+    k3 = entry(lookup_bytes, t_lookup_pass, "corr_lookup_f16out_f16pyr" if f16_pyr else "corr_lookup_f16out")
     k3["kernel"] = ("corr_lookup_kernel<4> (K3) as the timed frame runs it: channels-last output stored as fp16 (the operand of "
                     "the tensor-core convc1; 648 B instead of 1296 B written per query -- `algorithmic_bytes` keeps SURVEY.md "
                     "8(d)'s 2904 B per query of the fp32 operator, the bytes this variant really moves are 2256 B per query); "
@@ -246,6 +247,9 @@ def kernel_rooflines(torch, dev, corr_mode, peaks):
     k1["kernel"] = (f"pack + corr_tc_kernel + row-mean (K1+K2), mode {corr_mode}; 106.2 GFLOP; algorithmic bytes = both feature "
                     f"maps in + every level out once in the mode's storage format ({blk.corr_pyramid[0].element_size()} B per value)")
     k1["tflops"] = round(2.0 * (H * W) ** 2 * C / t_build / 1e12, 1)
+    # SURVEY.md 8(d)'s figure for the fp32 operator (both maps in, every level out once as fp32), whatever the storage mode
+    fp32_bytes = 2 * f1.numel() * 4 + sum(l.numel() * 4 for l in blk.corr_pyramid)
+    k1["frac_on_fp32_operator_bytes"] = round(fp32_bytes / t_build / 1e9 / hbm, 4)
     k4 = entry(h_bytes, t_h, "homography_fit_config3")
     k4["kernel"] = "homography_fit_kernel (K4), B=1024 x N=14400, nonhomogeneous"
     k3_nchw = entry(lookup_bytes, t_lookup_nchw, "corr_lookup")
@@ -434,6 +438,8 @@ def run_woft(args, rank, world, local):
         "data": "synthetic",
         "config": {"workload": WORKLOAD,
                    "corr_mode": args.corr_mode, "weights": WEIGHTS,
+                   "corr_storage": ("fp16 operands, fp32 accumulation, every pyramid level stored as fp16 (rounded once)"
+                                    if args.corr_mode == "fp16s" else "pyramid stored as fp32"),
                    "convolutions": "hand-written tcgen05 implicit GEMMs (woft_conv_tc: fp16 operands, fp32 accumulation, fused "
                                    "epilogues) for every wide convolution of both encoders, the update block and the "
                                    "weight head; no cuDNN kernel in this configuration", "cuda_graph": True,
@@ -577,7 +583,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["woft", "reference"], default="woft")
-    ap.add_argument("--corr-mode", default=os.environ.get("WOFT_CORR_MODE", "fp16"),
+    ap.add_argument("--corr-mode", default=os.environ.get("WOFT_CORR_MODE", "fp16s"),
                     choices=["tf32", "tf32x3", "bf16", "fp16", "fp16s", "fp16x3", "fp32"])
     ap.add_argument("--workload", choices=["config2", "config4", "config5"], default="config2",
                     help="config2 (default): the headline frame-pair workload; config4 / config5: 8 sequences x --frames "

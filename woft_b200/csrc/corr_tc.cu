@@ -298,17 +298,25 @@ __device__ __forceinline__ void direct_row(float* level, int lh, int lw, int HW,
 // DEBUG = false is the production instantiation: streamed A tile, 3 operand stages, 3 ring slots, no tracing, all of
 // them compile-time so the role loops stay tight.  DEBUG = true takes stages / slots / the resident-A schedule /
 // the trace buffer from the parameters (experiments described in DESIGN.md 4).
-template <bool DEBUG>
-__global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_constant__ CorrTcParams p) {
+// threads: TMA warp, MMA warp, four epilogue warps per group.  TWO: two epilogue groups -- the instantiation for fp16
+// storage, whose tile is bound by the chain of store events (255 -> 214 us for the call); with the fp32 volume the kernel
+// sits at the HBM write rate and two groups on two-slot rings measured slower (266 -> 317 us), so it keeps one group.
+__host__ __device__ constexpr int tc_threads(bool two) { return two ? TC_THREADS + EPI_THREADS : TC_THREADS; }
+// ring bytes: one group, NSLOT slots; two groups, two slots each + the 8 KB level-2 exchange buffer
+__host__ __device__ constexpr int tc_ring_bytes(bool two, int nslot) { return two ? 4 * SLOT + 8192 : nslot * SLOT; }
+
+template <bool DEBUG, bool TWO = false>
+__global__ void __launch_bounds__(tc_threads(TWO), 1) corr_tc_kernel(const __grid_constant__ CorrTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int STAGES = DEBUG ? p.stages : 3, NSLOT = DEBUG ? p.nslot : 3;
+  constexpr int EPI_GROUPS = TWO ? 2 : 1;
+  const int STAGES = DEBUG ? p.stages : 3, NSLOT = TWO ? 2 : DEBUG ? p.nslot : 3;
   const bool a_resident = DEBUG && p.a_resident;
   const int unit = DEBUG ? p.unit : 1;
   uint8_t* sA = smem;  // streamed: STAGES x 16 KB; resident: k_blocks x 16 KB
   uint8_t* sB = sA + (a_resident ? p.k_blocks : STAGES) * A_STAGE;
   uint8_t* ring = sB + STAGES * B_STAGE;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + NSLOT * SLOT);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(ring + tc_ring_bytes(TWO, NSLOT));
   uint64_t* full = bars;                     // [MAX_STAGES] TMA -> MMA
   uint64_t* empty = bars + MAX_STAGES;       // [MAX_STAGES] MMA -> TMA
   uint64_t* tfull = bars + 2 * MAX_STAGES;   // [2] MMA -> epilogue
@@ -328,7 +336,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(tfull + i, 1);
-      ptx::mbar_init(tempty + i, EPI_THREADS);
+      ptx::mbar_init(tempty + i, EPI_GROUPS * EPI_THREADS);
     }
     ptx::mbar_init(a_full, 1);
     ptx::mbar_init(a_empty, 1);
@@ -471,15 +479,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
         }
       }
     }
-  } else {
+  } else if (warp < 2 + 4 * EPI_GROUPS) {
     // ================================ epilogue ================================
-    const int et = threadIdx.x - 64;              // 0..127
+    // EPI_GROUPS groups of four warps (one warp per TMEM lane quadrant).  A group owns RPG = TH / EPI_GROUPS consecutive
+    // patch rows of every tile -- whole 2x2 and 4x4 pooling cells, so levels 1 and 2 need nothing from the other group --
+    // with its own store ring, named barrier and issuing thread.  The tile costs a chain of store events (TMEM read,
+    // staging, proxy fence, a 128-thread barrier, one TMA store), 11 of them with one group: with half the bytes (fp16
+    // storage) the kernel took the same time, i.e. the chain, not HBM, bounds it; two groups walk 6 events each side by
+    // side.  Only level 3 (one 8x8 cell row per tile) needs both groups' level-2 rows: group 1 hands its row over
+    // through shared memory and a 256-thread barrier, once per tile.
+    constexpr int G = EPI_GROUPS, RPG = TH / G;
+    const int g = (warp - 2) >> 2;
+    const int et = threadIdx.x - 64 - g * EPI_THREADS;   // 0..127 within the group
     const bool issuer = (et == 0);
     const int m = (warp & 3) * 32 + lane;         // TMEM lane == query row of the tile
     const uint32_t lane_base = uint32_t((warp & 3) * 32) << 16;
     const float scale = p.scale;
     const bool f16o = p.out_f16 != 0;
-    uint32_t ev = 0;  // ring event counter (identical in all epilogue threads)
+    const int NS = G == 1 ? NSLOT : 2;            // ring slots of this group
+    uint8_t* gring = ring + g * NS * SLOT;
+    const uint32_t bar_id = 1u + uint32_t(g);
+    float* xchg = reinterpret_cast<float*>(ring + G * NS * SLOT);   // [2][128][8] floats, G == 2 only
+    uint32_t ev = 0;  // ring event counter (identical in all threads of the group)
     int it = 0;
     bool go = true;
     for (int chunk = blockIdx.x; chunk * unit < p.total_tiles && go; chunk += gridDim.x) {
@@ -488,42 +509,44 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
       const TileCoord tc = decode_tile(p, t);
       const int buf = it & 1;
       const uint32_t use = uint32_t(it >> 1);
-      if (issuer) *epi_go = wait_or_abort(tfull + buf, use & 1u, p.abort_flag) ? 1 : 0;
-      ptx::named_bar_sync(1, EPI_THREADS);
-      if (*epi_go == 0) {
+      if (issuer) epi_go[g] = wait_or_abort(tfull + buf, use & 1u, p.abort_flag) ? 1 : 0;
+      ptx::named_bar_sync(bar_id, EPI_THREADS);
+      if (epi_go[g] == 0) {
         go = false;
         break;
       }
-      if (issuer) trace_stamp<DEBUG>(p, it, 4);
+      if (issuer && g == 0) trace_stamp<DEBUG>(p, it, 4);
       ptx::tc_fence_after_sync();
       const int mq = tc.m0 + m;
+      const int r0 = g * RPG;   // first patch row of this group
 
-      float hs[16];      // horizontal pair sums of the even row
-      float l1[4][16];   // level-1 rows of this tile
+      float hs[16];             // horizontal pair sums of the even row
+      float l1[RPG / 2][16];    // level-1 rows of this group
       // the TMEM read of the next patch row is in flight while this one is staged, fenced, synchronised and stored
       uint32_t ra[32], rb[32];
-      ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN), ra);
+      ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN + r0 * TW), ra);
 #pragma unroll
-      for (int r = 0; r < TH; ++r) {
+      for (int rr = 0; rr < RPG; ++rr) {
+        const int r = r0 + rr;
         float v[32];
-        if ((r & 1) == 0) {
+        if ((rr & 1) == 0) {
           ptx::tmem_ld_32x32_wait(ra);
-          if (r + 1 < TH) ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN + (r + 1) * TW), rb);
+          if (rr + 1 < RPG) ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN + (r + 1) * TW), rb);
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(ra[j]);
         } else {
           ptx::tmem_ld_32x32_wait(rb);
-          if (r + 1 < TH) ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN + (r + 1) * TW), ra);
+          if (rr + 1 < RPG) ptx::tmem_ld_32x32_issue(tmem_base + lane_base + uint32_t(buf * BN + (r + 1) * TW), ra);
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(rb[j]);
         }
-        if (r == TH - 1) {  // accumulator fully read: hand it back to the MMA warp
+        if (rr == RPG - 1) {  // this group's rows of the accumulator are read: hand them back to the MMA warp
           ptx::tc_fence_before_sync();
           ptx::mbar_arrive(tempty + buf);
         }
 #pragma unroll
         for (int j = 0; j < 32; ++j) v[j] *= scale;
-        uint8_t* slot = ring + (ev % NSLOT) * SLOT;
+        uint8_t* slot = gring + (ev % NS) * SLOT;
         if (p.tma_ok[0]) {
           if (f16o)
             stage_row_h<32>(slot, m, v);
@@ -535,81 +558,110 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
         } else {
           direct_row<32>(p.level[0], p.lh[0], p.lw[0], p.HW, tc.b, mq, tc.h0 + r, tc.w0, v);
         }
-        ptx::named_bar_sync(1, EPI_THREADS);
+        ptx::named_bar_sync(bar_id, EPI_THREADS);
         if (issuer) {
           if (p.tma_ok[0] && tc.h0 + r < p.lh[0]) ptx::tma_store_4d(&p.tmOut[0], slot, tc.w0, tc.h0 + r, tc.m0, tc.b);
           ptx::tma_store_commit();
-          store_ring_wait(NSLOT);
+          store_ring_wait(NS);
         }
         ++ev;
         // 2x2 mean in avg_pool2d's summation order: ((a00 + a01) + a10) + a11, then * 0.25
-        if ((r & 1) == 0) {
+        if ((rr & 1) == 0) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) hs[j] = v[2 * j] + v[2 * j + 1];
         } else {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) l1[r >> 1][j] = ((hs[j] + v[2 * j]) + v[2 * j + 1]) * 0.25f;
+          for (int j = 0; j < 16; ++j) l1[rr >> 1][j] = ((hs[j] + v[2 * j]) + v[2 * j + 1]) * 0.25f;
         }
       }
 
       if (p.num_levels > 1) {
 #pragma unroll
-        for (int half = 0; half < 2; ++half) {  // level-1 rows {0,1} then {2,3}
-          uint8_t* slot = ring + (ev % NSLOT) * SLOT;
+        for (int half = 0; half < RPG / 4; ++half) {  // level-1 rows in pairs
+          uint8_t* slot = gring + (ev % NS) * SLOT;
 #pragma unroll
           for (int rr = 0; rr < 2; ++rr) {
-            const int r1 = half * 2 + rr;
+            const int i1 = half * 2 + rr;                     // row within the group
+            const int h1 = tc.h0 / 2 + g * (RPG / 2) + i1;    // row of the level-1 map
             if (p.tma_ok[1]) {
               if (f16o)
-                stage_row_h<16>(slot + rr * 8192, m, l1[r1]);
+                stage_row_h<16>(slot + rr * 8192, m, l1[i1]);
               else
-                stage_row<16>(slot + rr * 8192, m, l1[r1]);
+                stage_row<16>(slot + rr * 8192, m, l1[i1]);
             } else if (f16o) {
-              direct_row_h<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, tc.h0 / 2 + r1, tc.w0 / 2, l1[r1]);
+              direct_row_h<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, h1, tc.w0 / 2, l1[i1]);
             } else {
-              direct_row<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, tc.h0 / 2 + r1, tc.w0 / 2, l1[r1]);
+              direct_row<16>(p.level[1], p.lh[1], p.lw[1], p.HW, tc.b, mq, h1, tc.w0 / 2, l1[i1]);
             }
           }
           if (p.tma_ok[1]) {  // (kernel parameter: uniform) no ring event when the level goes out by direct stores
             ptx::fence_proxy_async_smem();
-            ptx::named_bar_sync(1, EPI_THREADS);
+            ptx::named_bar_sync(bar_id, EPI_THREADS);
             if (issuer) {
 #pragma unroll
               for (int rr = 0; rr < 2; ++rr) {
-                const int h1 = tc.h0 / 2 + half * 2 + rr;
+                const int h1 = tc.h0 / 2 + g * (RPG / 2) + half * 2 + rr;
                 if (h1 < p.lh[1]) ptx::tma_store_4d(&p.tmOut[1], slot + rr * 8192, tc.w0 / 2, h1, tc.m0, tc.b);
               }
               ptx::tma_store_commit();
-              store_ring_wait(NSLOT);
+              store_ring_wait(NS);
             }
             ++ev;
           }
         }
       }
       if (p.num_levels > 2) {
-        float l2[2][8], l3[4];
+        float l2[RPG / 4][8], l3[4];
 #pragma unroll
-        for (int i = 0; i < 2; ++i)
+        for (int i = 0; i < RPG / 4; ++i)
 #pragma unroll
           for (int j = 0; j < 8; ++j)
             l2[i][j] = ((l1[2 * i][2 * j] + l1[2 * i][2 * j + 1]) + l1[2 * i + 1][2 * j] + l1[2 * i + 1][2 * j + 1]) * 0.25f;
+        bool have_l3 = false;
+        if (p.num_levels > 3) {
+          if (G == 1) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) l3[j] = ((l2[0][2 * j] + l2[0][2 * j + 1]) + l2[1][2 * j] + l2[1][2 * j + 1]) * 0.25f;
-        uint8_t* slot = ring + (ev % NSLOT) * SLOT;
+            for (int j = 0; j < 4; ++j)
+              l3[j] = ((l2[0][2 * j] + l2[0][2 * j + 1]) + l2[RPG / 4 - 1][2 * j] + l2[RPG / 4 - 1][2 * j + 1]) * 0.25f;
+            have_l3 = true;
+          } else {
+            // group 1's level-2 row goes to group 0, which forms the level-3 row (the 8x8 cell spans both groups); the
+            // exchange buffer alternates with the tile parity: a group cannot be more than one such barrier ahead
+            float* x = xchg + ((it & 1) * BM + m) * 8;
+            if (g == 1) {
 #pragma unroll
-        for (int i = 0; i < 2; ++i) {
+              for (int j = 0; j < 8; j += 4) *reinterpret_cast<float4*>(x + j) = make_float4(l2[0][j], l2[0][j + 1], l2[0][j + 2], l2[0][j + 3]);
+            }
+            ptx::named_bar_sync(3, G * EPI_THREADS);
+            if (g == 0) {
+              float o[8];
+#pragma unroll
+              for (int j = 0; j < 8; j += 4) {
+                const float4 t4 = *reinterpret_cast<const float4*>(x + j);
+                o[j] = t4.x; o[j + 1] = t4.y; o[j + 2] = t4.z; o[j + 3] = t4.w;
+              }
+#pragma unroll
+              for (int j = 0; j < 4; ++j) l3[j] = ((l2[0][2 * j] + l2[0][2 * j + 1]) + o[2 * j] + o[2 * j + 1]) * 0.25f;
+              have_l3 = true;
+            }
+          }
+        }
+        uint8_t* slot = gring + (ev % NS) * SLOT;
+#pragma unroll
+        for (int i = 0; i < RPG / 4; ++i) {
+          const int h2 = tc.h0 / 4 + g * (RPG / 4) + i;
           if (p.tma_ok[2]) {
             if (f16o)
               stage_row_h<8>(slot + i * 4096, m, l2[i]);
             else
               stage_row<8>(slot + i * 4096, m, l2[i]);
           } else if (f16o) {
-            direct_row_h<8>(p.level[2], p.lh[2], p.lw[2], p.HW, tc.b, mq, tc.h0 / 4 + i, tc.w0 / 4, l2[i]);
+            direct_row_h<8>(p.level[2], p.lh[2], p.lw[2], p.HW, tc.b, mq, h2, tc.w0 / 4, l2[i]);
           } else {
-            direct_row<8>(p.level[2], p.lh[2], p.lw[2], p.HW, tc.b, mq, tc.h0 / 4 + i, tc.w0 / 4, l2[i]);
+            direct_row<8>(p.level[2], p.lh[2], p.lw[2], p.HW, tc.b, mq, h2, tc.w0 / 4, l2[i]);
           }
         }
-        if (p.num_levels > 3) {
+        if (have_l3) {   // uniform within a group
           if (p.tma_ok[3])   // never with fp16 storage: a 4-value row is 8 bytes, below TMA's 16-byte granule
             stage_row<4>(slot + 8192, m, l3);
           else if (f16o)
@@ -617,26 +669,26 @@ __global__ void __launch_bounds__(TC_THREADS, 1) corr_tc_kernel(const __grid_con
           else
             direct_row<4>(p.level[3], p.lh[3], p.lw[3], p.HW, tc.b, mq, tc.h0 / 8, tc.w0 / 8, l3);
         }
-        if (p.tma_ok[2] || (p.num_levels > 3 && p.tma_ok[3])) {
+        if (p.tma_ok[2] || (have_l3 && p.tma_ok[3])) {
           ptx::fence_proxy_async_smem();
-          ptx::named_bar_sync(1, EPI_THREADS);
+          ptx::named_bar_sync(bar_id, EPI_THREADS);
           if (issuer) {
             if (p.tma_ok[2]) {
 #pragma unroll
-              for (int i = 0; i < 2; ++i) {
-                const int h2 = tc.h0 / 4 + i;
+              for (int i = 0; i < RPG / 4; ++i) {
+                const int h2 = tc.h0 / 4 + g * (RPG / 4) + i;
                 if (h2 < p.lh[2]) ptx::tma_store_4d(&p.tmOut[2], slot + i * 4096, tc.w0 / 4, h2, tc.m0, tc.b);
               }
             }
-            if (p.num_levels > 3 && p.tma_ok[3] && tc.h0 / 8 < p.lh[3])
+            if (have_l3 && p.tma_ok[3] && tc.h0 / 8 < p.lh[3])
               ptx::tma_store_4d(&p.tmOut[3], slot + 8192, tc.w0 / 8, tc.h0 / 8, tc.m0, tc.b);
             ptx::tma_store_commit();
-            store_ring_wait(NSLOT);
+            store_ring_wait(NS);
           }
           ++ev;
         }
       }
-      if (issuer) trace_stamp<DEBUG>(p, it, 5);
+      if (issuer && g == 0) trace_stamp<DEBUG>(p, it, 5);
     }
     }
     if (issuer) ptx::tma_store_wait_all();
@@ -843,7 +895,11 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
       p.unit = unit;
     }
   }
-  const int smem_bytes = (p.a_resident ? p.k_blocks : p.stages) * A_STAGE + p.stages * B_STAGE + p.nslot * SLOT + fixed;
+  const bool debug = p.a_resident || __atomic_load_n(&g_trace_buffer, __ATOMIC_ACQUIRE) != nullptr || p.stages != 3 ||
+                     p.nslot != 3 || p.unit != 1;
+  const bool two = store_f16 && !debug;   // two epilogue groups (see corr_tc_kernel)
+  const int smem_bytes = (p.a_resident ? p.k_blocks : p.stages) * A_STAGE + p.stages * B_STAGE +
+                         tc_ring_bytes(two, p.nslot) + fixed;
 
   int sms = 0;
   WOFT_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
@@ -853,12 +909,14 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   // debug aid: per-role timestamps of the first 4 CTAs into a buffer the caller handed over beforehand
   // (4 * 64 * 6 unsigned long long, zeroed by the caller); the library itself never allocates
   p.trace = __atomic_load_n(&g_trace_buffer, __ATOMIC_ACQUIRE);
-  const bool debug = p.a_resident || p.trace != nullptr || p.stages != 3 || p.nslot != 3 || p.unit != 1;
   if (debug) {
     WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    corr_tc_kernel<true><<<grid, TC_THREADS, smem_bytes, stream>>>(p);
+    corr_tc_kernel<true><<<grid, tc_threads(false), smem_bytes, stream>>>(p);
+  } else if (two) {
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(corr_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    corr_tc_kernel<false, true><<<grid, tc_threads(true), smem_bytes, stream>>>(p);
   } else {
-    corr_tc_kernel<false><<<grid, TC_THREADS, smem_bytes, stream>>>(p);
+    corr_tc_kernel<false><<<grid, tc_threads(false), smem_bytes, stream>>>(p);
   }
   int rc = launch_status("corr_tc_kernel");
   return rc;

@@ -55,6 +55,10 @@ enum woft_corr_mode {
  * then address __half arrays of the same shapes; read them with woft_corr_lookup flag 32.  A stated-tolerance storage
  * format (relative rounding 2^-11 per stored value), not the reference's fp32 volume. */
 #define WOFT_CORR_STORE_F16 0x200
+/* OR-ed into `mode` (WOFT_CORR_FP16 only, channels a multiple of 64): fmap1 / fmap2 are channels-last fp16 tensors
+ * (B, H, W, C) -- already the K-major fp16 operands of the GEMM, as an fp16 encoder epilogue leaves them -- so the
+ * packing pass disappears.  Values beyond +-65504 must not occur (the packing pass of fp32 maps saturates them). */
+#define WOFT_CORR_FMAPS_F16 0x400
 
 /* Estimators of pytracking/utils/least_squares_H.py served by woft_homography_fit (K4). */
 enum woft_h_method {

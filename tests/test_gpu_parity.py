@@ -142,6 +142,35 @@ def test_fp16_storage_is_the_fp16_mode_rounded_once(shape):
         assert torch.equal(a(coords, flags=flags)[:, :324], b(coords, flags=flags)[:, :324]), flags
 
 
+@pytest.mark.parametrize("mode", ["fp16", "fp16s"])
+def test_corr_block_takes_fp16_feature_maps(mode):
+    """WOFT_CORR_FMAPS_F16: channels-last fp16 maps are the GEMM's operands as they are (no packing pass) -- the volume
+    is the one the same numbers give as fp32 maps, bit for bit; the mean response is formed from the same values."""
+    from woft_b200 import _lib
+    from woft_b200.corr import CorrBlock
+    g = torch.Generator().manual_seed(23)
+    cl = torch.channels_last
+    for (B, C, H, W) in ((1, 256, 24, 40), (2, 64, 17, 23)):
+        f1 = torch.randn((B, C, H, W), generator=g).to(DEV).half().contiguous(memory_format=cl)
+        f2 = torch.randn((B, C, H, W), generator=g).to(DEV).half().contiguous(memory_format=cl)
+        a = CorrBlock(f1.float(), f2.float(), mode=mode)
+        b = CorrBlock(f1, f2, mode=mode)
+        b.check()
+        for la, lb in zip(a.corr_pyramid, b.corr_pyramid):
+            assert torch.equal(la, lb)
+        assert torch.allclose(a.mean_response(), b.mean_response(), atol=1e-6)
+    # other modes and channel counts convert instead (the Python class), the ABI refuses
+    c = CorrBlock(f1, f2, mode="fp16x3")
+    assert torch.allclose(c.corr_pyramid[0], a.corr_pyramid[0].float(), atol=4e-3)   # fp16s: the stored value is rounded
+    lib = _lib.load()
+    lv, keep = _lib.ptr_array(a.corr_pyramid)
+    ws = torch.empty(1 << 22, dtype=torch.uint8, device=DEV)
+    with pytest.raises(AssertionError):
+        _lib.check(lib.woft_corr_pyramid(_lib.ptr(f1), _lib.ptr(f2), B, C, H, W, 4, lv, None, _lib.ptr(ws), 1 << 22,
+                                         _lib.CORR_FP16X3 | _lib.CORR_FMAPS_F16, _lib.current_stream(torch.device(DEV))),
+                   "woft_corr_pyramid")
+
+
 def test_corr_block_rejects_what_the_reference_turns_into_nan():
     from woft_b200.corr import CorrBlock
     f = torch.randn(1, 16, 8, 12, device=DEV)  # coarsest level would be 1x1 -> reference returns NaN

@@ -15,6 +15,7 @@ OK, ERR_INVALID_ARGUMENT, ERR_CUDA, ERR_UNSUPPORTED, ERR_WORKSPACE = range(5)
 CORR_FP32_SIMT, CORR_TF32, CORR_TF32X3, CORR_BF16, CORR_FP16, CORR_FP16X3 = range(6)
 CORR_FMAPS_NHWC = 0x100
 CORR_STORE_F16 = 0x200
+CORR_FMAPS_F16 = 0x400
 H_NONHOMOGENEOUS, H_DLT, H_IRLS_L1, H_IRLS_HUBER = range(4)
 
 CORR_MODES = {"fp32": CORR_FP32_SIMT, "tf32": CORR_TF32, "tf32x3": CORR_TF32X3, "bf16": CORR_BF16, "fp16": CORR_FP16,

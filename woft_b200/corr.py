@@ -53,9 +53,12 @@ class CorrBlock:
         # channels-last feature maps (what the channels-last encoder produces) are packed as they are by the
         # tensor-core modes; anything else is brought to contiguous (B,C,H,W)
         cl = torch.channels_last
-        nhwc = (self.mode != "fp32" and fmap1.dtype == fmap2.dtype == torch.float32 and fmap1.shape[1] > 1
-                and all(t.is_contiguous(memory_format=cl) and not t.is_contiguous() for t in (fmap1, fmap2)))
-        if not nhwc:
+        is_cl = fmap1.shape[1] > 1 and all(t.is_contiguous(memory_format=cl) and not t.is_contiguous() for t in (fmap1, fmap2))
+        nhwc = self.mode != "fp32" and fmap1.dtype == fmap2.dtype == torch.float32 and is_cl
+        # channels-last fp16 maps with C % 64 == 0 ARE the K-major fp16 operands of the single-pass fp16 modes: no packing
+        f16_maps = (self.mode in ("fp16", "fp16s") and fmap1.dtype == fmap2.dtype == torch.float16 and is_cl
+                    and fmap1.shape[1] % 64 == 0)
+        if not (nhwc or f16_maps):
             fmap1, fmap2 = _as_f32c(fmap1), _as_f32c(fmap2)
         B, C, H, W = fmap1.shape
         self.shape = (B, C, H, W)
@@ -70,7 +73,8 @@ class CorrBlock:
             level_dtype = torch.float16 if self.store_f16 else torch.float32
             self.corr_pyramid = [torch.empty((B * H * W, 1, h, w), device=dev, dtype=level_dtype) for h, w in sizes]
             self._row_mean = torch.empty((B, H, W), device=dev, dtype=torch.float32)
-            mode_id = _lib.CORR_MODES[self.mode] | (_lib.CORR_FMAPS_NHWC if nhwc else 0)
+            mode_id = (_lib.CORR_MODES[self.mode] | (_lib.CORR_FMAPS_NHWC if nhwc else 0)
+                       | (_lib.CORR_FMAPS_F16 if f16_maps else 0))
             nbytes = lib.woft_corr_workspace_bytes(B, C, H, W, mode_id)
             self._workspace = torch.empty((nbytes,), device=dev, dtype=torch.uint8)
             levels, keep = _lib.ptr_array(self.corr_pyramid)

@@ -23,7 +23,7 @@ int corr_pyramid_simt(const float*, const float*, int, int, int, int, int, float
 int corr_pyramid_tc(const float*, const float*, int, int, int, int, int, float* const*, void*, int, cudaStream_t);
 size_t corr_tc_workspace_bytes(int, int, int, int);
 void corr_tc_set_trace_buffer(unsigned long long*);
-int launch_row_mean(const float*, const float*, int, int, int, float*, float*, float*, cudaStream_t);
+int launch_row_mean(const float*, const float*, int, int, int, float*, float*, float*, bool, cudaStream_t);
 
 bool pdl_enabled() {
   static const bool on = [] {
@@ -43,7 +43,7 @@ extern "C" const char* woft_last_error(void) { return woft::last_error_buffer();
 
 extern "C" size_t woft_corr_workspace_bytes(int batch, int channels, int height, int width, int mode) {
   if (batch <= 0 || channels <= 0 || height <= 0 || width <= 0) return 0;
-  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16);
+  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16 | WOFT_CORR_FMAPS_F16);
   if (mode == WOFT_CORR_FP32_SIMT) return woft::simt_workspace_bytes(batch, channels);
   return woft::corr_tc_workspace_bytes(batch, channels, height * width, mode);
 }
@@ -56,10 +56,14 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
   WOFT_REQUIRE(batch > 0 && channels > 0 && height > 0 && width > 0, "woft_corr_pyramid: non-positive extent");
   WOFT_REQUIRE(num_levels >= 1 && num_levels <= kMaxLevels, "woft_corr_pyramid: num_levels %d not in [1,%d]",
                num_levels, kMaxLevels);
-  const bool fmaps_nhwc = (mode & WOFT_CORR_FMAPS_NHWC) != 0;
+  const bool fmaps_f16 = (mode & WOFT_CORR_FMAPS_F16) != 0;
+  const bool fmaps_nhwc = (mode & WOFT_CORR_FMAPS_NHWC) != 0 || fmaps_f16;
   const bool store_f16 = (mode & WOFT_CORR_STORE_F16) != 0;
   const int mode_flags = mode;
-  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16);
+  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16 | WOFT_CORR_FMAPS_F16);
+  WOFT_REQUIRE(!fmaps_f16 || (mode == WOFT_CORR_FP16 && channels % 64 == 0 &&
+                              ((reinterpret_cast<uintptr_t>(fmap1) | reinterpret_cast<uintptr_t>(fmap2)) & 15) == 0),
+               "woft_corr_pyramid: fp16 feature maps need mode WOFT_CORR_FP16, channels %% 64 == 0 and 16-byte alignment");
   WOFT_REQUIRE(mode >= WOFT_CORR_FP32_SIMT && mode <= WOFT_CORR_FP16X3, "woft_corr_pyramid: unknown mode %d", mode);
   WOFT_REQUIRE(!((fmaps_nhwc || store_f16) && mode == WOFT_CORR_FP32_SIMT),
                "woft_corr_pyramid: channels-last feature maps and fp16 storage need one of the tensor-core modes");
@@ -90,7 +94,7 @@ extern "C" int woft_corr_pyramid(const float* fmap1, const float* fmap2, int bat
     if (fmaps_nhwc)
       scratch = reinterpret_cast<float*>(static_cast<uint8_t*>(workspace) +
                                          (256 + (size_t)batch * channels * 4 + 1023) / 1024 * 1024);
-    rc = launch_row_mean(fmap1, fmap2, batch, channels, height * width, row_mean, mean2, scratch, s);
+    rc = launch_row_mean(fmap1, fmap2, batch, channels, height * width, row_mean, mean2, scratch, fmaps_f16, s);
   }
   return rc;
 }

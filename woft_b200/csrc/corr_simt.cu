@@ -12,6 +12,8 @@
 //   row_mean kernels   mean over (H2, W2) of level 0 for every query, computed as
 //                      fmap1[:, q] . mean_j fmap2[:, j] / sqrt(C)  (linearity; no re-read of the volume, which
 //                      is what WeightHead.forward does, weighted_raft.py:358-361).
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace woft {
@@ -133,22 +135,27 @@ __global__ void __launch_bounds__(256) row_mean_kernel(const float* __restrict__
 // The kernels for channels-last feature maps (B, HW, C).
 // mean2[b, c] in two steps: per-strip partial sums (a CTA walks its strip of pixels, threads over channels: every pixel
 // is one coalesced row), then one CTA per image adds the strips in a fixed order.
-__global__ void __launch_bounds__(256) channel_partial_nhwc_kernel(const float* __restrict__ f2, float* __restrict__ partial,
+__device__ __forceinline__ float rm_ld(const float* p) { return __ldg(p); }
+__device__ __forceinline__ float rm_ld(const __half* p) { return __half2float(*p); }
+
+// T: float, or __half for maps handed over as fp16 (WOFT_CORR_FMAPS_F16); the sums are fp32 either way
+template <typename T>
+__global__ void __launch_bounds__(256) channel_partial_nhwc_kernel(const T* __restrict__ f2, float* __restrict__ partial,
                                                                    int C, int HW, int strips) {
   const int b = blockIdx.y, strip = blockIdx.x;
   const int len = (HW + strips - 1) / strips;
   const int p0 = strip * len, p1 = min(p0 + len, HW);
   for (int c = threadIdx.x; c < C; c += 256) {
-    const float* src = f2 + ((size_t)b * HW) * C + c;
+    const T* src = f2 + ((size_t)b * HW) * C + c;
     float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
     int p = p0;
     for (; p + 3 < p1; p += 4) {
-      s0 += __ldg(src + (size_t)p * C);
-      s1 += __ldg(src + (size_t)(p + 1) * C);
-      s2 += __ldg(src + (size_t)(p + 2) * C);
-      s3 += __ldg(src + (size_t)(p + 3) * C);
+      s0 += rm_ld(src + (size_t)p * C);
+      s1 += rm_ld(src + (size_t)(p + 1) * C);
+      s2 += rm_ld(src + (size_t)(p + 2) * C);
+      s3 += rm_ld(src + (size_t)(p + 3) * C);
     }
-    for (; p < p1; ++p) s0 += __ldg(src + (size_t)p * C);
+    for (; p < p1; ++p) s0 += rm_ld(src + (size_t)p * C);
     partial[((size_t)b * strips + strip) * C + c] = (s0 + s1) + (s2 + s3);
   }
 }
@@ -172,29 +179,37 @@ __global__ void __launch_bounds__(256) channel_finalize_nhwc_kernel(const float*
 }
 
 // row_mean[b, q]: one warp per query, lanes over channels
-__global__ void __launch_bounds__(256) row_mean_nhwc_kernel(const float* __restrict__ f1, const float* __restrict__ mean2,
+template <typename T>
+__global__ void __launch_bounds__(256) row_mean_nhwc_kernel(const T* __restrict__ f1, const float* __restrict__ mean2,
                                                             float* __restrict__ row_mean, int C, int HW, int B,
                                                             float denom) {
   const long long q = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
   if (q >= (long long)B * HW) return;
   const int b = int(q / HW), lane = threadIdx.x & 31;
-  const float* a = f1 + (size_t)q * C;
+  const T* a = f1 + (size_t)q * C;
   const float* m = mean2 + (size_t)b * C;
   float s = 0.f;
-  for (int c = lane; c < C; c += 32) s = fmaf(__ldg(a + c), __ldg(m + c), s);
+  for (int c = lane; c < C; c += 32) s = fmaf(rm_ld(a + c), __ldg(m + c), s);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane == 0) row_mean[q] = s / denom;
 }
 
 int launch_row_mean(const float* fmap1, const float* fmap2, int B, int C, int HW, float* row_mean, float* mean2,
-                    float* nhwc_scratch, cudaStream_t stream) {
+                    float* nhwc_scratch, bool f16, cudaStream_t stream) {
   if (nhwc_scratch) {   // channels-last maps; scratch holds strips * B * C floats (strips = min(128, HW / 2))
     const int strips = HW / 2 < 128 ? (HW / 2 > 0 ? HW / 2 : 1) : 128;
-    channel_partial_nhwc_kernel<<<dim3(strips, B), 256, 0, stream>>>(fmap2, nhwc_scratch, C, HW, strips);
-    channel_finalize_nhwc_kernel<<<B, 256, 0, stream>>>(nhwc_scratch, mean2, C, HW, strips);
-    row_mean_nhwc_kernel<<<(unsigned)(((long long)B * HW + 7) / 8), 256, 0, stream>>>(fmap1, mean2, row_mean, C, HW, B,
-                                                                                     sqrtf(float(C)));
+    const unsigned rows = (unsigned)(((long long)B * HW + 7) / 8);
+    if (f16) {
+      const __half *h1 = reinterpret_cast<const __half*>(fmap1), *h2 = reinterpret_cast<const __half*>(fmap2);
+      channel_partial_nhwc_kernel<__half><<<dim3(strips, B), 256, 0, stream>>>(h2, nhwc_scratch, C, HW, strips);
+      channel_finalize_nhwc_kernel<<<B, 256, 0, stream>>>(nhwc_scratch, mean2, C, HW, strips);
+      row_mean_nhwc_kernel<__half><<<rows, 256, 0, stream>>>(h1, mean2, row_mean, C, HW, B, sqrtf(float(C)));
+    } else {
+      channel_partial_nhwc_kernel<float><<<dim3(strips, B), 256, 0, stream>>>(fmap2, nhwc_scratch, C, HW, strips);
+      channel_finalize_nhwc_kernel<<<B, 256, 0, stream>>>(nhwc_scratch, mean2, C, HW, strips);
+      row_mean_nhwc_kernel<float><<<rows, 256, 0, stream>>>(fmap1, mean2, row_mean, C, HW, B, sqrtf(float(C)));
+    }
     return launch_status("row_mean kernels (channels-last)");
   }
   channel_mean_kernel<<<B * C, 256, 0, stream>>>(fmap2, mean2, HW);

@@ -757,7 +757,8 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
                     float* const* levels, void* workspace, int mode, cudaStream_t stream) {
   const bool fmaps_nhwc = (mode & WOFT_CORR_FMAPS_NHWC) != 0;
   const bool store_f16 = (mode & WOFT_CORR_STORE_F16) != 0;
-  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16);
+  const bool fmaps_f16 = (mode & WOFT_CORR_FMAPS_F16) != 0;   // the maps ARE the packed operands (checked by the caller)
+  mode &= ~(WOFT_CORR_FMAPS_NHWC | WOFT_CORR_STORE_F16 | WOFT_CORR_FMAPS_F16);
   if (num_levels > kMaxTcLevels)
     return fail(WOFT_ERR_UNSUPPORTED, "tensor-core correlation supports at most %d levels (8x32 pooling tile)",
                 kMaxTcLevels);
@@ -772,11 +773,13 @@ int corr_pyramid_tc(const float* fmap1, const float* fmap2, int B, int C, int H,
   const TcLayout L = tc_layout(B, C, HW, mode);
   uint8_t* ws = static_cast<uint8_t*>(workspace);
   int* flag = reinterpret_cast<int*>(ws);
-  void* packA = ws + L.off_a;
-  void* packB = ws + L.off_b;
+  void* packA = fmaps_f16 ? const_cast<float*>(fmap1) : static_cast<void*>(ws + L.off_a);
+  void* packB = fmaps_f16 ? const_cast<float*>(fmap2) : static_cast<void*>(ws + L.off_b);
 
-  // ---- pack both fmaps into K-major planes (also clears the abort flag)
-  if (fmaps_nhwc) {
+  // ---- pack both fmaps into K-major planes (also clears the abort flag; the entry point has cleared it already)
+  if (fmaps_f16) {
+    // channels-last fp16 maps with C % 64 == 0: nothing to do
+  } else if (fmaps_nhwc) {
     const size_t plane_elems = L.plane_bytes / L.elem_bytes, rows = (size_t)B * HW;
     dim3 grid(148 * 8, 2);
     if (mode == WOFT_CORR_BF16)

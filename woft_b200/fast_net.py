@@ -257,6 +257,14 @@ def _conv_f16(pc, x, stride=1, relu=False, residual=None, out_dtype=torch.float1
 # and measured SLOWER (4.82 vs 4.64 ms per frame): the flow branch of the next iteration then starts behind the lookup
 # instead of beside it, and its 7x7 kernel finds the SMs taken by convc1's one-CTA-per-SM launch.  Off by default.
 _FUSE_GATHER = os.environ.get("WOFT_FUSE_GATHER", "0") == "1"
+_F16_FMAPS = os.environ.get("WOFT_F16_FMAPS", "1") == "1"   # fp16 feature maps straight into the fp16 correlation modes
+
+
+def _corr_default_mode():
+    from . import corr
+    return corr.DEFAULT_MODE
+
+
 _CTX_STREAM = os.environ.get("WOFT_CTX_STREAM", "1") == "1"   # context encoder beside the feature encoder
 _TWO_STREAMS = os.environ.get("WOFT_TWO_STREAMS", "1") == "1"   # independent branches of the schedule on a second stream
 _ROW_HALO = os.environ.get("WOFT_ROW_HALO", "0") == "1"   # measured: no gain on the encoders (205.9 vs 208.7 frames/s)
@@ -510,7 +518,7 @@ class FastWeightedRAFT:
                 x = F.relu(x + y)
         return F.conv2d(x, enc.conv2.weight, enc.conv2.bias)
 
-    def _features_tc(self, x):
+    def _features_tc(self, x, f16_out=False):
         """Feature encoder (extractor.py:118-192, instance norm) on woft_conv_tc: fp16 activations, bias-free convolutions
         (a per-channel constant cancels in the norm), the residual tails fused into the norm pass."""
         x = instance_norm_relu_f16(stem_conv7x7_f16(x, self.net.fnet.conv1.weight))
@@ -519,7 +527,7 @@ class FastWeightedRAFT:
             if d["down"] is not None:
                 x = conv_instance_norm_f16(d["down"], x, stride=d["stride"], relu=False)
             x = conv_instance_norm_f16(d["c2"], y, residual=x)              # relu(x + relu(norm(conv2(y))))
-        return _conv_f16(self.enc_f["out"], x, out_dtype=torch.float32)
+        return _conv_f16(self.enc_f["out"], x, out_dtype=torch.float16 if f16_out else torch.float32)
 
     def _context_tc(self, x):
         """Context encoder (batch norm folded into the filters) on woft_conv_tc; returns the last convolution WITHOUT its
@@ -846,9 +854,15 @@ class FastWeightedRAFT:
             with torch.cuda.stream(side):
                 ctx_early = self._context_tc(image1)
             ctx_join = (main, side)
-        fmap1, fmap2 = self._features(images).chunk(2, dim=0)
-        if not (self.nhwc and os.environ.get("WOFT_NHWC_FMAPS", "1") == "1"
-                and (corr_block is _CorrBlock or getattr(corr_block, "func", None) is _CorrBlock)):
+        own_corr = corr_block is _CorrBlock or getattr(corr_block, "func", None) is _CorrBlock
+        nhwc_maps = self.nhwc and os.environ.get("WOFT_NHWC_FMAPS", "1") == "1" and own_corr
+        # single-pass fp16 correlation: the encoder's last convolution writes the fp16 maps the GEMM multiplies (no packing
+        # pass, WOFT_CORR_FMAPS_F16)
+        corr_mode = (getattr(corr_block, "keywords", None) or {}).get("mode") or _corr_default_mode()
+        f16_maps = (nhwc_maps and self.own_encoders and _F16_FMAPS and corr_mode in ("fp16", "fp16s")
+                    and net_.fnet.conv2.out_channels % 64 == 0)
+        fmap1, fmap2 = (self._features_tc(images, f16_out=True) if f16_maps else self._features(images)).chunk(2, dim=0)
+        if not nhwc_maps:
             fmap1, fmap2 = fmap1.contiguous(), fmap2.contiguous()   # this library's CorrBlock takes channels-last maps as is
         corr_fn = corr_block(fmap1, fmap2, num_levels=net_.corr_levels, radius=net_.corr_radius)
         nhwc = self.nhwc and isinstance(corr_fn, _CorrBlock) and net_.hidden_dim == net_.context_dim

@@ -12,6 +12,7 @@
 #include <cuda_fp16.h>
 
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace woft {
 
@@ -206,6 +207,208 @@ __global__ void __launch_bounds__(256, 2) weight_head_conv1_kernel(const float* 
   }
 }
 
+// ---- the same layer on tcgen05 (stacked fp16 output) ------------------------------------------------------------------
+// A tile is 128 consecutive output pixels (TMEM lanes) of the (image, y, x) sequence; K = 45 padded to 64 fp16 = ONE
+// 128-byte K row, so the whole tile is four MMAs (128 x 128 x 16).  The A operand has no tensor to be loaded from -- it is
+// the im2col of 9x9x5 images, the lookup channels re-read as (level, y, x) -- so 256 threads build it in shared memory
+// (two per pixel, each gathering half of the 45 values from the zero-bordered images and writing four swizzled 16-byte
+// pieces); the filters sit in shared memory for the whole kernel.  Against the mma.sync kernel above this reads every
+// input value once per pixel instead of once per (pixel, channel quarter) and leaves the legacy tensor pipe.  Three CTAs
+// per SM (128 TMEM columns and ~57 KB of shared memory each) overlap their gather, MMA and store phases.
+constexpr int kTcRows = 128, kTcImgs = 3, kTcThreads = 256;
+constexpr int kTcSmem = 1024 + 16384 + 16384 + 16384 + kTcImgs * kWhTile * 4 + 4 * kWhCout + 64;
+
+__device__ int g_wh_abort = 0;
+
+__device__ __forceinline__ uint64_t wh_desc(uint32_t saddr) {  // K-major, 128-byte swizzle, 8-row groups 1024 B apart
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
+// offset of im2col column k in a zero-bordered 11 x 11 x 5 image, relative to the pixel's top-left neighbour
+__host__ __device__ constexpr int wh_koff(int k) { return ((k / kWhCin) / 3 * 11 + (k / kWhCin) % 3) * kWhCin + k % kWhCin; }
+
+template <int K0>
+__device__ __forceinline__ void wh_build_half(const float* px, uint8_t* row_base, int r) {
+  // 32 columns K0 .. K0 + 31 of one pixel's im2col row -> four swizzled 16-byte pieces
+#pragma unroll
+  for (int jj = 0; jj < 4; ++jj) {
+    uint32_t w[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = K0 + jj * 8 + 2 * e;
+      const float a = (k < kWhK && px) ? px[wh_koff(k < kWhK ? k : 0)] : 0.f;
+      const float b = (k + 1 < kWhK && px) ? px[wh_koff(k + 1 < kWhK ? k + 1 : 0)] : 0.f;
+      const __half2 h = __floats2half2_rn(a, b);
+      w[e] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    const int j = K0 / 8 + jj;
+    *reinterpret_cast<uint4*>(row_base + ((j ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+__global__ void __launch_bounds__(kTcThreads, 3) weight_head_conv1_tc_kernel(const float* __restrict__ window,
+                                                                             const float* __restrict__ mean_resp,
+                                                                             const float* __restrict__ weight,
+                                                                             const float* __restrict__ bias,
+                                                                             __half* __restrict__ out, int n_img,
+                                                                             int total_tiles) {
+  extern __shared__ uint8_t wh_smem_raw[];
+  uint8_t* smem = wh_smem_raw + ((1024u - (ptx::smem_u32(wh_smem_raw) & 1023u)) & 1023u);
+  uint8_t* sA = smem;                       // 128 pixels x 128 bytes (K = 64 fp16), 128-byte swizzle
+  uint8_t* sB = sA + 16384;                 // 128 output channels x 128 bytes
+  uint8_t* s_stage = sB + 16384;            // 8 warps x 2 KB
+  uint64_t* bar = reinterpret_cast<uint64_t*>(s_stage + 16384);   // 8-byte aligned: everything before is a multiple of 1 KB
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bar + 1);
+  float* s_bias = reinterpret_cast<float*>(bar + 2);
+  float* tiles = s_bias + kWhCout;                                // kTcImgs zero-bordered images
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+  if (tid == 0) {
+    ptx::mbar_init(bar, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) ptx::tmem_alloc(tmem_ptr, 128);
+  for (int i = tid; i < kTcImgs * kWhTile; i += kTcThreads) tiles[i] = 0.f;   // borders stay zero for the whole kernel
+  if (tid < kWhCout) s_bias[tid] = __ldg(bias + tid);
+  // filters: B[n][k] = W[n][ci][tap], k = tap * 5 + ci, K-major rows of 64 fp16 (45 real), swizzled like A
+  for (int i = tid; i < kWhCout * 8; i += kTcThreads) {
+    const int n = i >> 3, j = i & 7;
+    uint32_t w[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float v2[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int k = j * 8 + 2 * e + u;
+        v2[u] = k < kWhK ? __ldg(weight + ((size_t)n * kWhCin + k % kWhCin) * 9 + k / kWhCin) : 0.f;
+      }
+      const __half2 h = __floats2half2_rn(v2[0], v2[1]);
+      w[e] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(sB + n * 128 + ((j ^ (n & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before_sync();
+  __syncthreads();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+  const uint32_t idesc = (1u << 4) | (uint32_t(kWhCout >> 3) << 17) | (uint32_t(128 >> 4) << 24);   // f16 x f16 -> f32
+  const uint64_t da = wh_desc(ptx::smem_u32(sA)), db = wh_desc(ptx::smem_u32(sB));
+  const long long total_rows = (long long)n_img * kWhPix;
+  uint32_t phase = 0;
+
+  for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    const long long row0 = (long long)tile * kTcRows;
+    const int img0 = int(row0 / kWhPix);
+    // ---- the images under this tile: 3 x 81 x 5 values, loads first, then the stores into the bordered images
+    {
+      constexpr int kPer = (kTcImgs * kWhPix * kWhCin + kTcThreads - 1) / kTcThreads;
+      float pv[kPer];
+#pragma unroll
+      for (int u = 0; u < kPer; ++u) {
+        const int i = tid + u * kTcThreads;
+        const int sl = i / (kWhPix * kWhCin), r = i - sl * kWhPix * kWhCin;
+        const int pp = r / kWhCin, ci = r - pp * kWhCin;
+        pv[u] = 0.f;
+        if (i < kTcImgs * kWhPix * kWhCin && img0 + sl < n_img)
+          pv[u] = ci < kWhL ? __ldg(window + ((size_t)(img0 + sl) * kWhPix + pp) * kWhL + ci) : __ldg(mean_resp + img0 + sl);
+      }
+#pragma unroll
+      for (int u = 0; u < kPer; ++u) {
+        const int i = tid + u * kTcThreads;
+        if (i >= kTcImgs * kWhPix * kWhCin) continue;
+        const int sl = i / (kWhPix * kWhCin), r = i - sl * kWhPix * kWhCin;
+        const int pp = r / kWhCin, ci = r - pp * kWhCin;
+        const int y = pp / kWhP, x = pp - y * kWhP;
+        tiles[sl * kWhTile + ((y + 1) * 11 + x + 1) * kWhCin + ci] = pv[u];
+      }
+    }
+    __syncthreads();
+    // ---- im2col row of pixel r, half (tid & 1) of its 64 columns
+    {
+      const int r = tid >> 1;
+      const long long p = row0 + r;
+      const float* px = nullptr;
+      if (p < total_rows) {
+        const int img = int(p / kWhPix), pp = int(p - (long long)img * kWhPix);
+        const int y = pp / kWhP, x = pp - y * kWhP;
+        px = tiles + (img - img0) * kWhTile + (y * 11 + x) * kWhCin;
+      }
+      if (tid & 1)
+        wh_build_half<32>(px, sA + r * 128, r);
+      else
+        wh_build_half<0>(px, sA + r * 128, r);
+    }
+    ptx::fence_proxy_async_smem();
+    __syncthreads();
+    if (warp == 0 && ptx::elect_one()) {
+      ptx::tc_fence_after_sync();
+      ptx::mma_row4<true>(tmem_base, uint32_t(da), uint32_t(db), uint32_t(da >> 32), idesc, 0u);
+      ptx::mma_commit(bar);
+    }
+    // ---- epilogue: two warps per TMEM lane quadrant, two 32-channel chunks each
+    {
+      uint32_t spins = 0;
+      const uint64_t t0 = ptx::globaltimer_ns();
+      while (!ptx::mbar_try_wait(bar, phase)) {
+        if ((++spins & 255u) == 0 && (g_wh_abort != 0 || ptx::globaltimer_ns() - t0 > 2000000000ull)) {
+          g_wh_abort = 1;
+          break;
+        }
+      }
+      phase ^= 1u;
+      ptx::tc_fence_after_sync();
+      const int q = warp & 3, chalf = warp >> 2;
+      uint32_t* sw = reinterpret_cast<uint32_t*>(s_stage + warp * 2048);
+#pragma unroll
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = chalf * 2 + cc;
+        float v[32];
+        ptx::tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + uint32_t(c * 32), v);
+        // lane = pixel row of the quadrant: 32 channels -> 16 words, 4-word pieces XOR-ed by the row
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          uint32_t w[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int ch = j * 8 + 2 * e;
+            const __half2 h = __floats2half2_rn(fmaxf(v[ch] + s_bias[c * 32 + ch], 0.f), fmaxf(v[ch + 1] + s_bias[c * 32 + ch + 1], 0.f));
+            w[e] = *reinterpret_cast<const uint32_t*>(&h);
+          }
+          *reinterpret_cast<uint4*>(sw + lane * 16 + ((j ^ ((lane >> 1) & 3)) << 2)) = make_uint4(w[0], w[1], w[2], w[3]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = (lane >> 2) + 8 * i, piece = lane & 3;
+          const long long p = row0 + q * 32 + r;
+          if (p < total_rows) {
+            const uint4 t4 = *reinterpret_cast<const uint4*>(sw + r * 16 + ((piece ^ ((r >> 1) & 3)) << 2));
+            const int img = int(p / kWhPix), pp = int(p - (long long)img * kWhPix);
+            *reinterpret_cast<uint4*>(out + ((size_t)img * (kWhPix + kWhP) + pp) * kWhCout + c * 32 + piece * 8) = t4;
+          }
+        }
+        __syncwarp();
+      }
+    }
+    // the zero row behind every image that starts in this tile
+    for (int img_s = int((row0 + kWhPix - 1) / kWhPix); img_s < n_img && (long long)img_s * kWhPix < row0 + kTcRows; ++img_s) {
+      uint32_t* z = reinterpret_cast<uint32_t*>(out + ((size_t)img_s * (kWhPix + kWhP) + kWhPix) * kWhCout);
+      for (int i = tid; i < kWhP * kWhCout / 2; i += kTcThreads) z[i] = 0u;
+    }
+    ptx::tc_fence_before_sync();
+    __syncthreads();   // accumulator, A tile and image buffers are free for the next tile
+    ptx::tc_fence_after_sync();
+  }
+  if (warp == 0) ptx::tmem_dealloc(tmem_base, 128);
+}
+
 }  // namespace woft
 
 extern "C" int woft_weight_head_conv1(const float* window_nhwc, const float* mean_response, const float* weight,
@@ -234,6 +437,18 @@ extern "C" int woft_weight_head_conv1_stacked_f16(const float* window_nhwc, cons
                "woft_weight_head_conv1_stacked_f16: built for 9x9 patches, 4 levels and 128 output channels");
   WOFT_REQUIRE(n_images > 0 && n_images * (kWhPix + kWhP) + kWhRows < (1LL << 31),
                "woft_weight_head_conv1_stacked_f16: bad image count");
+  static const bool use_tc = [] {   // WOFT_HEAD_CONV1_TC=0: the mma.sync kernel (TF32 operands) instead of the tcgen05 one
+    const char* e = getenv("WOFT_HEAD_CONV1_TC");
+    return !(e && e[0] == '0');
+  }();
+  if (use_tc && (reinterpret_cast<uintptr_t>(out_stacked_f16) & 15) == 0) {
+    const long long tiles = (n_images * kWhPix + kTcRows - 1) / kTcRows;
+    const int grid = (int)(tiles < 148 * 3 ? tiles : 148 * 3);
+    WOFT_CUDA_CHECK(cudaFuncSetAttribute(weight_head_conv1_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kTcSmem));
+    weight_head_conv1_tc_kernel<<<grid, kTcThreads, kTcSmem, static_cast<cudaStream_t>(stream)>>>(
+        window_nhwc, mean_response, weight, bias, static_cast<__half*>(out_stacked_f16), (int)n_images, (int)tiles);
+    return launch_status("weight_head_conv1_tc_kernel");
+  }
   const long long tiles = (n_images * kWhPix + kWhRows - 1) / kWhRows;
   const int grid = (int)(tiles < 148 * 2 ? tiles : 148 * 2);
   weight_head_conv1_kernel<true><<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(

@@ -135,7 +135,9 @@ void woft_corr_set_trace_buffer(unsigned long long* device_buffer);
  *            NHWC consumer (same values); bit 4 (16, with bit 3) = `out` holds fp16 with the channels of a query padded
  *            to a multiple of 8 (328 for 4 levels of radius 4; the padding is not written): the operand of an fp16
  *            tensor-core convolution, whose TMA loads need 16-byte multiples between pixels; bit 5 (32) = the levels hold
- *            fp16 (written with WOFT_CORR_STORE_F16): interpolation in fp32 as before
+ *            fp16 (written with WOFT_CORR_STORE_F16): interpolation in fp32 as before; levels whose width is a multiple
+ *            of 8 are then read in 16-byte pieces (2-3 loads per 20-byte footprint row instead of 3-4) -- bit 1 (2) keeps
+ *            the 8-byte pieces (testing)
  * Level maps narrower than 2 pixels make the reference return NaN (division by W-1 = 0, utils.py:63-64);
  * this call rejects them with WOFT_ERR_INVALID_ARGUMENT instead.
  */

@@ -140,6 +140,8 @@ def test_fp16_storage_is_the_fp16_mode_rounded_once(shape):
     a.corr_pyramid = [l.float() for l in b.corr_pyramid]   # the same numbers as fp32 levels
     for flags in (0, 1, 8, 24):   # 24: fp16 output, channels padded to 328 (the padding is never written)
         assert torch.equal(a(coords, flags=flags)[:, :324], b(coords, flags=flags)[:, :324]), flags
+    # 16-byte pieces (default where the level width allows) and 8-byte pieces (flag 2) fetch the same values
+    assert torch.equal(b(coords, flags=8), b(coords, flags=8 | 2))
 
 
 @pytest.mark.parametrize("mode", ["fp16", "fp16s"])

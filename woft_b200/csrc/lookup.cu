@@ -30,6 +30,7 @@ struct LookupParams {
   const float* level[kMaxLevels];   // const __half* in the instantiations for fp16 storage (flag 32)
   int lh[kMaxLevels];
   int lw[kMaxLevels];
+  int wide[kMaxLevels];   // fp16 levels only: rows of this level may be read in 16-byte pieces (width % 8 == 0, 16-byte base)
   int num_levels;
   const float* coords;  // (B, 2, H1, W1)
   float* out;           // (B, L*P*P, H1, W1)
@@ -61,6 +62,8 @@ struct LookupGeom {
   static constexpr int WIN = P + 1;
   static constexpr int STRIDE = WIN * WIN + 1;  // odd => lanes (queries) hit distinct banks
   static constexpr int NCHUNK = (WIN + 3 + 3) / 4;  // aligned float4 chunks that cover any WIN-float run
+  static constexpr int NWIDE = (WIN + 7 + 7) / 8;   // aligned 8-value (16-byte fp16) pieces that cover any WIN-value run
+  static constexpr int RAW = 4 * NWIDE > 2 * NCHUNK ? 4 * NWIDE : 2 * NCHUNK;   // 32-bit words of a row kept packed
   static constexpr int ROWS = kLevelsPerPass * kQueriesPerCta * WIN;
   static constexpr int ROWS_PER_THREAD = (ROWS + kLookupThreads - 1) / kLookupThreads;
 };
@@ -158,7 +161,12 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
     __syncthreads();
 
     // ---- load phase: one footprint row per thread and step, all loads issued before any store
-    float vals[G::ROWS_PER_THREAD][VEC ? 4 * G::NCHUNK : WIN];
+    // fp16 levels, vector path: a row stays packed in registers (12 words instead of 16 floats) and is fetched in 16-byte
+    // pieces where the level's width allows -- 2-3 loads per 20-byte row instead of 3-4: every load instruction of a
+    // gather costs the L1 one wavefront per lane
+    constexpr bool HALFV = VEC && sizeof(T) == 2;
+    float vals[HALFV ? 1 : G::ROWS_PER_THREAD][VEC ? 4 * G::NCHUNK : WIN];
+    uint32_t raw[HALFV ? G::ROWS_PER_THREAD : 1][G::RAW];
 #pragma unroll
     for (int j = 0; j < G::ROWS_PER_THREAD; ++j) {
       const int s = tid + j * kLookupThreads;
@@ -172,7 +180,32 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
       const int y = s_y0[sq & (kLevelsPerPass * kQueriesPerCta - 1)] + r;
       const bool row_in = live && y >= 0 && y < H;
       const T* row = reinterpret_cast<const T*>(p.level[lvc]) + ((size_t)(q0 + ql) * H + (row_in ? y : 0)) * W;
-      if (VEC) {
+      if constexpr (HALFV) {
+        const uint16_t* hrow = reinterpret_cast<const uint16_t*>(row);
+#pragma unroll
+        for (int k = 0; k < G::RAW; ++k) raw[j][k] = 0u;
+        if (p.wide[lvc]) {
+          const int xa = x0 & ~7, sh = x0 - xa;
+#pragma unroll
+          for (int k = 0; k < G::NWIDE; ++k) {
+            const int xc = xa + 8 * k;
+            if (row_in && 8 * k < sh + WIN && xc >= 0 && xc < W) {
+              const uint4 c = __ldg(reinterpret_cast<const uint4*>(hrow + xc));
+              raw[j][4 * k] = c.x; raw[j][4 * k + 1] = c.y; raw[j][4 * k + 2] = c.z; raw[j][4 * k + 3] = c.w;
+            }
+          }
+        } else {
+          const int xa = x0 & ~3, sh = x0 - xa;
+#pragma unroll
+          for (int k = 0; k < G::NCHUNK; ++k) {
+            const int xc = xa + 4 * k;
+            if (row_in && 4 * k < sh + WIN && xc >= 0 && xc < W) {
+              const uint2 c = __ldg(reinterpret_cast<const uint2*>(hrow + xc));
+              raw[j][2 * k] = c.x; raw[j][2 * k + 1] = c.y;
+            }
+          }
+        }
+      } else if (VEC) {
         const int xa = x0 & ~3;
         const int sh = x0 - xa;
 #pragma unroll
@@ -200,7 +233,18 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
       if (s >= G::ROWS) continue;
       const int sq = s / WIN, r = s - sq * WIN;
       float* d = win + sq * STRIDE + r * WIN;
-      if (VEC) {
+      if constexpr (HALFV) {
+        const int lvl = lv0 + (sq >> 4);
+        const int sh = s_x0[sq] & (p.wide[lvl < p.num_levels ? lvl : 0] ? 7 : 3);
+#pragma unroll
+        for (int k = 0; k < 2 * G::RAW; ++k) {
+          const int c = k - sh;
+          if (c >= 0 && c < WIN) {
+            const __half_raw hr{(unsigned short)((raw[j][k >> 1] >> (16 * (k & 1))) & 0xffffu)};
+            d[c] = __half2float(__half(hr));
+          }
+        }
+      } else if (VEC) {
         const int sh = s_x0[sq] & 3;  // x0 - (x0 & ~3)
 #pragma unroll
         for (int k = 0; k < 4 * G::NCHUNK; ++k) {
@@ -395,6 +439,7 @@ static int woft::corr_lookup_impl(const float* const* levels, int num_levels, co
     p.lh[l] = h;
     p.lw[l] = w;
     vec = vec && (w % 4 == 0) && ((reinterpret_cast<uintptr_t>(levels[l]) & (f16_levels ? 7 : 15)) == 0);
+    p.wide[l] = (f16_levels && w % 8 == 0 && (reinterpret_cast<uintptr_t>(levels[l]) & 15) == 0 && !(flags & 2)) ? 1 : 0;
     h /= 2;
     w /= 2;
   }

@@ -22,6 +22,8 @@
 // DRAM moves more than that: a 40-byte row at a random offset costs one or two 64-byte sectors pairs.
 #include <cuda_fp16.h>
 
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace woft {
@@ -83,7 +85,11 @@ template <int R, bool VEC, bool NHWC, typename T = float>
 __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __grid_constant__ LookupParams p) {
   using G = LookupGeom<R>;
   constexpr int P = G::P, WIN = G::WIN, STRIDE = G::STRIDE;
-  __shared__ float win[kLevelsPerPass * kQueriesPerCta * STRIDE];
+  // fp16 levels keep their footprints as fp16 in shared memory: half the carve-out leaves the L1 twice the room, and the
+  // pieces of a footprint row depend on the line their first piece brought in (7 CTAs/SM or no-allocate loads, both of which
+  // shrink that room, measured 6 % and 35 % slower)
+  using WT = typename std::conditional<sizeof(T) == 2, __half, float>::type;
+  __shared__ WT win[kLevelsPerPass * kQueriesPerCta * STRIDE];
   __shared__ int s_x0[kLevelsPerPass * kQueriesPerCta], s_y0[kLevelsPerPass * kQueriesPerCta];
   __shared__ float s_ax[kLevelsPerPass * kQueriesPerCta], s_ay[kLevelsPerPass * kQueriesPerCta];
   __shared__ float s_cx[kQueriesPerCta], s_cy[kQueriesPerCta];
@@ -232,7 +238,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
       const int s = tid + j * kLookupThreads;
       if (s >= G::ROWS) continue;
       const int sq = s / WIN, r = s - sq * WIN;
-      float* d = win + sq * STRIDE + r * WIN;
+      WT* d = win + sq * STRIDE + r * WIN;
       if constexpr (HALFV) {
         const int lvl = lv0 + (sq >> 4);
         const int sh = s_x0[sq] & (p.wide[lvl < p.num_levels ? lvl : 0] ? 7 : 3);
@@ -241,7 +247,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
           const int c = k - sh;
           if (c >= 0 && c < WIN) {
             const __half_raw hr{(unsigned short)((raw[j][k >> 1] >> (16 * (k & 1))) & 0xffffu)};
-            d[c] = __half2float(__half(hr));
+            d[c] = WT(__half(hr));
           }
         }
       } else if (VEC) {
@@ -249,11 +255,11 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
 #pragma unroll
         for (int k = 0; k < 4 * G::NCHUNK; ++k) {
           const int c = k - sh;
-          if (c >= 0 && c < WIN) d[c] = vals[j][k];
+          if (c >= 0 && c < WIN) d[c] = WT(vals[j][k]);
         }
       } else {
 #pragma unroll
-        for (int c = 0; c < WIN; ++c) d[c] = vals[j][c];
+        for (int c = 0; c < WIN; ++c) d[c] = WT(vals[j][c]);
       }
     }
     __syncthreads();
@@ -271,12 +277,12 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
         const int slot = pair >> 4, ql = pair & 15;
         const int lvl = lv0 + slot, q = q0 + ql;
         if (lvl >= p.num_levels || q >= p.nq || !active) continue;
-        const float* c = win + pair * STRIDE + y3 * WIN + xo;
+        const WT* c = win + pair * STRIDE + y3 * WIN + xo;
         const float ax = s_ax[pair], ay = s_ay[pair];
         const float bx = 1.f - ax, by = 1.f - ay;
         float h[4];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) h[r] = fmaf(ax, c[r * WIN + 1], bx * c[r * WIN]);
+        for (int r = 0; r < 4; ++r) h[r] = fmaf(ax, float(c[r * WIN + 1]), bx * float(c[r * WIN]));
         const size_t oi = (size_t)q * p.out_stride + (size_t)lvl * P * P + xo * P + y3;
         if (p.out_f16) {
           __half* o = reinterpret_cast<__half*>(p.out) + oi;
@@ -303,15 +309,15 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
         const int slot = pair >> 4, ql = pair & 15;
         const int lvl = lv0 + slot, q = q0 + ql;
         if (lvl >= p.num_levels || q >= p.nq) continue;  // warp-uniform
-        const float* my = win + pair * STRIDE;
+        const WT* my = win + pair * STRIDE;
         const float ax = s_ax[pair], ay = s_ay[pair];
         const float w00 = (1.f - ax) * (1.f - ay), w01 = ax * (1.f - ay), w10 = (1.f - ax) * ay, w11 = ax * ay;
         const size_t oi = (size_t)q * p.out_stride + (size_t)lvl * P * P + lane;
 #pragma unroll
         for (int k = 0; k < ROUNDS; ++k) {
           if (tap_off[k] >= 0) {
-            const float* c = my + tap_off[k];
-            const float r = c[0] * w00 + c[1] * w01 + c[WIN] * w10 + c[WIN + 1] * w11;
+            const WT* c = my + tap_off[k];
+            const float r = float(c[0]) * w00 + float(c[1]) * w01 + float(c[WIN]) * w10 + float(c[WIN + 1]) * w11;
             if (p.out_f16)
               reinterpret_cast<__half*>(p.out)[oi + 32 * k] = __float2half_rn(r);
             else
@@ -327,7 +333,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
       const int q = q0 + ql;
       if (lvl < p.num_levels && q < p.nq) {
         const int b = q / p.hw1, pix = q - b * p.hw1;
-        const float* my = win + (slot * kQueriesPerCta + ql) * STRIDE;
+        const WT* my = win + (slot * kQueriesPerCta + ql) * STRIDE;
         const float ax = s_ax[slot * kQueriesPerCta + ql], ay = s_ay[slot * kQueriesPerCta + ql];
         const float bx = 1.f - ax, by = 1.f - ay;
         float* o = p.out + ((size_t)b * channels + (size_t)lvl * P * P) * p.hw1 + pix;
@@ -341,7 +347,7 @@ __global__ void __launch_bounds__(kLookupThreads, 6) corr_lookup_kernel(const __
           if (r <= r_end) {
             float v[WIN];
 #pragma unroll
-            for (int c = 0; c < WIN; ++c) v[c] = my[r * WIN + c];
+            for (int c = 0; c < WIN; ++c) v[c] = float(my[r * WIN + c]);
 #pragma unroll
             for (int xo = 0; xo < P; ++xo) cur[xo] = fmaf(ax, v[xo + 1], bx * v[xo]);
             if (rr > 0) {
